@@ -1,0 +1,274 @@
+/*
+ * srb_c_api.h — C ABI of libsrb.so: the B200-native scan -> filter -> hash-aggregate / hash-join
+ * operators that sit directly under the StarRocks BE pipeline Operator surface.
+ *
+ * The reference has no FFI for this path: operators are C++ classes linked into starrocks_be
+ * (be/src/exec/pipeline/operator.h:43-344). This ABI is therefore the level one below that surface;
+ * each entry point names the reference interface it stands in for. Host C++ operators that subclass
+ * the mirrored Operator (include/srb/compat/operator.h) and the ctypes test harness are the callers.
+ *
+ * Conventions
+ *  - every function returns an srb_status (values of TStatusCode, gensrc/thrift/StatusCode.thrift:53-83);
+ *    SRB_END_OF_FILE from pull is "done", as Status::EndOfFile is in pipeline_driver.cpp:329.
+ *  - no C++ types, no exceptions, no torch types cross this boundary; plain pointers and sizes only.
+ *  - threading is the reference's: one thread at a time per srb_op (pipeline_driver.cpp:246), different
+ *    ops concurrently. Each op owns its CUDA stream.
+ *  - there is no CPU fallback anywhere behind this ABI: without a CUDA device srb_ctx_create fails.
+ */
+#ifndef SRB_C_API_H
+#define SRB_C_API_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes: TStatusCode (gensrc/thrift/StatusCode.thrift:53-83) --------------------------- */
+typedef int32_t srb_status;
+#define SRB_OK 0
+#define SRB_CANCELLED 1
+#define SRB_NOT_IMPLEMENTED 3
+#define SRB_RUNTIME_ERROR 4
+#define SRB_MEM_LIMIT_EXCEEDED 5
+#define SRB_INTERNAL_ERROR 6
+#define SRB_END_OF_FILE 30
+#define SRB_INVALID_ARGUMENT 33
+
+/* ---- logical types: LogicalType (be/src/types/logical_type.h:27-77), same numeric values -------- */
+#define SRB_TYPE_TINYINT 1
+#define SRB_TYPE_SMALLINT 3
+#define SRB_TYPE_INT 5
+#define SRB_TYPE_BIGINT 7
+#define SRB_TYPE_LARGEINT 9
+#define SRB_TYPE_DOUBLE 11
+#define SRB_TYPE_VARCHAR 17
+#define SRB_TYPE_BOOLEAN 24
+#define SRB_TYPE_VARBINARY 46
+#define SRB_TYPE_DECIMAL32 47
+#define SRB_TYPE_DECIMAL64 48
+#define SRB_TYPE_DECIMAL128 49
+#define SRB_TYPE_DATE 50 /* int32 Julian day, types/date_value.h:113 */
+
+/* where a column's buffers live */
+#define SRB_MEM_HOST 0   /* pageable host memory (std::vector-backed Buffer<T>, column/vectorized_fwd.h:47) */
+#define SRB_MEM_PINNED 1 /* page-locked host memory */
+#define SRB_MEM_DEVICE 2 /* device memory of the ctx's GPU */
+
+/*
+ * One column of a chunk. Layouts are the reference's:
+ *  - FixedLengthColumnBase<T>::get_data() flat T[n]        (column/fixed_length_column_base.h:213)
+ *  - DecimalV3Column<T>: same + precision/scale            (column/decimalv3_column.h:27-59)
+ *  - NullableColumn: data column + uint8 null[n], 1 = null (column/nullable_column.h:23-31)
+ *  - BinaryColumn: bytes + uint32 offsets[n+1]             (column/binary_column.h:34-37)
+ */
+typedef struct srb_column {
+    int32_t type; /* SRB_TYPE_* */
+    int32_t precision;
+    int32_t scale;
+    int32_t mem_kind;        /* SRB_MEM_* */
+    const void* data;        /* T[n_rows]; for VARCHAR/VARBINARY the byte buffer */
+    const uint8_t* nulls;    /* NULL when the column has no null map */
+    const uint32_t* offsets; /* VARCHAR/VARBINARY only: n_rows + 1 entries */
+    int64_t n_bytes;         /* VARCHAR/VARBINARY only: size of the byte buffer */
+} srb_column;
+
+/* Chunk (column/chunk.h:50-318): columns addressed by slot id. */
+typedef struct srb_chunk {
+    int64_t n_rows;
+    int32_t n_cols;
+    const int32_t* slot_ids;
+    const srb_column* cols;
+} srb_chunk;
+
+/* ---- predicates: storage/column_predicate.h:66-84 (PredicateType values) -------------------------- */
+#define SRB_PRED_EQ 1
+#define SRB_PRED_NE 2
+#define SRB_PRED_GT 3
+#define SRB_PRED_GE 4
+#define SRB_PRED_LT 5
+#define SRB_PRED_LE 6
+#define SRB_PRED_IS_NULL 9
+#define SRB_PRED_NOT_NULL 10
+
+/*
+ * One `column <op> constant` predicate (ColumnPredicateCmpBase, storage/column_predicate_cmp.cpp:217-239).
+ * A NULL row never satisfies a comparison (:233-237). Predicates that share or_group != 0 are OR-ed
+ * (DisjunctivePredicates / PredicateTree OR node); the groups and all or_group == 0 predicates are
+ * AND-ed in order (ConjunctivePredicates::evaluate, storage/conjunctive_predicates.cpp:35-52).
+ */
+typedef struct srb_predicate {
+    int32_t slot_id;
+    int32_t op;       /* SRB_PRED_* */
+    int32_t type;     /* SRB_TYPE_* of the column; the literal is already in the column's representation */
+    int32_t or_group; /* 0 = plain conjunct */
+    int64_t lit_lo;   /* literal, low 64 bits (sign-extended into lit_hi for <=64-bit types) */
+    int64_t lit_hi;
+} srb_predicate;
+
+/* ---- scalar expressions: flattened Expr tree (exprs/expr.h, exprs/arithmetic_expr.cpp:66-128) ----- */
+#define SRB_EXPR_SLOT_REF 1
+#define SRB_EXPR_LITERAL 2
+#define SRB_EXPR_CAST 3 /* decimal<->decimal / int->decimal casts that keep or raise the scale */
+#define SRB_EXPR_ADD 4
+#define SRB_EXPR_SUB 5
+#define SRB_EXPR_MUL 6
+
+/*
+ * Node i may only reference nodes < i. Arithmetic on DECIMAL types follows
+ * VectorizedArithmeticExpr::evaluate_checked (exprs/arithmetic_expr.cpp:103-128): a MUL whose children are
+ * both same-scale casts of DECIMAL64 (or DECIMAL32) into DECIMAL128 takes the i64 x i64 -> i128 fast path
+ * (:70-101, never overflows); every other decimal ADD/SUB/MUL runs in the result type with
+ * OverflowMode::OUTPUT_NULL — an overflowing row becomes NULL (exprs/decimal_binary_function.h:94-109).
+ * Integer (INT/BIGINT) arithmetic wraps (exprs/arithmetic_operation.h:127-134).
+ */
+typedef struct srb_expr_node {
+    int32_t op;   /* SRB_EXPR_* */
+    int32_t type; /* result SRB_TYPE_* */
+    int32_t precision;
+    int32_t scale;
+    int32_t lhs;     /* node index; CAST uses lhs only */
+    int32_t rhs;     /* node index or -1 */
+    int32_t slot_id; /* SLOT_REF */
+    int32_t _pad;
+    int64_t lit_lo; /* LITERAL value in the node's own type/scale */
+    int64_t lit_hi;
+} srb_expr_node;
+
+/* ---- aggregation: exec/aggregator.h:256-618, exprs/agg/{sum,avg,count,maxmin}.h -------------------- */
+#define SRB_AGG_SUM 1
+#define SRB_AGG_AVG 2
+#define SRB_AGG_COUNT 3 /* count(expr): non-null rows; arg == -1 is count(*) (exprs/agg/count.h:36-120) */
+#define SRB_AGG_MIN 4
+#define SRB_AGG_MAX 5
+
+typedef struct srb_agg_fn {
+    int32_t fn;  /* SRB_AGG_* */
+    int32_t arg; /* expr node index, -1 for count(*) */
+} srb_agg_fn;
+
+/* TAggregationOp phases as wired by AggregateBlockingNode (exec/aggregate/aggregate_blocking_node.cpp:178-254) */
+#define SRB_AGG_UPDATE_FINALIZE 0  /* single phase: raw rows in, final values out */
+#define SRB_AGG_UPDATE_SERIALIZE 1 /* phase 1: raw rows in, intermediate states out (aggregator.cpp:858) */
+#define SRB_AGG_MERGE_FINALIZE 2   /* phase 2: intermediate states in (aggregator.cpp:871-875), final out */
+#define SRB_AGG_MERGE_SERIALIZE 3
+
+/*
+ * A pipeline fragment scan-filter -> project -> aggregate, fused into one operator. Any stage may be empty:
+ *  n_preds == 0          : no filtering
+ *  n_aggs == 0, n_keys==0: a pure filter operator; pull returns the compacted input columns (Chunk::filter,
+ *                          column/chunk.cpp:302) in `out_slots` order
+ *  n_keys == 0, n_aggs>0 : no-group-by aggregation (Aggregator::compute_single_agg_state, aggregator.cpp:833)
+ */
+typedef struct srb_scan_agg_plan {
+    int32_t n_preds;
+    const srb_predicate* preds;
+    int32_t n_nodes;
+    const srb_expr_node* nodes;
+    int32_t n_keys;
+    const int32_t* key_nodes; /* group-by exprs: node indexes (SLOT_REFs) */
+    int32_t n_aggs;
+    const srb_agg_fn* aggs;
+    int32_t phase;       /* SRB_AGG_* phase */
+    int32_t n_out_slots; /* filter-only mode: columns to emit */
+    const int32_t* out_slots;
+    int64_t group_hint; /* expected number of groups (FE cardinality estimate); 0 = unknown */
+} srb_scan_agg_plan;
+
+/* ---- hash join: exec/hash_joiner.h:169, exec/join_hash_map.h:101-214 -------------------------------- */
+#define SRB_JOIN_INNER 0     /* TJoinOp::INNER_JOIN */
+#define SRB_JOIN_LEFT_SEMI 3 /* TJoinOp::LEFT_SEMI_JOIN */
+
+typedef struct srb_join_plan {
+    int32_t join_type;
+    int32_t n_keys; /* equi-join key pairs; all fixed-width, packed size <= 16 bytes */
+    const int32_t* build_key_slots;
+    const int32_t* probe_key_slots;
+    int32_t n_build_out; /* build-side payload columns gathered for matched rows (late materialisation) */
+    const int32_t* build_out_slots;
+    int32_t n_probe_out;
+    const int32_t* probe_out_slots;
+    int32_t emit_indexes; /* 1: also emit probe_index/build_index UInt32 columns under slots -4 / -3
+                             (HASH_JOIN_PROBE_INDEX_SLOT_ID / HASH_JOIN_BUILD_INDEX_SLOT_ID, column/chunk.h:52-58) */
+    int32_t _pad;
+} srb_join_plan;
+
+/* ---- handles ------------------------------------------------------------------------------------- */
+typedef struct srb_ctx srb_ctx; /* device, streams, scratch pools, optional NCCL communicator */
+typedef struct srb_op srb_op;   /* one operator instance (one driver's operator) */
+
+typedef struct srb_config {
+    int32_t device;         /* CUDA device ordinal */
+    int32_t chunk_size;     /* rows per pulled chunk; RuntimeState::chunk_size(), config.h:776 (4096) */
+    int64_t staging_rows;   /* host-chunk staging batch before a launch (0 = default 4 Mi rows) */
+    int32_t rank;           /* multi-GPU: this process's rank, 0 when single */
+    int32_t world_size;     /* 1 when single */
+    int64_t mem_limit;      /* bytes of device memory this ctx may hold (0 = unlimited) */
+} srb_config;
+
+srb_status srb_ctx_create(const srb_config* cfg, srb_ctx** out);
+void srb_ctx_destroy(srb_ctx* ctx);
+/* message of the last non-OK status returned on this thread ("" if none); never NULL */
+const char* srb_last_error(void);
+/* library/device facts for harnesses: fills n_sms, HBM bytes, compute capability (major*10+minor) */
+srb_status srb_ctx_device_info(srb_ctx* ctx, int32_t* n_sms, int64_t* hbm_bytes, int32_t* sm_arch);
+/* the CUDA stream an op launches on (cudaStream_t as void*), so harnesses can time with events on it */
+void* srb_op_stream(srb_op* op);
+
+/* ---- operators ----------------------------------------------------------------------------------- */
+/* replaces OlapScan predicate evaluation + Project + AggregateBlockingSink/Source (or the streaming pair)
+ * for one driver: be/src/exec/pipeline/scan/olap_chunk_source.cpp:586-624,
+ * pipeline/aggregate/aggregate_blocking_sink_operator.cpp:97-134, aggregate_blocking_source_operator.cpp:47-72 */
+srb_status srb_scan_agg_create(srb_ctx* ctx, const srb_scan_agg_plan* plan, srb_op** out);
+
+/* replaces HashJoinBuildOperator + HashJoinProbeOperator sharing one HashJoiner:
+ * pipeline/hashjoin/hash_join_build_operator.cpp:40-213, hash_join_probe_operator.cpp:55-104.
+ * Build side: srb_op_push_chunk(op,...) then srb_op_set_finishing(op). Probe side: srb_join_probe_* below. */
+srb_status srb_join_create(srb_ctx* ctx, const srb_join_plan* plan, srb_op** out);
+
+/* Operator::push_chunk (operator.h:121). Columns may be HOST/PINNED (staged + copied) or DEVICE (used in place,
+ * must stay valid until the next srb_op_sync / set_finishing). n_rows is not limited to chunk_size. */
+srb_status srb_op_push_chunk(srb_op* op, const srb_chunk* chunk);
+/* Operator::set_finishing (operator.h:66), idempotent */
+srb_status srb_op_set_finishing(srb_op* op);
+/* Operator::has_output / need_input / is_finished (operator.h:95-105): 1 / 0 */
+int32_t srb_op_has_output(srb_op* op);
+int32_t srb_op_need_input(srb_op* op);
+int32_t srb_op_is_finished(srb_op* op);
+/* Operator::pull_chunk (operator.h:118): at most chunk_size rows; buffers are library-owned pinned host memory
+ * valid until the next pull/close on this op. Returns SRB_END_OF_FILE after the last chunk. */
+srb_status srb_op_pull_chunk(srb_op* op, srb_chunk* out);
+/* whole-result variant for harnesses: all remaining rows in one chunk (no chunk_size slicing) */
+srb_status srb_op_pull_all(srb_op* op, srb_chunk* out);
+/* Operator::set_cancelled (operator.h:84) / close (operator.h:92) */
+srb_status srb_op_cancel(srb_op* op);
+void srb_op_close(srb_op* op);
+/* wait for everything this op has enqueued */
+srb_status srb_op_sync(srb_op* op);
+/* rows pushed / rows that passed the predicates / kernels launched so far (RuntimeProfile counters, operator.h:310-327) */
+srb_status srb_op_counters(srb_op* op, int64_t* rows_in, int64_t* rows_selected, int64_t* kernel_launches);
+
+/* probe side of a join op: HashJoinProbeOperator::push_chunk / pull_chunk (hash_join_probe_operator.cpp:79-88).
+ * The probe state is separate from the build operator state so that has_output/need_input keep the reference's
+ * meaning on each side. */
+srb_status srb_join_probe_push_chunk(srb_op* op, const srb_chunk* chunk);
+srb_status srb_join_probe_set_finishing(srb_op* op);
+int32_t srb_join_probe_has_output(srb_op* op);
+int32_t srb_join_probe_need_input(srb_op* op);
+int32_t srb_join_probe_is_finished(srb_op* op);
+srb_status srb_join_probe_pull_chunk(srb_op* op, srb_chunk* out);
+srb_status srb_join_probe_pull_all(srb_op* op, srb_chunk* out);
+
+/* ---- device memory helpers for harnesses (plain cudaMalloc/cudaMemcpy wrappers) ------------------- */
+srb_status srb_device_alloc(srb_ctx* ctx, int64_t bytes, void** out);
+void srb_device_free(srb_ctx* ctx, void* p);
+srb_status srb_pinned_alloc(srb_ctx* ctx, int64_t bytes, void** out);
+void srb_pinned_free(srb_ctx* ctx, void* p);
+srb_status srb_memcpy_h2d(srb_ctx* ctx, void* dst, const void* src, int64_t bytes);
+srb_status srb_memcpy_d2h(srb_ctx* ctx, void* dst, const void* src, int64_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SRB_C_API_H */

@@ -1,0 +1,106 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see orc_arith.h header). extern "C" surface for ctypes.
+#include <string>
+
+#include "orc_agg.h"
+
+namespace orc {
+Result* run_scan_agg(const srb_scan_agg_plan* plan, const srb_chunk* in, int n_threads, int chunk_size);
+Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe);
+void join_build_raw(const void* keys, int width, uint32_t n, uint32_t* bucket_size, uint32_t* first, uint32_t* next);
+int pack_keys_raw(const srb_chunk* ch, const int32_t* slots, int n_keys, void* out16);
+} // namespace orc
+
+static thread_local std::string g_err;
+
+extern "C" {
+
+const char* orc_last_error() { return g_err.c_str(); }
+
+// returns NULL on error
+void* orc_scan_agg(const srb_scan_agg_plan* plan, const srb_chunk* in, int n_threads, int chunk_size) {
+    try {
+        return orc::run_scan_agg(plan, in, n_threads, chunk_size);
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return nullptr;
+    }
+}
+void* orc_join(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe) {
+    try {
+        return orc::run_join(plan, build, probe);
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return nullptr;
+    }
+}
+const srb_chunk* orc_result_chunk(void* r) { return &((orc::Result*)r)->chunk; }
+void orc_result_counters(void* r, int64_t* rows_in, int64_t* rows_selected) {
+    *rows_in = ((orc::Result*)r)->rows_in;
+    *rows_selected = ((orc::Result*)r)->rows_selected;
+}
+void orc_result_free(void* r) { delete (orc::Result*)r; }
+
+// ---- scalar entry points for the golden-vector tests ------------------------------------------------
+int32_t orc_from_date(int y, int m, int d) { return orc::from_date(y, m, d); }
+void orc_to_date(int32_t j, int* y, int* m, int* d) { orc::to_date(j, y, m, d); }
+
+// width: 4, 8, 16; op: SRB_EXPR_ADD/SUB/MUL; values passed as (lo, hi) of a sign-extended int128
+int orc_checked_binop(int width, int op, int64_t alo, int64_t ahi, int64_t blo, int64_t bhi, int64_t* rlo, int64_t* rhi) {
+    orc::int128_t a = ((orc::int128_t)ahi << 64) | (uint64_t)alo, b = ((orc::int128_t)bhi << 64) | (uint64_t)blo, r;
+    bool ov = width == 16 ? orc::checked_binop<orc::int128_t>(op, a, b, &r)
+                          : (width == 8 ? orc::checked_binop<int64_t>(op, a, b, &r) : orc::checked_binop<int32_t>(op, a, b, &r));
+    *rlo = (int64_t)r;
+    *rhi = (int64_t)(r >> 64);
+    return ov;
+}
+void orc_decimal_div_integer(int64_t slo, int64_t shi, int64_t count, int scale, int64_t* rlo, int64_t* rhi) {
+    orc::int128_t s = ((orc::int128_t)shi << 64) | (uint64_t)slo;
+    orc::int128_t r = orc::decimal_div_integer(s, (orc::int128_t)count, scale);
+    *rlo = (int64_t)r;
+    *rhi = (int64_t)(r >> 64);
+}
+void orc_div_round128(int64_t alo, int64_t ahi, int64_t blo, int64_t bhi, int64_t* rlo, int64_t* rhi) {
+    orc::int128_t a = ((orc::int128_t)ahi << 64) | (uint64_t)alo, b = ((orc::int128_t)bhi << 64) | (uint64_t)blo;
+    orc::int128_t r = orc::div_round<orc::int128_t>(a, b);
+    *rlo = (int64_t)r;
+    *rhi = (int64_t)(r >> 64);
+}
+int64_t orc_div_round64(int64_t a, int64_t b) { return orc::div_round<int64_t>(a, b); }
+
+uint32_t orc_join_key_hash32(uint32_t v, uint32_t log_buckets) { return orc::join_key_hash32(v, log_buckets); }
+uint32_t orc_join_key_hash64(uint64_t v, uint32_t log_buckets) { return orc::join_key_hash64(v, log_buckets); }
+uint32_t orc_join_key_hash_bytes(const void* p, int32_t n, uint32_t num_buckets) { return orc::join_key_hash_bytes(p, n, num_buckets); }
+uint32_t orc_calc_bucket_size(uint32_t size) { return orc::calc_bucket_size(size); }
+void orc_join_build_raw(const void* keys, int width, uint32_t n, uint32_t* bucket_size, uint32_t* first, uint32_t* next) {
+    orc::join_build_raw(keys, width, n, bucket_size, first, next);
+}
+int orc_pack_keys(const srb_chunk* ch, const int32_t* slots, int n_keys, void* out16) {
+    try {
+        return orc::pack_keys_raw(ch, slots, n_keys, out16);
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return -1;
+    }
+}
+uint32_t orc_crc_hash_32(const void* p, int32_t n, uint32_t seed) { return orc::crc_hash_32(p, n, seed); }
+uint64_t orc_crc_hash_64(const void* p, int32_t n, uint64_t seed) { return orc::crc_hash_64(p, n, seed); }
+uint64_t orc_phmap_mix8(uint64_t v, int seed) { return orc::phmap_mix8(v, seed); }
+uint64_t orc_hash128_with_seed(int64_t lo, int64_t hi, int seed) {
+    return orc::hash128_with_seed(((orc::int128_t)hi << 64) | (uint64_t)lo, seed);
+}
+uint32_t orc_fnv_hash(const void* p, int32_t n, uint32_t seed) { return orc::fnv_hash(p, n, seed); }
+uint32_t orc_xorshift32(uint32_t x) { return orc::xorshift32(x); }
+// ExchangeSinkOperator HASH_PARTITIONED channel of one fixed-width key (exchange_sink_operator.cpp:581-610,
+// shuffler.h:70-85): FNV-1 over the value bytes from FNV_SEED, then ReduceOp
+uint32_t orc_shuffle_channel(const void* value, int32_t width, uint32_t n_channels) {
+    return orc::reduce_op(orc::fnv_hash(value, width, orc::FNV_SEED), n_channels);
+}
+#if defined(__SSE4_2__)
+// hardware cross-check of the software CRC32C
+uint32_t orc_hw_crc32c_u64(uint32_t crc, uint64_t v) { return (uint32_t)_mm_crc32_u64(crc, v); }
+uint32_t orc_hw_crc32c_u8(uint32_t crc, uint8_t v) { return _mm_crc32_u8(crc, v); }
+int orc_has_hw_crc() { return 1; }
+#else
+int orc_has_hw_crc() { return 0; }
+#endif
+}

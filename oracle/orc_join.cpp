@@ -1,0 +1,172 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see orc_arith.h header).
+// Chained hash join restating:
+//   JoinHashTable::append_chunk (row 0 is a dummy; indices 1-based)   be/src/exec/join_hash_map.cpp:613-642
+//   JoinBuildFunc::prepare / construct_hash_table                     be/src/exec/join_hash_map.tpp:29-91
+//   JoinProbeFunc::lookup_init (first[bucket] gather)                 be/src/exec/join_hash_map.tpp:283-309
+//   JoinHashMap::_do_probe_from_ht (inner-join chain walk)            be/src/exec/join_hash_map.tpp:1066-1143
+//   serialize_fixed_size_key_column (multi-column fixed keys)         be/src/exec/join_hash_map.h:391-406
+//   _probe_output / _build_output (append_selective by index)         be/src/exec/join_hash_map.tpp:534-550,624-640
+#include <stdexcept>
+
+#include "orc_agg.h"
+
+namespace orc {
+
+struct PackedKeys {
+    int width = 0;          // 4, 8 or 16 bytes
+    std::vector<int128_t> k; // zero-extended packed key
+    std::vector<uint8_t> null;
+};
+
+// packs the key columns of `ch` (rows 0..n) column by column at increasing byte offsets (join_hash_map.h:391-406)
+static PackedKeys pack_keys(const srb_chunk& ch, const int32_t* slots, int n_keys) {
+    PackedKeys pk;
+    int total = 0;
+    std::vector<const srb_column*> cols(n_keys);
+    for (int i = 0; i < n_keys; i++) {
+        cols[i] = find_slot(ch, slots[i]);
+        int w = type_width(cols[i]->type);
+        if (w == 0) throw std::runtime_error("join: binary keys not supported");
+        total += w;
+    }
+    pk.width = total <= 4 ? 4 : (total <= 8 ? 8 : 16);
+    if (total > 16) throw std::runtime_error("join: packed key wider than 16 bytes");
+    pk.k.assign(ch.n_rows, 0);
+    pk.null.assign(ch.n_rows, 0);
+    for (int64_t r = 0; r < ch.n_rows; r++) {
+        uint8_t buf[16] = {0};
+        int off = 0;
+        for (int i = 0; i < n_keys; i++) {
+            int w = type_width(cols[i]->type);
+            memcpy(buf + off, (const uint8_t*)cols[i]->data + (size_t)w * r, w);
+            off += w;
+            if (cols[i]->nulls && cols[i]->nulls[r]) pk.null[r] = 1;
+        }
+        memcpy(&pk.k[r], buf, 16);
+    }
+    return pk;
+}
+
+static inline uint32_t bucket_of(const PackedKeys& pk, int128_t key, uint32_t bucket_size, uint32_t log_bucket) {
+    if (pk.width == 4) return join_key_hash32((uint32_t)key, log_bucket);
+    if (pk.width == 8) return join_key_hash64((uint64_t)key, log_bucket);
+    return join_key_hash_bytes(&key, 16, bucket_size); // JoinKeyHash<int128>: crc_hash_32 & (B-1) (join_hash_map.h:310-318)
+}
+
+struct JoinTable {
+    PackedKeys keys; // index i-1 holds build row i
+    std::vector<uint32_t> first, next;
+    uint32_t bucket_size = 0, log_bucket = 0, row_count = 0;
+};
+
+static void build_table(JoinTable& t) {
+    t.row_count = (uint32_t)t.keys.k.size();
+    t.bucket_size = calc_bucket_size(t.row_count + 1);
+    t.log_bucket = (uint32_t)__builtin_ctz(t.bucket_size);
+    t.first.assign(t.bucket_size, 0);
+    t.next.assign((size_t)t.row_count + 1, 0);
+    for (uint32_t i = 1; i < t.row_count + 1; i++) {
+        if (t.keys.null[i - 1]) continue; // null keys are never inserted (tpp:62-72)
+        uint32_t b = bucket_of(t.keys, t.keys.k[i - 1], t.bucket_size, t.log_bucket);
+        t.next[i] = t.first[b];
+        t.first[b] = i;
+    }
+}
+
+static void copy_rows(const srb_column& s, const std::vector<uint32_t>& rows, OutCol& o) {
+    o.type = s.type;
+    o.precision = s.precision;
+    o.scale = s.scale;
+    o.has_nulls = s.nulls != nullptr;
+    for (uint32_t row : rows) {
+        if (s.nulls) o.nulls.push_back(s.nulls[row]);
+        if (is_binary(s.type))
+            o.push_bytes((const char*)s.data + s.offsets[row], s.offsets[row + 1] - s.offsets[row]);
+        else {
+            int w = type_width(s.type);
+            size_t off = o.data.size();
+            o.data.resize(off + w);
+            memcpy(o.data.data() + off, (const uint8_t*)s.data + (size_t)w * row, w);
+        }
+    }
+    if (is_binary(s.type) && o.offsets.empty()) o.offsets.push_back(0);
+}
+
+Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe) {
+    auto* r = new Result();
+    JoinTable t;
+    t.keys = pack_keys(*build, plan->build_key_slots, plan->n_keys);
+    build_table(t);
+    PackedKeys pk = pack_keys(*probe, plan->probe_key_slots, plan->n_keys);
+    if (pk.width != t.keys.width) throw std::runtime_error("join: key width mismatch");
+    std::vector<uint32_t> probe_index, build_index; // build_index is 1-based like the reference's
+    for (int64_t i = 0; i < probe->n_rows; i++) {
+        if (pk.null[i]) continue;
+        uint32_t bi = t.first[bucket_of(pk, pk.k[i], t.bucket_size, t.log_bucket)];
+        bool matched = false;
+        while (bi != 0) {
+            if (t.keys.k[bi - 1] == pk.k[i]) {
+                if (plan->join_type == SRB_JOIN_LEFT_SEMI) {
+                    if (!matched) {
+                        probe_index.push_back((uint32_t)i);
+                        build_index.push_back(bi);
+                    }
+                    matched = true;
+                    break;
+                }
+                probe_index.push_back((uint32_t)i);
+                build_index.push_back(bi);
+            }
+            bi = t.next[bi];
+        }
+    }
+    r->rows_in = probe->n_rows;
+    r->rows_selected = (int64_t)probe_index.size();
+    r->n_rows = (int64_t)probe_index.size();
+    std::vector<uint32_t> build_rows(build_index.size());
+    for (size_t i = 0; i < build_index.size(); i++) build_rows[i] = build_index[i] - 1;
+    for (int i = 0; i < plan->n_probe_out; i++) {
+        r->cols.emplace_back();
+        r->slot_ids.push_back(plan->probe_out_slots[i]);
+        copy_rows(*find_slot(*probe, plan->probe_out_slots[i]), probe_index, r->cols.back());
+    }
+    if (plan->join_type != SRB_JOIN_LEFT_SEMI)
+        for (int i = 0; i < plan->n_build_out; i++) {
+            r->cols.emplace_back();
+            r->slot_ids.push_back(plan->build_out_slots[i]);
+            copy_rows(*find_slot(*build, plan->build_out_slots[i]), build_rows, r->cols.back());
+        }
+    if (plan->emit_indexes) {
+        for (int which = 0; which < 2; which++) {
+            r->cols.emplace_back();
+            OutCol& c = r->cols.back();
+            c.type = SRB_TYPE_INT;
+            r->slot_ids.push_back(which == 0 ? -4 : -3);
+            for (uint32_t x : (which == 0 ? probe_index : build_index)) c.push_int((int128_t)x);
+        }
+    }
+    r->finish();
+    return r;
+}
+
+// packed fixed-size keys of a chunk, 16 bytes per row (CompileFixedSizeKeyColumn, join_hash_map_test.cpp:1041-1056)
+int pack_keys_raw(const srb_chunk* ch, const int32_t* slots, int n_keys, void* out16) {
+    PackedKeys pk = pack_keys(*ch, slots, n_keys);
+    memcpy(out16, pk.k.data(), 16 * pk.k.size());
+    return pk.width;
+}
+
+// raw table for the reference's unit vectors (be/test/exec/join_hash_map_test.cpp:1126-1478)
+void join_build_raw(const void* keys, int width, uint32_t n, uint32_t* bucket_size, uint32_t* first, uint32_t* next) {
+    JoinTable t;
+    t.keys.width = width;
+    t.keys.k.assign(n, 0);
+    t.keys.null.assign(n, 0);
+    for (uint32_t i = 0; i < n; i++) memcpy(&t.keys.k[i], (const uint8_t*)keys + (size_t)width * i, width);
+    build_table(t);
+    *bucket_size = t.bucket_size;
+    if (first) memcpy(first, t.first.data(), sizeof(uint32_t) * t.bucket_size);
+    if (next) memcpy(next, t.next.data(), sizeof(uint32_t) * ((size_t)n + 1));
+}
+
+} // namespace orc

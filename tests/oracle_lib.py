@@ -1,0 +1,112 @@
+"""ctypes wrapper of oracle/build/liboracle.so — the CPU restatement of the reference (TEST INFRASTRUCTURE).
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+from starrocks_b200 import capi as K
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "oracle", "build", "liboracle.so")
+
+
+def build_oracle(force: bool = False) -> str:
+    srcs = [os.path.join(ROOT, "oracle", f) for f in os.listdir(os.path.join(ROOT, "oracle")) if f.endswith((".cpp", ".h"))]
+    srcs.append(os.path.join(ROOT, "include", "srb", "srb_c_api.h"))
+    stale = force or not os.path.exists(LIB) or any(os.path.getmtime(s) > os.path.getmtime(LIB) for s in srcs)
+    if stale:
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
+    return LIB
+
+
+class Oracle:
+    def __init__(self):
+        self.lib = C.CDLL(build_oracle())
+        L = self.lib
+        L.orc_last_error.restype = C.c_char_p
+        L.orc_scan_agg.restype = C.c_void_p
+        L.orc_scan_agg.argtypes = [C.POINTER(K.srb_scan_agg_plan), C.POINTER(K.srb_chunk), C.c_int, C.c_int]
+        L.orc_join.restype = C.c_void_p
+        L.orc_join.argtypes = [C.POINTER(K.srb_join_plan), C.POINTER(K.srb_chunk), C.POINTER(K.srb_chunk)]
+        L.orc_result_chunk.restype = C.POINTER(K.srb_chunk)
+        L.orc_result_chunk.argtypes = [C.c_void_p]
+        L.orc_result_counters.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.orc_result_free.argtypes = [C.c_void_p]
+        L.orc_from_date.restype = C.c_int32
+        L.orc_checked_binop.argtypes = [C.c_int, C.c_int] + [C.c_int64] * 4 + [C.POINTER(C.c_int64)] * 2
+        L.orc_decimal_div_integer.argtypes = [C.c_int64, C.c_int64, C.c_int64, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.orc_div_round128.argtypes = [C.c_int64] * 4 + [C.POINTER(C.c_int64)] * 2
+        L.orc_div_round64.restype = C.c_int64
+        L.orc_div_round64.argtypes = [C.c_int64, C.c_int64]
+        L.orc_join_key_hash32.restype = C.c_uint32
+        L.orc_join_key_hash32.argtypes = [C.c_uint32, C.c_uint32]
+        L.orc_join_key_hash64.restype = C.c_uint32
+        L.orc_join_key_hash64.argtypes = [C.c_uint64, C.c_uint32]
+        L.orc_join_key_hash_bytes.restype = C.c_uint32
+        L.orc_join_key_hash_bytes.argtypes = [C.c_char_p, C.c_int32, C.c_uint32]
+        L.orc_calc_bucket_size.restype = C.c_uint32
+        L.orc_calc_bucket_size.argtypes = [C.c_uint32]
+        L.orc_join_build_raw.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.POINTER(C.c_uint32), C.c_void_p, C.c_void_p]
+        L.orc_crc_hash_32.restype = C.c_uint32
+        L.orc_crc_hash_32.argtypes = [C.c_char_p, C.c_int32, C.c_uint32]
+        L.orc_crc_hash_64.restype = C.c_uint64
+        L.orc_crc_hash_64.argtypes = [C.c_char_p, C.c_int32, C.c_uint64]
+        L.orc_phmap_mix8.restype = C.c_uint64
+        L.orc_phmap_mix8.argtypes = [C.c_uint64, C.c_int]
+        L.orc_hash128_with_seed.restype = C.c_uint64
+        L.orc_hash128_with_seed.argtypes = [C.c_int64, C.c_int64, C.c_int]
+        L.orc_fnv_hash.restype = C.c_uint32
+        L.orc_fnv_hash.argtypes = [C.c_char_p, C.c_int32, C.c_uint32]
+        L.orc_xorshift32.restype = C.c_uint32
+        L.orc_xorshift32.argtypes = [C.c_uint32]
+        L.orc_shuffle_channel.restype = C.c_uint32
+        L.orc_shuffle_channel.argtypes = [C.c_char_p, C.c_int32, C.c_uint32]
+        if L.orc_has_hw_crc():
+            L.orc_hw_crc32c_u64.restype = C.c_uint32
+            L.orc_hw_crc32c_u64.argtypes = [C.c_uint32, C.c_uint64]
+
+    def _err(self):
+        return self.lib.orc_last_error().decode()
+
+    def scan_agg(self, plan, chunk: K.Chunk, n_threads: int = 1, chunk_size: int = 4096, with_counters=False):
+        cch, keep = chunk.to_c()
+        r = self.lib.orc_scan_agg(C.byref(plan.c), C.byref(cch), n_threads, chunk_size)
+        if not r:
+            raise RuntimeError("oracle: " + self._err())
+        try:
+            out = K.decode_chunk(self.lib.orc_result_chunk(r).contents)
+            a, b = C.c_int64(), C.c_int64()
+            self.lib.orc_result_counters(r, C.byref(a), C.byref(b))
+        finally:
+            self.lib.orc_result_free(r)
+        return (out, a.value, b.value) if with_counters else out
+
+    def join(self, plan, build: K.Chunk, probe: K.Chunk):
+        b, k1 = build.to_c()
+        p, k2 = probe.to_c()
+        r = self.lib.orc_join(C.byref(plan.c), C.byref(b), C.byref(p))
+        if not r:
+            raise RuntimeError("oracle: " + self._err())
+        try:
+            return K.decode_chunk(self.lib.orc_result_chunk(r).contents)
+        finally:
+            self.lib.orc_result_free(r)
+
+    def checked_binop(self, width, op, a, b):
+        alo, ahi = K.split128(a)
+        blo, bhi = K.split128(b)
+        rlo, rhi = C.c_int64(), C.c_int64()
+        ov = self.lib.orc_checked_binop(width, op, alo, ahi, blo, bhi, C.byref(rlo), C.byref(rhi))
+        v = K.join128(rlo.value, rhi.value)
+        if v >= 1 << 127:
+            v -= 1 << 128
+        return bool(ov), v
+
+    def decimal_div_integer(self, s, count, scale):
+        lo, hi = K.split128(s)
+        rlo, rhi = C.c_int64(), C.c_int64()
+        self.lib.orc_decimal_div_integer(lo, hi, count, scale, C.byref(rlo), C.byref(rhi))
+        v = K.join128(rlo.value, rhi.value)
+        return v - (1 << 128) if v >= 1 << 127 else v

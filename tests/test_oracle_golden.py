@@ -1,0 +1,284 @@
+"""Pins the CPU oracle to the reference's own known-answer tests. CPU only.
+
+Each test names the reference test it restates (be/test/...:line). Expected values are the reference's
+literals; inputs are rebuilt exactly as the reference's generators build them.
+"""
+import numpy as np
+import pytest
+
+from starrocks_b200 import capi as K
+from starrocks_b200.plan import ExprBuilder, ScanAggPlan, JoinPlan, pred
+
+I32MAX, I32MIN = 2**31 - 1, -2**31
+I64MAX, I64MIN = 2**63 - 1, -2**63
+I128MAX, I128MIN = 2**127 - 1, -2**127
+
+
+def wrap(x, bits):
+    x &= (1 << bits) - 1
+    return x - (1 << bits) if x >= 1 << (bits - 1) else x
+
+
+def cdiv(a, b):  # C truncating division
+    q = abs(a) // abs(b)
+    return q if (a < 0) == (b < 0) else -q
+
+
+# ---- be/test/runtime/decimalv3_test.cpp:402-491 (prepare_add_data / prepare_sub_data / prepare_mul_data) ----
+def _limits(width):
+    return {4: (I32MAX, I32MIN), 8: (I64MAX, I64MIN), 16: (I128MAX, I128MIN)}[width]
+
+
+def _add_cases(width):
+    mx, mn = _limits(width)
+    hmx, hmn = cdiv(mx, 2), cdiv(mn, 2)
+    # decimalv3_test.cpp prepare_add_data (mirrors prepare_sub_data with the second operand negated)
+    return [(0, 0, False), (hmx, -hmx, False), (hmn, -hmn, False), (hmx - 1, hmx - 1, False), (mx - hmx, hmx, False),
+            (hmn + 1, hmn + 1, False), (mn - hmn, hmn, False), (mx, 1, True), (mx, hmx, True), (mx, mx, True),
+            (mn, -1, True), (mn, hmn, True), (mn, mn, True)]
+
+
+def _sub_cases(width):
+    mx, mn = _limits(width)
+    hmx, hmn = cdiv(mx, 2), cdiv(mn, 2)
+    return [(0, 0, False), (hmx, hmx, False), (hmn, hmn, False), (hmx - 1, -(hmx - 1), False), (mx - hmx, -hmx, False),
+            (hmn + 1, -(hmn + 1), False), (mn - hmn, -hmn, False), (mx, -1, True), (mx, -hmx, True), (mx, -mx, True),
+            (mn, 1, True), (mn, -hmn, True), (mn, wrap(-mn, width * 8), False)]
+
+
+def _mul_cases(width):
+    mx, mn = _limits(width)
+    v0 = 1 << (width // 2)  # `static_cast<T>(1) << (sizeof(T) / 2)`: sizeof is in bytes
+    v1 = v0 // 2
+    nmn = wrap(-mn, width * 8)
+    return [(0, 0, False), (0, v0, False), (v0, 0, False), (v0, v0, False), (v1, v1, False), (v1 - 1, v1 - 1, False),
+            (v1, v0, False), (v0, v1, False), (v0, v1 >> 1, False), (mx, mx, True), (mn, mn, True),
+            (v0, -v0, False), (-v1, v1, False), (v1 - 1, -(v1 - 1), False), (v1, -v0, False), (v0, -v1, False),
+            (v0, -(v1 >> 1), False), (mx, -mx, True), (mn, nmn, True),
+            (-v0, -v0, False), (-v1, -v1, False), (-(v1 - 1), -(v1 - 1), False), (-v1, -v0, False), (-v0, -v1, False),
+            (-v0, -(v1 >> 1), False), (-mx, -mx, True), (nmn, nmn, True)]
+
+
+@pytest.mark.parametrize("width", [4, 8, 16])
+def test_decimalv3_add_sub_mul(oracle, width):
+    bits = width * 8
+    for op, cases, f in ((K.EXPR_ADD, _add_cases(width), lambda a, b: a + b),
+                         (K.EXPR_SUB, _sub_cases(width), lambda a, b: a - b),
+                         (K.EXPR_MUL, _mul_cases(width), lambda a, b: a * b)):
+        for a, b, expect_ov in cases:
+            ov, z = oracle.checked_binop(width, op, a, b)
+            assert ov == expect_ov, (width, op, a, b)
+            if not expect_ov:  # the reference also pins the wrapped value; for non-overflow it is the exact one
+                assert z == wrap(f(a, b), bits), (width, op, a, b)
+
+
+def test_int128_mul_is_multi3_not_builtin(oracle):
+    # int128_arithmetics_x86_64.h:184-229: |x|*|y| == 2^127 is flagged although -2^127 is representable
+    ov, _ = oracle.checked_binop(16, K.EXPR_MUL, -(1 << 64), 1 << 63)
+    assert ov is True
+    ov, z = oracle.checked_binop(16, K.EXPR_MUL, -(1 << 63), (1 << 63) - 1)
+    assert ov is False and z == -(1 << 63) * ((1 << 63) - 1)
+
+
+# ---- be/test/exec/join_hash_map_test.cpp:914-1000 (JoinKeyHash) ------------------------------------------
+def _occupancy(fn, keys, nb):
+    b = np.fromiter((fn(int(k)) for k in keys), dtype=np.int64, count=len(keys))
+    cnt = np.bincount(b, minlength=nb)
+    return int(cnt.min()), int(cnt.max())
+
+
+def test_join_key_hash_vectors(oracle):
+    nb, lg = 1 << 16, 16
+    L = oracle.lib
+    h32 = lambda v: L.orc_join_key_hash32(v & 0xFFFFFFFF, lg)
+    h64 = lambda v: L.orc_join_key_hash64(v, lg)
+    assert _occupancy(h32, range(0, nb * 3 * 5, 3), nb) == (0, 11)
+    assert _occupancy(h32, range(0, nb * 7 * 5, 7), nb) == (0, 14)
+    assert _occupancy(h32, range(0, nb * 5), nb) == (4, 6)
+    assert _occupancy(h64, range(0, nb * 3 * 5, 3), nb) == (3, 7)
+    assert _occupancy(h64, range(0, nb * 7 * 5, 7), nb) == (4, 7)
+    assert _occupancy(h64, range(0, nb * 5), nb) == (4, 6)
+    assert L.orc_join_key_hash_bytes(b"abcd", 4, nb) == 2777932099 % nb
+
+
+def test_calc_bucket_num(oracle):
+    # :1002-1023
+    L = oracle.lib
+    assert L.orc_join_key_hash32(1, 2) == 2
+    assert [L.orc_join_key_hash32(v, 2) for v in (1, 2, 3, 4)] == [2, 0, 3, 1]
+
+
+def test_crc32c_matches_hardware(oracle):
+    L = oracle.lib
+    if not L.orc_has_hw_crc():
+        pytest.skip("no SSE4.2")
+    rng = np.random.default_rng(7)
+    for _ in range(200):
+        v = int(rng.integers(0, 2**63)) * 2 + int(rng.integers(0, 2))
+        seed = int(rng.integers(0, 2**32))
+        import struct
+        sw = L.orc_crc_hash_64(struct.pack("<Q", v), 8, seed)
+        # crc_hash_64 over exactly 8 bytes = two identical-word crc steps (util/hash.h:145-167)
+        hw = L.orc_hw_crc32c_u64(L.orc_hw_crc32c_u64(seed, v), v)
+        assert sw == hw
+
+
+# ---- be/test/exprs/agg/aggregate_test.cpp -----------------------------------------------------------------
+COL1 = list(range(1024)) + [100, 200]   # gen_input_column1 :104-113
+COL2 = list(range(2000, 3000))          # gen_input_column2 :127-133
+
+
+def _agg(oracle, fn, type_, values, precision=0, scale=0, nulls=None, phase=K.AGG_UPDATE_FINALIZE, threads=1):
+    e = ExprBuilder()
+    arg = e.slot(0, type_, precision, scale)
+    plan = ScanAggPlan(exprs=e, aggs=[(fn, arg)], phase=phase)
+    ch = K.Chunk(len(values), {0: K.Column.from_ints(type_, values, nulls, precision, scale)})
+    return oracle.scan_agg(plan, ch, n_threads=threads, chunk_size=256)
+
+
+def _two_phase(oracle, fn, type_, v1, v2, precision=0, scale=0):
+    """update+serialize each input, then merge+finalize both intermediates (test_agg_function :224-261)."""
+    inter = [_agg(oracle, fn, type_, v, precision, scale, phase=K.AGG_UPDATE_SERIALIZE) for v in (v1, v2)]
+    c0, c1 = inter[0].columns[0], inter[1].columns[0]
+    if K.is_binary(c0.type):
+        blobs = K.column_pyvalues(c0) + K.column_pyvalues(c1)
+        col = K.Column.from_strings(blobs, type_=K.TYPE_VARBINARY)
+        col.precision, col.scale = c0.precision, c0.scale
+    else:
+        vals = K.column_pyvalues(c0) + K.column_pyvalues(c1)
+        col = K.Column.from_ints(c0.type, vals, None, c0.precision, c0.scale)
+    e = ExprBuilder()
+    arg = e.slot(0, col.type, col.precision, col.scale)
+    plan = ScanAggPlan(exprs=e, aggs=[(fn, arg)], phase=K.AGG_MERGE_FINALIZE)
+    return K.column_pyvalues(oracle.scan_agg(plan, K.Chunk(2, {0: col})).columns[0])[0]
+
+
+def _one(chunk):
+    return K.column_pyvalues(chunk.columns[0])[0]
+
+
+@pytest.mark.parametrize("type_", [K.TYPE_SMALLINT, K.TYPE_INT, K.TYPE_BIGINT, K.TYPE_LARGEINT, K.TYPE_DOUBLE])
+def test_sum_count_avg_max_min(oracle, type_):
+    # test_count :331-343, test_sum :345-367, test_avg :399-414, test_max :957-976, test_min :993-1012
+    assert _one(_agg(oracle, K.AGG_COUNT, type_, COL1)) == 1026
+    assert _one(_agg(oracle, K.AGG_COUNT, type_, COL2)) == 1000
+    assert _two_phase(oracle, K.AGG_COUNT, type_, COL1, COL2) == 2026
+    assert _one(_agg(oracle, K.AGG_SUM, type_, COL1)) == 524076
+    assert _one(_agg(oracle, K.AGG_SUM, type_, COL2)) == 2499500
+    assert _two_phase(oracle, K.AGG_SUM, type_, COL1, COL2) == 3023576
+    assert _one(_agg(oracle, K.AGG_AVG, type_, COL1)) == 524076 / 1026.0
+    assert _one(_agg(oracle, K.AGG_AVG, type_, COL2)) == 2499500 / 1000.0
+    assert _two_phase(oracle, K.AGG_AVG, type_, COL1, COL2) == 3023576 / 2026.0
+    assert _one(_agg(oracle, K.AGG_MAX, type_, COL1)) == 1023
+    assert _one(_agg(oracle, K.AGG_MAX, type_, COL2)) == 2999
+    assert _two_phase(oracle, K.AGG_MAX, type_, COL1, COL2) == 2999
+    assert _one(_agg(oracle, K.AGG_MIN, type_, COL1)) == 0
+    assert _one(_agg(oracle, K.AGG_MIN, type_, COL2)) == 2000
+    assert _two_phase(oracle, K.AGG_MIN, type_, COL1, COL2) == 0
+
+
+@pytest.mark.parametrize("type_,p,s", [(K.TYPE_DECIMAL32, 9, 9), (K.TYPE_DECIMAL64, 9, 3), (K.TYPE_DECIMAL128, 38, 15)])
+def test_decimal_sum_avg(oracle, type_, p, s):
+    # test_decimal_sum :369-397: every decimal width sums into DECIMAL128 with the same integers
+    r = _agg(oracle, K.AGG_SUM, type_, COL1, p, s)
+    assert r.columns[0].type == K.TYPE_DECIMAL128 and r.columns[0].scale == s
+    assert _one(r) == 524076
+    assert _one(_agg(oracle, K.AGG_SUM, type_, COL2, p, s)) == 2499500
+    assert _two_phase(oracle, K.AGG_SUM, type_, COL1, COL2, p, s) == 3023576
+    # test_decimal_avg :431-468: decimal_div_integer(sum, count, scale)
+    ddi = oracle.decimal_div_integer
+    assert _one(_agg(oracle, K.AGG_AVG, type_, COL1, p, s)) == ddi(524076, 1026, s)
+    assert _one(_agg(oracle, K.AGG_AVG, type_, COL2, p, s)) == ddi(2499500, 1000, s)
+    assert _two_phase(oracle, K.AGG_AVG, type_, COL1, COL2, p, s) == ddi(3023576, 2026, s)
+
+
+def test_decimal_div_integer_is_half_away_from_zero(oracle):
+    # arithmetic_operation.h:409-441 + decimalv3.h:86-100, checked against exact rational arithmetic
+    from fractions import Fraction
+    for s, count, scale in [(524076, 1026, 9), (2499500, 1000, 3), (3023576, 2026, 15), (-524076, 1026, 2), (7, 2, 0), (-7, 2, 0),
+                            (1, 3, 2), (2, 3, 2), (-2, 3, 2)]:
+        rs = scale + 6 if scale <= 6 else (12 if scale <= 12 else scale)
+        q = Fraction(s * 10 ** (rs - scale), count)
+        fl = q.numerator // q.denominator
+        frac = q - fl
+        expect = fl + (1 if (frac > Fraction(1, 2) or (frac == Fraction(1, 2) and q > 0)) else 0)
+        assert oracle.decimal_div_integer(s, count, scale) == expect
+
+
+def test_date_avg_pins_from_date(oracle):
+    # test_avg :428-429 with gen_input_column1/2<DateValue> :193-212 — pins date::from_date for 44 dates
+    L = oracle.lib
+    d1 = [L.orc_from_date(2000 + j, 1, 1) for j in range(20)] + [L.orc_from_date(2000, 1, 1), L.orc_from_date(2001, 1, 1)]
+    d2 = [L.orc_from_date(1000 + j, 1, 1) for j in range(20)] + [L.orc_from_date(2000, 1, 1), L.orc_from_date(1000, 1, 1)]
+    assert _one(_agg(oracle, K.AGG_AVG, K.TYPE_DATE, d1)) == 2454716
+    assert _one(_agg(oracle, K.AGG_AVG, K.TYPE_DATE, d2)) == 2106058
+    assert (sum(d1) + sum(d2)) // 44 == 2280387
+    assert L.orc_from_date(1970, 1, 1) == 2440588  # date::UNIX_EPOCH_JULIAN, runtime/time_types.h:177
+    # max/min DATE :990-991
+    assert _one(_agg(oracle, K.AGG_MAX, K.TYPE_DATE, d1)) == L.orc_from_date(2019, 1, 1)
+
+
+def test_nullable_sum_count(oracle):
+    # test_sum_nullable :1250-1297 / test_count_nullable :1299-1318: NULL rows are skipped; all-NULL sum is NULL
+    vals = list(range(100))
+    nulls = [1 if i % 3 == 0 else 0 for i in range(100)]
+    expect = sum(v for v, n in zip(vals, nulls) if not n)
+    assert _one(_agg(oracle, K.AGG_SUM, K.TYPE_INT, vals, nulls=nulls)) == expect
+    assert _one(_agg(oracle, K.AGG_COUNT, K.TYPE_INT, vals, nulls=nulls)) == 100 - sum(nulls)
+    assert _one(_agg(oracle, K.AGG_SUM, K.TYPE_INT, vals, nulls=[1] * 100)) is None
+    assert _one(_agg(oracle, K.AGG_COUNT, K.TYPE_INT, vals, nulls=[1] * 100)) == 0
+    # no-group-by over empty input: sum is NULL, count is 0 (aggregator.cpp:938-945)
+    assert _one(_agg(oracle, K.AGG_SUM, K.TYPE_INT, [])) is None
+    assert _one(_agg(oracle, K.AGG_COUNT, K.TYPE_INT, [])) == 0
+
+
+def test_threads_do_not_change_results(oracle):
+    for t in (1, 2, 5):
+        assert _one(_agg(oracle, K.AGG_SUM, K.TYPE_BIGINT, COL1, threads=t)) == 524076
+
+
+# ---- join tables: be/test/exec/join_hash_map_test.cpp:1126-1220, 1964-2030 --------------------------------
+def test_join_build_chain_layout(oracle):
+    import ctypes as C
+    keys = np.arange(0, 10, dtype=np.int32)  # JoinBuildFunc test: keys 0..9 after the dummy row
+    bs = C.c_uint32()
+    oracle.lib.orc_join_build_raw(keys.ctypes.data, 4, 10, C.byref(bs), None, None)
+    assert bs.value == oracle.lib.orc_calc_bucket_size(11) == 16  # NormalizeCapacity(11 + 10/4) + 1
+    first = np.zeros(bs.value, np.uint32)
+    nxt = np.zeros(11, np.uint32)
+    oracle.lib.orc_join_build_raw(keys.ctypes.data, 4, 10, C.byref(bs), first.ctypes.data, nxt.ctypes.data)
+    # every row is reachable exactly once by walking first[]/next[]; row 0 is the sentinel
+    seen = []
+    for b in range(bs.value):
+        i = int(first[b])
+        while i:
+            assert oracle.lib.orc_join_key_hash32(int(keys[i - 1]), 4) == b
+            seen.append(i)
+            i = int(nxt[i])
+    assert sorted(seen) == list(range(1, 11))
+
+
+def test_join_inner_one_to_many_and_nulls(oracle):
+    build = K.Chunk(6, {0: K.Column.from_ints(K.TYPE_INT, [1, 2, 2, 3, 5, 7], nulls=[0, 0, 0, 0, 1, 0]),
+                        1: K.Column.from_ints(K.TYPE_BIGINT, [10, 20, 21, 30, 50, 70])})
+    probe = K.Chunk(5, {2: K.Column.from_ints(K.TYPE_INT, [2, 3, 4, 5, 7], nulls=[0, 0, 0, 0, 1]),
+                        3: K.Column.from_ints(K.TYPE_BIGINT, [200, 300, 400, 500, 700])})
+    plan = JoinPlan([0], [2], build_out=[1], probe_out=[3])
+    rows = K.chunk_rows(oracle.join(plan, build, probe))
+    assert rows == [(200, 20), (200, 21), (300, 30)]  # NULL keys never match (tpp:62-72)
+
+
+def test_fixed_size_key_packing(oracle):
+    # CompileFixedSizeKeyColumn :1041-1056: (0,2)->8589934592, (1,3)->12884901889 — two int32 keys pack low-to-high
+    build = K.Chunk(2, {0: K.Column.from_ints(K.TYPE_INT, [0, 1]), 1: K.Column.from_ints(K.TYPE_INT, [2, 3]),
+                        9: K.Column.from_ints(K.TYPE_BIGINT, [8589934592, 12884901889])})
+    probe = K.Chunk(2, {4: K.Column.from_ints(K.TYPE_BIGINT, [8589934592, 12884901889])})
+    import ctypes as C
+    cch, keep = build.to_c()
+    out = np.zeros(2, dtype=K.I128)
+    slots = (C.c_int32 * 2)(0, 1)
+    assert oracle.lib.orc_pack_keys(C.byref(cch), slots, 2, C.c_void_p(out.ctypes.data)) == 8
+    assert K.i128_to_pyints(out) == [8589934592, 12884901889]
+    # and a join on the packed BIGINT finds exactly those rows
+    plan = JoinPlan([9], [4], build_out=[0, 1], probe_out=[4])
+    assert K.chunk_rows(oracle.join(plan, build, probe)) == [(8589934592, 0, 2), (12884901889, 1, 3)]
