@@ -241,6 +241,10 @@ int32_t srb_op_is_finished(srb_op* op);
 srb_status srb_op_pull_chunk(srb_op* op, srb_chunk* out);
 /* whole-result variant for harnesses: all remaining rows in one chunk (no chunk_size slicing) */
 srb_status srb_op_pull_all(srb_op* op, srb_chunk* out);
+/* device-resident variant for operator chaining on the GPU (scan/filter -> join probe -> aggregate without a host
+ * round trip): all remaining rows, columns are SRB_MEM_DEVICE buffers owned by the op and valid until its next
+ * push/pull/close. Fixed-width columns only. */
+srb_status srb_op_pull_device(srb_op* op, srb_chunk* out);
 /* Operator::set_cancelled (operator.h:84) / close (operator.h:92) */
 srb_status srb_op_cancel(srb_op* op);
 void srb_op_close(srb_op* op);
@@ -259,6 +263,35 @@ int32_t srb_join_probe_need_input(srb_op* op);
 int32_t srb_join_probe_is_finished(srb_op* op);
 srb_status srb_join_probe_pull_chunk(srb_op* op, srb_chunk* out);
 srb_status srb_join_probe_pull_all(srb_op* op, srb_chunk* out);
+srb_status srb_join_probe_pull_device(srb_op* op, srb_chunk* out);
+
+/* ---- exchange: what replaces ExchangeSinkOperator / ExchangeSourceOperator + brpc between GPUs ---------------------- */
+typedef struct srb_partitioner srb_partitioner;
+typedef struct srb_comm srb_comm; /* one NCCL communicator over the ctx's rank / world_size */
+
+/* HASH_PARTITIONED row routing (exchange_sink_operator.cpp:569-633): per-row FNV-1 chained over the partition columns
+ * (fixed_length_column_base.cpp:223-227; NULL rows nullable_column.cpp:346-369), channel = (hash * n) >> 32
+ * (shuffler.h:70-85). `in` is a device-resident chunk of fixed-width columns; `out` has the same columns with every
+ * destination's rows contiguous, destination 0 first (library-owned device buffers, valid until the next run/destroy);
+ * counts[d] = rows for destination d. */
+srb_status srb_partition_create(srb_ctx* ctx, int32_t n_partitions, int32_t reserved, srb_partitioner** out);
+srb_status srb_partition_run(srb_partitioner* p, const srb_chunk* in, int32_t n_key_slots, const int32_t* key_slots, srb_chunk* out,
+                             int64_t* counts);
+void srb_partition_destroy(srb_partitioner* p);
+
+/* communicator bootstrap: rank 0 calls srb_comm_unique_id, the 128 bytes travel out of band (the harness uses
+ * torch.distributed's store), every rank calls srb_comm_create with them. */
+srb_status srb_comm_unique_id(void* out128);
+srb_status srb_comm_create(srb_ctx* ctx, const void* id128, srb_comm** out);
+void srb_comm_destroy(srb_comm* c);
+void* srb_comm_stream(srb_comm* c);
+/* the shuffle itself (replaces transmit_chunk over brpc, data_stream_sender/recvr): `send` rows are grouped by destination
+ * rank with send_counts[world]; `recv` (library-owned device buffers, valid until the next call on this comm) holds the
+ * rows from rank 0, 1, ... in that order with recv_counts[world]. Counts travel first (ncclAllGather), then one grouped
+ * ncclSend/ncclRecv per column and peer. */
+srb_status srb_comm_all_to_all(srb_comm* c, const srb_chunk* send, const int64_t* send_counts, srb_chunk* recv, int64_t* recv_counts);
+/* UNPARTITIONED / broadcast exchange (exchange_sink_operator.cpp:508-547): every rank's rows replicated on every rank */
+srb_status srb_comm_all_gather(srb_comm* c, const srb_chunk* mine, srb_chunk* out);
 
 /* ---- device memory helpers for harnesses (plain cudaMalloc/cudaMemcpy wrappers) ------------------- */
 srb_status srb_device_alloc(srb_ctx* ctx, int64_t bytes, void** out);

@@ -1,0 +1,472 @@
+// srb_exchange.cu — hash partitioning (K9) and the NCCL exchange that stands where the brpc shuffle is in the reference.
+//
+// Replaces:
+//   ExchangeSinkOperator::push_chunk, HASH_PARTITIONED branch    be/src/exec/pipeline/exchange/exchange_sink_operator.cpp:569-633
+//     per-row hash = FNV-1 chained over the partition columns    be/src/column/fixed_length_column_base.cpp:223-227,
+//       (NULL: h ^= 0x9e3779b9 + (h<<6) + (h>>2))                be/src/column/nullable_column.cpp:346-369, util/hash_util.hpp:195-214
+//     channel = ReduceOp(hash, n) = (hash * n) >> 32             be/src/exec/pipeline/exchange/shuffler.h:70-85
+//     counting sort of row ids per channel + append_selective    exchange_sink_operator.cpp:595-630
+//   UNPARTITIONED (broadcast) branch                              exchange_sink_operator.cpp:508-547
+//   the transport: PTransmitChunkParams over brpc                 be/src/runtime/data_stream_{sender,recvr}.cpp
+// by: one counting pass + one scatter pass on the device that leave every destination's rows contiguous, then a grouped
+// ncclSend/ncclRecv all-to-all (counts exchanged first with ncclAllGather), or ncclBroadcast / ncclAllGather for replicated
+// build sides. NCCL is bound at run time (dlopen libnccl.so.2 — the copy torch already loaded when there is one), so a
+// single-GPU process never needs it.
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cstring>
+#include <string>
+
+#include "srb_dev.cuh"
+#include "srb_host.h"
+
+namespace srb {
+
+constexpr int PMAX_COLS = 16, PMAX_KEYS = 4, PMAX_PARTS = 64;
+
+struct PCol {
+    const uint8_t* src;
+    uint8_t* dst;
+    const uint8_t* src_null;
+    uint8_t* dst_null;
+    int32_t width;
+    int32_t _pad;
+};
+struct PArgs {
+    int32_t n_cols, n_keys, n_parts, _pad;
+    int32_t key_col[PMAX_KEYS];
+    PCol cols[PMAX_COLS];
+    unsigned long long base[PMAX_PARTS]; // first output row of each partition (scatter pass)
+};
+
+SRB_D uint32_t part_of(const PArgs& a, int64_t r) {
+    uint32_t h = 0x811C9DC5u; // HashUtil::FNV_SEED
+    for (int k = 0; k < a.n_keys; k++) {
+        const PCol& c = a.cols[a.key_col[k]];
+        if (c.src_null && c.src_null[r]) {
+            h = h ^ (0x9e3779b9u + (h << 6) + (h >> 2));
+        } else {
+            const uint8_t* p = c.src + (size_t)r * c.width;
+            for (int b = 0; b < c.width; b++) h = (p[b] ^ h) * 0x01000193u;
+        }
+    }
+    return reduce_op(h, (uint32_t)a.n_parts);
+}
+
+// pass 1: destination per row (1 byte) + per-partition totals
+__global__ void __launch_bounds__(256) k_part_count(const __grid_constant__ PArgs a, int64_t n, uint8_t* __restrict__ dest,
+                                                     unsigned long long* __restrict__ totals) {
+    __shared__ unsigned int hist[PMAX_PARTS];
+    for (int i = threadIdx.x; i < PMAX_PARTS; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t d = part_of(a, r);
+        dest[r] = (uint8_t)d;
+        unsigned peers = __match_any_sync(__activemask(), d);
+        if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&hist[d], __popc(peers));
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < a.n_parts; i += blockDim.x)
+        if (hist[i]) atomicAdd(&totals[i], (unsigned long long)hist[i]);
+}
+
+// pass 2: each block reserves a contiguous run per partition for its tile, then scatters every column
+constexpr int PTILE = 2048;
+__global__ void __launch_bounds__(256) k_part_scatter(const __grid_constant__ PArgs a, int64_t n, const uint8_t* __restrict__ dest,
+                                                       unsigned long long* __restrict__ cursors) {
+    __shared__ unsigned int hist[PMAX_PARTS];
+    __shared__ unsigned long long run_base[PMAX_PARTS];
+    const int64_t n_tiles = (n + PTILE - 1) / PTILE;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (int i = threadIdx.x; i < PMAX_PARTS; i += blockDim.x) hist[i] = 0;
+        __syncthreads();
+        uint32_t d[PTILE / 256], rank[PTILE / 256];
+#pragma unroll
+        for (int j = 0; j < PTILE / 256; j++) {
+            int64_t r = tile * PTILE + j * 256 + threadIdx.x;
+            d[j] = 0xffffffffu;
+            rank[j] = 0;
+            bool on = r < n;
+            if (on) d[j] = dest[r];
+            unsigned act = __ballot_sync(0xffffffffu, on);
+            if (on) {
+                unsigned peers = __match_any_sync(act, d[j]);
+                int leader = __ffs(peers) - 1, lane = threadIdx.x & 31;
+                unsigned int b = 0;
+                if (lane == leader) b = atomicAdd(&hist[d[j]], __popc(peers));
+                b = __shfl_sync(peers, b, leader);
+                rank[j] = b + __popc(peers & ((1u << lane) - 1));
+            }
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < a.n_parts; i += blockDim.x)
+            run_base[i] = hist[i] ? a.base[i] + atomicAdd(&cursors[i], (unsigned long long)hist[i]) : 0;
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < PTILE / 256; j++) {
+            if (d[j] == 0xffffffffu) continue;
+            const int64_t r = tile * PTILE + j * 256 + threadIdx.x;
+            const unsigned long long pos = run_base[d[j]] + rank[j];
+            for (int c = 0; c < a.n_cols; c++) {
+                const PCol& pc = a.cols[c];
+                switch (pc.width) {
+                case 1: pc.dst[pos] = pc.src[r]; break;
+                case 2: ((uint16_t*)pc.dst)[pos] = ((const uint16_t*)pc.src)[r]; break;
+                case 4: ((uint32_t*)pc.dst)[pos] = ((const uint32_t*)pc.src)[r]; break;
+                case 8: ((uint64_t*)pc.dst)[pos] = ((const uint64_t*)pc.src)[r]; break;
+                default: ((ulonglong2*)pc.dst)[pos] = ((const ulonglong2*)pc.src)[r];
+                }
+                if (pc.src_null) pc.dst_null[pos] = pc.src_null[r];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+} // namespace srb
+
+using namespace srb;
+
+struct srb_partitioner {
+    srb_ctx* ctx;
+    int n_parts;
+    cudaStream_t stream = nullptr;
+    DevBuf dest, totals, out_data[PMAX_COLS], out_null[PMAX_COLS];
+    PinnedBuf htotals;
+    std::vector<srb_column> cview;
+    std::vector<int32_t> slots;
+    int64_t launches = 0;
+};
+
+// ---- NCCL, bound at run time ---------------------------------------------------------------------------------------------------
+namespace {
+typedef struct ncclComm* ncclComm_t;
+struct ncclUniqueId_ {
+    char internal[128];
+};
+enum { ncclInt8_ = 0, ncclUint8_ = 1, ncclInt64_ = 4, ncclUint64_ = 5 };
+struct Nccl {
+    void* h = nullptr;
+    int (*GetUniqueId)(ncclUniqueId_*) = nullptr;
+    int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId_, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Broadcast)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+Nccl g_nccl;
+Nccl& nccl() {
+    if (g_nccl.h) return g_nccl;
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) throw Error(SRB_INTERNAL_ERROR, std::string("cannot load libnccl.so.2: ") + dlerror());
+    auto sym = [&](const char* n) {
+        void* p = dlsym(h, n);
+        if (!p) throw Error(SRB_INTERNAL_ERROR, std::string("libnccl lacks ") + n);
+        return p;
+    };
+    g_nccl.GetUniqueId = (decltype(g_nccl.GetUniqueId))sym("ncclGetUniqueId");
+    g_nccl.CommInitRank = (decltype(g_nccl.CommInitRank))sym("ncclCommInitRank");
+    g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))sym("ncclCommDestroy");
+    g_nccl.GroupStart = (decltype(g_nccl.GroupStart))sym("ncclGroupStart");
+    g_nccl.GroupEnd = (decltype(g_nccl.GroupEnd))sym("ncclGroupEnd");
+    g_nccl.Send = (decltype(g_nccl.Send))sym("ncclSend");
+    g_nccl.Recv = (decltype(g_nccl.Recv))sym("ncclRecv");
+    g_nccl.AllGather = (decltype(g_nccl.AllGather))sym("ncclAllGather");
+    g_nccl.Broadcast = (decltype(g_nccl.Broadcast))sym("ncclBroadcast");
+    g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))sym("ncclGetErrorString");
+    g_nccl.h = h;
+    return g_nccl;
+}
+#define SRB_NCCL(expr)                                                                                              \
+    do {                                                                                                            \
+        int _r = (expr);                                                                                            \
+        if (_r != 0) throw Error(SRB_INTERNAL_ERROR, fmt("%s failed: %s", #expr, nccl().GetErrorString(_r)));        \
+    } while (0)
+} // namespace
+
+struct srb_comm {
+    srb_ctx* ctx;
+    ncclComm_t comm = nullptr;
+    int rank = 0, world = 1;
+    cudaStream_t stream = nullptr;
+    DevBuf counts_dev, recv_data[PMAX_COLS], recv_null[PMAX_COLS];
+    PinnedBuf counts_host;
+    std::vector<srb_column> cview;
+    std::vector<int32_t> slots;
+};
+
+// the C ABI's error string lives in srb_capi.cu; exchange entry points report through the same convention
+namespace srb {
+void set_last_error(const std::string& s);
+}
+#define X_BEGIN try {
+#define X_END                                 \
+    }                                         \
+    catch (const srb::Error& e) {             \
+        srb::set_last_error(e.what());        \
+        return e.code;                        \
+    }                                         \
+    catch (const std::exception& e) {         \
+        srb::set_last_error(e.what());        \
+        return SRB_INTERNAL_ERROR;            \
+    }
+
+extern "C" {
+
+srb_status srb_partition_create(srb_ctx* ctx, int32_t n_partitions, int32_t reserved, srb_partitioner** out) {
+    X_BEGIN
+    (void)reserved;
+    if (!ctx || !out) throw Error(SRB_INVALID_ARGUMENT, "null argument");
+    if (n_partitions < 1 || n_partitions > PMAX_PARTS) throw Error(SRB_INVALID_ARGUMENT, fmt("1..%d partitions supported", PMAX_PARTS));
+    SRB_CUDA(cudaSetDevice(ctx->cfg.device));
+    auto* p = new srb_partitioner();
+    p->ctx = ctx;
+    p->n_parts = n_partitions;
+    SRB_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+    p->totals.ensure(ctx, 2 * PMAX_PARTS * 8);
+    p->htotals.ensure(PMAX_PARTS * 8);
+    *out = p;
+    return SRB_OK;
+    X_END
+}
+
+void srb_partition_destroy(srb_partitioner* p) {
+    if (!p) return;
+    cudaSetDevice(p->ctx->cfg.device);
+    if (p->stream) {
+        cudaStreamSynchronize(p->stream);
+        cudaStreamDestroy(p->stream);
+    }
+    delete p;
+}
+
+// in: device chunk of fixed-width columns; out: same columns with rows grouped by destination (library-owned device
+// buffers, valid until the next run/destroy); counts[d] = rows for destination d.
+srb_status srb_partition_run(srb_partitioner* p, const srb_chunk* in, int32_t n_key_slots, const int32_t* key_slots, srb_chunk* out,
+                             int64_t* counts) {
+    X_BEGIN
+    if (!p || !in || !out || !counts || !key_slots) throw Error(SRB_INVALID_ARGUMENT, "null argument");
+    if (n_key_slots < 1 || n_key_slots > PMAX_KEYS) throw Error(SRB_INVALID_ARGUMENT, "bad number of partition columns");
+    if (in->n_cols < 1 || in->n_cols > PMAX_COLS) throw Error(SRB_NOT_IMPLEMENTED, "too many columns");
+    SRB_CUDA(cudaSetDevice(p->ctx->cfg.device));
+    const int64_t n = in->n_rows;
+    PArgs a{};
+    a.n_cols = in->n_cols;
+    a.n_keys = n_key_slots;
+    a.n_parts = p->n_parts;
+    p->cview.assign(in->cols, in->cols + in->n_cols);
+    p->slots.assign(in->slot_ids, in->slot_ids + in->n_cols);
+    for (int c = 0; c < in->n_cols; c++) {
+        const srb_column& col = in->cols[c];
+        int w = type_width(col.type);
+        if (w == 0) throw Error(SRB_NOT_IMPLEMENTED, "partitioning of binary columns");
+        if (col.mem_kind != SRB_MEM_DEVICE) throw Error(SRB_INVALID_ARGUMENT, "partitioner takes device-resident chunks");
+        p->out_data[c].ensure(p->ctx, (size_t)std::max<int64_t>(n, 1) * w);
+        if (col.nulls) p->out_null[c].ensure(p->ctx, (size_t)std::max<int64_t>(n, 1));
+        a.cols[c] = PCol{(const uint8_t*)col.data, p->out_data[c].as<uint8_t>(), col.nulls, col.nulls ? p->out_null[c].as<uint8_t>() : nullptr, w, 0};
+        p->cview[c].data = p->out_data[c].p;
+        p->cview[c].nulls = col.nulls ? p->out_null[c].as<uint8_t>() : nullptr;
+    }
+    for (int k = 0; k < n_key_slots; k++) {
+        int idx = -1;
+        for (int c = 0; c < in->n_cols; c++)
+            if (in->slot_ids[c] == key_slots[k]) idx = c;
+        if (idx < 0) throw Error(SRB_INVALID_ARGUMENT, fmt("partition slot %d not in chunk", key_slots[k]));
+        a.key_col[k] = idx;
+    }
+    unsigned long long* totals = p->totals.as<unsigned long long>();
+    unsigned long long* cursors = totals + PMAX_PARTS;
+    SRB_CUDA(cudaMemsetAsync(totals, 0, 2 * PMAX_PARTS * 8, p->stream));
+    unsigned long long* ht = p->htotals.as<unsigned long long>();
+    memset(ht, 0, PMAX_PARTS * 8);
+    if (n > 0) {
+        p->dest.ensure(p->ctx, (size_t)n);
+        int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, (int64_t)p->ctx->n_sms * 8));
+        k_part_count<<<grid, 256, 0, p->stream>>>(a, n, p->dest.as<uint8_t>(), totals);
+        SRB_CUDA(cudaMemcpyAsync(ht, totals, PMAX_PARTS * 8, cudaMemcpyDeviceToHost, p->stream));
+        SRB_CUDA(cudaStreamSynchronize(p->stream));
+        unsigned long long acc = 0;
+        for (int d = 0; d < p->n_parts; d++) {
+            a.base[d] = acc;
+            acc += ht[d];
+        }
+        int grid2 = (int)std::max<int64_t>(1, std::min<int64_t>((n + PTILE - 1) / PTILE, (int64_t)p->ctx->n_sms * 4));
+        k_part_scatter<<<grid2, 256, 0, p->stream>>>(a, n, p->dest.as<uint8_t>(), cursors);
+        SRB_CUDA(cudaGetLastError());
+        SRB_CUDA(cudaStreamSynchronize(p->stream));
+        p->launches += 2;
+    }
+    for (int d = 0; d < p->n_parts; d++) counts[d] = (int64_t)ht[d];
+    out->n_rows = n;
+    out->n_cols = in->n_cols;
+    out->slot_ids = p->slots.data();
+    out->cols = p->cview.data();
+    return SRB_OK;
+    X_END
+}
+
+// ---- communicator ------------------------------------------------------------------------------------------------------------
+srb_status srb_comm_unique_id(void* out128) {
+    X_BEGIN
+    if (!out128) throw Error(SRB_INVALID_ARGUMENT, "null argument");
+    ncclUniqueId_ id;
+    SRB_NCCL(nccl().GetUniqueId(&id));
+    memcpy(out128, &id, 128);
+    return SRB_OK;
+    X_END
+}
+
+srb_status srb_comm_create(srb_ctx* ctx, const void* id128, srb_comm** out) {
+    X_BEGIN
+    if (!ctx || !id128 || !out) throw Error(SRB_INVALID_ARGUMENT, "null argument");
+    if (ctx->cfg.world_size > PMAX_PARTS) throw Error(SRB_NOT_IMPLEMENTED, "world size");
+    SRB_CUDA(cudaSetDevice(ctx->cfg.device));
+    auto* c = new srb_comm();
+    c->ctx = ctx;
+    c->rank = ctx->cfg.rank;
+    c->world = ctx->cfg.world_size;
+    ncclUniqueId_ id;
+    memcpy(&id, id128, 128);
+    SRB_NCCL(nccl().CommInitRank(&c->comm, c->world, id, c->rank));
+    SRB_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    c->counts_dev.ensure(ctx, (size_t)(c->world + c->world * c->world) * 8);
+    c->counts_host.ensure((size_t)(c->world + c->world * c->world) * 8);
+    *out = c;
+    return SRB_OK;
+    X_END
+}
+
+void srb_comm_destroy(srb_comm* c) {
+    if (!c) return;
+    cudaSetDevice(c->ctx->cfg.device);
+    if (c->stream) {
+        cudaStreamSynchronize(c->stream);
+        cudaStreamDestroy(c->stream);
+    }
+    if (c->comm) nccl().CommDestroy(c->comm);
+    delete c;
+}
+
+void* srb_comm_stream(srb_comm* c) { return c ? (void*)c->stream : nullptr; }
+
+// send: device chunk whose rows are grouped by destination rank (srb_partition_run output), send_counts[world].
+// recv: library-owned device chunk holding the rows received from rank 0, 1, ... in that order; recv_counts[world].
+srb_status srb_comm_all_to_all(srb_comm* c, const srb_chunk* send, const int64_t* send_counts, srb_chunk* recv, int64_t* recv_counts) {
+    X_BEGIN
+    if (!c || !send || !send_counts || !recv || !recv_counts) throw Error(SRB_INVALID_ARGUMENT, "null argument");
+    if (send->n_cols > PMAX_COLS) throw Error(SRB_NOT_IMPLEMENTED, "too many columns");
+    SRB_CUDA(cudaSetDevice(c->ctx->cfg.device));
+    const int W = c->world;
+    // counts: every rank learns the whole W x W matrix
+    int64_t* hc = c->counts_host.as<int64_t>();
+    int64_t* dc = c->counts_dev.as<int64_t>();
+    for (int d = 0; d < W; d++) hc[d] = send_counts[d];
+    SRB_CUDA(cudaMemcpyAsync(dc, hc, (size_t)W * 8, cudaMemcpyHostToDevice, c->stream));
+    SRB_NCCL(nccl().AllGather(dc, dc + W, (size_t)W, ncclInt64_, c->comm, c->stream));
+    SRB_CUDA(cudaMemcpyAsync(hc + W, dc + W, (size_t)W * W * 8, cudaMemcpyDeviceToHost, c->stream));
+    SRB_CUDA(cudaStreamSynchronize(c->stream));
+    int64_t total = 0;
+    std::vector<int64_t> roff(W), soff(W);
+    int64_t sacc = 0;
+    for (int s = 0; s < W; s++) {
+        recv_counts[s] = hc[W + (size_t)s * W + c->rank]; // what rank s sends to me
+        roff[s] = total;
+        total += recv_counts[s];
+        soff[s] = sacc;
+        sacc += send_counts[s];
+    }
+    if (sacc != send->n_rows) throw Error(SRB_INVALID_ARGUMENT, "send_counts do not add up to the chunk's rows");
+    c->cview.assign(send->cols, send->cols + send->n_cols);
+    c->slots.assign(send->slot_ids, send->slot_ids + send->n_cols);
+    SRB_NCCL(nccl().GroupStart());
+    for (int col = 0; col < send->n_cols; col++) {
+        const srb_column& sc = send->cols[col];
+        const int w = type_width(sc.type);
+        if (w == 0 || sc.mem_kind != SRB_MEM_DEVICE) throw Error(SRB_INVALID_ARGUMENT, "all-to-all takes device-resident fixed-width columns");
+        c->recv_data[col].ensure(c->ctx, (size_t)std::max<int64_t>(total, 1) * w);
+        if (sc.nulls) c->recv_null[col].ensure(c->ctx, (size_t)std::max<int64_t>(total, 1));
+        for (int peer = 0; peer < W; peer++) {
+            if (send_counts[peer])
+                SRB_NCCL(nccl().Send((const uint8_t*)sc.data + (size_t)soff[peer] * w, (size_t)send_counts[peer] * w, ncclUint8_, peer, c->comm, c->stream));
+            if (recv_counts[peer])
+                SRB_NCCL(nccl().Recv(c->recv_data[col].as<uint8_t>() + (size_t)roff[peer] * w, (size_t)recv_counts[peer] * w, ncclUint8_, peer, c->comm,
+                                     c->stream));
+            if (sc.nulls) {
+                if (send_counts[peer]) SRB_NCCL(nccl().Send(sc.nulls + soff[peer], (size_t)send_counts[peer], ncclUint8_, peer, c->comm, c->stream));
+                if (recv_counts[peer])
+                    SRB_NCCL(nccl().Recv(c->recv_null[col].as<uint8_t>() + roff[peer], (size_t)recv_counts[peer], ncclUint8_, peer, c->comm, c->stream));
+            }
+        }
+        c->cview[col].data = c->recv_data[col].p;
+        c->cview[col].nulls = sc.nulls ? c->recv_null[col].as<uint8_t>() : nullptr;
+    }
+    SRB_NCCL(nccl().GroupEnd());
+    SRB_CUDA(cudaStreamSynchronize(c->stream));
+    recv->n_rows = total;
+    recv->n_cols = send->n_cols;
+    recv->slot_ids = c->slots.data();
+    recv->cols = c->cview.data();
+    return SRB_OK;
+    X_END
+}
+
+// every rank contributes `mine` (device, fixed width, same schema); out holds all ranks' rows, rank 0 first. Used to replicate
+// a filtered build side (broadcast join) and to gather small partial aggregates.
+srb_status srb_comm_all_gather(srb_comm* c, const srb_chunk* mine, srb_chunk* out) {
+    X_BEGIN
+    if (!c || !mine || !out) throw Error(SRB_INVALID_ARGUMENT, "null argument");
+    SRB_CUDA(cudaSetDevice(c->ctx->cfg.device));
+    const int W = c->world;
+    int64_t* hc = c->counts_host.as<int64_t>();
+    int64_t* dc = c->counts_dev.as<int64_t>();
+    hc[0] = mine->n_rows;
+    SRB_CUDA(cudaMemcpyAsync(dc, hc, 8, cudaMemcpyHostToDevice, c->stream));
+    SRB_NCCL(nccl().AllGather(dc, dc + W, 1, ncclInt64_, c->comm, c->stream));
+    SRB_CUDA(cudaMemcpyAsync(hc + W, dc + W, (size_t)W * 8, cudaMemcpyDeviceToHost, c->stream));
+    SRB_CUDA(cudaStreamSynchronize(c->stream));
+    std::vector<int64_t> off(W);
+    int64_t total = 0;
+    for (int r = 0; r < W; r++) {
+        off[r] = total;
+        total += hc[W + r];
+    }
+    c->cview.assign(mine->cols, mine->cols + mine->n_cols);
+    c->slots.assign(mine->slot_ids, mine->slot_ids + mine->n_cols);
+    SRB_NCCL(nccl().GroupStart());
+    for (int col = 0; col < mine->n_cols; col++) {
+        const srb_column& sc = mine->cols[col];
+        const int w = type_width(sc.type);
+        if (w == 0 || sc.mem_kind != SRB_MEM_DEVICE) throw Error(SRB_INVALID_ARGUMENT, "all-gather takes device-resident fixed-width columns");
+        c->recv_data[col].ensure(c->ctx, (size_t)std::max<int64_t>(total, 1) * w);
+        if (sc.nulls) c->recv_null[col].ensure(c->ctx, (size_t)std::max<int64_t>(total, 1));
+        for (int r = 0; r < W; r++) { // one broadcast per root: variable-size all-gather
+            if (hc[W + r] == 0) continue;
+            const void* src = r == c->rank ? sc.data : nullptr;
+            SRB_NCCL(nccl().Broadcast(src ? src : c->recv_data[col].as<uint8_t>() + (size_t)off[r] * w, c->recv_data[col].as<uint8_t>() + (size_t)off[r] * w,
+                                      (size_t)hc[W + r] * w, ncclUint8_, r, c->comm, c->stream));
+            if (sc.nulls) {
+                const void* ns = r == c->rank ? sc.nulls : nullptr;
+                SRB_NCCL(nccl().Broadcast(ns ? ns : c->recv_null[col].as<uint8_t>() + off[r], c->recv_null[col].as<uint8_t>() + off[r], (size_t)hc[W + r],
+                                          ncclUint8_, r, c->comm, c->stream));
+            }
+        }
+        c->cview[col].data = c->recv_data[col].p;
+        c->cview[col].nulls = sc.nulls ? c->recv_null[col].as<uint8_t>() : nullptr;
+    }
+    SRB_NCCL(nccl().GroupEnd());
+    SRB_CUDA(cudaStreamSynchronize(c->stream));
+    out->n_rows = total;
+    out->n_cols = mine->n_cols;
+    out->slot_ids = c->slots.data();
+    out->cols = c->cview.data();
+    return SRB_OK;
+    X_END
+}
+
+} // extern "C"

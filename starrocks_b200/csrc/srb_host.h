@@ -1,0 +1,169 @@
+// srb_host.h — host-side plumbing of libsrb.so: context, operator base class, error convention, device buffers.
+//
+// The operator contract mirrored here is starrocks::pipeline::Operator (be/src/exec/pipeline/operator.h:43-344):
+// push_chunk / pull_chunk / set_finishing / has_output / need_input / is_finished, one thread at a time per
+// operator instance (pipeline_driver.cpp:246). Status codes are TStatusCode values (include/srb/srb_c_api.h).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/srb/srb_c_api.h"
+
+namespace srb {
+
+struct Error : public std::runtime_error {
+    srb_status code;
+    Error(srb_status c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+
+inline std::string fmt(const char* f, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, f);
+    vsnprintf(buf, sizeof(buf), f, ap);
+    va_end(ap);
+    return buf;
+}
+
+#define SRB_CUDA(expr)                                                                                            \
+    do {                                                                                                          \
+        cudaError_t _e = (expr);                                                                                  \
+        if (_e != cudaSuccess)                                                                                    \
+            throw srb::Error(_e == cudaErrorMemoryAllocation ? SRB_MEM_LIMIT_EXCEEDED : SRB_INTERNAL_ERROR,       \
+                             srb::fmt("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__)); \
+    } while (0)
+
+inline int type_width(int t) {
+    switch (t) {
+    case SRB_TYPE_TINYINT:
+    case SRB_TYPE_BOOLEAN: return 1;
+    case SRB_TYPE_SMALLINT: return 2;
+    case SRB_TYPE_INT:
+    case SRB_TYPE_DATE:
+    case SRB_TYPE_DECIMAL32: return 4;
+    case SRB_TYPE_BIGINT:
+    case SRB_TYPE_DECIMAL64:
+    case SRB_TYPE_DOUBLE: return 8;
+    case SRB_TYPE_LARGEINT:
+    case SRB_TYPE_DECIMAL128: return 16;
+    default: return 0;
+    }
+}
+inline bool is_decimal(int t) { return t == SRB_TYPE_DECIMAL32 || t == SRB_TYPE_DECIMAL64 || t == SRB_TYPE_DECIMAL128; }
+inline bool is_binary(int t) { return t == SRB_TYPE_VARCHAR || t == SRB_TYPE_VARBINARY; }
+
+} // namespace srb
+
+struct srb_ctx {
+    srb_config cfg{};
+    int n_sms = 0;
+    int sm_arch = 0;
+    int64_t hbm_bytes = 0;
+    int64_t mem_in_use = 0;
+};
+
+namespace srb {
+
+// RAII device / pinned buffers that charge the ctx's mem_limit
+struct DevBuf {
+    srb_ctx* ctx = nullptr;
+    void* p = nullptr;
+    size_t bytes = 0;
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    DevBuf(DevBuf&& o) noexcept : ctx(o.ctx), p(o.p), bytes(o.bytes) {
+        o.p = nullptr;
+        o.bytes = 0;
+    }
+    ~DevBuf() { release(); }
+    void release() {
+        if (p) {
+            cudaFree(p);
+            if (ctx) ctx->mem_in_use -= (int64_t)bytes;
+        }
+        p = nullptr;
+        bytes = 0;
+    }
+    // (re)allocate when the current capacity is too small; contents are NOT preserved
+    void ensure(srb_ctx* c, size_t n) {
+        if (n <= bytes && p) return;
+        release();
+        ctx = c;
+        if (n == 0) n = 16;
+        if (c->cfg.mem_limit > 0 && c->mem_in_use + (int64_t)n > c->cfg.mem_limit)
+            throw Error(SRB_MEM_LIMIT_EXCEEDED, fmt("device memory limit exceeded: %lld + %zu > %lld", (long long)c->mem_in_use, n,
+                                                    (long long)c->cfg.mem_limit));
+        SRB_CUDA(cudaMalloc(&p, n));
+        bytes = n;
+        c->mem_in_use += (int64_t)n;
+    }
+    template <typename T>
+    T* as() const {
+        return (T*)p;
+    }
+};
+
+struct PinnedBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    PinnedBuf() = default;
+    PinnedBuf(const PinnedBuf&) = delete;
+    PinnedBuf& operator=(const PinnedBuf&) = delete;
+    ~PinnedBuf() {
+        if (p) cudaFreeHost(p);
+    }
+    void ensure(size_t n) {
+        if (n <= bytes && p) return;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        if (n == 0) n = 16;
+        SRB_CUDA(cudaMallocHost(&p, n));
+        bytes = n;
+    }
+    template <typename T>
+    T* as() const {
+        return (T*)p;
+    }
+};
+
+} // namespace srb
+
+// Operator base: the C ABI forwards to these virtuals.
+struct srb_op {
+    srb_ctx* ctx;
+    cudaStream_t stream = nullptr;
+    bool finishing = false, finished = false, cancelled = false;
+    int64_t rows_in = 0, rows_selected = 0, launches = 0;
+    explicit srb_op(srb_ctx* c) : ctx(c) { SRB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)); }
+    virtual ~srb_op() {
+        if (stream) cudaStreamDestroy(stream);
+    }
+    virtual void push_chunk(const srb_chunk* ch) = 0;
+    virtual void set_finishing() = 0;
+    virtual bool has_output() = 0;
+    virtual bool need_input() = 0;
+    virtual bool is_finished() = 0;
+    virtual srb_status pull_chunk(srb_chunk* out, bool all) = 0;
+    virtual srb_status pull_device(srb_chunk*) { throw srb::Error(SRB_NOT_IMPLEMENTED, "device pull not supported by this operator"); }
+    virtual void refresh_counters() {}
+    // join ops override the probe side
+    virtual void probe_push_chunk(const srb_chunk*) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
+    virtual void probe_set_finishing() { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
+    virtual bool probe_has_output() { return false; }
+    virtual bool probe_need_input() { return false; }
+    virtual bool probe_is_finished() { return true; }
+    virtual srb_status probe_pull_chunk(srb_chunk*, bool) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
+    virtual srb_status probe_pull_device(srb_chunk*) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
+};
+
+namespace srb {
+srb_op* make_scan_agg_op(srb_ctx* ctx, const srb_scan_agg_plan* plan);
+srb_op* make_join_op(srb_ctx* ctx, const srb_join_plan* plan);
+} // namespace srb

@@ -1,0 +1,541 @@
+// srb_join.cu — hash join build / probe / late-materialised output (K6 / K7 / K8) and the operator pair around them.
+//
+// Stands in for, and keeps the call contract of:
+//   HashJoinBuildOperator::push_chunk / set_finishing         be/src/exec/pipeline/hashjoin/hash_join_build_operator.cpp:40-213
+//   HashJoinProbeOperator::push_chunk / pull_chunk / need_input / has_output   .../hash_join_probe_operator.cpp:55-104
+//   JoinHashTable::append_chunk (row 0 = dummy, 1-based indexes)               be/src/exec/join_hash_map.cpp:613-642
+//   JoinBuildFunc::prepare / construct_hash_table               be/src/exec/join_hash_map.tpp:29-91
+//   JoinProbeFunc::lookup_init + _do_probe_from_ht (inner)      be/src/exec/join_hash_map.tpp:283-309,1066-1143
+//   serialize_fixed_size_key_column (multi-column fixed keys)   be/src/exec/join_hash_map.h:391-406
+//   _probe_output / _build_output (append_selective by index)   be/src/exec/join_hash_map.tpp:534-550,624-640
+//
+// Table layout is the reference's: first[bucket_size] + next[rows+1] of uint32, bucket = JoinKeyHash(key), bucket_size
+// from calc_bucket_size, build rows numbered from 1 with 0 = end of chain, NULL keys never inserted. What changes is
+// the execution: the build links rows with one atomicExch per row instead of a serial loop; the probe runs one thread
+// per probe row over the whole pushed range (thousands of outstanding loads replace the coroutine interleaving of
+// join_hash_map.tpp:1146-1184) in two passes — count, then warp-aggregated append of (probe_index, build_index) pairs —
+// and payload columns are gathered only for matched rows.
+#include <algorithm>
+#include <cstring>
+
+#include "srb_dev.cuh"
+#include "srb_host.h"
+
+namespace srb {
+
+constexpr int JMAX_KEYS = 4, JMAX_OUT = 16;
+
+struct JKeyCol {
+    const uint8_t* data;
+    const uint8_t* nulls;
+    int32_t width;
+    int32_t _pad;
+};
+struct JPackArgs {
+    int32_t n_keys;
+    int32_t width; // packed width: 4, 8 or 16
+    JKeyCol cols[JMAX_KEYS];
+};
+
+// packs the key columns of rows [0,n) column by column at increasing byte offsets, zero padded to `width`
+__global__ void __launch_bounds__(256) k_join_pack(const __grid_constant__ JPackArgs a, int64_t n, uint8_t* __restrict__ out,
+                                                    uint8_t* __restrict__ out_null) {
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        uint64_t w[2] = {0, 0};
+        int off = 0;
+        uint8_t isnull = 0;
+        for (int k = 0; k < a.n_keys; k++) {
+            const JKeyCol& c = a.cols[k];
+            const uint8_t* p = c.data + (size_t)r * c.width;
+            for (int b = 0; b < c.width; b++, off++) w[off >> 3] |= (uint64_t)p[b] << (8 * (off & 7));
+            if (c.nulls && c.nulls[r]) isnull = 1;
+        }
+        if (a.width == 4)
+            ((uint32_t*)out)[r] = (uint32_t)w[0];
+        else if (a.width == 8)
+            ((uint64_t*)out)[r] = w[0];
+        else
+            ((ulonglong2*)out)[r] = make_ulonglong2(w[0], w[1]);
+        out_null[r] = isnull;
+    }
+}
+
+struct JTable {
+    const uint8_t* keys; // packed build keys, row i (1-based) at index i-1
+    const uint8_t* key_null;
+    uint32_t* first;
+    uint32_t* next;
+    uint32_t bucket_size, log_bucket, rows;
+    int32_t width;
+};
+
+SRB_D uint32_t jbucket(const JTable& t, uint64_t lo, uint64_t hi) {
+    if (t.width == 4) return join_key_hash32((uint32_t)lo, t.log_bucket);
+    if (t.width == 8) return join_key_hash64(lo, t.log_bucket);
+    return join_key_hash128(lo, hi, t.bucket_size);
+}
+SRB_D void jload(const uint8_t* keys, int width, int64_t i, uint64_t* lo, uint64_t* hi) {
+    *hi = 0;
+    if (width == 4)
+        *lo = ((const uint32_t*)keys)[i];
+    else if (width == 8)
+        *lo = ((const uint64_t*)keys)[i];
+    else {
+        ulonglong2 v = ((const ulonglong2*)keys)[i];
+        *lo = v.x;
+        *hi = v.y;
+    }
+}
+
+// K6: next[i] = exchange(first[bucket], i) — the chained table of join_hash_map.tpp:59-91 built in parallel
+__global__ void __launch_bounds__(256) k_join_build(JTable t) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x + 1; i <= t.rows; i += gridDim.x * blockDim.x) {
+        if (t.key_null[i - 1]) continue;
+        uint64_t lo, hi;
+        jload(t.keys, t.width, i - 1, &lo, &hi);
+        uint32_t b = jbucket(t, lo, hi);
+        t.next[i] = atomicExch(&t.first[b], i);
+    }
+}
+
+// K7: mode 0 counts matches (block-reduced into *total); mode 1 appends (probe_index, build_index) pairs
+template <int MODE>
+__global__ void __launch_bounds__(256) k_join_probe(JTable t, const uint8_t* __restrict__ pkeys, const uint8_t* __restrict__ pnull, int64_t n,
+                                                     int semi, unsigned long long* __restrict__ total, uint32_t* __restrict__ out_probe,
+                                                     uint32_t* __restrict__ out_build) {
+    unsigned long long mine = 0;
+    const int lane = threadIdx.x & 31;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t n_round = (n + 31) & ~(int64_t)31; // keep warps converged for the ballots of mode 1
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_round; r += stride) {
+        uint32_t cnt = 0;
+        uint32_t bi = 0;
+        uint64_t lo = 0, hi = 0;
+        if (r < n && !pnull[r]) {
+            jload(pkeys, t.width, r, &lo, &hi);
+            bi = t.first[jbucket(t, lo, hi)];
+        }
+        if (MODE == 0) {
+            while (bi) {
+                uint64_t blo, bhi;
+                jload(t.keys, t.width, bi - 1, &blo, &bhi);
+                if (blo == lo && bhi == hi) {
+                    cnt++;
+                    if (semi) break;
+                }
+                bi = t.next[bi];
+            }
+            mine += cnt;
+        } else {
+            // walk the chain; every match takes a ticket from a warp-aggregated atomic
+            for (;;) {
+                bool hit = false;
+                while (bi) {
+                    uint64_t blo, bhi;
+                    jload(t.keys, t.width, bi - 1, &blo, &bhi);
+                    if (blo == lo && bhi == hi) {
+                        hit = true;
+                        break;
+                    }
+                    bi = t.next[bi];
+                }
+                unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (!m) break;
+                unsigned long long base = 0;
+                int leader = __ffs(m) - 1;
+                if (lane == leader) base = atomicAdd(total, (unsigned long long)__popc(m));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (hit) {
+                    unsigned long long pos = base + __popc(m & ((1u << lane) - 1));
+                    out_probe[pos] = (uint32_t)r;
+                    out_build[pos] = bi; // 1-based, as the reference's build_index
+                    bi = semi ? 0 : t.next[bi];
+                }
+            }
+        }
+    }
+    if (MODE == 0) {
+        for (int o = 16; o > 0; o >>= 1) mine += __shfl_down_sync(0xffffffffu, mine, o);
+        if (lane == 0 && mine) atomicAdd(total, mine);
+    }
+}
+
+// K8: late materialisation — payload columns gathered for matched rows only
+struct GatherCol {
+    const uint8_t* src;
+    uint8_t* dst;
+    const uint8_t* src_null;
+    uint8_t* dst_null;
+    int32_t width;
+    int32_t from_build; // index array to use
+};
+struct GatherArgs {
+    int32_t n_cols;
+    int32_t _pad;
+    GatherCol cols[JMAX_OUT];
+};
+__global__ void __launch_bounds__(256) k_join_gather(const __grid_constant__ GatherArgs g, int64_t n, const uint32_t* __restrict__ probe_idx,
+                                                      const uint32_t* __restrict__ build_idx) {
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t pi = probe_idx[j], bi = build_idx[j] - 1;
+        for (int c = 0; c < g.n_cols; c++) {
+            const GatherCol& gc = g.cols[c];
+            const size_t s = gc.from_build ? bi : pi;
+            switch (gc.width) {
+            case 1: gc.dst[j] = gc.src[s]; break;
+            case 2: ((uint16_t*)gc.dst)[j] = ((const uint16_t*)gc.src)[s]; break;
+            case 4: ((uint32_t*)gc.dst)[j] = ((const uint32_t*)gc.src)[s]; break;
+            case 8: ((uint64_t*)gc.dst)[j] = ((const uint64_t*)gc.src)[s]; break;
+            default: ((ulonglong2*)gc.dst)[j] = ((const ulonglong2*)gc.src)[s];
+            }
+            if (gc.src_null) gc.dst_null[j] = gc.src_null[s];
+        }
+    }
+}
+
+// =================================================================================================================
+struct GrowCol { // device column that grows by appends
+    DevBuf data, nulls;
+    int type = 0, precision = 0, scale = 0, width = 0;
+    bool nullable = false, known = false;
+};
+
+class JoinOp : public srb_op {
+public:
+    JoinOp(srb_ctx* c, const srb_join_plan* p) : srb_op(c) {
+        if (!p) throw Error(SRB_INVALID_ARGUMENT, "null plan");
+        if (p->join_type != SRB_JOIN_INNER && p->join_type != SRB_JOIN_LEFT_SEMI) throw Error(SRB_NOT_IMPLEMENTED, fmt("join type %d", p->join_type));
+        if (p->n_keys < 1 || p->n_keys > JMAX_KEYS) throw Error(SRB_NOT_IMPLEMENTED, fmt("join with %d key columns", p->n_keys));
+        if (p->n_build_out < 0 || p->n_probe_out < 0 || p->n_build_out + p->n_probe_out > JMAX_OUT)
+            throw Error(SRB_NOT_IMPLEMENTED, "too many join output columns");
+        semi_ = p->join_type == SRB_JOIN_LEFT_SEMI;
+        bkeys_.assign(p->build_key_slots, p->build_key_slots + p->n_keys);
+        pkeys_.assign(p->probe_key_slots, p->probe_key_slots + p->n_keys);
+        bout_.assign(p->build_out_slots, p->build_out_slots + p->n_build_out);
+        pout_.assign(p->probe_out_slots, p->probe_out_slots + p->n_probe_out);
+        if (semi_) bout_.clear(); // LEFT SEMI emits probe columns only
+        emit_indexes_ = p->emit_indexes != 0;
+        chunk_size_ = c->cfg.chunk_size > 0 ? c->cfg.chunk_size : 4096;
+        bcols_.resize(bkeys_.size() + bout_.size());
+        total_dev_.ensure(c, 8);
+        total_host_.ensure(8);
+    }
+    ~JoinOp() override { cudaStreamSynchronize(stream); }
+
+    // ---- build side ---------------------------------------------------------------------------------------------
+    void push_chunk(const srb_chunk* ch) override {
+        if (finishing) throw Error(SRB_INTERNAL_ERROR, "push_chunk after set_finishing");
+        if (!ch || ch->n_rows < 0) throw Error(SRB_INVALID_ARGUMENT, "bad chunk");
+        if (ch->n_rows == 0) return;
+        if ((uint64_t)build_rows_ + (uint64_t)ch->n_rows >= ((uint64_t)1 << 32) - 1)
+            throw Error(SRB_NOT_IMPLEMENTED, "build side exceeds 2^32 rows (uint32 first/next, join_hash_map.h:101-120)");
+        for (size_t i = 0; i < bcols_.size(); i++) {
+            int slot = i < bkeys_.size() ? bkeys_[i] : bout_[i - bkeys_.size()];
+            append_col(bcols_[i], find_or_throw(ch, slot), slot, build_rows_, ch->n_rows);
+        }
+        build_rows_ += ch->n_rows;
+        rows_in += ch->n_rows;
+    }
+
+    void set_finishing() override {
+        if (finishing) return;
+        finishing = true;
+        // packed key width from the declared key column widths (join_hash_map.h:391-406)
+        int total = 0;
+        for (size_t k = 0; k < bkeys_.size(); k++) {
+            if (!bcols_[k].known) { // empty build side: widths come from the probe side later
+                total = -1;
+                break;
+            }
+            total += bcols_[k].width;
+        }
+        if (total > 16) throw Error(SRB_NOT_IMPLEMENTED, "packed join key wider than 16 bytes");
+        if (total > 0) {
+            width_ = total <= 4 ? 4 : (total <= 8 ? 8 : 16);
+            build_table();
+        }
+        build_done_ = true;
+    }
+    bool has_output() override { return false; }
+    bool need_input() override { return !finishing; }
+    bool is_finished() override { return finishing; }
+    srb_status pull_chunk(srb_chunk*, bool) override { return SRB_END_OF_FILE; }
+
+    // ---- probe side ----------------------------------------------------------------------------------------------
+    bool probe_need_input() override { return build_done_ && !probe_finishing_ && out_pos_ >= out_rows_; }
+    bool probe_has_output() override { return out_pos_ < out_rows_; }
+    bool probe_is_finished() override { return probe_finishing_ && out_pos_ >= out_rows_; }
+    void probe_set_finishing() override { probe_finishing_ = true; }
+
+    void probe_push_chunk(const srb_chunk* ch) override {
+        if (!build_done_) throw Error(SRB_INTERNAL_ERROR, "probe before the build side finished (need_input() is false)");
+        if (probe_finishing_) throw Error(SRB_INTERNAL_ERROR, "probe push after set_finishing");
+        if (out_pos_ < out_rows_) throw Error(SRB_INTERNAL_ERROR, "probe push while output is pending (need_input() is false)");
+        if (!ch || ch->n_rows < 0) throw Error(SRB_INVALID_ARGUMENT, "bad chunk");
+        if (ch->n_rows >= ((int64_t)1 << 32)) throw Error(SRB_INVALID_ARGUMENT, "chunk exceeds 2^32 rows");
+        out_rows_ = out_pos_ = 0;
+        probe_rows_in_ += ch->n_rows;
+        const int64_t n = ch->n_rows;
+        // stage probe key + output columns on the device (device columns are used in place)
+        pcols_.resize(pkeys_.size() + pout_.size());
+        std::vector<const uint8_t*> data(pcols_.size()), nulls(pcols_.size());
+        int total = 0;
+        for (size_t i = 0; i < pcols_.size(); i++) {
+            int slot = i < pkeys_.size() ? pkeys_[i] : pout_[i - pkeys_.size()];
+            const srb_column* c = find_or_throw(ch, slot);
+            GrowCol& g = pcols_[i];
+            describe(g, c, slot);
+            if (c->mem_kind == SRB_MEM_DEVICE) {
+                data[i] = (const uint8_t*)c->data;
+                nulls[i] = c->nulls;
+            } else {
+                g.data.ensure(ctx, (size_t)n * g.width);
+                if (n) SRB_CUDA(cudaMemcpyAsync(g.data.p, c->data, (size_t)n * g.width, cudaMemcpyHostToDevice, stream));
+                data[i] = g.data.as<uint8_t>();
+                nulls[i] = nullptr;
+                if (c->nulls) {
+                    g.nulls.ensure(ctx, (size_t)n);
+                    if (n) SRB_CUDA(cudaMemcpyAsync(g.nulls.p, c->nulls, (size_t)n, cudaMemcpyHostToDevice, stream));
+                    nulls[i] = g.nulls.as<uint8_t>();
+                }
+            }
+            if (i < pkeys_.size()) total += g.width;
+        }
+        if (n == 0 || build_rows_ == 0) return;
+        int pw = total <= 4 ? 4 : (total <= 8 ? 8 : 16);
+        if (total > 16 || pw != width_) throw Error(SRB_INVALID_ARGUMENT, "probe key width does not match the build key width");
+        // pack probe keys
+        JPackArgs pa{};
+        pa.n_keys = (int)pkeys_.size();
+        pa.width = width_;
+        for (size_t k = 0; k < pkeys_.size(); k++) pa.cols[k] = JKeyCol{data[k], nulls[k], pcols_[k].width, 0};
+        ppacked_.ensure(ctx, (size_t)n * width_);
+        pnull_.ensure(ctx, (size_t)n);
+        int grid = grid_for(n);
+        k_join_pack<<<grid, 256, 0, stream>>>(pa, n, ppacked_.as<uint8_t>(), pnull_.as<uint8_t>());
+        // pass 1: count
+        JTable t = table();
+        SRB_CUDA(cudaMemsetAsync(total_dev_.p, 0, 8, stream));
+        k_join_probe<0><<<grid, 256, 0, stream>>>(t, ppacked_.as<uint8_t>(), pnull_.as<uint8_t>(), n, semi_ ? 1 : 0,
+                                                   total_dev_.as<unsigned long long>(), nullptr, nullptr);
+        SRB_CUDA(cudaMemcpyAsync(total_host_.p, total_dev_.p, 8, cudaMemcpyDeviceToHost, stream));
+        SRB_CUDA(cudaMemsetAsync(total_dev_.p, 0, 8, stream));
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        launches += 2;
+        const int64_t m = (int64_t)*total_host_.as<unsigned long long>();
+        rows_selected += m;
+        if (m == 0) return;
+        if (m >= ((int64_t)1 << 32)) throw Error(SRB_NOT_IMPLEMENTED, "join output of one probe chunk exceeds 2^32 rows; push smaller chunks");
+        // pass 2: append pairs
+        oprobe_.ensure(ctx, (size_t)m * 4);
+        obuild_.ensure(ctx, (size_t)m * 4);
+        k_join_probe<1><<<grid, 256, 0, stream>>>(t, ppacked_.as<uint8_t>(), pnull_.as<uint8_t>(), n, semi_ ? 1 : 0,
+                                                   total_dev_.as<unsigned long long>(), oprobe_.as<uint32_t>(), obuild_.as<uint32_t>());
+        launches++;
+        // K8 gather
+        GatherArgs ga{};
+        ocols_.resize(pout_.size() + bout_.size());
+        for (size_t i = 0; i < ocols_.size(); i++) {
+            bool fb = i >= pout_.size();
+            const GrowCol& src = fb ? bcols_[bkeys_.size() + (i - pout_.size())] : pcols_[pkeys_.size() + i];
+            GrowCol& o = ocols_[i];
+            o.type = src.type;
+            o.precision = src.precision;
+            o.scale = src.scale;
+            o.width = src.width;
+            o.known = true;
+            const uint8_t* sdata = fb ? src.data.as<uint8_t>() : data[pkeys_.size() + i];
+            const uint8_t* snull = fb ? (src.nullable ? src.nulls.as<uint8_t>() : nullptr) : nulls[pkeys_.size() + i];
+            o.nullable = snull != nullptr;
+            o.data.ensure(ctx, (size_t)m * o.width);
+            if (o.nullable) o.nulls.ensure(ctx, (size_t)m);
+            ga.cols[i] = GatherCol{sdata, o.data.as<uint8_t>(), snull, o.nullable ? o.nulls.as<uint8_t>() : nullptr, o.width, fb ? 1 : 0};
+        }
+        ga.n_cols = (int)ocols_.size();
+        if (ga.n_cols) {
+            k_join_gather<<<grid_for(m), 256, 0, stream>>>(ga, m, oprobe_.as<uint32_t>(), obuild_.as<uint32_t>());
+            launches++;
+        }
+        SRB_CUDA(cudaGetLastError());
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        out_rows_ = m;
+    }
+
+    srb_status probe_pull_chunk(srb_chunk* out, bool all) override { return pull(out, all, false); }
+    srb_status probe_pull_device(srb_chunk* out) override { return pull(out, true, true); }
+
+    void refresh_counters() override {}
+
+private:
+    srb_status pull(srb_chunk* out, bool all, bool device) {
+        if (out_pos_ >= out_rows_) {
+            // a harness pulling "all" gets one empty, typed chunk when nothing was ever produced; otherwise done
+            if (!(all && !gave_empty_)) return SRB_END_OF_FILE;
+        }
+        int64_t n = out_rows_ - out_pos_;
+        if (!all && n > chunk_size_) n = chunk_size_;
+        gave_empty_ = true;
+        hslots_.clear();
+        cview_.clear();
+        size_t nc = pout_.size() + bout_.size() + (emit_indexes_ ? 2 : 0);
+        hdata_.resize(nc);
+        hnull_.resize(nc);
+        for (size_t i = 0; i < nc; i++) {
+            srb_column c{};
+            const uint8_t* ddata;
+            const uint8_t* dnull = nullptr;
+            int w;
+            if (i < pout_.size() + bout_.size()) {
+                if (i >= ocols_.size() || !ocols_[i].known) { // nothing was ever produced: describe from the inputs
+                    const GrowCol* src = i < pout_.size() ? (pkeys_.size() + i < pcols_.size() ? &pcols_[pkeys_.size() + i] : nullptr)
+                                                          : &bcols_[bkeys_.size() + (i - pout_.size())];
+                    c.type = src ? src->type : SRB_TYPE_BIGINT;
+                    c.precision = src ? src->precision : 0;
+                    c.scale = src ? src->scale : 0;
+                    w = type_width(c.type);
+                    ddata = nullptr;
+                } else {
+                    const GrowCol& o = ocols_[i];
+                    c.type = o.type;
+                    c.precision = o.precision;
+                    c.scale = o.scale;
+                    w = o.width;
+                    ddata = o.data.as<uint8_t>();
+                    dnull = o.nullable ? o.nulls.as<uint8_t>() : nullptr;
+                }
+                hslots_.push_back(i < pout_.size() ? pout_[i] : bout_[i - pout_.size()]);
+            } else {
+                bool is_probe = i == pout_.size() + bout_.size();
+                c.type = SRB_TYPE_INT;
+                w = 4;
+                ddata = n ? (is_probe ? oprobe_.as<uint8_t>() : obuild_.as<uint8_t>()) : nullptr;
+                hslots_.push_back(is_probe ? -4 : -3); // HASH_JOIN_PROBE_INDEX_SLOT_ID / HASH_JOIN_BUILD_INDEX_SLOT_ID
+            }
+            if (device) {
+                c.mem_kind = SRB_MEM_DEVICE;
+                c.data = ddata ? ddata + (size_t)out_pos_ * w : nullptr;
+                c.nulls = dnull ? dnull + out_pos_ : nullptr;
+            } else {
+                c.mem_kind = SRB_MEM_HOST;
+                hdata_[i].resize((size_t)n * w + 16);
+                if (n && ddata) SRB_CUDA(cudaMemcpyAsync(hdata_[i].data(), ddata + (size_t)out_pos_ * w, (size_t)n * w, cudaMemcpyDeviceToHost, stream));
+                c.data = hdata_[i].data();
+                if (dnull) {
+                    hnull_[i].resize((size_t)n + 16);
+                    if (n) SRB_CUDA(cudaMemcpyAsync(hnull_[i].data(), dnull + out_pos_, (size_t)n, cudaMemcpyDeviceToHost, stream));
+                    c.nulls = hnull_[i].data();
+                }
+            }
+            cview_.push_back(c);
+        }
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        out_pos_ += n;
+        out->n_rows = n;
+        out->n_cols = (int32_t)cview_.size();
+        out->slot_ids = hslots_.data();
+        out->cols = cview_.data();
+        return SRB_OK;
+    }
+
+    static const srb_column* find_or_throw(const srb_chunk* ch, int slot) {
+        for (int i = 0; i < ch->n_cols; i++)
+            if (ch->slot_ids[i] == slot) return &ch->cols[i];
+        throw Error(SRB_INVALID_ARGUMENT, fmt("slot %d not in chunk", slot));
+    }
+    void describe(GrowCol& g, const srb_column* c, int slot) {
+        int w = type_width(c->type);
+        if (w == 0) throw Error(SRB_NOT_IMPLEMENTED, fmt("slot %d: binary columns are not supported by the join yet", slot));
+        if (g.known && g.type != c->type) throw Error(SRB_INVALID_ARGUMENT, fmt("slot %d changed type", slot));
+        g.type = c->type;
+        g.precision = c->precision;
+        g.scale = c->scale;
+        g.width = w;
+        g.known = true;
+    }
+    void append_col(GrowCol& g, const srb_column* c, int slot, int64_t have, int64_t n) {
+        describe(g, c, slot);
+        size_t need = (size_t)(have + n) * g.width;
+        if (need > g.data.bytes) regrow(g.data, (size_t)have * g.width, std::max(need, g.data.bytes * 2));
+        SRB_CUDA(cudaMemcpyAsync(g.data.as<uint8_t>() + (size_t)have * g.width, c->data, (size_t)n * g.width,
+                                 c->mem_kind == SRB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, stream));
+        if (c->nulls && !g.nullable) { // first null map: earlier rows were all non-null
+            g.nullable = true;
+            regrow(g.nulls, 0, (size_t)std::max<int64_t>(have + n, 1024));
+            SRB_CUDA(cudaMemsetAsync(g.nulls.p, 0, (size_t)have, stream));
+        }
+        if (g.nullable) {
+            if ((size_t)(have + n) > g.nulls.bytes) regrow(g.nulls, (size_t)have, std::max((size_t)(have + n), g.nulls.bytes * 2));
+            if (c->nulls)
+                SRB_CUDA(cudaMemcpyAsync(g.nulls.as<uint8_t>() + have, c->nulls, (size_t)n,
+                                         c->mem_kind == SRB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, stream));
+            else
+                SRB_CUDA(cudaMemsetAsync(g.nulls.as<uint8_t>() + have, 0, (size_t)n, stream));
+        }
+        if (c->mem_kind != SRB_MEM_DEVICE) SRB_CUDA(cudaStreamSynchronize(stream)); // pageable source may be reused by the caller
+    }
+    void regrow(DevBuf& b, size_t used, size_t ncap) {
+        DevBuf nb;
+        nb.ensure(ctx, ncap);
+        if (used) SRB_CUDA(cudaMemcpyAsync(nb.p, b.p, used, cudaMemcpyDeviceToDevice, stream));
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        std::swap(b.p, nb.p);
+        std::swap(b.bytes, nb.bytes);
+        nb.ctx = ctx;
+        b.ctx = ctx;
+    }
+    int grid_for(int64_t n) const { return (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, (int64_t)ctx->n_sms * 8)); }
+
+    void build_table() {
+        const int64_t n = build_rows_;
+        JPackArgs pa{};
+        pa.n_keys = (int)bkeys_.size();
+        pa.width = width_;
+        for (size_t k = 0; k < bkeys_.size(); k++)
+            pa.cols[k] = JKeyCol{bcols_[k].data.as<uint8_t>(), bcols_[k].nullable ? bcols_[k].nulls.as<uint8_t>() : nullptr, bcols_[k].width, 0};
+        bpacked_.ensure(ctx, (size_t)std::max<int64_t>(n, 1) * width_);
+        bnull_.ensure(ctx, (size_t)std::max<int64_t>(n, 1));
+        bucket_size_ = calc_bucket_size((uint32_t)n + 1);
+        log_bucket_ = (uint32_t)__builtin_ctz(bucket_size_);
+        first_.ensure(ctx, (size_t)bucket_size_ * 4);
+        next_.ensure(ctx, (size_t)(n + 1) * 4);
+        SRB_CUDA(cudaMemsetAsync(first_.p, 0, (size_t)bucket_size_ * 4, stream));
+        SRB_CUDA(cudaMemsetAsync(next_.p, 0, (size_t)(n + 1) * 4, stream));
+        if (n > 0) {
+            k_join_pack<<<grid_for(n), 256, 0, stream>>>(pa, n, bpacked_.as<uint8_t>(), bnull_.as<uint8_t>());
+            k_join_build<<<grid_for(n), 256, 0, stream>>>(table());
+            launches += 2;
+        }
+        SRB_CUDA(cudaGetLastError());
+        SRB_CUDA(cudaStreamSynchronize(stream));
+    }
+    JTable table() {
+        JTable t;
+        t.keys = bpacked_.as<uint8_t>();
+        t.key_null = bnull_.as<uint8_t>();
+        t.first = first_.as<uint32_t>();
+        t.next = next_.as<uint32_t>();
+        t.bucket_size = bucket_size_;
+        t.log_bucket = log_bucket_;
+        t.rows = (uint32_t)build_rows_;
+        t.width = width_;
+        return t;
+    }
+
+    bool semi_ = false, emit_indexes_ = false, build_done_ = false, probe_finishing_ = false, gave_empty_ = false;
+    std::vector<int32_t> bkeys_, pkeys_, bout_, pout_;
+    int64_t chunk_size_;
+    std::vector<GrowCol> bcols_, pcols_, ocols_;
+    int64_t build_rows_ = 0, probe_rows_in_ = 0;
+    int width_ = 0;
+    uint32_t bucket_size_ = 0, log_bucket_ = 0;
+    DevBuf bpacked_, bnull_, first_, next_, ppacked_, pnull_, oprobe_, obuild_, total_dev_;
+    PinnedBuf total_host_;
+    int64_t out_rows_ = 0, out_pos_ = 0;
+    std::vector<std::vector<uint8_t>> hdata_, hnull_;
+    std::vector<int32_t> hslots_;
+    std::vector<srb_column> cview_;
+};
+
+srb_op* make_join_op(srb_ctx* ctx, const srb_join_plan* plan) { return new JoinOp(ctx, plan); }
+
+} // namespace srb

@@ -1,0 +1,116 @@
+// srb_prog.h — the lowered, device-readable form of an srb_scan_agg_plan ("program"), shared by host and device.
+//
+// The host lowers the plan (flattened Expr tree + predicates + aggregate list, include/srb/srb_c_api.h) once per
+// operator: slot ids become indexes into a bound-column array, decimal typing decisions (fast-mul, scale
+// adjustment factors, overflow -> NULL) are resolved into explicit node fields, and the aggregate states get their
+// byte offsets inside a group-table slot. Kernels either interpret this program (runtime form) or are instantiated
+// on a compile-time copy of the same structures (static shapes, srb_shapes.cuh) so the interpreter folds away.
+#pragma once
+#include <cstdint>
+
+#include "srb_dev.cuh"
+
+namespace srb {
+
+constexpr int MAX_COLS = 16;
+constexpr int MAX_NODES = 24;
+constexpr int MAX_PREDS = 16;
+constexpr int MAX_KEYS = 8;
+constexpr int MAX_AGGS = 12;
+
+// column kinds
+constexpr int CK_INT = 0, CK_DOUBLE = 1, CK_BINARY = 2;
+
+struct ColBind {
+    const void* data;
+    const uint8_t* nulls;    // may be null
+    const uint32_t* offsets; // binary only
+    int32_t width;           // 1,2,4,8,16 (0 for binary)
+    int32_t kind;
+};
+
+// node ops (device level)
+constexpr int DOP_LOAD = 1, DOP_LIT = 2, DOP_CAST = 3, DOP_ADD = 4, DOP_SUB = 5, DOP_MUL = 6, DOP_MULFAST = 7;
+
+struct DNode {
+    int32_t op;
+    int32_t width;   // result width in bytes (1,2,4,8,16)
+    int32_t lhs, rhs;
+    int32_t col;     // DOP_LOAD
+    int32_t checked; // decimal semantics: overflow -> NULL; otherwise wraps in `width`
+    int32_t adj_l, adj_r; // ADD/SUB: operand must be multiplied (checked) by fl / fr first
+    int32_t kind;    // CK_* of the value
+    int32_t _pad;
+    uint64_t lit_lo; // LIT value / CAST factor
+    int64_t lit_hi;
+    uint64_t fl_lo; // scale factor of the left operand
+    int64_t fl_hi;
+    uint64_t fr_lo;
+    int64_t fr_hi;
+};
+
+struct DPred {
+    int32_t col;
+    int32_t op;    // SRB_PRED_*
+    int32_t group; // 0 = conjunct; otherwise OR-group id (groups are contiguous after lowering)
+    int32_t _pad;
+    uint64_t lit_lo;
+    int64_t lit_hi;
+};
+
+// aggregate functions, same codes as SRB_AGG_*
+constexpr int FN_SUM = 1, FN_AVG = 2, FN_COUNT = 3, FN_MIN = 4, FN_MAX = 5;
+
+struct DAgg {
+    int32_t fn;
+    int32_t arg;       // node index, -1 = count(*)
+    int32_t is_double; // state holds a double in `lo`
+    int32_t avg_as_double; // AVG over plain integers accumulates in double (avg.h:49-53)
+    int32_t merge;     // 1: the argument is an intermediate state column (phase-2 merge)
+    int32_t blob_col;  // merge of AVG: bound column index of the VARBINARY {sum,count} blobs
+    int32_t off_lo, off_hi, off_n; // byte offsets inside a slot; -1 = field not kept
+    int32_t wide;      // MIN/MAX compares 128-bit (lo,hi) pairs
+};
+
+struct DKey {
+    int32_t node;     // must be a DOP_LOAD node
+    int32_t nullable; // contributes a leading null byte
+    int32_t width;    // fixed width; 0 = binary ([u32 len][bytes])
+    int32_t _pad;
+};
+
+struct DProg {
+    int32_t n_cols, n_nodes, n_preds, n_keys, n_aggs;
+    int32_t phase_seed;  // 1 or 2: which phmap seed the table hash uses (agg_hash_variant.h:303-308)
+    int32_t key_bytes;   // fixed packed key length, 0 when a binary key makes it per-row
+    int32_t key_words;   // 1 or 2 (8- or 16-byte key area in a slot)
+    int32_t slot_bytes;  // stride of one table slot
+    int32_t off_key;     // byte offset of the key area
+    int32_t _pad[2];
+    ColBind cols[MAX_COLS];
+    DNode nodes[MAX_NODES];
+    DPred preds[MAX_PREDS];
+    DKey keys[MAX_KEYS];
+    DAgg aggs[MAX_AGGS];
+};
+
+// one evaluated value in a row pipeline
+struct Val {
+    uint64_t lo;
+    int64_t hi;
+    bool null;
+};
+
+// slot meta word: low 2 bits = state, rest = hash tag
+constexpr uint64_t SLOT_EMPTY = 0, SLOT_CLAIMED = 1, SLOT_READY = 3;
+
+struct TableView {
+    uint8_t* slots;
+    uint64_t mask; // capacity - 1
+    uint64_t limit; // occupied slots allowed before rows are deferred
+    unsigned long long* occupied;
+    int32_t slot_bytes;
+    int32_t key_words;
+};
+
+} // namespace srb

@@ -1,0 +1,1196 @@
+// srb_scan_agg.cu — the fused scan-filter -> project -> aggregate operator (one driver's operator instance).
+//
+// Stands in for, and keeps the call contract of:
+//   OlapChunkSource::_read_chunk_from_storage predicate part    be/src/exec/pipeline/scan/olap_chunk_source.cpp:586-624
+//   Chunk::filter / ColumnHelper::t_filter_range                be/src/column/chunk.cpp:302, column/column_helper.h:468-577
+//   AggregateBlockingSinkOperator::push_chunk / set_finishing   be/src/exec/pipeline/aggregate/aggregate_blocking_sink_operator.cpp:51-134
+//   AggregateBlockingSourceOperator::pull_chunk                 be/src/exec/pipeline/aggregate/aggregate_blocking_source_operator.cpp:47-72
+//   Aggregator::build_hash_map / compute_*_agg_states / convert_hash_map_to_chunk   be/src/exec/aggregator.cpp:833-959,1357-1514
+//
+// Design (B200-first): whole column ranges per launch instead of 4096-row chunks; predicates, expressions, key packing,
+// table probe and state update fused in one kernel so no intermediate column ever touches HBM; the group table is an
+// open-addressing table in HBM updated with 64-bit atomics (int128 sums as lo/hi words with carry); recognised program
+// shapes run on statically specialised kernels with TMA-staged column tiles and register pre-aggregation
+// (srb_shapes.cuh). There is no CPU path: every row is processed by a CUDA kernel.
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+
+#include "srb_host.h"
+#include "srb_lower.h"
+#include "srb_rowpipe.cuh"
+#include "srb_shapes.cuh"
+
+namespace srb {
+
+struct Counters {
+    unsigned long long rows_selected;
+    unsigned long long deferred;
+    unsigned long long key_too_long;
+    unsigned long long emitted;
+};
+
+// ---- generic kernel: interprets the lowered program, one row per thread iteration ---------------------------
+struct LocalAcc {
+    uint64_t lo, hi, n;
+};
+
+SRB_D void update_agg_local(const DProg& p, const DAgg& g, LocalAcc& s, const Val* v, int64_t row) {
+    if (g.fn == FN_COUNT) {
+        if (g.merge) {
+            if (!v[g.arg].null) s.n += v[g.arg].lo;
+        } else if (g.arg < 0 || !v[g.arg].null)
+            s.n++;
+        return;
+    }
+    if (g.merge && g.fn == FN_AVG) {
+        const ColBind& c = p.cols[g.blob_col];
+        if (c.nulls && c.nulls[row]) return;
+        uint32_t b = c.offsets[row], e = c.offsets[row + 1];
+        const uint8_t* ptr = (const uint8_t*)c.data + b;
+        if (e - b == 24) {
+            u128 sum = (u128)make_i128(s.lo, (int64_t)s.hi) + (u128)make_i128(load_u64_le(ptr), (int64_t)load_u64_le(ptr + 8));
+            s.lo = (uint64_t)sum;
+            s.hi = (uint64_t)(sum >> 64);
+            s.n += load_u64_le(ptr + 16);
+        } else if (e - b == 16) {
+            double d = __longlong_as_double((long long)s.lo) + __longlong_as_double((long long)load_u64_le(ptr));
+            s.lo = (uint64_t)__double_as_longlong(d);
+            s.n += load_u64_le(ptr + 8);
+        }
+        return;
+    }
+    const Val& x = v[g.arg];
+    if (x.null) return;
+    if (g.fn == FN_SUM || g.fn == FN_AVG) {
+        if (g.is_double || g.avg_as_double) {
+            double add = g.is_double ? __longlong_as_double((long long)x.lo) : (double)(int64_t)x.lo;
+            s.lo = (uint64_t)__double_as_longlong(__longlong_as_double((long long)s.lo) + add);
+        } else {
+            u128 sum = (u128)make_i128(s.lo, (int64_t)s.hi) + (u128)make_i128(x.lo, x.hi);
+            s.lo = (uint64_t)sum;
+            s.hi = (uint64_t)(sum >> 64);
+        }
+    } else {
+        const bool mn = g.fn == FN_MIN;
+        if (g.is_double) {
+            double c = __longlong_as_double((long long)s.lo), d = __longlong_as_double((long long)x.lo);
+            if (s.n == 0 || (mn ? d < c : d > c)) s.lo = x.lo;
+        } else {
+            i128 c = make_i128(s.lo, (int64_t)s.hi), d = make_i128(x.lo, x.hi);
+            if (s.n == 0 || (mn ? d < c : d > c)) {
+                s.lo = x.lo;
+                s.hi = (uint64_t)x.hi;
+            }
+        }
+    }
+    s.n++;
+}
+
+// merges one thread's private accumulator into the (single) global state block
+SRB_D void flush_local(const DAgg& g, const LocalAcc& s, uint8_t* slot) {
+    if (s.n == 0) return;
+    if (g.fn == FN_COUNT) {
+        atomicAdd((unsigned long long*)(slot + g.off_n), (unsigned long long)s.n);
+        return;
+    }
+    if (g.fn == FN_SUM || g.fn == FN_AVG) {
+        if (g.is_double || g.avg_as_double)
+            atomicAdd((double*)(slot + g.off_lo), __longlong_as_double((long long)s.lo));
+        else
+            atomic_add128(slot, g.off_lo, g.off_hi, s.lo, s.hi);
+    } else {
+        const bool mn = g.fn == FN_MIN;
+        if (g.is_double)
+            atomic_minmax_f64(slot, g.off_lo, mn, __longlong_as_double((long long)s.lo));
+        else if (g.wide)
+            atomic_minmax128(slot, g.off_lo, mn, make_i128(s.lo, (int64_t)s.hi));
+        else if (mn)
+            atomicMin((long long*)(slot + g.off_lo), (long long)s.lo);
+        else
+            atomicMax((long long*)(slot + g.off_lo), (long long)s.lo);
+    }
+    if (g.off_n >= 0) atomicAdd((unsigned long long*)(slot + g.off_n), (unsigned long long)s.n);
+}
+
+__global__ void __launch_bounds__(256) k_scan_agg_generic(const __grid_constant__ DProg prog, const TableView tv, const int64_t base,
+                                                           const int64_t n, const int64_t bit_base, const uint32_t* __restrict__ defer_in,
+                                                           uint32_t* __restrict__ defer_out, Counters* __restrict__ ctr) {
+    const DProg& p = prog;
+    Val v[MAX_NODES];
+    LocalAcc acc[MAX_AGGS];
+    const bool no_keys = p.n_keys == 0;
+    if (no_keys)
+        for (int a = 0; a < p.n_aggs; a++) acc[a] = LocalAcc{0, 0, 0};
+    unsigned long long selected = 0, deferred = 0, too_long = 0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const int64_t bit = i + bit_base; // position of this row in the batch's deferral bitmaps
+        if (defer_in && !((defer_in[bit >> 5] >> (bit & 31)) & 1u)) continue;
+        const int64_t row = base + i;
+        if (!eval_preds(p, row)) continue;
+        if (!defer_in) selected++;
+        for (int k = 0; k < p.n_nodes; k++) v[k] = eval_node(p.nodes[k], v, p.cols, row);
+        if (no_keys) {
+            for (int a = 0; a < p.n_aggs; a++) update_agg_local(p, p.aggs[a], acc[a], v, row);
+            continue;
+        }
+        PackedKey k = pack_key(p, v, row);
+        if (k.too_long) {
+            too_long++;
+            continue;
+        }
+        uint8_t* slot = table_find_or_insert(tv, p, k.lo, k.hi, hash_packed_key(k, p.phase_seed));
+        if (!slot) {
+            atomicOr(&defer_out[bit >> 5], 1u << (bit & 31));
+            deferred++;
+            continue;
+        }
+        for (int a = 0; a < p.n_aggs; a++) update_agg_global(p, p.aggs[a], slot, v, row);
+    }
+    if (no_keys)
+        for (int a = 0; a < p.n_aggs; a++) flush_local(p.aggs[a], acc[a], tv.slots);
+    // one atomic per warp for the counters
+    for (int o = 16; o > 0; o >>= 1) {
+        selected += __shfl_down_sync(0xffffffffu, selected, o);
+        deferred += __shfl_down_sync(0xffffffffu, deferred, o);
+        too_long += __shfl_down_sync(0xffffffffu, too_long, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (selected) atomicAdd(&ctr->rows_selected, selected);
+        if (deferred) atomicAdd(&ctr->deferred, deferred);
+        if (too_long) atomicAdd(&ctr->key_too_long, too_long);
+    }
+}
+
+__global__ void k_init_slot0(const __grid_constant__ DProg prog, uint8_t* slot) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        *(uint64_t*)slot = SLOT_READY;
+        init_slot_states(prog, slot);
+    }
+}
+
+// moves every ready slot of the old table into the (empty, larger) new one; keys are unique so no state merging
+__global__ void k_rehash(const __grid_constant__ DProg prog, const uint8_t* __restrict__ old_slots, uint64_t old_cap, TableView nt) {
+    const DProg& p = prog;
+    const int sb = p.slot_bytes;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < old_cap; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint8_t* s = old_slots + i * sb;
+        uint64_t m = *(const uint64_t*)s;
+        if ((m & 3ULL) != SLOT_READY) continue;
+        uint64_t idx = ((m & ~3ULL) >> 7) & nt.mask; // tag keeps hash bits 2..63, enough to recompute the home bucket
+        for (;;) {
+            uint8_t* d = nt.slots + idx * (uint64_t)sb;
+            uint64_t old = atomicCAS((unsigned long long*)d, 0ULL, (unsigned long long)m);
+            if (old == SLOT_EMPTY) {
+                for (int b = 8; b < sb; b += 8) *(uint64_t*)(d + b) = *(const uint64_t*)(s + b);
+                break;
+            }
+            idx = (idx + 1) & nt.mask;
+        }
+    }
+}
+
+// ---- emit: table -> columnar result (K5), with AVG finalisation on the device --------------------------------
+struct EmitAgg {
+    void* val;      // out_width bytes per row (blob: the sum part)
+    uint8_t* null;  // may be nullptr (COUNT)
+    int64_t* cnt;   // blob only
+    int32_t out_width;
+    int32_t mode;   // 0 count, 1 raw state (sum/min/max/blob sum), 2 avg decimal, 3 avg date, 4 avg largeint->double, 5 avg double
+    int32_t scale;  // avg decimal: argument scale
+    int32_t _pad;
+};
+struct EmitArgs {
+    ulonglong2* keys;
+    EmitAgg aggs[MAX_AGGS];
+};
+
+SRB_D void store_w(void* base, int64_t row, int w, uint64_t lo, uint64_t hi) {
+    switch (w) {
+    case 1: ((uint8_t*)base)[row] = (uint8_t)lo; break;
+    case 2: ((uint16_t*)base)[row] = (uint16_t)lo; break;
+    case 4: ((uint32_t*)base)[row] = (uint32_t)lo; break;
+    case 8: ((uint64_t*)base)[row] = lo; break;
+    default: ((ulonglong2*)base)[row] = make_ulonglong2(lo, hi);
+    }
+}
+
+__global__ void k_emit(const __grid_constant__ DProg prog, const uint8_t* __restrict__ slots, uint64_t cap, const __grid_constant__ EmitArgs ea,
+                       Counters* __restrict__ ctr) {
+    const DProg& p = prog;
+    const int sb = p.slot_bytes;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < cap; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint8_t* s = slots + i * sb;
+        if (((*(const uint64_t*)s) & 3ULL) != SLOT_READY) continue;
+        // warp-aggregated ticket
+        unsigned m = __activemask();
+        int leader = __ffs(m) - 1, lane = threadIdx.x & 31;
+        unsigned long long basepos = 0;
+        if (lane == leader) basepos = atomicAdd(&ctr->emitted, (unsigned long long)__popc(m));
+        basepos = __shfl_sync(m, basepos, leader);
+        int64_t row = (int64_t)(basepos + __popc(m & ((1u << lane) - 1)));
+        if (p.n_keys) {
+            const uint64_t* k = (const uint64_t*)(s + p.off_key);
+            ea.keys[row] = make_ulonglong2(k[0], p.key_words > 1 ? k[1] : 0ULL);
+        }
+        for (int a = 0; a < p.n_aggs; a++) {
+            const DAgg& g = p.aggs[a];
+            const EmitAgg& e = ea.aggs[a];
+            uint64_t n = g.off_n >= 0 ? *(const uint64_t*)(s + g.off_n) : 1;
+            uint64_t lo = g.off_lo >= 0 ? *(const uint64_t*)(s + g.off_lo) : 0;
+            uint64_t hi = g.off_hi >= 0 ? *(const uint64_t*)(s + g.off_hi) : (uint64_t)((int64_t)lo >> 63);
+            bool isnull = e.null != nullptr && n == 0;
+            if (e.null) e.null[row] = isnull ? 1 : 0;
+            if (e.cnt) e.cnt[row] = (int64_t)n;
+            if (isnull) {
+                store_w(e.val, row, e.out_width, 0, 0);
+                continue;
+            }
+            switch (e.mode) {
+            case 0: store_w(e.val, row, 8, n, 0); break;
+            case 1: store_w(e.val, row, e.out_width, lo, hi); break;
+            case 2: {
+                i128 r = decimal_div_integer(make_i128(lo, (int64_t)hi), (i128)(int64_t)n, e.scale);
+                store_w(e.val, row, 16, lo64(r), (uint64_t)hi64(r));
+                break;
+            }
+            case 3: {
+                i128 r = make_i128(lo, (int64_t)hi) / (i128)(int64_t)n; // DATE avg: truncating (avg.h:231)
+                store_w(e.val, row, 4, lo64(r), 0);
+                break;
+            }
+            case 4: {
+                double r = (double)make_i128(lo, (int64_t)hi) / (double)(int64_t)n;
+                store_w(e.val, row, 8, (uint64_t)__double_as_longlong(r), 0);
+                break;
+            }
+            default: {
+                double r = __longlong_as_double((long long)lo) / (double)(int64_t)n;
+                store_w(e.val, row, 8, (uint64_t)__double_as_longlong(r), 0);
+            }
+            }
+        }
+    }
+}
+
+// ---- filter-only mode: predicates -> bitmap + per-tile popcounts (K1), then order-preserving compaction (K2) ------
+constexpr int FTILE = 8192; // rows per tile = 256 mask words
+
+__global__ void __launch_bounds__(256) k_filter_mask(const __grid_constant__ DProg prog, int64_t base, int64_t n, uint32_t* __restrict__ mask,
+                                                      uint32_t* __restrict__ tile_counts) {
+    const DProg& p = prog;
+    __shared__ uint32_t wcount[8];
+    const int64_t tile0 = (int64_t)blockIdx.x * FTILE;
+    uint32_t mine = 0;
+    for (int it = 0; it < FTILE / 256; it++) {
+        int64_t i = tile0 + it * 256 + threadIdx.x;
+        bool pass = i < n && eval_preds(p, base + i);
+        uint32_t w = __ballot_sync(0xffffffffu, pass);
+        if ((threadIdx.x & 31) == 0) {
+            if (i < n) mask[i >> 5] = w;
+            mine += __popc(w);
+        }
+    }
+    if ((threadIdx.x & 31) == 0) wcount[threadIdx.x >> 5] = mine;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int w = 0; w < 8; w++) t += wcount[w];
+        tile_counts[blockIdx.x] = t;
+    }
+}
+
+// exclusive scan of the tile counts (a few thousand to ~100k entries): one block, sequential over 1024-entry strips
+__global__ void __launch_bounds__(1024) k_scan_tiles(const uint32_t* __restrict__ counts, uint64_t* __restrict__ offsets, int64_t n_tiles,
+                                                      Counters* __restrict__ ctr) {
+    __shared__ uint64_t sm[1024];
+    __shared__ uint64_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int64_t b = 0; b < n_tiles; b += 1024) {
+        int64_t i = b + threadIdx.x;
+        uint64_t x = i < n_tiles ? counts[i] : 0;
+        sm[threadIdx.x] = x;
+        __syncthreads();
+        for (int o = 1; o < 1024; o <<= 1) {
+            uint64_t y = threadIdx.x >= o ? sm[threadIdx.x - o] : 0;
+            __syncthreads();
+            sm[threadIdx.x] += y;
+            __syncthreads();
+        }
+        if (i < n_tiles) offsets[i] = carry + sm[threadIdx.x] - x;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry += sm[1023];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) ctr->rows_selected = carry;
+}
+
+struct CompactCol {
+    const uint8_t* src; // already offset to the batch base
+    uint8_t* dst;       // already offset to the output base of this batch
+    const uint8_t* src_null;
+    uint8_t* dst_null;
+    int32_t width;
+    int32_t _pad;
+};
+struct CompactArgs {
+    int32_t n_cols;
+    int32_t _pad;
+    CompactCol cols[MAX_COLS];
+};
+
+__global__ void __launch_bounds__(256) k_compact(const __grid_constant__ CompactArgs ca, int64_t n, const uint32_t* __restrict__ mask,
+                                                  const uint64_t* __restrict__ tile_offsets) {
+    __shared__ uint32_t woff[256];
+    const int64_t tile0 = (int64_t)blockIdx.x * FTILE;
+    const int64_t w0 = tile0 >> 5;
+    const int64_t n_words = (n + 31) >> 5;
+    uint32_t word = (w0 + threadIdx.x) < n_words ? mask[w0 + threadIdx.x] : 0;
+    // rows past n inside the last word were never set (k_filter_mask ballots `i < n && pass`)
+    uint32_t c = __popc(word);
+    woff[threadIdx.x] = c;
+    __syncthreads();
+    for (int o = 1; o < 256; o <<= 1) {
+        uint32_t y = threadIdx.x >= o ? woff[threadIdx.x - o] : 0;
+        __syncthreads();
+        woff[threadIdx.x] += y;
+        __syncthreads();
+    }
+    const uint64_t tile_base = tile_offsets[blockIdx.x];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int w = warp * 32; w < warp * 32 + 32; w++) {
+        uint32_t bits = (w0 + w) < n_words ? mask[w0 + w] : 0;
+        if (!((bits >> lane) & 1u)) continue;
+        uint64_t pos = tile_base + (woff[w] - __popc(bits)) + __popc(bits & ((1u << lane) - 1));
+        int64_t i = tile0 + (int64_t)w * 32 + lane;
+        for (int cidx = 0; cidx < ca.n_cols; cidx++) {
+            const CompactCol& cc = ca.cols[cidx];
+            switch (cc.width) {
+            case 1: cc.dst[pos] = cc.src[i]; break;
+            case 2: ((uint16_t*)cc.dst)[pos] = ((const uint16_t*)cc.src)[i]; break;
+            case 4: ((uint32_t*)cc.dst)[pos] = ((const uint32_t*)cc.src)[i]; break;
+            case 8: ((uint64_t*)cc.dst)[pos] = ((const uint64_t*)cc.src)[i]; break;
+            default: ((ulonglong2*)cc.dst)[pos] = ((const ulonglong2*)cc.src)[i];
+            }
+            if (cc.src_null) cc.dst_null[pos] = cc.src_null[i];
+        }
+    }
+}
+
+// packed 16-byte group keys -> one device column per (fixed-width) key, for device-resident result chunks
+struct UnpackKey {
+    uint8_t* dst;
+    uint8_t* dst_null;
+    int32_t width;
+    int32_t nullable;
+};
+struct UnpackArgs {
+    int32_t n_keys;
+    int32_t _pad;
+    UnpackKey keys[MAX_KEYS];
+};
+__global__ void __launch_bounds__(256) k_unpack_keys(const __grid_constant__ UnpackArgs ua, const ulonglong2* __restrict__ packed, int64_t n) {
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        const ulonglong2 k = packed[r];
+        int off = 0;
+        for (int i = 0; i < ua.n_keys; i++) {
+            const UnpackKey& u = ua.keys[i];
+            auto byte_at = [&](int o) -> uint64_t { return ((o < 8 ? k.x >> (8 * o) : k.y >> (8 * (o - 8))) & 0xffULL); };
+            if (u.nullable) u.dst_null[r] = (uint8_t)byte_at(off++);
+            uint64_t lo = 0, hi = 0;
+            for (int b = 0; b < u.width; b++) {
+                uint64_t v = byte_at(off + b);
+                if (b < 8)
+                    lo |= v << (8 * b);
+                else
+                    hi |= v << (8 * (b - 8));
+            }
+            off += u.width;
+            store_w(u.dst, r, u.width, lo, hi);
+        }
+    }
+}
+
+// =================================================================================================================
+// host operator
+// =================================================================================================================
+struct HostCol { // result column handed out by pull_chunk (host memory owned by the op)
+    int type = 0, precision = 0, scale = 0;
+    std::vector<uint8_t> data, nulls;
+    std::vector<uint32_t> offsets;
+    bool has_nulls = false;
+};
+
+struct Stage { // device staging of host chunks: one buffer per bound column
+    DevBuf data[MAX_COLS], nulls[MAX_COLS], offsets[MAX_COLS];
+    int64_t rows = 0;
+    int64_t bin_bytes[MAX_COLS] = {0};
+    cudaEvent_t copied = nullptr;
+};
+
+class ScanAggOp : public srb_op {
+public:
+    ScanAggOp(srb_ctx* c, const srb_scan_agg_plan* plan) : srb_op(c), plan_(plan) {
+        filter_only_ = plan_.aggs.empty() && plan_.key_nodes.empty();
+        staging_rows_ = c->cfg.staging_rows > 0 ? c->cfg.staging_rows : (int64_t)4 << 20;
+        chunk_size_ = c->cfg.chunk_size > 0 ? c->cfg.chunk_size : 4096;
+        SRB_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+        ctr_dev_.ensure(c, sizeof(Counters));
+        ctr_host_.ensure(sizeof(Counters) + TABLE_SHARDS * SHARD_STRIDE * 8);
+        SRB_CUDA(cudaMemsetAsync(ctr_dev_.p, 0, sizeof(Counters), stream));
+    }
+    ~ScanAggOp() override {
+        cudaStreamSynchronize(stream);
+        if (copy_stream_) cudaStreamDestroy(copy_stream_);
+        for (auto& s : stage_)
+            if (s.copied) cudaEventDestroy(s.copied);
+        if (kernel_done_) cudaEventDestroy(kernel_done_);
+    }
+
+    void push_chunk(const srb_chunk* ch) override {
+        if (finishing) throw Error(SRB_INTERNAL_ERROR, "push_chunk after set_finishing");
+        if (cancelled) throw Error(SRB_CANCELLED, "operator cancelled");
+        if (!ch || ch->n_rows < 0) throw Error(SRB_INVALID_ARGUMENT, "bad chunk");
+        if (ch->n_rows == 0) return; // empty chunks are dropped by the driver (pipeline_driver.cpp:340-342)
+        if (ch->n_rows >= ((int64_t)1 << 32)) throw Error(SRB_INVALID_ARGUMENT, "chunk exceeds Column::MAX_CAPACITY_LIMIT rows");
+        if (!lowered_) lower(ch);
+        const srb_column* cols[MAX_COLS];
+        bool any_dev = false, any_host = false;
+        for (size_t i = 0; i < L_.cols.size(); i++) {
+            const srb_column* c = find_slot(ch, L_.cols[i].slot);
+            if (!c) throw Error(SRB_INVALID_ARGUMENT, fmt("slot %d not in chunk", L_.cols[i].slot));
+            if (c->type != L_.cols[i].type) throw Error(SRB_INVALID_ARGUMENT, fmt("slot %d changed type", L_.cols[i].slot));
+            if (c->nulls && !L_.cols[i].nullable)
+                throw Error(SRB_NOT_IMPLEMENTED, fmt("slot %d: null map appeared after the first chunk had none", L_.cols[i].slot));
+            if (!c->data && !is_binary(c->type)) throw Error(SRB_INVALID_ARGUMENT, "null data pointer");
+            (c->mem_kind == SRB_MEM_DEVICE ? any_dev : any_host) = true;
+            cols[i] = c;
+        }
+        if (any_dev && any_host) throw Error(SRB_NOT_IMPLEMENTED, "chunk mixes device and host columns");
+        rows_in += ch->n_rows;
+        if (any_dev || L_.cols.empty()) {
+            flush_stage(); // keep row order between staged host rows and this device range
+            ColBind b[MAX_COLS];
+            for (size_t i = 0; i < L_.cols.size(); i++) {
+                b[i] = L_.prog.cols[i];
+                b[i].data = cols[i]->data;
+                b[i].nulls = L_.cols[i].nullable ? cols[i]->nulls : nullptr;
+                b[i].offsets = cols[i]->offsets;
+            }
+            process_device_range(b, ch->n_rows);
+        } else {
+            append_host(cols, ch->n_rows);
+        }
+    }
+
+    void set_finishing() override {
+        if (finishing) return;
+        finishing = true;
+        if (cancelled) {
+            finished = true;
+            return;
+        }
+        flush_stage();
+        wait_pending();
+        if (!lowered_) { // no chunk ever arrived: lower against an empty description so that result types exist
+            lower(nullptr);
+        }
+        produce_output();
+    }
+    bool has_output() override { return finishing && !finished && out_pos_ < out_rows_; }
+    bool need_input() override { return !finishing; }
+    bool is_finished() override { return finished || (finishing && out_pos_ >= out_rows_); }
+
+    srb_status pull_chunk(srb_chunk* out, bool all) override {
+        if (cancelled) throw Error(SRB_CANCELLED, "operator cancelled");
+        if (!finishing) throw Error(SRB_INTERNAL_ERROR, "pull_chunk before set_finishing (blocking aggregate has no output yet)");
+        if (out_pos_ >= out_rows_ && !(out_rows_ == 0 && !pulled_empty_ && all)) {
+            finished = true;
+            return SRB_END_OF_FILE;
+        }
+        int64_t n = out_rows_ - out_pos_;
+        if (!all && n > chunk_size_) n = chunk_size_;
+        materialize(out_pos_, n);
+        out_pos_ += n;
+        pulled_empty_ = true;
+        fill_chunk(out, n);
+        if (out_pos_ >= out_rows_) finished = true;
+        return SRB_OK;
+    }
+
+    void refresh_counters() override { rows_selected = (int64_t)selected_total_; }
+
+    // all remaining rows as device-resident columns (operator chaining on the GPU)
+    srb_status pull_device(srb_chunk* out) override {
+        if (cancelled) throw Error(SRB_CANCELLED, "operator cancelled");
+        if (!finishing) throw Error(SRB_INTERNAL_ERROR, "pull before set_finishing");
+        if (out_pos_ >= out_rows_ && pulled_empty_) {
+            finished = true;
+            return SRB_END_OF_FILE;
+        }
+        const int64_t n = out_rows_ - out_pos_;
+        hslots_.clear();
+        cview_.clear();
+        if (filter_only_) {
+            for (size_t k = 0; k < out_col_idx_.size(); k++) {
+                const ColMeta& cm = L_.cols[out_col_idx_[k]];
+                srb_column c{};
+                c.type = cm.type;
+                c.precision = cm.precision;
+                c.scale = cm.scale;
+                c.mem_kind = SRB_MEM_DEVICE;
+                int w = type_width(cm.type);
+                c.data = k < fout_.size() && fout_[k].data.p ? fout_[k].data.as<uint8_t>() + (size_t)out_pos_ * w : nullptr;
+                c.nulls = cm.nullable && k < fout_.size() && fout_[k].nulls.p ? fout_[k].nulls.as<uint8_t>() + out_pos_ : nullptr;
+                cview_.push_back(c);
+                hslots_.push_back(cm.slot);
+            }
+        } else {
+            device_result_columns(n);
+        }
+        out_pos_ = out_rows_;
+        pulled_empty_ = true;
+        finished = true;
+        out->n_rows = n;
+        out->n_cols = (int32_t)cview_.size();
+        out->slot_ids = hslots_.data();
+        out->cols = cview_.data();
+        return SRB_OK;
+    }
+
+private:
+    // aggregate result as device columns: keys unpacked by a kernel, aggregate values as emitted
+    void device_result_columns(int64_t n);
+
+    // ---- lowering / table ------------------------------------------------------------------------------------
+    void lower(const srb_chunk* first) {
+        srb_chunk empty{};
+        std::vector<srb_column> fake;
+        std::vector<int32_t> fake_slots;
+        if (!first) {
+            // synthesize column descriptions from the plan's own SLOT_REF / predicate types
+            auto add = [&](int slot, int type, int prec, int scale) {
+                for (int s : fake_slots)
+                    if (s == slot) return;
+                srb_column c{};
+                c.type = type;
+                c.precision = prec;
+                c.scale = scale;
+                fake.push_back(c);
+                fake_slots.push_back(slot);
+            };
+            for (auto& e : plan_.nodes)
+                if (e.op == SRB_EXPR_SLOT_REF) add(e.slot_id, e.type, e.precision, e.scale);
+            for (auto& p : plan_.preds) add(p.slot_id, p.type, 0, 0);
+            for (int s : plan_.out_slots) add(s, SRB_TYPE_BIGINT, 0, 0);
+            empty.n_cols = (int)fake.size();
+            empty.slot_ids = fake_slots.data();
+            empty.cols = fake.data();
+            first = &empty;
+        }
+        L_ = lower_plan(plan_, first);
+        if (filter_only_) {
+            for (int s : plan_.out_slots) {
+                bool found = false;
+                for (size_t i = 0; i < L_.cols.size(); i++) found |= L_.cols[i].slot == s;
+                if (!found) {
+                    const srb_column* c = find_slot(first, s);
+                    if (!c) throw Error(SRB_INVALID_ARGUMENT, fmt("output slot %d not in chunk", s));
+                    if ((int)L_.cols.size() >= MAX_COLS) throw Error(SRB_NOT_IMPLEMENTED, "too many columns");
+                    int idx = (int)L_.cols.size();
+                    L_.cols.push_back({s, c->type, c->precision, c->scale, c->nulls != nullptr});
+                    L_.prog.cols[idx].width = type_width(c->type);
+                    L_.prog.cols[idx].kind = is_binary(c->type) ? CK_BINARY : (c->type == SRB_TYPE_DOUBLE ? CK_DOUBLE : CK_INT);
+                    L_.prog.n_cols = idx + 1;
+                }
+            }
+            for (int s : plan_.out_slots)
+                for (size_t i = 0; i < L_.cols.size(); i++)
+                    if (L_.cols[i].slot == s) {
+                        if (is_binary(L_.cols[i].type)) throw Error(SRB_NOT_IMPLEMENTED, "filter output of binary columns");
+                        out_col_idx_.push_back((int)i);
+                    }
+        } else {
+            init_table();
+            shape_ = match_static_shape(L_.prog);
+        }
+        lowered_ = true;
+    }
+
+    void init_table() {
+        const DProg& P = L_.prog;
+        if (P.n_keys == 0) {
+            cap_ = 1;
+        } else {
+            uint64_t want = 1024;
+            if (plan_.group_hint > 0) {
+                uint64_t h = (uint64_t)plan_.group_hint * 2;
+                while (want < h) want <<= 1;
+            }
+            cap_ = want;
+        }
+        alloc_table(slots_, cap_);
+        shards_.ensure(ctx, TABLE_SHARDS * SHARD_STRIDE * 8);
+        SRB_CUDA(cudaMemsetAsync(shards_.p, 0, shards_.bytes, stream));
+        if (P.n_keys == 0) {
+            k_init_slot0<<<1, 32, 0, stream>>>(P, slots_.as<uint8_t>());
+            launches++;
+        }
+        occupied_ = 0;
+    }
+    void alloc_table(DevBuf& buf, uint64_t cap) {
+        size_t bytes = (size_t)cap * (size_t)L_.prog.slot_bytes;
+        buf.ensure(ctx, bytes);
+        SRB_CUDA(cudaMemsetAsync(buf.p, 0, bytes, stream));
+    }
+    TableView view(uint64_t shard_limit) {
+        TableView t;
+        t.slots = slots_.as<uint8_t>();
+        t.mask = cap_ - 1;
+        t.limit = shard_limit;
+        t.occupied = shards_.as<unsigned long long>();
+        t.slot_bytes = L_.prog.slot_bytes;
+        t.key_words = L_.prog.key_words;
+        return t;
+    }
+    void grow_table(uint64_t min_cap) {
+        uint64_t ncap = cap_ * 2;
+        while (ncap < min_cap) ncap <<= 1;
+        DevBuf nb;
+        alloc_table(nb, ncap);
+        TableView nt;
+        nt.slots = nb.as<uint8_t>();
+        nt.mask = ncap - 1;
+        nt.limit = 0;
+        nt.occupied = nullptr;
+        nt.slot_bytes = L_.prog.slot_bytes;
+        nt.key_words = L_.prog.key_words;
+        int blocks = (int)std::min<uint64_t>((cap_ + 255) / 256, (uint64_t)ctx->n_sms * 16);
+        k_rehash<<<blocks, 256, 0, stream>>>(L_.prog, slots_.as<uint8_t>(), cap_, nt);
+        launches++;
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        std::swap(slots_.p, nb.p);
+        std::swap(slots_.bytes, nb.bytes);
+        nb.ctx = ctx;
+        slots_.ctx = ctx;
+        cap_ = ncap;
+    }
+
+    // ---- batches ---------------------------------------------------------------------------------------------
+    static constexpr int64_t BATCH = (int64_t)1 << 27;
+
+    void process_device_range(const ColBind* cols, int64_t n) {
+        if (filter_only_) {
+            filter_range(cols, n);
+            return;
+        }
+        for (int64_t off = 0; off < n; off += BATCH) {
+            int64_t m = std::min<int64_t>(BATCH, n - off);
+            launch_batch(cols, off, m);
+            check_batch(cols, off, m);
+        }
+    }
+
+    uint64_t shard_limit() const {
+        // inserts allowed per shard in one launch so that the table never exceeds ~7/8 full
+        uint64_t hard = cap_ - cap_ / 8;
+        uint64_t room = hard > occupied_ ? hard - occupied_ : 0;
+        return room / TABLE_SHARDS;
+    }
+
+    void bind_prog(const ColBind* cols) {
+        for (int i = 0; i < L_.prog.n_cols; i++) {
+            L_.prog.cols[i].data = cols[i].data;
+            L_.prog.cols[i].nulls = cols[i].nulls;
+            L_.prog.cols[i].offsets = cols[i].offsets;
+        }
+    }
+
+    int grid_for(int64_t n) const {
+        int64_t blocks = (n + 255) / 256;
+        int64_t maxb = (int64_t)ctx->n_sms * 8;
+        return (int)std::max<int64_t>(1, std::min(blocks, maxb));
+    }
+
+    void launch_batch(const ColBind* cols, int64_t off, int64_t n, const uint32_t* defer_in = nullptr) {
+        bind_prog(cols);
+        if (L_.prog.n_keys) {
+            size_t words = (size_t)((std::min<int64_t>(n, BATCH) + 31) / 32);
+            for (int i = 0; i < 2; i++)
+                if (defer_[i].bytes < words * 4) {
+                    defer_[i].ensure(ctx, words * 4);
+                    SRB_CUDA(cudaMemsetAsync(defer_[i].p, 0, words * 4, stream));
+                }
+        }
+        TableView tv = view(shard_limit());
+        uint32_t* dout = L_.prog.n_keys ? defer_[defer_cur_].as<uint32_t>() : nullptr;
+        // recognised shapes run the TMA-staged static kernel over the whole tiles; the generic kernel takes the rest
+        int64_t covered = 0;
+        Counters* dc = ctr_dev_.as<Counters>();
+        if (shape_ >= 0 && !defer_in && !force_generic_) {
+            covered = launch_static_shape(shape_, L_.prog, tv, off, n, dout, &dc->rows_selected, &dc->deferred, ctx->n_sms, stream);
+            if (covered) launches++;
+        }
+        if (covered < n) {
+            k_scan_agg_generic<<<grid_for(n - covered), 256, 0, stream>>>(L_.prog, tv, off + covered, n - covered, covered, defer_in, dout, dc);
+            launches++;
+        }
+        SRB_CUDA(cudaGetLastError());
+    }
+
+    // waits for the batch, folds the counters, replays deferred rows after growing the table
+    void check_batch(const ColBind* cols, int64_t off, int64_t n) {
+        for (;;) {
+            Counters* hc = ctr_host_.as<Counters>();
+            unsigned long long* hs = (unsigned long long*)(hc + 1);
+            SRB_CUDA(cudaMemcpyAsync(hc, ctr_dev_.p, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+            if (L_.prog.n_keys) SRB_CUDA(cudaMemcpyAsync(hs, shards_.p, shards_.bytes, cudaMemcpyDeviceToHost, stream));
+            SRB_CUDA(cudaMemsetAsync(ctr_dev_.p, 0, sizeof(Counters), stream));
+            if (L_.prog.n_keys) SRB_CUDA(cudaMemsetAsync(shards_.p, 0, shards_.bytes, stream));
+            SRB_CUDA(cudaStreamSynchronize(stream));
+            selected_total_ += hc->rows_selected;
+            if (hc->key_too_long) throw Error(SRB_NOT_IMPLEMENTED, "serialized group key longer than 16 bytes");
+            if (L_.prog.n_keys)
+                for (int s = 0; s < TABLE_SHARDS; s++) occupied_ += hs[s * SHARD_STRIDE];
+            uint64_t deferred = hc->deferred;
+            // deferred counts rows, not groups: bound one growth step so a burst of duplicates cannot over-allocate
+            if (L_.prog.n_keys && (deferred || occupied_ * 2 > cap_))
+                grow_table(std::min<uint64_t>(std::max<uint64_t>(cap_ * 2, (occupied_ + deferred) * 4), std::max<uint64_t>(cap_ * 8, occupied_ * 4)));
+            if (!deferred) return;
+            // replay: the bitmap just written becomes the input, the other one (cleared) the output
+            int in = defer_cur_;
+            defer_cur_ ^= 1;
+            SRB_CUDA(cudaMemsetAsync(defer_[defer_cur_].p, 0, defer_[defer_cur_].bytes, stream));
+            launch_batch(cols, off, n, defer_[in].as<uint32_t>());
+            // the consumed bitmap is cleared for its next use as an output
+            SRB_CUDA(cudaMemsetAsync(defer_[in].p, 0, defer_[in].bytes, stream));
+        }
+    }
+
+    // ---- host chunk staging ------------------------------------------------------------------------------------
+    void append_host(const srb_column* const* cols, int64_t n) {
+        int64_t done = 0;
+        while (done < n) {
+            Stage& st = stage_[cur_stage_];
+            if (st.rows == 0) begin_stage(st);
+            int64_t take = std::min<int64_t>(n - done, staging_rows_ - st.rows);
+            for (size_t i = 0; i < L_.cols.size(); i++) {
+                const srb_column* c = cols[i];
+                int w = L_.prog.cols[i].width;
+                if (w) {
+                    SRB_CUDA(cudaMemcpyAsync(st.data[i].as<uint8_t>() + (size_t)st.rows * w, (const uint8_t*)c->data + (size_t)done * w,
+                                             (size_t)take * w, cudaMemcpyHostToDevice, copy_stream_));
+                } else {
+                    // binary: bytes appended, offsets rebased on the host (cheap, sequential) then copied
+                    uint32_t b0 = c->offsets[done], b1 = c->offsets[done + take];
+                    size_t nbytes = b1 - b0;
+                    if ((size_t)st.bin_bytes[i] + nbytes + 16 > st.data[i].bytes) grow_bin(st, (int)i, (size_t)st.bin_bytes[i] + nbytes + 16);
+                    if (nbytes)
+                        SRB_CUDA(cudaMemcpyAsync(st.data[i].as<uint8_t>() + st.bin_bytes[i], (const uint8_t*)c->data + b0, nbytes,
+                                                 cudaMemcpyHostToDevice, copy_stream_));
+                    off_scratch_.resize((size_t)take + 1);
+                    for (int64_t r = 0; r <= take; r++) off_scratch_[r] = c->offsets[done + r] - b0 + (uint32_t)st.bin_bytes[i];
+                    SRB_CUDA(cudaMemcpyAsync(st.offsets[i].as<uint32_t>() + st.rows, off_scratch_.data(), (size_t)(take + 1) * 4,
+                                             cudaMemcpyHostToDevice, copy_stream_));
+                    SRB_CUDA(cudaStreamSynchronize(copy_stream_)); // off_scratch_ is reused
+                    st.bin_bytes[i] += (int64_t)nbytes;
+                }
+                if (L_.cols[i].nullable) {
+                    if (c->nulls)
+                        SRB_CUDA(cudaMemcpyAsync(st.nulls[i].as<uint8_t>() + st.rows, c->nulls + done, (size_t)take, cudaMemcpyHostToDevice,
+                                                 copy_stream_));
+                    else
+                        SRB_CUDA(cudaMemsetAsync(st.nulls[i].as<uint8_t>() + st.rows, 0, (size_t)take, copy_stream_));
+                }
+            }
+            st.rows += take;
+            done += take;
+            if (st.rows >= staging_rows_) flush_stage();
+        }
+    }
+    void begin_stage(Stage& st) {
+        if (!st.copied) SRB_CUDA(cudaEventCreateWithFlags(&st.copied, cudaEventDisableTiming));
+        for (size_t i = 0; i < L_.cols.size(); i++) {
+            int w = L_.prog.cols[i].width;
+            if (w)
+                st.data[i].ensure(ctx, (size_t)staging_rows_ * w);
+            else {
+                if (!st.data[i].p) st.data[i].ensure(ctx, (size_t)1 << 20);
+                st.offsets[i].ensure(ctx, (size_t)(staging_rows_ + 1) * 4);
+                st.bin_bytes[i] = 0;
+            }
+            if (L_.cols[i].nullable) st.nulls[i].ensure(ctx, (size_t)staging_rows_);
+        }
+    }
+    void grow_bin(Stage& st, int i, size_t need) {
+        SRB_CUDA(cudaStreamSynchronize(copy_stream_));
+        size_t ncap = std::max(need, st.data[i].bytes * 2);
+        DevBuf nb;
+        nb.ensure(ctx, ncap);
+        if (st.bin_bytes[i]) SRB_CUDA(cudaMemcpy(nb.p, st.data[i].p, (size_t)st.bin_bytes[i], cudaMemcpyDeviceToDevice));
+        std::swap(st.data[i].p, nb.p);
+        std::swap(st.data[i].bytes, nb.bytes);
+        nb.ctx = ctx;
+        st.data[i].ctx = ctx;
+    }
+    // launches the kernel over the current stage and switches to the other one; the previous stage's kernel is
+    // checked first, so at most one batch is in flight while the host fills the next stage.
+    void flush_stage() {
+        Stage& st = stage_[cur_stage_];
+        if (st.rows == 0) return;
+        wait_pending();
+        SRB_CUDA(cudaEventRecord(st.copied, copy_stream_));
+        SRB_CUDA(cudaStreamWaitEvent(stream, st.copied, 0));
+        ColBind* b = pending_cols_;
+        for (size_t i = 0; i < L_.cols.size(); i++) {
+            b[i] = L_.prog.cols[i];
+            b[i].data = st.data[i].p;
+            b[i].nulls = L_.cols[i].nullable ? st.nulls[i].as<uint8_t>() : nullptr;
+            b[i].offsets = st.offsets[i].as<uint32_t>();
+        }
+        if (filter_only_) {
+            filter_range(b, st.rows);
+            st.rows = 0;
+        } else {
+            launch_batch(b, 0, st.rows);
+            pending_rows_ = st.rows;
+            pending_ = true;
+            pending_stage_ = cur_stage_;
+        }
+        cur_stage_ ^= 1;
+    }
+    void wait_pending() {
+        if (!pending_) return;
+        pending_ = false;
+        check_batch(pending_cols_, 0, pending_rows_);
+        stage_[pending_stage_].rows = 0;
+    }
+
+    // ---- filter-only -----------------------------------------------------------------------------------------------
+    void filter_range(const ColBind* cols, int64_t n) {
+        bind_prog(cols);
+        for (int64_t off = 0; off < n; off += BATCH) {
+            int64_t m = std::min<int64_t>(BATCH, n - off);
+            int64_t tiles = (m + FTILE - 1) / FTILE;
+            mask_.ensure(ctx, (size_t)((m + 31) / 32) * 4 + 4);
+            tile_counts_.ensure(ctx, (size_t)tiles * 4);
+            tile_offsets_.ensure(ctx, (size_t)tiles * 8);
+            k_filter_mask<<<(int)tiles, 256, 0, stream>>>(L_.prog, off, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>());
+            k_scan_tiles<<<1, 1024, 0, stream>>>(tile_counts_.as<uint32_t>(), tile_offsets_.as<uint64_t>(), tiles, ctr_dev_.as<Counters>());
+            launches += 2;
+            Counters* hc = ctr_host_.as<Counters>();
+            SRB_CUDA(cudaMemcpyAsync(hc, ctr_dev_.p, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+            SRB_CUDA(cudaStreamSynchronize(stream));
+            int64_t sel = (int64_t)hc->rows_selected;
+            // grow the device result columns, then compact into them
+            CompactArgs ca{};
+            ca.n_cols = (int)out_col_idx_.size();
+            fout_.resize(out_col_idx_.size());
+            for (size_t k = 0; k < out_col_idx_.size(); k++) {
+                int ci = out_col_idx_[k];
+                int w = L_.prog.cols[ci].width;
+                grow_out(fout_[k].data, (size_t)out_rows_ * w, (size_t)(out_rows_ + sel) * w);
+                if (L_.cols[ci].nullable) grow_out(fout_[k].nulls, (size_t)out_rows_, (size_t)(out_rows_ + sel));
+                ca.cols[k].src = (const uint8_t*)cols[ci].data + (size_t)off * w;
+                ca.cols[k].dst = fout_[k].data.as<uint8_t>() + (size_t)out_rows_ * w;
+                ca.cols[k].src_null = L_.cols[ci].nullable ? cols[ci].nulls + off : nullptr;
+                ca.cols[k].dst_null = L_.cols[ci].nullable ? fout_[k].nulls.as<uint8_t>() + out_rows_ : nullptr;
+                ca.cols[k].width = w;
+            }
+            if (sel > 0 && ca.n_cols > 0) {
+                k_compact<<<(int)tiles, 256, 0, stream>>>(ca, m, mask_.as<uint32_t>(), tile_offsets_.as<uint64_t>());
+                launches++;
+            }
+            SRB_CUDA(cudaGetLastError());
+            SRB_CUDA(cudaStreamSynchronize(stream));
+            out_rows_ += sel;
+            selected_total_ += (uint64_t)sel;
+        }
+    }
+    struct FOut {
+        DevBuf data, nulls;
+    };
+    void grow_out(DevBuf& b, size_t used, size_t need) {
+        if (need <= b.bytes) return;
+        size_t ncap = std::max(need, b.bytes * 2);
+        DevBuf nb;
+        nb.ensure(ctx, ncap);
+        if (used) SRB_CUDA(cudaMemcpyAsync(nb.p, b.p, used, cudaMemcpyDeviceToDevice, stream));
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        std::swap(b.p, nb.p);
+        std::swap(b.bytes, nb.bytes);
+        nb.ctx = ctx;
+        b.ctx = ctx;
+    }
+
+    // ---- output ------------------------------------------------------------------------------------------------------
+    void produce_output() {
+        if (filter_only_) return; // rows already sit in fout_
+        const DProg& P = L_.prog;
+        uint64_t max_rows = P.n_keys ? occupied_ : 1;
+        EmitArgs ea{};
+        ekeys_.ensure(ctx, (size_t)std::max<uint64_t>(1, max_rows) * 16);
+        ea.keys = ekeys_.as<ulonglong2>();
+        eval_.resize(P.n_aggs);
+        for (int a = 0; a < P.n_aggs; a++) {
+            const AggOutMeta& m = L_.agg_out[a];
+            EmitAgg& e = ea.aggs[a];
+            eval_[a].val.ensure(ctx, (size_t)std::max<uint64_t>(1, max_rows) * m.out_width);
+            e.val = eval_[a].val.p;
+            e.out_width = m.out_width;
+            if (m.nullable) {
+                eval_[a].null.ensure(ctx, (size_t)std::max<uint64_t>(1, max_rows));
+                e.null = eval_[a].null.as<uint8_t>();
+            }
+            if (m.blob) {
+                eval_[a].cnt.ensure(ctx, (size_t)std::max<uint64_t>(1, max_rows) * 8);
+                e.cnt = eval_[a].cnt.as<int64_t>();
+            }
+            e.scale = m.arg_scale;
+            if (m.fn == SRB_AGG_COUNT)
+                e.mode = 0;
+            else if (m.fn != SRB_AGG_AVG || m.blob)
+                e.mode = 1;
+            else if (is_decimal(m.arg_type))
+                e.mode = 2;
+            else if (m.arg_type == SRB_TYPE_DATE)
+                e.mode = 3;
+            else if (m.arg_type == SRB_TYPE_LARGEINT)
+                e.mode = 4;
+            else
+                e.mode = 5;
+        }
+        SRB_CUDA(cudaMemsetAsync(ctr_dev_.p, 0, sizeof(Counters), stream));
+        int blocks = (int)std::min<uint64_t>((cap_ + 255) / 256, (uint64_t)ctx->n_sms * 16);
+        k_emit<<<blocks, 256, 0, stream>>>(P, slots_.as<uint8_t>(), cap_, ea, ctr_dev_.as<Counters>());
+        launches++;
+        SRB_CUDA(cudaGetLastError());
+        Counters* hc = ctr_host_.as<Counters>();
+        SRB_CUDA(cudaMemcpyAsync(hc, ctr_dev_.p, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        out_rows_ = (int64_t)hc->emitted;
+        if ((uint64_t)out_rows_ != max_rows) throw Error(SRB_INTERNAL_ERROR, fmt("emit produced %lld rows, table holds %llu", (long long)out_rows_, (unsigned long long)max_rows));
+    }
+
+    // copies rows [pos, pos+n) of the device result into host columns
+    void materialize(int64_t pos, int64_t n) {
+        hcols_.clear();
+        hslots_.clear();
+        if (filter_only_) {
+            for (size_t k = 0; k < out_col_idx_.size(); k++) {
+                const ColMeta& cm = L_.cols[out_col_idx_[k]];
+                HostCol h;
+                h.type = cm.type;
+                h.precision = cm.precision;
+                h.scale = cm.scale;
+                int w = type_width(cm.type);
+                h.data.resize((size_t)n * w);
+                if (n) SRB_CUDA(cudaMemcpyAsync(h.data.data(), fout_[k].data.as<uint8_t>() + (size_t)pos * w, (size_t)n * w, cudaMemcpyDeviceToHost, stream));
+                if (cm.nullable) {
+                    h.has_nulls = true;
+                    h.nulls.resize((size_t)n);
+                    if (n) SRB_CUDA(cudaMemcpyAsync(h.nulls.data(), fout_[k].nulls.as<uint8_t>() + pos, (size_t)n, cudaMemcpyDeviceToHost, stream));
+                }
+                hcols_.push_back(std::move(h));
+                hslots_.push_back(cm.slot);
+            }
+            SRB_CUDA(cudaStreamSynchronize(stream));
+            return;
+        }
+        const DProg& P = L_.prog;
+        // keys: packed 16-byte records -> one column per key
+        std::vector<uint8_t> packed;
+        if (P.n_keys) {
+            packed.resize((size_t)n * 16);
+            if (n) SRB_CUDA(cudaMemcpyAsync(packed.data(), ekeys_.as<uint8_t>() + (size_t)pos * 16, (size_t)n * 16, cudaMemcpyDeviceToHost, stream));
+        }
+        std::vector<std::vector<uint8_t>> vals(P.n_aggs), nulls(P.n_aggs);
+        std::vector<std::vector<int64_t>> cnts(P.n_aggs);
+        for (int a = 0; a < P.n_aggs; a++) {
+            const AggOutMeta& m = L_.agg_out[a];
+            vals[a].resize((size_t)n * m.out_width);
+            if (n) SRB_CUDA(cudaMemcpyAsync(vals[a].data(), eval_[a].val.as<uint8_t>() + (size_t)pos * m.out_width, (size_t)n * m.out_width, cudaMemcpyDeviceToHost, stream));
+            if (m.nullable) {
+                nulls[a].resize((size_t)n);
+                if (n) SRB_CUDA(cudaMemcpyAsync(nulls[a].data(), eval_[a].null.as<uint8_t>() + pos, (size_t)n, cudaMemcpyDeviceToHost, stream));
+            }
+            if (m.blob) {
+                cnts[a].resize((size_t)n);
+                if (n) SRB_CUDA(cudaMemcpyAsync(cnts[a].data(), eval_[a].cnt.as<int64_t>() + pos, (size_t)n * 8, cudaMemcpyDeviceToHost, stream));
+            }
+        }
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        for (int k = 0; k < P.n_keys; k++) {
+            const ColMeta& cm = L_.key_out[k];
+            HostCol h;
+            h.type = cm.type;
+            h.precision = cm.precision;
+            h.scale = cm.scale;
+            h.has_nulls = cm.nullable;
+            if (is_binary(cm.type)) h.offsets.push_back(0);
+            hcols_.push_back(std::move(h));
+            hslots_.push_back(k);
+        }
+        for (int64_t r = 0; r < n; r++) {
+            const uint8_t* kb = packed.data() + (size_t)r * 16;
+            int off = 0;
+            for (int k = 0; k < P.n_keys; k++) {
+                HostCol& h = hcols_[k];
+                const DKey& kd = P.keys[k];
+                if (kd.nullable) h.nulls.push_back(kb[off++]);
+                if (kd.width == 0) {
+                    uint32_t len;
+                    memcpy(&len, kb + off, 4);
+                    off += 4;
+                    h.data.insert(h.data.end(), kb + off, kb + off + len);
+                    off += (int)len;
+                    h.offsets.push_back((uint32_t)h.data.size());
+                } else {
+                    h.data.insert(h.data.end(), kb + off, kb + off + kd.width);
+                    off += kd.width;
+                }
+            }
+        }
+        for (int a = 0; a < P.n_aggs; a++) {
+            const AggOutMeta& m = L_.agg_out[a];
+            HostCol h;
+            h.type = m.out_type;
+            h.precision = m.out_precision;
+            h.scale = m.out_scale;
+            h.has_nulls = m.nullable;
+            h.nulls = std::move(nulls[a]);
+            if (m.blob) { // {sum, count}: 24 bytes (int128 sum) or 16 bytes (double sum); empty when NULL (avg.h:168-181)
+                h.offsets.push_back(0);
+                int sw = m.out_width;
+                for (int64_t r = 0; r < n; r++) {
+                    if (!h.nulls[r]) {
+                        h.data.insert(h.data.end(), vals[a].data() + (size_t)r * sw, vals[a].data() + (size_t)(r + 1) * sw);
+                        const uint8_t* cp = (const uint8_t*)&cnts[a][r];
+                        h.data.insert(h.data.end(), cp, cp + 8);
+                    }
+                    h.offsets.push_back((uint32_t)h.data.size());
+                }
+            } else {
+                h.data = std::move(vals[a]);
+            }
+            hcols_.push_back(std::move(h));
+            hslots_.push_back(P.n_keys + a);
+        }
+    }
+
+    void fill_chunk(srb_chunk* out, int64_t n) {
+        cview_.resize(hcols_.size());
+        for (size_t i = 0; i < hcols_.size(); i++) {
+            HostCol& h = hcols_[i];
+            srb_column& c = cview_[i];
+            c.type = h.type;
+            c.precision = h.precision;
+            c.scale = h.scale;
+            c.mem_kind = SRB_MEM_HOST;
+            if (h.data.empty()) h.data.reserve(16);
+            c.data = h.data.data();
+            c.nulls = h.has_nulls ? h.nulls.data() : nullptr;
+            if (h.has_nulls && h.nulls.empty()) {
+                h.nulls.reserve(16);
+                c.nulls = h.nulls.data();
+            }
+            c.offsets = is_binary(h.type) ? h.offsets.data() : nullptr;
+            c.n_bytes = (int64_t)h.data.size();
+        }
+        out->n_rows = n;
+        out->n_cols = (int32_t)hcols_.size();
+        out->slot_ids = hslots_.data();
+        out->cols = cview_.data();
+    }
+
+    PlanCopy plan_;
+    Lowered L_;
+    bool lowered_ = false, filter_only_ = false;
+    int shape_ = -1;
+    bool force_generic_ = getenv("SRB_FORCE_GENERIC") != nullptr; // test hook: compare the two kernel families
+    int64_t staging_rows_, chunk_size_;
+    cudaStream_t copy_stream_ = nullptr;
+    cudaEvent_t kernel_done_ = nullptr;
+    // table
+    DevBuf slots_, shards_, defer_[2];
+    int defer_cur_ = 0;
+    uint64_t cap_ = 0, occupied_ = 0, selected_total_ = 0;
+    DevBuf ctr_dev_;
+    PinnedBuf ctr_host_;
+    // staging
+    Stage stage_[2];
+    int cur_stage_ = 0, pending_stage_ = 0;
+    bool pending_ = false;
+    int64_t pending_rows_ = 0;
+    ColBind pending_cols_[MAX_COLS];
+    std::vector<uint32_t> off_scratch_;
+    // filter-only
+    DevBuf mask_, tile_counts_, tile_offsets_;
+    std::vector<int> out_col_idx_;
+    std::vector<FOut> fout_;
+    // output
+    struct EVal {
+        DevBuf val, null, cnt;
+    };
+    DevBuf ekeys_;
+    std::vector<FOut> dkeys_;
+    std::vector<EVal> eval_;
+    int64_t out_rows_ = 0, out_pos_ = 0;
+    bool pulled_empty_ = false;
+    std::vector<HostCol> hcols_;
+    std::vector<int32_t> hslots_;
+    std::vector<srb_column> cview_;
+};
+
+void ScanAggOp::device_result_columns(int64_t n) {
+    const DProg& P = L_.prog;
+    UnpackArgs ua{};
+    ua.n_keys = P.n_keys;
+    dkeys_.resize(P.n_keys);
+    for (int k = 0; k < P.n_keys; k++) {
+        const ColMeta& cm = L_.key_out[k];
+        if (P.keys[k].width == 0) throw Error(SRB_NOT_IMPLEMENTED, "device pull of binary group keys");
+        dkeys_[k].data.ensure(ctx, (size_t)std::max<int64_t>(n, 1) * P.keys[k].width);
+        if (cm.nullable) dkeys_[k].nulls.ensure(ctx, (size_t)std::max<int64_t>(n, 1));
+        ua.keys[k] = UnpackKey{dkeys_[k].data.as<uint8_t>(), cm.nullable ? dkeys_[k].nulls.as<uint8_t>() : nullptr, P.keys[k].width,
+                               cm.nullable ? 1 : 0};
+        srb_column c{};
+        c.type = cm.type;
+        c.precision = cm.precision;
+        c.scale = cm.scale;
+        c.mem_kind = SRB_MEM_DEVICE;
+        c.data = dkeys_[k].data.p;
+        c.nulls = cm.nullable ? dkeys_[k].nulls.as<uint8_t>() : nullptr;
+        cview_.push_back(c);
+        hslots_.push_back(k);
+    }
+    if (P.n_keys && n > 0) {
+        k_unpack_keys<<<grid_for(n), 256, 0, stream>>>(ua, ekeys_.as<ulonglong2>() + out_pos_, n);
+        launches++;
+        SRB_CUDA(cudaGetLastError());
+    }
+    for (int a = 0; a < P.n_aggs; a++) {
+        const AggOutMeta& m = L_.agg_out[a];
+        if (m.blob) throw Error(SRB_NOT_IMPLEMENTED, "device pull of AVG intermediate blobs");
+        srb_column c{};
+        c.type = m.out_type;
+        c.precision = m.out_precision;
+        c.scale = m.out_scale;
+        c.mem_kind = SRB_MEM_DEVICE;
+        c.data = eval_[a].val.as<uint8_t>() + (size_t)out_pos_ * m.out_width;
+        c.nulls = m.nullable ? eval_[a].null.as<uint8_t>() + out_pos_ : nullptr;
+        cview_.push_back(c);
+        hslots_.push_back(P.n_keys + a);
+    }
+    SRB_CUDA(cudaStreamSynchronize(stream));
+}
+
+srb_op* make_scan_agg_op(srb_ctx* ctx, const srb_scan_agg_plan* plan) {
+    if (!plan) throw Error(SRB_INVALID_ARGUMENT, "null plan");
+    return new ScanAggOp(ctx, plan);
+}
+
+} // namespace srb

@@ -1,0 +1,596 @@
+"""GPU parity: every result of libsrb.so (through the C ABI) is compared with the CPU oracle on the same inputs.
+Bit-exact for integer / DECIMAL / key / row-set outputs (order-normalised); 1e-9 relative for DOUBLE.
+The known-answer vectors of the reference's own unit tests (be/test/exprs/agg/aggregate_test.cpp,
+be/test/exec/join_hash_map_test.cpp) are replayed through the CUDA path as well."""
+import math
+import os
+
+import numpy as np
+import pytest
+
+from starrocks_b200 import capi as K
+from starrocks_b200 import queries as Q
+from starrocks_b200 import tpch_synth as T
+from starrocks_b200.plan import ExprBuilder, JoinPlan, ScanAggPlan, pred
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from starrocks_b200 import ops
+    c = ops.Context(device=0, chunk_size=4096)
+    yield c
+    c.close()
+
+
+def rows_equal(a, b, rel=1e-9):
+    if len(a) != len(b):
+        return False
+    for ra, rb in zip(a, b):
+        if len(ra) != len(rb):
+            return False
+        for x, y in zip(ra, rb):
+            if isinstance(x, float) or isinstance(y, float):
+                if x is None or y is None:
+                    if x is not y:
+                        return False
+                elif not (x == y or abs(x - y) <= rel * max(abs(x), abs(y))):
+                    return False
+            elif x != y:
+                return False
+    return True
+
+
+def run_gpu(ctx, plan, chunk, piece_rows=0, device=False):
+    from starrocks_b200 import ops
+    if device:
+        dch, ptrs = ctx.device_chunk(chunk)
+        try:
+            return ops.run_scan_agg(ctx, plan, dch)
+        finally:
+            for p in ptrs:
+                ctx.device_free(p)
+    return ops.run_scan_agg(ctx, plan, chunk, piece_rows)
+
+
+def check(ctx, oracle, plan, chunk, sort=True, **kw):
+    want = oracle.scan_agg(plan, chunk)
+    got = run_gpu(ctx, plan, chunk, **kw)
+    assert list(got.columns.keys()) == list(want.columns.keys())
+    for s in want.columns:
+        assert got.columns[s].type == want.columns[s].type, s
+        assert got.columns[s].scale == want.columns[s].scale, s
+    a, b = K.chunk_rows(got, sort), K.chunk_rows(want, sort)
+    assert rows_equal(a, b), (a[:5], b[:5])
+    return got
+
+
+# ---- the reference's aggregate known-answer vectors, through the CUDA path ------------------------------------------------
+COL1 = list(range(1024)) + [100, 200]
+COL2 = list(range(2000, 3000))
+
+
+def _agg_plan(fn, type_, p=0, s=0, phase=K.AGG_UPDATE_FINALIZE):
+    e = ExprBuilder()
+    return ScanAggPlan(exprs=e, aggs=[(fn, e.slot(0, type_, p, s))], phase=phase)
+
+
+def _one(ch):
+    return K.column_pyvalues(ch.columns[0])[0]
+
+
+def _gpu_agg(ctx, fn, type_, vals, p=0, s=0, nulls=None, phase=K.AGG_UPDATE_FINALIZE, **kw):
+    ch = K.Chunk(len(vals), {0: K.Column.from_ints(type_, vals, nulls, p, s)})
+    return run_gpu(ctx, _agg_plan(fn, type_, p, s, phase), ch, **kw)
+
+
+def _gpu_two_phase(ctx, fn, type_, v1, v2, p=0, s=0):
+    inter = [_gpu_agg(ctx, fn, type_, v, p, s, phase=K.AGG_UPDATE_SERIALIZE) for v in (v1, v2)]
+    c0, c1 = inter[0].columns[0], inter[1].columns[0]
+    if K.is_binary(c0.type):
+        col = K.Column.from_strings(K.column_pyvalues(c0) + K.column_pyvalues(c1), type_=K.TYPE_VARBINARY)
+        col.precision, col.scale = c0.precision, c0.scale
+    else:
+        col = K.Column.from_ints(c0.type, K.column_pyvalues(c0) + K.column_pyvalues(c1), None, c0.precision, c0.scale)
+    e = ExprBuilder()
+    plan = ScanAggPlan(exprs=e, aggs=[(fn, e.slot(0, col.type, col.precision, col.scale))], phase=K.AGG_MERGE_FINALIZE)
+    return _one(run_gpu(ctx, plan, K.Chunk(2, {0: col})))
+
+
+@pytest.mark.parametrize("type_", [K.TYPE_SMALLINT, K.TYPE_INT, K.TYPE_BIGINT, K.TYPE_LARGEINT, K.TYPE_DOUBLE])
+def test_reference_agg_vectors(ctx, type_):
+    # aggregate_test.cpp:331-367,399-414,957-1012
+    assert _one(_gpu_agg(ctx, K.AGG_COUNT, type_, COL1)) == 1026
+    assert _gpu_two_phase(ctx, K.AGG_COUNT, type_, COL1, COL2) == 2026
+    assert _one(_gpu_agg(ctx, K.AGG_SUM, type_, COL1)) == 524076
+    assert _one(_gpu_agg(ctx, K.AGG_SUM, type_, COL2)) == 2499500
+    assert _gpu_two_phase(ctx, K.AGG_SUM, type_, COL1, COL2) == 3023576
+    assert _one(_gpu_agg(ctx, K.AGG_AVG, type_, COL1)) == 524076 / 1026.0
+    assert _gpu_two_phase(ctx, K.AGG_AVG, type_, COL1, COL2) == 3023576 / 2026.0
+    assert _one(_gpu_agg(ctx, K.AGG_MAX, type_, COL1)) == 1023
+    assert _gpu_two_phase(ctx, K.AGG_MAX, type_, COL1, COL2) == 2999
+    assert _one(_gpu_agg(ctx, K.AGG_MIN, type_, COL2)) == 2000
+    assert _gpu_two_phase(ctx, K.AGG_MIN, type_, COL1, COL2) == 0
+
+
+@pytest.mark.parametrize("type_,p,s", [(K.TYPE_DECIMAL32, 9, 9), (K.TYPE_DECIMAL64, 9, 3), (K.TYPE_DECIMAL128, 38, 15)])
+def test_reference_decimal_vectors(ctx, oracle, type_, p, s):
+    # aggregate_test.cpp:369-397,431-468
+    r = _gpu_agg(ctx, K.AGG_SUM, type_, COL1, p, s)
+    assert r.columns[0].type == K.TYPE_DECIMAL128 and r.columns[0].scale == s and _one(r) == 524076
+    assert _gpu_two_phase(ctx, K.AGG_SUM, type_, COL1, COL2, p, s) == 3023576
+    ddi = oracle.decimal_div_integer
+    assert _one(_gpu_agg(ctx, K.AGG_AVG, type_, COL1, p, s)) == ddi(524076, 1026, s)
+    assert _one(_gpu_agg(ctx, K.AGG_AVG, type_, COL2, p, s)) == ddi(2499500, 1000, s)
+    assert _gpu_two_phase(ctx, K.AGG_AVG, type_, COL1, COL2, p, s) == ddi(3023576, 2026, s)
+
+
+def test_reference_date_avg_and_nullable(ctx):
+    d1 = [Q.from_date(2000 + j, 1, 1) for j in range(20)] + [Q.from_date(2000, 1, 1), Q.from_date(2001, 1, 1)]
+    assert _one(_gpu_agg(ctx, K.AGG_AVG, K.TYPE_DATE, d1)) == 2454716  # aggregate_test.cpp:428
+    assert _one(_gpu_agg(ctx, K.AGG_MAX, K.TYPE_DATE, d1)) == Q.from_date(2019, 1, 1)
+    vals = list(range(100))
+    nulls = [1 if i % 3 == 0 else 0 for i in range(100)]
+    assert _one(_gpu_agg(ctx, K.AGG_SUM, K.TYPE_INT, vals, nulls=nulls)) == sum(v for v, n in zip(vals, nulls) if not n)
+    assert _one(_gpu_agg(ctx, K.AGG_COUNT, K.TYPE_INT, vals, nulls=nulls)) == 100 - sum(nulls)
+    assert _one(_gpu_agg(ctx, K.AGG_SUM, K.TYPE_INT, vals, nulls=[1] * 100)) is None  # aggregate_test.cpp:1250-1297
+    assert _one(_gpu_agg(ctx, K.AGG_COUNT, K.TYPE_INT, vals, nulls=[1] * 100)) == 0
+
+
+def test_empty_input_no_group_by(ctx):
+    # aggregator.cpp:938-945: one row, SUM NULL, COUNT 0 — with a chunk of zero rows and with no chunk at all
+    from starrocks_b200 import ops
+    assert _one(_gpu_agg(ctx, K.AGG_SUM, K.TYPE_INT, [])) is None
+    assert _one(_gpu_agg(ctx, K.AGG_COUNT, K.TYPE_INT, [])) == 0
+    op = ops.ScanAggOperator(ctx, _agg_plan(K.AGG_MIN, K.TYPE_BIGINT))
+    op.set_finishing()
+    out = op.pull_all()
+    op.close()
+    assert out.n_rows == 1 and _one(out) is None
+
+
+# ---- predicates, expressions, keys: randomised plans against the oracle --------------------------------------------------
+def _rand_col(rng, type_, n, null_frac=0.0, small=False, p=0, s=0):
+    w = K.type_width(type_)
+    if type_ == K.TYPE_DOUBLE:
+        vals = rng.normal(0, 1e6, n)
+    elif w == 16:
+        vals = [int(rng.integers(-2**62, 2**62)) * int(rng.integers(1, 2**40)) for _ in range(n)]
+        if small:
+            vals = [int(x) for x in rng.integers(-50, 50, n)]
+    else:
+        hi = 50 if small else 2 ** (8 * w - 2)
+        vals = rng.integers(-hi, hi, n)
+    nulls = (rng.random(n) < null_frac).astype(np.uint8) if null_frac > 0 else None
+    return K.Column.from_ints(type_, vals, nulls, p, s)
+
+
+@pytest.mark.parametrize("type_", [K.TYPE_TINYINT, K.TYPE_SMALLINT, K.TYPE_INT, K.TYPE_BIGINT, K.TYPE_DATE, K.TYPE_DECIMAL32,
+                                   K.TYPE_DECIMAL64, K.TYPE_DECIMAL128, K.TYPE_DOUBLE])
+def test_predicates_all_ops(ctx, oracle, type_):
+    rng = np.random.default_rng(type_)
+    n = 20000
+    col = _rand_col(rng, type_, n, null_frac=0.1, small=True)
+    ch = K.Chunk(n, {0: col, 1: K.Column.from_ints(K.TYPE_BIGINT, np.arange(n))})
+    e = ExprBuilder()
+    arg = e.slot(1, K.TYPE_BIGINT)
+    for op in (K.PRED_EQ, K.PRED_NE, K.PRED_GT, K.PRED_GE, K.PRED_LT, K.PRED_LE, K.PRED_IS_NULL, K.PRED_NOT_NULL):
+        lit = 3.5 if type_ == K.TYPE_DOUBLE else 3
+        plan = ScanAggPlan(preds=[pred(0, op, type_, lit)], exprs=e, aggs=[(K.AGG_SUM, arg), (K.AGG_COUNT, None)])
+        check(ctx, oracle, plan, ch)
+
+
+def test_predicate_conjunction_and_or_groups(ctx, oracle):
+    rng = np.random.default_rng(5)
+    n = 50000
+    ch = K.Chunk(n, {0: _rand_col(rng, K.TYPE_INT, n, 0.05, small=True), 1: _rand_col(rng, K.TYPE_BIGINT, n, 0.05, small=True),
+                     2: _rand_col(rng, K.TYPE_DECIMAL128, n, 0.0, small=True), 3: K.Column.from_ints(K.TYPE_BIGINT, np.arange(n))})
+    e = ExprBuilder()
+    arg = e.slot(3, K.TYPE_BIGINT)
+    preds = [pred(0, K.PRED_GE, K.TYPE_INT, -20), pred(1, K.PRED_LT, K.TYPE_BIGINT, 5, or_group=7), pred(2, K.PRED_EQ, K.TYPE_DECIMAL128, 3, or_group=7),
+             pred(0, K.PRED_NE, K.TYPE_INT, 0), pred(1, K.PRED_IS_NULL, K.TYPE_BIGINT, 0, or_group=9), pred(2, K.PRED_GT, K.TYPE_DECIMAL128, -10, or_group=9)]
+    plan = ScanAggPlan(preds=preds, exprs=e, aggs=[(K.AGG_SUM, arg), (K.AGG_COUNT, None), (K.AGG_MIN, arg), (K.AGG_MAX, arg)])
+    check(ctx, oracle, plan, ch)
+    check(ctx, oracle, plan, ch, device=True)
+
+
+def test_filter_only_compaction_preserves_order(ctx, oracle):
+    # Chunk::filter (column/chunk.cpp:302): surviving rows keep their order, every column compacted by the same mask
+    rng = np.random.default_rng(11)
+    n = 100003
+    ch = K.Chunk(n, {0: _rand_col(rng, K.TYPE_INT, n, 0.1, small=True), 1: _rand_col(rng, K.TYPE_DECIMAL128, n, 0.2),
+                     2: _rand_col(rng, K.TYPE_SMALLINT, n), 3: _rand_col(rng, K.TYPE_DOUBLE, n), 4: _rand_col(rng, K.TYPE_TINYINT, n, 0.3)})
+    for preds in ([pred(0, K.PRED_GT, K.TYPE_INT, 0)], [pred(0, K.PRED_GT, K.TYPE_INT, 48)], [pred(0, K.PRED_GE, K.TYPE_INT, -1000)], []):
+        plan = ScanAggPlan(preds=preds, out_slots=[1, 0, 2, 3, 4])
+        check(ctx, oracle, plan, ch, sort=False)
+        check(ctx, oracle, plan, ch, sort=False, piece_rows=4096)
+        check(ctx, oracle, plan, ch, sort=False, device=True)
+
+
+DEC_EDGE = [0, 1, -1, 99, -100, 2**31 - 1, -2**31, 2**63 - 1, -2**63, 2**64, 10**18, -10**18, 10**37, -10**37, 2**126, -2**126, 2**127 - 1, -2**127]
+
+
+@pytest.mark.parametrize("rtype", [K.TYPE_DECIMAL32, K.TYPE_DECIMAL64, K.TYPE_DECIMAL128])
+def test_decimal_arithmetic_overflow_to_null(ctx, oracle, rtype):
+    # decimal_binary_function.h:94-109: an overflowing row becomes NULL and is skipped by the nullable aggregate
+    w = K.type_width(rtype)
+    lim = 2 ** (8 * w - 1)
+    edge = [x for x in DEC_EDGE if -lim <= x < lim]
+    rng = np.random.default_rng(w)
+    a = edge * len(edge) + [int(x) for x in rng.integers(-1000, 1000, 500)]
+    b = [y for y in edge for _ in edge] + [int(x) for x in rng.integers(-1000, 1000, 500)]
+    n = len(a)
+    ch = K.Chunk(n, {0: K.Column.from_ints(rtype, a, None, 9, 2), 1: K.Column.from_ints(rtype, b, None, 9, 1),
+                     2: K.Column.from_ints(K.TYPE_INT, np.arange(n) % 7)})
+    for op in ("add", "sub", "mul"):
+        e = ExprBuilder()
+        x, y, k = e.slot(0, rtype, 9, 2), e.slot(1, rtype, 9, 1), e.slot(2, K.TYPE_INT)
+        r = getattr(e, op)(x, y, rtype)
+        plan = ScanAggPlan(exprs=e, keys=[k], aggs=[(K.AGG_SUM, r), (K.AGG_COUNT, r), (K.AGG_MIN, r), (K.AGG_MAX, r), (K.AGG_AVG, r)])
+        check(ctx, oracle, plan, ch)
+        plan2 = ScanAggPlan(exprs=e, aggs=[(K.AGG_SUM, r), (K.AGG_COUNT, r), (K.AGG_MIN, r), (K.AGG_MAX, r)])
+        check(ctx, oracle, plan2, ch)
+
+
+def test_cast_and_fast_mul(ctx, oracle):
+    rng = np.random.default_rng(3)
+    n = 30000
+    a = [int(x) for x in rng.integers(-2**62, 2**62, n)]
+    b = [int(x) for x in rng.integers(-2**62, 2**62, n)]
+    a[:4] = [2**63 - 1, -2**63, -2**63, 2**63 - 1]
+    b[:4] = [2**63 - 1, -2**63, 2**63 - 1, -1]
+    ch = K.Chunk(n, {0: K.Column.from_ints(K.TYPE_DECIMAL64, a, None, 18, 2), 1: K.Column.from_ints(K.TYPE_DECIMAL64, b, None, 18, 2),
+                     2: K.Column.from_ints(K.TYPE_INT, rng.integers(0, 5, n))})
+    e = ExprBuilder()
+    x, y, k = e.slot(0, K.TYPE_DECIMAL64, 18, 2), e.slot(1, K.TYPE_DECIMAL64, 18, 2), e.slot(2, K.TYPE_INT)
+    prod = e.mul(e.cast(x, K.TYPE_DECIMAL128, 18, 2), e.cast(y, K.TYPE_DECIMAL128, 18, 2), K.TYPE_DECIMAL128, 38)  # fast path
+    up = e.cast(x, K.TYPE_DECIMAL128, 38, 10)  # scale-up by 10^8 (checked)
+    up64 = e.cast(y, K.TYPE_DECIMAL64, 18, 6)  # overflows int64 for most rows -> NULL
+    plan = ScanAggPlan(exprs=e, keys=[k], aggs=[(K.AGG_SUM, prod), (K.AGG_SUM, up), (K.AGG_COUNT, up64), (K.AGG_MAX, prod), (K.AGG_MIN, up)])
+    check(ctx, oracle, plan, ch)
+
+
+def test_integer_arithmetic_wraps(ctx, oracle):
+    rng = np.random.default_rng(4)
+    n = 10000
+    ch = K.Chunk(n, {0: _rand_col(rng, K.TYPE_INT, n), 1: _rand_col(rng, K.TYPE_INT, n), 2: _rand_col(rng, K.TYPE_BIGINT, n)})
+    e = ExprBuilder()
+    x, y, z = e.slot(0, K.TYPE_INT), e.slot(1, K.TYPE_INT), e.slot(2, K.TYPE_BIGINT)
+    plan = ScanAggPlan(exprs=e, aggs=[(K.AGG_SUM, e.mul(x, y)), (K.AGG_SUM, e.add(x, y)), (K.AGG_SUM, e.mul(z, z)), (K.AGG_MIN, e.sub(z, e.cast(x, K.TYPE_BIGINT)))])
+    check(ctx, oracle, plan, ch)
+
+
+@pytest.mark.parametrize("keys", [[K.TYPE_INT], [K.TYPE_BIGINT], [K.TYPE_DATE], [K.TYPE_TINYINT, K.TYPE_SMALLINT], [K.TYPE_INT, K.TYPE_INT],
+                                  [K.TYPE_INT, K.TYPE_DATE, K.TYPE_INT], [K.TYPE_DECIMAL128], [K.TYPE_BIGINT, K.TYPE_INT]])
+@pytest.mark.parametrize("null_frac", [0.0, 0.2])
+def test_group_by_key_shapes(ctx, oracle, keys, null_frac):
+    # AggHashMap variants (agg_hash_variant.h:40-105): single number key, fixed-size packed keys, nullable keys
+    rng = np.random.default_rng(len(keys) * 10 + int(null_frac * 10))
+    n = 40000
+    cols = {i: _rand_col(rng, t, n, null_frac, small=True) for i, t in enumerate(keys)}
+    cols[10] = _rand_col(rng, K.TYPE_DECIMAL64, n, 0.1, p=15, s=2)
+    cols[11] = _rand_col(rng, K.TYPE_DOUBLE, n, 0.1)
+    ch = K.Chunk(n, cols)
+    e = ExprBuilder()
+    ks = [e.slot(i, t) for i, t in enumerate(keys)]
+    m, d = e.slot(10, K.TYPE_DECIMAL64, 15, 2), e.slot(11, K.TYPE_DOUBLE)
+    aggs = [(K.AGG_SUM, m), (K.AGG_AVG, m), (K.AGG_COUNT, m), (K.AGG_COUNT, None), (K.AGG_MIN, m), (K.AGG_MAX, m), (K.AGG_SUM, d), (K.AGG_AVG, d),
+            (K.AGG_MIN, d), (K.AGG_MAX, d)]
+    plan = ScanAggPlan(exprs=e, keys=ks, aggs=aggs)
+    check(ctx, oracle, plan, ch)
+    check(ctx, oracle, plan, ch, piece_rows=4096)
+
+
+def test_group_by_binary_keys(ctx, oracle):
+    # AggHashMapWithSerializedKey (agg_hash_map.h:652-898): two VARCHAR(1) keys serialise to 10 bytes
+    rng = np.random.default_rng(8)
+    n = 30000
+    a = [bytes([65 + int(x)]) for x in rng.integers(0, 3, n)]
+    b = [b"" if x == 0 else bytes([70 + int(x)]) * int(x) for x in rng.integers(0, 3, n)]
+    nulls = (rng.random(n) < 0.1).astype(np.uint8)
+    ch = K.Chunk(n, {0: K.Column.from_strings(a), 1: K.Column.from_strings(b, nulls), 2: _rand_col(rng, K.TYPE_BIGINT, n, small=True)})
+    e = ExprBuilder()
+    k1, k2, v = e.slot(0, K.TYPE_VARCHAR), e.slot(1, K.TYPE_VARCHAR), e.slot(2, K.TYPE_BIGINT)
+    plan = ScanAggPlan(exprs=e, keys=[k1, k2], aggs=[(K.AGG_SUM, v), (K.AGG_COUNT, None)])
+    check(ctx, oracle, plan, ch)
+    check(ctx, oracle, plan, ch, piece_rows=1000)
+    check(ctx, oracle, plan, ch, device=True)
+
+
+def test_table_growth_and_deferred_rows(ctx, oracle):
+    # no cardinality hint: the table starts at 1024 slots and must grow (rehash) while rows are deferred and replayed
+    rng = np.random.default_rng(9)
+    n = 600000
+    keys = rng.integers(0, 200000, n)
+    ch = K.Chunk(n, {0: K.Column.from_ints(K.TYPE_BIGINT, keys), 1: K.Column.from_ints(K.TYPE_BIGINT, rng.integers(-1000, 1000, n))})
+    e = ExprBuilder()
+    k, v = e.slot(0, K.TYPE_BIGINT), e.slot(1, K.TYPE_BIGINT)
+    plan = ScanAggPlan(exprs=e, keys=[k], aggs=[(K.AGG_SUM, v), (K.AGG_COUNT, None), (K.AGG_MIN, v)])
+    got = check(ctx, oracle, plan, ch)
+    assert got.n_rows == len(np.unique(keys))
+    check(ctx, oracle, plan, ch, piece_rows=50000)
+
+
+def test_all_phases_with_groups(ctx, oracle):
+    rng = np.random.default_rng(10)
+    n = 20000
+    ch = K.Chunk(n, {0: K.Column.from_ints(K.TYPE_INT, rng.integers(0, 50, n)), 1: _rand_col(rng, K.TYPE_DECIMAL64, n, 0.1, p=15, s=2),
+                     2: _rand_col(rng, K.TYPE_DOUBLE, n, 0.1), 3: _rand_col(rng, K.TYPE_INT, n, 0.1)})
+    e = ExprBuilder()
+    k, m, d, i = e.slot(0, K.TYPE_INT), e.slot(1, K.TYPE_DECIMAL64, 15, 2), e.slot(2, K.TYPE_DOUBLE), e.slot(3, K.TYPE_INT)
+    aggs = [(K.AGG_SUM, m), (K.AGG_AVG, m), (K.AGG_COUNT, m), (K.AGG_MIN, m), (K.AGG_AVG, d), (K.AGG_SUM, d), (K.AGG_AVG, i), (K.AGG_MAX, i), (K.AGG_COUNT, None)]
+    p1 = ScanAggPlan(exprs=e, keys=[k], aggs=aggs, phase=K.AGG_UPDATE_SERIALIZE)
+    halves = [K.Chunk(n // 2, {s: K.Column(c.type, c.data[:n // 2], None if c.nulls is None else c.nulls[:n // 2], None, c.precision, c.scale)
+                               for s, c in ch.columns.items()}),
+              K.Chunk(n - n // 2, {s: K.Column(c.type, c.data[n // 2:], None if c.nulls is None else c.nulls[n // 2:], None, c.precision, c.scale)
+                                   for s, c in ch.columns.items()})]
+    inter = [check(ctx, oracle, p1, h) for h in halves]
+    # concatenate the two intermediate chunks and merge them (phase 2)
+    cols = {}
+    for s in inter[0].columns:
+        c0, c1 = inter[0].columns[s], inter[1].columns[s]
+        vals = K.column_pyvalues(c0) + K.column_pyvalues(c1)
+        nulls = [1 if v is None else 0 for v in vals]
+        if K.is_binary(c0.type):
+            col = K.Column.from_strings([b"" if v is None else v for v in vals], nulls, type_=c0.type)
+        elif c0.type == K.TYPE_DOUBLE:
+            col = K.Column.from_ints(c0.type, [0.0 if v is None else v for v in vals], nulls)
+        else:
+            col = K.Column.from_ints(c0.type, [0 if v is None else v for v in vals], nulls)
+        col.precision, col.scale = c0.precision, c0.scale
+        cols[s] = col
+    merged_in = K.Chunk(inter[0].n_rows + inter[1].n_rows, cols)
+    e2 = ExprBuilder()
+    k2 = e2.slot(0, K.TYPE_INT)
+    args = [e2.slot(1 + a, cols[1 + a].type, cols[1 + a].precision, cols[1 + a].scale) for a in range(len(aggs))]
+    p2 = ScanAggPlan(exprs=e2, keys=[k2], aggs=[(fn, args[a]) for a, (fn, _) in enumerate(aggs)], phase=K.AGG_MERGE_FINALIZE)
+    two_phase = check(ctx, oracle, p2, merged_in)
+    single = run_gpu(ctx, ScanAggPlan(exprs=e, keys=[k], aggs=aggs), ch)
+    assert rows_equal(K.chunk_rows(two_phase), K.chunk_rows(single))
+
+
+# ---- the benchmark pipelines on synthetic TPC-H-shaped data: static (TMA) kernels vs generic kernel vs oracle ---------------
+def _both_kernel_families(ctx, oracle, plan_fn, chunk, **kw):
+    want = K.chunk_rows(oracle.scan_agg(plan_fn(), chunk, n_threads=4))
+    outs = []
+    for force in (False, True):
+        if force:
+            os.environ["SRB_FORCE_GENERIC"] = "1"
+        try:
+            for dev in (True, False):
+                outs.append(K.chunk_rows(run_gpu(ctx, plan_fn(), chunk, device=dev, **kw)))
+        finally:
+            os.environ.pop("SRB_FORCE_GENERIC", None)
+    for o in outs:
+        assert rows_equal(o, want), (o[:2], want[:2])
+
+
+@pytest.mark.parametrize("n", [1024, 5000, 300001, 2_000_000])
+def test_q6_pipeline(ctx, oracle, n):
+    _both_kernel_families(ctx, oracle, Q.q6_plan, T.host_chunk("lineitem", 12345, n, T.LINEITEM_Q6))
+
+
+@pytest.mark.parametrize("n", [1024, 70000, 1_500_000])
+def test_q1_pipeline_dict_keys(ctx, oracle, n):
+    ch = T.host_chunk("lineitem", 777, n, T.LINEITEM_Q1)
+    _both_kernel_families(ctx, oracle, Q.q1_plan, ch)
+    got = run_gpu(ctx, Q.q1_plan(), ch, device=True)
+    assert got.n_rows == 4 or n < 5000
+
+
+def test_q1_pipeline_binary_keys(ctx, oracle):
+    ch = T.add_binary_keys(T.host_chunk("lineitem", 0, 200000, T.LINEITEM_Q1))
+    plan = Q.q1_plan(dict_keys=False)
+    got = check(ctx, oracle, plan, ch)
+    assert got.n_rows == 4
+    check(ctx, oracle, plan, ch, piece_rows=4096)
+
+
+def test_q1_more_groups_than_register_banks(ctx, oracle):
+    # the static Q1 kernel keeps 4 groups in registers; extra groups must take the global-table path and still be exact
+    ch = T.host_chunk("lineitem", 0, 400000, T.LINEITEM_Q1)
+    rf = ch.columns[Q.L_RETURNFLAG_CODE].data
+    rf[:] = np.arange(len(rf)) % 11
+    _both_kernel_families(ctx, oracle, Q.q1_plan, ch)
+
+
+def test_q1_overflowing_charge_is_null(ctx, oracle):
+    ch = T.host_chunk("lineitem", 0, 100000, T.LINEITEM_Q1)
+    ext = ch.columns[Q.L_EXTENDEDPRICE].data
+    ext[::7] = 2**62  # ext*(1-disc) fits int128, times (1+tax) overflows -> NULL rows inside sum(charge)
+    ext[5::11] = -2**62
+    _both_kernel_families(ctx, oracle, Q.q1_plan, ch)
+
+
+@pytest.mark.parametrize("n,nk", [(1024, 100), (500000, 1000), (3_000_000, 1_000_000)])
+def test_highcard_pipeline(ctx, oracle, n, nk):
+    ch = T.host_chunk("highcard", 0, n, ["k", "v"], n_keys=nk)
+    _both_kernel_families(ctx, oracle, lambda: Q.highcard_plan(group_hint=0), ch)
+    _both_kernel_families(ctx, oracle, lambda: Q.highcard_plan(group_hint=nk), ch)
+
+
+def test_host_chunks_of_4096_rows_like_the_pipeline_driver(ctx, oracle):
+    # pipeline_driver.cpp:345-351: chunks of <= chunk_size rows; results must not depend on the chunking
+    ch = T.host_chunk("lineitem", 99, 123457, T.LINEITEM_Q1)
+    want = K.chunk_rows(oracle.scan_agg(Q.q1_plan(), ch))
+    for piece in (4096, 1000, 50000):
+        assert rows_equal(K.chunk_rows(run_gpu(ctx, Q.q1_plan(), ch, piece_rows=piece)), want)
+
+
+def test_pull_chunk_slices_of_chunk_size(ctx, oracle):
+    from starrocks_b200 import ops
+    ch = T.host_chunk("highcard", 0, 100000, ["k", "v"], n_keys=10000)
+    op = ops.ScanAggOperator(ctx, Q.highcard_plan())
+    assert op.need_input() and not op.has_output()
+    op.push_chunk(ch)
+    op.set_finishing()
+    op.set_finishing()  # idempotent (operator.h:66)
+    rows, n_chunks = [], 0
+    while op.has_output():
+        c = op.pull_chunk()
+        assert c is not None and 0 < c.n_rows <= 4096
+        rows += K.chunk_rows(c, sort=False)
+        n_chunks += 1
+    assert op.is_finished() and op.pull_chunk() is None
+    cnt = op.counters()
+    assert cnt["rows_in"] == 100000 and cnt["rows_selected"] == 100000 and cnt["kernel_launches"] > 0
+    op.close()
+    assert n_chunks == math.ceil(len(rows) / 4096)
+    assert sorted(rows) == K.chunk_rows(oracle.scan_agg(Q.highcard_plan(), ch))
+
+
+def test_error_convention(ctx):
+    from starrocks_b200 import ops
+    op = ops.ScanAggOperator(ctx, Q.q6_plan())
+    with pytest.raises(ops.SrbError) as ei:
+        op.pull_chunk()  # blocking aggregate: no output before set_finishing
+    assert ei.value.code == K.INTERNAL_ERROR
+    op.set_finishing()
+    with pytest.raises(ops.SrbError):
+        op.push_chunk(T.host_chunk("lineitem", 0, 10, T.LINEITEM_Q6))
+    op.close()
+    op = ops.ScanAggOperator(ctx, Q.q6_plan())
+    with pytest.raises(ops.SrbError) as ei:
+        op.push_chunk(K.Chunk(3, {0: K.Column.from_ints(K.TYPE_INT, [1, 2, 3])}))  # slots of the plan missing
+    assert ei.value.code == K.INVALID_ARGUMENT
+    op.set_cancelled()
+    assert op.is_finished() and not op.has_output() and not op.need_input()
+    op.close()
+    e = ExprBuilder()
+    long_keys = [e.slot(i, K.TYPE_BIGINT) for i in range(3)]  # 24-byte packed key
+    op = ops.ScanAggOperator(ctx, ScanAggPlan(exprs=e, keys=long_keys, aggs=[(K.AGG_COUNT, None)]))
+    with pytest.raises(ops.SrbError) as ei:
+        op.push_chunk(K.Chunk(1, {i: K.Column.from_ints(K.TYPE_BIGINT, [1]) for i in range(3)}))
+    assert ei.value.code == K.NOT_IMPLEMENTED
+    op.close()
+
+
+# ---- joins ------------------------------------------------------------------------------------------------------------------
+def run_join(ctx, plan, build, probe, build_pieces=1, device=False):
+    from starrocks_b200 import ops
+    op = ops.HashJoinOperator(ctx, plan)
+    ptrs = []
+    try:
+        assert not op.probe.need_input()  # hash_join_probe_operator.cpp:55-77: gated on the build
+        step = max(1, build.n_rows // build_pieces)
+        for a in range(0, build.n_rows, step):
+            op.push_chunk(ops.slice_chunk(build, a, min(build.n_rows, a + step)))
+        op.set_finishing()
+        assert op.probe.need_input()
+        if device:
+            probe, ptrs = ctx.device_chunk(probe)
+        op.probe.push_chunk(probe)
+        op.probe.set_finishing()
+        out = op.probe.pull_all()
+        assert op.probe.is_finished()
+        return out
+    finally:
+        for p in ptrs:
+            ctx.device_free(p)
+        op.close()
+
+
+def test_join_reference_vectors(ctx, oracle):
+    # be/test/exec/join_hash_map_test.cpp semantics: 1-based build indexes, NULL keys never match, one-to-many chains
+    build = K.Chunk(6, {0: K.Column.from_ints(K.TYPE_INT, [1, 2, 2, 3, 5, 7], nulls=[0, 0, 0, 0, 1, 0]),
+                        1: K.Column.from_ints(K.TYPE_BIGINT, [10, 20, 21, 30, 50, 70])})
+    probe = K.Chunk(5, {2: K.Column.from_ints(K.TYPE_INT, [2, 3, 4, 5, 7], nulls=[0, 0, 0, 0, 1]),
+                        3: K.Column.from_ints(K.TYPE_BIGINT, [200, 300, 400, 500, 700])})
+    plan = JoinPlan([0], [2], build_out=[1], probe_out=[3], emit_indexes=True)
+    rows = K.chunk_rows(run_join(ctx, plan, build, probe))
+    assert rows == [(200, 20, 0, 2), (200, 21, 0, 3), (300, 30, 1, 4)]
+    assert rows == K.chunk_rows(oracle.join(plan, build, probe))
+    semi = JoinPlan([0], [2], probe_out=[3], join_type=K.JOIN_LEFT_SEMI)
+    assert K.chunk_rows(run_join(ctx, semi, build, probe)) == [(200,), (300,)]
+
+
+@pytest.mark.parametrize("ktypes", [[K.TYPE_INT], [K.TYPE_BIGINT], [K.TYPE_INT, K.TYPE_INT], [K.TYPE_SMALLINT], [K.TYPE_BIGINT, K.TYPE_INT],
+                                    [K.TYPE_DECIMAL128]])
+def test_join_key_widths_against_oracle(ctx, oracle, ktypes):
+    rng = np.random.default_rng(len(ktypes) + ktypes[0])
+    nb, npb = 30000, 100000
+    bcols = {i: _rand_col(rng, t, nb, 0.05, small=True) for i, t in enumerate(ktypes)}
+    pcols = {10 + i: _rand_col(rng, t, npb, 0.05, small=True) for i, t in enumerate(ktypes)}
+    if len(ktypes) == 1 and ktypes[0] != K.TYPE_SMALLINT:  # wider domain: mostly unique build keys
+        bcols[0] = K.Column.from_ints(ktypes[0], rng.permutation(nb * 3)[:nb] - nb)
+        pcols[10] = K.Column.from_ints(ktypes[0], rng.integers(-nb, 2 * nb, npb))
+    bcols[5] = _rand_col(rng, K.TYPE_DECIMAL64, nb, 0.1, p=15, s=2)
+    bcols[6] = K.Column.from_ints(K.TYPE_INT, np.arange(nb))
+    pcols[15] = K.Column.from_ints(K.TYPE_BIGINT, np.arange(npb))
+    build, probe = K.Chunk(nb, bcols), K.Chunk(npb, pcols)
+    plan = JoinPlan(list(range(len(ktypes))), [10 + i for i in range(len(ktypes))], build_out=[5, 6], probe_out=[15, 10])
+    if ktypes == [K.TYPE_SMALLINT]:  # 100 distinct keys x 30000 x 100000 rows would explode: shrink
+        build = K.Chunk(300, {s: K.Column(c.type, c.data[:300], None if c.nulls is None else c.nulls[:300], None, c.precision, c.scale) for s, c in bcols.items()})
+        probe = K.Chunk(2000, {s: K.Column(c.type, c.data[:2000], None if c.nulls is None else c.nulls[:2000], None, c.precision, c.scale) for s, c in pcols.items()})
+    want = K.chunk_rows(oracle.join(plan, build, probe))
+    assert K.chunk_rows(run_join(ctx, plan, build, probe)) == want
+    assert K.chunk_rows(run_join(ctx, plan, build, probe, build_pieces=7, device=True)) == want
+    assert len(want) > 0
+
+
+def test_join_empty_sides(ctx, oracle):
+    build = K.Chunk(3, {0: K.Column.from_ints(K.TYPE_INT, [1, 2, 3]), 1: K.Column.from_ints(K.TYPE_INT, [7, 8, 9])})
+    probe = K.Chunk(2, {2: K.Column.from_ints(K.TYPE_INT, [10, 11])})
+    plan = JoinPlan([0], [2], build_out=[1], probe_out=[2])
+    assert run_join(ctx, plan, build, probe).n_rows == 0
+    empty_build = K.Chunk(0, {0: K.Column.from_ints(K.TYPE_INT, []), 1: K.Column.from_ints(K.TYPE_INT, [])})
+    assert run_join(ctx, plan, empty_build, probe).n_rows == 0
+
+
+def test_q3_pipeline_chained_on_device(ctx, oracle):
+    """customer(filter) -> build; orders(filter) -> probe -> build; lineitem(filter) -> probe -> group by, all operator outputs
+    handed over as device chunks; compared with the same chain through the oracle."""
+    from starrocks_b200 import ops
+    n_c, n_o, n_l = 15000, 150000, 600000
+    cust = T.host_chunk("customer", 0, n_c, ["c_custkey", "c_mktsegment_code"])
+    orders = T.host_chunk("orders", 0, n_o, ["o_orderkey", "o_custkey", "o_orderdate", "o_shippriority"], n_customers=n_c)
+    line = T.host_chunk("lineitem", 0, n_l, ["l_orderkey", "l_extendedprice", "l_discount", "l_shipdate"])
+
+    # oracle chain
+    oc = oracle.scan_agg(Q.q3_customer_filter(), cust)
+    oo = oracle.scan_agg(Q.q3_orders_filter(), orders)
+    j1 = oracle.join(Q.q3_join_customer_orders(), oc, oo)
+    ol = oracle.scan_agg(Q.q3_lineitem_filter(), line)
+    j2 = oracle.join(Q.q3_join_orders_lineitem(), j1, ol)
+    want = K.chunk_rows(oracle.scan_agg(Q.q3_agg_plan(), j2))
+    assert len(want) > 100
+
+    def filt(plan, ch):
+        op = ops.ScanAggOperator(ctx, plan)
+        op.push_chunk(ch)
+        op.set_finishing()
+        return op, op.pull_device()
+
+    fc, dc = filt(Q.q3_customer_filter(), cust)
+    jo1 = ops.HashJoinOperator(ctx, Q.q3_join_customer_orders())
+    jo1.push_chunk(dc)
+    jo1.set_finishing()
+    fo, do = filt(Q.q3_orders_filter(), orders)
+    jo1.probe.push_chunk(do)
+    d1 = jo1.probe.pull_device()
+    jo2 = ops.HashJoinOperator(ctx, Q.q3_join_orders_lineitem())
+    jo2.push_chunk(d1)
+    jo2.set_finishing()
+    fl, dl = filt(Q.q3_lineitem_filter(), line)
+    jo2.probe.push_chunk(dl)
+    d2 = jo2.probe.pull_device()
+    agg = ops.ScanAggOperator(ctx, Q.q3_agg_plan())
+    agg.push_chunk(d2)
+    agg.set_finishing()
+    got = K.chunk_rows(agg.pull_all())
+    for o in (fc, fo, fl, jo1, jo2, agg):
+        o.close()
+    assert got == want
+
+
+def test_device_pull_of_aggregate_result(ctx, oracle):
+    from starrocks_b200 import ops
+    ch = T.host_chunk("highcard", 0, 200000, ["k", "v"], n_keys=5000)
+    op = ops.ScanAggOperator(ctx, Q.highcard_plan())
+    op.push_chunk(ch)
+    op.set_finishing()
+    d = op.pull_device()
+    got = ctx.fetch_chunk(d)
+    op.close()
+    assert K.chunk_rows(got) == K.chunk_rows(oracle.scan_agg(Q.highcard_plan(), ch))
