@@ -253,6 +253,10 @@ srb_status srb_op_sync(srb_op* op);
 /* rows pushed / rows that passed the predicates / kernels launched so far (RuntimeProfile counters, operator.h:310-327) */
 srb_status srb_op_counters(srb_op* op, int64_t* rows_in, int64_t* rows_selected, int64_t* kernel_launches);
 
+/* device time (CUDA events on the op's stream) spent in the main scan/aggregate kernel(s), the number of timed batches,
+ * how many of them ran a statically specialised (TMA-staged) kernel, and which shape matched (-1 = generic interpreter) */
+srb_status srb_op_profile(srb_op* op, double* kernel_ms, int64_t* batches, int64_t* static_launches, int32_t* shape);
+
 /* probe side of a join op: HashJoinProbeOperator::push_chunk / pull_chunk (hash_join_probe_operator.cpp:79-88).
  * The probe state is separate from the build operator state so that has_output/need_input keep the reference's
  * meaning on each side. */

@@ -164,6 +164,14 @@ srb_status srb_op_counters(srb_op* op, int64_t* rows_in, int64_t* rows_selected,
     SRB_API_END
 }
 
+srb_status srb_op_profile(srb_op* op, double* kernel_ms, int64_t* batches, int64_t* static_launches, int32_t* shape) {
+    SRB_API_BEGIN
+    if (!op || !kernel_ms || !batches || !static_launches || !shape) throw srb::Error(SRB_INVALID_ARGUMENT, "null argument");
+    op->profile(kernel_ms, batches, static_launches, shape);
+    return SRB_OK;
+    SRB_API_END
+}
+
 srb_status srb_join_probe_push_chunk(srb_op* op, const srb_chunk* chunk) {
     SRB_API_BEGIN
     OP_GUARD(op)

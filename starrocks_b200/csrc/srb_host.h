@@ -153,6 +153,12 @@ struct srb_op {
     virtual srb_status pull_chunk(srb_chunk* out, bool all) = 0;
     virtual srb_status pull_device(srb_chunk*) { throw srb::Error(SRB_NOT_IMPLEMENTED, "device pull not supported by this operator"); }
     virtual void refresh_counters() {}
+    virtual void profile(double* kernel_ms, int64_t* batches, int64_t* static_launches, int32_t* shape) {
+        *kernel_ms = 0;
+        *batches = 0;
+        *static_launches = 0;
+        *shape = -1;
+    }
     // join ops override the probe side
     virtual void probe_push_chunk(const srb_chunk*) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
     virtual void probe_set_finishing() { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }

@@ -389,7 +389,7 @@ private:
                 if (i >= ocols_.size() || !ocols_[i].known) { // nothing was ever produced: describe from the inputs
                     const GrowCol* src = i < pout_.size() ? (pkeys_.size() + i < pcols_.size() ? &pcols_[pkeys_.size() + i] : nullptr)
                                                           : &bcols_[bkeys_.size() + (i - pout_.size())];
-                    c.type = src ? src->type : SRB_TYPE_BIGINT;
+                    c.type = src && src->known ? src->type : SRB_TYPE_BIGINT; // no chunk ever described it (empty side)
                     c.precision = src ? src->precision : 0;
                     c.scale = src ? src->scale : 0;
                     w = type_width(c.type);

@@ -448,6 +448,8 @@ public:
         for (auto& s : stage_)
             if (s.copied) cudaEventDestroy(s.copied);
         if (kernel_done_) cudaEventDestroy(kernel_done_);
+        if (ev0_) cudaEventDestroy(ev0_);
+        if (ev1_) cudaEventDestroy(ev1_);
     }
 
     void push_chunk(const srb_chunk* ch) override {
@@ -522,6 +524,12 @@ public:
     }
 
     void refresh_counters() override { rows_selected = (int64_t)selected_total_; }
+    void profile(double* kernel_ms, int64_t* batches, int64_t* static_launches, int32_t* shape) override {
+        *kernel_ms = kernel_ms_;
+        *batches = timed_batches_;
+        *static_launches = static_launches_;
+        *shape = shape_;
+    }
 
     // all remaining rows as device-resident columns (operator chaining on the GPU)
     srb_status pull_device(srb_chunk* out) override {
@@ -730,14 +738,24 @@ private:
         // recognised shapes run the TMA-staged static kernel over the whole tiles; the generic kernel takes the rest
         int64_t covered = 0;
         Counters* dc = ctr_dev_.as<Counters>();
+        if (!ev0_) {
+            SRB_CUDA(cudaEventCreate(&ev0_));
+            SRB_CUDA(cudaEventCreate(&ev1_));
+        }
+        SRB_CUDA(cudaEventRecord(ev0_, stream)); // device time of the main kernel(s) of this batch, read in check_batch
         if (shape_ >= 0 && !defer_in && !force_generic_) {
             covered = launch_static_shape(shape_, L_.prog, tv, off, n, dout, &dc->rows_selected, &dc->deferred, ctx->n_sms, stream);
-            if (covered) launches++;
+            if (covered) {
+                launches++;
+                static_launches_++;
+            }
         }
         if (covered < n) {
             k_scan_agg_generic<<<grid_for(n - covered), 256, 0, stream>>>(L_.prog, tv, off + covered, n - covered, covered, defer_in, dout, dc);
             launches++;
         }
+        SRB_CUDA(cudaEventRecord(ev1_, stream));
+        timed_pending_ = true;
         SRB_CUDA(cudaGetLastError());
     }
 
@@ -751,6 +769,13 @@ private:
             SRB_CUDA(cudaMemsetAsync(ctr_dev_.p, 0, sizeof(Counters), stream));
             if (L_.prog.n_keys) SRB_CUDA(cudaMemsetAsync(shards_.p, 0, shards_.bytes, stream));
             SRB_CUDA(cudaStreamSynchronize(stream));
+            if (timed_pending_) {
+                float ms = 0;
+                SRB_CUDA(cudaEventElapsedTime(&ms, ev0_, ev1_));
+                kernel_ms_ += ms;
+                timed_batches_++;
+                timed_pending_ = false;
+            }
             selected_total_ += hc->rows_selected;
             if (hc->key_too_long) throw Error(SRB_NOT_IMPLEMENTED, "serialized group key longer than 16 bytes");
             if (L_.prog.n_keys)
@@ -1113,7 +1138,10 @@ private:
     bool force_generic_ = getenv("SRB_FORCE_GENERIC") != nullptr; // test hook: compare the two kernel families
     int64_t staging_rows_, chunk_size_;
     cudaStream_t copy_stream_ = nullptr;
-    cudaEvent_t kernel_done_ = nullptr;
+    cudaEvent_t kernel_done_ = nullptr, ev0_ = nullptr, ev1_ = nullptr;
+    bool timed_pending_ = false;
+    double kernel_ms_ = 0;
+    int64_t timed_batches_ = 0, static_launches_ = 0;
     // table
     DevBuf slots_, shards_, defer_[2];
     int defer_cur_ = 0;

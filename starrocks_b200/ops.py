@@ -23,7 +23,7 @@ EXPORTS = [
     "srb_ctx_create", "srb_ctx_destroy", "srb_last_error", "srb_ctx_device_info", "srb_op_stream",
     "srb_scan_agg_create", "srb_join_create", "srb_op_push_chunk", "srb_op_set_finishing", "srb_op_has_output",
     "srb_op_need_input", "srb_op_is_finished", "srb_op_pull_chunk", "srb_op_pull_all", "srb_op_pull_device",
-    "srb_op_cancel", "srb_op_close", "srb_op_sync", "srb_op_counters",
+    "srb_op_cancel", "srb_op_close", "srb_op_sync", "srb_op_counters", "srb_op_profile",
     "srb_join_probe_push_chunk", "srb_join_probe_set_finishing", "srb_join_probe_has_output",
     "srb_join_probe_need_input", "srb_join_probe_is_finished", "srb_join_probe_pull_chunk",
     "srb_join_probe_pull_all", "srb_join_probe_pull_device",
@@ -69,6 +69,7 @@ def lib() -> C.CDLL:
     L.srb_op_close.argtypes = [vp]
     L.srb_op_close.restype = None
     L.srb_op_counters.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]
+    L.srb_op_profile.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), C.POINTER(i64), C.POINTER(i32)]
     L.srb_device_alloc.argtypes = [vp, i64, C.POINTER(vp)]
     L.srb_device_free.argtypes = [vp, vp]
     L.srb_device_free.restype = None
@@ -253,6 +254,11 @@ class ScanAggOperator(_Operator):
         a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
         _check(self.L.srb_op_counters(self.h, C.byref(a), C.byref(b), C.byref(c)))
         return {"rows_in": a.value, "rows_selected": b.value, "kernel_launches": c.value}
+
+    def profile(self):
+        ms, b, sl, sh = C.c_double(), C.c_int64(), C.c_int64(), C.c_int32()
+        _check(self.L.srb_op_profile(self.h, C.byref(ms), C.byref(b), C.byref(sl), C.byref(sh)))
+        return {"kernel_ms": ms.value, "batches": b.value, "static_launches": sl.value, "shape": sh.value}
 
     def close(self):
         if self.h:
