@@ -41,6 +41,8 @@ srb_status srb_ctx_create(const srb_config* cfg, srb_ctx** out) {
     cudaDeviceProp p;
     SRB_CUDA(cudaGetDeviceProperties(&p, cfg->device));
     if (p.major < 10) throw srb::Error(SRB_INTERNAL_ERROR, srb::fmt("device is sm_%d%d; libsrb is built for sm_100a only", p.major, p.minor));
+    // the group table is probed with random 16..32-byte accesses: ask L2 not to over-fetch neighbouring sectors
+    cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, 32);
     auto* c = new srb_ctx();
     c->cfg = *cfg;
     if (c->cfg.world_size <= 0) c->cfg.world_size = 1;

@@ -9,6 +9,8 @@
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
+#include <map>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -66,6 +68,41 @@ struct srb_ctx {
     int sm_arch = 0;
     int64_t hbm_bytes = 0;
     int64_t mem_in_use = 0;
+    // freed device buffers kept for reuse: operators are created per query fragment, and cudaMalloc / cudaFree (which
+    // synchronises the device) would otherwise dominate short pipelines
+    std::mutex pool_mu;
+    std::multimap<size_t, void*> pool;
+    int64_t pool_bytes = 0;
+    static size_t round_size(size_t n) {
+        if (n <= 256) return 256;
+        if (n >= ((size_t)2 << 20)) return (n + ((size_t)2 << 20) - 1) & ~(((size_t)2 << 20) - 1);
+        size_t r = 256;
+        while (r < n) r <<= 1;
+        return r;
+    }
+    void* pool_take(size_t rounded) {
+        std::lock_guard<std::mutex> g(pool_mu);
+        auto it = pool.find(rounded);
+        if (it == pool.end()) return nullptr;
+        void* p = it->second;
+        pool.erase(it);
+        pool_bytes -= (int64_t)rounded;
+        return p;
+    }
+    bool pool_give(size_t rounded, void* p) {
+        std::lock_guard<std::mutex> g(pool_mu);
+        if (pool_bytes + (int64_t)rounded > ((int64_t)48 << 30)) return false;
+        pool.emplace(rounded, p);
+        pool_bytes += (int64_t)rounded;
+        return true;
+    }
+    void pool_clear() {
+        std::lock_guard<std::mutex> g(pool_mu);
+        for (auto& kv : pool) cudaFree(kv.second);
+        pool.clear();
+        pool_bytes = 0;
+    }
+    ~srb_ctx() { pool_clear(); }
 };
 
 namespace srb {
@@ -85,7 +122,7 @@ struct DevBuf {
     ~DevBuf() { release(); }
     void release() {
         if (p) {
-            cudaFree(p);
+            if (!ctx || !ctx->pool_give(bytes, p)) cudaFree(p);
             if (ctx) ctx->mem_in_use -= (int64_t)bytes;
         }
         p = nullptr;
@@ -96,11 +133,23 @@ struct DevBuf {
         if (n <= bytes && p) return;
         release();
         ctx = c;
-        if (n == 0) n = 16;
+        n = srb_ctx::round_size(n);
         if (c->cfg.mem_limit > 0 && c->mem_in_use + (int64_t)n > c->cfg.mem_limit)
             throw Error(SRB_MEM_LIMIT_EXCEEDED, fmt("device memory limit exceeded: %lld + %zu > %lld", (long long)c->mem_in_use, n,
                                                     (long long)c->cfg.mem_limit));
-        SRB_CUDA(cudaMalloc(&p, n));
+        p = c->pool_take(n);
+        if (!p) {
+            cudaError_t e = cudaMalloc(&p, n);
+            if (e == cudaErrorMemoryAllocation) { // give the cached buffers back to the driver and retry once
+                cudaGetLastError();
+                c->pool_clear();
+                e = cudaMalloc(&p, n);
+            }
+            if (e != cudaSuccess) {
+                p = nullptr;
+                SRB_CUDA(e);
+            }
+        }
         bytes = n;
         c->mem_in_use += (int64_t)n;
     }

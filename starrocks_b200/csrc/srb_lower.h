@@ -300,9 +300,9 @@ inline Lowered lower_plan(const PlanCopy& plan, const srb_chunk* first) {
         }
         return false;
     };
-    int off = 8; // meta word
-    P.off_key = P.n_keys ? (P.key_words == 2 ? 16 : 8) : 8;
-    off = P.n_keys ? P.off_key + 8 * P.key_words : 8;
+    // slot header: pair A {meta, key word 0}, pair B {key word 1, ready flag} for 16-byte keys (srb_prog.h)
+    int off = (P.n_keys && P.key_words == 2) ? 32 : 16;
+    P.off_state = off;
     // pairs need 16-byte alignment
     std::vector<int> need_pair(P.n_aggs, 0), need_n(P.n_aggs, 0);
     for (int a = 0; a < P.n_aggs; a++) {

@@ -84,8 +84,8 @@ struct DProg {
     int32_t phase_seed;  // 1 or 2: which phmap seed the table hash uses (agg_hash_variant.h:303-308)
     int32_t key_bytes;   // fixed packed key length, 0 when a binary key makes it per-row
     int32_t key_words;   // 1 or 2 (8- or 16-byte key area in a slot)
-    int32_t slot_bytes;  // stride of one table slot
-    int32_t off_key;     // byte offset of the key area
+    int32_t slot_bytes;  // stride of one table slot (multiple of 16)
+    int32_t off_state;   // first byte after the key header (16 or 32)
     int32_t _pad[2];
     ColBind cols[MAX_COLS];
     DNode nodes[MAX_NODES];
@@ -101,14 +101,18 @@ struct Val {
     bool null;
 };
 
-// slot meta word: low 2 bits = state, rest = hash tag
-constexpr uint64_t SLOT_EMPTY = 0, SLOT_CLAIMED = 1, SLOT_READY = 3;
+// Group-table slot: [A: meta u64 | key word 0] [B: key word 1 | ready flag  (16-byte keys only)] [states ...], 16-byte aligned.
+// meta = (hash & ~3) | 3 once the slot is taken, 0 while empty. A is claimed with ONE 128-bit compare-and-swap that writes the
+// tag and the first key word together, so an 8-byte key is published atomically: no lock state, no fence, no spinning. The
+// second key word of a 16-byte key follows in pair B as a single 16-byte store whose flag makes it self-validating.
+// Every aggregate state is valid when zero-filled (MIN/MAX keep order-preserving biased encodings), so a fresh slot needs
+// no initialisation.
+constexpr uint64_t SLOT_EMPTY = 0, SLOT_READY = 3;
+constexpr int TABLE_MAX_PROBE = 256; // a longer linear probe means the table is too full: the row is deferred and replayed
 
 struct TableView {
     uint8_t* slots;
     uint64_t mask; // capacity - 1
-    uint64_t limit; // occupied slots allowed before rows are deferred
-    unsigned long long* occupied;
     int32_t slot_bytes;
     int32_t key_words;
 };

@@ -214,73 +214,56 @@ SRB_D Val eval_node(const DNode& nd, const Val* v, const ColBind* cols, int64_t 
 }
 
 // ---- group table ---------------------------------------------------------------------------------------
-constexpr int TABLE_SHARDS = 256;       // insert-budget counters, one 128-byte line each
-constexpr int SHARD_STRIDE = 16;        // in uint64 units
-
-SRB_D void init_slot_states(const DProg& p, uint8_t* slot) {
-    for (int a = 0; a < p.n_aggs; a++) {
-        const DAgg& g = p.aggs[a];
-        if (g.fn != FN_MIN && g.fn != FN_MAX) continue;
-        const bool mn = g.fn == FN_MIN;
-        if (g.is_double) {
-            double init = mn ? __longlong_as_double(0x7ff0000000000000LL) : __longlong_as_double((long long)0xfff0000000000000ULL);
-            *(double*)(slot + g.off_lo) = init;
-        } else if (g.wide) {
-            *(uint64_t*)(slot + g.off_lo) = mn ? ~0ULL : 0ULL;
-            *(uint64_t*)(slot + g.off_hi) = mn ? 0x7fffffffffffffffULL : 0x8000000000000000ULL;
-        } else {
-            *(int64_t*)(slot + g.off_lo) = mn ? INT64_MAX : INT64_MIN;
-        }
-    }
+// 16-byte accesses on a 16-byte aligned pair: one L2 transaction, so a reader sees either the empty pair or the complete one
+SRB_D ulonglong2 ld_pair(const void* p) {
+    ulonglong2 v;
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
+    return v;
+}
+SRB_D void st_pair(void* p, uint64_t a, uint64_t b) { asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory"); }
+SRB_D ulonglong2 cas_pair(void* p, uint64_t c0, uint64_t c1, uint64_t n0, uint64_t n1) {
+    ulonglong2 o;
+    asm volatile(
+            "{\n\t.reg .b128 c, n, o;\n\t"
+            "mov.b128 c, {%2, %3};\n\t"
+            "mov.b128 n, {%4, %5};\n\t"
+            "atom.global.relaxed.gpu.cas.b128 o, [%6], c, n;\n\t"
+            "mov.b128 {%0, %1}, o;\n\t}"
+            : "=l"(o.x), "=l"(o.y)
+            : "l"(c0), "l"(c1), "l"(n0), "l"(n1), "l"(p)
+            : "memory");
+    return o;
 }
 
-// Open addressing, linear probing. Returns the slot of (klo,khi), inserting it when absent; nullptr when the
-// insert budget of this block's shard is spent (the row is then deferred and replayed after the host grew the table).
-SRB_D uint8_t* table_find_or_insert(const TableView& t, const DProg& p, uint64_t klo, uint64_t khi, uint64_t hash) {
-    const uint64_t tag = hash & ~3ULL;
+// Open addressing, linear probing. Returns the slot of (klo,khi), inserting it when absent (*inserted = true); nullptr when
+// the probe ran past TABLE_MAX_PROBE slots (table too full: the row is deferred and replayed after the host grew the table).
+SRB_D uint8_t* table_find_or_insert(const TableView& t, uint64_t klo, uint64_t khi, uint64_t hash, bool* inserted) {
+    const uint64_t tagw = (hash & ~3ULL) | SLOT_READY;
     uint64_t idx = (hash >> 7) & t.mask;
-    bool reserved = false;
-    unsigned long long* shard = t.occupied + (size_t)(blockIdx.x & (TABLE_SHARDS - 1)) * SHARD_STRIDE;
-    for (;;) {
+    *inserted = false;
+    for (int probe = 0; probe < TABLE_MAX_PROBE; probe++) {
         uint8_t* slot = t.slots + idx * (uint64_t)t.slot_bytes;
-        uint64_t* meta = (uint64_t*)slot;
-        uint64_t m = ld_relaxed_u64(meta);
-        if (m == SLOT_EMPTY) {
-            if (!reserved) {
-                unsigned long long used = atomicAdd(shard, 1ULL);
-                if (used >= t.limit) {
-                    atomicAdd(shard, (unsigned long long)-1LL);
-                    return nullptr;
-                }
-                reserved = true;
-            }
-            uint64_t old = atomicCAS((unsigned long long*)meta, 0ULL, (unsigned long long)(tag | SLOT_CLAIMED));
-            if (old == SLOT_EMPTY) {
-                uint64_t* k = (uint64_t*)(slot + p.off_key);
-                k[0] = klo;
-                if (t.key_words > 1) k[1] = khi;
-                init_slot_states(p, slot);
-                __threadfence();
-                st_release_u64(meta, tag | SLOT_READY);
+        ulonglong2 a = ld_pair(slot);
+        if (a.x == SLOT_EMPTY) {
+            a = cas_pair(slot, 0ULL, 0ULL, tagw, klo);
+            if (a.x == SLOT_EMPTY) { // claimed: tag and first key word are already visible as one unit
+                if (t.key_words > 1) st_pair(slot + 16, khi, 1ULL);
+                *inserted = true;
                 return slot;
             }
-            m = old; // somebody else claimed it; fall through and examine
         }
-        if ((m & ~3ULL) == tag) {
-            while ((m & 3ULL) != SLOT_READY) {
+        if (a.x == tagw && a.y == klo) {
+            if (t.key_words == 1) return slot;
+            ulonglong2 b = ld_pair(slot + 16);
+            while (b.y == 0) { // the claimer's second pair is in flight
                 __nanosleep(20);
-                m = ld_relaxed_u64(meta);
+                b = ld_pair(slot + 16);
             }
-            const uint64_t* k = (const uint64_t*)(slot + p.off_key);
-            bool eq = ld_relaxed_u64(k) == klo;
-            if (eq && t.key_words > 1) eq = ld_relaxed_u64(k + 1) == khi;
-            if (eq) {
-                if (reserved) atomicAdd(shard, (unsigned long long)-1LL);
-                return slot;
-            }
+            if (b.x == khi) return slot;
         }
         idx = (idx + 1) & t.mask;
     }
+    return nullptr;
 }
 
 // ---- packed group key ----------------------------------------------------------------------------------
@@ -365,38 +348,36 @@ SRB_D void atomic_add128(uint8_t* slot, int off_lo, int off_hi, uint64_t lo, uin
     if (add_hi) atomicAdd((unsigned long long*)(slot + off_hi), add_hi);
 }
 
-SRB_D void atomic_minmax128(uint8_t* slot, int off_lo, bool is_min, i128 x) {
-    // 16-byte aligned (lo,hi) pair, compare-and-swap loop on the whole pair
-    unsigned long long* p = (unsigned long long*)(slot + off_lo);
-    uint64_t cur_lo = ld_relaxed_u64((const uint64_t*)p), cur_hi = ld_relaxed_u64((const uint64_t*)p + 1);
-    for (;;) {
-        i128 cur = make_i128(cur_lo, (int64_t)cur_hi);
-        if (is_min ? !(x < cur) : !(x > cur)) return;
-        uint64_t nlo = lo64(x), nhi = (uint64_t)hi64(x), olo, ohi;
-        asm volatile(
-                "{\n\t.reg .b128 c, n, o;\n\t"
-                "mov.b128 c, {%2, %3};\n\t"
-                "mov.b128 n, {%4, %5};\n\t"
-                "atom.global.relaxed.gpu.cas.b128 o, [%6], c, n;\n\t"
-                "mov.b128 {%0, %1}, o;\n\t}"
-                : "=l"(olo), "=l"(ohi)
-                : "l"(cur_lo), "l"(cur_hi), "l"(nlo), "l"(nhi), "l"(p)
-                : "memory");
-        if (olo == cur_lo && ohi == cur_hi) return;
-        cur_lo = olo;
-        cur_hi = ohi;
-    }
+// MIN / MAX states hold order-preserving unsigned encodings whose identity is all-zero bits, so a zero-filled slot is a
+// valid empty state: MAX keeps enc(x) = x ^ signbit, MIN keeps ~enc(x); both are folded with an unsigned atomic max.
+SRB_HD uint64_t enc_i64(int64_t x, bool is_min) {
+    uint64_t u = (uint64_t)x ^ 0x8000000000000000ULL;
+    return is_min ? ~u : u;
 }
+SRB_HD int64_t dec_i64(uint64_t u, bool is_min) { return (int64_t)((is_min ? ~u : u) ^ 0x8000000000000000ULL); }
+SRB_HD uint64_t enc_f64(uint64_t bits, bool is_min) {
+    uint64_t u = bits ^ ((bits >> 63) ? ~0ULL : 0x8000000000000000ULL);
+    return is_min ? ~u : u;
+}
+SRB_HD uint64_t dec_f64(uint64_t u, bool is_min) {
+    if (is_min) u = ~u;
+    return u ^ ((u >> 63) ? 0x8000000000000000ULL : ~0ULL);
+}
+SRB_HD u128 enc_i128(i128 x, bool is_min) {
+    u128 u = (u128)x ^ ((u128)1 << 127);
+    return is_min ? ~u : u;
+}
+SRB_HD i128 dec_i128(u128 u, bool is_min) { return (i128)((is_min ? ~u : u) ^ ((u128)1 << 127)); }
 
-SRB_D void atomic_minmax_f64(uint8_t* slot, int off, bool is_min, double x) {
-    unsigned long long* p = (unsigned long long*)(slot + off);
-    unsigned long long cur = ld_relaxed_u64((const uint64_t*)p);
+SRB_D void atomic_umax128(uint8_t* slot, int off_lo, u128 x) {
+    // 16-byte aligned (lo,hi) pair, compare-and-swap loop on the whole pair
+    ulonglong2 cur = ld_pair(slot + off_lo);
     for (;;) {
-        double c = __longlong_as_double((long long)cur);
-        if (is_min ? !(x < c) : !(x > c)) return;
-        unsigned long long old = atomicCAS(p, cur, (unsigned long long)__double_as_longlong(x));
-        if (old == cur) return;
-        cur = old;
+        u128 c = ((u128)cur.y << 64) | cur.x;
+        if (!(x > c)) return;
+        ulonglong2 o = cas_pair(slot + off_lo, cur.x, cur.y, (uint64_t)x, (uint64_t)(x >> 64));
+        if (o.x == cur.x && o.y == cur.y) return;
+        cur = o;
     }
 }
 
@@ -442,13 +423,11 @@ SRB_D void update_agg_global(const DProg& p, const DAgg& g, uint8_t* slot, const
     default: {
         const bool mn = g.fn == FN_MIN;
         if (g.is_double)
-            atomic_minmax_f64(slot, g.off_lo, mn, __longlong_as_double((long long)x.lo));
+            atomicMax((unsigned long long*)(slot + g.off_lo), (unsigned long long)enc_f64(x.lo, mn));
         else if (g.wide)
-            atomic_minmax128(slot, g.off_lo, mn, make_i128(x.lo, x.hi));
-        else if (mn)
-            atomicMin((long long*)(slot + g.off_lo), (long long)x.lo);
+            atomic_umax128(slot, g.off_lo, enc_i128(make_i128(x.lo, x.hi), mn));
         else
-            atomicMax((long long*)(slot + g.off_lo), (long long)x.lo);
+            atomicMax((unsigned long long*)(slot + g.off_lo), (unsigned long long)enc_i64((int64_t)x.lo, mn));
     }
     }
     if (g.off_n >= 0) atomicAdd((unsigned long long*)(slot + g.off_n), 1ULL);

@@ -29,6 +29,7 @@ struct Counters {
     unsigned long long deferred;
     unsigned long long key_too_long;
     unsigned long long emitted;
+    unsigned long long inserted;
 };
 
 // ---- generic kernel: interprets the lowered program, one row per thread iteration ---------------------------
@@ -103,13 +104,11 @@ SRB_D void flush_local(const DAgg& g, const LocalAcc& s, uint8_t* slot) {
     } else {
         const bool mn = g.fn == FN_MIN;
         if (g.is_double)
-            atomic_minmax_f64(slot, g.off_lo, mn, __longlong_as_double((long long)s.lo));
+            atomicMax((unsigned long long*)(slot + g.off_lo), (unsigned long long)enc_f64(s.lo, mn));
         else if (g.wide)
-            atomic_minmax128(slot, g.off_lo, mn, make_i128(s.lo, (int64_t)s.hi));
-        else if (mn)
-            atomicMin((long long*)(slot + g.off_lo), (long long)s.lo);
+            atomic_umax128(slot, g.off_lo, enc_i128(make_i128(s.lo, (int64_t)s.hi), mn));
         else
-            atomicMax((long long*)(slot + g.off_lo), (long long)s.lo);
+            atomicMax((unsigned long long*)(slot + g.off_lo), (unsigned long long)enc_i64((int64_t)s.lo, mn));
     }
     if (g.off_n >= 0) atomicAdd((unsigned long long*)(slot + g.off_n), (unsigned long long)s.n);
 }
@@ -123,7 +122,7 @@ __global__ void __launch_bounds__(256) k_scan_agg_generic(const __grid_constant_
     const bool no_keys = p.n_keys == 0;
     if (no_keys)
         for (int a = 0; a < p.n_aggs; a++) acc[a] = LocalAcc{0, 0, 0};
-    unsigned long long selected = 0, deferred = 0, too_long = 0;
+    unsigned long long selected = 0, deferred = 0, too_long = 0, inserted = 0;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const int64_t bit = i + bit_base; // position of this row in the batch's deferral bitmaps
@@ -141,7 +140,9 @@ __global__ void __launch_bounds__(256) k_scan_agg_generic(const __grid_constant_
             too_long++;
             continue;
         }
-        uint8_t* slot = table_find_or_insert(tv, p, k.lo, k.hi, hash_packed_key(k, p.phase_seed));
+        bool fresh;
+        uint8_t* slot = table_find_or_insert(tv, k.lo, k.hi, hash_packed_key(k, p.phase_seed), &fresh);
+        inserted += fresh ? 1 : 0;
         if (!slot) {
             atomicOr(&defer_out[bit >> 5], 1u << (bit & 31));
             deferred++;
@@ -156,18 +157,13 @@ __global__ void __launch_bounds__(256) k_scan_agg_generic(const __grid_constant_
         selected += __shfl_down_sync(0xffffffffu, selected, o);
         deferred += __shfl_down_sync(0xffffffffu, deferred, o);
         too_long += __shfl_down_sync(0xffffffffu, too_long, o);
+        inserted += __shfl_down_sync(0xffffffffu, inserted, o);
     }
     if ((threadIdx.x & 31) == 0) {
         if (selected) atomicAdd(&ctr->rows_selected, selected);
         if (deferred) atomicAdd(&ctr->deferred, deferred);
         if (too_long) atomicAdd(&ctr->key_too_long, too_long);
-    }
-}
-
-__global__ void k_init_slot0(const __grid_constant__ DProg prog, uint8_t* slot) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
-        *(uint64_t*)slot = SLOT_READY;
-        init_slot_states(prog, slot);
+        if (inserted) atomicAdd(&ctr->inserted, inserted);
     }
 }
 
@@ -183,7 +179,7 @@ __global__ void k_rehash(const __grid_constant__ DProg prog, const uint8_t* __re
         for (;;) {
             uint8_t* d = nt.slots + idx * (uint64_t)sb;
             uint64_t old = atomicCAS((unsigned long long*)d, 0ULL, (unsigned long long)m);
-            if (old == SLOT_EMPTY) {
+            if (old == SLOT_EMPTY) { // the rehash runs alone on the stream: plain copies of the rest of the slot are safe
                 for (int b = 8; b < sb; b += 8) *(uint64_t*)(d + b) = *(const uint64_t*)(s + b);
                 break;
             }
@@ -200,7 +196,7 @@ struct EmitAgg {
     int32_t out_width;
     int32_t mode;   // 0 count, 1 raw state (sum/min/max/blob sum), 2 avg decimal, 3 avg date, 4 avg largeint->double, 5 avg double
     int32_t scale;  // avg decimal: argument scale
-    int32_t _pad;
+    int32_t decode; // MIN/MAX states are biased encodings (srb_rowpipe.cuh): 0 none, 1 max, 2 min; width/is_double pick the codec
 };
 struct EmitArgs {
     ulonglong2* keys;
@@ -232,8 +228,8 @@ __global__ void k_emit(const __grid_constant__ DProg prog, const uint8_t* __rest
         basepos = __shfl_sync(m, basepos, leader);
         int64_t row = (int64_t)(basepos + __popc(m & ((1u << lane) - 1)));
         if (p.n_keys) {
-            const uint64_t* k = (const uint64_t*)(s + p.off_key);
-            ea.keys[row] = make_ulonglong2(k[0], p.key_words > 1 ? k[1] : 0ULL);
+            const uint64_t* k = (const uint64_t*)s;
+            ea.keys[row] = make_ulonglong2(k[1], p.key_words > 1 ? k[2] : 0ULL);
         }
         for (int a = 0; a < p.n_aggs; a++) {
             const DAgg& g = p.aggs[a];
@@ -250,7 +246,20 @@ __global__ void k_emit(const __grid_constant__ DProg prog, const uint8_t* __rest
             }
             switch (e.mode) {
             case 0: store_w(e.val, row, 8, n, 0); break;
-            case 1: store_w(e.val, row, e.out_width, lo, hi); break;
+            case 1:
+                if (e.decode) {
+                    const bool mn = e.decode == 2;
+                    if (g.is_double)
+                        lo = dec_f64(lo, mn);
+                    else if (g.wide) {
+                        i128 x = dec_i128(((u128)hi << 64) | lo, mn);
+                        lo = lo64(x);
+                        hi = (uint64_t)hi64(x);
+                    } else
+                        lo = (uint64_t)dec_i64(lo, mn);
+                }
+                store_w(e.val, row, e.out_width, lo, hi);
+                break;
             case 2: {
                 i128 r = decimal_div_integer(make_i128(lo, (int64_t)hi), (i128)(int64_t)n, e.scale);
                 store_w(e.val, row, 16, lo64(r), (uint64_t)hi64(r));
@@ -439,7 +448,7 @@ public:
         chunk_size_ = c->cfg.chunk_size > 0 ? c->cfg.chunk_size : 4096;
         SRB_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
         ctr_dev_.ensure(c, sizeof(Counters));
-        ctr_host_.ensure(sizeof(Counters) + TABLE_SHARDS * SHARD_STRIDE * 8);
+        ctr_host_.ensure(sizeof(Counters));
         SRB_CUDA(cudaMemsetAsync(ctr_dev_.p, 0, sizeof(Counters), stream));
     }
     ~ScanAggOp() override {
@@ -641,11 +650,9 @@ private:
             cap_ = want;
         }
         alloc_table(slots_, cap_);
-        shards_.ensure(ctx, TABLE_SHARDS * SHARD_STRIDE * 8);
-        SRB_CUDA(cudaMemsetAsync(shards_.p, 0, shards_.bytes, stream));
-        if (P.n_keys == 0) {
-            k_init_slot0<<<1, 32, 0, stream>>>(P, slots_.as<uint8_t>());
-            launches++;
+        if (P.n_keys == 0) { // the single state block of a no-group-by aggregation: zero-filled states are valid, mark it taken
+            static const uint64_t ready = SLOT_READY;
+            SRB_CUDA(cudaMemcpyAsync(slots_.p, &ready, 8, cudaMemcpyHostToDevice, stream));
         }
         occupied_ = 0;
     }
@@ -654,12 +661,10 @@ private:
         buf.ensure(ctx, bytes);
         SRB_CUDA(cudaMemsetAsync(buf.p, 0, bytes, stream));
     }
-    TableView view(uint64_t shard_limit) {
+    TableView view() {
         TableView t;
         t.slots = slots_.as<uint8_t>();
         t.mask = cap_ - 1;
-        t.limit = shard_limit;
-        t.occupied = shards_.as<unsigned long long>();
         t.slot_bytes = L_.prog.slot_bytes;
         t.key_words = L_.prog.key_words;
         return t;
@@ -672,8 +677,6 @@ private:
         TableView nt;
         nt.slots = nb.as<uint8_t>();
         nt.mask = ncap - 1;
-        nt.limit = 0;
-        nt.occupied = nullptr;
         nt.slot_bytes = L_.prog.slot_bytes;
         nt.key_words = L_.prog.key_words;
         int blocks = (int)std::min<uint64_t>((cap_ + 255) / 256, (uint64_t)ctx->n_sms * 16);
@@ -702,13 +705,6 @@ private:
         }
     }
 
-    uint64_t shard_limit() const {
-        // inserts allowed per shard in one launch so that the table never exceeds ~7/8 full
-        uint64_t hard = cap_ - cap_ / 8;
-        uint64_t room = hard > occupied_ ? hard - occupied_ : 0;
-        return room / TABLE_SHARDS;
-    }
-
     void bind_prog(const ColBind* cols) {
         for (int i = 0; i < L_.prog.n_cols; i++) {
             L_.prog.cols[i].data = cols[i].data;
@@ -733,7 +729,7 @@ private:
                     SRB_CUDA(cudaMemsetAsync(defer_[i].p, 0, words * 4, stream));
                 }
         }
-        TableView tv = view(shard_limit());
+        TableView tv = view();
         uint32_t* dout = L_.prog.n_keys ? defer_[defer_cur_].as<uint32_t>() : nullptr;
         // recognised shapes run the TMA-staged static kernel over the whole tiles; the generic kernel takes the rest
         int64_t covered = 0;
@@ -744,7 +740,7 @@ private:
         }
         SRB_CUDA(cudaEventRecord(ev0_, stream)); // device time of the main kernel(s) of this batch, read in check_batch
         if (shape_ >= 0 && !defer_in && !force_generic_) {
-            covered = launch_static_shape(shape_, L_.prog, tv, off, n, dout, &dc->rows_selected, &dc->deferred, ctx->n_sms, stream);
+            covered = launch_static_shape(shape_, L_.prog, tv, off, n, dout, &dc->rows_selected, &dc->deferred, &dc->inserted, ctx->n_sms, stream);
             if (covered) {
                 launches++;
                 static_launches_++;
@@ -763,11 +759,8 @@ private:
     void check_batch(const ColBind* cols, int64_t off, int64_t n) {
         for (;;) {
             Counters* hc = ctr_host_.as<Counters>();
-            unsigned long long* hs = (unsigned long long*)(hc + 1);
             SRB_CUDA(cudaMemcpyAsync(hc, ctr_dev_.p, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
-            if (L_.prog.n_keys) SRB_CUDA(cudaMemcpyAsync(hs, shards_.p, shards_.bytes, cudaMemcpyDeviceToHost, stream));
             SRB_CUDA(cudaMemsetAsync(ctr_dev_.p, 0, sizeof(Counters), stream));
-            if (L_.prog.n_keys) SRB_CUDA(cudaMemsetAsync(shards_.p, 0, shards_.bytes, stream));
             SRB_CUDA(cudaStreamSynchronize(stream));
             if (timed_pending_) {
                 float ms = 0;
@@ -778,8 +771,7 @@ private:
             }
             selected_total_ += hc->rows_selected;
             if (hc->key_too_long) throw Error(SRB_NOT_IMPLEMENTED, "serialized group key longer than 16 bytes");
-            if (L_.prog.n_keys)
-                for (int s = 0; s < TABLE_SHARDS; s++) occupied_ += hs[s * SHARD_STRIDE];
+            occupied_ += hc->inserted;
             uint64_t deferred = hc->deferred;
             // deferred counts rows, not groups: bound one growth step so a burst of duplicates cannot over-allocate
             if (L_.prog.n_keys && (deferred || occupied_ * 2 > cap_))
@@ -975,6 +967,7 @@ private:
                 e.cnt = eval_[a].cnt.as<int64_t>();
             }
             e.scale = m.arg_scale;
+            e.decode = m.fn == SRB_AGG_MAX ? 1 : (m.fn == SRB_AGG_MIN ? 2 : 0);
             if (m.fn == SRB_AGG_COUNT)
                 e.mode = 0;
             else if (m.fn != SRB_AGG_AVG || m.blob)
@@ -1143,7 +1136,7 @@ private:
     double kernel_ms_ = 0;
     int64_t timed_batches_ = 0, static_launches_ = 0;
     // table
-    DevBuf slots_, shards_, defer_[2];
+    DevBuf slots_, defer_[2];
     int defer_cur_ = 0;
     uint64_t cap_ = 0, occupied_ = 0, selected_total_ = 0;
     DevBuf ctr_dev_;

@@ -43,7 +43,7 @@ struct SKey {
 //   sum(cast(l_extendedprice as D128) * cast(l_discount as D128)), no GROUP BY
 struct ShapeSumMulFast {
     static constexpr const char* name = "sum(d64*d64) no-group";
-    static constexpr int N_NODES = 5, N_AGGS = 1, N_KEYS = 0, GMAX = 1, THREADS = 512;
+    static constexpr int N_NODES = 5, N_AGGS = 1, N_KEYS = 0, GMAX = 1, THREADS = 1024;
     static constexpr SNode node(int i) {
         constexpr SNode t[N_NODES] = {{DOP_LOAD, 8, -1, -1, 0, 0, 0},
                                       {DOP_LOAD, 8, -1, -1, 0, 0, 0},
@@ -61,7 +61,7 @@ struct ShapeSumMulFast {
 //   sum(qty), sum(ext), sum(ext*(1-disc)), sum(ext*(1-disc)*(1+tax)), avg(qty), avg(ext), avg(disc), count(*)
 struct ShapeQ1Dict {
     static constexpr const char* name = "q1 (2 int keys, 8 decimal aggregates)";
-    static constexpr int N_NODES = 14, N_AGGS = 8, N_KEYS = 2, GMAX = 4, THREADS = 384;
+    static constexpr int N_NODES = 14, N_AGGS = 8, N_KEYS = 2, GMAX = 4, THREADS = 512;
     static constexpr SNode node(int i) {
         constexpr SNode t[N_NODES] = {
                 {DOP_LOAD, 8, -1, -1, 0, 0, 0},    // 0 l_quantity
@@ -150,13 +150,27 @@ SRB_D void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" :
 SRB_D void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
 // ---- static row pipeline ---------------------------------------------------------------------------------------------------
-constexpr int ST_TILE = 1024;  // rows per tile
-constexpr int ST_STAGES = 4;
+constexpr int ST_TILE = 256;       // rows per tile (one consumer group of 128 threads takes 2 rows per thread)
+constexpr int ST_MAX_STAGES = 4;   // ring depth (the host picks the deepest ring that fits beside the accumulators)
+constexpr int ST_SMEM_BUDGET = 220 * 1024;
 
+// predicate lowered for the tile layout: column offset inside a stage, width, and a 3-bit truth table over
+// {v > lit, v == lit, v < lit} (bit 0, 1, 2) so that one compare pair serves all six operators without branching
+struct SPred {
+    int32_t col_off;
+    int32_t width;
+    uint32_t opmask;
+    int32_t group;
+    uint64_t lit_lo;
+    int64_t lit_hi;
+};
 struct StaticArgs { // host-computed tile layout: column c sits at col_off[c] inside a stage of stage_bytes
     int32_t col_off[MAX_COLS];
     int32_t stage_bytes;
-    int32_t _pad;
+    int32_t n_stages;
+    int32_t n_preds;
+    int32_t acc_off; // byte offset of the per-thread accumulators inside dynamic shared memory
+    SPred preds[MAX_PREDS];
 };
 struct SmemCols {
     const uint8_t* stage; // current stage
@@ -191,34 +205,51 @@ SRB_D Val lds_val(const uint8_t* col, int r) {
     }
     return v;
 }
-SRB_D Val lds_val_rt(const uint8_t* col, int width, int r) {
-    switch (width) {
-    case 1: return lds_val<1>(col, r);
-    case 2: return lds_val<2>(col, r);
-    case 4: return lds_val<4>(col, r);
-    case 8: return lds_val<8>(col, r);
-    default: return lds_val<16>(col, r);
-    }
-}
 
-// predicates over the shared-memory tile (runtime list; same semantics as eval_preds)
-SRB_D bool eval_preds_smem(const DProg& p, const SmemCols& sc, int r) {
-    bool pass = true;
-    int i = 0;
-    const int n = p.n_preds;
-    while (i < n) {
-        const int g = p.preds[i].group;
-        bool any = false;
-        do {
-            const DPred& pr = p.preds[i];
-            Val v = lds_val_rt(sc.base(pr.col), p.cols[pr.col].width, r);
-            bool res = pr.op == 9 ? false : (pr.op == 10 ? true : cmp_i128(pr.op, make_i128(v.lo, v.hi), make_i128(pr.lit_lo, pr.lit_hi)));
-            any = any || res;
-            i++;
-        } while (g != 0 && i < n && p.preds[i].group == g);
-        pass = pass && any;
+// one predicate on one row of the tile (NULL-free columns): NULL never satisfies a compare, IS_NULL is constant false
+SRB_D bool spred_eval(const SPred& pr, const uint8_t* stage, int r) {
+    const uint8_t* col = stage + pr.col_off;
+    int idx;
+    if (pr.width == 16) {
+        ulonglong2 x = ((const ulonglong2*)col)[r];
+        i128 v = make_i128(x.x, (int64_t)x.y), lit = make_i128(pr.lit_lo, pr.lit_hi);
+        idx = v < lit ? 2 : (v == lit ? 1 : 0);
+    } else {
+        int64_t v;
+        if (pr.width == 8)
+            v = ((const int64_t*)col)[r];
+        else if (pr.width == 4)
+            v = ((const int32_t*)col)[r];
+        else if (pr.width == 2)
+            v = ((const int16_t*)col)[r];
+        else
+            v = ((const int8_t*)col)[r];
+        const int64_t lit = (int64_t)pr.lit_lo;
+        idx = v < lit ? 2 : (v == lit ? 1 : 0);
     }
-    return pass;
+    return (pr.opmask >> idx) & 1u;
+}
+// AND of conjuncts and OR-groups over R rows at once (predicate loop outside, rows inside: uniform control flow is amortised)
+template <int R>
+SRB_D void eval_preds_rows(const StaticArgs& sa, const uint8_t* stage, const int (&rows)[R], bool (&pass)[R]) {
+#pragma unroll
+    for (int j = 0; j < R; j++) pass[j] = true;
+    int i = 0;
+    const int n = sa.n_preds;
+    while (i < n) {
+        const int g = sa.preds[i].group;
+        bool any[R];
+#pragma unroll
+        for (int j = 0; j < R; j++) any[j] = false;
+        do {
+            const SPred& pr = sa.preds[i];
+#pragma unroll
+            for (int j = 0; j < R; j++) any[j] = any[j] || spred_eval(pr, stage, rows[j]);
+            i++;
+        } while (g != 0 && i < n && sa.preds[i].group == g);
+#pragma unroll
+        for (int j = 0; j < R; j++) pass[j] = pass[j] && any[j];
+    }
 }
 
 template <class S, int I>
@@ -285,7 +316,21 @@ constexpr int agg_rep(int a) {
     }
     return a;
 }
-// can the argument of aggregate a be NULL? (static shapes bind NOT NULL columns, so only checked ops produce NULLs)
+// dense index of a representative among the representatives (its accumulator plane), and their number
+template <class S>
+constexpr int rep_index(int a) {
+    int n = 0;
+    for (int b = 0; b < a; b++) {
+        const SAgg h = S::agg(b);
+        if ((h.fn == FN_SUM || h.fn == FN_AVG) && agg_rep<S>(b) == b) n++;
+    }
+    return n;
+}
+template <class S>
+constexpr int n_reps() {
+    return rep_index<S>(S::N_AGGS);
+}
+// can the value of node n be NULL? (static shapes bind NOT NULL columns, so only checked ops produce NULLs)
 template <class S>
 constexpr bool node_can_be_null(int n) {
     if (n < 0) return false;
@@ -294,48 +339,74 @@ constexpr bool node_can_be_null(int n) {
     return node_can_be_null<S>(nd.lhs) || node_can_be_null<S>(nd.rhs);
 }
 
-// register accumulator bank of one group
+// Per-thread accumulators of the low-cardinality path. The LOW 64 bits of every partial sum live in shared memory, one
+// private word per (representative, group, thread): lanes of a warp hit distinct banks whatever their groups are, so the
+// update is a plain LDS / add / STS with the group as a runtime address — no atomics and no per-group predication. The
+// HIGH part (carries + sign words, almost always zero per row) stays in registers and is only touched when a warp vote
+// finds a non-zero delta.
 template <class S>
-struct Bank {
-    uint64_t lo[S::N_AGGS], hi[S::N_AGGS]; // only representatives are touched; the rest is dead and removed
-    uint32_t n[S::N_AGGS];
-    uint32_t rows;
+struct HiRegs {
+    static constexpr int G = S::GMAX > 0 ? S::GMAX : 1;
+    static constexpr int NR = n_reps<S>() > 0 ? n_reps<S>() : 1;
+    uint32_t w2[G][NR], w3[G][NR]; // bits 64..95 and 96..127 of each partial sum (w3 only for 16-byte arguments)
+    uint32_t n[G][NR];             // non-NULL rows (only for arguments that can be NULL)
+    uint32_t rows[G];
 };
 
-template <class S, int A>
-SRB_D void bank_update(Bank<S>& b, const Val* v, bool on) {
+template <class S, int A, int THREADS>
+SRB_D void acc_update(HiRegs<S>& h, uint8_t* acc_tid, const Val* v, bool on, int gid) {
     constexpr SAgg g = S::agg(A);
+    constexpr int G = HiRegs<S>::G;
     if constexpr (g.fn == FN_COUNT) {
-        if constexpr (g.arg >= 0 && node_can_be_null<S>(g.arg)) {
-            if (on && !v[g.arg].null) b.n[A]++;
-        }
+        // count(*) and count of a NOT NULL argument are the group's row count
     } else if constexpr (agg_rep<S>(A) == A) {
+        constexpr int RI = rep_index<S>(A);
+        constexpr bool wide = S::node(g.arg).width == 16;
+        constexpr bool nullable = node_can_be_null<S>(g.arg);
         const Val& x = v[g.arg];
         bool take = on;
-        if constexpr (node_can_be_null<S>(g.arg)) take = take && !x.null;
-        const uint64_t alo = take ? x.lo : 0ULL, ahi = take ? (uint64_t)x.hi : 0ULL;
-        const uint64_t nlo = b.lo[A] + alo;
-        b.hi[A] += ahi + (nlo < alo ? 1ULL : 0ULL);
-        b.lo[A] = nlo;
-        if constexpr (node_can_be_null<S>(g.arg)) b.n[A] += take ? 1u : 0u;
+        if constexpr (nullable) take = take && !x.null;
+        uint32_t d2 = 0, d3 = 0;
+        if (take) {
+            uint64_t* slot = (uint64_t*)(acc_tid + (size_t)(RI * G + gid) * THREADS * 8);
+            const uint64_t old = *slot, nw = old + x.lo;
+            *slot = nw;
+            const uint64_t dh = (uint64_t)x.hi + (nw < old ? 1ULL : 0ULL);
+            d2 = (uint32_t)dh;
+            d3 = (uint32_t)(dh >> 32);
+        }
+        const bool any_hi = wide ? ((d2 | d3) != 0) : (d2 != 0);
+        if (__any_sync(0xffffffffu, any_hi)) {
+#pragma unroll
+            for (int q = 0; q < G; q++) {
+                const bool mine = gid == q;
+                if constexpr (wide) {
+                    const uint32_t a2 = mine ? d2 : 0u, a3 = mine ? d3 : 0u;
+                    const uint32_t s2 = h.w2[q][RI] + a2;
+                    h.w3[q][RI] += a3 + (s2 < a2 ? 1u : 0u);
+                    h.w2[q][RI] = s2;
+                } else {
+                    h.w2[q][RI] += mine ? d2 : 0u;
+                }
+            }
+        }
+        if constexpr (nullable) {
+#pragma unroll
+            for (int q = 0; q < G; q++) h.n[q][RI] += (take && gid == q) ? 1u : 0u;
+        }
     }
 }
-template <class S, int... A>
-SRB_D void bank_update_all(Bank<S>& b, const Val* v, bool on, std::integer_sequence<int, A...>) {
-    (bank_update<S, A>(b, v, on), ...);
-    b.rows += on ? 1u : 0u;
-}
-template <class S, int... A>
-SRB_D void bank_clear(Bank<S>& b, std::integer_sequence<int, A...>) {
-    ((b.lo[A] = 0, b.hi[A] = 0, b.n[A] = 0), ...);
-    b.rows = 0;
+template <class S, int THREADS, int... A>
+SRB_D void acc_update_all(HiRegs<S>& h, uint8_t* acc_tid, const Val* v, bool on, int gid, std::integer_sequence<int, A...>) {
+    (acc_update<S, A, THREADS>(h, acc_tid, v, on, gid), ...);
+#pragma unroll
+    for (int q = 0; q < HiRegs<S>::G; q++) h.rows[q] += (on && gid == q) ? 1u : 0u;
 }
 
 SRB_D uint64_t warp_sum_u64(uint64_t x) {
     for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
     return x;
 }
-// 128-bit warp reduction: the low words are summed as three 32-bit-safe pieces so that carries are exact
 SRB_D void warp_sum_u128(uint64_t& lo, uint64_t& hi) {
     for (int o = 16; o > 0; o >>= 1) {
         uint64_t olo = __shfl_down_sync(0xffffffffu, lo, o), ohi = __shfl_down_sync(0xffffffffu, hi, o);
@@ -345,39 +416,65 @@ SRB_D void warp_sum_u128(uint64_t& lo, uint64_t& hi) {
     }
 }
 
-// flush one bank into table slot `slot` (lane 0 of each warp issues the atomics)
-template <class S, int A>
-SRB_D void bank_flush_one(const DProg& p, Bank<S>& b, uint8_t* slot, uint64_t rows_total) {
-    constexpr SAgg g = S::agg(A);
-    const DAgg& rt = p.aggs[A];
-    const int lane = threadIdx.x & 31;
-    if constexpr (g.fn == FN_COUNT) {
-        uint64_t n = rows_total;
-        if constexpr (g.arg >= 0 && node_can_be_null<S>(g.arg)) n = warp_sum_u64(b.n[A]);
-        if (lane == 0 && n) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)n);
-    } else {
-        constexpr int R = agg_rep<S>(A);
-        // the representative's registers are reduced once per representative and re-used by its followers
-        uint64_t lo = b.lo[R], hi = b.hi[R];
-        if constexpr (R == A) {
+// fold group q of this thread's accumulators into table slot `slot`: warp reduction, then lane 0 issues the atomics
+template <class S, int THREADS>
+struct Flusher {
+    static constexpr int G = HiRegs<S>::G;
+    static constexpr int NR = HiRegs<S>::NR;
+    uint64_t red_lo[NR], red_hi[NR], red_n[NR];
+
+    template <int A>
+    __device__ __forceinline__ void reduce_rep(const HiRegs<S>& h, const uint8_t* acc_tid, int q) {
+        constexpr SAgg g = S::agg(A);
+        if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
+            constexpr int RI = rep_index<S>(A);
+            constexpr bool wide = S::node(g.arg).width == 16;
+            uint64_t lo = *(const uint64_t*)(acc_tid + (size_t)(RI * G + q) * THREADS * 8);
+            // static q is needed for the register arrays: select by unrolled compare
+            uint32_t w2 = 0, w3 = 0, n = 0;
+#pragma unroll
+            for (int k = 0; k < G; k++)
+                if (k == q) {
+                    w2 = h.w2[k][RI];
+                    w3 = h.w3[k][RI];
+                    n = h.n[k][RI];
+                }
+            uint64_t hi = wide ? (((uint64_t)w3 << 32) | w2) : (uint64_t)(int64_t)(int32_t)w2;
             warp_sum_u128(lo, hi);
-            b.lo[R] = lo; // lane 0 now holds the warp total
-            b.hi[R] = hi;
-            if constexpr (node_can_be_null<S>(g.arg)) b.n[R] = (uint32_t)warp_sum_u64(b.n[R]);
-        }
-        uint64_t n = rows_total;
-        if constexpr (node_can_be_null<S>(g.arg)) n = b.n[R];
-        if (lane == 0 && n) {
-            atomic_add128(slot, rt.off_lo, rt.off_hi, lo, hi);
-            if (rt.off_n >= 0) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)n);
+            red_lo[RI] = lo;
+            red_hi[RI] = hi;
+            if constexpr (node_can_be_null<S>(g.arg)) red_n[RI] = warp_sum_u64(n);
         }
     }
-}
-template <class S, int... A>
-SRB_D void bank_flush(const DProg& p, Bank<S>& b, uint8_t* slot, std::integer_sequence<int, A...>) {
-    const uint64_t rows_total = warp_sum_u64(b.rows);
-    (bank_flush_one<S, A>(p, b, slot, rows_total), ...);
-}
+    template <int A>
+    __device__ __forceinline__ void emit(const DProg& p, uint8_t* slot, uint64_t rows_total) {
+        constexpr SAgg g = S::agg(A);
+        const DAgg& rt = p.aggs[A];
+        const int lane = threadIdx.x & 31;
+        if constexpr (g.fn == FN_COUNT) {
+            if (lane == 0 && rows_total) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)rows_total);
+        } else {
+            constexpr int RI = rep_index<S>(agg_rep<S>(A));
+            uint64_t n = rows_total;
+            if constexpr (node_can_be_null<S>(g.arg)) n = red_n[RI];
+            if (lane == 0 && n) {
+                atomic_add128(slot, rt.off_lo, rt.off_hi, red_lo[RI], red_hi[RI]);
+                if (rt.off_n >= 0) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)n);
+            }
+        }
+    }
+    template <int... A>
+    __device__ __forceinline__ void run(const DProg& p, const HiRegs<S>& h, const uint8_t* acc_tid, int q, uint8_t* slot,
+                                        std::integer_sequence<int, A...>) {
+        uint32_t rows = 0;
+#pragma unroll
+        for (int k = 0; k < G; k++)
+            if (k == q) rows = h.rows[k];
+        const uint64_t rows_total = warp_sum_u64(rows);
+        (reduce_rep<A>(h, acc_tid, q), ...);
+        (emit<A>(p, slot, rows_total), ...);
+    }
+};
 
 // per-row update of a table slot with compile-time operand indexes (static shapes carry SUM / AVG / COUNT over integers)
 template <class S, int A>
@@ -429,78 +526,110 @@ SRB_D PackedKey pack_key_static(const Val* v) {
 struct StaticCtr {
     unsigned long long* rows_selected;
     unsigned long long* deferred;
+    unsigned long long* inserted;
 };
 
+constexpr int ST_GROUP = 128;                  // threads per consumer group
+constexpr int ST_MAX_GROUPS = 8;
+SRB_D void group_barrier(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(ST_GROUP) : "memory"); }
+
+// The CTA is split into consumer groups of 128 threads. Every group streams its OWN tiles through its OWN ring of stages and
+// synchronises only with itself (named barrier), so the groups drift apart and one group's barrier / latency bubbles are
+// filled by the others — the block never stalls as a whole, and there is no block-wide barrier in the steady state.
 template <class S>
 __global__ void __launch_bounds__(S::THREADS, 1)
         k_scan_agg_static(const __grid_constant__ DProg prog, const __grid_constant__ StaticArgs sa, const TableView tv, const int64_t base,
                           const int64_t n_tiles, uint32_t* __restrict__ defer_out, StaticCtr ctr) {
+    constexpr int THREADS = S::THREADS;
+    constexpr int NG = THREADS / ST_GROUP;
+    constexpr int R = ST_TILE / ST_GROUP; // rows per thread per tile, strided by the group size (conflict-free LDS)
+    constexpr int G = HiRegs<S>::G;
+    static_assert(THREADS % ST_GROUP == 0 && NG <= ST_MAX_GROUPS && ST_TILE % ST_GROUP == 0, "block / tile geometry");
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ uint64_t full_bar[ST_STAGES];
-    __shared__ uint64_t dir_lo[S::GMAX > 0 ? S::GMAX : 1], dir_hi[S::GMAX > 0 ? S::GMAX : 1];
-    __shared__ uint8_t* dir_slot[S::GMAX > 0 ? S::GMAX : 1];
+    __shared__ uint64_t full_bar[ST_MAX_GROUPS][ST_MAX_STAGES];
+    __shared__ uint64_t dir_lo[G], dir_hi[G];
+    __shared__ uint8_t* dir_slot[G];
     __shared__ int dir_cnt, dir_lock;
     const DProg& p = prog;
     using NodeSeq = std::make_integer_sequence<int, S::N_NODES>;
     using AggSeq = std::make_integer_sequence<int, S::N_AGGS>;
 
-    // column c occupies [col_off[c], col_off[c] + TILE*width) inside a stage (TILE*width keeps 16-byte alignment)
-    const int stage_bytes = sa.stage_bytes;
-    const int tid = threadIdx.x;
+    const int stage_bytes = sa.stage_bytes, n_stages = sa.n_stages;
+    const int tid = threadIdx.x, grp = tid / ST_GROUP, gtid = tid % ST_GROUP;
     if (tid == 0) {
-        for (int s = 0; s < ST_STAGES; s++) mbar_init(&full_bar[s], 1);
+        for (int g = 0; g < NG; g++)
+            for (int s = 0; s < n_stages; s++) mbar_init(&full_bar[g][s], 1);
         dir_cnt = 0;
         dir_lock = 0;
         fence_barrier_init();
     }
+    // this thread's private accumulator words start zeroed
+    uint8_t* acc_tid = smem + sa.acc_off + tid * 8;
+    if constexpr (S::GMAX > 0) {
+#pragma unroll
+        for (int k = 0; k < HiRegs<S>::NR * G; k++) *(uint64_t*)(acc_tid + (size_t)k * THREADS * 8) = 0;
+    }
     __syncthreads();
 
-    auto issue = [&](int64_t tile, int s) { // one elected thread: one bulk copy per column, all completing on full_bar[s]
-        mbar_expect_tx(&full_bar[s], (uint32_t)stage_bytes);
-        uint8_t* dst = smem + (size_t)s * stage_bytes;
+    uint8_t* ring = smem + (size_t)grp * n_stages * stage_bytes; // this group's stages
+    auto issue = [&](int64_t tile, int s) { // the group's elected thread: one bulk copy per column, all completing on full_bar[grp][s]
+        mbar_expect_tx(&full_bar[grp][s], (uint32_t)stage_bytes);
+        uint8_t* dst = ring + (size_t)s * stage_bytes;
         for (int c = 0; c < p.n_cols; c++) {
             const int w = p.cols[c].width;
             tma_load_1d(dst + sa.col_off[c], (const uint8_t*)p.cols[c].data + (size_t)(base + tile * ST_TILE) * w, (uint32_t)(ST_TILE * w),
-                        &full_bar[s]);
+                        &full_bar[grp][s]);
         }
     };
-    const int64_t first = blockIdx.x, step = gridDim.x;
-    if (tid == 0)
-        for (int s = 0; s < ST_STAGES; s++)
+    const int64_t first = (int64_t)blockIdx.x * NG + grp, step = (int64_t)gridDim.x * NG;
+    if (gtid == 0)
+        for (int s = 0; s < n_stages; s++)
             if (first + s * step < n_tiles) issue(first + s * step, s);
 
-    Bank<S> bank[S::GMAX > 0 ? S::GMAX : 1];
+    HiRegs<S> h;
 #pragma unroll
-    for (int g = 0; g < (S::GMAX > 0 ? S::GMAX : 1); g++) bank_clear<S>(bank[g], AggSeq{});
-    unsigned long long selected = 0, deferred = 0;
+    for (int q = 0; q < G; q++) {
+        h.rows[q] = 0;
+#pragma unroll
+        for (int k = 0; k < HiRegs<S>::NR; k++) h.w2[q][k] = h.w3[q][k] = h.n[q][k] = 0;
+    }
+    unsigned long long selected = 0, deferred = 0, inserted = 0;
 
-    int it = 0;
-    for (int64_t tile = first; tile < n_tiles; tile += step, it++) {
-        const int s = it % ST_STAGES;
-        mbar_wait(&full_bar[s], (uint32_t)((it / ST_STAGES) & 1));
-        const SmemCols sc{smem + (size_t)s * stage_bytes, sa.col_off};
-        for (int r = tid; r < ST_TILE; r += S::THREADS) {
-            const bool pass = eval_preds_smem(p, sc, r);
-            selected += pass ? 1 : 0;
-            if (!__any_sync(__activemask(), pass)) continue;
+    int s = 0;
+    uint32_t parity = 0;
+    for (int64_t tile = first; tile < n_tiles; tile += step) {
+        mbar_wait(&full_bar[grp][s], parity);
+        const uint8_t* stage = ring + (size_t)s * stage_bytes;
+        const SmemCols sc{stage, sa.col_off};
+        int rows[R];
+        bool pass[R];
+#pragma unroll
+        for (int j = 0; j < R; j++) rows[j] = gtid + j * ST_GROUP;
+        eval_preds_rows<R>(sa, stage, rows, pass);
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            selected += pass[j] ? 1 : 0;
+            if (!__any_sync(0xffffffffu, pass[j])) continue;
+            const int r = rows[j];
             Val v[S::N_NODES];
             eval_static_all<S>(p, v, sc, r, NodeSeq{});
             if constexpr (S::N_KEYS == 0) {
-                bank_update_all<S>(bank[0], v, pass, AggSeq{});
+                acc_update_all<S, THREADS>(h, acc_tid, v, pass[j], 0, AggSeq{});
             } else {
                 const PackedKey k = pack_key_static<S>(v);
                 int gid = -1;
                 if constexpr (S::GMAX > 0) {
                     const int cnt = *(volatile int*)&dir_cnt;
 #pragma unroll
-                    for (int g = 0; g < S::GMAX; g++)
-                        if (g < cnt && ((volatile uint64_t*)dir_lo)[g] == k.lo && (p.key_words == 1 || ((volatile uint64_t*)dir_hi)[g] == k.hi)) gid = g;
-#pragma unroll
-                    for (int g = 0; g < S::GMAX; g++) bank_update_all<S>(bank[g], v, pass && gid == g, AggSeq{});
+                    for (int q = 0; q < G; q++)
+                        if (q < cnt && ((volatile uint64_t*)dir_lo)[q] == k.lo && (p.key_words == 1 || ((volatile uint64_t*)dir_hi)[q] == k.hi)) gid = q;
+                    acc_update_all<S, THREADS>(h, acc_tid, v, pass[j] && gid >= 0, gid < 0 ? 0 : gid, AggSeq{});
                 }
-                if (pass && gid < 0) {
+                if (pass[j] && gid < 0) {
                     // global-table path: the group is not (yet) in this CTA's directory
-                    uint8_t* slot = table_find_or_insert(tv, p, k.lo, k.hi, hash_packed_key_static<static_key_bytes<S>()>(k, p.phase_seed));
+                    bool fresh;
+                    uint8_t* slot = table_find_or_insert(tv, k.lo, k.hi, hash_packed_key_static<static_key_bytes<S>()>(k, p.phase_seed), &fresh);
+                    inserted += fresh ? 1 : 0;
                     if (!slot) {
                         const int64_t i = tile * ST_TILE + r;
                         atomicOr(&defer_out[i >> 5], 1u << (i & 31));
@@ -509,12 +638,12 @@ __global__ void __launch_bounds__(S::THREADS, 1)
                         row_update_global<S>(p, slot, v, AggSeq{});
                         if constexpr (S::GMAX > 0) {
                             // best-effort publication into the directory (try-lock; duplicates are excluded under the lock)
-                            if (*(volatile int*)&dir_cnt < S::GMAX && atomicCAS(&dir_lock, 0, 1) == 0) {
+                            if (*(volatile int*)&dir_cnt < G && atomicCAS(&dir_lock, 0, 1) == 0) {
                                 const int c = *(volatile int*)&dir_cnt;
                                 bool present = false;
-                                for (int g = 0; g < c; g++)
-                                    present = present || (((volatile uint64_t*)dir_lo)[g] == k.lo && ((volatile uint64_t*)dir_hi)[g] == k.hi);
-                                if (!present && c < S::GMAX) {
+                                for (int q = 0; q < c; q++)
+                                    present = present || (((volatile uint64_t*)dir_lo)[q] == k.lo && ((volatile uint64_t*)dir_hi)[q] == k.hi);
+                                if (!present && c < G) {
                                     ((volatile uint64_t*)dir_lo)[c] = k.lo;
                                     ((volatile uint64_t*)dir_hi)[c] = k.hi;
                                     ((uint8_t* volatile*)dir_slot)[c] = slot;
@@ -529,27 +658,34 @@ __global__ void __launch_bounds__(S::THREADS, 1)
                 }
             }
         }
-        __syncthreads(); // every thread is done with stage s
-        if (tid == 0 && tile + (int64_t)ST_STAGES * step < n_tiles) {
+        group_barrier(1 + grp); // every thread of the group is done with stage s
+        if (gtid == 0 && tile + (int64_t)n_stages * step < n_tiles) {
             fence_proxy_async();
-            issue(tile + (int64_t)ST_STAGES * step, s);
+            issue(tile + (int64_t)n_stages * step, s);
+        }
+        if (++s == n_stages) {
+            s = 0;
+            parity ^= 1u;
         }
     }
-    __syncthreads();
-    // retire: warp-reduce every bank and fold it into the table
-    if constexpr (S::N_KEYS == 0) {
-        bank_flush<S>(p, bank[0], tv.slots, AggSeq{});
-    } else if constexpr (S::GMAX > 0) {
-        const int cnt = dir_cnt;
-#pragma unroll
-        for (int g = 0; g < S::GMAX; g++)
-            if (g < cnt) bank_flush<S>(p, bank[g], dir_slot[g], AggSeq{});
+    __syncthreads(); // the directory is final
+    // retire: warp-reduce every group's accumulators and fold them into the table
+    if constexpr (S::GMAX > 0) {
+        Flusher<S, THREADS> f;
+        if constexpr (S::N_KEYS == 0) {
+            f.run(p, h, acc_tid, 0, tv.slots, AggSeq{});
+        } else {
+            const int cnt = dir_cnt;
+            for (int q = 0; q < cnt; q++) f.run(p, h, acc_tid, q, dir_slot[q], AggSeq{});
+        }
     }
     selected = warp_sum_u64(selected);
     deferred = warp_sum_u64(deferred);
+    inserted = warp_sum_u64(inserted);
     if ((tid & 31) == 0) {
         if (selected) atomicAdd(ctr.rows_selected, selected);
         if (deferred) atomicAdd(ctr.deferred, deferred);
+        if (inserted) atomicAdd(ctr.inserted, inserted);
     }
 }
 
@@ -569,9 +705,22 @@ inline const char* static_shape_name(int id) {
     return "generic";
 }
 
+inline uint32_t pred_opmask(int op) {
+    switch (op) {
+    case 1: return 0b010; // EQ
+    case 2: return 0b101; // NE
+    case 3: return 0b001; // GT
+    case 4: return 0b011; // GE
+    case 5: return 0b100; // LT
+    case 6: return 0b110; // LE
+    case 10: return 0b111; // NOT NULL on a NULL-free column
+    default: return 0;     // IS NULL
+    }
+}
+
 template <class S>
 inline int64_t launch_shape(const DProg& p, const TableView& tv, int64_t base, int64_t n, uint32_t* defer_out, unsigned long long* rows_selected,
-                            unsigned long long* deferred, int n_sms, cudaStream_t stream) {
+                            unsigned long long* deferred, unsigned long long* inserted, int n_sms, cudaStream_t stream) {
     int row_bytes = 0;
     StaticArgs sa{};
     for (int c = 0; c < p.n_cols; c++) {
@@ -583,15 +732,27 @@ inline int64_t launch_shape(const DProg& p, const TableView& tv, int64_t base, i
     const int64_t n_tiles = n / ST_TILE;
     if (n_tiles == 0 || row_bytes == 0) return 0;
     sa.stage_bytes = ST_TILE * row_bytes;
-    const size_t smem = (size_t)ST_STAGES * ST_TILE * row_bytes;
-    if (smem > 200 * 1024) return 0;
+    const int acc_bytes = S::GMAX > 0 ? HiRegs<S>::NR * HiRegs<S>::G * S::THREADS * 8 : 0;
+    constexpr int NG = S::THREADS / ST_GROUP;
+    int stages = (ST_SMEM_BUDGET - acc_bytes) / (sa.stage_bytes * NG);
+    if (stages > ST_MAX_STAGES) stages = ST_MAX_STAGES;
+    if (stages < 2) return 0;
+    sa.n_stages = stages;
+    sa.acc_off = NG * stages * sa.stage_bytes;
+    sa.n_preds = p.n_preds;
+    for (int i = 0; i < p.n_preds; i++) {
+        const DPred& d = p.preds[i];
+        sa.preds[i] = SPred{sa.col_off[d.col], p.cols[d.col].width, pred_opmask(d.op), d.group, d.lit_lo, d.lit_hi};
+    }
+    const size_t smem = (size_t)sa.acc_off + acc_bytes;
     static bool configured = false;
     if (!configured) {
-        cudaFuncSetAttribute(k_scan_agg_static<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(k_scan_agg_static<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM_BUDGET);
         configured = true;
     }
-    const int grid = (int)(n_tiles < n_sms ? n_tiles : n_sms);
-    StaticCtr ctr{rows_selected, deferred};
+    const int64_t want = (n_tiles + NG - 1) / NG;
+    const int grid = (int)(want < n_sms ? want : n_sms);
+    StaticCtr ctr{rows_selected, deferred, inserted};
     k_scan_agg_static<S><<<grid, S::THREADS, smem, stream>>>(p, sa, tv, base, n_tiles, defer_out, ctr);
     return n_tiles * ST_TILE;
 }
@@ -600,11 +761,12 @@ inline int64_t launch_shape(const DProg& p, const TableView& tv, int64_t base, i
 // covered (0 when the preconditions — no null maps, 16-byte aligned columns, at least one tile — do not hold). The caller
 // runs the generic kernel over the remaining rows.
 inline int64_t launch_static_shape(int shape, const DProg& p, const TableView& tv, int64_t base, int64_t n, uint32_t* defer_out,
-                                   unsigned long long* rows_selected, unsigned long long* deferred, int n_sms, cudaStream_t stream) {
+                                   unsigned long long* rows_selected, unsigned long long* deferred, unsigned long long* inserted, int n_sms,
+                                   cudaStream_t stream) {
     switch (shape) {
-    case 0: return launch_shape<ShapeSumMulFast>(p, tv, base, n, defer_out, rows_selected, deferred, n_sms, stream);
-    case 1: return launch_shape<ShapeQ1Dict>(p, tv, base, n, defer_out, rows_selected, deferred, n_sms, stream);
-    case 2: return launch_shape<ShapeHighCard>(p, tv, base, n, defer_out, rows_selected, deferred, n_sms, stream);
+    case 0: return launch_shape<ShapeSumMulFast>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
+    case 1: return launch_shape<ShapeQ1Dict>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
+    case 2: return launch_shape<ShapeHighCard>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
     }
     return 0;
 }
