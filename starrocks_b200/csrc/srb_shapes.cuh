@@ -43,7 +43,7 @@ struct SKey {
 //   sum(cast(l_extendedprice as D128) * cast(l_discount as D128)), no GROUP BY
 struct ShapeSumMulFast {
     static constexpr const char* name = "sum(d64*d64) no-group";
-    static constexpr int N_NODES = 5, N_AGGS = 1, N_KEYS = 0, GMAX = 1, THREADS = 1024;
+    static constexpr int N_NODES = 5, N_AGGS = 1, N_KEYS = 0, GMAX = 1, THREADS = 512, ROWS = 4;
     static constexpr SNode node(int i) {
         constexpr SNode t[N_NODES] = {{DOP_LOAD, 8, -1, -1, 0, 0, 0},
                                       {DOP_LOAD, 8, -1, -1, 0, 0, 0},
@@ -61,7 +61,7 @@ struct ShapeSumMulFast {
 //   sum(qty), sum(ext), sum(ext*(1-disc)), sum(ext*(1-disc)*(1+tax)), avg(qty), avg(ext), avg(disc), count(*)
 struct ShapeQ1Dict {
     static constexpr const char* name = "q1 (2 int keys, 8 decimal aggregates)";
-    static constexpr int N_NODES = 14, N_AGGS = 8, N_KEYS = 2, GMAX = 4, THREADS = 512;
+    static constexpr int N_NODES = 14, N_AGGS = 8, N_KEYS = 2, GMAX = 4, THREADS = 512, ROWS = 2;
     static constexpr SNode node(int i) {
         constexpr SNode t[N_NODES] = {
                 {DOP_LOAD, 8, -1, -1, 0, 0, 0},    // 0 l_quantity
@@ -91,7 +91,7 @@ struct ShapeQ1Dict {
 // High-cardinality GROUP BY: select k, sum(v), count(*) group by k   (k, v BIGINT)
 struct ShapeHighCard {
     static constexpr const char* name = "group by bigint: sum(bigint), count(*)";
-    static constexpr int N_NODES = 2, N_AGGS = 2, N_KEYS = 1, GMAX = 0, THREADS = 1024;
+    static constexpr int N_NODES = 2, N_AGGS = 2, N_KEYS = 1, GMAX = 0, THREADS = 992, ROWS = 2; // + the producer warp = 1024
     static constexpr SNode node(int) { return SNode{DOP_LOAD, 8, -1, -1, 0, 0, 0}; }
     static constexpr SAgg agg(int i) { return i == 0 ? SAgg{FN_SUM, 1, 0, 0} : SAgg{FN_COUNT, -1, 0, 1}; }
     static constexpr SKey key(int) { return SKey{0, 8}; }
@@ -150,9 +150,35 @@ SRB_D void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" :
 SRB_D void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
 // ---- static row pipeline ---------------------------------------------------------------------------------------------------
-constexpr int ST_TILE = 256;       // rows per tile (one consumer group of 128 threads takes 2 rows per thread)
 constexpr int ST_MAX_STAGES = 4;   // ring depth (the host picks the deepest ring that fits beside the accumulators)
-constexpr int ST_SMEM_BUDGET = 220 * 1024;
+constexpr int ST_SMEM_BUDGET = 222 * 1024;
+constexpr int ST_MAX_RANGES = 6;   // conjunct predicates after lowering to per-column ranges (more: the generic predicate loop)
+
+// rows of one tile: every consumer thread takes S::ROWS rows, strided by the thread count (conflict-free LDS)
+template <class S>
+constexpr int tile_rows() {
+    return S::THREADS * S::ROWS;
+}
+// LOAD nodes own the leading columns of a stage, in node order: their offsets are compile-time constants, so a row's
+// operands are fetched with LDS [row_base + immediate]
+template <class S>
+constexpr int load_off(int node) {
+    int off = 0;
+    for (int j = 0; j < node; j++)
+        if (S::node(j).op == DOP_LOAD) off += S::node(j).width * tile_rows<S>();
+    return off;
+}
+
+// A conjunct (or several on one column) lowered to "lo <= v <= lo + span" (unsigned compare after the subtraction),
+// optionally negated: one subtract and one compare per row whatever the operator was.
+struct SRange {
+    int32_t col_off;
+    int32_t width; // 4 or 8
+    int32_t neg;
+    int32_t _pad;
+    int64_t lo;
+    uint64_t span;
+};
 
 // predicate lowered for the tile layout: column offset inside a stage, width, and a 3-bit truth table over
 // {v > lit, v == lit, v < lit} (bit 0, 1, 2) so that one compare pair serves all six operators without branching
@@ -170,13 +196,41 @@ struct StaticArgs { // host-computed tile layout: column c sits at col_off[c] in
     int32_t n_stages;
     int32_t n_preds;
     int32_t acc_off; // byte offset of the per-thread accumulators inside dynamic shared memory
+    int32_t n_ranges; // >= 0: the predicates are the conjunction of rng[0..n_ranges); -1: evaluate preds[] generically
+    int32_t _pad;
+    SRange rng[ST_MAX_RANGES];
     SPred preds[MAX_PREDS];
 };
-struct SmemCols {
-    const uint8_t* stage; // current stage
-    const int32_t* col_off;
-    __device__ __forceinline__ const uint8_t* base(int c) const { return stage + col_off[c]; }
-};
+
+// the conjunction of the lowered ranges over R rows (range loop outside, rows inside; every field of a range is a
+// fixed kernel-parameter address, so nothing is fetched through an index)
+template <int R, int STRIDE>
+SRB_D void eval_ranges_rows(const StaticArgs& sa, const uint8_t* stage, int r0, bool (&pass)[R]) {
+#pragma unroll
+    for (int j = 0; j < R; j++) pass[j] = true;
+#pragma unroll
+    for (int i = 0; i < ST_MAX_RANGES; i++) {
+        if (i < sa.n_ranges) {
+            const SRange& g = sa.rng[i];
+            const uint8_t* col = stage + g.col_off;
+            const bool neg = g.neg != 0;
+            if (g.width == 8) {
+#pragma unroll
+                for (int j = 0; j < R; j++) {
+                    const uint64_t d = (uint64_t)((const int64_t*)col)[r0 + j * STRIDE] - (uint64_t)g.lo;
+                    pass[j] = pass[j] && ((d <= g.span) != neg);
+                }
+            } else {
+                const uint32_t lo = (uint32_t)g.lo, span = (uint32_t)g.span;
+#pragma unroll
+                for (int j = 0; j < R; j++) {
+                    const uint32_t d = (uint32_t)((const int32_t*)col)[r0 + j * STRIDE] - lo;
+                    pass[j] = pass[j] && ((d <= span) != neg);
+                }
+            }
+        }
+    }
+}
 
 template <int W>
 SRB_D Val lds_val(const uint8_t* col, int r) {
@@ -252,12 +306,29 @@ SRB_D void eval_preds_rows(const StaticArgs& sa, const uint8_t* stage, const int
     }
 }
 
+// i64 x i64 -> i128. When every lane of the warp holds two operands in [0, 2^32) (money amounts times small factors: the
+// common case) one 32x32->64 multiply is the whole product; the vote keeps the warp converged on either side.
+SRB_D void mul_i64_i64_warp(int64_t a, int64_t b, uint64_t& lo, int64_t& hi) {
+    const bool small = (((uint64_t)a | (uint64_t)b) >> 32) == 0;
+    if (__all_sync(0xffffffffu, small)) {
+        lo = (uint64_t)(uint32_t)a * (uint64_t)(uint32_t)b;
+        hi = 0;
+    } else {
+        const i128 r = mul_i64_i64(a, b);
+        lo = lo64(r);
+        hi = hi64(r);
+    }
+}
+
+// one node of the shape on one row. Narrow (<= 8 byte) checked ADD / SUB stay in 64-bit arithmetic; 128-bit products try
+// the warp-uniform small-operand path first; everything else is the generic primitive of srb_dev.cuh, so results are
+// the same bits as the interpreter's. Must be called by all 32 lanes (votes inside).
 template <class S, int I>
-SRB_D void eval_static_node(const DProg& p, Val* v, const SmemCols& sc, int r) {
+SRB_D void eval_static_node(const DProg& p, Val* v, const uint8_t* stage, int r) {
     constexpr SNode nd = S::node(I);
     const DNode& rt = p.nodes[I];
     if constexpr (nd.op == DOP_LOAD) {
-        v[I] = lds_val<nd.width>(sc.base(rt.col), r);
+        v[I] = lds_val<nd.width>(stage + load_off<S>(I), r);
     } else if constexpr (nd.op == DOP_LIT) {
         v[I].lo = rt.lit_lo;
         v[I].hi = rt.lit_hi;
@@ -277,10 +348,18 @@ SRB_D void eval_static_node(const DProg& p, Val* v, const SmemCols& sc, int r) {
         v[I].null = a.null || ov;
     } else if constexpr (nd.op == DOP_MULFAST) {
         const Val a = v[nd.lhs], b = v[nd.rhs];
-        i128 res = mul_i64_i64((int64_t)a.lo, (int64_t)b.lo);
-        v[I].lo = lo64(res);
-        v[I].hi = hi64(res);
+        mul_i64_i64_warp((int64_t)a.lo, (int64_t)b.lo, v[I].lo, v[I].hi);
         v[I].null = a.null || b.null;
+    } else if constexpr (nd.checked != 0 && nd.width == 8 && nd.adj_l == 0 && nd.adj_r == 0 && (nd.op == DOP_ADD || nd.op == DOP_SUB)) {
+        const Val a = v[nd.lhs], b = v[nd.rhs];
+        const uint64_t x = a.lo, y = b.lo;
+        const uint64_t s = nd.op == DOP_ADD ? x + y : x - y;
+        // signed overflow: ADD when the operands agree in sign and the sum does not; SUB when they differ and the result left x's sign
+        const uint64_t o = nd.op == DOP_ADD ? ((x ^ s) & (y ^ s)) : ((x ^ y) & (x ^ s));
+        const bool ov = (int64_t)o < 0;
+        v[I].lo = s; // the value of a NULL is never read: consumers test .null first
+        v[I].hi = (int64_t)s >> 63;
+        v[I].null = a.null || b.null || ov;
     } else {
         const Val a = v[nd.lhs], b = v[nd.rhs];
         i128 x = make_i128(a.lo, a.hi), y = make_i128(b.lo, b.hi), res = 0;
@@ -288,8 +367,19 @@ SRB_D void eval_static_node(const DProg& p, Val* v, const SmemCols& sc, int r) {
         if constexpr (nd.checked != 0) {
             if constexpr (nd.adj_l != 0) ov |= checked_binop<nd.width>(6, x, make_i128(rt.fl_lo, rt.fl_hi), &x);
             if constexpr (nd.adj_r != 0) ov |= checked_binop<nd.width>(6, y, make_i128(rt.fr_lo, rt.fr_hi), &y);
-            if (!ov) ov = checked_binop<nd.width>(nd.op, x, y, &res);
-            if (ov) res = 0;
+            bool done = false;
+            if constexpr (nd.op == DOP_MUL && nd.width == 16) {
+                // both operands in [0, 2^32): the product is exact in 64 bits and no multi3 flag can be set
+                const bool small = !ov && (((lo64(x) | lo64(y)) >> 32) == 0) && ((hi64(x) | hi64(y)) == 0);
+                if (__all_sync(0xffffffffu, small)) {
+                    res = make_i128((uint64_t)(uint32_t)lo64(x) * (uint64_t)(uint32_t)lo64(y), 0);
+                    done = true;
+                }
+            }
+            if (!done) {
+                if (!ov) ov = checked_binop<nd.width>(nd.op, x, y, &res);
+                if (ov) res = 0;
+            }
         } else {
             u128 ux = (u128)x, uy = (u128)y;
             u128 ur = nd.op == DOP_ADD ? ux + uy : (nd.op == DOP_SUB ? ux - uy : ux * uy);
@@ -301,9 +391,10 @@ SRB_D void eval_static_node(const DProg& p, Val* v, const SmemCols& sc, int r) {
     }
 }
 template <class S, int... I>
-SRB_D void eval_static_all(const DProg& p, Val* v, const SmemCols& sc, int r, std::integer_sequence<int, I...>) {
-    (eval_static_node<S, I>(p, v, sc, r), ...);
+SRB_D void eval_static_all(const DProg& p, Val* v, const uint8_t* stage, int r, std::integer_sequence<int, I...>) {
+    (eval_static_node<S, I>(p, v, stage, r), ...);
 }
+
 
 // aggregate a is a "representative" when no earlier SUM/AVG aggregate has the same argument (their partial sums are identical)
 template <class S>
@@ -339,68 +430,70 @@ constexpr bool node_can_be_null(int n) {
     return node_can_be_null<S>(nd.lhs) || node_can_be_null<S>(nd.rhs);
 }
 
-// Per-thread accumulators of the low-cardinality path. The LOW 64 bits of every partial sum live in shared memory, one
-// private word per (representative, group, thread): lanes of a warp hit distinct banks whatever their groups are, so the
-// update is a plain LDS / add / STS with the group as a runtime address — no atomics and no per-group predication. The
-// HIGH part (carries + sign words, almost always zero per row) stays in registers and is only touched when a warp vote
-// finds a non-zero delta.
+// Per-thread accumulators of the low-cardinality path. The LOW 64 bits of every partial sum and the row count live in
+// shared memory, one private word per (representative, group, thread): lanes of a warp hit distinct banks whatever their
+// groups are, so an update is a plain LDS / add / STS with the group as a runtime address — no atomics, no per-group
+// predication. What is almost never non-zero per row — the carry / sign word above bit 63 and NULL arguments — is
+// collected into ONE warp vote per row; only when it fires are the rare-path counters (thread-local memory, indexed by
+// group) touched.
 template <class S>
-struct HiRegs {
+struct AccGeom {
     static constexpr int G = S::GMAX > 0 ? S::GMAX : 1;
     static constexpr int NR = n_reps<S>() > 0 ? n_reps<S>() : 1;
-    uint32_t w2[G][NR], w3[G][NR]; // bits 64..95 and 96..127 of each partial sum (w3 only for 16-byte arguments)
-    uint32_t n[G][NR];             // non-NULL rows (only for arguments that can be NULL)
-    uint32_t rows[G];
+    static constexpr int LO_BYTES = NR * G * S::THREADS * 8; // [rep][group][thread] u64
+    static constexpr int ROWS_BYTES = G * S::THREADS * 4;    // [group][thread] u32
+    static constexpr int BYTES = S::GMAX > 0 ? LO_BYTES + ROWS_BYTES : 0;
+};
+template <class S>
+struct RareAcc {
+    uint64_t hi[AccGeom<S>::G * AccGeom<S>::NR];    // bits 64..127 of each partial sum (sign-extended for 8-byte arguments)
+    uint32_t nulls[AccGeom<S>::G * AccGeom<S>::NR]; // selected rows whose argument was NULL
 };
 
-template <class S, int A, int THREADS>
-SRB_D void acc_update(HiRegs<S>& h, uint8_t* acc_tid, const Val* v, bool on, int gid) {
+template <class S, int A>
+SRB_D void acc_one(uint8_t* a, const Val* v, bool on, uint64_t* dh, bool* nl, uint64_t& any_hi, bool& any_null) {
     constexpr SAgg g = S::agg(A);
-    constexpr int G = HiRegs<S>::G;
-    if constexpr (g.fn == FN_COUNT) {
-        // count(*) and count of a NOT NULL argument are the group's row count
-    } else if constexpr (agg_rep<S>(A) == A) {
+    if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
         constexpr int RI = rep_index<S>(A);
-        constexpr bool wide = S::node(g.arg).width == 16;
         constexpr bool nullable = node_can_be_null<S>(g.arg);
         const Val& x = v[g.arg];
         bool take = on;
-        if constexpr (nullable) take = take && !x.null;
-        uint32_t d2 = 0, d3 = 0;
+        nl[RI] = false;
+        if constexpr (nullable) {
+            take = on && !x.null;
+            nl[RI] = on && x.null;
+            any_null = any_null || nl[RI];
+        }
+        dh[RI] = 0;
         if (take) {
-            uint64_t* slot = (uint64_t*)(acc_tid + (size_t)(RI * G + gid) * THREADS * 8);
+            uint64_t* slot = (uint64_t*)(a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8);
             const uint64_t old = *slot, nw = old + x.lo;
             *slot = nw;
-            const uint64_t dh = (uint64_t)x.hi + (nw < old ? 1ULL : 0ULL);
-            d2 = (uint32_t)dh;
-            d3 = (uint32_t)(dh >> 32);
+            dh[RI] = (uint64_t)x.hi + (nw < old ? 1ULL : 0ULL);
         }
-        const bool any_hi = wide ? ((d2 | d3) != 0) : (d2 != 0);
-        if (__any_sync(0xffffffffu, any_hi)) {
-#pragma unroll
-            for (int q = 0; q < G; q++) {
-                const bool mine = gid == q;
-                if constexpr (wide) {
-                    const uint32_t a2 = mine ? d2 : 0u, a3 = mine ? d3 : 0u;
-                    const uint32_t s2 = h.w2[q][RI] + a2;
-                    h.w3[q][RI] += a3 + (s2 < a2 ? 1u : 0u);
-                    h.w2[q][RI] = s2;
-                } else {
-                    h.w2[q][RI] += mine ? d2 : 0u;
-                }
-            }
-        }
-        if constexpr (nullable) {
-#pragma unroll
-            for (int q = 0; q < G; q++) h.n[q][RI] += (take && gid == q) ? 1u : 0u;
-        }
+        any_hi |= dh[RI];
     }
 }
-template <class S, int THREADS, int... A>
-SRB_D void acc_update_all(HiRegs<S>& h, uint8_t* acc_tid, const Val* v, bool on, int gid, std::integer_sequence<int, A...>) {
-    (acc_update<S, A, THREADS>(h, acc_tid, v, on, gid), ...);
-#pragma unroll
-    for (int q = 0; q < HiRegs<S>::G; q++) h.rows[q] += (on && gid == q) ? 1u : 0u;
+template <class S, int A>
+SRB_D void acc_rare_one(RareAcc<S>& ra, int gid, const uint64_t* dh, const bool* nl) {
+    constexpr SAgg g = S::agg(A);
+    if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
+        constexpr int RI = rep_index<S>(A);
+        ra.hi[gid * AccGeom<S>::NR + RI] += dh[RI];
+        if constexpr (node_can_be_null<S>(g.arg)) ra.nulls[gid * AccGeom<S>::NR + RI] += nl[RI] ? 1u : 0u;
+    }
+}
+// one row into group gid (0 <= gid < G; `on` false: the row does not count). All 32 lanes must call.
+template <class S, int... A>
+SRB_D void acc_update_all(RareAcc<S>& ra, uint8_t* acc_tid, uint8_t* rows_tid, const Val* v, bool on, int gid, std::integer_sequence<int, A...>) {
+    uint64_t dh[AccGeom<S>::NR];
+    bool nl[AccGeom<S>::NR];
+    uint64_t any_hi = 0;
+    bool any_null = false;
+    uint8_t* a = acc_tid + (size_t)gid * (S::THREADS * 8);
+    (acc_one<S, A>(a, v, on, dh, nl, any_hi, any_null), ...);
+    if (on) *(uint32_t*)(rows_tid + (size_t)gid * (S::THREADS * 4)) += 1u;
+    if (__any_sync(0xffffffffu, any_hi != 0 || any_null)) (acc_rare_one<S, A>(ra, gid, dh, nl), ...);
 }
 
 SRB_D uint64_t warp_sum_u64(uint64_t x) {
@@ -416,65 +509,78 @@ SRB_D void warp_sum_u128(uint64_t& lo, uint64_t& hi) {
     }
 }
 
-// fold group q of this thread's accumulators into table slot `slot`: warp reduction, then lane 0 issues the atomics
-template <class S, int THREADS>
+// Retiring a CTA's accumulators in two steps, so that the few table slots of a low-cardinality GROUP BY see one set of
+// atomics per CTA rather than one per warp: (1) every warp reduces its lanes and stashes the totals in shared memory,
+// (2) one thread per group adds the warps' totals and folds them into the group's table slot.
+template <class S>
 struct Flusher {
-    static constexpr int G = HiRegs<S>::G;
-    static constexpr int NR = HiRegs<S>::NR;
-    uint64_t red_lo[NR], red_hi[NR], red_n[NR];
+    static constexpr int G = AccGeom<S>::G;
+    static constexpr int NR = AccGeom<S>::NR;
+    static constexpr int WORDS = 3 * NR + 1; // per (warp, group): {lo, hi, nulls} per representative, then the row count
+    static constexpr int STASH_BYTES = (S::THREADS / 32) * G * WORDS * 8;
 
     template <int A>
-    __device__ __forceinline__ void reduce_rep(const HiRegs<S>& h, const uint8_t* acc_tid, int q) {
+    static __device__ __forceinline__ void stash_rep(const RareAcc<S>& ra, const uint8_t* acc_tid, int q, uint64_t* st) {
         constexpr SAgg g = S::agg(A);
         if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
             constexpr int RI = rep_index<S>(A);
-            constexpr bool wide = S::node(g.arg).width == 16;
-            uint64_t lo = *(const uint64_t*)(acc_tid + (size_t)(RI * G + q) * THREADS * 8);
-            // static q is needed for the register arrays: select by unrolled compare
-            uint32_t w2 = 0, w3 = 0, n = 0;
-#pragma unroll
-            for (int k = 0; k < G; k++)
-                if (k == q) {
-                    w2 = h.w2[k][RI];
-                    w3 = h.w3[k][RI];
-                    n = h.n[k][RI];
-                }
-            uint64_t hi = wide ? (((uint64_t)w3 << 32) | w2) : (uint64_t)(int64_t)(int32_t)w2;
+            uint64_t lo = *(const uint64_t*)(acc_tid + (size_t)(RI * G + q) * S::THREADS * 8);
+            uint64_t hi = ra.hi[q * NR + RI];
             warp_sum_u128(lo, hi);
-            red_lo[RI] = lo;
-            red_hi[RI] = hi;
-            if constexpr (node_can_be_null<S>(g.arg)) red_n[RI] = warp_sum_u64(n);
+            uint64_t nulls = 0;
+            if constexpr (node_can_be_null<S>(g.arg)) nulls = warp_sum_u64(ra.nulls[q * NR + RI]);
+            if ((threadIdx.x & 31) == 0) {
+                st[RI * 3 + 0] = lo;
+                st[RI * 3 + 1] = hi;
+                st[RI * 3 + 2] = nulls;
+            }
         }
     }
+    // step 1, whole warps: group q of this warp's lanes -> stash
+    template <int... A>
+    static __device__ __forceinline__ void stash(const RareAcc<S>& ra, const uint8_t* acc_tid, const uint8_t* rows_tid, int q, uint64_t* stash_base,
+                                                 std::integer_sequence<int, A...>) {
+        uint64_t* st = stash_base + (size_t)((threadIdx.x >> 5) * G + q) * WORDS;
+        const uint64_t rows = warp_sum_u64(*(const uint32_t*)(rows_tid + (size_t)q * (S::THREADS * 4)));
+        if ((threadIdx.x & 31) == 0) st[3 * NR] = rows;
+        (stash_rep<A>(ra, acc_tid, q, st), ...);
+    }
     template <int A>
-    __device__ __forceinline__ void emit(const DProg& p, uint8_t* slot, uint64_t rows_total) {
+    static __device__ __forceinline__ void emit(const DProg& p, uint8_t* slot, const uint64_t* tot, uint64_t rows_total) {
         constexpr SAgg g = S::agg(A);
         const DAgg& rt = p.aggs[A];
-        const int lane = threadIdx.x & 31;
         if constexpr (g.fn == FN_COUNT) {
-            if (lane == 0 && rows_total) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)rows_total);
+            if (rows_total) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)rows_total);
         } else {
             constexpr int RI = rep_index<S>(agg_rep<S>(A));
-            uint64_t n = rows_total;
-            if constexpr (node_can_be_null<S>(g.arg)) n = red_n[RI];
-            if (lane == 0 && n) {
-                atomic_add128(slot, rt.off_lo, rt.off_hi, red_lo[RI], red_hi[RI]);
+            const uint64_t n = rows_total - tot[RI * 3 + 2];
+            if (n) {
+                atomic_add128(slot, rt.off_lo, rt.off_hi, tot[RI * 3 + 0], tot[RI * 3 + 1]);
                 if (rt.off_n >= 0) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)n);
             }
         }
     }
+    // step 2, one thread: totals of group q over the warps -> table slot
     template <int... A>
-    __device__ __forceinline__ void run(const DProg& p, const HiRegs<S>& h, const uint8_t* acc_tid, int q, uint8_t* slot,
-                                        std::integer_sequence<int, A...>) {
-        uint32_t rows = 0;
+    static __device__ __forceinline__ void fold(const DProg& p, const uint64_t* stash_base, int q, uint8_t* slot, std::integer_sequence<int, A...>) {
+        uint64_t tot[WORDS];
 #pragma unroll
-        for (int k = 0; k < G; k++)
-            if (k == q) rows = h.rows[k];
-        const uint64_t rows_total = warp_sum_u64(rows);
-        (reduce_rep<A>(h, acc_tid, q), ...);
-        (emit<A>(p, slot, rows_total), ...);
+        for (int k = 0; k < WORDS; k++) tot[k] = 0;
+        for (int w = 0; w < S::THREADS / 32; w++) {
+            const uint64_t* st = stash_base + (size_t)(w * G + q) * WORDS;
+#pragma unroll
+            for (int r = 0; r < NR; r++) {
+                const uint64_t lo = tot[r * 3] + st[r * 3];
+                tot[r * 3 + 1] += st[r * 3 + 1] + (lo < st[r * 3] ? 1ULL : 0ULL);
+                tot[r * 3] = lo;
+                tot[r * 3 + 2] += st[r * 3 + 2];
+            }
+            tot[3 * NR] += st[3 * NR];
+        }
+        (emit<A>(p, slot, tot, tot[3 * NR]), ...);
     }
 };
+
 
 // per-row update of a table slot with compile-time operand indexes (static shapes carry SUM / AVG / COUNT over integers)
 template <class S, int A>
@@ -529,24 +635,25 @@ struct StaticCtr {
     unsigned long long* inserted;
 };
 
-constexpr int ST_GROUP = 128;                  // threads per consumer group
-constexpr int ST_MAX_GROUPS = 8;
-SRB_D void group_barrier(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(ST_GROUP) : "memory"); }
+SRB_D void mbar_arrive(uint64_t* bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory"); }
 
-// The CTA is split into consumer groups of 128 threads. Every group streams its OWN tiles through its OWN ring of stages and
-// synchronises only with itself (named barrier), so the groups drift apart and one group's barrier / latency bubbles are
-// filled by the others — the block never stalls as a whole, and there is no block-wide barrier in the steady state.
+// One persistent CTA per SM: S::THREADS consumer threads plus one producer warp. The producer's elected lane keeps the
+// ring full (one bulk copy per column and tile, completing on full_bar[s]) and only it ever waits for a stage to drain
+// (empty_bar[s], one arrival per consumer warp). Consumer warps therefore never wait for each other: a warp that is
+// done with its rows of a tile arrives and moves on to the next stage, so up to n_stages tiles are being consumed at once
+// and there is no block-wide barrier in the steady state.
 template <class S>
-__global__ void __launch_bounds__(S::THREADS, 1)
+__global__ void __launch_bounds__(S::THREADS + 32, 1)
         k_scan_agg_static(const __grid_constant__ DProg prog, const __grid_constant__ StaticArgs sa, const TableView tv, const int64_t base,
                           const int64_t n_tiles, uint32_t* __restrict__ defer_out, StaticCtr ctr) {
     constexpr int THREADS = S::THREADS;
-    constexpr int NG = THREADS / ST_GROUP;
-    constexpr int R = ST_TILE / ST_GROUP; // rows per thread per tile, strided by the group size (conflict-free LDS)
-    constexpr int G = HiRegs<S>::G;
-    static_assert(THREADS % ST_GROUP == 0 && NG <= ST_MAX_GROUPS && ST_TILE % ST_GROUP == 0, "block / tile geometry");
+    constexpr int R = S::ROWS;
+    constexpr int TILE = tile_rows<S>();
+    constexpr int G = AccGeom<S>::G;
+    constexpr int KW = static_key_bytes<S>() > 8 ? 2 : 1;
+    static_assert(THREADS % 32 == 0 && THREADS + 32 <= 1024 && (TILE * 1) % 16 == 0, "block / tile geometry");
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ uint64_t full_bar[ST_MAX_GROUPS][ST_MAX_STAGES];
+    __shared__ uint64_t full_bar[ST_MAX_STAGES], empty_bar[ST_MAX_STAGES];
     __shared__ uint64_t dir_lo[G], dir_hi[G];
     __shared__ uint8_t* dir_slot[G];
     __shared__ int dir_cnt, dir_lock;
@@ -555,130 +662,204 @@ __global__ void __launch_bounds__(S::THREADS, 1)
     using AggSeq = std::make_integer_sequence<int, S::N_AGGS>;
 
     const int stage_bytes = sa.stage_bytes, n_stages = sa.n_stages;
-    const int tid = threadIdx.x, grp = tid / ST_GROUP, gtid = tid % ST_GROUP;
+    const int tid = threadIdx.x;
     if (tid == 0) {
-        for (int g = 0; g < NG; g++)
-            for (int s = 0; s < n_stages; s++) mbar_init(&full_bar[g][s], 1);
+        for (int s = 0; s < n_stages; s++) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], THREADS / 32);
+        }
         dir_cnt = 0;
         dir_lock = 0;
         fence_barrier_init();
     }
     // this thread's private accumulator words start zeroed
     uint8_t* acc_tid = smem + sa.acc_off + tid * 8;
+    uint8_t* rows_tid = smem + sa.acc_off + AccGeom<S>::LO_BYTES + tid * 4;
+    RareAcc<S> ra;
     if constexpr (S::GMAX > 0) {
+        if (tid < THREADS) {
 #pragma unroll
-        for (int k = 0; k < HiRegs<S>::NR * G; k++) *(uint64_t*)(acc_tid + (size_t)k * THREADS * 8) = 0;
+            for (int k = 0; k < AccGeom<S>::NR * G; k++) *(uint64_t*)(acc_tid + (size_t)k * THREADS * 8) = 0;
+#pragma unroll
+            for (int k = 0; k < G; k++) *(uint32_t*)(rows_tid + (size_t)k * THREADS * 4) = 0;
+        }
+#pragma unroll
+        for (int k = 0; k < AccGeom<S>::NR * G; k++) {
+            ra.hi[k] = 0;
+            ra.nulls[k] = 0;
+        }
     }
     __syncthreads();
 
-    uint8_t* ring = smem + (size_t)grp * n_stages * stage_bytes; // this group's stages
-    auto issue = [&](int64_t tile, int s) { // the group's elected thread: one bulk copy per column, all completing on full_bar[grp][s]
-        mbar_expect_tx(&full_bar[grp][s], (uint32_t)stage_bytes);
-        uint8_t* dst = ring + (size_t)s * stage_bytes;
-        for (int c = 0; c < p.n_cols; c++) {
-            const int w = p.cols[c].width;
-            tma_load_1d(dst + sa.col_off[c], (const uint8_t*)p.cols[c].data + (size_t)(base + tile * ST_TILE) * w, (uint32_t)(ST_TILE * w),
-                        &full_bar[grp][s]);
-        }
-    };
-    const int64_t first = (int64_t)blockIdx.x * NG + grp, step = (int64_t)gridDim.x * NG;
-    if (gtid == 0)
-        for (int s = 0; s < n_stages; s++)
-            if (first + s * step < n_tiles) issue(first + s * step, s);
-
-    HiRegs<S> h;
-#pragma unroll
-    for (int q = 0; q < G; q++) {
-        h.rows[q] = 0;
-#pragma unroll
-        for (int k = 0; k < HiRegs<S>::NR; k++) h.w2[q][k] = h.w3[q][k] = h.n[q][k] = 0;
-    }
     unsigned long long selected = 0, deferred = 0, inserted = 0;
-
-    int s = 0;
-    uint32_t parity = 0;
-    for (int64_t tile = first; tile < n_tiles; tile += step) {
-        mbar_wait(&full_bar[grp][s], parity);
-        const uint8_t* stage = ring + (size_t)s * stage_bytes;
-        const SmemCols sc{stage, sa.col_off};
-        int rows[R];
-        bool pass[R];
-#pragma unroll
-        for (int j = 0; j < R; j++) rows[j] = gtid + j * ST_GROUP;
-        eval_preds_rows<R>(sa, stage, rows, pass);
-#pragma unroll
-        for (int j = 0; j < R; j++) {
-            selected += pass[j] ? 1 : 0;
-            if (!__any_sync(0xffffffffu, pass[j])) continue;
-            const int r = rows[j];
-            Val v[S::N_NODES];
-            eval_static_all<S>(p, v, sc, r, NodeSeq{});
-            if constexpr (S::N_KEYS == 0) {
-                acc_update_all<S, THREADS>(h, acc_tid, v, pass[j], 0, AggSeq{});
-            } else {
-                const PackedKey k = pack_key_static<S>(v);
-                int gid = -1;
-                if constexpr (S::GMAX > 0) {
-                    const int cnt = *(volatile int*)&dir_cnt;
-#pragma unroll
-                    for (int q = 0; q < G; q++)
-                        if (q < cnt && ((volatile uint64_t*)dir_lo)[q] == k.lo && (p.key_words == 1 || ((volatile uint64_t*)dir_hi)[q] == k.hi)) gid = q;
-                    acc_update_all<S, THREADS>(h, acc_tid, v, pass[j] && gid >= 0, gid < 0 ? 0 : gid, AggSeq{});
+    if (tid >= THREADS) {
+        // ---- producer warp ----
+        if (tid == THREADS) {
+            int s = 0;
+            uint32_t parity = 1; // a fresh mbarrier passes a wait on parity 1: the first lap needs no arrivals
+            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                mbar_wait(&empty_bar[s], parity);
+                mbar_expect_tx(&full_bar[s], (uint32_t)stage_bytes);
+                uint8_t* dst = smem + (size_t)s * stage_bytes;
+                for (int c = 0; c < p.n_cols; c++) {
+                    const int w = p.cols[c].width;
+                    tma_load_1d(dst + sa.col_off[c], (const uint8_t*)p.cols[c].data + (size_t)(base + tile * TILE) * w, (uint32_t)(TILE * w),
+                                &full_bar[s]);
                 }
-                if (pass[j] && gid < 0) {
-                    // global-table path: the group is not (yet) in this CTA's directory
-                    bool fresh;
-                    uint8_t* slot = table_find_or_insert(tv, k.lo, k.hi, hash_packed_key_static<static_key_bytes<S>()>(k, p.phase_seed), &fresh);
-                    inserted += fresh ? 1 : 0;
-                    if (!slot) {
-                        const int64_t i = tile * ST_TILE + r;
-                        atomicOr(&defer_out[i >> 5], 1u << (i & 31));
-                        deferred++;
+                if (++s == n_stages) {
+                    s = 0;
+                    parity ^= 1u;
+                }
+            }
+        }
+    } else {
+        // ---- consumer warps ----
+        uint64_t kd_lo[G], kd_hi[G]; // register copy of the directory keys, refreshed when the directory grew
+        int my_cnt = 0;
+#pragma unroll
+        for (int q = 0; q < G; q++) kd_lo[q] = kd_hi[q] = 0;
+        int s = 0;
+        uint32_t parity = 0;
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            if constexpr (S::GMAX > 0 && S::N_KEYS > 0) {
+                // my_cnt steers warp votes below, so it must be ONE value per warp even if the lanes poll at different times
+                // (the minimum: every lane's own read saw at least that many published entries before it loads them)
+                const int c = (int)__reduce_min_sync(0xffffffffu, (unsigned)*(volatile int*)&dir_cnt);
+                if (c != my_cnt) {
+#pragma unroll
+                    for (int q = 0; q < G; q++) {
+                        kd_lo[q] = ((volatile uint64_t*)dir_lo)[q];
+                        if constexpr (KW == 2) kd_hi[q] = ((volatile uint64_t*)dir_hi)[q];
+                    }
+                    my_cnt = c;
+                }
+            }
+            mbar_wait(&full_bar[s], parity);
+            __syncwarp(); // lanes may leave the wait loop on different polls
+            const uint8_t* stage = smem + (size_t)s * stage_bytes;
+            bool pass[R];
+            if (sa.n_ranges >= 0) {
+                eval_ranges_rows<R, THREADS>(sa, stage, tid, pass);
+            } else {
+                int rows[R];
+#pragma unroll
+                for (int j = 0; j < R; j++) rows[j] = tid + j * THREADS;
+                eval_preds_rows<R>(sa, stage, rows, pass);
+            }
+            bool any_pass = false;
+#pragma unroll
+            for (int j = 0; j < R; j++) {
+                selected += pass[j] ? 1 : 0;
+                any_pass = any_pass || pass[j];
+            }
+            if (__any_sync(0xffffffffu, any_pass)) {
+                Val v[R][S::N_NODES];
+#pragma unroll
+                for (int j = 0; j < R; j++) eval_static_all<S>(p, v[j], stage, tid + j * THREADS, NodeSeq{});
+#pragma unroll
+                for (int j = 0; j < R; j++) {
+                    if constexpr (S::N_KEYS == 0) {
+                        acc_update_all<S>(ra, acc_tid, rows_tid, v[j], pass[j], 0, AggSeq{});
                     } else {
-                        row_update_global<S>(p, slot, v, AggSeq{});
+                        const PackedKey k = pack_key_static<S>(v[j]);
+                        bool miss = pass[j]; // this row still has to reach its group
                         if constexpr (S::GMAX > 0) {
-                            // best-effort publication into the directory (try-lock; duplicates are excluded under the lock)
-                            if (*(volatile int*)&dir_cnt < G && atomicCAS(&dir_lock, 0, 1) == 0) {
-                                const int c = *(volatile int*)&dir_cnt;
-                                bool present = false;
-                                for (int q = 0; q < c; q++)
-                                    present = present || (((volatile uint64_t*)dir_lo)[q] == k.lo && ((volatile uint64_t*)dir_hi)[q] == k.hi);
-                                if (!present && c < G) {
-                                    ((volatile uint64_t*)dir_lo)[c] = k.lo;
-                                    ((volatile uint64_t*)dir_hi)[c] = k.hi;
-                                    ((uint8_t* volatile*)dir_slot)[c] = slot;
-                                    __threadfence_block();
-                                    *(volatile int*)&dir_cnt = c + 1;
+                            // descending: the lowest matching entry wins, and a match at or past my_cnt (a stale register) is discarded
+                            int gid = G;
+#pragma unroll
+                            for (int q = G - 1; q >= 0; q--)
+                                if (kd_lo[q] == k.lo && (KW == 1 || kd_hi[q] == k.hi)) gid = q;
+                            bool hit = gid < my_cnt;
+                            if (my_cnt < G && __any_sync(0xffffffffu, pass[j] && !hit)) {
+                                // Some lane's group is not in the directory copy. One leader per distinct missing key of the warp
+                                // takes the directory lock and — only if the group is still absent — claims its table slot and
+                                // publishes it, so the HBM table sees one probe per (CTA, group) instead of one per row while the
+                                // directory fills. Then every lane refreshes its copy and looks again.
+                                const bool need = pass[j] && !hit;
+                                const unsigned need_mask = __ballot_sync(0xffffffffu, need);
+                                const unsigned peers = __match_any_sync(0xffffffffu, k.lo ^ (k.hi * 0x9e3779b97f4a7c15ULL)) & need_mask;
+                                if (need && (peers & ((1u << (tid & 31)) - 1u)) == 0) {
+                                    for (int t = 0; t < 256; t++) {
+                                        const int c = *(volatile int*)&dir_cnt;
+                                        bool present = false;
+                                        for (int q = 0; q < c; q++)
+                                            present = present || (((volatile uint64_t*)dir_lo)[q] == k.lo && ((volatile uint64_t*)dir_hi)[q] == k.hi);
+                                        if (present || c >= G) break;
+                                        if (atomicCAS(&dir_lock, 0, 1) == 0) {
+                                            const int c2 = *(volatile int*)&dir_cnt;
+                                            present = false;
+                                            for (int q = 0; q < c2; q++)
+                                                present = present || (((volatile uint64_t*)dir_lo)[q] == k.lo && ((volatile uint64_t*)dir_hi)[q] == k.hi);
+                                            if (!present && c2 < G) {
+                                                bool fresh;
+                                                uint8_t* sl = table_find_or_insert(tv, k.lo, k.hi, hash_packed_key_static<static_key_bytes<S>()>(k, p.phase_seed), &fresh);
+                                                inserted += fresh ? 1 : 0;
+                                                if (sl) {
+                                                    ((volatile uint64_t*)dir_lo)[c2] = k.lo;
+                                                    ((volatile uint64_t*)dir_hi)[c2] = k.hi;
+                                                    ((uint8_t* volatile*)dir_slot)[c2] = sl;
+                                                    __threadfence_block();
+                                                    *(volatile int*)&dir_cnt = c2 + 1;
+                                                }
+                                            }
+                                            __threadfence_block();
+                                            atomicExch(&dir_lock, 0);
+                                            break;
+                                        }
+                                        __nanosleep(64);
+                                    }
                                 }
-                                __threadfence_block();
-                                atomicExch(&dir_lock, 0);
+                                __syncwarp();
+                                my_cnt = (int)__reduce_min_sync(0xffffffffu, (unsigned)*(volatile int*)&dir_cnt);
+#pragma unroll
+                                for (int q = 0; q < G; q++) {
+                                    kd_lo[q] = ((volatile uint64_t*)dir_lo)[q];
+                                    if constexpr (KW == 2) kd_hi[q] = ((volatile uint64_t*)dir_hi)[q];
+                                }
+                                gid = G;
+#pragma unroll
+                                for (int q = G - 1; q >= 0; q--)
+                                    if (kd_lo[q] == k.lo && (KW == 1 || kd_hi[q] == k.hi)) gid = q;
+                                hit = gid < my_cnt;
+                            }
+                            acc_update_all<S>(ra, acc_tid, rows_tid, v[j], pass[j] && hit, hit ? gid : 0, AggSeq{});
+                            miss = pass[j] && !hit;
+                        }
+                        if (miss) {
+                            // global-table path: the directory is full of other groups (or the shape keeps none)
+                            bool fresh;
+                            uint8_t* slot = table_find_or_insert(tv, k.lo, k.hi, hash_packed_key_static<static_key_bytes<S>()>(k, p.phase_seed), &fresh);
+                            inserted += fresh ? 1 : 0;
+                            if (!slot) {
+                                const int64_t i = tile * TILE + tid + j * THREADS;
+                                atomicOr(&defer_out[i >> 5], 1u << (i & 31));
+                                deferred++;
+                            } else {
+                                row_update_global<S>(p, slot, v[j], AggSeq{});
                             }
                         }
                     }
                 }
             }
-        }
-        group_barrier(1 + grp); // every thread of the group is done with stage s
-        if (gtid == 0 && tile + (int64_t)n_stages * step < n_tiles) {
-            fence_proxy_async();
-            issue(tile + (int64_t)n_stages * step, s);
-        }
-        if (++s == n_stages) {
-            s = 0;
-            parity ^= 1u;
+            __syncwarp();
+            if ((tid & 31) == 0) mbar_arrive(&empty_bar[s]); // this warp is done with stage s
+            if (++s == n_stages) {
+                s = 0;
+                parity ^= 1u;
+            }
         }
     }
-    __syncthreads(); // the directory is final
-    // retire: warp-reduce every group's accumulators and fold them into the table
+    __syncthreads(); // the directory is final and the ring is idle: its first bytes become the stash
     if constexpr (S::GMAX > 0) {
-        Flusher<S, THREADS> f;
-        if constexpr (S::N_KEYS == 0) {
-            f.run(p, h, acc_tid, 0, tv.slots, AggSeq{});
-        } else {
-            const int cnt = dir_cnt;
-            for (int q = 0; q < cnt; q++) f.run(p, h, acc_tid, q, dir_slot[q], AggSeq{});
-        }
+        static_assert(Flusher<S>::STASH_BYTES <= 32 * 1024, "stash must fit the first stage");
+        uint64_t* stash = (uint64_t*)smem;
+        const int cnt = S::N_KEYS == 0 ? 1 : dir_cnt;
+        if (tid < THREADS)
+            for (int q = 0; q < cnt; q++) Flusher<S>::stash(ra, acc_tid, rows_tid, q, stash, AggSeq{});
+        __syncthreads();
+        if (tid < cnt) Flusher<S>::fold(p, stash, tid, S::N_KEYS == 0 ? tv.slots : dir_slot[tid], AggSeq{});
     }
+    if (tid >= THREADS) return;
     selected = warp_sum_u64(selected);
     deferred = warp_sum_u64(deferred);
     inserted = warp_sum_u64(inserted);
@@ -688,6 +869,7 @@ __global__ void __launch_bounds__(S::THREADS, 1)
         if (inserted) atomicAdd(ctr.inserted, inserted);
     }
 }
+
 
 // ---- registry ---------------------------------------------------------------------------------------------------------------
 inline int match_static_shape(const DProg& p) {
@@ -718,44 +900,114 @@ inline uint32_t pred_opmask(int op) {
     }
 }
 
+// Lower conjunct predicates over 4- / 8-byte integer columns to per-column ranges. Returns false (caller keeps the
+// generic predicate loop) for OR-groups, other widths, or more distinct ranges than ST_MAX_RANGES.
+inline bool lower_ranges(const DProg& p, StaticArgs& sa) {
+    int n = 0;
+    for (int i = 0; i < p.n_preds; i++) {
+        const DPred& d = p.preds[i];
+        const int w = p.cols[d.col].width;
+        if (d.group != 0 || (w != 4 && w != 8)) return false;
+        const i128 tmin = w == 4 ? (i128)INT32_MIN : (i128)INT64_MIN, tmax = w == 4 ? (i128)INT32_MAX : (i128)INT64_MAX;
+        const i128 lit = make_i128(d.lit_lo, d.lit_hi);
+        i128 lo = tmin, hi = tmax; // inclusive bounds
+        bool neg = false;
+        switch (d.op) {
+        case SRB_PRED_EQ: lo = hi = lit; break;
+        case SRB_PRED_NE: lo = hi = lit; neg = true; break;
+        case SRB_PRED_GT: lo = lit + 1; break;
+        case SRB_PRED_GE: lo = lit; break;
+        case SRB_PRED_LT: hi = lit - 1; break;
+        case SRB_PRED_LE: hi = lit; break;
+        case SRB_PRED_NOT_NULL: continue;  // NULL-free column: always true
+        default: neg = true; break;        // IS NULL on a NULL-free column: never true (NOT of the full range)
+        }
+        if (lo < tmin) lo = tmin;
+        if (hi > tmax) hi = tmax;
+        if (lo > hi) { // empty range: NOT(full) when plain, full when negated
+            lo = tmin;
+            hi = tmax;
+            neg = !neg;
+        }
+        // intersect with an earlier plain range on the same column
+        bool merged = false;
+        if (!neg) {
+            for (int k = 0; k < n && !merged; k++) {
+                SRange& g = sa.rng[k];
+                if (g.col_off != sa.col_off[d.col] || g.neg) continue;
+                i128 glo = (i128)g.lo, ghi = (i128)g.lo + (i128)g.span;
+                if (lo > glo) glo = lo;
+                if (hi < ghi) ghi = hi;
+                if (glo > ghi) { // empty intersection
+                    g.lo = (int64_t)tmin;
+                    g.span = (uint64_t)(tmax - tmin);
+                    g.neg = 1;
+                } else {
+                    g.lo = (int64_t)glo;
+                    g.span = (uint64_t)(ghi - glo);
+                }
+                merged = true;
+            }
+        }
+        if (merged) continue;
+        if (n == ST_MAX_RANGES) return false;
+        sa.rng[n++] = SRange{sa.col_off[d.col], w, neg ? 1 : 0, 0, (int64_t)lo, (uint64_t)(hi - lo)};
+    }
+    sa.n_ranges = n;
+    return true;
+}
+
 template <class S>
 inline int64_t launch_shape(const DProg& p, const TableView& tv, int64_t base, int64_t n, uint32_t* defer_out, unsigned long long* rows_selected,
                             unsigned long long* deferred, unsigned long long* inserted, int n_sms, cudaStream_t stream) {
-    int row_bytes = 0;
+    constexpr int TILE = tile_rows<S>();
     StaticArgs sa{};
+    // stage layout: the columns of the LOAD nodes first, in node order (compile-time offsets), then predicate-only columns
+    bool placed[MAX_COLS] = {};
+    int bytes = 0;
+    for (int i = 0; i < S::N_NODES; i++) {
+        if (S::node(i).op != DOP_LOAD) continue;
+        const int c = p.nodes[i].col;
+        if (c < 0 || c >= p.n_cols || placed[c] || p.cols[c].width != S::node(i).width) return 0; // a column bound twice: generic kernel
+        placed[c] = true;
+        sa.col_off[c] = load_off<S>(i);
+        bytes = load_off<S>(i) + S::node(i).width * TILE;
+    }
     for (int c = 0; c < p.n_cols; c++) {
-        sa.col_off[c] = ST_TILE * row_bytes;
-        row_bytes += p.cols[c].width;
+        if (!placed[c]) {
+            sa.col_off[c] = bytes;
+            bytes += p.cols[c].width * TILE;
+        }
         // TMA bulk copies need 16-byte aligned sources: tile starts are multiples of 1024 rows, so the base pointers decide
         if (p.cols[c].nulls || (((uintptr_t)p.cols[c].data + (size_t)base * p.cols[c].width) & 15)) return 0;
     }
-    const int64_t n_tiles = n / ST_TILE;
-    if (n_tiles == 0 || row_bytes == 0) return 0;
-    sa.stage_bytes = ST_TILE * row_bytes;
-    const int acc_bytes = S::GMAX > 0 ? HiRegs<S>::NR * HiRegs<S>::G * S::THREADS * 8 : 0;
-    constexpr int NG = S::THREADS / ST_GROUP;
-    int stages = (ST_SMEM_BUDGET - acc_bytes) / (sa.stage_bytes * NG);
+    const int64_t n_tiles = n / TILE;
+    if (n_tiles == 0 || bytes == 0) return 0;
+    sa.stage_bytes = bytes;
+    const int acc_bytes = AccGeom<S>::BYTES;
+    int stages = (ST_SMEM_BUDGET - acc_bytes) / sa.stage_bytes;
     if (stages > ST_MAX_STAGES) stages = ST_MAX_STAGES;
     if (stages < 2) return 0;
     sa.n_stages = stages;
-    sa.acc_off = NG * stages * sa.stage_bytes;
+    sa.acc_off = stages * sa.stage_bytes;
     sa.n_preds = p.n_preds;
     for (int i = 0; i < p.n_preds; i++) {
         const DPred& d = p.preds[i];
         sa.preds[i] = SPred{sa.col_off[d.col], p.cols[d.col].width, pred_opmask(d.op), d.group, d.lit_lo, d.lit_hi};
     }
+    if (!lower_ranges(p, sa)) sa.n_ranges = -1;
     const size_t smem = (size_t)sa.acc_off + acc_bytes;
     static bool configured = false;
     if (!configured) {
         cudaFuncSetAttribute(k_scan_agg_static<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM_BUDGET);
         configured = true;
     }
-    const int64_t want = (n_tiles + NG - 1) / NG;
-    const int grid = (int)(want < n_sms ? want : n_sms);
+    const int grid = (int)(n_tiles < n_sms ? n_tiles : n_sms);
     StaticCtr ctr{rows_selected, deferred, inserted};
-    k_scan_agg_static<S><<<grid, S::THREADS, smem, stream>>>(p, sa, tv, base, n_tiles, defer_out, ctr);
-    return n_tiles * ST_TILE;
+    k_scan_agg_static<S><<<grid, S::THREADS + 32, smem, stream>>>(p, sa, tv, base, n_tiles, defer_out, ctr);
+    return n_tiles * TILE;
 }
+
 
 // Launches the static kernel of `shape` over the leading whole tiles of [base, base+n); returns the number of rows it
 // covered (0 when the preconditions — no null maps, 16-byte aligned columns, at least one tile — do not hold). The caller
