@@ -151,7 +151,7 @@ SRB_D void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.clus
 
 // ---- static row pipeline ---------------------------------------------------------------------------------------------------
 constexpr int ST_MAX_STAGES = 4;   // ring depth (the host picks the deepest ring that fits beside the accumulators)
-constexpr int ST_SMEM_BUDGET = 222 * 1024;
+constexpr int ST_SMEM_BUDGET = 226 * 1024; // of the 227 KB a CTA may take; the kernel's static shared data is < 1 KB
 constexpr int ST_MAX_RANGES = 6;   // conjunct predicates after lowering to per-column ranges (more: the generic predicate loop)
 
 // rows of one tile: every consumer thread takes S::ROWS rows, strided by the thread count (conflict-free LDS)
@@ -306,93 +306,132 @@ SRB_D void eval_preds_rows(const StaticArgs& sa, const uint8_t* stage, const int
     }
 }
 
-// i64 x i64 -> i128. When every lane of the warp holds two operands in [0, 2^32) (money amounts times small factors: the
-// common case) one 32x32->64 multiply is the whole product; the vote keeps the warp converged on either side.
-SRB_D void mul_i64_i64_warp(int64_t a, int64_t b, uint64_t& lo, int64_t& hi) {
-    const bool small = (((uint64_t)a | (uint64_t)b) >> 32) == 0;
-    if (__all_sync(0xffffffffu, small)) {
-        lo = (uint64_t)(uint32_t)a * (uint64_t)(uint32_t)b;
-        hi = 0;
-    } else {
-        const i128 r = mul_i64_i64(a, b);
-        lo = lo64(r);
-        hi = hi64(r);
-    }
+// the general checked 128-bit product, kept out of line: the hot loop only carries the call
+struct Mul128Res {
+    uint64_t lo;
+    int64_t hi;
+    int ov;
+};
+static __device__ __noinline__ Mul128Res mul_overflow128_cold(uint64_t xl, int64_t xh, uint64_t yl, int64_t yh) {
+    i128 r;
+    const bool ov = mul_overflow128(make_i128(xl, xh), make_i128(yl, yh), &r);
+    return Mul128Res{lo64(r), hi64(r), ov ? 1 : 0};
 }
 
-// one node of the shape on one row. Narrow (<= 8 byte) checked ADD / SUB stay in 64-bit arithmetic; 128-bit products try
-// the warp-uniform small-operand path first; everything else is the generic primitive of srb_dev.cuh, so results are
-// the same bits as the interpreter's. Must be called by all 32 lanes (votes inside).
-template <class S, int I>
-SRB_D void eval_static_node(const DProg& p, Val* v, const uint8_t* stage, int r) {
+// One node of the shape over the R rows a thread owns in a tile (row j = r0 + j * S::THREADS). Working node-by-node across
+// the rows gives the scheduler R independent dependency chains and lets every warp vote cover all R rows at once.
+// Narrow (<= 8 byte) checked ADD / SUB stay in 64-bit arithmetic; products first try the warp-uniform small-operand path
+// (every lane, every row in [0, 2^32): money amounts times small factors — one 32x32->64 multiply is the exact product
+// and no overflow flag can be set); everything else is the generic primitive of srb_dev.cuh, so results are the same bits
+// as the interpreter's. Must be called by all 32 lanes (votes inside).
+template <class S, int I, int R>
+SRB_D void eval_static_node(const DProg& p, Val (&v)[R][S::N_NODES], const uint8_t* stage, int r0) {
     constexpr SNode nd = S::node(I);
     const DNode& rt = p.nodes[I];
     if constexpr (nd.op == DOP_LOAD) {
-        v[I] = lds_val<nd.width>(stage + load_off<S>(I), r);
+#pragma unroll
+        for (int j = 0; j < R; j++) v[j][I] = lds_val<nd.width>(stage + load_off<S>(I), r0 + j * S::THREADS);
     } else if constexpr (nd.op == DOP_LIT) {
-        v[I].lo = rt.lit_lo;
-        v[I].hi = rt.lit_hi;
-        v[I].null = false;
-    } else if constexpr (nd.op == DOP_CAST) {
-        const Val a = v[nd.lhs];
-        i128 x = make_i128(a.lo, a.hi), res = x;
-        bool ov = false;
-        if constexpr (nd.checked != 0) {
-            const i128 f = make_i128(rt.lit_lo, rt.lit_hi);
-            if (f != 1) ov = checked_binop<nd.width>(6, x, f, &res);
-            if constexpr (nd.width == 8) ov = ov || !fits<8>(x);
-            if constexpr (nd.width == 4) ov = ov || !fits<4>(x);
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            v[j][I].lo = rt.lit_lo;
+            v[j][I].hi = rt.lit_hi;
+            v[j][I].null = false;
         }
-        v[I].lo = lo64(res);
-        v[I].hi = hi64(res);
-        v[I].null = a.null || ov;
-    } else if constexpr (nd.op == DOP_MULFAST) {
-        const Val a = v[nd.lhs], b = v[nd.rhs];
-        mul_i64_i64_warp((int64_t)a.lo, (int64_t)b.lo, v[I].lo, v[I].hi);
-        v[I].null = a.null || b.null;
-    } else if constexpr (nd.checked != 0 && nd.width == 8 && nd.adj_l == 0 && nd.adj_r == 0 && (nd.op == DOP_ADD || nd.op == DOP_SUB)) {
-        const Val a = v[nd.lhs], b = v[nd.rhs];
-        const uint64_t x = a.lo, y = b.lo;
-        const uint64_t s = nd.op == DOP_ADD ? x + y : x - y;
-        // signed overflow: ADD when the operands agree in sign and the sum does not; SUB when they differ and the result left x's sign
-        const uint64_t o = nd.op == DOP_ADD ? ((x ^ s) & (y ^ s)) : ((x ^ y) & (x ^ s));
-        const bool ov = (int64_t)o < 0;
-        v[I].lo = s; // the value of a NULL is never read: consumers test .null first
-        v[I].hi = (int64_t)s >> 63;
-        v[I].null = a.null || b.null || ov;
-    } else {
-        const Val a = v[nd.lhs], b = v[nd.rhs];
-        i128 x = make_i128(a.lo, a.hi), y = make_i128(b.lo, b.hi), res = 0;
-        bool ov = false;
-        if constexpr (nd.checked != 0) {
-            if constexpr (nd.adj_l != 0) ov |= checked_binop<nd.width>(6, x, make_i128(rt.fl_lo, rt.fl_hi), &x);
-            if constexpr (nd.adj_r != 0) ov |= checked_binop<nd.width>(6, y, make_i128(rt.fr_lo, rt.fr_hi), &y);
-            bool done = false;
-            if constexpr (nd.op == DOP_MUL && nd.width == 16) {
-                // both operands in [0, 2^32): the product is exact in 64 bits and no multi3 flag can be set
-                const bool small = !ov && (((lo64(x) | lo64(y)) >> 32) == 0) && ((hi64(x) | hi64(y)) == 0);
-                if (__all_sync(0xffffffffu, small)) {
-                    res = make_i128((uint64_t)(uint32_t)lo64(x) * (uint64_t)(uint32_t)lo64(y), 0);
-                    done = true;
-                }
+    } else if constexpr (nd.op == DOP_CAST) {
+        const i128 f = make_i128(rt.lit_lo, rt.lit_hi);
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const Val a = v[j][nd.lhs];
+            i128 x = make_i128(a.lo, a.hi), res = x;
+            bool ov = false;
+            if constexpr (nd.checked != 0) {
+                if (f != 1) ov = checked_binop<nd.width>(6, x, f, &res);
+                if constexpr (nd.width == 8) ov = ov || !fits<8>(x);
+                if constexpr (nd.width == 4) ov = ov || !fits<4>(x);
             }
-            if (!done) {
+            v[j][I].lo = lo64(res);
+            v[j][I].hi = hi64(res);
+            v[j][I].null = a.null || ov;
+        }
+    } else if constexpr (nd.op == DOP_MULFAST) {
+        bool small = true;
+#pragma unroll
+        for (int j = 0; j < R; j++) small = small && (((v[j][nd.lhs].lo | v[j][nd.rhs].lo) >> 32) == 0);
+        const bool fast = __all_sync(0xffffffffu, small);
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const Val a = v[j][nd.lhs], b = v[j][nd.rhs];
+            if (fast) {
+                v[j][I].lo = (uint64_t)(uint32_t)a.lo * (uint64_t)(uint32_t)b.lo;
+                v[j][I].hi = 0;
+            } else {
+                const i128 r = mul_i64_i64((int64_t)a.lo, (int64_t)b.lo);
+                v[j][I].lo = lo64(r);
+                v[j][I].hi = hi64(r);
+            }
+            v[j][I].null = a.null || b.null;
+        }
+    } else if constexpr (nd.checked != 0 && nd.width == 8 && nd.adj_l == 0 && nd.adj_r == 0 && (nd.op == DOP_ADD || nd.op == DOP_SUB)) {
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const Val a = v[j][nd.lhs], b = v[j][nd.rhs];
+            const uint64_t x = a.lo, y = b.lo;
+            const uint64_t s = nd.op == DOP_ADD ? x + y : x - y;
+            // signed overflow: ADD when the operands agree in sign and the sum does not; SUB when they differ and the result left x's sign
+            const uint64_t o = nd.op == DOP_ADD ? ((x ^ s) & (y ^ s)) : ((x ^ y) & (x ^ s));
+            v[j][I].lo = s; // the value of a NULL is never read: consumers test .null first
+            v[j][I].hi = (int64_t)s >> 63;
+            v[j][I].null = a.null || b.null || ((int64_t)o < 0);
+        }
+    } else if constexpr (nd.checked != 0 && nd.op == DOP_MUL && nd.width == 16 && nd.adj_l == 0 && nd.adj_r == 0) {
+        bool small = true;
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const Val a = v[j][nd.lhs], b = v[j][nd.rhs];
+            small = small && (((a.lo | b.lo) >> 32) == 0) && ((a.hi | b.hi) == 0);
+        }
+        const bool fast = __all_sync(0xffffffffu, small);
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const Val a = v[j][nd.lhs], b = v[j][nd.rhs];
+            bool ov = false;
+            if (fast) {
+                v[j][I].lo = (uint64_t)(uint32_t)a.lo * (uint64_t)(uint32_t)b.lo;
+                v[j][I].hi = 0;
+            } else {
+                const Mul128Res m = mul_overflow128_cold(a.lo, a.hi, b.lo, b.hi);
+                v[j][I].lo = m.lo;
+                v[j][I].hi = m.hi;
+                ov = m.ov != 0;
+            }
+            v[j][I].null = a.null || b.null || ov;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const Val a = v[j][nd.lhs], b = v[j][nd.rhs];
+            i128 x = make_i128(a.lo, a.hi), y = make_i128(b.lo, b.hi), res = 0;
+            bool ov = false;
+            if constexpr (nd.checked != 0) {
+                if constexpr (nd.adj_l != 0) ov |= checked_binop<nd.width>(6, x, make_i128(rt.fl_lo, rt.fl_hi), &x);
+                if constexpr (nd.adj_r != 0) ov |= checked_binop<nd.width>(6, y, make_i128(rt.fr_lo, rt.fr_hi), &y);
                 if (!ov) ov = checked_binop<nd.width>(nd.op, x, y, &res);
                 if (ov) res = 0;
+            } else {
+                u128 ux = (u128)x, uy = (u128)y;
+                u128 ur = nd.op == DOP_ADD ? ux + uy : (nd.op == DOP_SUB ? ux - uy : ux * uy);
+                res = wrap_to<nd.width>((i128)ur);
             }
-        } else {
-            u128 ux = (u128)x, uy = (u128)y;
-            u128 ur = nd.op == DOP_ADD ? ux + uy : (nd.op == DOP_SUB ? ux - uy : ux * uy);
-            res = wrap_to<nd.width>((i128)ur);
+            v[j][I].lo = lo64(res);
+            v[j][I].hi = hi64(res);
+            v[j][I].null = a.null || b.null || ov;
         }
-        v[I].lo = lo64(res);
-        v[I].hi = hi64(res);
-        v[I].null = a.null || b.null || ov;
     }
 }
-template <class S, int... I>
-SRB_D void eval_static_all(const DProg& p, Val* v, const uint8_t* stage, int r, std::integer_sequence<int, I...>) {
-    (eval_static_node<S, I>(p, v, stage, r), ...);
+template <class S, int R, int... I>
+SRB_D void eval_static_all(const DProg& p, Val (&v)[R][S::N_NODES], const uint8_t* stage, int r0, std::integer_sequence<int, I...>) {
+    (eval_static_node<S, I, R>(p, v, stage, r0), ...);
 }
 
 
@@ -442,7 +481,8 @@ struct AccGeom {
     static constexpr int NR = n_reps<S>() > 0 ? n_reps<S>() : 1;
     static constexpr int LO_BYTES = NR * G * S::THREADS * 8; // [rep][group][thread] u64
     static constexpr int ROWS_BYTES = G * S::THREADS * 4;    // [group][thread] u32
-    static constexpr int BYTES = S::GMAX > 0 ? LO_BYTES + ROWS_BYTES : 0;
+    static constexpr int TRASH_BYTES = S::THREADS * 8;       // [thread] u64: where rows that do not count are steered
+    static constexpr int BYTES = S::GMAX > 0 ? LO_BYTES + ROWS_BYTES + TRASH_BYTES : 0;
 };
 template <class S>
 struct RareAcc {
@@ -450,51 +490,75 @@ struct RareAcc {
     uint32_t nulls[AccGeom<S>::G * AccGeom<S>::NR]; // selected rows whose argument was NULL
 };
 
+// old (64-bit accumulator word) + x (128-bit addend): the new word and what spills above bit 63, as one carry chain
+SRB_D void add_word_spill(uint64_t old, uint64_t xlo, uint64_t xhi, uint64_t& nw, uint64_t& spill) {
+    uint32_t n0, n1, d0, d1;
+    asm("add.cc.u32 %0, %4, %6;\n\t"
+        "addc.cc.u32 %1, %5, %7;\n\t"
+        "addc.cc.u32 %2, %8, 0;\n\t"
+        "addc.u32 %3, %9, 0;"
+        : "=r"(n0), "=r"(n1), "=r"(d0), "=r"(d1)
+        : "r"((uint32_t)old), "r"((uint32_t)(old >> 32)), "r"((uint32_t)xlo), "r"((uint32_t)(xlo >> 32)), "r"((uint32_t)xhi), "r"((uint32_t)(xhi >> 32)));
+    nw = ((uint64_t)n1 << 32) | n0;
+    spill = ((uint64_t)d1 << 32) | d0;
+}
+
+// One representative, one row. Branch-free: a row that does not count (filtered out, NULL argument) is steered to the
+// thread's trash word instead of being skipped, so the instruction stream is the same for every lane.
 template <class S, int A>
-SRB_D void acc_one(uint8_t* a, const Val* v, bool on, uint64_t* dh, bool* nl, uint64_t& any_hi, bool& any_null) {
+SRB_D void acc_one(uint8_t* a, uint8_t* trash, const Val* v, bool on, uint64_t* dh, uint64_t& row_spill, bool& any_null) {
     constexpr SAgg g = S::agg(A);
     if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
         constexpr int RI = rep_index<S>(A);
-        constexpr bool nullable = node_can_be_null<S>(g.arg);
         const Val& x = v[g.arg];
         bool take = on;
-        nl[RI] = false;
-        if constexpr (nullable) {
+        if constexpr (node_can_be_null<S>(g.arg)) {
             take = on && !x.null;
-            nl[RI] = on && x.null;
-            any_null = any_null || nl[RI];
+            any_null = any_null || (on && x.null);
         }
-        dh[RI] = 0;
-        if (take) {
-            uint64_t* slot = (uint64_t*)(a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8);
-            const uint64_t old = *slot, nw = old + x.lo;
-            *slot = nw;
-            dh[RI] = (uint64_t)x.hi + (nw < old ? 1ULL : 0ULL);
-        }
-        any_hi |= dh[RI];
+        uint64_t* slot = (uint64_t*)(take ? a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8 : trash);
+        uint64_t nw;
+        add_word_spill(*slot, x.lo, (uint64_t)x.hi, nw, dh[RI]);
+        *slot = nw;
+        row_spill |= dh[RI]; // meaningless for a trashed row: the caller masks it (or any_null already forces the rare path)
     }
 }
 template <class S, int A>
-SRB_D void acc_rare_one(RareAcc<S>& ra, int gid, const uint64_t* dh, const bool* nl) {
+SRB_D void acc_rare_one(RareAcc<S>& ra, int gid, const Val* v, bool on, const uint64_t* dh) {
     constexpr SAgg g = S::agg(A);
     if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
         constexpr int RI = rep_index<S>(A);
-        ra.hi[gid * AccGeom<S>::NR + RI] += dh[RI];
-        if constexpr (node_can_be_null<S>(g.arg)) ra.nulls[gid * AccGeom<S>::NR + RI] += nl[RI] ? 1u : 0u;
+        bool take = on;
+        if constexpr (node_can_be_null<S>(g.arg)) {
+            take = on && !v[g.arg].null;
+            ra.nulls[gid * AccGeom<S>::NR + RI] += (on && v[g.arg].null) ? 1u : 0u;
+        }
+        ra.hi[gid * AccGeom<S>::NR + RI] += take ? dh[RI] : 0ULL;
     }
 }
-// one row into group gid (0 <= gid < G; `on` false: the row does not count). All 32 lanes must call.
-template <class S, int... A>
-SRB_D void acc_update_all(RareAcc<S>& ra, uint8_t* acc_tid, uint8_t* rows_tid, const Val* v, bool on, int gid, std::integer_sequence<int, A...>) {
-    uint64_t dh[AccGeom<S>::NR];
-    bool nl[AccGeom<S>::NR];
-    uint64_t any_hi = 0;
+// the R rows of a tile into their groups (0 <= gid[j] < G; on[j] false: the row does not count). One vote covers the
+// spills and NULLs of all R rows. All 32 lanes must call.
+template <class S, int R, int... A>
+SRB_D void acc_update_rows(RareAcc<S>& ra, uint8_t* acc_tid, uint8_t* rows_tid, uint8_t* trash, const Val (&v)[R][S::N_NODES], const bool (&on)[R],
+                           const int (&gid)[R], std::integer_sequence<int, A...>) {
+    uint64_t dh[R][AccGeom<S>::NR];
+    uint64_t any_spill = 0;
     bool any_null = false;
-    uint8_t* a = acc_tid + (size_t)gid * (S::THREADS * 8);
-    (acc_one<S, A>(a, v, on, dh, nl, any_hi, any_null), ...);
-    if (on) *(uint32_t*)(rows_tid + (size_t)gid * (S::THREADS * 4)) += 1u;
-    if (__any_sync(0xffffffffu, any_hi != 0 || any_null)) (acc_rare_one<S, A>(ra, gid, dh, nl), ...);
+#pragma unroll
+    for (int j = 0; j < R; j++) {
+        uint8_t* a = acc_tid + (size_t)gid[j] * (S::THREADS * 8);
+        uint64_t row_spill = 0;
+        (acc_one<S, A>(a, trash, v[j], on[j], dh[j], row_spill, any_null), ...);
+        any_spill |= on[j] ? row_spill : 0ULL;
+        uint32_t* rc = (uint32_t*)(on[j] ? rows_tid + (size_t)gid[j] * (S::THREADS * 4) : trash);
+        *rc += 1u;
+    }
+    if (__any_sync(0xffffffffu, any_spill != 0 || any_null)) {
+#pragma unroll
+        for (int j = 0; j < R; j++) (acc_rare_one<S, A>(ra, gid[j], v[j], on[j], dh[j]), ...);
+    }
 }
+
 
 SRB_D uint64_t warp_sum_u64(uint64_t x) {
     for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
@@ -637,6 +701,62 @@ struct StaticCtr {
 
 SRB_D void mbar_arrive(uint64_t* bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory"); }
 
+// The CTA's group directory (shared memory): packed key -> accumulator bank + table slot. Entries below cnt are immutable.
+template <int G>
+struct GroupDir {
+    uint64_t lo[G], hi[G];
+    uint8_t* slot[G];
+    int cnt, lock;
+};
+template <int G>
+SRB_D bool dir_has(const GroupDir<G>* d, int c, uint64_t klo, uint64_t khi) {
+    bool present = false;
+    for (int q = 0; q < c; q++)
+        present = present || (((const volatile uint64_t*)d->lo)[q] == klo && ((const volatile uint64_t*)d->hi)[q] == khi);
+    return present;
+}
+// Rows of a warp whose group is not in the directory yet (need). One leader per distinct missing key of the warp takes
+// the directory lock and — only if the group is still absent — claims its table slot and publishes it, so the HBM table
+// sees one probe per (CTA, group) instead of one per row while the directory fills. Tries are bounded: a lane that gives
+// up leaves its rows to the global-table path, which is always correct. All 32 lanes call; returns 1 for a fresh table
+// insert by this lane. Out of line: it runs a handful of times per CTA.
+template <int G, int KEYLEN>
+static __device__ __noinline__ int dir_resolve(GroupDir<G>* d, uint8_t* slots, uint64_t mask, int slot_bytes, int key_words, uint64_t klo, uint64_t khi,
+                                               int seed, bool need) {
+    const unsigned need_mask = __ballot_sync(0xffffffffu, need);
+    const unsigned peers = __match_any_sync(0xffffffffu, klo ^ (khi * 0x9e3779b97f4a7c15ULL)) & need_mask;
+    int inserted = 0;
+    if (need && (peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0) {
+        for (int t = 0; t < 256; t++) {
+            const int c = *(volatile int*)&d->cnt;
+            if (c >= G || dir_has(d, c, klo, khi)) break;
+            if (atomicCAS(&d->lock, 0, 1) == 0) {
+                const int c2 = *(volatile int*)&d->cnt;
+                if (c2 < G && !dir_has(d, c2, klo, khi)) {
+                    const TableView tv{slots, mask, slot_bytes, key_words};
+                    PackedKey k{klo, khi, KEYLEN, false};
+                    bool fresh;
+                    uint8_t* sl = table_find_or_insert(tv, klo, khi, hash_packed_key_static<KEYLEN>(k, seed), &fresh);
+                    inserted = fresh ? 1 : 0;
+                    if (sl) {
+                        ((volatile uint64_t*)d->lo)[c2] = klo;
+                        ((volatile uint64_t*)d->hi)[c2] = khi;
+                        ((uint8_t* volatile*)d->slot)[c2] = sl;
+                        __threadfence_block();
+                        *(volatile int*)&d->cnt = c2 + 1;
+                    }
+                }
+                __threadfence_block();
+                atomicExch(&d->lock, 0);
+                break;
+            }
+            __nanosleep(64);
+        }
+    }
+    __syncwarp();
+    return inserted;
+}
+
 // One persistent CTA per SM: S::THREADS consumer threads plus one producer warp. The producer's elected lane keeps the
 // ring full (one bulk copy per column and tile, completing on full_bar[s]) and only it ever waits for a stage to drain
 // (empty_bar[s], one arrival per consumer warp). Consumer warps therefore never wait for each other: a warp that is
@@ -654,9 +774,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
     static_assert(THREADS % 32 == 0 && THREADS + 32 <= 1024 && (TILE * 1) % 16 == 0, "block / tile geometry");
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ uint64_t full_bar[ST_MAX_STAGES], empty_bar[ST_MAX_STAGES];
-    __shared__ uint64_t dir_lo[G], dir_hi[G];
-    __shared__ uint8_t* dir_slot[G];
-    __shared__ int dir_cnt, dir_lock;
+    __shared__ GroupDir<G> dir;
     const DProg& p = prog;
     using NodeSeq = std::make_integer_sequence<int, S::N_NODES>;
     using AggSeq = std::make_integer_sequence<int, S::N_AGGS>;
@@ -668,13 +786,14 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], THREADS / 32);
         }
-        dir_cnt = 0;
-        dir_lock = 0;
+        dir.cnt = 0;
+        dir.lock = 0;
         fence_barrier_init();
     }
     // this thread's private accumulator words start zeroed
     uint8_t* acc_tid = smem + sa.acc_off + tid * 8;
     uint8_t* rows_tid = smem + sa.acc_off + AccGeom<S>::LO_BYTES + tid * 4;
+    uint8_t* trash = smem + sa.acc_off + AccGeom<S>::LO_BYTES + AccGeom<S>::ROWS_BYTES + tid * 8;
     RareAcc<S> ra;
     if constexpr (S::GMAX > 0) {
         if (tid < THREADS) {
@@ -724,12 +843,12 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
             if constexpr (S::GMAX > 0 && S::N_KEYS > 0) {
                 // my_cnt steers warp votes below, so it must be ONE value per warp even if the lanes poll at different times
                 // (the minimum: every lane's own read saw at least that many published entries before it loads them)
-                const int c = (int)__reduce_min_sync(0xffffffffu, (unsigned)*(volatile int*)&dir_cnt);
+                const int c = (int)__reduce_min_sync(0xffffffffu, (unsigned)*(volatile int*)&dir.cnt);
                 if (c != my_cnt) {
 #pragma unroll
                     for (int q = 0; q < G; q++) {
-                        kd_lo[q] = ((volatile uint64_t*)dir_lo)[q];
-                        if constexpr (KW == 2) kd_hi[q] = ((volatile uint64_t*)dir_hi)[q];
+                        kd_lo[q] = ((volatile uint64_t*)dir.lo)[q];
+                        if constexpr (KW == 2) kd_hi[q] = ((volatile uint64_t*)dir.hi)[q];
                     }
                     my_cnt = c;
                 }
@@ -754,81 +873,66 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
             }
             if (__any_sync(0xffffffffu, any_pass)) {
                 Val v[R][S::N_NODES];
+                eval_static_all<S, R>(p, v, stage, tid, NodeSeq{});
+                if constexpr (S::N_KEYS == 0) {
+                    int gid[R];
 #pragma unroll
-                for (int j = 0; j < R; j++) eval_static_all<S>(p, v[j], stage, tid + j * THREADS, NodeSeq{});
+                    for (int j = 0; j < R; j++) gid[j] = 0;
+                    acc_update_rows<S, R>(ra, acc_tid, rows_tid, trash, v, pass, gid, AggSeq{});
+                } else {
+                    PackedKey k[R];
+                    bool miss[R]; // row j still has to reach its group
 #pragma unroll
-                for (int j = 0; j < R; j++) {
-                    if constexpr (S::N_KEYS == 0) {
-                        acc_update_all<S>(ra, acc_tid, rows_tid, v[j], pass[j], 0, AggSeq{});
-                    } else {
-                        const PackedKey k = pack_key_static<S>(v[j]);
-                        bool miss = pass[j]; // this row still has to reach its group
-                        if constexpr (S::GMAX > 0) {
-                            // descending: the lowest matching entry wins, and a match at or past my_cnt (a stale register) is discarded
-                            int gid = G;
+                    for (int j = 0; j < R; j++) {
+                        k[j] = pack_key_static<S>(v[j]);
+                        miss[j] = pass[j];
+                    }
+                    if constexpr (S::GMAX > 0) {
+                        int gid[R];
+                        bool hit[R], need_any = false;
+                        // descending: the lowest matching entry wins, and a match at or past my_cnt (a stale register) is discarded
+                        auto lookup = [&]() {
 #pragma unroll
-                            for (int q = G - 1; q >= 0; q--)
-                                if (kd_lo[q] == k.lo && (KW == 1 || kd_hi[q] == k.hi)) gid = q;
-                            bool hit = gid < my_cnt;
-                            if (my_cnt < G && __any_sync(0xffffffffu, pass[j] && !hit)) {
-                                // Some lane's group is not in the directory copy. One leader per distinct missing key of the warp
-                                // takes the directory lock and — only if the group is still absent — claims its table slot and
-                                // publishes it, so the HBM table sees one probe per (CTA, group) instead of one per row while the
-                                // directory fills. Then every lane refreshes its copy and looks again.
-                                const bool need = pass[j] && !hit;
-                                const unsigned need_mask = __ballot_sync(0xffffffffu, need);
-                                const unsigned peers = __match_any_sync(0xffffffffu, k.lo ^ (k.hi * 0x9e3779b97f4a7c15ULL)) & need_mask;
-                                if (need && (peers & ((1u << (tid & 31)) - 1u)) == 0) {
-                                    for (int t = 0; t < 256; t++) {
-                                        const int c = *(volatile int*)&dir_cnt;
-                                        bool present = false;
-                                        for (int q = 0; q < c; q++)
-                                            present = present || (((volatile uint64_t*)dir_lo)[q] == k.lo && ((volatile uint64_t*)dir_hi)[q] == k.hi);
-                                        if (present || c >= G) break;
-                                        if (atomicCAS(&dir_lock, 0, 1) == 0) {
-                                            const int c2 = *(volatile int*)&dir_cnt;
-                                            present = false;
-                                            for (int q = 0; q < c2; q++)
-                                                present = present || (((volatile uint64_t*)dir_lo)[q] == k.lo && ((volatile uint64_t*)dir_hi)[q] == k.hi);
-                                            if (!present && c2 < G) {
-                                                bool fresh;
-                                                uint8_t* sl = table_find_or_insert(tv, k.lo, k.hi, hash_packed_key_static<static_key_bytes<S>()>(k, p.phase_seed), &fresh);
-                                                inserted += fresh ? 1 : 0;
-                                                if (sl) {
-                                                    ((volatile uint64_t*)dir_lo)[c2] = k.lo;
-                                                    ((volatile uint64_t*)dir_hi)[c2] = k.hi;
-                                                    ((uint8_t* volatile*)dir_slot)[c2] = sl;
-                                                    __threadfence_block();
-                                                    *(volatile int*)&dir_cnt = c2 + 1;
-                                                }
-                                            }
-                                            __threadfence_block();
-                                            atomicExch(&dir_lock, 0);
-                                            break;
-                                        }
-                                        __nanosleep(64);
-                                    }
-                                }
-                                __syncwarp();
-                                my_cnt = (int)__reduce_min_sync(0xffffffffu, (unsigned)*(volatile int*)&dir_cnt);
-#pragma unroll
-                                for (int q = 0; q < G; q++) {
-                                    kd_lo[q] = ((volatile uint64_t*)dir_lo)[q];
-                                    if constexpr (KW == 2) kd_hi[q] = ((volatile uint64_t*)dir_hi)[q];
-                                }
-                                gid = G;
+                            for (int j = 0; j < R; j++) {
+                                gid[j] = G;
 #pragma unroll
                                 for (int q = G - 1; q >= 0; q--)
-                                    if (kd_lo[q] == k.lo && (KW == 1 || kd_hi[q] == k.hi)) gid = q;
-                                hit = gid < my_cnt;
+                                    if (kd_lo[q] == k[j].lo && (KW == 1 || kd_hi[q] == k[j].hi)) gid[j] = q;
+                                hit[j] = gid[j] < my_cnt;
                             }
-                            acc_update_all<S>(ra, acc_tid, rows_tid, v[j], pass[j] && hit, hit ? gid : 0, AggSeq{});
-                            miss = pass[j] && !hit;
+                        };
+                        lookup();
+#pragma unroll
+                        for (int j = 0; j < R; j++) need_any = need_any || (pass[j] && !hit[j]);
+                        if (my_cnt < G && __any_sync(0xffffffffu, need_any)) {
+                            // some row's group is not in the directory copy: publish it (dir_resolve), refresh the copy, look again
+#pragma unroll
+                            for (int j = 0; j < R; j++)
+                                inserted += dir_resolve<G, static_key_bytes<S>()>(&dir, tv.slots, tv.mask, tv.slot_bytes, tv.key_words, k[j].lo, k[j].hi,
+                                                                                  p.phase_seed, pass[j] && !hit[j]);
+                            my_cnt = (int)__reduce_min_sync(0xffffffffu, (unsigned)*(volatile int*)&dir.cnt);
+#pragma unroll
+                            for (int q = 0; q < G; q++) {
+                                kd_lo[q] = ((volatile uint64_t*)dir.lo)[q];
+                                if constexpr (KW == 2) kd_hi[q] = ((volatile uint64_t*)dir.hi)[q];
+                            }
+                            lookup();
                         }
-                        if (miss) {
+                        bool on[R];
+#pragma unroll
+                        for (int j = 0; j < R; j++) {
+                            on[j] = pass[j] && hit[j];
+                            miss[j] = pass[j] && !hit[j];
+                            if (!hit[j]) gid[j] = 0;
+                        }
+                        acc_update_rows<S, R>(ra, acc_tid, rows_tid, trash, v, on, gid, AggSeq{});
+                    }
+#pragma unroll
+                    for (int j = 0; j < R; j++) {
+                        if (miss[j]) {
                             // global-table path: the directory is full of other groups (or the shape keeps none)
                             bool fresh;
-                            uint8_t* slot = table_find_or_insert(tv, k.lo, k.hi, hash_packed_key_static<static_key_bytes<S>()>(k, p.phase_seed), &fresh);
+                            uint8_t* slot = table_find_or_insert(tv, k[j].lo, k[j].hi, hash_packed_key_static<static_key_bytes<S>()>(k[j], p.phase_seed), &fresh);
                             inserted += fresh ? 1 : 0;
                             if (!slot) {
                                 const int64_t i = tile * TILE + tid + j * THREADS;
@@ -853,11 +957,11 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
     if constexpr (S::GMAX > 0) {
         static_assert(Flusher<S>::STASH_BYTES <= 32 * 1024, "stash must fit the first stage");
         uint64_t* stash = (uint64_t*)smem;
-        const int cnt = S::N_KEYS == 0 ? 1 : dir_cnt;
+        const int cnt = S::N_KEYS == 0 ? 1 : dir.cnt;
         if (tid < THREADS)
             for (int q = 0; q < cnt; q++) Flusher<S>::stash(ra, acc_tid, rows_tid, q, stash, AggSeq{});
         __syncthreads();
-        if (tid < cnt) Flusher<S>::fold(p, stash, tid, S::N_KEYS == 0 ? tv.slots : dir_slot[tid], AggSeq{});
+        if (tid < cnt) Flusher<S>::fold(p, stash, tid, S::N_KEYS == 0 ? tv.slots : dir.slot[tid], AggSeq{});
     }
     if (tid >= THREADS) return;
     selected = warp_sum_u64(selected);
