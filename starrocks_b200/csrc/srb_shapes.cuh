@@ -61,7 +61,7 @@ struct ShapeSumMulFast {
 //   sum(qty), sum(ext), sum(ext*(1-disc)), sum(ext*(1-disc)*(1+tax)), avg(qty), avg(ext), avg(disc), count(*)
 struct ShapeQ1Dict {
     static constexpr const char* name = "q1 (2 int keys, 8 decimal aggregates)";
-    static constexpr int N_NODES = 14, N_AGGS = 8, N_KEYS = 2, GMAX = 4, THREADS = 512, ROWS = 2;
+    static constexpr int N_NODES = 14, N_AGGS = 8, N_KEYS = 2, GMAX = 4, THREADS = 512, ROWS = 2; // 256 x 4 measured slower (IPC 1.35 vs 2.1)
     static constexpr SNode node(int i) {
         constexpr SNode t[N_NODES] = {
                 {DOP_LOAD, 8, -1, -1, 0, 0, 0},    // 0 l_quantity
@@ -339,14 +339,22 @@ SRB_D void eval_static_node(const DProg& p, Val (&v)[R][S::N_NODES], const uint8
             v[j][I].null = false;
         }
     } else if constexpr (nd.op == DOP_CAST) {
-        const i128 f = make_i128(rt.lit_lo, rt.lit_hi);
+        const bool rescale = !(rt.lit_lo == 1 && rt.lit_hi == 0); // uniform: a cast between equal scales multiplies by 1
 #pragma unroll
         for (int j = 0; j < R; j++) {
             const Val a = v[j][nd.lhs];
             i128 x = make_i128(a.lo, a.hi), res = x;
             bool ov = false;
             if constexpr (nd.checked != 0) {
-                if (f != 1) ov = checked_binop<nd.width>(6, x, f, &res);
+                if (rescale) {
+                    if constexpr (nd.width == 16) {
+                        const Mul128Res m = mul_overflow128_cold(a.lo, a.hi, rt.lit_lo, rt.lit_hi);
+                        res = make_i128(m.lo, m.hi);
+                        ov = m.ov != 0;
+                    } else {
+                        ov = checked_binop<nd.width>(6, x, make_i128(rt.lit_lo, rt.lit_hi), &res);
+                    }
+                }
                 if constexpr (nd.width == 8) ov = ov || !fits<8>(x);
                 if constexpr (nd.width == 4) ov = ov || !fits<4>(x);
             }
@@ -757,6 +765,50 @@ static __device__ __noinline__ int dir_resolve(GroupDir<G>* d, uint8_t* slots, u
     return inserted;
 }
 
+// The per-row global-table update of a low-cardinality shape, out of line (it only runs for groups that found no room in
+// the directory). The aggregate arguments travel by value; returns bit 0 = fresh insert, bit 1 = no slot (defer the row).
+template <class S>
+struct AggArgs {
+    uint64_t lo[S::N_AGGS];
+    int64_t hi[S::N_AGGS];
+    uint32_t nulls; // bit a: the argument of aggregate a is NULL
+};
+template <class S, int... A>
+SRB_D AggArgs<S> pack_agg_args(const Val* v, std::integer_sequence<int, A...>) {
+    AggArgs<S> r;
+    r.nulls = 0;
+    ((r.lo[A] = S::agg(A).arg >= 0 ? v[S::agg(A).arg < 0 ? 0 : S::agg(A).arg].lo : 0,
+      r.hi[A] = S::agg(A).arg >= 0 ? v[S::agg(A).arg < 0 ? 0 : S::agg(A).arg].hi : 0,
+      r.nulls |= (S::agg(A).arg >= 0 && v[S::agg(A).arg < 0 ? 0 : S::agg(A).arg].null) ? (1u << A) : 0u),
+     ...);
+    return r;
+}
+template <class S, int A>
+SRB_D void row_update_args_one(const DProg& p, uint8_t* slot, const AggArgs<S>& x) {
+    constexpr SAgg g = S::agg(A);
+    const DAgg& rt = p.aggs[A];
+    const bool null = (x.nulls >> A) & 1u;
+    if constexpr (g.fn == FN_COUNT) {
+        if (!null) atomicAdd((unsigned long long*)(slot + rt.off_n), 1ULL);
+    } else {
+        if (!null) {
+            atomic_add128(slot, rt.off_lo, rt.off_hi, x.lo[A], (uint64_t)x.hi[A]);
+            if (rt.off_n >= 0) atomicAdd((unsigned long long*)(slot + rt.off_n), 1ULL);
+        }
+    }
+}
+template <class S, int... A>
+static __device__ __noinline__ int global_row_cold(const DProg* pp, uint8_t* slots, uint64_t mask, int slot_bytes, int key_words, uint64_t klo, uint64_t khi,
+                                                   AggArgs<S> x, std::integer_sequence<int, A...>) {
+    const TableView tv{slots, mask, slot_bytes, key_words};
+    const PackedKey k{klo, khi, static_key_bytes<S>(), false};
+    bool fresh;
+    uint8_t* slot = table_find_or_insert(tv, klo, khi, hash_packed_key_static<static_key_bytes<S>()>(k, pp->phase_seed), &fresh);
+    if (!slot) return 2;
+    (row_update_args_one<S, A>(*pp, slot, x), ...);
+    return fresh ? 1 : 0;
+}
+
 // One persistent CTA per SM: S::THREADS consumer threads plus one producer warp. The producer's elected lane keeps the
 // ring full (one bulk copy per column and tile, completing on full_bar[s]) and only it ever waits for a stage to drain
 // (empty_bar[s], one arrival per consumer warp). Consumer warps therefore never wait for each other: a warp that is
@@ -810,7 +862,8 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
     }
     __syncthreads();
 
-    unsigned long long selected = 0, deferred = 0, inserted = 0;
+    uint32_t selected32 = 0; // a thread sees well under 2^32 rows of one launch (a launch covers at most 2^27 rows)
+    unsigned long long deferred = 0, inserted = 0;
     if (tid >= THREADS) {
         // ---- producer warp ----
         if (tid == THREADS) {
@@ -840,7 +893,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
         int s = 0;
         uint32_t parity = 0;
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-            if constexpr (S::GMAX > 0 && S::N_KEYS > 0) {
+            if (S::GMAX > 0 && S::N_KEYS > 0 && my_cnt < G) { // a full directory never changes again
                 // my_cnt steers warp votes below, so it must be ONE value per warp even if the lanes poll at different times
                 // (the minimum: every lane's own read saw at least that many published entries before it loads them)
                 const int c = (int)__reduce_min_sync(0xffffffffu, (unsigned)*(volatile int*)&dir.cnt);
@@ -868,7 +921,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
             bool any_pass = false;
 #pragma unroll
             for (int j = 0; j < R; j++) {
-                selected += pass[j] ? 1 : 0;
+                selected32 += pass[j] ? 1u : 0u;
                 any_pass = any_pass || pass[j];
             }
             if (__any_sync(0xffffffffu, any_pass)) {
@@ -931,15 +984,22 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                     for (int j = 0; j < R; j++) {
                         if (miss[j]) {
                             // global-table path: the directory is full of other groups (or the shape keeps none)
-                            bool fresh;
-                            uint8_t* slot = table_find_or_insert(tv, k[j].lo, k[j].hi, hash_packed_key_static<static_key_bytes<S>()>(k[j], p.phase_seed), &fresh);
-                            inserted += fresh ? 1 : 0;
-                            if (!slot) {
+                            int rc;
+                            if constexpr (S::GMAX > 0) { // the exception here: keep its code out of the loop body
+                                rc = global_row_cold<S>(&prog, tv.slots, tv.mask, tv.slot_bytes, tv.key_words, k[j].lo, k[j].hi, pack_agg_args<S>(v[j], AggSeq{}),
+                                                        AggSeq{});
+                            } else {
+                                bool fresh;
+                                uint8_t* slot =
+                                        table_find_or_insert(tv, k[j].lo, k[j].hi, hash_packed_key_static<static_key_bytes<S>()>(k[j], p.phase_seed), &fresh);
+                                rc = (fresh ? 1 : 0) | (slot ? 0 : 2);
+                                if (slot) row_update_global<S>(p, slot, v[j], AggSeq{});
+                            }
+                            inserted += rc & 1;
+                            if (rc & 2) {
                                 const int64_t i = tile * TILE + tid + j * THREADS;
                                 atomicOr(&defer_out[i >> 5], 1u << (i & 31));
                                 deferred++;
-                            } else {
-                                row_update_global<S>(p, slot, v[j], AggSeq{});
                             }
                         }
                     }
@@ -964,7 +1024,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
         if (tid < cnt) Flusher<S>::fold(p, stash, tid, S::N_KEYS == 0 ? tv.slots : dir.slot[tid], AggSeq{});
     }
     if (tid >= THREADS) return;
-    selected = warp_sum_u64(selected);
+    const unsigned long long selected = warp_sum_u64(selected32);
     deferred = warp_sum_u64(deferred);
     inserted = warp_sum_u64(inserted);
     if ((tid & 31) == 0) {
