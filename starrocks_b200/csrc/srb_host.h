@@ -102,7 +102,59 @@ struct srb_ctx {
         pool.clear();
         pool_bytes = 0;
     }
-    ~srb_ctx() { pool_clear(); }
+    // idle streams and events of closed operators, reused by the next operator (a returned stream has been synchronised)
+    std::vector<cudaStream_t> idle_streams;
+    std::vector<cudaEvent_t> idle_events, idle_events_notiming;
+    cudaStream_t take_stream() {
+        {
+            std::lock_guard<std::mutex> g(pool_mu);
+            if (!idle_streams.empty()) {
+                cudaStream_t s = idle_streams.back();
+                idle_streams.pop_back();
+                return s;
+            }
+        }
+        cudaStream_t s = nullptr;
+        if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        return s;
+    }
+    void give_stream(cudaStream_t s) {
+        if (!s) return;
+        std::lock_guard<std::mutex> g(pool_mu);
+        if (idle_streams.size() < 64)
+            idle_streams.push_back(s);
+        else
+            cudaStreamDestroy(s);
+    }
+    cudaEvent_t take_event(bool timing) {
+        {
+            std::lock_guard<std::mutex> g(pool_mu);
+            auto& v = timing ? idle_events : idle_events_notiming;
+            if (!v.empty()) {
+                cudaEvent_t e = v.back();
+                v.pop_back();
+                return e;
+            }
+        }
+        cudaEvent_t e = nullptr;
+        if (cudaEventCreateWithFlags(&e, timing ? cudaEventDefault : cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        return e;
+    }
+    void give_event(cudaEvent_t e, bool timing) {
+        if (!e) return;
+        std::lock_guard<std::mutex> g(pool_mu);
+        auto& v = timing ? idle_events : idle_events_notiming;
+        if (v.size() < 256)
+            v.push_back(e);
+        else
+            cudaEventDestroy(e);
+    }
+    ~srb_ctx() {
+        pool_clear();
+        for (auto s : idle_streams) cudaStreamDestroy(s);
+        for (auto e : idle_events) cudaEventDestroy(e);
+        for (auto e : idle_events_notiming) cudaEventDestroy(e);
+    }
 };
 
 namespace srb {
@@ -159,21 +211,61 @@ struct DevBuf {
     }
 };
 
+// Small pinned buffers (counters, totals) are recycled process-wide: cudaMallocHost / cudaFreeHost cost about a
+// millisecond each, which is as long as a whole kernel of a short pipeline. Large ones go straight to the driver.
+struct PinnedPool {
+    static constexpr size_t MAX_POOLED = (size_t)1 << 20, MAX_TOTAL = (size_t)64 << 20;
+    std::mutex mu;
+    std::multimap<size_t, void*> free_;
+    size_t total = 0;
+    static PinnedPool& get() {
+        static PinnedPool* g = new PinnedPool(); // never destroyed: buffers may outlive static destruction order
+        return *g;
+    }
+    static size_t round_size(size_t n) {
+        size_t r = 256;
+        while (r < n) r <<= 1;
+        return r;
+    }
+    void* take(size_t rounded) {
+        std::lock_guard<std::mutex> g(mu);
+        auto it = free_.find(rounded);
+        if (it == free_.end()) return nullptr;
+        void* p = it->second;
+        free_.erase(it);
+        total -= rounded;
+        return p;
+    }
+    bool give(size_t rounded, void* p) {
+        std::lock_guard<std::mutex> g(mu);
+        if (rounded > MAX_POOLED || total + rounded > MAX_TOTAL) return false;
+        free_.emplace(rounded, p);
+        total += rounded;
+        return true;
+    }
+};
+
 struct PinnedBuf {
     void* p = nullptr;
     size_t bytes = 0;
     PinnedBuf() = default;
     PinnedBuf(const PinnedBuf&) = delete;
     PinnedBuf& operator=(const PinnedBuf&) = delete;
-    ~PinnedBuf() {
-        if (p) cudaFreeHost(p);
+    ~PinnedBuf() { release(); }
+    void release() {
+        if (p && !PinnedPool::get().give(bytes, p)) cudaFreeHost(p);
+        p = nullptr;
+        bytes = 0;
     }
     void ensure(size_t n) {
         if (n <= bytes && p) return;
-        if (p) cudaFreeHost(p);
-        p = nullptr;
+        release();
         if (n == 0) n = 16;
-        SRB_CUDA(cudaMallocHost(&p, n));
+        if (n <= PinnedPool::MAX_POOLED) {
+            n = PinnedPool::round_size(n);
+            p = PinnedPool::get().take(n);
+        }
+        if (!p) SRB_CUDA(cudaMallocHost(&p, n));
         bytes = n;
     }
     template <typename T>
@@ -190,9 +282,15 @@ struct srb_op {
     cudaStream_t stream = nullptr;
     bool finishing = false, finished = false, cancelled = false;
     int64_t rows_in = 0, rows_selected = 0, launches = 0;
-    explicit srb_op(srb_ctx* c) : ctx(c) { SRB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking)); }
+    explicit srb_op(srb_ctx* c) : ctx(c) {
+        stream = c->take_stream();
+        if (!stream) throw srb::Error(SRB_INTERNAL_ERROR, "cudaStreamCreate failed");
+    }
     virtual ~srb_op() {
-        if (stream) cudaStreamDestroy(stream);
+        if (stream) {
+            cudaStreamSynchronize(stream);
+            ctx->give_stream(stream);
+        }
     }
     virtual void push_chunk(const srb_chunk* ch) = 0;
     virtual void set_finishing() = 0;

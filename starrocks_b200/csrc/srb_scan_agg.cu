@@ -446,19 +446,20 @@ public:
         filter_only_ = plan_.aggs.empty() && plan_.key_nodes.empty();
         staging_rows_ = c->cfg.staging_rows > 0 ? c->cfg.staging_rows : (int64_t)4 << 20;
         chunk_size_ = c->cfg.chunk_size > 0 ? c->cfg.chunk_size : 4096;
-        SRB_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
         ctr_dev_.ensure(c, sizeof(Counters));
         ctr_host_.ensure(sizeof(Counters));
         SRB_CUDA(cudaMemsetAsync(ctr_dev_.p, 0, sizeof(Counters), stream));
     }
     ~ScanAggOp() override {
         cudaStreamSynchronize(stream);
-        if (copy_stream_) cudaStreamDestroy(copy_stream_);
-        for (auto& s : stage_)
-            if (s.copied) cudaEventDestroy(s.copied);
-        if (kernel_done_) cudaEventDestroy(kernel_done_);
-        if (ev0_) cudaEventDestroy(ev0_);
-        if (ev1_) cudaEventDestroy(ev1_);
+        if (copy_stream_) {
+            cudaStreamSynchronize(copy_stream_);
+            ctx->give_stream(copy_stream_);
+        }
+        for (auto& s : stage_) ctx->give_event(s.copied, false);
+        ctx->give_event(kernel_done_, false);
+        ctx->give_event(ev0_, true);
+        ctx->give_event(ev1_, true);
     }
 
     void push_chunk(const srb_chunk* ch) override {
@@ -735,8 +736,9 @@ private:
         int64_t covered = 0;
         Counters* dc = ctr_dev_.as<Counters>();
         if (!ev0_) {
-            SRB_CUDA(cudaEventCreate(&ev0_));
-            SRB_CUDA(cudaEventCreate(&ev1_));
+            ev0_ = ctx->take_event(true);
+            ev1_ = ctx->take_event(true);
+            if (!ev0_ || !ev1_) throw Error(SRB_INTERNAL_ERROR, "cudaEventCreate failed");
         }
         SRB_CUDA(cudaEventRecord(ev0_, stream)); // device time of the main kernel(s) of this batch, read in check_batch
         if (shape_ >= 0 && !defer_in && !force_generic_) {
@@ -829,7 +831,8 @@ private:
         }
     }
     void begin_stage(Stage& st) {
-        if (!st.copied) SRB_CUDA(cudaEventCreateWithFlags(&st.copied, cudaEventDisableTiming));
+        if (!copy_stream_ && !(copy_stream_ = ctx->take_stream())) throw Error(SRB_INTERNAL_ERROR, "cudaStreamCreate failed");
+        if (!st.copied && !(st.copied = ctx->take_event(false))) throw Error(SRB_INTERNAL_ERROR, "cudaEventCreate failed");
         for (size_t i = 0; i < L_.cols.size(); i++) {
             int w = L_.prog.cols[i].width;
             if (w)
