@@ -243,6 +243,16 @@ def main():
         peak = float(peaks.get("hbm_gbs", 6650.0))
         per_batch_rows = rows * args.steps / max(1, batches)
         achieved = w["bytes_per_row"] * per_batch_rows / (kernel_s_max / max(1, batches)) / 1e9 if kernel_s_max > 0 else 0.0
+        # DRAM bytes per launch from the committed `ncu --set full` capture of this kernel (profiles/traffic.json, written by
+        # tools/ncu_summary.py): measured bytes per row of the captured launch x the rows of an average launch here
+        traffic, traffic_src = None, None
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.query)
+            if tj and tj.get("rows_per_launch"):
+                traffic = tj["dram_bytes_per_launch"] / tj["rows_per_launch"] * per_batch_rows
+                traffic_src = f"{tj['report']}: {tj['dram_bytes_per_launch'] / tj['rows_per_launch']:.2f} B/row x rows per launch"
+        except Exception:
+            pass
         result = {
             "metric": f"TPC-H SF100 {args.query.upper()} rows/s" if args.query != "highcard" else "high-cardinality GROUP BY rows/s",
             "value": rows * world * args.steps / dt_max, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -253,7 +263,7 @@ def main():
             "scan_gb_per_s": rows * world * args.steps * w["bytes_per_row"] / dt_max / 1e9,
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None,
-                         "traffic": None, "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650",
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650",
                          "launch": f"{int(per_batch_rows)} rows x {w['bytes_per_row']} B per launch, {kernel_s_max / max(1, batches) * 1e3:.3f} ms avg (CUDA events on the op stream)"},
             "clocks": sampler.result(),
             "result_rows": n_out,
