@@ -21,6 +21,7 @@
 #include "srb_lower.h"
 #include "srb_rowpipe.cuh"
 #include "srb_shapes.cuh"
+#include "srb_hcpart.cuh"
 
 namespace srb {
 
@@ -720,7 +721,59 @@ private:
         return (int)std::max<int64_t>(1, std::min(blocks, maxb));
     }
 
+    // ---- L2-blocked high-cardinality path (srb_hcpart.cuh) ----------------------------------------------------------------
+    // worth it when the table is far larger than L2 and the batch is large enough to amortise three extra launches
+    bool hc_partition_applies(int64_t n) const {
+        const DProg& P = L_.prog;
+        return shape_ == 2 && !force_generic_ && !no_partition_ && P.n_preds == 0 && P.n_cols == 2 && P.nodes[0].col != P.nodes[1].col &&
+               (size_t)cap_ * (size_t)P.slot_bytes >= ((size_t)256 << 20) && cap_ >= ((uint64_t)1 << 16) && n >= ((int64_t)1 << 22);
+    }
+    void hc_partition(const ColBind* cols, int64_t off, int64_t n) {
+        const DProg& P = L_.prog;
+        const int kc = P.nodes[0].col, vc = P.nodes[1].col;
+        hc_k_.ensure(ctx, (size_t)n * 8);
+        hc_v_.ensure(ctx, (size_t)n * 8);
+        if (!hc_ctr_.p) {
+            hc_ctr_.ensure(ctx, 2 * HC_PARTS * sizeof(unsigned long long));
+            SRB_CUDA(cudaMemsetAsync(hc_ctr_.p, 0, 2 * HC_PARTS * sizeof(unsigned long long), stream));
+        }
+        unsigned long long* hist = hc_ctr_.as<unsigned long long>();
+        unsigned long long* cursor = hist + HC_PARTS;
+        int log2cap = 0;
+        while (((uint64_t)1 << log2cap) < cap_) log2cap++;
+        const int shift = log2cap - HC_PBITS;
+        const uint64_t* keys = (const uint64_t*)cols[kc].data + off;
+        const uint64_t* vals = (const uint64_t*)cols[vc].data + off;
+        static bool configured = false;
+        if (!configured) {
+            cudaFuncSetAttribute(k_hc_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HcSmem));
+            configured = true;
+        }
+        k_hc_hist<<<ctx->n_sms * 2, 1024, 0, stream>>>(keys, n, P.phase_seed, cap_ - 1, shift, hist);
+        k_hc_scan<<<1, HC_PARTS, 0, stream>>>(hist, cursor);
+        k_hc_scatter<<<ctx->n_sms, HC_THREADS, sizeof(HcSmem), stream>>>(keys, vals, n, P.phase_seed, cap_ - 1, shift, cursor, hc_k_.as<uint64_t>(),
+                                                                        hc_v_.as<uint64_t>());
+        launches += 3;
+        for (int i = 0; i < P.n_cols; i++) hc_cols_[i] = cols[i];
+        hc_cols_[kc].data = hc_k_.p;
+        hc_cols_[vc].data = hc_v_.p;
+    }
+
     void launch_batch(const ColBind* cols, int64_t off, int64_t n, const uint32_t* defer_in = nullptr) {
+        if (!ev0_) {
+            ev0_ = ctx->take_event(true);
+            ev1_ = ctx->take_event(true);
+            if (!ev0_ || !ev1_) throw Error(SRB_INTERNAL_ERROR, "cudaEventCreate failed");
+        }
+        SRB_CUDA(cudaEventRecord(ev0_, stream)); // device time of this batch's kernels, read in check_batch
+        if (!defer_in) {
+            batch_partitioned_ = hc_partition_applies(n);
+            if (batch_partitioned_) hc_partition(cols, off, n);
+        }
+        if (batch_partitioned_) { // the batch (and a replay of its deferred rows) reads the permuted copy
+            cols = hc_cols_;
+            off = 0;
+        }
         bind_prog(cols);
         if (L_.prog.n_keys) {
             size_t words = (size_t)((std::min<int64_t>(n, BATCH) + 31) / 32);
@@ -735,12 +788,6 @@ private:
         // recognised shapes run the TMA-staged static kernel over the whole tiles; the generic kernel takes the rest
         int64_t covered = 0;
         Counters* dc = ctr_dev_.as<Counters>();
-        if (!ev0_) {
-            ev0_ = ctx->take_event(true);
-            ev1_ = ctx->take_event(true);
-            if (!ev0_ || !ev1_) throw Error(SRB_INTERNAL_ERROR, "cudaEventCreate failed");
-        }
-        SRB_CUDA(cudaEventRecord(ev0_, stream)); // device time of the main kernel(s) of this batch, read in check_batch
         if (shape_ >= 0 && !defer_in && !force_generic_) {
             covered = launch_static_shape(shape_, L_.prog, tv, off, n, dout, &dc->rows_selected, &dc->deferred, &dc->inserted, ctx->n_sms, stream);
             if (covered) {
@@ -1132,6 +1179,10 @@ private:
     bool lowered_ = false, filter_only_ = false;
     int shape_ = -1;
     bool force_generic_ = getenv("SRB_FORCE_GENERIC") != nullptr; // test hook: compare the two kernel families
+    bool no_partition_ = getenv("SRB_NO_PARTITION") != nullptr;   // test / measurement hook: direct table updates for every batch
+    DevBuf hc_k_, hc_v_, hc_ctr_;                                 // permuted (key, value) copy of the current batch + its 2 x 256 counters
+    ColBind hc_cols_[MAX_COLS];
+    bool batch_partitioned_ = false;
     int64_t staging_rows_, chunk_size_;
     cudaStream_t copy_stream_ = nullptr;
     cudaEvent_t kernel_done_ = nullptr, ev0_ = nullptr, ev1_ = nullptr;

@@ -435,6 +435,33 @@ def test_highcard_pipeline(ctx, oracle, n, nk):
     _both_kernel_families(ctx, oracle, lambda: Q.highcard_plan(group_hint=nk), ch)
 
 
+def test_highcard_l2_blocked_partition_path(ctx, oracle, monkeypatch):
+    # a table far larger than L2 (2^24 slots x 32 B = 512 MB) and a device batch >= 4 Mi rows take the partition-then-aggregate
+    # path (srb_hcpart.cuh; the reference's answer to the same wall is its two-level maps, agg_hash_map.h:92-98)
+    from starrocks_b200 import ops
+    n, nk = 6_000_000, 5_000_000
+    ch = T.host_chunk("highcard", 0, n, ["k", "v"], n_keys=nk)
+    want = K.chunk_rows(oracle.scan_agg(Q.highcard_plan(), ch))
+    dch, ptrs = ctx.device_chunk(ch)
+    try:
+        launches = {}
+        for mode in ("partitioned", "direct"):
+            if mode == "direct":
+                monkeypatch.setenv("SRB_NO_PARTITION", "1")
+            op = ops.ScanAggOperator(ctx, Q.highcard_plan(group_hint=nk))
+            op.push_chunk(dch)
+            op.set_finishing()
+            got = K.chunk_rows(op.pull_all())
+            launches[mode] = op.counters()["kernel_launches"]
+            op.close()
+            assert rows_equal(got, want), mode
+        assert launches["partitioned"] == launches["direct"] + 3  # histogram, scan, scatter
+    finally:
+        monkeypatch.delenv("SRB_NO_PARTITION", raising=False)
+        for p in ptrs:
+            ctx.device_free(p)
+
+
 def test_host_chunks_of_4096_rows_like_the_pipeline_driver(ctx, oracle):
     # pipeline_driver.cpp:345-351: chunks of <= chunk_size rows; results must not depend on the chunking
     ch = T.host_chunk("lineitem", 99, 123457, T.LINEITEM_Q1)
