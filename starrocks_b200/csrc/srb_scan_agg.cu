@@ -214,20 +214,55 @@ SRB_D void store_w(void* base, int64_t row, int w, uint64_t lo, uint64_t hi) {
     }
 }
 
-__global__ void k_emit(const __grid_constant__ DProg prog, const uint8_t* __restrict__ slots, uint64_t cap, const __grid_constant__ EmitArgs ea,
-                       Counters* __restrict__ ctr) {
+SRB_D void emit_row(const DProg& p, const uint8_t* s, const EmitArgs& ea, int64_t row);
+
+// One output position per occupied slot. A block takes 8 x 256 slots at a time, counts its occupied ones, scans the
+// counts and reserves the block's output range with ONE atomic (a ticket per warp made the single counter the bottleneck
+// of a 10^8-group emit).
+constexpr int EMIT_ROWS = 8;
+__global__ void __launch_bounds__(256) k_emit(const __grid_constant__ DProg prog, const uint8_t* __restrict__ slots, uint64_t cap,
+                                              const __grid_constant__ EmitArgs ea, Counters* __restrict__ ctr) {
     const DProg& p = prog;
     const int sb = p.slot_bytes;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < cap; i += (uint64_t)gridDim.x * blockDim.x) {
-        const uint8_t* s = slots + i * sb;
-        if (((*(const uint64_t*)s) & 3ULL) != SLOT_READY) continue;
-        // warp-aggregated ticket
-        unsigned m = __activemask();
-        int leader = __ffs(m) - 1, lane = threadIdx.x & 31;
-        unsigned long long basepos = 0;
-        if (lane == leader) basepos = atomicAdd(&ctr->emitted, (unsigned long long)__popc(m));
-        basepos = __shfl_sync(m, basepos, leader);
-        int64_t row = (int64_t)(basepos + __popc(m & ((1u << lane) - 1)));
+    __shared__ unsigned int warp_tot[8];
+    __shared__ unsigned long long block_base;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint64_t chunk = (uint64_t)EMIT_ROWS * 256;
+    for (uint64_t c0 = (uint64_t)blockIdx.x * chunk; c0 < cap; c0 += (uint64_t)gridDim.x * chunk) {
+        unsigned int ready = 0;
+#pragma unroll
+        for (int r = 0; r < EMIT_ROWS; r++) {
+            const uint64_t i = c0 + (uint64_t)r * 256 + tid;
+            if (i < cap && ((*(const uint64_t*)(slots + i * sb)) & 3ULL) == SLOT_READY) ready |= 1u << r;
+        }
+        const unsigned int mine = __popc(ready);
+        unsigned int incl = mine;
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int y = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        if (lane == 31) warp_tot[wid] = incl;
+        __syncthreads();
+        if (tid == 0) {
+            unsigned int t = 0;
+            for (int w = 0; w < 8; w++) {
+                const unsigned int x = warp_tot[w];
+                warp_tot[w] = t;
+                t += x;
+            }
+            block_base = t ? atomicAdd(&ctr->emitted, (unsigned long long)t) : 0ULL;
+        }
+        __syncthreads();
+        int64_t row = (int64_t)(block_base + warp_tot[wid] + (incl - mine));
+#pragma unroll
+        for (int r = 0; r < EMIT_ROWS; r++)
+            if (ready & (1u << r)) emit_row(p, slots + (c0 + (uint64_t)r * 256 + tid) * sb, ea, row++);
+        __syncthreads(); // warp_tot / block_base are rewritten by the next chunk
+    }
+}
+
+SRB_D void emit_row(const DProg& p, const uint8_t* s, const EmitArgs& ea, int64_t row) {
+    {
         if (p.n_keys) {
             const uint64_t* k = (const uint64_t*)s;
             ea.keys[row] = make_ulonglong2(k[1], p.key_words > 1 ? k[2] : 0ULL);
@@ -700,8 +735,19 @@ private:
             filter_range(cols, n);
             return;
         }
-        for (int64_t off = 0; off < n; off += BATCH) {
-            int64_t m = std::min<int64_t>(BATCH, n - off);
+        // The L2-blocked path wants the LARGEST batch memory allows: the table region that is live at any moment is
+        // (rows in flight / rows per batch) x table bytes, so more rows per batch means a smaller, L2-resident window and
+        // more updates per table sector while it is cached.
+        int64_t batch = BATCH;
+        if (hc_partition_applies(n)) {
+            size_t free_b = 0, total_b = 0;
+            cudaMemGetInfo(&free_b, &total_b);
+            free_b += (size_t)ctx->pool_bytes; // pooled buffers are reusable
+            batch = (int64_t)1 << 30;
+            while (batch > BATCH && (size_t)std::min<int64_t>(batch, n) * 17 + ((size_t)1 << 30) > free_b) batch >>= 1;
+        }
+        for (int64_t off = 0; off < n; off += batch) {
+            int64_t m = std::min<int64_t>(batch, n - off);
             launch_batch(cols, off, m);
             check_batch(cols, off, m);
         }
@@ -776,7 +822,7 @@ private:
         }
         bind_prog(cols);
         if (L_.prog.n_keys) {
-            size_t words = (size_t)((std::min<int64_t>(n, BATCH) + 31) / 32);
+            size_t words = (size_t)((n + 31) / 32);
             for (int i = 0; i < 2; i++)
                 if (defer_[i].bytes < words * 4) {
                     defer_[i].ensure(ctx, words * 4);
