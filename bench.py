@@ -12,8 +12,9 @@ HOST buffers through the same C ABI (host->device copies and the result read ins
 slice. `roofline` = algorithmic bytes of the dominant kernel / its CUDA-event duration vs the measured HBM copy peak.
 `cpu_baseline` / `--impl reference` = the CPU restatement of the reference's pipeline (oracle/, the real BE cannot be
 built here) on the box's host cores over a bounded sample of the same table.
-Shards scale weakly (every rank scans its own 600 M-row range of the synthetic table); the only exchange is the
-gather of <= 4 intermediate state rows per rank, merged by a phase-2 (merge-finalize) operator on rank 0.
+Shards scale weakly (every rank scans its own 600 M-row range of the synthetic table); the only exchange of Q1 is the
+gather of <= 4 intermediate state rows per rank, merged by a phase-2 (merge-finalize) operator on every rank INSIDE the
+timed step. `--query highcard` at N > 1 runs phase 1 -> device hash partition -> NCCL all-to-all -> phase 2.
 """
 from __future__ import annotations
 
@@ -57,7 +58,7 @@ def workload(query: str):
         return dict(name="TPC-H SF100 Q6: lineitem range filter + SUM(DECIMAL128)", table="lineitem", cols=T.LINEITEM_Q6, plan=Q.q6_plan,
                     bytes_per_row=28, rows=SF100_LINEITEM, kw={})
     return dict(name="GROUP BY 100M distinct BIGINT keys: SUM, COUNT over 600M rows", table="highcard", cols=["k", "v"],
-                plan=lambda: Q.highcard_plan(group_hint=HIGHCARD_KEYS), bytes_per_row=16, rows=HIGHCARD_ROWS, kw={"n_keys": HIGHCARD_KEYS})
+                plan=lambda **kw: Q.highcard_plan(group_hint=HIGHCARD_KEYS, **kw), bytes_per_row=16, rows=HIGHCARD_ROWS, kw={"n_keys": HIGHCARD_KEYS})
 
 
 # ---- clocks sampled DURING the timed region -----------------------------------------------------------------------------------
@@ -162,7 +163,7 @@ def main():
         return
     import torch
     import torch.distributed as dist
-    from starrocks_b200 import capi as K, ops, tpch_synth as T
+    from starrocks_b200 import capi as K, distributed as D, ops, tpch_synth as T
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -180,21 +181,60 @@ def main():
     chunk, keep = T.device_chunk(w["table"], rank * rows, rows, w["cols"], dev, **w["kw"])
     torch.cuda.synchronize()
 
+    comm = part = None
+    if world > 1:
+        # libsrb's own NCCL communicator moves the intermediate rows; torch.distributed only carries the 128-byte NCCL id
+        def put(b):
+            dist.broadcast_object_list([b], src=0)
+
+        def get():
+            box = [None]
+            dist.broadcast_object_list(box, src=0)
+            return box[0]
+
+        comm = ops.Communicator(ctx, put, get)
+        part = ops.Partitioner(ctx, world)
+        host_ex = D.ObjectExchange(dist, rank, world, group=dist.new_group(backend="gloo"))  # a few host rows: no GPU round trip
+
     def step(collect=None):
-        """one pass of the hot path; returns (result chunk, op counters, op profile)"""
-        phase = K.AGG_UPDATE_SERIALIZE if world > 1 and args.query == "q1" else K.AGG_UPDATE_FINALIZE
-        plan = w["plan"]() if phase == K.AGG_UPDATE_FINALIZE else w["plan"](phase=phase)
+        """one pass of the hot path over this rank's shard; at N > 1 it includes the exchange and the phase-2 merge
+        (starrocks_b200/distributed.py: gather for the low-cardinality plans, hash shuffle for the high-cardinality one)"""
+        from starrocks_b200 import queries as Q
+        two_phase = world > 1 and args.query in ("q1", "highcard")
+        plan = w["plan"](phase=K.AGG_UPDATE_SERIALIZE) if two_phase else w["plan"]()
         op = ops.ScanAggOperator(ctx, plan)
         op.push_chunk(chunk)
         op.set_finishing()
-        out = op.pull_all() if args.query != "highcard" else op.pull_device()
+        c, p = None, None
+        op2 = None
+        if two_phase:
+            if args.query == "q1":
+                # <= 4 intermediate rows (AVG states are {sum,count} blobs): a host object gather is the whole exchange
+                inter = op.pull_all()
+                recv = host_ex.all_gather(inter)
+                op2 = ops.ScanAggOperator(ctx, Q.q1_merge_plan(inter))
+            else:
+                inter = op.pull_device()
+                grouped, counts = part.run(inter, [0])
+                recv, _ = comm.all_to_all(grouped, counts)
+                op2 = ops.ScanAggOperator(ctx, Q.highcard_merge_plan(group_hint=HIGHCARD_KEYS // world))
+            op2.push_chunk(recv)
+            op2.set_finishing()
+            out = op2.pull_all() if args.query == "q1" else op2.pull_device()
+        else:
+            out = op.pull_all() if args.query != "highcard" else op.pull_device()
         n_out = out.n_rows
         c, p = op.counters(), op.profile()
+        if op2 is not None:
+            c2 = op2.counters()
+            c = dict(c, kernel_launches=c["kernel_launches"] + c2["kernel_launches"])
         if collect is not None:
             collect.append((c, p))
         if args.query == "highcard":
-            out = None  # 100 M result rows stay on the device (24 B/row); only the row count is read
+            out = None  # ~10^8 result rows stay on the device (24 B/row); only the row count is read
         op.close()
+        if op2 is not None:
+            op2.close()
         return out, n_out
 
     def barrier():
@@ -224,14 +264,11 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dt_max, kernel_s_max = t.tolist()
 
-    # multi-GPU Q1: gather the <= 4 intermediate rows of every rank and merge them with a phase-2 operator (outside the timed region
-    # only for result checking; the per-step gather is 4 rows and is reported, not hidden: it is included in e2e below)
-    final = out
-    if world > 1 and args.query == "q1":
-        gathered = [None] * world
-        dist.all_gather_object(gathered, {s: (c.type, c.precision, c.scale, K.column_pyvalues(c)) for s, c in out.columns.items()})
-        if rank == 0:
-            final = merge_q1(ctx, gathered)
+    final = out  # at N > 1 every rank already holds the merged Q1 result (gather + phase 2 ran inside the step)
+    if world > 1 and args.query == "highcard":
+        tot = torch.tensor([n_out], dtype=torch.int64, device=dev)
+        dist.all_reduce(tot)
+        n_out = int(tot.item())  # groups over all ranks (every group lives on exactly one rank after the shuffle)
 
     result = None
     if rank == 0:
@@ -284,6 +321,9 @@ def main():
         result["parity_on_cpu_sample"] = K.chunk_rows(got) == K.chunk_rows(cpu_out)
     if rank == 0:
         print(json.dumps(result))
+    if comm is not None:
+        part.close()
+        comm.close()
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
@@ -293,31 +333,6 @@ def ops_shape_name(stats):
     shapes = {p["shape"] for _, p in stats}
     static = sum(p["static_launches"] for _, p in stats)
     return f"static shape {sorted(shapes)} (TMA-staged), {static} static launches" if static else "generic interpreter"
-
-
-def merge_q1(ctx, gathered):
-    """phase 2: merge-finalize over the gathered intermediate rows (aggregator.cpp:871-875)"""
-    from starrocks_b200 import capi as K, ops
-    from starrocks_b200.plan import ExprBuilder, ScanAggPlan
-    cols = {}
-    slots = list(gathered[0].keys())
-    for s in slots:
-        t, p, sc, _ = gathered[0][s]
-        vals = [v for g in gathered for v in g[s][3]]
-        nulls = [1 if v is None else 0 for v in vals]
-        if K.is_binary(t):
-            col = K.Column.from_strings([b"" if v is None else v for v in vals], nulls, type_=t)
-        else:
-            col = K.Column.from_ints(t, [0 if v is None else v for v in vals], nulls)
-        col.precision, col.scale = p, sc
-        cols[s] = col
-    n = len(next(iter(cols.values())).nulls)
-    e = ExprBuilder()
-    keys = [e.slot(0, cols[0].type), e.slot(1, cols[1].type)]
-    fns = [K.AGG_SUM] * 4 + [K.AGG_AVG] * 3 + [K.AGG_COUNT]
-    args_ = [e.slot(2 + a, cols[2 + a].type, cols[2 + a].precision, cols[2 + a].scale) for a in range(8)]
-    plan = ScanAggPlan(exprs=e, keys=keys, aggs=list(zip(fns, args_)), phase=K.AGG_MERGE_FINALIZE)
-    return ops.run_scan_agg(ctx, plan, K.Chunk(n, cols))
 
 
 def run_e2e(args, ctx, w, chunk, rows, dev, rank, world):

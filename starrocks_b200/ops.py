@@ -354,7 +354,29 @@ class Communicator:
     """NCCL communicator of libsrb (all-to-all shuffle, all-gather/broadcast). `store_set` / `store_get` move the 128-byte
     ncclUniqueId between ranks (torch.distributed's store in the harness)."""
 
+    _nccl_preloaded = False
+
+    @classmethod
+    def _preload_nccl(cls):
+        """libsrb binds NCCL with dlopen("libnccl.so.2"). When PyTorch is installed its wheel carries a newer NCCL under the
+        same soname; whichever copy is mapped first wins for the whole process, and libtorch_cuda needs symbols of its own
+        copy. So map the wheel's copy first (no-op when torch is already imported or no wheel copy exists)."""
+        if cls._nccl_preloaded:
+            return
+        cls._nccl_preloaded = True
+        try:
+            import importlib.util
+            spec = importlib.util.find_spec("nvidia.nccl")
+            for d in (spec.submodule_search_locations if spec else []):
+                p = os.path.join(d, "lib", "libnccl.so.2")
+                if os.path.exists(p):
+                    C.CDLL(p, mode=C.RTLD_GLOBAL)
+                    return
+        except Exception:
+            pass
+
     def __init__(self, ctx: Context, store_set, store_get):
+        self._preload_nccl()
         self.ctx, self.L = ctx, ctx.L
         buf = (C.c_char * 128)()
         if ctx.rank == 0:

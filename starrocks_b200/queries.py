@@ -80,6 +80,17 @@ def q1_plan(dict_keys: bool = True, phase: int = K.AGG_UPDATE_FINALIZE, group_hi
     return ScanAggPlan(preds=preds, exprs=e, keys=[k1, k2], aggs=aggs, phase=phase, group_hint=group_hint)
 
 
+def q1_merge_plan(inter: K.Chunk) -> ScanAggPlan:
+    """phase 2 of Q1 over the intermediate rows of q1_plan(phase=AGG_UPDATE_SERIALIZE): slots 0,1 = keys, 2..9 = the eight
+    states in aggregate order (SUM values, AVG {sum,count} blobs, COUNT) (aggregator.cpp:871-875, avg.h:161-181)"""
+    e = ExprBuilder()
+    c = inter.columns
+    keys = [e.slot(0, c[0].type), e.slot(1, c[1].type)]
+    fns = [K.AGG_SUM] * 4 + [K.AGG_AVG] * 3 + [K.AGG_COUNT]
+    args = [e.slot(2 + a, c[2 + a].type, c[2 + a].precision, c[2 + a].scale) for a in range(8)]
+    return ScanAggPlan(exprs=e, keys=keys, aggs=list(zip(fns, args)), phase=K.AGG_MERGE_FINALIZE)
+
+
 def highcard_plan(phase: int = K.AGG_UPDATE_FINALIZE, group_hint: int = 0) -> ScanAggPlan:
     """select k, sum(v), count(*) from t group by k   (k, v BIGINT)"""
     e = ExprBuilder()

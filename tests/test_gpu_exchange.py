@@ -1,0 +1,149 @@
+"""GPU tests of the exchange step (SURVEY §8 a12 / e): device hash partitioning against the oracle's shuffle hash, the NCCL
+all-to-all / all-gather of libsrb, and — when two GPUs are visible — the whole two-phase high-cardinality aggregation."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from starrocks_b200 import capi as K, distributed as D, queries as Q, tpch_synth as T  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from starrocks_b200 import ops
+    c = ops.Context(device=0)
+    yield c
+    c.close()
+
+
+def _dest(oracle, col, world):
+    w = K.type_width(col.type)
+    raw = np.ascontiguousarray(col.data).view(np.uint8).reshape(-1, w)
+    return np.array([oracle.lib.orc_shuffle_channel(raw[i].tobytes(), w, world) for i in range(raw.shape[0])], dtype=np.int64)
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_partitioner_routes_rows_like_the_shuffle_hash(ctx, oracle, world):
+    from starrocks_b200 import ops
+    n = 50_000
+    ch = T.host_chunk("highcard", 0, n, ["k", "v"], n_keys=7000)
+    dch, ptrs = ctx.device_chunk(ch)
+    part = ops.Partitioner(ctx, world)
+    try:
+        grouped, counts = part.run(dch, [Q.HC_K])
+        got = ctx.fetch_chunk(grouped)
+        dest = _dest(oracle, ch.columns[Q.HC_K], world)
+        assert counts == np.bincount(dest, minlength=world).tolist() and sum(counts) == n
+        pos = 0
+        want_rows = K.chunk_rows(ch, sort=False)
+        for d in range(world):  # destination d's rows are contiguous and are exactly the rows that hash to d (any order inside)
+            piece = sorted(K.chunk_rows(ops.slice_chunk(got, pos, pos + counts[d]), sort=False))
+            assert piece == sorted(r for r, dd in zip(want_rows, dest) if dd == d)
+            pos += counts[d]
+    finally:
+        part.close()
+        for p in ptrs:
+            ctx.device_free(p)
+
+
+def test_single_rank_communicator_round_trip(ctx):
+    from starrocks_b200 import ops
+    box = {}
+    comm = ops.Communicator(ctx, lambda b: box.__setitem__("id", b), lambda: box["id"])
+    ch = T.host_chunk("highcard", 0, 10_000, ["k", "v"], n_keys=100)
+    dch, ptrs = ctx.device_chunk(ch)
+    try:
+        recv, rc = comm.all_to_all(dch, [ch.n_rows])
+        assert rc == [ch.n_rows]
+        assert K.chunk_rows(ctx.fetch_chunk(recv), sort=False) == K.chunk_rows(ch, sort=False)
+        allg = comm.all_gather(dch)
+        assert K.chunk_rows(ctx.fetch_chunk(allg), sort=False) == K.chunk_rows(ch, sort=False)
+    finally:
+        comm.close()
+        for p in ptrs:
+            ctx.device_free(p)
+
+
+# ---- two GPUs: phase 1 -> device partition -> NCCL all-to-all -> phase 2 ------------------------------------------------------
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, n_rows, n_keys, out_q):
+    import torch
+    import torch.distributed as dist
+    from starrocks_b200 import ops
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)  # only carries the NCCL id; the data moves through libsrb
+    ctx = ops.Context(device=rank, rank=rank, world_size=world)
+    try:
+        def put(b):
+            dist.broadcast_object_list([b], src=0)
+
+        def get():
+            box = [None]
+            dist.broadcast_object_list(box, src=0)
+            return box[0]
+
+        comm = ops.Communicator(ctx, put, get)
+        part = ops.Partitioner(ctx, world)
+        b, e = D.shard_range(n_rows, rank, world)
+        shard = T.host_chunk("highcard", b, e - b, ["k", "v"], n_keys=n_keys)
+        dch, ptrs = ctx.device_chunk(shard)
+        op1 = ops.ScanAggOperator(ctx, Q.highcard_plan(phase=K.AGG_UPDATE_SERIALIZE))
+        op1.push_chunk(dch)
+        op1.set_finishing()
+        inter = op1.pull_device()
+        grouped, counts = part.run(inter, [0])
+        recv, _ = comm.all_to_all(grouped, counts)
+        op2 = ops.ScanAggOperator(ctx, Q.highcard_merge_plan())
+        op2.push_chunk(recv)
+        op2.set_finishing()
+        rows = K.chunk_rows(op2.pull_all())
+        out_q.put((rank, rows))
+        for o in (op1, op2):
+            o.close()
+        part.close()
+        comm.close()
+        for p in ptrs:
+            ctx.device_free(p)
+        dist.barrier()
+    finally:
+        ctx.close()
+        dist.destroy_process_group()
+
+
+def test_two_gpu_highcard_two_phase(oracle):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+    n, nk, world = 400_000, 50_000, 2
+    mpc = mp.get_context("spawn")
+    q = mpc.Queue()
+    port = _free_port()
+    procs = [mpc.Process(target=_worker, args=(r, world, port, n, nk, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=300) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    whole = T.host_chunk("highcard", 0, n, ["k", "v"], n_keys=nk)
+    want = K.chunk_rows(oracle.scan_agg(Q.highcard_plan(), whole))
+    assert not ({r[0] for r in res[0]} & {r[0] for r in res[1]})
+    assert sorted(res[0] + res[1]) == want
