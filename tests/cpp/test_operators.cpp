@@ -191,18 +191,22 @@ static void test_group_by_nullable_key(srb_ctx* ctx) {
 // ---- inner hash join: build (key, payload) |><| probe (key, x) ---------------------------------------------------------------------
 static void test_inner_join(srb_ctx* ctx) {
     const int BK = 20, BP = 21, PK = 30, PX = 31;
-    auto bk = std::make_shared<Int32Column>(SRB_TYPE_INT);
-    auto bp = std::make_shared<Int64Column>(SRB_TYPE_BIGINT);
     std::multimap<int32_t, int64_t> table;
-    for (int i = 0; i < 5000; i++) {
-        const int32_t k = (int32_t)(splitmix(i) % 3000);
-        bk->append(k);
-        bp->append(1000 + i);
-        table.emplace(k, 1000 + i);
+    std::vector<ChunkPtr> builds; // the build side arrives in chunks of <= chunk_size rows too
+    for (int base = 0; base < 5000; base += 4096) {
+        auto bk = std::make_shared<Int32Column>(SRB_TYPE_INT);
+        auto bp = std::make_shared<Int64Column>(SRB_TYPE_BIGINT);
+        for (int i = base; i < std::min(base + 4096, 5000); i++) {
+            const int32_t k = (int32_t)(splitmix(i) % 3000);
+            bk->append(k);
+            bp->append(1000 + i);
+            table.emplace(k, 1000 + i);
+        }
+        auto build = std::make_shared<Chunk>();
+        build->append_column(bk, BK);
+        build->append_column(bp, BP);
+        builds.push_back(build);
     }
-    auto build = std::make_shared<Chunk>();
-    build->append_column(bk, BK);
-    build->append_column(bp, BP);
     std::vector<ChunkPtr> probes;
     std::multiset<std::tuple<int32_t, int64_t, int64_t>> want;
     for (int base = 0; base < 20000; base += 4096) {
@@ -227,12 +231,13 @@ static void test_inner_join(srb_ctx* ctx) {
     jp.probe_out_slots = {PK, PX};
     auto joiner = std::make_shared<GpuHashJoiner>(ctx, jp);
     RuntimeState state(4096);
-    ChunkSourceOperator bsrc({build});
+    ChunkSourceOperator bsrc(builds);
     GpuHashJoinBuildOperator bop(joiner);
     GpuHashJoinProbeOperator pop(joiner);
     CHECK(!pop.need_input()); // the probe side is blocked until the build side finished (hash_joiner.h:60-65)
     auto bres = run_pipeline(&state, {&bsrc, &bop});
     CHECK(bres.ok());
+    if (!bres.ok()) std::printf("  build: %s\n", bres.status().to_string().c_str());
     ChunkSourceOperator psrc(probes);
     auto res = run_pipeline(&state, {&psrc, &pop});
     CHECK(res.ok());
