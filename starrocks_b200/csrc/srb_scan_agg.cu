@@ -216,6 +216,23 @@ SRB_D void store_w(void* base, int64_t row, int w, uint64_t lo, uint64_t hi) {
 
 SRB_D void emit_row(const DProg& p, const uint8_t* s, const EmitArgs& ea, int64_t row);
 
+// gathers the pieces of a small result (a row range of every output column) into one contiguous buffer, so that a pull
+// costs one device->host copy instead of one per column
+struct PackArgs {
+    static constexpr int MAX = 40;
+    int n;
+    const uint8_t* src[MAX];
+    uint32_t bytes[MAX];
+    uint32_t dst_off[MAX];
+};
+__global__ void k_pack_result(const __grid_constant__ PackArgs a, uint8_t* __restrict__ dst) {
+    for (int i = blockIdx.x; i < a.n; i += gridDim.x) {
+        const uint8_t* s = a.src[i];
+        uint8_t* d = dst + a.dst_off[i];
+        for (uint32_t b = threadIdx.x; b < a.bytes[i]; b += blockDim.x) d[b] = s[b];
+    }
+}
+
 // One output position per occupied slot. A block takes 8 x 256 slots at a time, counts its occupied ones, scans the
 // counts and reserves the block's output range with ONE atomic (a ticket per warp made the single counter the bottleneck
 // of a 10^8-group emit).
@@ -1117,26 +1134,56 @@ private:
         const DProg& P = L_.prog;
         // keys: packed 16-byte records -> one column per key
         std::vector<uint8_t> packed;
-        if (P.n_keys) {
-            packed.resize((size_t)n * 16);
-            if (n) SRB_CUDA(cudaMemcpyAsync(packed.data(), ekeys_.as<uint8_t>() + (size_t)pos * 16, (size_t)n * 16, cudaMemcpyDeviceToHost, stream));
-        }
+        if (P.n_keys) packed.resize((size_t)n * 16);
         std::vector<std::vector<uint8_t>> vals(P.n_aggs), nulls(P.n_aggs);
         std::vector<std::vector<int64_t>> cnts(P.n_aggs);
+        // every piece of the result rows [pos, pos+n): (device source, bytes, host destination)
+        struct Piece {
+            const uint8_t* src;
+            size_t bytes;
+            void* dst;
+        };
+        std::vector<Piece> pieces;
+        if (P.n_keys && n) pieces.push_back({ekeys_.as<uint8_t>() + (size_t)pos * 16, (size_t)n * 16, packed.data()});
         for (int a = 0; a < P.n_aggs; a++) {
             const AggOutMeta& m = L_.agg_out[a];
             vals[a].resize((size_t)n * m.out_width);
-            if (n) SRB_CUDA(cudaMemcpyAsync(vals[a].data(), eval_[a].val.as<uint8_t>() + (size_t)pos * m.out_width, (size_t)n * m.out_width, cudaMemcpyDeviceToHost, stream));
+            if (n) pieces.push_back({eval_[a].val.as<uint8_t>() + (size_t)pos * m.out_width, (size_t)n * m.out_width, vals[a].data()});
             if (m.nullable) {
                 nulls[a].resize((size_t)n);
-                if (n) SRB_CUDA(cudaMemcpyAsync(nulls[a].data(), eval_[a].null.as<uint8_t>() + pos, (size_t)n, cudaMemcpyDeviceToHost, stream));
+                if (n) pieces.push_back({eval_[a].null.as<uint8_t>() + pos, (size_t)n, nulls[a].data()});
             }
             if (m.blob) {
                 cnts[a].resize((size_t)n);
-                if (n) SRB_CUDA(cudaMemcpyAsync(cnts[a].data(), eval_[a].cnt.as<int64_t>() + pos, (size_t)n * 8, cudaMemcpyDeviceToHost, stream));
+                if (n) pieces.push_back({(const uint8_t*)(eval_[a].cnt.as<int64_t>() + pos), (size_t)n * 8, cnts[a].data()});
             }
         }
-        SRB_CUDA(cudaStreamSynchronize(stream));
+        size_t total = 0;
+        for (auto& pc : pieces) total += (pc.bytes + 15) & ~(size_t)15;
+        if (total <= ((size_t)1 << 20) && (int)pieces.size() <= PackArgs::MAX) { // (<= 1 MB: the pinned buffer comes from the pool)
+            // small result: one pack kernel + ONE pinned copy instead of a pageable copy per column
+            PackArgs pa{};
+            pa.n = (int)pieces.size();
+            size_t off = 0;
+            for (int i = 0; i < pa.n; i++) {
+                pa.src[i] = pieces[i].src;
+                pa.bytes[i] = (uint32_t)pieces[i].bytes;
+                pa.dst_off[i] = (uint32_t)off;
+                off += (pieces[i].bytes + 15) & ~(size_t)15;
+            }
+            if (pa.n) {
+                pack_dev_.ensure(ctx, total);
+                pack_host_.ensure(total);
+                k_pack_result<<<std::min(64, pa.n * 4), 256, 0, stream>>>(pa, pack_dev_.as<uint8_t>());
+                launches++;
+                SRB_CUDA(cudaMemcpyAsync(pack_host_.p, pack_dev_.p, total, cudaMemcpyDeviceToHost, stream));
+            }
+            SRB_CUDA(cudaStreamSynchronize(stream));
+            for (int i = 0; i < pa.n; i++) memcpy(pieces[i].dst, pack_host_.as<uint8_t>() + pa.dst_off[i], pieces[i].bytes);
+        } else {
+            for (auto& pc : pieces) SRB_CUDA(cudaMemcpyAsync(pc.dst, pc.src, pc.bytes, cudaMemcpyDeviceToHost, stream));
+            SRB_CUDA(cudaStreamSynchronize(stream));
+        }
         for (int k = 0; k < P.n_keys; k++) {
             const ColMeta& cm = L_.key_out[k];
             HostCol h;
@@ -1229,6 +1276,8 @@ private:
     DevBuf hc_k_, hc_v_, hc_ctr_;                                 // permuted (key, value) copy of the current batch + its 2 x 256 counters
     ColBind hc_cols_[MAX_COLS];
     bool batch_partitioned_ = false;
+    DevBuf pack_dev_;    // small results: all pulled columns packed contiguously ...
+    PinnedBuf pack_host_; // ... and their pinned landing buffer
     int64_t staging_rows_, chunk_size_;
     cudaStream_t copy_stream_ = nullptr;
     cudaEvent_t kernel_done_ = nullptr, ev0_ = nullptr, ev1_ = nullptr;
