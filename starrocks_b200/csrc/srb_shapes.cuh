@@ -141,6 +141,18 @@ SRB_D void mbar_wait(uint64_t* bar, uint32_t parity) {
             "r"(parity)
             : "memory");
 }
+SRB_D void mbar_wait_a(uint32_t bar, uint32_t parity) { // bar: shared-window address
+    asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "WAIT_%=:\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+            "@p bra DONE_%=;\n\t"
+            "bra WAIT_%=;\n\t"
+            "DONE_%=:\n\t}" ::"r"(bar),
+            "r"(parity)
+            : "memory");
+}
+SRB_D void mbar_arrive_a(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
 SRB_D void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
                  "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
@@ -197,21 +209,18 @@ struct StaticArgs { // host-computed tile layout: column c sits at col_off[c] in
     int32_t n_preds;
     int32_t acc_off; // byte offset of the per-thread accumulators inside dynamic shared memory
     int32_t n_ranges; // >= 0: the predicates are the conjunction of rng[0..n_ranges); -1: evaluate preds[] generically
-    int32_t _pad;
+    int32_t narrow_ok; // the plan's literals and casts allow the narrow tile body (narrow_literals_ok)
     SRange rng[ST_MAX_RANGES];
     SPred preds[MAX_PREDS];
 };
 
 // the conjunction of the lowered ranges over R rows (range loop outside, rows inside; every field of a range is a
 // fixed kernel-parameter address, so nothing is fetched through an index)
-template <int R, int STRIDE>
-SRB_D void eval_ranges_rows(const StaticArgs& sa, const uint8_t* stage, int r0, bool (&pass)[R]) {
-#pragma unroll
-    for (int j = 0; j < R; j++) pass[j] = true;
-#pragma unroll
-    for (int i = 0; i < ST_MAX_RANGES; i++) {
-        if (i < sa.n_ranges) {
-            const SRange& g = sa.rng[i];
+template <int R, int STRIDE, int I>
+SRB_D void eval_ranges_from(const StaticArgs& sa, const uint8_t* stage, int r0, bool (&pass)[R]) {
+    if constexpr (I < ST_MAX_RANGES) {
+        if (I < sa.n_ranges) { // nested, not chained: a plan with one range leaves after one test
+            const SRange& g = sa.rng[I];
             const uint8_t* col = stage + g.col_off;
             const bool neg = g.neg != 0;
             if (g.width == 8) {
@@ -228,8 +237,15 @@ SRB_D void eval_ranges_rows(const StaticArgs& sa, const uint8_t* stage, int r0, 
                     pass[j] = pass[j] && ((d <= span) != neg);
                 }
             }
+            eval_ranges_from<R, STRIDE, I + 1>(sa, stage, r0, pass);
         }
     }
+}
+template <int R, int STRIDE>
+SRB_D void eval_ranges_rows(const StaticArgs& sa, const uint8_t* stage, int r0, bool (&pass)[R]) {
+#pragma unroll
+    for (int j = 0; j < R; j++) pass[j] = true;
+    eval_ranges_from<R, STRIDE, 0>(sa, stage, r0, pass);
 }
 
 template <int W>
@@ -494,6 +510,7 @@ struct AccGeom {
 };
 template <class S>
 struct RareAcc {
+    uint64_t lo[AccGeom<S>::G * AccGeom<S>::NR];    // what the narrow path moved out of a shared-memory word that reached 2^63
     uint64_t hi[AccGeom<S>::G * AccGeom<S>::NR];    // bits 64..127 of each partial sum (sign-extended for 8-byte arguments)
     uint32_t nulls[AccGeom<S>::G * AccGeom<S>::NR]; // selected rows whose argument was NULL
 };
@@ -568,6 +585,205 @@ SRB_D void acc_update_rows(RareAcc<S>& ra, uint8_t* acc_tid, uint8_t* rows_tid, 
 }
 
 
+// ---- the narrow tile body ---------------------------------------------------------------------------------------------------
+// Money amounts, quantities, rates and their products are small non-negative integers. When EVERY value of a warp's rows is
+// (every column value and every operand in [0, 2^32), products in [0, 2^64)), no checked operation can overflow, nothing is
+// NULL, and the exact results are plain 32/64-bit unsigned arithmetic. The narrow body computes exactly that and ORs into
+// `esc` every bit that would break the assumption; one warp vote on esc (together with "a group is missing from the
+// directory") decides whether its results are used or the tile is redone by the general body. Values are identical either
+// way; only the instruction count differs (no 128-bit products, no overflow flags, no sign words).
+template <class S>
+constexpr bool node_is_operand(int n) {
+    for (int i = 0; i < S::N_NODES; i++) {
+        const SNode nd = S::node(i);
+        if (nd.op != DOP_LOAD && nd.op != DOP_LIT && (nd.lhs == n || nd.rhs == n)) return true;
+    }
+    return false;
+}
+template <class S>
+constexpr bool node_is_key(int n) {
+    for (int k = 0; k < S::N_KEYS; k++)
+        if (S::key(k).node == n) return true;
+    return false;
+}
+template <class S>
+constexpr bool shape_has_narrow() {
+    bool ok = S::GMAX > 0;
+    for (int i = 0; ok && i < S::N_NODES; i++) {
+        const SNode nd = S::node(i);
+        const bool key = node_is_key<S>(i);
+        if (key && (nd.op != DOP_LOAD || node_is_operand<S>(i))) return false; // keys: plain columns, bits taken as they are
+        switch (nd.op) {
+        case DOP_LOAD:
+            if (nd.width != 8 && !(key && nd.width == 4)) return false;
+            break;
+        case DOP_LIT: break;
+        case DOP_CAST:
+            if (nd.width < 8) return false;
+            break;
+        case DOP_ADD:
+        case DOP_SUB:
+        case DOP_MUL:
+        case DOP_MULFAST:
+            if (nd.width < 8 || nd.adj_l != 0 || nd.adj_r != 0) return false;
+            break;
+        default: return false;
+        }
+    }
+    for (int a = 0; a < S::N_AGGS; a++) {
+        const SAgg g = S::agg(a);
+        if (g.fn == FN_COUNT ? g.arg >= 0 : (g.fn != FN_SUM && g.fn != FN_AVG)) return false;
+    }
+    return true;
+}
+// uniform part of the assumption, checked once on the host: literals in [0, 2^32), casts that do not rescale
+template <class S>
+inline bool narrow_literals_ok(const DProg& p) {
+    constexpr bool has = shape_has_narrow<S>();
+    for (int i = 0; has && i < S::N_NODES; i++) {
+        const SNode nd = S::node(i);
+        const DNode& rt = p.nodes[i];
+        if (nd.op == DOP_LIT && !(rt.lit_hi == 0 && (rt.lit_lo >> 32) == 0)) return false;
+        if (nd.op == DOP_CAST && !(rt.lit_hi == 0 && rt.lit_lo == 1)) return false;
+    }
+    return has;
+}
+
+template <class S, int I, int R>
+SRB_D void eval_narrow_node(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const uint8_t* stage, int r0, uint32_t& esc) {
+    constexpr SNode nd = S::node(I);
+    if constexpr (nd.op == DOP_LOAD && nd.width == 4) {
+#pragma unroll
+        for (int j = 0; j < R; j++) nv[j][I] = ((const uint32_t*)(stage + load_off<S>(I)))[r0 + j * S::THREADS]; // key bits
+    } else if constexpr (nd.op == DOP_LOAD) {
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const uint64_t x = ((const uint64_t*)(stage + load_off<S>(I)))[r0 + j * S::THREADS];
+            esc |= (uint32_t)(x >> 32);
+            nv[j][I] = (uint32_t)x;
+        }
+    } else if constexpr (nd.op == DOP_LIT) {
+#pragma unroll
+        for (int j = 0; j < R; j++) nv[j][I] = (uint32_t)p.nodes[I].lit_lo;
+    } else if constexpr (nd.op == DOP_CAST) {
+#pragma unroll
+        for (int j = 0; j < R; j++) nv[j][I] = nv[j][nd.lhs];
+    } else if constexpr (nd.op == DOP_ADD || nd.op == DOP_SUB) {
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const uint64_t r = nd.op == DOP_ADD ? nv[j][nd.lhs] + nv[j][nd.rhs] : nv[j][nd.lhs] - nv[j][nd.rhs];
+            esc |= (uint32_t)(r >> 32); // a negative difference sets every high bit
+            nv[j][I] = (uint32_t)r;
+        }
+    } else { // MUL / MULFAST: operands are < 2^32, the product is exact in 64 bits
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const uint64_t r = (uint64_t)(uint32_t)nv[j][nd.lhs] * (uint64_t)(uint32_t)nv[j][nd.rhs];
+            if constexpr (node_is_operand<S>(I)) {
+                esc |= (uint32_t)(r >> 32);
+                nv[j][I] = (uint32_t)r;
+            } else {
+                nv[j][I] = r;
+            }
+        }
+    }
+}
+template <class S, int R, int... I>
+SRB_D void eval_narrow_all(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const uint8_t* stage, int r0, uint32_t& esc, std::integer_sequence<int, I...>) {
+    (eval_narrow_node<S, I, R>(p, nv, stage, r0, esc), ...);
+}
+template <class S>
+SRB_D PackedKey pack_key_narrow(const uint64_t* nv) {
+    PackedKey k{0, 0, 0, false};
+    if constexpr (S::N_KEYS >= 1) key_put(k, nv[S::key(0).node], S::key(0).width);
+    if constexpr (S::N_KEYS >= 2) key_put(k, nv[S::key(1).node], S::key(1).width);
+    if constexpr (S::N_KEYS >= 3) key_put(k, nv[S::key(2).node], S::key(2).width);
+    if constexpr (S::N_KEYS >= 4) key_put(k, nv[S::key(3).node], S::key(3).width);
+    return k;
+}
+
+// x (< 2^64, non-negative) into a shared-memory word: plain 64-bit add. No carry can be lost while the word and the
+// addend are both below 2^63; `flag` collects the top bits of both, and when its sign bit is set after the tile the
+// exact carries are recovered from the words themselves (acc_narrow_fixup).
+template <class S, int A>
+SRB_D void acc_narrow_one(uint8_t* a, uint8_t* trash, const uint64_t* nv, bool on, uint32_t& flag) {
+    constexpr SAgg g = S::agg(A);
+    if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
+        constexpr int RI = rep_index<S>(A);
+        const uint64_t x = nv[g.arg];
+        uint64_t* slot = (uint64_t*)(on ? a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8 : trash);
+        const uint64_t old = *slot;
+        *slot = old + x;
+        flag |= (uint32_t)(old >> 32) | (uint32_t)(x >> 32);
+    }
+}
+// Rare: some word or addend of the warp had bit 63 set. Every add of the tile has already been applied modulo 2^64; the
+// carry of row j's add is (word right after it) < x_j, and that word is the final one minus the later rows' addends to the
+// same word. Words that reached 2^63 are then moved to the thread-local low/high pair so the next tiles stay quiet.
+template <class S, int R>
+struct NarrowFix { // by value into the out-of-line fix-up: the tile's arrays must not have their address taken
+    uint64_t x[R][AccGeom<S>::NR];
+    int gid[R];
+    bool on[R];
+};
+template <class S, int R, int A>
+SRB_D void narrow_fix_put(NarrowFix<S, R>& f, const uint64_t (&nv)[R][S::N_NODES]) {
+    constexpr SAgg g = S::agg(A);
+    if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
+#pragma unroll
+        for (int j = 0; j < R; j++) f.x[j][rep_index<S>(A)] = nv[j][g.arg];
+    }
+}
+template <class S, int R>
+static __device__ __noinline__ void acc_narrow_fixup(RareAcc<S>* ra, uint8_t* acc_tid, uint8_t* trash, const NarrowFix<S, R> f) {
+    constexpr int NR = AccGeom<S>::NR;
+    for (int ri = 0; ri < NR; ri++) {
+        for (int j = R - 1; j >= 0; j--) {
+            if (!f.on[j]) continue;
+            const uint64_t* slot = (const uint64_t*)(acc_tid + (size_t)f.gid[j] * (S::THREADS * 8) + (size_t)ri * AccGeom<S>::G * S::THREADS * 8);
+            uint64_t after = *slot;
+            for (int k = j + 1; k < R; k++)
+                if (f.on[k] && f.gid[k] == f.gid[j]) after -= f.x[k][ri];
+            if (after < f.x[j][ri]) ra->hi[f.gid[j] * NR + ri] += 1;
+        }
+        for (int j = 0; j < R; j++) {
+            if (!f.on[j]) continue;
+            uint64_t* slot = (uint64_t*)(acc_tid + (size_t)f.gid[j] * (S::THREADS * 8) + (size_t)ri * AccGeom<S>::G * S::THREADS * 8);
+            const uint64_t w = *slot;
+            if (w >> 63) {
+                const uint64_t lo = ra->lo[f.gid[j] * NR + ri] + w;
+                ra->hi[f.gid[j] * NR + ri] += lo < w ? 1 : 0;
+                ra->lo[f.gid[j] * NR + ri] = lo;
+                *slot = 0;
+            }
+        }
+    }
+    if (*(uint64_t*)trash >> 63) *(uint64_t*)trash = 0; // the trash word only ever matters through its top bit
+}
+template <class S, int R, int... A>
+SRB_D void acc_narrow_rows(RareAcc<S>& ra, uint8_t* acc_tid, uint8_t* rows_tid, uint8_t* trash, const uint64_t (&nv)[R][S::N_NODES], const bool (&on)[R],
+                           const int (&gid)[R], std::integer_sequence<int, A...>) {
+    uint32_t flag = 0;
+#pragma unroll
+    for (int j = 0; j < R; j++) {
+        uint8_t* a = acc_tid + (size_t)gid[j] * (S::THREADS * 8);
+        (acc_narrow_one<S, A>(a, trash, nv[j], on[j], flag), ...);
+        uint32_t* rc = (uint32_t*)(on[j] ? rows_tid + (size_t)gid[j] * (S::THREADS * 4) : trash);
+        *rc += 1u;
+    }
+    if (__any_sync(0xffffffffu, (int32_t)flag < 0)) {
+        NarrowFix<S, R> f;
+        (narrow_fix_put<S, R, A>(f, nv), ...);
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            f.gid[j] = gid[j];
+            f.on[j] = on[j];
+        }
+        acc_narrow_fixup<S, R>(&ra, acc_tid, trash, f);
+    }
+}
+
+
 SRB_D uint64_t warp_sum_u64(uint64_t x) {
     for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
     return x;
@@ -596,8 +812,9 @@ struct Flusher {
         constexpr SAgg g = S::agg(A);
         if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
             constexpr int RI = rep_index<S>(A);
-            uint64_t lo = *(const uint64_t*)(acc_tid + (size_t)(RI * G + q) * S::THREADS * 8);
-            uint64_t hi = ra.hi[q * NR + RI];
+            const uint64_t w = *(const uint64_t*)(acc_tid + (size_t)(RI * G + q) * S::THREADS * 8);
+            uint64_t lo = w + ra.lo[q * NR + RI];
+            uint64_t hi = ra.hi[q * NR + RI] + (lo < w ? 1ULL : 0ULL);
             warp_sum_u128(lo, hi);
             uint64_t nulls = 0;
             if constexpr (node_can_be_null<S>(g.arg)) nulls = warp_sum_u64(ra.nulls[q * NR + RI]);
@@ -856,6 +1073,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
         }
 #pragma unroll
         for (int k = 0; k < AccGeom<S>::NR * G; k++) {
+            ra.lo[k] = 0;
             ra.hi[k] = 0;
             ra.nulls[k] = 0;
         }
@@ -892,7 +1110,10 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
         for (int q = 0; q < G; q++) kd_lo[q] = kd_hi[q] = 0;
         int s = 0;
         uint32_t parity = 0;
-        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint32_t full0 = smem_u32(&full_bar[0]), empty0 = smem_u32(&empty_bar[0]);
+        const uint8_t* stage = smem; // walks the ring with s
+        const int nt = (int)n_tiles, tstep = (int)gridDim.x; // a launch covers <= 2^27 rows
+        for (int tile = blockIdx.x; tile < nt; tile += tstep) {
             if (S::GMAX > 0 && S::N_KEYS > 0 && my_cnt < G) { // a full directory never changes again
                 // my_cnt steers warp votes below, so it must be ONE value per warp even if the lanes poll at different times
                 // (the minimum: every lane's own read saw at least that many published entries before it loads them)
@@ -906,9 +1127,8 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                     my_cnt = c;
                 }
             }
-            mbar_wait(&full_bar[s], parity);
+            mbar_wait_a(full0 + 8u * (uint32_t)s, parity);
             __syncwarp(); // lanes may leave the wait loop on different polls
-            const uint8_t* stage = smem + (size_t)s * stage_bytes;
             bool pass[R];
             if (sa.n_ranges >= 0) {
                 eval_ranges_rows<R, THREADS>(sa, stage, tid, pass);
@@ -924,7 +1144,31 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                 selected32 += pass[j] ? 1u : 0u;
                 any_pass = any_pass || pass[j];
             }
-            if (__any_sync(0xffffffffu, any_pass)) {
+            bool done = false; // warp-uniform: the narrow body handled this tile
+            if constexpr (shape_has_narrow<S>() && S::N_KEYS > 0) {
+                if (sa.narrow_ok && __any_sync(0xffffffffu, any_pass)) {
+                    uint64_t nv[R][S::N_NODES];
+                    uint32_t esc = 0;
+                    eval_narrow_all<S, R>(p, nv, stage, tid, esc, NodeSeq{});
+                    int gid[R];
+                    bool bad = esc != 0;
+#pragma unroll
+                    for (int j = 0; j < R; j++) {
+                        const PackedKey k = pack_key_narrow<S>(nv[j]);
+                        gid[j] = G;
+#pragma unroll
+                        for (int q = G - 1; q >= 0; q--)
+                            if (kd_lo[q] == k.lo && (KW == 1 || kd_hi[q] == k.hi)) gid[j] = q;
+                        bad = bad || (pass[j] && gid[j] >= my_cnt);
+                        if (gid[j] >= my_cnt) gid[j] = 0;
+                    }
+                    if (!__any_sync(0xffffffffu, bad)) {
+                        acc_narrow_rows<S, R>(ra, acc_tid, rows_tid, trash, nv, pass, gid, AggSeq{});
+                        done = true;
+                    }
+                }
+            }
+            if (!done && __any_sync(0xffffffffu, any_pass)) {
                 Val v[R][S::N_NODES];
                 eval_static_all<S, R>(p, v, stage, tid, NodeSeq{});
                 if constexpr (S::N_KEYS == 0) {
@@ -980,9 +1224,13 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                         }
                         acc_update_rows<S, R>(ra, acc_tid, rows_tid, trash, v, on, gid, AggSeq{});
                     }
+                    bool any_miss = false;
+#pragma unroll
+                    for (int j = 0; j < R; j++) any_miss = any_miss || miss[j];
+                    if (S::GMAX > 0 && !__any_sync(0xffffffffu, any_miss)) any_miss = false; // one test per tile on the common path
 #pragma unroll
                     for (int j = 0; j < R; j++) {
-                        if (miss[j]) {
+                        if (any_miss && miss[j]) {
                             // global-table path: the directory is full of other groups (or the shape keeps none)
                             int rc;
                             if constexpr (S::GMAX > 0) { // the exception here: keep its code out of the loop body
@@ -997,7 +1245,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                             }
                             inserted += rc & 1;
                             if (rc & 2) {
-                                const int64_t i = tile * TILE + tid + j * THREADS;
+                                const int64_t i = (int64_t)tile * TILE + tid + j * THREADS;
                                 atomicOr(&defer_out[i >> 5], 1u << (i & 31));
                                 deferred++;
                             }
@@ -1006,10 +1254,12 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                 }
             }
             __syncwarp();
-            if ((tid & 31) == 0) mbar_arrive(&empty_bar[s]); // this warp is done with stage s
+            if ((tid & 31) == 0) mbar_arrive_a(empty0 + 8u * (uint32_t)s); // this warp is done with stage s
+            stage += stage_bytes;
             if (++s == n_stages) {
                 s = 0;
                 parity ^= 1u;
+                stage = smem;
             }
         }
     }
@@ -1160,6 +1410,7 @@ inline int64_t launch_shape(const DProg& p, const TableView& tv, int64_t base, i
         sa.preds[i] = SPred{sa.col_off[d.col], p.cols[d.col].width, pred_opmask(d.op), d.group, d.lit_lo, d.lit_hi};
     }
     if (!lower_ranges(p, sa)) sa.n_ranges = -1;
+    sa.narrow_ok = (narrow_literals_ok<S>(p) && !getenv("SRB_NO_NARROW")) ? 1 : 0; // the env hook: A/B runs and tests of the general body
     const size_t smem = (size_t)sa.acc_off + acc_bytes;
     static bool configured = false;
     if (!configured) {

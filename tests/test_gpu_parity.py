@@ -379,14 +379,16 @@ def test_all_phases_with_groups(ctx, oracle):
 def _both_kernel_families(ctx, oracle, plan_fn, chunk, **kw):
     want = K.chunk_rows(oracle.scan_agg(plan_fn(), chunk, n_threads=4))
     outs = []
-    for force in (False, True):
-        if force:
-            os.environ["SRB_FORCE_GENERIC"] = "1"
+    # static kernel (narrow tile body where the data allows), static kernel with the general body only, generic interpreter
+    for env in (None, "SRB_NO_NARROW", "SRB_FORCE_GENERIC"):
+        if env:
+            os.environ[env] = "1"
         try:
             for dev in (True, False):
                 outs.append(K.chunk_rows(run_gpu(ctx, plan_fn(), chunk, device=dev, **kw)))
         finally:
-            os.environ.pop("SRB_FORCE_GENERIC", None)
+            if env:
+                os.environ.pop(env, None)
     for o in outs:
         assert rows_equal(o, want), (o[:2], want[:2])
 
@@ -425,6 +427,33 @@ def test_q1_overflowing_charge_is_null(ctx, oracle):
     ext = ch.columns[Q.L_EXTENDEDPRICE].data
     ext[::7] = 2**62  # ext*(1-disc) fits int128, times (1+tax) overflows -> NULL rows inside sum(charge)
     ext[5::11] = -2**62
+    _both_kernel_families(ctx, oracle, Q.q1_plan, ch)
+
+
+@pytest.mark.parametrize("case", ["wide_rows", "negative", "discount_above_one", "carries", "carries_filtered"])
+def test_q1_narrow_body_escapes_and_carries(ctx, oracle, case):
+    # The static Q1 kernel runs a narrow tile body (32x32->64 products, plain 64-bit accumulation) while every value of a warp is a
+    # small non-negative integer, and redoes the tile with the general body otherwise. Values around the borders of that assumption:
+    n = 1_500_000
+    ch = T.host_chunk("lineitem", 31, n, T.LINEITEM_Q1)
+    qty, ext = ch.columns[Q.L_QUANTITY].data, ch.columns[Q.L_EXTENDEDPRICE].data
+    disc, tax = ch.columns[Q.L_DISCOUNT].data, ch.columns[Q.L_TAX].data
+    if case == "wide_rows":          # a few rows per many warps leave [0, 2^32)
+        ext[::1999] = 2**32
+        ext[7::4001] = 2**40 + 12345
+        qty[11::997] = 2**33
+    elif case == "negative":
+        qty[::313] = -qty[::313]
+        ext[5::1201] = -ext[5::1201]
+    elif case == "discount_above_one":  # 1 - l_discount < 0
+        disc[::777] = 250
+    else:
+        # products just below 2^64: every accumulator word wraps many times (carries recovered after the fact)
+        ext[:] = 42_000_000
+        disc[:] = 0
+        tax[:] = 4_100_000_000
+        if case == "carries_filtered":  # half the rows fail the shipdate predicate: their adds land in the trash word
+            ch.columns[Q.L_SHIPDATE].data[::2] = Q.from_date(1999, 1, 1)
     _both_kernel_families(ctx, oracle, Q.q1_plan, ch)
 
 
