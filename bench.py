@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--gather", choices=["nccl", "gloo"], default="nccl", help="N > 1, low-cardinality plans: backend of the intermediate-row all-gather")
     return ap.parse_args()
 
 
@@ -194,7 +195,8 @@ def main():
 
         comm = ops.Communicator(ctx, put, get)
         part = ops.Partitioner(ctx, world)
-        host_ex = D.ObjectExchange(dist, rank, world, group=dist.new_group(backend="gloo"))  # a few host rows: no GPU round trip
+        # the <= 4 intermediate rows of a low-cardinality plan: one fixed-size all-gather (NCCL by default; --gather gloo keeps it on the host)
+        host_ex = D.ObjectExchange(dist, rank, world, group=dist.new_group(backend="gloo") if args.gather == "gloo" else None)
 
     def step(collect=None):
         """one pass of the hot path over this rank's shard; at N > 1 it includes the exchange and the phase-2 merge

@@ -745,7 +745,8 @@ private:
     }
 
     // ---- batches ---------------------------------------------------------------------------------------------
-    static constexpr int64_t BATCH = (int64_t)1 << 27;
+    static constexpr int64_t BATCH = (int64_t)1 << 27;     // filter batches (their output buffers are sized per batch)
+    static constexpr int64_t AGG_BATCH = (int64_t)1 << 29; // aggregation batches: the host waits for the counters once per batch
 
     void process_device_range(const ColBind* cols, int64_t n) {
         if (filter_only_) {
@@ -755,13 +756,13 @@ private:
         // The L2-blocked path wants the LARGEST batch memory allows: the table region that is live at any moment is
         // (rows in flight / rows per batch) x table bytes, so more rows per batch means a smaller, L2-resident window and
         // more updates per table sector while it is cached.
-        int64_t batch = BATCH;
+        int64_t batch = AGG_BATCH;
         if (hc_partition_applies(n)) {
             size_t free_b = 0, total_b = 0;
             cudaMemGetInfo(&free_b, &total_b);
             free_b += (size_t)ctx->pool_bytes; // pooled buffers are reusable
             batch = (int64_t)1 << 30;
-            while (batch > BATCH && (size_t)std::min<int64_t>(batch, n) * 17 + ((size_t)1 << 30) > free_b) batch >>= 1;
+            while (batch > AGG_BATCH && (size_t)std::min<int64_t>(batch, n) * 17 + ((size_t)1 << 30) > free_b) batch >>= 1;
         }
         for (int64_t off = 0; off < n; off += batch) {
             int64_t m = std::min<int64_t>(batch, n - off);

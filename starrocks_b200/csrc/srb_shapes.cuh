@@ -1080,7 +1080,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
     }
     __syncthreads();
 
-    uint32_t selected32 = 0; // a thread sees well under 2^32 rows of one launch (a launch covers at most 2^27 rows)
+    uint32_t selected32 = 0; // a thread sees well under 2^32 rows of one launch (a launch covers at most 2^30 rows)
     unsigned long long deferred = 0, inserted = 0;
     if (tid >= THREADS) {
         // ---- producer warp ----
@@ -1112,7 +1112,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
         uint32_t parity = 0;
         const uint32_t full0 = smem_u32(&full_bar[0]), empty0 = smem_u32(&empty_bar[0]);
         const uint8_t* stage = smem; // walks the ring with s
-        const int nt = (int)n_tiles, tstep = (int)gridDim.x; // a launch covers <= 2^27 rows
+        const int nt = (int)n_tiles, tstep = (int)gridDim.x; // a launch covers <= 2^30 rows
         for (int tile = blockIdx.x; tile < nt; tile += tstep) {
             if (S::GMAX > 0 && S::N_KEYS > 0 && my_cnt < G) { // a full directory never changes again
                 // my_cnt steers warp votes below, so it must be ONE value per warp even if the lanes poll at different times
