@@ -46,7 +46,8 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--gather", choices=["nccl", "gloo"], default="nccl", help="N > 1, low-cardinality plans: backend of the intermediate-row all-gather")
+    ap.add_argument("--phase-times", action="store_true", help="add the per-stage host times of a step to the JSON line")
+    ap.add_argument("--gather", choices=["nccl", "gloo", "torch"], default="nccl", help="N > 1, low-cardinality plans: backend of the intermediate-row all-gather")
     return ap.parse_args()
 
 
@@ -195,36 +196,54 @@ def main():
 
         comm = ops.Communicator(ctx, put, get)
         part = ops.Partitioner(ctx, world)
-        # the <= 4 intermediate rows of a low-cardinality plan: one fixed-size all-gather (NCCL by default; --gather gloo keeps it on the host)
-        host_ex = D.ObjectExchange(dist, rank, world, group=dist.new_group(backend="gloo") if args.gather == "gloo" else None)
+        # the <= 4 intermediate rows of a low-cardinality plan: one fixed-slot ncclAllGather inside the library (srb_comm_all_gather on
+        # host chunks); --gather gloo / torch route them through torch.distributed object collectives instead
+        host_ex = comm if args.gather == "nccl" else D.ObjectExchange(dist, rank, world, group=dist.new_group(backend="gloo") if args.gather == "gloo" else None)
+
+    phase_ms = [] if args.phase_times else None  # host wall time between the step's stages (rank 0; a diagnostic, not the metric)
 
     def step(collect=None):
         """one pass of the hot path over this rank's shard; at N > 1 it includes the exchange and the phase-2 merge
         (starrocks_b200/distributed.py: gather for the low-cardinality plans, hash shuffle for the high-cardinality one)"""
         from starrocks_b200 import queries as Q
         two_phase = world > 1 and args.query in ("q1", "highcard")
+        marks = [time.perf_counter()] if phase_ms is not None else None
+
+        def mark():
+            if marks is not None:
+                marks.append(time.perf_counter())
+
         plan = w["plan"](phase=K.AGG_UPDATE_SERIALIZE) if two_phase else w["plan"]()
         op = ops.ScanAggOperator(ctx, plan)
         op.push_chunk(chunk)
         op.set_finishing()
+        mark()
         c, p = None, None
         op2 = None
         if two_phase:
             if args.query == "q1":
                 # <= 4 intermediate rows (AVG states are {sum,count} blobs): a host object gather is the whole exchange
                 inter = op.pull_all()
+                mark()
                 recv = host_ex.all_gather(inter)
+                mark()
                 op2 = ops.ScanAggOperator(ctx, Q.q1_merge_plan(inter))
             else:
                 inter = op.pull_device()
+                mark()
                 grouped, counts = part.run(inter, [0])
                 recv, _ = comm.all_to_all(grouped, counts)
+                mark()
                 op2 = ops.ScanAggOperator(ctx, Q.highcard_merge_plan(group_hint=HIGHCARD_KEYS // world))
             op2.push_chunk(recv)
             op2.set_finishing()
+            mark()
             out = op2.pull_all() if args.query == "q1" else op2.pull_device()
         else:
             out = op.pull_all() if args.query != "highcard" else op.pull_device()
+        mark()
+        if marks is not None:
+            phase_ms.append([(marks[i + 1] - marks[i]) * 1e3 for i in range(len(marks) - 1)])
         n_out = out.n_rows
         c, p = op.counters(), op.profile()
         if op2 is not None:
@@ -307,6 +326,9 @@ def main():
             "clocks": sampler.result(),
             "result_rows": n_out,
         }
+        if phase_ms:
+            timed = phase_ms[-args.steps:]
+            result["phase_ms_rank0"] = [sum(t[i] for t in timed) / len(timed) for i in range(len(timed[0]))]
     # ---- e2e: the same pipeline fed from pinned host buffers through the C ABI ------------------------------------------------
     if not args.no_e2e:
         e2e = run_e2e(args, ctx, w, chunk, rows, dev, rank, world)

@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "srb_dev.cuh"
 #include "srb_host.h"
@@ -199,6 +200,14 @@ struct srb_comm {
     PinnedBuf counts_host;
     std::vector<srb_column> cview;
     std::vector<int32_t> slots;
+    // host-chunk gather (a few intermediate rows): wire buffers and the concatenated result
+    DevBuf wire_dev;
+    PinnedBuf wire_host;
+    struct HostOut {
+        std::vector<uint8_t> data, nulls;
+        std::vector<uint32_t> offsets;
+    };
+    std::vector<HostOut> hout;
 };
 
 // the C ABI's error string lives in srb_capi.cu; exchange entry points report through the same convention
@@ -216,6 +225,139 @@ void set_last_error(const std::string& s);
         srb::set_last_error(e.what());        \
         return SRB_INTERNAL_ERROR;            \
     }
+
+// Host chunks (any column kind, binary included): the few intermediate rows of a low-cardinality aggregation. Each rank
+// serialises its chunk as [n_rows][per column: data bytes][payload: data | nulls | offsets], the blobs travel in ONE
+// fixed-slot ncclAllGather when every rank's fits SMALL_SLOT (a second, exactly sized one otherwise), and the columns are
+// concatenated in rank order into buffers owned by the communicator (valid until its next call).
+static constexpr size_t SMALL_SLOT = 16 << 10;
+
+static size_t host_col_data_bytes(const srb_chunk* ch, const srb_column& sc) {
+    const int w = type_width(sc.type);
+    const size_t n = (size_t)ch->n_rows;
+    return w ? n * (size_t)w : (n ? (size_t)(sc.offsets[n] - sc.offsets[0]) : 0);
+}
+static size_t host_chunk_wire_bytes(const srb_chunk* ch) {
+    size_t b = 8 + (size_t)ch->n_cols * 8;
+    const size_t n = (size_t)ch->n_rows;
+    for (int col = 0; col < ch->n_cols; col++) {
+        const srb_column& sc = ch->cols[col];
+        b += host_col_data_bytes(ch, sc) + (sc.nulls ? n : 0);
+        if (type_width(sc.type) == 0) b += 4 + (n + 1) * 4; // offsets, 4-byte aligned inside the blob
+    }
+    return (b + 15) & ~(size_t)15;
+}
+static void host_chunk_write(const srb_chunk* ch, uint8_t* dst) {
+    const size_t n = (size_t)ch->n_rows;
+    int64_t* hdr = (int64_t*)dst;
+    hdr[0] = (int64_t)n;
+    uint8_t* p = dst + 8 + (size_t)ch->n_cols * 8;
+    for (int col = 0; col < ch->n_cols; col++) {
+        const srb_column& sc = ch->cols[col];
+        const bool binary = type_width(sc.type) == 0;
+        const uint32_t base = (binary && n) ? sc.offsets[0] : 0;
+        const size_t data = host_col_data_bytes(ch, sc);
+        hdr[1 + col] = (int64_t)data | (sc.nulls ? (int64_t)1 << 62 : 0); // bit 62: a null map follows the data
+        if (data) memcpy(p, (const uint8_t*)sc.data + base, data);
+        p += data;
+        if (sc.nulls) {
+            if (n) memcpy(p, sc.nulls, n);
+            p += n;
+        }
+        if (binary) { // offsets rebased to 0
+            uint32_t* o = (uint32_t*)(dst + (((size_t)(p - dst) + 3) & ~(size_t)3));
+            o[0] = 0;
+            for (size_t r = 1; r <= n; r++) o[r] = sc.offsets[r] - base;
+            p = (uint8_t*)(o + n + 1);
+        }
+    }
+}
+static void gather_host_chunk(srb_comm* c, const srb_chunk* mine, srb_chunk* out) {
+    const int W = c->world;
+    for (int col = 0; col < mine->n_cols; col++) {
+        const srb_column& sc = mine->cols[col];
+        if (type_width(sc.type) == 0 && mine->n_rows && !sc.offsets) throw Error(SRB_INVALID_ARGUMENT, "binary column without offsets");
+        if (mine->n_rows && !sc.data && type_width(sc.type) != 0) throw Error(SRB_INVALID_ARGUMENT, "null data pointer");
+    }
+    const size_t need = host_chunk_wire_bytes(mine);
+    size_t slot = SMALL_SLOT;
+    auto exchange = [&](size_t slot_bytes, bool with_payload) {
+        c->wire_host.ensure(slot_bytes * (size_t)(W + 1));
+        c->wire_dev.ensure(c->ctx, slot_bytes * (size_t)(W + 1));
+        uint8_t* h = c->wire_host.as<uint8_t>();
+        ((int64_t*)h)[0] = (int64_t)need; // first word of the slot: this rank's blob size; second: its column count
+        ((int64_t*)h)[1] = (int64_t)mine->n_cols;
+        if (with_payload) host_chunk_write(mine, h + 16);
+        uint8_t* d = c->wire_dev.as<uint8_t>();
+        SRB_CUDA(cudaMemcpyAsync(d, h, with_payload ? 16 + need : 16, cudaMemcpyHostToDevice, c->stream));
+        SRB_NCCL(nccl().AllGather(d, d + slot_bytes, slot_bytes, ncclUint8_, c->comm, c->stream));
+        SRB_CUDA(cudaMemcpyAsync(h + slot_bytes, d + slot_bytes, slot_bytes * (size_t)W, cudaMemcpyDeviceToHost, c->stream));
+        SRB_CUDA(cudaStreamSynchronize(c->stream));
+    };
+    exchange(slot, 16 + need <= SMALL_SLOT);
+    size_t max_need = 0;
+    for (int r = 0; r < W; r++) {
+        const int64_t* head = (const int64_t*)(c->wire_host.as<uint8_t>() + slot * (size_t)(r + 1));
+        max_need = std::max(max_need, (size_t)head[0]);
+        if (head[1] != (int64_t)mine->n_cols) throw Error(SRB_INVALID_ARGUMENT, fmt("all-gather: rank %d sent %d columns, this rank %d", r, (int)head[1], mine->n_cols));
+    }
+    if (16 + max_need > SMALL_SLOT) { // some rank did not fit: every rank sees that and repeats with an exactly sized slot
+        slot = (16 + max_need + 255) & ~(size_t)255;
+        exchange(slot, true);
+    }
+    // concatenate in rank order; a column has a null map in the result when any rank sent one
+    c->hout.assign((size_t)mine->n_cols, srb_comm::HostOut{});
+    std::vector<char> any_nulls((size_t)mine->n_cols, 0);
+    for (int r = 0; r < W; r++) {
+        const int64_t* hdr = (const int64_t*)(c->wire_host.as<uint8_t>() + slot * (size_t)(r + 1) + 16);
+        for (int col = 0; col < mine->n_cols; col++) any_nulls[(size_t)col] |= (char)((hdr[1 + col] >> 62) & 1);
+    }
+    int64_t total = 0;
+    for (int r = 0; r < W; r++) {
+        const uint8_t* blob = c->wire_host.as<uint8_t>() + slot * (size_t)(r + 1) + 16;
+        const int64_t* hdr = (const int64_t*)blob;
+        const size_t n = (size_t)hdr[0];
+        const uint8_t* p = blob + 8 + (size_t)mine->n_cols * 8;
+        for (int col = 0; col < mine->n_cols; col++) {
+            srb_comm::HostOut& o = c->hout[(size_t)col];
+            const size_t data = (size_t)(hdr[1 + col] & (((int64_t)1 << 62) - 1));
+            const uint32_t byte_base = (uint32_t)o.data.size();
+            o.data.insert(o.data.end(), p, p + data);
+            p += data;
+            if ((hdr[1 + col] >> 62) & 1) {
+                o.nulls.insert(o.nulls.end(), p, p + n);
+                p += n;
+            } else if (any_nulls[(size_t)col]) {
+                o.nulls.insert(o.nulls.end(), n, (uint8_t)0);
+            }
+            if (type_width(mine->cols[col].type) == 0) {
+                const uint32_t* off = (const uint32_t*)(blob + (((size_t)(p - blob) + 3) & ~(size_t)3));
+                if (o.offsets.empty()) o.offsets.push_back(0);
+                for (size_t i = 1; i <= n; i++) o.offsets.push_back(byte_base + off[i]);
+                p = (const uint8_t*)(off + n + 1);
+            }
+        }
+        total += (int64_t)n;
+    }
+    c->cview.assign(mine->cols, mine->cols + mine->n_cols);
+    c->slots.assign(mine->slot_ids, mine->slot_ids + mine->n_cols);
+    for (int col = 0; col < mine->n_cols; col++) {
+        srb_comm::HostOut& o = c->hout[(size_t)col];
+        const bool binary = type_width(mine->cols[col].type) == 0;
+        if (binary && o.offsets.empty()) o.offsets.push_back(0);
+        const size_t used = o.data.size();
+        o.data.resize(used + 16); // BinaryColumn readers may touch 16 bytes past the end (column/bytes.h:27)
+        c->cview[col].data = o.data.data();
+        c->cview[col].nulls = any_nulls[(size_t)col] ? o.nulls.data() : nullptr;
+        c->cview[col].offsets = binary ? o.offsets.data() : nullptr;
+        c->cview[col].n_bytes = binary ? (int64_t)used : 0;
+        c->cview[col].mem_kind = SRB_MEM_HOST;
+    }
+    out->n_rows = total;
+    out->n_cols = mine->n_cols;
+    out->slot_ids = c->slots.data();
+    out->cols = c->cview.data();
+}
 
 extern "C" {
 
@@ -423,6 +565,12 @@ srb_status srb_comm_all_gather(srb_comm* c, const srb_chunk* mine, srb_chunk* ou
     if (!c || !mine || !out) throw Error(SRB_INVALID_ARGUMENT, "null argument");
     SRB_CUDA(cudaSetDevice(c->ctx->cfg.device));
     const int W = c->world;
+    bool all_host = mine->n_cols > 0;
+    for (int col = 0; col < mine->n_cols; col++) all_host = all_host && mine->cols[col].mem_kind == SRB_MEM_HOST;
+    if (all_host) {
+        gather_host_chunk(c, mine, out);
+        return SRB_OK;
+    }
     int64_t* hc = c->counts_host.as<int64_t>();
     int64_t* dc = c->counts_dev.as<int64_t>();
     hc[0] = mine->n_rows;

@@ -399,10 +399,13 @@ class Communicator:
         return _raw_chunk(out), list(rc)
 
     def all_gather(self, chunk: K.Chunk) -> K.Chunk:
+        """Every rank's rows on every rank, rank 0 first. Device chunks (fixed-width columns) stay on the device; host chunks
+        (any column kind: the few intermediate rows of a low-cardinality plan) come back as host chunks."""
         cch, keep = chunk.to_c()
         out = K.srb_chunk()
         _check(self.L.srb_comm_all_gather(self.h, C.byref(cch), C.byref(out)))
-        return _raw_chunk(out)
+        on_host = chunk.columns and all(c.mem_kind == K.MEM_HOST for c in chunk.columns.values())
+        return K.decode_chunk(out) if on_host else _raw_chunk(out)
 
     def close(self):
         if self.h:

@@ -66,6 +66,20 @@ def test_single_rank_communicator_round_trip(ctx):
         assert K.chunk_rows(ctx.fetch_chunk(recv), sort=False) == K.chunk_rows(ch, sort=False)
         allg = comm.all_gather(dch)
         assert K.chunk_rows(ctx.fetch_chunk(allg), sort=False) == K.chunk_rows(ch, sort=False)
+        # host chunks of any column kind (the intermediate rows of a low-cardinality plan: DECIMAL128 sums, {sum,count} blobs, nullable)
+        li = T.host_chunk("lineitem", 0, 50_000, T.LINEITEM_Q1)
+        op = ops.ScanAggOperator(ctx, Q.q1_plan(phase=K.AGG_UPDATE_SERIALIZE))
+        op.push_chunk(li)
+        op.set_finishing()
+        inter = op.pull_all()
+        op.close()
+        assert any(K.is_binary(c.type) for c in inter.columns.values())
+        got = comm.all_gather(inter)
+        assert K.chunk_rows(got, sort=False) == K.chunk_rows(inter, sort=False)
+        empty = ops.slice_chunk(inter, 0, 0)
+        assert comm.all_gather(empty).n_rows == 0
+        big = D.concat_chunks([inter] * 400)  # > the 16 KB fixed slot: the exactly sized second collective
+        assert K.chunk_rows(comm.all_gather(big), sort=False) == K.chunk_rows(big, sort=False)
     finally:
         comm.close()
         for p in ptrs:
@@ -114,8 +128,22 @@ def _worker(rank, world, port, n_rows, n_keys, out_q):
         op2.push_chunk(recv)
         op2.set_finishing()
         rows = K.chunk_rows(op2.pull_all())
-        out_q.put((rank, rows))
-        for o in (op1, op2):
+        # low-cardinality plan: phase 1 on the rank's lineitem rows, host gather of the <= 4 intermediate rows, phase 2 everywhere
+        lb, le = D.shard_range(n_rows, rank, world)
+        li = T.host_chunk("lineitem", lb, le - lb, T.LINEITEM_Q1)
+        if rank == 1:
+            li = ops.slice_chunk(li, 0, 0)  # a rank without rows still takes part in the gather
+        op3 = ops.ScanAggOperator(ctx, Q.q1_plan(phase=K.AGG_UPDATE_SERIALIZE))
+        op3.push_chunk(li)
+        op3.set_finishing()
+        inter3 = op3.pull_all()
+        everyone = comm.all_gather(inter3)
+        op4 = ops.ScanAggOperator(ctx, Q.q1_merge_plan(inter3))
+        op4.push_chunk(everyone)
+        op4.set_finishing()
+        q1_rows = K.chunk_rows(op4.pull_all())
+        out_q.put((rank, (rows, q1_rows)))
+        for o in (op1, op2, op3, op4):
             o.close()
         part.close()
         comm.close()
@@ -145,5 +173,9 @@ def test_two_gpu_highcard_two_phase(oracle):
         assert p.exitcode == 0
     whole = T.host_chunk("highcard", 0, n, ["k", "v"], n_keys=nk)
     want = K.chunk_rows(oracle.scan_agg(Q.highcard_plan(), whole))
-    assert not ({r[0] for r in res[0]} & {r[0] for r in res[1]})
-    assert sorted(res[0] + res[1]) == want
+    hc = {r: res[r][0] for r in res}
+    assert not ({r[0] for r in hc[0]} & {r[0] for r in hc[1]})
+    assert sorted(hc[0] + hc[1]) == want
+    b0, e0 = D.shard_range(n, 0, world)
+    want_q1 = K.chunk_rows(oracle.scan_agg(Q.q1_plan(), T.host_chunk("lineitem", b0, e0 - b0, T.LINEITEM_Q1)))
+    assert res[0][1] == want_q1 and res[1][1] == want_q1
