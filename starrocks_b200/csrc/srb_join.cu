@@ -193,6 +193,201 @@ __global__ void __launch_bounds__(256) k_join_gather(const __grid_constant__ Gat
     }
 }
 
+// ---- the tiled probe: at most one match per probe row ---------------------------------------------------------------------------
+// Joins against a key (every TPC-H / SSB join of the configs: the build side is a primary key or a filtered slice of one) and
+// LEFT SEMI joins produce at most one output row per probe row. Then the probe is two streaming passes over the probe rows:
+//   pass A  per row, the build index of its match (0 = none) into match[], and the number of matches per 2048-row tile;
+//           a thread walks the chains of its 8 rows round by round, so 8 independent loads are in flight per thread;
+//   scan    exclusive prefix of the tile counts (the output offset of every tile, and the output size for the host);
+//   pass B  per tile, matched rows ranked in row order and the output columns written straight from the probe columns
+//           (row r) and the build columns (match[r]) — no (probe_index, build_index) arrays unless the plan asks for them,
+//           no separate gather kernel, and the output keeps the probe row order like the reference's probe loop.
+// k_join_unique decides after the build whether the table qualifies for INNER joins.
+constexpr int JT_THREADS = 256, JT_ROWS = 8, JT_TILE = JT_THREADS * JT_ROWS;
+
+// sets *dup when two build rows carry the same key (checked per row against the rest of its chain)
+__global__ void __launch_bounds__(256) k_join_unique(JTable t, unsigned int* __restrict__ dup) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x + 1; i <= t.rows; i += gridDim.x * blockDim.x) {
+        if (t.key_null[i - 1]) continue;
+        uint64_t lo, hi;
+        jload(t.keys, t.width, i - 1, &lo, &hi);
+        for (uint32_t bi = t.next[i]; bi; bi = t.next[bi]) {
+            uint64_t blo, bhi;
+            jload(t.keys, t.width, bi - 1, &blo, &bhi);
+            if (blo == lo && bhi == hi) {
+                *dup = 1u;
+                return;
+            }
+        }
+    }
+}
+
+template <int W>
+SRB_D void jload_w(const uint8_t* keys, int64_t i, uint64_t* lo, uint64_t* hi) {
+    *hi = 0;
+    if constexpr (W == 4)
+        *lo = ((const uint32_t*)keys)[i];
+    else if constexpr (W == 8)
+        *lo = ((const uint64_t*)keys)[i];
+    else {
+        const ulonglong2 v = ((const ulonglong2*)keys)[i];
+        *lo = v.x;
+        *hi = v.y;
+    }
+}
+template <int W>
+SRB_D uint32_t jbucket_w(const JTable& t, uint64_t lo, uint64_t hi) {
+    if constexpr (W == 4) return join_key_hash32((uint32_t)lo, t.log_bucket);
+    if constexpr (W == 8) return join_key_hash64(lo, t.log_bucket);
+    return join_key_hash128(lo, hi, t.bucket_size);
+}
+
+template <int W>
+__global__ void __launch_bounds__(JT_THREADS) k_join_probe_first(JTable t, const uint8_t* __restrict__ pkeys, const uint8_t* __restrict__ pnull, int64_t n,
+                                                                  uint32_t* __restrict__ match, uint32_t* __restrict__ tile_counts) {
+    __shared__ uint32_t warp_cnt[JT_THREADS / 32];
+    const int64_t n_tiles = (n + JT_TILE - 1) / JT_TILE;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        uint64_t lo[JT_ROWS], hi[JT_ROWS];
+        uint32_t bi[JT_ROWS], m[JT_ROWS];
+        bool any = false;
+#pragma unroll
+        for (int j = 0; j < JT_ROWS; j++) {
+            const int64_t r = tile * JT_TILE + j * JT_THREADS + threadIdx.x;
+            bi[j] = m[j] = 0;
+            lo[j] = hi[j] = 0;
+            if (r < n && !(pnull && pnull[r])) {
+                jload_w<W>(pkeys, r, &lo[j], &hi[j]);
+                bi[j] = t.first[jbucket_w<W>(t, lo[j], hi[j])];
+            }
+            any = any || bi[j] != 0;
+        }
+        while (any) { // one chain step of every row per round
+            any = false;
+#pragma unroll
+            for (int j = 0; j < JT_ROWS; j++) {
+                if (bi[j]) {
+                    uint64_t blo, bhi;
+                    jload_w<W>(t.keys, bi[j] - 1, &blo, &bhi);
+                    if (blo == lo[j] && (W < 16 || bhi == hi[j])) {
+                        m[j] = bi[j];
+                        bi[j] = 0;
+                    } else {
+                        bi[j] = t.next[bi[j]];
+                    }
+                    any = any || bi[j] != 0;
+                }
+            }
+        }
+        uint32_t cnt = 0;
+#pragma unroll
+        for (int j = 0; j < JT_ROWS; j++) {
+            const int64_t r = tile * JT_TILE + j * JT_THREADS + threadIdx.x;
+            if (r < n) match[r] = m[j];
+            cnt += m[j] ? 1u : 0u;
+        }
+        for (int o = 16; o > 0; o >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, o);
+        if ((threadIdx.x & 31) == 0) warp_cnt[threadIdx.x >> 5] = cnt;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t s = 0;
+            for (int w = 0; w < JT_THREADS / 32; w++) s += warp_cnt[w];
+            tile_counts[tile] = s;
+        }
+        __syncthreads();
+    }
+}
+
+// exclusive prefix of the tile counts (one block; the count of tiles is rows / 2048) and the grand total
+__global__ void __launch_bounds__(1024) k_join_scan(const uint32_t* __restrict__ counts, uint64_t* __restrict__ offsets, int64_t n_tiles,
+                                                     unsigned long long* __restrict__ total) {
+    __shared__ uint64_t warp_sum[32];
+    __shared__ uint64_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t base = 0; base < n_tiles; base += 1024) {
+        const int64_t i = base + threadIdx.x;
+        const uint64_t v = i < n_tiles ? counts[i] : 0;
+        uint64_t x = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint64_t y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_sum[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            uint64_t w = warp_sum[lane];
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint64_t y = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += y;
+            }
+            warp_sum[lane] = w; // inclusive over warps
+        }
+        __syncthreads();
+        const uint64_t before = carry + (warp ? warp_sum[warp - 1] : 0) + (x - v);
+        if (i < n_tiles) offsets[i] = before;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = before + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = carry;
+}
+
+// pass B: rank the tile's matched rows in row order and write the output columns (and, when asked, the index pairs)
+__global__ void __launch_bounds__(JT_THREADS) k_join_emit(const __grid_constant__ GatherArgs g, int64_t n, const uint32_t* __restrict__ match,
+                                                           const uint64_t* __restrict__ tile_offsets, uint32_t* __restrict__ out_probe,
+                                                           uint32_t* __restrict__ out_build) {
+    __shared__ uint32_t warp_cnt[JT_THREADS / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t n_tiles = (n + JT_TILE - 1) / JT_TILE;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        uint64_t base = tile_offsets[tile];
+        uint32_t m[JT_ROWS];
+#pragma unroll
+        for (int j = 0; j < JT_ROWS; j++) {
+            const int64_t r = tile * JT_TILE + j * JT_THREADS + threadIdx.x;
+            m[j] = r < n ? match[r] : 0;
+        }
+#pragma unroll
+        for (int j = 0; j < JT_ROWS; j++) { // slab j = 256 consecutive rows
+            const unsigned b = __ballot_sync(0xffffffffu, m[j] != 0);
+            if (lane == 0) warp_cnt[warp] = __popc(b);
+            __syncthreads();
+            uint32_t before = 0, slab = 0;
+#pragma unroll
+            for (int w = 0; w < JT_THREADS / 32; w++) {
+                const uint32_t c = warp_cnt[w];
+                before += w < warp ? c : 0;
+                slab += c;
+            }
+            __syncthreads();
+            if (m[j]) {
+                const int64_t r = tile * JT_TILE + j * JT_THREADS + threadIdx.x;
+                const uint64_t pos = base + before + __popc(b & ((1u << lane) - 1));
+                const size_t bi = m[j] - 1;
+                for (int c = 0; c < g.n_cols; c++) {
+                    const GatherCol& gc = g.cols[c];
+                    const size_t s = gc.from_build ? bi : (size_t)r;
+                    switch (gc.width) {
+                    case 1: gc.dst[pos] = gc.src[s]; break;
+                    case 2: ((uint16_t*)gc.dst)[pos] = ((const uint16_t*)gc.src)[s]; break;
+                    case 4: ((uint32_t*)gc.dst)[pos] = ((const uint32_t*)gc.src)[s]; break;
+                    case 8: ((uint64_t*)gc.dst)[pos] = ((const uint64_t*)gc.src)[s]; break;
+                    default: ((ulonglong2*)gc.dst)[pos] = ((const ulonglong2*)gc.src)[s];
+                    }
+                    if (gc.src_null) gc.dst_null[pos] = gc.src_null[s];
+                }
+                if (out_probe) {
+                    out_probe[pos] = (uint32_t)r;
+                    out_build[pos] = m[j];
+                }
+            }
+            base += slab;
+        }
+    }
+}
+
 // =================================================================================================================
 struct GrowCol { // device column that grows by appends
     DevBuf data, nulls;
@@ -304,6 +499,10 @@ public:
         if (n == 0 || build_rows_ == 0) return;
         int pw = total <= 4 ? 4 : (total <= 8 ? 8 : 16);
         if (total > 16 || pw != width_) throw Error(SRB_INVALID_ARGUMENT, "probe key width does not match the build key width");
+        if (unique_ && !force_general_) {
+            probe_tiled(n, data, nulls);
+            return;
+        }
         // pack probe keys
         JPackArgs pa{};
         pa.n_keys = (int)pkeys_.size();
@@ -333,6 +532,18 @@ public:
                                                    total_dev_.as<unsigned long long>(), oprobe_.as<uint32_t>(), obuild_.as<uint32_t>());
         launches++;
         // K8 gather
+        GatherArgs ga = describe_outputs(m, data, nulls);
+        if (ga.n_cols) {
+            k_join_gather<<<grid_for(m), 256, 0, stream>>>(ga, m, oprobe_.as<uint32_t>(), obuild_.as<uint32_t>());
+            launches++;
+        }
+        SRB_CUDA(cudaGetLastError());
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        out_rows_ = m;
+    }
+
+    // output columns for m rows: probe_out columns (from the pushed chunk) then build_out columns (from the build side)
+    GatherArgs describe_outputs(int64_t m, const std::vector<const uint8_t*>& data, const std::vector<const uint8_t*>& nulls) {
         GatherArgs ga{};
         ocols_.resize(pout_.size() + bout_.size());
         for (size_t i = 0; i < ocols_.size(); i++) {
@@ -352,8 +563,59 @@ public:
             ga.cols[i] = GatherCol{sdata, o.data.as<uint8_t>(), snull, o.nullable ? o.nulls.as<uint8_t>() : nullptr, o.width, fb ? 1 : 0};
         }
         ga.n_cols = (int)ocols_.size();
-        if (ga.n_cols) {
-            k_join_gather<<<grid_for(m), 256, 0, stream>>>(ga, m, oprobe_.as<uint32_t>(), obuild_.as<uint32_t>());
+        return ga;
+    }
+
+    // at most one match per probe row (unique build keys, or LEFT SEMI): two streaming passes, output in probe row order
+    void probe_tiled(int64_t n, const std::vector<const uint8_t*>& data, const std::vector<const uint8_t*>& nulls) {
+        const uint8_t* keys = nullptr;
+        const uint8_t* knull = nullptr;
+        if (pkeys_.size() == 1 && pcols_[0].width == width_) { // a single 4/8/16-byte key column is its own packed form
+            keys = data[0];
+            knull = nulls[0];
+        } else {
+            JPackArgs pa{};
+            pa.n_keys = (int)pkeys_.size();
+            pa.width = width_;
+            for (size_t k = 0; k < pkeys_.size(); k++) pa.cols[k] = JKeyCol{data[k], nulls[k], pcols_[k].width, 0};
+            ppacked_.ensure(ctx, (size_t)n * width_);
+            pnull_.ensure(ctx, (size_t)n);
+            k_join_pack<<<grid_for(n), 256, 0, stream>>>(pa, n, ppacked_.as<uint8_t>(), pnull_.as<uint8_t>());
+            launches++;
+            keys = ppacked_.as<uint8_t>();
+            knull = pnull_.as<uint8_t>();
+        }
+        const int64_t tiles = (n + JT_TILE - 1) / JT_TILE;
+        const int grid = (int)std::min<int64_t>(tiles, (int64_t)ctx->n_sms * 8);
+        match_.ensure(ctx, (size_t)n * 4);
+        tcounts_.ensure(ctx, (size_t)tiles * 4);
+        toffs_.ensure(ctx, (size_t)tiles * 8);
+        JTable t = table();
+        uint32_t* match = match_.as<uint32_t>();
+        uint32_t* tc = tcounts_.as<uint32_t>();
+        if (width_ == 4)
+            k_join_probe_first<4><<<grid, JT_THREADS, 0, stream>>>(t, keys, knull, n, match, tc);
+        else if (width_ == 8)
+            k_join_probe_first<8><<<grid, JT_THREADS, 0, stream>>>(t, keys, knull, n, match, tc);
+        else
+            k_join_probe_first<16><<<grid, JT_THREADS, 0, stream>>>(t, keys, knull, n, match, tc);
+        k_join_scan<<<1, 1024, 0, stream>>>(tc, toffs_.as<uint64_t>(), tiles, total_dev_.as<unsigned long long>());
+        SRB_CUDA(cudaMemcpyAsync(total_host_.p, total_dev_.p, 8, cudaMemcpyDeviceToHost, stream));
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        launches += 2;
+        const int64_t m = (int64_t)*total_host_.as<unsigned long long>();
+        rows_selected += m;
+        if (m == 0) return;
+        GatherArgs ga = describe_outputs(m, data, nulls);
+        uint32_t *op = nullptr, *ob = nullptr;
+        if (emit_indexes_) {
+            oprobe_.ensure(ctx, (size_t)m * 4);
+            obuild_.ensure(ctx, (size_t)m * 4);
+            op = oprobe_.as<uint32_t>();
+            ob = obuild_.as<uint32_t>();
+        }
+        if (ga.n_cols || emit_indexes_) {
+            k_join_emit<<<grid, JT_THREADS, 0, stream>>>(ga, n, match, toffs_.as<uint64_t>(), op, ob);
             launches++;
         }
         SRB_CUDA(cudaGetLastError());
@@ -504,9 +766,16 @@ private:
             k_join_pack<<<grid_for(n), 256, 0, stream>>>(pa, n, bpacked_.as<uint8_t>(), bnull_.as<uint8_t>());
             k_join_build<<<grid_for(n), 256, 0, stream>>>(table());
             launches += 2;
+            if (!semi_) { // does any key occur twice? (decides whether INNER probes may take the one-match-per-row path)
+                SRB_CUDA(cudaMemsetAsync(total_dev_.p, 0, 8, stream));
+                k_join_unique<<<grid_for(n), 256, 0, stream>>>(table(), total_dev_.as<unsigned int>());
+                SRB_CUDA(cudaMemcpyAsync(total_host_.p, total_dev_.p, 8, cudaMemcpyDeviceToHost, stream));
+                launches++;
+            }
         }
         SRB_CUDA(cudaGetLastError());
         SRB_CUDA(cudaStreamSynchronize(stream));
+        unique_ = semi_ || n == 0 || *total_host_.as<unsigned int>() == 0;
     }
     JTable table() {
         JTable t;
@@ -528,7 +797,9 @@ private:
     int64_t build_rows_ = 0, probe_rows_in_ = 0;
     int width_ = 0;
     uint32_t bucket_size_ = 0, log_bucket_ = 0;
-    DevBuf bpacked_, bnull_, first_, next_, ppacked_, pnull_, oprobe_, obuild_, total_dev_;
+    DevBuf bpacked_, bnull_, first_, next_, ppacked_, pnull_, oprobe_, obuild_, total_dev_, match_, tcounts_, toffs_;
+    bool unique_ = false;                                               // no key occurs twice on the build side (or LEFT SEMI)
+    bool force_general_ = getenv("SRB_JOIN_GENERAL") != nullptr;        // test hook: the chain-walking two-pass probe for every join
     PinnedBuf total_host_;
     int64_t out_rows_ = 0, out_pos_ = 0;
     std::vector<std::vector<uint8_t>> hdata_, hnull_;

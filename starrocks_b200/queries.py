@@ -36,6 +36,13 @@ O_ORDERKEY, O_CUSTKEY, O_ORDERDATE, O_SHIPPRIORITY = 20, 21, 22, 23
 C_CUSTKEY, C_MKTSEGMENT_CODE = 30, 31
 # high-cardinality table
 HC_K, HC_V = 40, 41
+# SSB star schema (test/common/sql/ssb/create.sql: every key and measure is INT; the VARCHAR attributes the query touches
+# are carried as dictionary codes, as the low-cardinality dictionary rewrite does)
+LO_CUSTKEY, LO_PARTKEY, LO_SUPPKEY, LO_ORDERDATE, LO_REVENUE, LO_SUPPLYCOST = 50, 51, 52, 53, 54, 55
+SC_CUSTKEY, SC_NATION_CODE, SC_REGION_CODE = 60, 61, 62
+SS_SUPPKEY, SS_REGION_CODE = 65, 66
+SP_PARTKEY, SP_MFGR_CODE = 70, 71
+SD_DATEKEY, SD_YEAR = 75, 76
 
 D64 = K.TYPE_DECIMAL64
 D128 = K.TYPE_DECIMAL128
@@ -151,3 +158,58 @@ def q3_agg_plan(group_hint: int = 0) -> ScanAggPlan:
     omd = e.sub(one, disc, D64, 16)
     rev = e.mul(e.cast(ext, D128, 15, 2), e.cast(omd, D128, 16, 2), D128, 31)
     return ScanAggPlan(exprs=e, keys=[ok, od, sp], aggs=[(K.AGG_SUM, rev)], group_hint=group_hint)
+
+
+# ---- SSB Q4.1: lineorder |><| supplier |><| customer |><| part |><| dates -> group by d_year, c_nation ----------------------
+#   select d_year, c_nation, sum(lo_revenue - lo_supplycost) as profit from dates, customer, supplier, part, lineorder
+#   where lo_custkey = c_custkey and lo_suppkey = s_suppkey and lo_partkey = p_partkey and lo_orderdate = d_datekey
+#     and c_region = 'AMERICA' and s_region = 'AMERICA' and (p_mfgr = 'MFGR#1' or p_mfgr = 'MFGR#2') group by d_year, c_nation
+# The dimensions are filtered, then replicated on every GPU (broadcast join); lineorder is range-partitioned and probes them in turn.
+REGION_AMERICA = 1  # code of 'AMERICA' in tpch_synth.REGIONS
+MFGR_1, MFGR_2 = 0, 1
+
+
+def ssb_customer_filter() -> ScanAggPlan:
+    return filter_plan([pred(SC_REGION_CODE, K.PRED_EQ, K.TYPE_INT, REGION_AMERICA)], [SC_CUSTKEY, SC_NATION_CODE])
+
+
+def ssb_supplier_filter() -> ScanAggPlan:
+    return filter_plan([pred(SS_REGION_CODE, K.PRED_EQ, K.TYPE_INT, REGION_AMERICA)], [SS_SUPPKEY])
+
+
+def ssb_part_filter() -> ScanAggPlan:
+    return filter_plan([pred(SP_MFGR_CODE, K.PRED_EQ, K.TYPE_INT, MFGR_1, or_group=1), pred(SP_MFGR_CODE, K.PRED_EQ, K.TYPE_INT, MFGR_2, or_group=1)],
+                       [SP_PARTKEY])
+
+
+def ssb_join_supplier() -> JoinPlan:
+    return JoinPlan([SS_SUPPKEY], [LO_SUPPKEY], build_out=[], probe_out=[LO_CUSTKEY, LO_PARTKEY, LO_ORDERDATE, LO_REVENUE, LO_SUPPLYCOST])
+
+
+def ssb_join_customer() -> JoinPlan:
+    return JoinPlan([SC_CUSTKEY], [LO_CUSTKEY], build_out=[SC_NATION_CODE], probe_out=[LO_PARTKEY, LO_ORDERDATE, LO_REVENUE, LO_SUPPLYCOST])
+
+
+def ssb_join_part() -> JoinPlan:
+    return JoinPlan([SP_PARTKEY], [LO_PARTKEY], build_out=[], probe_out=[SC_NATION_CODE, LO_ORDERDATE, LO_REVENUE, LO_SUPPLYCOST])
+
+
+def ssb_join_dates() -> JoinPlan:
+    return JoinPlan([SD_DATEKEY], [LO_ORDERDATE], build_out=[SD_YEAR], probe_out=[SC_NATION_CODE, LO_REVENUE, LO_SUPPLYCOST])
+
+
+def ssb_q41_agg_plan(phase: int = K.AGG_UPDATE_FINALIZE, group_hint: int = 64) -> ScanAggPlan:
+    """group by d_year, c_nation; sum(lo_revenue - lo_supplycost): INT - INT is computed in BIGINT, the sum is BIGINT"""
+    e = ExprBuilder()
+    year = e.slot(SD_YEAR, K.TYPE_INT)
+    nation = e.slot(SC_NATION_CODE, K.TYPE_INT)
+    rev = e.cast(e.slot(LO_REVENUE, K.TYPE_INT), K.TYPE_BIGINT)
+    cost = e.cast(e.slot(LO_SUPPLYCOST, K.TYPE_INT), K.TYPE_BIGINT)
+    return ScanAggPlan(exprs=e, keys=[year, nation], aggs=[(K.AGG_SUM, e.sub(rev, cost, K.TYPE_BIGINT))], phase=phase, group_hint=group_hint)
+
+
+def ssb_q41_merge_plan(group_hint: int = 64) -> ScanAggPlan:
+    e = ExprBuilder()
+    year = e.slot(0, K.TYPE_INT)
+    nation = e.slot(1, K.TYPE_INT)
+    return ScanAggPlan(exprs=e, keys=[year, nation], aggs=[(K.AGG_SUM, e.slot(2, K.TYPE_BIGINT))], phase=K.AGG_MERGE_FINALIZE, group_hint=group_hint)

@@ -19,6 +19,9 @@ SEED = 0x5EED0000
 MKTSEGMENTS = [b"AUTOMOBILE", b"BUILDING", b"FURNITURE", b"HOUSEHOLD", b"MACHINERY"]
 RETURNFLAGS = [b"A", b"N", b"R"]
 LINESTATUS = [b"F", b"O"]
+REGIONS = [b"AFRICA", b"AMERICA", b"ASIA", b"EUROPE", b"MIDDLE EAST"]  # SSB: 5 regions x 5 nations, 5 manufacturers
+SSB_DATE_LO = Q.from_date(1992, 1, 1)  # the dates dimension: 2556 days, 1992-01-01 .. 1998-12-30
+SSB_DAYS = 2556
 
 D_SHIP_LO = Q.from_date(1992, 1, 2)
 D_SHIP_HI = Q.from_date(1998, 12, 1)
@@ -163,7 +166,15 @@ _SLOT = {"l_orderkey": (Q.L_ORDERKEY, K.TYPE_INT, 0, 0), "l_quantity": (Q.L_QUAN
          "o_orderkey": (Q.O_ORDERKEY, K.TYPE_INT, 0, 0), "o_custkey": (Q.O_CUSTKEY, K.TYPE_INT, 0, 0),
          "o_orderdate": (Q.O_ORDERDATE, K.TYPE_DATE, 0, 0), "o_shippriority": (Q.O_SHIPPRIORITY, K.TYPE_INT, 0, 0),
          "c_custkey": (Q.C_CUSTKEY, K.TYPE_INT, 0, 0), "c_mktsegment_code": (Q.C_MKTSEGMENT_CODE, K.TYPE_TINYINT, 0, 0),
-         "k": (Q.HC_K, K.TYPE_BIGINT, 0, 0), "v": (Q.HC_V, K.TYPE_BIGINT, 0, 0)}
+         "k": (Q.HC_K, K.TYPE_BIGINT, 0, 0), "v": (Q.HC_V, K.TYPE_BIGINT, 0, 0),
+         "lo_custkey": (Q.LO_CUSTKEY, K.TYPE_INT, 0, 0), "lo_partkey": (Q.LO_PARTKEY, K.TYPE_INT, 0, 0), "lo_suppkey": (Q.LO_SUPPKEY, K.TYPE_INT, 0, 0),
+         "lo_orderdate": (Q.LO_ORDERDATE, K.TYPE_INT, 0, 0), "lo_revenue": (Q.LO_REVENUE, K.TYPE_INT, 0, 0),
+         "lo_supplycost": (Q.LO_SUPPLYCOST, K.TYPE_INT, 0, 0), "sc_custkey": (Q.SC_CUSTKEY, K.TYPE_INT, 0, 0),
+         "sc_nation_code": (Q.SC_NATION_CODE, K.TYPE_INT, 0, 0), "sc_region_code": (Q.SC_REGION_CODE, K.TYPE_INT, 0, 0),
+         "ss_suppkey": (Q.SS_SUPPKEY, K.TYPE_INT, 0, 0), "ss_region_code": (Q.SS_REGION_CODE, K.TYPE_INT, 0, 0),
+         "sp_partkey": (Q.SP_PARTKEY, K.TYPE_INT, 0, 0), "sp_mfgr_code": (Q.SP_MFGR_CODE, K.TYPE_INT, 0, 0),
+         "sd_datekey": (Q.SD_DATEKEY, K.TYPE_INT, 0, 0), "sd_year": (Q.SD_YEAR, K.TYPE_INT, 0, 0)}
+LINEORDER_Q41 = ["lo_custkey", "lo_partkey", "lo_suppkey", "lo_orderdate", "lo_revenue", "lo_supplycost"]
 
 
 def _orders_cols(B, row0, n, cols, n_customers):
@@ -210,7 +221,64 @@ def _highcard_cols(B, row0, n, cols, n_keys):
     return out
 
 
+def _ssb_datekey(B, day):
+    """yyyymmdd of SSB_DATE_LO + day (Fliegel-Van Flandern inverse of from_date), and the year"""
+    j = day + SSB_DATE_LO + 32044
+    g = j // 146097
+    dg = j % 146097
+    c = (dg // 36524 + 1) * 3 // 4
+    dc = dg - c * 36524
+    b = dc // 1461
+    db = dc % 1461
+    a = (db // 365 + 1) * 3 // 4
+    da = db - a * 365
+    y = g * 400 + c * 100 + b * 4 + a
+    m = (da * 5 + 308) // 153 - 2
+    d = da - (m + 4) * 153 // 5 + 122
+    year = y - 4800 + (m + 2) // 12
+    month = (m + 2) % 12 + 1
+    return year * 10000 + month * 100 + d + 1, year
+
+
+def _ssb_cols(table, B, row0, n, cols, kw):
+    out = {}
+    idx = B.arange(row0, n)
+    n_cust, n_supp, n_part = kw.get("n_customers", 30000), kw.get("n_suppliers", 2000), kw.get("n_parts", 200000)
+    for c in cols:
+        if c == "lo_custkey":
+            out[c] = B.cast(B.umod(B.h(50, row0, n), n_cust) + 1, "i32")
+        elif c == "lo_partkey":
+            out[c] = B.cast(B.umod(B.h(51, row0, n), n_part) + 1, "i32")
+        elif c == "lo_suppkey":
+            out[c] = B.cast(B.umod(B.h(52, row0, n), n_supp) + 1, "i32")
+        elif c == "lo_orderdate":
+            out[c] = B.cast(_ssb_datekey(B, B.umod(B.h(53, row0, n), SSB_DAYS))[0], "i32")
+        elif c == "lo_revenue":
+            out[c] = B.cast(B.umod(B.h(54, row0, n), 10_000_000) + 90_000, "i32")
+        elif c == "lo_supplycost":
+            out[c] = B.cast(B.umod(B.h(55, row0, n), 120_000) + 6_000, "i32")
+        elif c in ("sc_custkey", "ss_suppkey", "sp_partkey"):
+            out[c] = B.cast(idx + 1, "i32")
+        elif c == "sc_nation_code":  # nation = region * 5 + 0..4
+            out[c] = B.cast(B.umod(B.h(60, row0, n), 25), "i32")
+        elif c == "sc_region_code":
+            out[c] = B.cast(B.umod(B.h(60, row0, n), 25) // 5, "i32")
+        elif c == "ss_region_code":
+            out[c] = B.cast(B.umod(B.h(65, row0, n), 25) // 5, "i32")
+        elif c == "sp_mfgr_code":
+            out[c] = B.cast(B.umod(B.h(70, row0, n), 5), "i32")
+        elif c == "sd_datekey":
+            out[c] = B.cast(_ssb_datekey(B, idx)[0], "i32")
+        elif c == "sd_year":
+            out[c] = B.cast(_ssb_datekey(B, idx)[1], "i32")
+        else:
+            raise KeyError(c)
+    return out
+
+
 def _gen(table: str, B, row0: int, n: int, cols, **kw):
+    if table in ("lineorder", "ssb_customer", "ssb_supplier", "ssb_part", "ssb_dates"):
+        return _ssb_cols(table, B, row0, n, cols, kw)
     if table == "lineitem":
         return _lineitem_cols(B, row0, n, cols)
     if table == "orders":

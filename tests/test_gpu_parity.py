@@ -548,6 +548,17 @@ def test_error_convention(ctx):
 
 
 # ---- joins ------------------------------------------------------------------------------------------------------------------
+@pytest.fixture(params=["tiled", "general"])
+def join_mode(request, monkeypatch):
+    """Joins with at most one match per probe row (unique build keys, LEFT SEMI) take the tiled two-pass probe; SRB_JOIN_GENERAL
+    forces the chain-walking count/append probe that serves every other join. Both must give the oracle's rows."""
+    if request.param == "general":
+        monkeypatch.setenv("SRB_JOIN_GENERAL", "1")
+    else:
+        monkeypatch.delenv("SRB_JOIN_GENERAL", raising=False)
+    return request.param
+
+
 def run_join(ctx, plan, build, probe, build_pieces=1, device=False):
     from starrocks_b200 import ops
     op = ops.HashJoinOperator(ctx, plan)
@@ -572,7 +583,7 @@ def run_join(ctx, plan, build, probe, build_pieces=1, device=False):
         op.close()
 
 
-def test_join_reference_vectors(ctx, oracle):
+def test_join_reference_vectors(ctx, oracle, join_mode):
     # be/test/exec/join_hash_map_test.cpp semantics: 1-based build indexes, NULL keys never match, one-to-many chains
     build = K.Chunk(6, {0: K.Column.from_ints(K.TYPE_INT, [1, 2, 2, 3, 5, 7], nulls=[0, 0, 0, 0, 1, 0]),
                         1: K.Column.from_ints(K.TYPE_BIGINT, [10, 20, 21, 30, 50, 70])})
@@ -588,7 +599,7 @@ def test_join_reference_vectors(ctx, oracle):
 
 @pytest.mark.parametrize("ktypes", [[K.TYPE_INT], [K.TYPE_BIGINT], [K.TYPE_INT, K.TYPE_INT], [K.TYPE_SMALLINT], [K.TYPE_BIGINT, K.TYPE_INT],
                                     [K.TYPE_DECIMAL128]])
-def test_join_key_widths_against_oracle(ctx, oracle, ktypes):
+def test_join_key_widths_against_oracle(ctx, oracle, ktypes, join_mode):
     rng = np.random.default_rng(len(ktypes) + ktypes[0])
     nb, npb = 30000, 100000
     bcols = {i: _rand_col(rng, t, nb, 0.05, small=True) for i, t in enumerate(ktypes)}
@@ -610,7 +621,7 @@ def test_join_key_widths_against_oracle(ctx, oracle, ktypes):
     assert len(want) > 0
 
 
-def test_join_empty_sides(ctx, oracle):
+def test_join_empty_sides(ctx, oracle, join_mode):
     build = K.Chunk(3, {0: K.Column.from_ints(K.TYPE_INT, [1, 2, 3]), 1: K.Column.from_ints(K.TYPE_INT, [7, 8, 9])})
     probe = K.Chunk(2, {2: K.Column.from_ints(K.TYPE_INT, [10, 11])})
     plan = JoinPlan([0], [2], build_out=[1], probe_out=[2])
@@ -619,7 +630,7 @@ def test_join_empty_sides(ctx, oracle):
     assert run_join(ctx, plan, empty_build, probe).n_rows == 0
 
 
-def test_q3_pipeline_chained_on_device(ctx, oracle):
+def test_q3_pipeline_chained_on_device(ctx, oracle, join_mode):
     """customer(filter) -> build; orders(filter) -> probe -> build; lineitem(filter) -> probe -> group by, all operator outputs
     handed over as device chunks; compared with the same chain through the oracle."""
     from starrocks_b200 import ops
@@ -663,6 +674,37 @@ def test_q3_pipeline_chained_on_device(ctx, oracle):
     for o in (fc, fo, fl, jo1, jo2, agg):
         o.close()
     assert got == want
+
+
+def _ssb_tables(n_lo, n_c, n_s, n_p, row0=0):
+    kw = dict(n_customers=n_c, n_suppliers=n_s, n_parts=n_p)
+    from starrocks_b200 import pipelines as P
+    dims = {"ssb_customer": T.host_chunk("ssb_customer", 0, n_c, P.SSB_DIM_COLS["ssb_customer"]),
+            "ssb_supplier": T.host_chunk("ssb_supplier", 0, n_s, P.SSB_DIM_COLS["ssb_supplier"]),
+            "ssb_part": T.host_chunk("ssb_part", 0, n_p, P.SSB_DIM_COLS["ssb_part"]),
+            "ssb_dates": T.host_chunk("ssb_dates", 0, T.SSB_DAYS, P.SSB_DIM_COLS["ssb_dates"])}
+    return dims, T.host_chunk("lineorder", row0, n_lo, T.LINEORDER_Q41, **kw)
+
+
+def test_ssb_q41_star_join_chained_on_device(ctx, oracle, join_mode):
+    """SSB Q4.1: three filtered dimensions + dates as build sides, lineorder probing them in turn with late
+    materialisation, GROUP BY d_year, c_nation — every operator output handed on as a device chunk; compared with the oracle chain."""
+    from starrocks_b200 import pipelines as P
+    dims, lo = _ssb_tables(600_000, 30_000, 2_000, 200_000)
+    want = K.chunk_rows(P.ssb_q41_oracle(oracle, dims, lo))
+    assert len(want) == 7 * 5  # 7 years x the 5 nations of AMERICA
+    q = P.SsbQ41(ctx).build(dims)
+    stage_rows = []
+    agg = q.probe(lo, stage_rows=stage_rows)
+    got = K.chunk_rows(agg.pull_all())
+    agg.close()
+    # a second fact-table pass through the same build sides (the next lineorder morsel range) gives the same answer
+    agg2 = q.probe(lo)
+    got2 = K.chunk_rows(agg2.pull_all())
+    agg2.close()
+    q.close()
+    assert got == want and got2 == want
+    assert stage_rows[0] > stage_rows[1] > stage_rows[2] == stage_rows[3] > 0  # 1/5 supplier, 1/5 customer, 2/5 part, every date matches
 
 
 def test_device_pull_of_aggregate_result(ctx, oracle):
