@@ -364,30 +364,167 @@ __global__ void __launch_bounds__(256) k_filter_mask(const __grid_constant__ DPr
     }
 }
 
-// exclusive scan of the tile counts (a few thousand to ~100k entries): one block, sequential over 1024-entry strips
+// The same bitmap for predicates that lower to per-column ranges over NULL-free 4- / 8-byte columns (lower_ranges): every
+// thread takes four consecutive rows per step with 128-bit loads (one LDG.128 per 4-byte column, two per 8-byte column), all
+// loads of four steps are issued before the first result is used, and a warp assembles its four mask words with three
+// shuffles. One subtract + one unsigned compare per row and range whatever the operators were.
+struct FRange {
+    const uint8_t* data; // already offset to the first row of the range being filtered; 16-byte aligned
+    int32_t width;       // 4 or 8
+    int32_t neg;
+    int64_t lo;
+    uint64_t span;
+};
+struct FRangeArgs {
+    int32_t n;
+    int32_t _pad;
+    FRange r[ST_MAX_RANGES];
+};
+
+template <int I>
+SRB_D uint32_t quad_ranges(const FRangeArgs& fa, int64_t row, uint32_t nib) {
+    if constexpr (I < ST_MAX_RANGES) {
+        if (I < fa.n) {
+            const FRange& g = fa.r[I];
+            uint32_t b;
+            if (g.width == 4) {
+                const uint4 v = __ldg((const uint4*)(g.data + row * 4));
+                const uint32_t lo = (uint32_t)g.lo, span = (uint32_t)g.span;
+                b = (uint32_t)(v.x - lo <= span) | ((uint32_t)(v.y - lo <= span) << 1) | ((uint32_t)(v.z - lo <= span) << 2) | ((uint32_t)(v.w - lo <= span) << 3);
+            } else {
+                const ulonglong2 v0 = __ldg((const ulonglong2*)(g.data + row * 8));
+                const ulonglong2 v1 = __ldg((const ulonglong2*)(g.data + row * 8 + 16));
+                const uint64_t lo = (uint64_t)g.lo;
+                b = (uint32_t)(v0.x - lo <= g.span) | ((uint32_t)(v0.y - lo <= g.span) << 1) | ((uint32_t)(v1.x - lo <= g.span) << 2) |
+                    ((uint32_t)(v1.y - lo <= g.span) << 3);
+            }
+            nib &= g.neg ? ~b : b;
+            return quad_ranges<I + 1>(fa, row, nib);
+        }
+    }
+    return nib;
+}
+
+SRB_D uint32_t quad_ranges_tail(const FRangeArgs& fa, int64_t row, int64_t n) { // the last, partial quad of the range
+    uint32_t nib = 0;
+    for (int j = 0; j < 4 && row + j < n; j++) {
+        bool pass = true;
+        for (int k = 0; k < fa.n; k++) {
+            const FRange& g = fa.r[k];
+            bool in;
+            if (g.width == 4) in = (uint32_t)(((const uint32_t*)g.data)[row + j] - (uint32_t)g.lo) <= (uint32_t)g.span;
+            else in = (uint64_t)(((const uint64_t*)g.data)[row + j] - (uint64_t)g.lo) <= g.span;
+            pass = pass && (in != (g.neg != 0));
+        }
+        nib |= (uint32_t)pass << j;
+    }
+    return nib;
+}
+
+// a single range over a W-byte column: straight-line code, so the loads of all four steps are issued back to back
+template <int W>
+SRB_D uint32_t quad_one_range(const FRange& g, int64_t row) {
+    uint32_t b;
+    if constexpr (W == 4) {
+        const uint4 v = __ldg((const uint4*)(g.data + row * 4));
+        const uint32_t lo = (uint32_t)g.lo, span = (uint32_t)g.span;
+        b = (uint32_t)(v.x - lo <= span) | ((uint32_t)(v.y - lo <= span) << 1) | ((uint32_t)(v.z - lo <= span) << 2) | ((uint32_t)(v.w - lo <= span) << 3);
+    } else {
+        const ulonglong2 v0 = __ldg((const ulonglong2*)(g.data + row * 8));
+        const ulonglong2 v1 = __ldg((const ulonglong2*)(g.data + row * 8 + 16));
+        const uint64_t lo = (uint64_t)g.lo;
+        b = (uint32_t)(v0.x - lo <= g.span) | ((uint32_t)(v0.y - lo <= g.span) << 1) | ((uint32_t)(v1.x - lo <= g.span) << 2) | ((uint32_t)(v1.y - lo <= g.span) << 3);
+    }
+    return (g.neg ? ~b : b) & 0xFu;
+}
+
+// MODE 0: any conjunction of ranges; MODE 4 / 8: exactly one range over a 4- / 8-byte column
+template <int MODE>
+__global__ void __launch_bounds__(256) k_filter_mask_ranges(const __grid_constant__ FRangeArgs fa, int64_t n, uint32_t* __restrict__ mask,
+                                                             uint32_t* __restrict__ tile_counts) {
+    __shared__ uint32_t wcount[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t tile0 = (int64_t)blockIdx.x * FTILE;
+    uint32_t mine = 0;
+#pragma unroll 1
+    for (int it = 0; it < FTILE / 1024; it += 4) {
+        uint32_t nib[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) { // a warp covers 128 consecutive rows per step; steps of one block are 1024 rows apart
+            const int64_t row = tile0 + (int64_t)(it + u) * 1024 + warp * 128 + lane * 4;
+            if constexpr (MODE == 0) {
+                nib[u] = row + 4 <= n ? quad_ranges<0>(fa, row, 0xFu) : (row < n ? quad_ranges_tail(fa, row, n) : 0u);
+            } else {
+                nib[u] = row + 4 <= n ? quad_one_range<MODE>(fa.r[0], row) : 0x10u; // 0x10: not a whole quad, settled below
+            }
+        }
+        if constexpr (MODE != 0) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (nib[u] == 0x10u) {
+                    const int64_t row = tile0 + (int64_t)(it + u) * 1024 + warp * 128 + lane * 4;
+                    nib[u] = row < n ? quad_ranges_tail(fa, row, n) : 0u;
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            uint32_t w = (nib[u] & 0xFu) << (4 * (lane & 7)); // word j of the step = lanes 8j .. 8j+7
+            w |= __shfl_xor_sync(0xffffffffu, w, 1);
+            w |= __shfl_xor_sync(0xffffffffu, w, 2);
+            w |= __shfl_xor_sync(0xffffffffu, w, 4);
+            const int64_t row = tile0 + (int64_t)(it + u) * 1024 + warp * 128 + lane * 4;
+            if ((lane & 7) == 0 && row < n) {
+                mask[row >> 5] = w;
+                mine += __popc(w);
+            }
+        }
+    }
+    mine += __shfl_xor_sync(0xffffffffu, mine, 8);
+    mine += __shfl_xor_sync(0xffffffffu, mine, 16);
+    if (lane == 0) wcount[warp] = mine;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int w = 0; w < 8; w++) t += wcount[w];
+        tile_counts[blockIdx.x] = t;
+    }
+}
+
+// exclusive scan of the tile counts (a few to ~10^5 entries): one block; every thread sums a contiguous run, the 1024 run
+// totals are scanned with warp shuffles, then every thread writes its run's offsets
 __global__ void __launch_bounds__(1024) k_scan_tiles(const uint32_t* __restrict__ counts, uint64_t* __restrict__ offsets, int64_t n_tiles,
                                                       Counters* __restrict__ ctr) {
-    __shared__ uint64_t sm[1024];
-    __shared__ uint64_t carry;
-    if (threadIdx.x == 0) carry = 0;
-    __syncthreads();
-    for (int64_t b = 0; b < n_tiles; b += 1024) {
-        int64_t i = b + threadIdx.x;
-        uint64_t x = i < n_tiles ? counts[i] : 0;
-        sm[threadIdx.x] = x;
-        __syncthreads();
-        for (int o = 1; o < 1024; o <<= 1) {
-            uint64_t y = threadIdx.x >= o ? sm[threadIdx.x - o] : 0;
-            __syncthreads();
-            sm[threadIdx.x] += y;
-            __syncthreads();
-        }
-        if (i < n_tiles) offsets[i] = carry + sm[threadIdx.x] - x;
-        __syncthreads();
-        if (threadIdx.x == 1023) carry += sm[1023];
-        __syncthreads();
+    __shared__ uint64_t wsum[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t per = (n_tiles + 1023) / 1024;
+    const int64_t a = (int64_t)threadIdx.x * per, b = a + per < n_tiles ? a + per : n_tiles;
+    uint64_t run = 0;
+    for (int64_t i = a; i < b; i++) run += counts[i];
+    uint64_t inc = run;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint64_t y = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += y;
     }
-    if (threadIdx.x == 0) ctr->rows_selected = carry;
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        uint64_t v = wsum[lane], w = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint64_t y = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += y;
+        }
+        wsum[lane] = w - v; // exclusive over warps
+        if (lane == 31) ctr->rows_selected = w;
+    }
+    __syncthreads();
+    uint64_t pos = wsum[warp] + inc - run;
+    for (int64_t i = a; i < b; i++) {
+        offsets[i] = pos;
+        pos += counts[i];
+    }
 }
 
 struct CompactCol {
@@ -404,41 +541,67 @@ struct CompactArgs {
     CompactCol cols[MAX_COLS];
 };
 
-__global__ void __launch_bounds__(256) k_compact(const __grid_constant__ CompactArgs ca, int64_t n, const uint32_t* __restrict__ mask,
+// One column of a warp's 32 mask words (1024 rows): lane l holds word l's bits and its first output position. Column outside,
+// words inside: the element width is a compile-time constant of the loop, eight words' loads are in flight per lane before the
+// first store (source and destination never alias), a set bit's lane reads its row and writes it at the word's position plus
+// the number of set bits below it — rows keep their order, like Chunk::filter (column_helper.h:468-577).
+template <class T>
+SRB_D void compact_words(const T* __restrict__ src, T* __restrict__ dst, uint32_t my_bits, uint32_t my_pos, int lane) {
+    const uint32_t below = (1u << lane) - 1u;
+#pragma unroll 1
+    constexpr int U = sizeof(T) > 8 ? 4 : 8;
+    for (int w0 = 0; w0 < 32; w0 += U) {
+        T v[U];
+        uint32_t at[U];
+        bool take[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) { // all U loads are issued before the first store needs its value
+            const uint32_t bits = __shfl_sync(0xffffffffu, my_bits, w0 + u);
+            const uint32_t pos = __shfl_sync(0xffffffffu, my_pos, w0 + u);
+            take[u] = (bits >> lane) & 1u;
+            at[u] = pos + __popc(bits & below);
+            if (take[u]) v[u] = src[(w0 + u) * 32 + lane];
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (take[u]) dst[at[u]] = v[u];
+    }
+}
+
+__global__ void __launch_bounds__(256, 3) k_compact(const __grid_constant__ CompactArgs ca, int64_t n, const uint32_t* __restrict__ mask,
                                                   const uint64_t* __restrict__ tile_offsets) {
-    __shared__ uint32_t woff[256];
+    __shared__ uint32_t wtot[8];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t tile0 = (int64_t)blockIdx.x * FTILE;
     const int64_t w0 = tile0 >> 5;
     const int64_t n_words = (n + 31) >> 5;
-    uint32_t word = (w0 + threadIdx.x) < n_words ? mask[w0 + threadIdx.x] : 0;
-    // rows past n inside the last word were never set (k_filter_mask ballots `i < n && pass`)
-    uint32_t c = __popc(word);
-    woff[threadIdx.x] = c;
-    __syncthreads();
-    for (int o = 1; o < 256; o <<= 1) {
-        uint32_t y = threadIdx.x >= o ? woff[threadIdx.x - o] : 0;
-        __syncthreads();
-        woff[threadIdx.x] += y;
-        __syncthreads();
+    // rows past n inside the last word were never set (the mask kernels write `i < n && pass`)
+    const uint32_t word = (w0 + threadIdx.x) < n_words ? mask[w0 + threadIdx.x] : 0;
+    const uint32_t c = __popc(word);
+    uint32_t inc = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += y;
     }
-    const uint64_t tile_base = tile_offsets[blockIdx.x];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int w = warp * 32; w < warp * 32 + 32; w++) {
-        uint32_t bits = (w0 + w) < n_words ? mask[w0 + w] : 0;
-        if (!((bits >> lane) & 1u)) continue;
-        uint64_t pos = tile_base + (woff[w] - __popc(bits)) + __popc(bits & ((1u << lane) - 1));
-        int64_t i = tile0 + (int64_t)w * 32 + lane;
-        for (int cidx = 0; cidx < ca.n_cols; cidx++) {
-            const CompactCol& cc = ca.cols[cidx];
-            switch (cc.width) {
-            case 1: cc.dst[pos] = cc.src[i]; break;
-            case 2: ((uint16_t*)cc.dst)[pos] = ((const uint16_t*)cc.src)[i]; break;
-            case 4: ((uint32_t*)cc.dst)[pos] = ((const uint32_t*)cc.src)[i]; break;
-            case 8: ((uint64_t*)cc.dst)[pos] = ((const uint64_t*)cc.src)[i]; break;
-            default: ((ulonglong2*)cc.dst)[pos] = ((const ulonglong2*)cc.src)[i];
-            }
-            if (cc.src_null) cc.dst_null[pos] = cc.src_null[i];
+    if (lane == 31) wtot[warp] = inc;
+    __syncthreads();
+    uint32_t before = 0;
+    for (int w = 0; w < warp; w++) before += wtot[w];
+    const uint32_t my_pos = before + inc - c; // first output position of this thread's word, relative to the tile
+    if (__ballot_sync(0xffffffffu, word != 0) == 0) return;
+    const uint64_t out0 = tile_offsets[blockIdx.x];
+    const int64_t row0 = tile0 + (int64_t)warp * 1024;
+    for (int cidx = 0; cidx < ca.n_cols; cidx++) {
+        const CompactCol& cc = ca.cols[cidx];
+        switch (cc.width) {
+        case 1: compact_words((const uint8_t*)cc.src + row0, (uint8_t*)cc.dst + out0, word, my_pos, lane); break;
+        case 2: compact_words((const uint16_t*)cc.src + row0, (uint16_t*)cc.dst + out0, word, my_pos, lane); break;
+        case 4: compact_words((const uint32_t*)cc.src + row0, (uint32_t*)cc.dst + out0, word, my_pos, lane); break;
+        case 8: compact_words((const uint64_t*)cc.src + row0, (uint64_t*)cc.dst + out0, word, my_pos, lane); break;
+        default: compact_words((const ulonglong2*)cc.src + row0, (ulonglong2*)cc.dst + out0, word, my_pos, lane);
         }
+        if (cc.src_null) compact_words(cc.src_null + row0, cc.dst_null + out0, word, my_pos, lane);
     }
 }
 
@@ -745,7 +908,7 @@ private:
     }
 
     // ---- batches ---------------------------------------------------------------------------------------------
-    static constexpr int64_t BATCH = (int64_t)1 << 27;     // filter batches (their output buffers are sized per batch)
+    static constexpr int64_t BATCH = (int64_t)1 << 31;     // filter batches: one mask + count pass, one exactly sized growth, one compaction
     static constexpr int64_t AGG_BATCH = (int64_t)1 << 29; // aggregation batches: the host waits for the counters once per batch
 
     void process_device_range(const ColBind* cols, int64_t n) {
@@ -1001,15 +1164,44 @@ private:
     }
 
     // ---- filter-only -----------------------------------------------------------------------------------------------
+    // One mask + count pass over the whole range, one exactly sized growth of the result columns, one compaction pass: the range
+    // is read once (predicate columns by the mask kernel, output columns by the compaction) and the kept rows are written once.
     void filter_range(const ColBind* cols, int64_t n) {
         bind_prog(cols);
+        const DProg& P = L_.prog;
+        // predicates that lower to ranges over NULL-free, 16-byte aligned 4- / 8-byte columns take the vectorised mask kernel
+        FRangeArgs fa{};
+        bool fast = !getenv("SRB_NO_FAST_FILTER");
+        if (fast) {
+            StaticArgs sa{};
+            for (int c = 0; c < P.n_cols; c++) sa.col_off[c] = c; // lower_ranges identifies a column by this field
+            fast = lower_ranges(P, sa);
+            for (int i = 0; fast && i < P.n_preds; i++) fast = cols[P.preds[i].col].nulls == nullptr;
+            for (int k = 0; fast && k < sa.n_ranges; k++) {
+                const SRange& g = sa.rng[k];
+                fa.r[k] = FRange{(const uint8_t*)cols[g.col_off].data, g.width, g.neg, g.lo, g.span};
+                fast = ((uintptr_t)fa.r[k].data & 15) == 0;
+            }
+            fa.n = sa.n_ranges;
+        }
         for (int64_t off = 0; off < n; off += BATCH) {
             int64_t m = std::min<int64_t>(BATCH, n - off);
             int64_t tiles = (m + FTILE - 1) / FTILE;
             mask_.ensure(ctx, (size_t)((m + 31) / 32) * 4 + 4);
             tile_counts_.ensure(ctx, (size_t)tiles * 4);
             tile_offsets_.ensure(ctx, (size_t)tiles * 8);
-            k_filter_mask<<<(int)tiles, 256, 0, stream>>>(L_.prog, off, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>());
+            if (fast) {
+                FRangeArgs fb = fa;
+                for (int k = 0; k < fb.n; k++) fb.r[k].data += (size_t)off * fb.r[k].width; // BATCH keeps the 16-byte alignment
+                if (fb.n == 1 && fb.r[0].width == 4)
+                    k_filter_mask_ranges<4><<<(int)tiles, 256, 0, stream>>>(fb, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>());
+                else if (fb.n == 1)
+                    k_filter_mask_ranges<8><<<(int)tiles, 256, 0, stream>>>(fb, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>());
+                else
+                    k_filter_mask_ranges<0><<<(int)tiles, 256, 0, stream>>>(fb, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>());
+            } else {
+                k_filter_mask<<<(int)tiles, 256, 0, stream>>>(L_.prog, off, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>());
+            }
             k_scan_tiles<<<1, 1024, 0, stream>>>(tile_counts_.as<uint32_t>(), tile_offsets_.as<uint64_t>(), tiles, ctr_dev_.as<Counters>());
             launches += 2;
             Counters* hc = ctr_host_.as<Counters>();
@@ -1036,10 +1228,10 @@ private:
                 launches++;
             }
             SRB_CUDA(cudaGetLastError());
-            SRB_CUDA(cudaStreamSynchronize(stream));
             out_rows_ += sel;
             selected_total_ += (uint64_t)sel;
         }
+        SRB_CUDA(cudaStreamSynchronize(stream)); // the caller may reuse the input stage / read the result columns right away
     }
     struct FOut {
         DevBuf data, nulls;

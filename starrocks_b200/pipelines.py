@@ -1,6 +1,12 @@
 """Multi-operator pipelines of the benchmark configs, wired the way the BE's pipeline builder wires the fragments: every operator
 output is handed to the next operator as a device chunk (no host round trip between operators).
 
+TPC-H Q3: customer (filtered) is the build side of the orders join; at N > 1 it is replicated on every rank
+(all-gather: the FE plans this join as BROADCAST, fe/fe-core/src/test/resources/sql/external/hive/tpch/q3.sql:100-115); the joined
+orders and the filtered lineitem rows are both hash-partitioned on the order key and exchanged all-to-all (the "INNER JOIN
+(PARTITIONED)" of q3.sql:57-79), so every rank builds and probes its own key range and its groups (the key contains l_orderkey) are
+disjoint from every other rank's.
+
 SSB Q4.1: the four dimensions are filtered and become hash-join build sides (replicated on every GPU in
 the multi-GPU plan: broadcast join); lineorder probes supplier, customer, part and dates in turn with late materialisation
 (each probe carries only the columns later operators read), then GROUP BY d_year, c_nation.
@@ -20,6 +26,92 @@ def _filter(ctx, plan, chunk):
     op.push_chunk(chunk)
     op.set_finishing()
     return op, op.pull_device()
+
+
+class TpchQ3:
+    """One pass of Q3 over this rank's row ranges of customer / orders / lineitem. `comm` (ops.Communicator) and `part`
+    (ops.Partitioner over world_size destinations) switch on the multi-GPU plan; without them everything is local."""
+
+    STAGES = ["customer filter (+ broadcast) + build J1", "orders filter", "probe J1 (+ shuffle) + build J2", "lineitem filter (+ shuffle)",
+              "probe J2 + gather", "group by"]
+
+    def __init__(self, ctx, comm=None, part=None):
+        self.ctx, self.comm, self.part = ctx, comm, part
+        self.open = []
+
+    def _shuffle(self, chunk, key_slot):
+        if self.comm is None:
+            return chunk
+        if chunk is None or not chunk.n_rows:
+            raise ValueError("a rank with no rows to shuffle cannot describe the schema of the exchange; give every rank at least one row")
+        grouped, counts = self.part.run(chunk, [key_slot])
+        recv, _ = self.comm.all_to_all(grouped, counts)
+        return recv
+
+    def run(self, cust: K.Chunk, orders: K.Chunk, line: K.Chunk, mark: Optional[Callable[[], None]] = None, rows: Optional[dict] = None):
+        """-> the aggregation operator after set_finishing (pull from it; close() afterwards). `mark()` is called after every stage
+        (STAGES), `rows` collects the row counts between the operators."""
+        mark = mark or (lambda: None)
+        rows = rows if rows is not None else {}
+        fc, dc = _filter(self.ctx, Q.q3_customer_filter(), cust)
+        self.open.append(fc)
+        rows["customer_kept"] = dc.n_rows
+        if self.comm is not None:
+            dc = self.comm.all_gather(dc)
+        j1 = ops.HashJoinOperator(self.ctx, Q.q3_join_customer_orders())
+        self.open.append(j1)
+        j1.push_chunk(dc)
+        j1.set_finishing()
+        mark()
+        fo, do = _filter(self.ctx, Q.q3_orders_filter(), orders)
+        self.open.append(fo)
+        rows["orders_kept"] = do.n_rows
+        mark()
+        j1.probe.push_chunk(do)
+        d1 = j1.probe.pull_device()
+        rows["j1_out"] = d1.n_rows if d1 is not None else 0
+        d1 = self._shuffle(d1, Q.O_ORDERKEY)
+        j2 = ops.HashJoinOperator(self.ctx, Q.q3_join_orders_lineitem())
+        self.open.append(j2)
+        if d1 is not None and d1.n_rows:
+            j2.push_chunk(d1)
+        j2.set_finishing()
+        mark()
+        fl, dl = _filter(self.ctx, Q.q3_lineitem_filter(), line)
+        self.open.append(fl)
+        rows["lineitem_kept"] = dl.n_rows
+        dl = self._shuffle(dl, Q.L_ORDERKEY)
+        mark()
+        d2 = None
+        if dl is not None and dl.n_rows:
+            j2.probe.push_chunk(dl)
+            d2 = j2.probe.pull_device()
+        rows["j2_out"] = d2.n_rows if d2 is not None else 0
+        mark()
+        agg = ops.ScanAggOperator(self.ctx, Q.q3_agg_plan(group_hint=max(1024, rows["j2_out"] // 2)))
+        self.open.append(agg)
+        if d2 is not None and d2.n_rows:
+            agg.push_chunk(d2)
+        agg.set_finishing()
+        return agg
+
+    def launches(self) -> int:
+        return sum(o.counters()["kernel_launches"] for o in self.open)
+
+    def close(self):
+        for o in self.open:
+            o.close()
+        self.open = []
+
+
+def q3_oracle(oracle, cust: K.Chunk, orders: K.Chunk, line: K.Chunk, n_threads: int = 1) -> K.Chunk:
+    """the same chain through the CPU oracle (tests and the CPU baseline only)"""
+    c = oracle.scan_agg(Q.q3_customer_filter(), cust, n_threads=n_threads)
+    o = oracle.scan_agg(Q.q3_orders_filter(), orders, n_threads=n_threads)
+    l = oracle.scan_agg(Q.q3_lineitem_filter(), line, n_threads=n_threads)
+    d1 = oracle.join(Q.q3_join_customer_orders(), c, o)
+    d2 = oracle.join(Q.q3_join_orders_lineitem(), d1, l)
+    return oracle.scan_agg(Q.q3_agg_plan(), d2, n_threads=n_threads)
 
 
 class SsbQ41:
@@ -70,13 +162,13 @@ class SsbQ41:
         self.joins, self.keep = [], []
 
 
-def ssb_q41_oracle(oracle, dims: Dict[str, K.Chunk], lineorder: K.Chunk) -> K.Chunk:
+def ssb_q41_oracle(oracle, dims: Dict[str, K.Chunk], lineorder: K.Chunk, n_threads: int = 1) -> K.Chunk:
     """the same chain through the CPU oracle (tests and the CPU baseline only)"""
-    s = oracle.scan_agg(Q.ssb_supplier_filter(), dims["ssb_supplier"])
-    c = oracle.scan_agg(Q.ssb_customer_filter(), dims["ssb_customer"])
-    p = oracle.scan_agg(Q.ssb_part_filter(), dims["ssb_part"])
+    s = oracle.scan_agg(Q.ssb_supplier_filter(), dims["ssb_supplier"], n_threads=n_threads)
+    c = oracle.scan_agg(Q.ssb_customer_filter(), dims["ssb_customer"], n_threads=n_threads)
+    p = oracle.scan_agg(Q.ssb_part_filter(), dims["ssb_part"], n_threads=n_threads)
     cur = oracle.join(Q.ssb_join_supplier(), s, lineorder)
     cur = oracle.join(Q.ssb_join_customer(), c, cur)
     cur = oracle.join(Q.ssb_join_part(), p, cur)
     cur = oracle.join(Q.ssb_join_dates(), dims["ssb_dates"], cur)
-    return oracle.scan_agg(Q.ssb_q41_agg_plan(), cur)
+    return oracle.scan_agg(Q.ssb_q41_agg_plan(), cur, n_threads=n_threads)

@@ -86,6 +86,47 @@ def test_single_rank_communicator_round_trip(ctx):
             ctx.device_free(p)
 
 
+Q3_COLS = {"customer": ["c_custkey", "c_mktsegment_code"], "orders": ["o_orderkey", "o_custkey", "o_orderdate", "o_shippriority"],
+           "lineitem": ["l_orderkey", "l_extendedprice", "l_discount", "l_shipdate"]}
+
+
+def _q3_tables(n_c, n_o, n_l, rank=0, world=1):
+    """this rank's row ranges of the three tables (range-partitioned scans)"""
+    out = []
+    for name, n in (("customer", n_c), ("orders", n_o), ("lineitem", n_l)):
+        b, e = D.shard_range(n, rank, world)
+        out.append(T.host_chunk(name, b, e - b, Q3_COLS[name], **({"n_customers": n_c} if name == "orders" else {})))
+    return out
+
+
+def test_q3_shuffle_plan_on_a_single_rank_communicator(ctx, oracle):
+    """the multi-GPU Q3 plan (broadcast of the customer build side, hash partition + all-to-all of both sides of the orders
+    join) through a world-size-1 communicator: same code path as N > 1, result equal to the oracle chain"""
+    from starrocks_b200 import ops, pipelines as P
+    cust, orders, line = _q3_tables(3000, 30000, 120000)
+    want = K.chunk_rows(P.q3_oracle(oracle, cust, orders, line))
+    assert len(want) > 50
+    box = {}
+    comm = ops.Communicator(ctx, lambda b: box.__setitem__("id", b), lambda: box["id"])
+    part = ops.Partitioner(ctx, 1)
+    q = P.TpchQ3(ctx, comm, part)
+    rows = {}
+    try:
+        agg = q.run(cust, orders, line, rows=rows)
+        got = K.chunk_rows(agg.pull_all())
+        assert q.launches() > 0 and rows["j2_out"] >= len(want)
+    finally:
+        q.close()
+        part.close()
+        comm.close()
+    assert got == want
+    q = P.TpchQ3(ctx)  # the local plan gives the same rows
+    try:
+        assert K.chunk_rows(q.run(cust, orders, line).pull_all()) == want
+    finally:
+        q.close()
+
+
 # ---- two GPUs: phase 1 -> device partition -> NCCL all-to-all -> phase 2 ------------------------------------------------------
 def _free_port():
     s = socket.socket()
@@ -179,3 +220,88 @@ def test_two_gpu_highcard_two_phase(oracle):
     b0, e0 = D.shard_range(n, 0, world)
     want_q1 = K.chunk_rows(oracle.scan_agg(Q.q1_plan(), T.host_chunk("lineitem", b0, e0 - b0, T.LINEITEM_Q1)))
     assert res[0][1] == want_q1 and res[1][1] == want_q1
+
+
+def _join_worker(rank, world, port, sizes, out_q):
+    """Q3 (shuffle join) and SSB Q4.1 (broadcast join) on this rank's row ranges"""
+    import torch
+    import torch.distributed as dist
+    from starrocks_b200 import ops, pipelines as P
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    ctx = ops.Context(device=rank, rank=rank, world_size=world)
+    try:
+        def put(b):
+            dist.broadcast_object_list([b], src=0)
+
+        def get():
+            box = [None]
+            dist.broadcast_object_list(box, src=0)
+            return box[0]
+
+        comm = ops.Communicator(ctx, put, get)
+        part = ops.Partitioner(ctx, world)
+        cust, orders, line = _q3_tables(*sizes["q3"], rank=rank, world=world)
+        q3 = P.TpchQ3(ctx, comm, part)
+        q3_rows = K.chunk_rows(q3.run(cust, orders, line).pull_all())
+        q3.close()
+        # SSB Q4.1: every rank filters its slice of each dimension, the slices are all-gathered (broadcast join), lineorder is
+        # range-partitioned; phase 1 per rank, the <= 35 intermediate rows are gathered and merged on every rank
+        n_lo, n_c, n_s, n_p = sizes["ssb"]
+        dims = {}
+        for name, n in (("ssb_customer", n_c), ("ssb_supplier", n_s), ("ssb_part", n_p), ("ssb_dates", T.SSB_DAYS)):
+            b, e = D.shard_range(n, rank, world)
+            dims[name] = T.host_chunk(name, b, e - b, P.SSB_DIM_COLS[name])
+        b, e = D.shard_range(n_lo, rank, world)
+        lo = T.host_chunk("lineorder", b, e - b, T.LINEORDER_Q41, n_customers=n_c, n_suppliers=n_s, n_parts=n_p)
+        ssb = P.SsbQ41(ctx, replicate=comm.all_gather).build(dims)
+        agg = ssb.probe(lo, phase=K.AGG_UPDATE_SERIALIZE)
+        inter = agg.pull_all()
+        agg.close()
+        everyone = comm.all_gather(inter)
+        op2 = ops.ScanAggOperator(ctx, Q.ssb_q41_merge_plan())
+        op2.push_chunk(everyone)
+        op2.set_finishing()
+        ssb_rows = K.chunk_rows(op2.pull_all())
+        op2.close()
+        ssb.close()
+        out_q.put((rank, (q3_rows, ssb_rows)))
+        part.close()
+        comm.close()
+        dist.barrier()
+    finally:
+        ctx.close()
+        dist.destroy_process_group()
+
+
+def test_two_gpu_shuffle_join_and_broadcast_join(oracle):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+    from starrocks_b200 import pipelines as P
+    world = 2
+    sizes = {"q3": (6000, 60000, 240000), "ssb": (300_000, 30_000, 2_000, 200_000)}
+    mpc = mp.get_context("spawn")
+    q = mpc.Queue()
+    port = _free_port()
+    procs = [mpc.Process(target=_join_worker, args=(r, world, port, sizes, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=300) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    cust, orders, line = _q3_tables(*sizes["q3"])
+    want = K.chunk_rows(P.q3_oracle(oracle, cust, orders, line))
+    keys = [{r[:3] for r in res[k][0]} for k in range(world)]
+    assert not (keys[0] & keys[1])  # the order key decides the rank: groups are disjoint
+    assert sorted(res[0][0] + res[1][0]) == want
+    n_lo, n_c, n_s, n_p = sizes["ssb"]
+    kw = dict(n_customers=n_c, n_suppliers=n_s, n_parts=n_p)
+    dims = {name: T.host_chunk(name, 0, n, P.SSB_DIM_COLS[name]) for name, n in
+            (("ssb_customer", n_c), ("ssb_supplier", n_s), ("ssb_part", n_p), ("ssb_dates", T.SSB_DAYS))}
+    want_ssb = K.chunk_rows(P.ssb_q41_oracle(oracle, dims, T.host_chunk("lineorder", 0, n_lo, T.LINEORDER_Q41, **kw)))
+    assert res[0][1] == want_ssb and res[1][1] == want_ssb
