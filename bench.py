@@ -513,8 +513,11 @@ def main():
             else:
                 inter = op.pull_device()
                 mark()
-                grouped, counts = part.run(inter, [0])
-                recv, _ = comm.all_to_all(grouped, counts)
+                if os.environ.get("SRB_NO_P2P"):  # A/B: device partition, then NCCL send/recv of the grouped rows
+                    grouped, counts = part.run(inter, [0])
+                    recv, _ = comm.all_to_all(grouped, counts)
+                else:  # partition scatter fused with the exchange: rows go straight into the peers' receive buffers
+                    recv, _ = comm.shuffle(inter, [0])
                 mark()
                 op2 = ops.ScanAggOperator(ctx, Q.highcard_merge_plan(group_hint=HIGHCARD_KEYS // world))
             op2.push_chunk(recv)

@@ -294,6 +294,16 @@ void* srb_comm_stream(srb_comm* c);
  * rows from rank 0, 1, ... in that order with recv_counts[world]. Counts travel first (ncclAllGather), then one grouped
  * ncclSend/ncclRecv per column and peer. */
 srb_status srb_comm_all_to_all(srb_comm* c, const srb_chunk* send, const int64_t* send_counts, srb_chunk* recv, int64_t* recv_counts);
+/* Partitioning FUSED with the exchange (ExchangeSinkOperator::push_chunk HASH_PARTITIONED + transmit + ExchangeSourceOperator::pull_chunk,
+ * exchange_sink_operator.cpp:569-633): rows of the device chunk `in` are routed by the same shuffle hash as srb_partition_run and the
+ * scatter kernel stores each one straight into the destination rank's receive arena over NVLink peer memory (cudaIpc-mapped), so there
+ * is no grouped staging copy and no send/recv; the W x W count matrix travels in one ncclAllGather, and a second small collective behind
+ * the kernel publishes completion. `recv` / `recv_counts` as srb_comm_all_to_all (rows of source rank 0, 1, ... in that order; order inside
+ * a source's range unspecified). Needs peer access between the GPUs; fails with INTERNAL_ERROR otherwise. */
+srb_status srb_comm_shuffle(srb_comm* c, const srb_chunk* in, int32_t n_key_slots, const int32_t* key_slots, srb_chunk* recv,
+                            int64_t* recv_counts);
+/* kernels launched by this communicator's fused shuffles so far */
+srb_status srb_comm_counters(srb_comm* c, int64_t* kernel_launches);
 /* UNPARTITIONED / broadcast exchange (exchange_sink_operator.cpp:508-547): every rank's rows replicated on every rank */
 srb_status srb_comm_all_gather(srb_comm* c, const srb_chunk* mine, srb_chunk* out);
 

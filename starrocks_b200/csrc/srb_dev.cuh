@@ -252,6 +252,40 @@ SRB_HD uint32_t fnv_hash_value(uint64_t lo, uint64_t hi, int width, uint32_t has
     }
     return hash;
 }
+// ---- runtime bloom filter: SimdBlockFilter (exprs/runtime_filter.h:79-222, runtime_filter.cpp:26-35,114-123) ----------------------
+// A directory of 2^log_num_buckets buckets of 8 x uint32; a hash sets / tests one bit in each of the 8 words of ONE bucket:
+//   bucket = hash & directory_mask;  word i: bit ((uint32)(hash >> log_num_buckets) * SALT[i]) >> 27.
+// RuntimeBloomFilter::compute_hash (runtime_filter.h:1192-1198) = phmap_mix<8>(std::hash<T>(v)); ENABLE_PHMAP_MIX is not defined
+// anywhere in the reference tree, so phmap_mix<8> is the identity (util/phmap/phmap_utils.h:112-124) and the hash of an
+// integer key is its sign-extended value.
+struct RfView {
+    uint32_t* dir; // [n_buckets][8]
+    uint32_t directory_mask;
+    int32_t log_num_buckets;
+    int64_t min, max; // over the inserted non-NULL keys (min > max: nothing inserted)
+    int32_t has_null;
+    int32_t _pad;
+};
+SRB_HD uint32_t rf_salt(int i) {
+    switch (i) {
+    case 0: return 0x47b6137bu;
+    case 1: return 0x44974d91u;
+    case 2: return 0x8824ad5bu;
+    case 3: return 0xa2b7289du;
+    case 4: return 0x705495c7u;
+    case 5: return 0x2df1424bu;
+    case 6: return 0x9efc4947u;
+    default: return 0x5c6bfb31u;
+    }
+}
+SRB_HD uint32_t rf_word_mask(uint32_t key, int i) { return 1u << ((key * rf_salt(i)) >> 27); }
+SRB_HD int rf_log_num_buckets(uint64_t nums) { // SimdBlockFilter::init: max(1, ceil(log2(max(1, nums))) - 5)
+    if (nums < 1) nums = 1;
+    int log_heap = 0;
+    while (((uint64_t)1 << log_heap) < nums) log_heap++;
+    return log_heap - 5 > 1 ? log_heap - 5 : 1;
+}
+
 SRB_HD uint32_t reduce_op(uint32_t h, uint32_t n) { return (uint32_t)(((uint64_t)h * (uint64_t)n) >> 32); }
 SRB_HD uint32_t xorshift32(uint32_t x) {
     x ^= x << 13;

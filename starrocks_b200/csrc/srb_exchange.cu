@@ -48,8 +48,19 @@ SRB_D uint32_t part_of(const PArgs& a, int64_t r) {
         if (c.src_null && c.src_null[r]) {
             h = h ^ (0x9e3779b9u + (h << 6) + (h >> 2));
         } else {
-            const uint8_t* p = c.src + (size_t)r * c.width;
-            for (int b = 0; b < c.width; b++) h = (p[b] ^ h) * 0x01000193u;
+            // FNV-1 over the value's bytes, low byte first; 4- and 8-byte values are fetched with one load
+            if (c.width == 4) {
+                uint32_t x = ((const uint32_t*)c.src)[r];
+#pragma unroll
+                for (int b = 0; b < 4; b++, x >>= 8) h = ((x & 0xffu) ^ h) * 0x01000193u;
+            } else if (c.width == 8) {
+                uint64_t x = ((const uint64_t*)c.src)[r];
+#pragma unroll
+                for (int b = 0; b < 8; b++, x >>= 8) h = ((uint32_t)(x & 0xffu) ^ h) * 0x01000193u;
+            } else {
+                const uint8_t* p = c.src + (size_t)r * c.width;
+                for (int b = 0; b < c.width; b++) h = (p[b] ^ h) * 0x01000193u;
+            }
         }
     }
     return reduce_op(h, (uint32_t)a.n_parts);
@@ -120,6 +131,83 @@ __global__ void __launch_bounds__(256) k_part_scatter(const __grid_constant__ PA
                 }
                 if (pc.src_null) pc.dst_null[pos] = pc.src_null[r];
             }
+        }
+        __syncthreads();
+    }
+}
+
+
+// ---- shuffle fused with the exchange: scatter straight into the destination ranks' receive buffers ------------------------------
+// The receive buffers of every rank are mapped into this process (cudaIpc, NVLink peer memory). The scatter pass of the partitioner
+// then IS the all-to-all: a tile reserves a run per destination (shared-memory histogram + one atomic per destination and tile) and
+// every row is stored at  peer[d].column[c] + (first_row_of_this_source_in_d + run + rank) * width  — remote stores over NVLink for
+// d != me, local stores for d == me. No staging copy of the grouped rows, no ncclSend/ncclRecv; the W x W count matrix travels in
+// one ncclAllGather and a second tiny collective after the kernel tells every rank that all writes have landed.
+struct XDst {
+    uint8_t* data[PMAX_COLS];
+    uint8_t* nulls[PMAX_COLS];
+};
+template <class T>
+SRB_D void scatter_col(const T* __restrict__ src, int64_t row0, const uint32_t (&d)[PTILE / 256], const unsigned long long (&pos)[PTILE / 256],
+                       const XDst* __restrict__ dst, int col, bool nulls) {
+    constexpr int R = PTILE / 256, U = sizeof(T) > 8 ? 4 : 8;
+#pragma unroll
+    for (int j0 = 0; j0 < R; j0 += U) {
+        T v[U] = {};
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (d[j0 + u] != 0xffffffffu) v[u] = src[row0 + (j0 + u) * 256];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (d[j0 + u] != 0xffffffffu) ((T*)(nulls ? dst[d[j0 + u]].nulls[col] : dst[d[j0 + u]].data[col]))[pos[j0 + u]] = v[u];
+    }
+}
+
+__global__ void __launch_bounds__(256, 2) k_part_scatter_peers(const __grid_constant__ PArgs a, int64_t n, const uint8_t* __restrict__ dest,
+                                                                unsigned long long* __restrict__ cursors, const XDst* __restrict__ dst) {
+    __shared__ unsigned int hist[PMAX_PARTS];
+    __shared__ unsigned long long run_base[PMAX_PARTS];
+    constexpr int R = PTILE / 256;
+    const int64_t n_tiles = (n + PTILE - 1) / PTILE;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (int i = threadIdx.x; i < PMAX_PARTS; i += blockDim.x) hist[i] = 0;
+        __syncthreads();
+        uint32_t d[R], rank[R];
+        const int64_t row0 = tile * PTILE + threadIdx.x;
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const int64_t r = row0 + j * 256;
+            d[j] = 0xffffffffu;
+            rank[j] = 0;
+            const bool on = r < n;
+            if (on) d[j] = dest[r];
+            const unsigned act = __ballot_sync(0xffffffffu, on);
+            if (on) {
+                const unsigned peers = __match_any_sync(act, d[j]);
+                const int leader = __ffs(peers) - 1, lane = threadIdx.x & 31;
+                unsigned int b = 0;
+                if (lane == leader) b = atomicAdd(&hist[d[j]], __popc(peers));
+                b = __shfl_sync(peers, b, leader);
+                rank[j] = b + __popc(peers & ((1u << lane) - 1));
+            }
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < a.n_parts; i += blockDim.x)
+            run_base[i] = hist[i] ? a.base[i] + atomicAdd(&cursors[i], (unsigned long long)hist[i]) : 0;
+        __syncthreads();
+        unsigned long long pos[R];
+#pragma unroll
+        for (int j = 0; j < R; j++) pos[j] = d[j] != 0xffffffffu ? run_base[d[j]] + rank[j] : 0;
+        for (int c = 0; c < a.n_cols; c++) {
+            const PCol& pc = a.cols[c];
+            switch (pc.width) {
+            case 1: scatter_col((const uint8_t*)pc.src, row0, d, pos, dst, c, false); break;
+            case 2: scatter_col((const uint16_t*)pc.src, row0, d, pos, dst, c, false); break;
+            case 4: scatter_col((const uint32_t*)pc.src, row0, d, pos, dst, c, false); break;
+            case 8: scatter_col((const uint64_t*)pc.src, row0, d, pos, dst, c, false); break;
+            default: scatter_col((const ulonglong2*)pc.src, row0, d, pos, dst, c, false);
+            }
+            if (pc.src_null) scatter_col(pc.src_null, row0, d, pos, dst, c, true);
         }
         __syncthreads();
     }
@@ -208,6 +296,20 @@ struct srb_comm {
         std::vector<uint32_t> offsets;
     };
     std::vector<HostOut> hout;
+    // fused shuffle (srb_comm_shuffle): this rank's receive arena (plain cudaMalloc: exportable with cudaIpc) and the mapped
+    // arenas of the peers
+    struct Peer {
+        void* base = nullptr;
+        size_t cap = 0;
+        uint64_t gen = 0;
+    };
+    void* arena = nullptr;
+    size_t arena_cap = 0;
+    uint64_t arena_gen = 0;
+    std::vector<Peer> peers;
+    DevBuf x_dest, x_totals, x_dst_dev, x_hs_dev;
+    PinnedBuf x_dst_host, x_hs_host;
+    int64_t x_launches = 0;
 };
 
 // the C ABI's error string lives in srb_capi.cu; exchange entry points report through the same convention
@@ -491,6 +593,9 @@ void srb_comm_destroy(srb_comm* c) {
         cudaStreamSynchronize(c->stream);
         cudaStreamDestroy(c->stream);
     }
+    for (int d = 0; d < (int)c->peers.size(); d++)
+        if (d != c->rank && c->peers[d].base) cudaIpcCloseMemHandle(c->peers[d].base);
+    if (c->arena) cudaFree(c->arena);
     if (c->comm) nccl().CommDestroy(c->comm);
     delete c;
 }
@@ -556,6 +661,187 @@ srb_status srb_comm_all_to_all(srb_comm* c, const srb_chunk* send, const int64_t
     recv->cols = c->cview.data();
     return SRB_OK;
     X_END
+}
+
+// HASH_PARTITIONED exchange in one step (ExchangeSinkOperator::push_chunk -> transmit -> ExchangeSourceOperator, exchange_sink_operator.cpp:
+// 569-633): count pass, one ncclAllGather of the W x W count matrix, then the scatter kernel writes every row straight into its
+// destination rank's receive arena over peer memory (k_part_scatter_peers). Output as srb_comm_all_to_all.
+namespace {
+struct XHandshake {
+    cudaIpcMemHandle_t handle;
+    uint64_t cap, gen;
+};
+inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+} // namespace
+
+srb_status srb_comm_shuffle(srb_comm* c, const srb_chunk* in, int32_t n_key_slots, const int32_t* key_slots, srb_chunk* recv, int64_t* recv_counts) {
+    X_BEGIN
+    if (!c || !in || !key_slots || !recv || !recv_counts) throw Error(SRB_INVALID_ARGUMENT, "null argument");
+    if (n_key_slots < 1 || n_key_slots > PMAX_KEYS) throw Error(SRB_INVALID_ARGUMENT, "bad number of partition columns");
+    if (in->n_cols < 1 || in->n_cols > PMAX_COLS) throw Error(SRB_NOT_IMPLEMENTED, "too many columns");
+    SRB_CUDA(cudaSetDevice(c->ctx->cfg.device));
+    const int W = c->world, me = c->rank;
+    const int64_t n = in->n_rows;
+    if (c->peers.empty()) c->peers.resize(W);
+    PArgs a{};
+    a.n_cols = in->n_cols;
+    a.n_keys = n_key_slots;
+    a.n_parts = W;
+    uint64_t nullmask = 0;
+    int width[PMAX_COLS];
+    for (int col = 0; col < in->n_cols; col++) {
+        const srb_column& sc = in->cols[col];
+        width[col] = type_width(sc.type);
+        if (width[col] == 0) throw Error(SRB_NOT_IMPLEMENTED, "partitioning of binary columns");
+        if (n > 0 && sc.mem_kind != SRB_MEM_DEVICE) throw Error(SRB_INVALID_ARGUMENT, "the shuffle takes device-resident chunks");
+        a.cols[col] = PCol{(const uint8_t*)sc.data, nullptr, sc.nulls, nullptr, width[col], 0};
+        if (sc.nulls) nullmask |= 1ull << col;
+    }
+    for (int k = 0; k < n_key_slots; k++) {
+        int idx = -1;
+        for (int col = 0; col < in->n_cols; col++)
+            if (in->slot_ids[col] == key_slots[k]) idx = col;
+        if (idx < 0) throw Error(SRB_INVALID_ARGUMENT, fmt("partition slot %d not in chunk", key_slots[k]));
+        a.key_col[k] = idx;
+    }
+    // pass 1: destination per row + totals per destination
+    c->x_totals.ensure(c->ctx, 2 * PMAX_PARTS * 8);
+    unsigned long long* totals = c->x_totals.as<unsigned long long>();
+    unsigned long long* cursors = totals + PMAX_PARTS;
+    SRB_CUDA(cudaMemsetAsync(totals, 0, 2 * PMAX_PARTS * 8, c->stream));
+    c->x_dest.ensure(c->ctx, (size_t)std::max<int64_t>(n, 1));
+    if (n > 0) {
+        int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, (int64_t)c->ctx->n_sms * 8));
+        k_part_count<<<grid, 256, 0, c->stream>>>(a, n, c->x_dest.as<uint8_t>(), totals);
+        c->x_launches++;
+    }
+    // counts (+ this rank's null-map mask in one extra word): every rank learns the whole matrix
+    const int RW = W + 1; // words per rank
+    c->counts_dev.ensure(c->ctx, (size_t)(RW + RW * W) * 8);
+    c->counts_host.ensure((size_t)(RW + RW * W) * 8);
+    int64_t* hc = c->counts_host.as<int64_t>();
+    int64_t* dc = c->counts_dev.as<int64_t>();
+    hc[W] = (int64_t)nullmask;
+    SRB_CUDA(cudaMemcpyAsync(dc, totals, (size_t)W * 8, cudaMemcpyDeviceToDevice, c->stream));
+    SRB_CUDA(cudaMemcpyAsync(dc + W, hc + W, 8, cudaMemcpyHostToDevice, c->stream));
+    SRB_NCCL(nccl().AllGather(dc, dc + RW, (size_t)RW, ncclInt64_, c->comm, c->stream));
+    SRB_CUDA(cudaMemcpyAsync(hc + RW, dc + RW, (size_t)RW * W * 8, cudaMemcpyDeviceToHost, c->stream));
+    SRB_CUDA(cudaStreamSynchronize(c->stream));
+    auto M = [&](int s, int d) { return hc[RW + (size_t)s * RW + d]; };
+    std::vector<int64_t> T(W, 0), off(W, 0);
+    for (int d = 0; d < W; d++)
+        for (int s = 0; s < W; s++) {
+            if (s < me) off[d] += M(s, d);
+            T[d] += M(s, d);
+        }
+    for (int s = 0; s < W; s++) {
+        recv_counts[s] = M(s, me);
+        if ((uint64_t)hc[RW + (size_t)s * RW + W] != nullmask) throw Error(SRB_NOT_IMPLEMENTED, "null maps differ between the ranks of a shuffle");
+    }
+    // receive layout of rank d: columns back to back (256-byte aligned), then the null maps
+    auto layout = [&](int d, size_t* data_off, size_t* null_off) {
+        size_t pos = 0;
+        for (int col = 0; col < in->n_cols; col++) {
+            data_off[col] = pos;
+            pos += align256((size_t)T[d] * width[col]);
+        }
+        for (int col = 0; col < in->n_cols; col++) {
+            null_off[col] = pos;
+            if (nullmask >> col & 1) pos += align256((size_t)T[d]);
+        }
+        return std::max<size_t>(pos, 256);
+    };
+    size_t doff[PMAX_COLS], noff[PMAX_COLS];
+    bool handshake = false;
+    for (int d = 0; d < W; d++) handshake = handshake || layout(d, doff, noff) > (d == me ? c->arena_cap : c->peers[d].cap);
+    void* old_arena = nullptr;
+    if (handshake) { // some rank grows its arena: everyone republishes (the decision is the same on every rank)
+        const size_t need = layout(me, doff, noff);
+        if (need > c->arena_cap) {
+            old_arena = c->arena;
+            size_t cap = std::max(need, c->arena_cap + c->arena_cap / 2);
+            cap = (cap + ((size_t)2 << 20) - 1) & ~(((size_t)2 << 20) - 1);
+            SRB_CUDA(cudaMalloc(&c->arena, cap));
+            c->arena_cap = cap;
+            c->arena_gen++;
+        }
+        c->x_hs_host.ensure(sizeof(XHandshake) * (size_t)(W + 1));
+        c->x_hs_dev.ensure(c->ctx, sizeof(XHandshake) * (size_t)(W + 1));
+        XHandshake* hs = c->x_hs_host.as<XHandshake>();
+        memset(&hs[0], 0, sizeof(XHandshake));
+        if (W > 1) SRB_CUDA(cudaIpcGetMemHandle(&hs[0].handle, c->arena));
+        hs[0].cap = c->arena_cap;
+        hs[0].gen = c->arena_gen;
+        XHandshake* hd = c->x_hs_dev.as<XHandshake>();
+        SRB_CUDA(cudaMemcpyAsync(hd, hs, sizeof(XHandshake), cudaMemcpyHostToDevice, c->stream));
+        SRB_NCCL(nccl().AllGather(hd, hd + 1, sizeof(XHandshake), ncclUint8_, c->comm, c->stream));
+        SRB_CUDA(cudaMemcpyAsync(hs + 1, hd + 1, sizeof(XHandshake) * (size_t)W, cudaMemcpyDeviceToHost, c->stream));
+        SRB_CUDA(cudaStreamSynchronize(c->stream));
+        for (int d = 0; d < W; d++) {
+            srb_comm::Peer& p = c->peers[d];
+            const XHandshake& r = hs[1 + d];
+            if (d == me) {
+                p.base = c->arena;
+            } else if (r.gen != p.gen || !p.base) {
+                if (p.base) SRB_CUDA(cudaIpcCloseMemHandle(p.base));
+                p.base = nullptr;
+                cudaError_t e = cudaIpcOpenMemHandle(&p.base, r.handle, cudaIpcMemLazyEnablePeerAccess);
+                if (e != cudaSuccess) {
+                    cudaGetLastError();
+                    throw Error(SRB_INTERNAL_ERROR, fmt("cannot map the receive arena of rank %d (%s): the fused shuffle needs NVLink/PCIe peer access "
+                                                        "between the GPUs; use srb_partition_run + srb_comm_all_to_all instead", d, cudaGetErrorString(e)));
+                }
+            }
+            p.cap = r.cap;
+            p.gen = r.gen;
+        }
+    }
+    c->peers[me].base = c->arena;
+    // destination table + first row of this source inside every destination
+    c->x_dst_host.ensure(sizeof(XDst) * (size_t)W);
+    c->x_dst_dev.ensure(c->ctx, sizeof(XDst) * (size_t)W);
+    XDst* xh = c->x_dst_host.as<XDst>();
+    for (int d = 0; d < W; d++) {
+        layout(d, doff, noff);
+        uint8_t* base = (uint8_t*)c->peers[d].base;
+        for (int col = 0; col < PMAX_COLS; col++) {
+            xh[d].data[col] = col < in->n_cols ? base + doff[col] : nullptr;
+            xh[d].nulls[col] = col < in->n_cols && (nullmask >> col & 1) ? base + noff[col] : nullptr;
+        }
+        a.base[d] = (unsigned long long)off[d];
+    }
+    if (n > 0) {
+        SRB_CUDA(cudaMemcpyAsync(c->x_dst_dev.p, xh, sizeof(XDst) * (size_t)W, cudaMemcpyHostToDevice, c->stream));
+        int grid2 = (int)std::max<int64_t>(1, std::min<int64_t>((n + PTILE - 1) / PTILE, (int64_t)c->ctx->n_sms * 2));
+        k_part_scatter_peers<<<grid2, 256, 0, c->stream>>>(a, n, c->x_dest.as<uint8_t>(), cursors, c->x_dst_dev.as<XDst>());
+        SRB_CUDA(cudaGetLastError());
+        c->x_launches++;
+    }
+    // every rank's scatter has finished (its stores are visible) once this collective, queued behind the kernel, completes everywhere
+    SRB_NCCL(nccl().AllGather(dc, dc + RW, 1, ncclInt64_, c->comm, c->stream));
+    SRB_CUDA(cudaStreamSynchronize(c->stream));
+    if (old_arena) SRB_CUDA(cudaFree(old_arena)); // every peer re-mapped the new arena before it reached the collective above
+    layout(me, doff, noff);
+    c->cview.assign(in->cols, in->cols + in->n_cols);
+    c->slots.assign(in->slot_ids, in->slot_ids + in->n_cols);
+    for (int col = 0; col < in->n_cols; col++) {
+        c->cview[col].mem_kind = SRB_MEM_DEVICE;
+        c->cview[col].data = (uint8_t*)c->arena + doff[col];
+        c->cview[col].nulls = (nullmask >> col & 1) ? (uint8_t*)c->arena + noff[col] : nullptr;
+        c->cview[col].offsets = nullptr;
+    }
+    recv->n_rows = T[me];
+    recv->n_cols = in->n_cols;
+    recv->slot_ids = c->slots.data();
+    recv->cols = c->cview.data();
+    return SRB_OK;
+    X_END
+}
+
+srb_status srb_comm_counters(srb_comm* c, int64_t* kernel_launches) {
+    if (!c || !kernel_launches) return SRB_INVALID_ARGUMENT;
+    *kernel_launches = c->x_launches;
+    return SRB_OK;
 }
 
 // every rank contributes `mine` (device, fixed width, same schema); out holds all ranks' rows, rank 0 first. Used to replicate

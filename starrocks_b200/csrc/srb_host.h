@@ -15,6 +15,8 @@
 #include <string>
 #include <vector>
 
+#include "srb_dev.cuh"
+
 #include "../../include/srb/srb_c_api.h"
 
 namespace srb {
@@ -314,6 +316,25 @@ struct srb_op {
     virtual bool probe_is_finished() { return true; }
     virtual srb_status probe_pull_chunk(srb_chunk*, bool) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
     virtual srb_status probe_pull_device(srb_chunk*) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
+    // runtime filters: join ops build them from their build side, scan-filter ops apply them
+    virtual struct srb_runtime_filter* build_runtime_filter(int, int64_t) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
+    virtual void add_runtime_filter(const struct srb_runtime_filter*, int) { throw srb::Error(SRB_NOT_IMPLEMENTED, "this operator does not take runtime filters"); }
+};
+
+// a runtime filter built from a join's build side (HashJoinBuildOperator -> RuntimeBloomFilter): device-resident SimdBlockFilter
+// directory + min / max / has_null kept on the host
+struct srb_runtime_filter {
+    srb_ctx* ctx = nullptr;
+    srb::DevBuf dir;
+    int log_num_buckets = 1;
+    uint32_t directory_mask = 1;
+    int key_type = 0, key_width = 0;
+    int64_t min = INT64_MAX, max = INT64_MIN, inserted = 0;
+    bool has_null = false;
+    srb::RfView view() const {
+        return srb::RfView{(uint32_t*)dir.p, directory_mask, log_num_buckets, min, max, has_null ? 1 : 0, 0};
+    }
+    size_t dir_bytes() const { return (size_t)32 << log_num_buckets; }
 };
 
 namespace srb {

@@ -17,6 +17,7 @@
 // and payload columns are gathered only for matched rows.
 #include <algorithm>
 #include <cstring>
+#include <memory>
 
 #include "srb_dev.cuh"
 #include "srb_host.h"
@@ -334,57 +335,140 @@ __global__ void __launch_bounds__(1024) k_join_scan(const uint32_t* __restrict__
     if (threadIdx.x == 0) *total = carry;
 }
 
-// pass B: rank the tile's matched rows in row order and write the output columns (and, when asked, the index pairs)
-__global__ void __launch_bounds__(JT_THREADS) k_join_emit(const __grid_constant__ GatherArgs g, int64_t n, const uint32_t* __restrict__ match,
-                                                           const uint64_t* __restrict__ tile_offsets, uint32_t* __restrict__ out_probe,
-                                                           uint32_t* __restrict__ out_build) {
-    __shared__ uint32_t warp_cnt[JT_THREADS / 32];
+// pass B: rank the tile's matched rows in row order and write the output columns (and, when asked, the index pairs).
+// One barrier per tile: the eight slabs' ballots are taken first, their per-warp counts go to shared memory together, and every
+// thread derives the output positions of its eight rows from them. Columns are then copied one at a time with the element width
+// a compile-time constant and all of a thread's loads issued before its first store (probe columns: row r, coalesced with holes;
+// build columns: row match[r]-1, random), so eight independent loads per thread are in flight instead of one.
+template <class T, bool FROM_BUILD>
+SRB_D void emit_col(const T* __restrict__ src, T* __restrict__ dst, int64_t row0, const uint32_t (&m)[JT_ROWS], const uint32_t (&rel)[JT_ROWS]) {
+    constexpr int U = sizeof(T) > 8 ? 4 : 8;
+#pragma unroll
+    for (int j0 = 0; j0 < JT_ROWS; j0 += U) {
+        T v[U] = {};
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (m[j0 + u]) v[u] = FROM_BUILD ? src[m[j0 + u] - 1] : src[row0 + (j0 + u) * JT_THREADS];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (m[j0 + u]) dst[rel[j0 + u]] = v[u];
+    }
+}
+template <bool FROM_BUILD>
+SRB_D void emit_col_w(const GatherCol& gc, uint64_t base, int64_t row0, const uint32_t (&m)[JT_ROWS], const uint32_t (&rel)[JT_ROWS]) {
+    switch (gc.width) {
+    case 1: emit_col<uint8_t, FROM_BUILD>((const uint8_t*)gc.src, (uint8_t*)gc.dst + base, row0, m, rel); break;
+    case 2: emit_col<uint16_t, FROM_BUILD>((const uint16_t*)gc.src, (uint16_t*)gc.dst + base, row0, m, rel); break;
+    case 4: emit_col<uint32_t, FROM_BUILD>((const uint32_t*)gc.src, (uint32_t*)gc.dst + base, row0, m, rel); break;
+    case 8: emit_col<uint64_t, FROM_BUILD>((const uint64_t*)gc.src, (uint64_t*)gc.dst + base, row0, m, rel); break;
+    default: emit_col<ulonglong2, FROM_BUILD>((const ulonglong2*)gc.src, (ulonglong2*)gc.dst + base, row0, m, rel);
+    }
+    if (gc.src_null) emit_col<uint8_t, FROM_BUILD>(gc.src_null, gc.dst_null + base, row0, m, rel);
+}
+
+__global__ void __launch_bounds__(JT_THREADS, 2) k_join_emit(const __grid_constant__ GatherArgs g, int64_t n, const uint32_t* __restrict__ match,
+                                                              const uint64_t* __restrict__ tile_offsets, uint32_t* __restrict__ out_probe,
+                                                              uint32_t* __restrict__ out_build) {
+    constexpr int NW = JT_THREADS / 32;
+    __shared__ uint32_t cnt[JT_ROWS][NW];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t n_tiles = (n + JT_TILE - 1) / JT_TILE;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        uint64_t base = tile_offsets[tile];
-        uint32_t m[JT_ROWS];
+        const uint64_t base = tile_offsets[tile];
+        const int64_t row0 = tile * JT_TILE + threadIdx.x;
+        uint32_t m[JT_ROWS], rel[JT_ROWS], bal[JT_ROWS];
 #pragma unroll
         for (int j = 0; j < JT_ROWS; j++) {
-            const int64_t r = tile * JT_TILE + j * JT_THREADS + threadIdx.x;
+            const int64_t r = row0 + j * JT_THREADS;
             m[j] = r < n ? match[r] : 0;
         }
 #pragma unroll
         for (int j = 0; j < JT_ROWS; j++) { // slab j = 256 consecutive rows
-            const unsigned b = __ballot_sync(0xffffffffu, m[j] != 0);
-            if (lane == 0) warp_cnt[warp] = __popc(b);
-            __syncthreads();
+            bal[j] = __ballot_sync(0xffffffffu, m[j] != 0);
+            if (lane == 0) cnt[j][warp] = __popc(bal[j]);
+        }
+        __syncthreads();
+        uint32_t run = 0; // matched rows of the tile before slab j
+#pragma unroll
+        for (int j = 0; j < JT_ROWS; j++) {
             uint32_t before = 0, slab = 0;
 #pragma unroll
-            for (int w = 0; w < JT_THREADS / 32; w++) {
-                const uint32_t c = warp_cnt[w];
+            for (int w = 0; w < NW; w++) {
+                const uint32_t c = cnt[j][w];
                 before += w < warp ? c : 0;
                 slab += c;
             }
-            __syncthreads();
-            if (m[j]) {
-                const int64_t r = tile * JT_TILE + j * JT_THREADS + threadIdx.x;
-                const uint64_t pos = base + before + __popc(b & ((1u << lane) - 1));
-                const size_t bi = m[j] - 1;
-                for (int c = 0; c < g.n_cols; c++) {
-                    const GatherCol& gc = g.cols[c];
-                    const size_t s = gc.from_build ? bi : (size_t)r;
-                    switch (gc.width) {
-                    case 1: gc.dst[pos] = gc.src[s]; break;
-                    case 2: ((uint16_t*)gc.dst)[pos] = ((const uint16_t*)gc.src)[s]; break;
-                    case 4: ((uint32_t*)gc.dst)[pos] = ((const uint32_t*)gc.src)[s]; break;
-                    case 8: ((uint64_t*)gc.dst)[pos] = ((const uint64_t*)gc.src)[s]; break;
-                    default: ((ulonglong2*)gc.dst)[pos] = ((const ulonglong2*)gc.src)[s];
-                    }
-                    if (gc.src_null) gc.dst_null[pos] = gc.src_null[s];
-                }
-                if (out_probe) {
-                    out_probe[pos] = (uint32_t)r;
-                    out_build[pos] = m[j];
+            rel[j] = run + before + __popc(bal[j] & ((1u << lane) - 1));
+            run += slab;
+        }
+        __syncthreads(); // cnt[] is rewritten by the next tile
+        if (run == 0) continue;
+        for (int c = 0; c < g.n_cols; c++) {
+            const GatherCol& gc = g.cols[c];
+            if (gc.from_build) emit_col_w<true>(gc, base, row0, m, rel);
+            else emit_col_w<false>(gc, base, row0, m, rel);
+        }
+        if (out_probe) {
+#pragma unroll
+            for (int j = 0; j < JT_ROWS; j++) {
+                if (m[j]) {
+                    out_probe[base + rel[j]] = (uint32_t)(row0 + j * JT_THREADS);
+                    out_build[base + rel[j]] = m[j];
                 }
             }
-            base += slab;
         }
+    }
+}
+
+// ---- runtime filter from the build side ---------------------------------------------------------------------------------------------
+// HashJoinBuildOperator::set_finishing -> HashJoiner::create_runtime_filters (hash_join_build_operator.cpp:97-208, hash_joiner.cpp:516-611)
+// -> RuntimeBloomFilter::insert per build key (runtime_filter.h:1200-1205) + min/max (RuntimeFilterHelper). One thread per build
+// row: eight atomicOr into the key's bucket, warp-reduced min / max.
+struct RfMeta {
+    long long min, max;
+    unsigned long long inserted;
+    unsigned int has_null;
+    unsigned int _pad;
+};
+template <int W>
+__global__ void __launch_bounds__(256) k_rf_build(const uint8_t* __restrict__ keys, const uint8_t* __restrict__ nulls, int64_t n, RfView v,
+                                                   RfMeta* __restrict__ meta) {
+    long long mn = INT64_MAX, mx = INT64_MIN;
+    unsigned long long ins = 0;
+    unsigned int any_null = 0;
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        if (nulls && nulls[r]) {
+            any_null = 1;
+            continue;
+        }
+        long long x;
+        if constexpr (W == 1) x = ((const int8_t*)keys)[r];
+        else if constexpr (W == 2) x = ((const int16_t*)keys)[r];
+        else if constexpr (W == 4) x = ((const int32_t*)keys)[r];
+        else x = ((const long long*)keys)[r];
+        const uint64_t hash = (uint64_t)x; // std::hash of an integer = its sign-extended value; phmap_mix<8> is the identity here
+        uint32_t* b = v.dir + (size_t)((uint32_t)hash & v.directory_mask) * 8;
+        const uint32_t key = (uint32_t)(hash >> v.log_num_buckets);
+#pragma unroll
+        for (int i = 0; i < 8; i++) atomicOr(&b[i], rf_word_mask(key, i));
+        mn = x < mn ? x : mn;
+        mx = x > mx ? x : mx;
+        ins++;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        long long a = __shfl_down_sync(0xffffffffu, mn, o), c = __shfl_down_sync(0xffffffffu, mx, o);
+        mn = a < mn ? a : mn;
+        mx = c > mx ? c : mx;
+        ins += __shfl_down_sync(0xffffffffu, ins, o);
+        any_null |= __shfl_down_sync(0xffffffffu, any_null, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (ins) {
+            atomicMin(&meta->min, mn);
+            atomicMax(&meta->max, mx);
+            atomicAdd(&meta->inserted, ins);
+        }
+        if (any_null) atomicOr(&meta->has_null, 1u);
     }
 }
 
@@ -621,6 +705,52 @@ public:
         SRB_CUDA(cudaGetLastError());
         SRB_CUDA(cudaStreamSynchronize(stream));
         out_rows_ = m;
+    }
+
+    // partial runtime filter over build key column `key_index`; expected_rows sizes the directory (0: this op's build rows) so that
+    // the partial filters of several ranks can be merged (SimdBlockFilter::merge needs equal sizes)
+    srb_runtime_filter* build_runtime_filter(int key_index, int64_t expected_rows) override {
+        if (!build_done_) throw Error(SRB_INTERNAL_ERROR, "runtime filter requested before the build side finished");
+        if (key_index < 0 || key_index >= (int)bkeys_.size()) throw Error(SRB_INVALID_ARGUMENT, "bad build key index");
+        const GrowCol& kc = bcols_[key_index];
+        if (build_rows_ > 0 && (is_binary(kc.type) || kc.type == SRB_TYPE_DOUBLE || kc.width > 8))
+            throw Error(SRB_NOT_IMPLEMENTED, "runtime filters cover integer, DATE and DECIMAL32/64 keys");
+        auto rf = std::make_unique<srb_runtime_filter>();
+        rf->ctx = ctx;
+        rf->key_type = kc.type;
+        rf->key_width = kc.width;
+        rf->log_num_buckets = rf_log_num_buckets((uint64_t)(expected_rows > 0 ? expected_rows : build_rows_));
+        rf->directory_mask = (uint32_t)(((uint64_t)1 << rf->log_num_buckets) - 1);
+        rf->dir.ensure(ctx, rf->dir_bytes());
+        SRB_CUDA(cudaMemsetAsync(rf->dir.p, 0, rf->dir_bytes(), stream));
+        DevBuf meta;
+        PinnedBuf hmeta;
+        meta.ensure(ctx, sizeof(RfMeta));
+        hmeta.ensure(sizeof(RfMeta));
+        RfMeta* hm = hmeta.as<RfMeta>();
+        *hm = RfMeta{INT64_MAX, INT64_MIN, 0, 0, 0};
+        SRB_CUDA(cudaMemcpyAsync(meta.p, hm, sizeof(RfMeta), cudaMemcpyHostToDevice, stream));
+        if (build_rows_ > 0) {
+            const uint8_t* keys = kc.data.as<uint8_t>();
+            const uint8_t* nulls = kc.nullable ? kc.nulls.as<uint8_t>() : nullptr;
+            const int grid = grid_for(build_rows_);
+            const RfView v = rf->view();
+            switch (kc.width) {
+            case 1: k_rf_build<1><<<grid, 256, 0, stream>>>(keys, nulls, build_rows_, v, meta.as<RfMeta>()); break;
+            case 2: k_rf_build<2><<<grid, 256, 0, stream>>>(keys, nulls, build_rows_, v, meta.as<RfMeta>()); break;
+            case 4: k_rf_build<4><<<grid, 256, 0, stream>>>(keys, nulls, build_rows_, v, meta.as<RfMeta>()); break;
+            default: k_rf_build<8><<<grid, 256, 0, stream>>>(keys, nulls, build_rows_, v, meta.as<RfMeta>());
+            }
+            SRB_CUDA(cudaGetLastError());
+            launches++;
+        }
+        SRB_CUDA(cudaMemcpyAsync(hm, meta.p, sizeof(RfMeta), cudaMemcpyDeviceToHost, stream));
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        rf->min = hm->min;
+        rf->max = hm->max;
+        rf->inserted = (int64_t)hm->inserted;
+        rf->has_null = hm->has_null != 0;
+        return rf.release();
     }
 
     srb_status probe_pull_chunk(srb_chunk* out, bool all) override { return pull(out, all, false); }

@@ -491,6 +491,81 @@ __global__ void __launch_bounds__(256) k_filter_mask_ranges(const __grid_constan
     }
 }
 
+// Runtime filter on the scan side (Operator::eval_runtime_bloom_filters, pipeline/operator.h:185; RuntimeBloomFilter::_t_evaluate,
+// exprs/runtime_filter.h:1369-1422): rows still selected by the mask keep their bit only if the key lies in [min, max] and the
+// bucket of its hash has all eight bits set; NULL keys keep it iff the build side inserted a NULL. Four rows per thread and step:
+// the key loads of the four rows are issued together, then their 32-byte bucket loads (the directory of a build side of a few
+// 10^7 keys is tens of MB: L2-resident), then the ballots rewrite the mask words and the tile's count.
+struct RfArgs {
+    RfView v;
+    const uint8_t* data; // key column, already offset to the first row of the range
+    const uint8_t* nulls;
+};
+template <int W>
+__global__ void __launch_bounds__(256) k_filter_rf(const __grid_constant__ RfArgs a, int64_t n, uint32_t* __restrict__ mask,
+                                                    uint32_t* __restrict__ tile_counts) {
+    __shared__ uint32_t wcount[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t tile0 = (int64_t)blockIdx.x * FTILE;
+    const uint4* dir = (const uint4*)a.v.dir;
+    uint32_t mine = 0;
+#pragma unroll 1
+    for (int it = 0; it < FTILE / 256; it += 4) {
+        bool on[4], test[4];
+        long long x[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int64_t i = tile0 + (int64_t)(it + u) * 256 + threadIdx.x; // bit `lane` of mask word i >> 5
+            on[u] = i < n && ((mask[i >> 5] >> lane) & 1u);
+            test[u] = on[u];
+            x[u] = 0;
+            if (on[u]) {
+                if (a.nulls && a.nulls[i]) {
+                    on[u] = a.v.has_null != 0;
+                    test[u] = false;
+                } else if constexpr (W == 1) x[u] = ((const int8_t*)a.data)[i];
+                else if constexpr (W == 2) x[u] = ((const int16_t*)a.data)[i];
+                else if constexpr (W == 4) x[u] = ((const int32_t*)a.data)[i];
+                else x[u] = ((const long long*)a.data)[i];
+            }
+        }
+        uint4 b0[4], b1[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            if (test[u] && (x[u] < a.v.min || x[u] > a.v.max)) on[u] = test[u] = false;
+            b0[u] = b1[u] = make_uint4(0, 0, 0, 0);
+            if (test[u]) {
+                const size_t bucket = (uint32_t)(uint64_t)x[u] & a.v.directory_mask;
+                b0[u] = __ldg(dir + bucket * 2);
+                b1[u] = __ldg(dir + bucket * 2 + 1);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            if (test[u]) {
+                const uint32_t key = (uint32_t)((uint64_t)x[u] >> a.v.log_num_buckets);
+                const uint32_t miss = (~b0[u].x & rf_word_mask(key, 0)) | (~b0[u].y & rf_word_mask(key, 1)) | (~b0[u].z & rf_word_mask(key, 2)) |
+                                      (~b0[u].w & rf_word_mask(key, 3)) | (~b1[u].x & rf_word_mask(key, 4)) | (~b1[u].y & rf_word_mask(key, 5)) |
+                                      (~b1[u].z & rf_word_mask(key, 6)) | (~b1[u].w & rf_word_mask(key, 7));
+                on[u] = miss == 0;
+            }
+            const uint32_t w = __ballot_sync(0xffffffffu, on[u]);
+            const int64_t i = tile0 + (int64_t)(it + u) * 256 + threadIdx.x;
+            if (lane == 0 && i < n) {
+                mask[i >> 5] = w;
+                mine += __popc(w);
+            }
+        }
+    }
+    if (lane == 0) wcount[warp] = mine;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int w = 0; w < 8; w++) t += wcount[w];
+        tile_counts[blockIdx.x] = t;
+    }
+}
+
 // exclusive scan of the tile counts (a few to ~10^5 entries): one block; every thread sums a contiguous run, the 1024 run
 // totals are scanned with warp shuffles, then every thread writes its run's offsets
 __global__ void __launch_bounds__(1024) k_scan_tiles(const uint32_t* __restrict__ counts, uint64_t* __restrict__ offsets, int64_t n_tiles,
@@ -548,10 +623,10 @@ struct CompactArgs {
 template <class T>
 SRB_D void compact_words(const T* __restrict__ src, T* __restrict__ dst, uint32_t my_bits, uint32_t my_pos, int lane) {
     const uint32_t below = (1u << lane) - 1u;
-#pragma unroll 1
     constexpr int U = sizeof(T) > 8 ? 4 : 8;
+#pragma unroll 1
     for (int w0 = 0; w0 < 32; w0 += U) {
-        T v[U];
+        T v[U] = {};
         uint32_t at[U];
         bool take[U];
 #pragma unroll
@@ -568,7 +643,7 @@ SRB_D void compact_words(const T* __restrict__ src, T* __restrict__ dst, uint32_
     }
 }
 
-__global__ void __launch_bounds__(256, 3) k_compact(const __grid_constant__ CompactArgs ca, int64_t n, const uint32_t* __restrict__ mask,
+__global__ void __launch_bounds__(256, 4) k_compact(const __grid_constant__ CompactArgs ca, int64_t n, const uint32_t* __restrict__ mask,
                                                   const uint64_t* __restrict__ tile_offsets) {
     __shared__ uint32_t wtot[8];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -714,6 +789,15 @@ public:
         }
     }
 
+    // Operator::set_runtime_bloom_filters / eval_runtime_bloom_filters (pipeline/operator.h:185): a scan-filter operator narrows its
+    // selection with the join's runtime filter on column `slot` before compacting. Attach before the first chunk is pushed.
+    void add_runtime_filter(const srb_runtime_filter* rf, int slot) override {
+        if (!rf) throw Error(SRB_INVALID_ARGUMENT, "null runtime filter");
+        if (!filter_only_) throw Error(SRB_NOT_IMPLEMENTED, "runtime filters attach to scan-filter operators (plans without aggregates)");
+        if (lowered_) throw Error(SRB_INTERNAL_ERROR, "runtime filters must be attached before the first chunk is pushed");
+        rfs_.push_back(RfBind{rf, slot, -1});
+    }
+
     void set_finishing() override {
         if (finishing) return;
         finishing = true;
@@ -840,6 +924,23 @@ private:
                     L_.prog.cols[idx].kind = is_binary(c->type) ? CK_BINARY : (c->type == SRB_TYPE_DOUBLE ? CK_DOUBLE : CK_INT);
                     L_.prog.n_cols = idx + 1;
                 }
+            }
+            for (auto& r : rfs_) { // the key column of every runtime filter is bound like an output column
+                for (size_t i = 0; i < L_.cols.size(); i++)
+                    if (L_.cols[i].slot == r.slot) r.col = (int)i;
+                if (r.col < 0) {
+                    const srb_column* c = find_slot(first, r.slot);
+                    if (!c) throw Error(SRB_INVALID_ARGUMENT, fmt("runtime filter slot %d not in chunk", r.slot));
+                    if ((int)L_.cols.size() >= MAX_COLS) throw Error(SRB_NOT_IMPLEMENTED, "too many columns");
+                    r.col = (int)L_.cols.size();
+                    L_.cols.push_back({r.slot, c->type, c->precision, c->scale, c->nulls != nullptr});
+                    L_.prog.cols[r.col].width = type_width(c->type);
+                    L_.prog.cols[r.col].kind = CK_INT;
+                    L_.prog.n_cols = r.col + 1;
+                }
+                const int t = L_.cols[r.col].type;
+                if (is_binary(t) || t == SRB_TYPE_DOUBLE || type_width(t) > 8 || type_width(t) != r.rf->key_width)
+                    throw Error(SRB_INVALID_ARGUMENT, fmt("runtime filter on slot %d: column type does not match the build key", r.slot));
             }
             for (int s : plan_.out_slots)
                 for (size_t i = 0; i < L_.cols.size(); i++)
@@ -1202,6 +1303,18 @@ private:
             } else {
                 k_filter_mask<<<(int)tiles, 256, 0, stream>>>(L_.prog, off, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>());
             }
+            for (const auto& r : rfs_) { // runtime filters narrow the mask before anything is copied
+                const int ci = r.col;
+                const int w = P.cols[ci].width;
+                RfArgs ra{r.rf->view(), (const uint8_t*)cols[ci].data + (size_t)off * w, cols[ci].nulls ? cols[ci].nulls + off : nullptr};
+                switch (w) {
+                case 1: k_filter_rf<1><<<(int)tiles, 256, 0, stream>>>(ra, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>()); break;
+                case 2: k_filter_rf<2><<<(int)tiles, 256, 0, stream>>>(ra, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>()); break;
+                case 4: k_filter_rf<4><<<(int)tiles, 256, 0, stream>>>(ra, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>()); break;
+                default: k_filter_rf<8><<<(int)tiles, 256, 0, stream>>>(ra, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>());
+                }
+                launches++;
+            }
             k_scan_tiles<<<1, 1024, 0, stream>>>(tile_counts_.as<uint32_t>(), tile_offsets_.as<uint64_t>(), tiles, ctr_dev_.as<Counters>());
             launches += 2;
             Counters* hc = ctr_host_.as<Counters>();
@@ -1236,6 +1349,11 @@ private:
     struct FOut {
         DevBuf data, nulls;
     };
+    struct RfBind {
+        const srb_runtime_filter* rf;
+        int slot, col;
+    };
+    std::vector<RfBind> rfs_;
     void grow_out(DevBuf& b, size_t used, size_t need) {
         if (need <= b.bytes) return;
         size_t ncap = std::max(need, b.bytes * 2);

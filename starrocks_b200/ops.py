@@ -29,7 +29,7 @@ EXPORTS = [
     "srb_join_probe_pull_all", "srb_join_probe_pull_device",
     "srb_device_alloc", "srb_device_free", "srb_pinned_alloc", "srb_pinned_free", "srb_memcpy_h2d", "srb_memcpy_d2h",
     "srb_partition_create", "srb_partition_run", "srb_partition_destroy",
-    "srb_comm_unique_id", "srb_comm_create", "srb_comm_destroy", "srb_comm_stream", "srb_comm_all_to_all", "srb_comm_all_gather",
+    "srb_comm_unique_id", "srb_comm_create", "srb_comm_destroy", "srb_comm_stream", "srb_comm_all_to_all", "srb_comm_all_gather", "srb_comm_shuffle", "srb_comm_counters",
 ]
 
 
@@ -90,6 +90,8 @@ def lib() -> C.CDLL:
     L.srb_comm_stream.restype = vp
     L.srb_comm_all_to_all.argtypes = [vp, C.POINTER(K.srb_chunk), C.POINTER(i64), C.POINTER(K.srb_chunk), C.POINTER(i64)]
     L.srb_comm_all_gather.argtypes = [vp, C.POINTER(K.srb_chunk), C.POINTER(K.srb_chunk)]
+    L.srb_comm_shuffle.argtypes = [vp, C.POINTER(K.srb_chunk), C.c_int32, C.POINTER(C.c_int32), C.POINTER(K.srb_chunk), C.POINTER(i64)]
+    L.srb_comm_counters.argtypes = [vp, C.POINTER(i64)]
     _lib = L
     return L
 
@@ -397,6 +399,21 @@ class Communicator:
         out = K.srb_chunk()
         _check(self.L.srb_comm_all_to_all(self.h, C.byref(cch), sc, C.byref(out), rc))
         return _raw_chunk(out), list(rc)
+
+    def shuffle(self, chunk: K.Chunk, key_slots):
+        """Hash partitioning fused with the exchange: rows are scattered straight into the destination ranks' receive buffers over
+        peer memory (srb_comm_shuffle). -> (device Chunk of the rows this rank received, [rows per source rank])"""
+        cch, keep = chunk.to_c()
+        ks = (C.c_int32 * len(key_slots))(*key_slots)
+        rc = (C.c_int64 * self.ctx.world_size)()
+        out = K.srb_chunk()
+        _check(self.L.srb_comm_shuffle(self.h, C.byref(cch), len(key_slots), ks, C.byref(out), rc))
+        return _raw_chunk(out), list(rc)
+
+    def launches(self) -> int:
+        n = C.c_int64()
+        _check(self.L.srb_comm_counters(self.h, C.byref(n)))
+        return n.value
 
     def all_gather(self, chunk: K.Chunk) -> K.Chunk:
         """Every rank's rows on every rank, rank 0 first. Device chunks (fixed-width columns) stay on the device; host chunks

@@ -35,15 +35,22 @@ class TpchQ3:
     STAGES = ["customer filter (+ broadcast) + build J1", "orders filter", "probe J1 (+ shuffle) + build J2", "lineitem filter (+ shuffle)",
               "probe J2 + gather", "group by"]
 
-    def __init__(self, ctx, comm=None, part=None):
+    def __init__(self, ctx, comm=None, part=None, fused: Optional[bool] = None):
+        """fused (default: unless SRB_NO_P2P is set): shuffle with Communicator.shuffle (peer-memory scatter) instead of
+        Partitioner.run + Communicator.all_to_all (NCCL send/recv)"""
+        import os
         self.ctx, self.comm, self.part = ctx, comm, part
+        self.fused = (not os.environ.get("SRB_NO_P2P")) if fused is None else fused
         self.open = []
 
     def _shuffle(self, chunk, key_slot):
         if self.comm is None:
             return chunk
-        if chunk is None or not chunk.n_rows:
-            raise ValueError("a rank with no rows to shuffle cannot describe the schema of the exchange; give every rank at least one row")
+        if chunk is None:
+            raise ValueError("a rank with no chunk to shuffle cannot describe the schema of the exchange")
+        if self.fused:  # partitioning fused with the exchange: rows are scattered straight into the peers' receive buffers
+            recv, _ = self.comm.shuffle(chunk, [key_slot])
+            return recv
         grouped, counts = self.part.run(chunk, [key_slot])
         recv, _ = self.comm.all_to_all(grouped, counts)
         return recv

@@ -66,6 +66,20 @@ def test_single_rank_communicator_round_trip(ctx):
         assert K.chunk_rows(ctx.fetch_chunk(recv), sort=False) == K.chunk_rows(ch, sort=False)
         allg = comm.all_gather(dch)
         assert K.chunk_rows(ctx.fetch_chunk(allg), sort=False) == K.chunk_rows(ch, sort=False)
+        # the fused shuffle on one rank: every row routes to rank 0 and lands in the receive arena (any order)
+        for rows in (10_000, 3, 10_000):  # the arena is reused, then regrown
+            part_in = ops.slice_chunk(ch, 0, rows)
+            d2, p2 = ctx.device_chunk(part_in)
+            got, rc2 = comm.shuffle(d2, [Q.HC_K])
+            assert rc2 == [rows] and K.chunk_rows(ctx.fetch_chunk(got)) == K.chunk_rows(part_in)
+            for p in p2:
+                ctx.device_free(p)
+        big = T.host_chunk("lineitem", 0, 300_000, ["l_orderkey", "l_extendedprice", "l_shipdate"])
+        d3, p3 = ctx.device_chunk(big)
+        got, rc3 = comm.shuffle(d3, [Q.L_ORDERKEY])
+        assert rc3 == [big.n_rows] and K.chunk_rows(ctx.fetch_chunk(got)) == K.chunk_rows(big) and comm.launches() >= 8
+        for p in p3:
+            ctx.device_free(p)
         # host chunks of any column kind (the intermediate rows of a low-cardinality plan: DECIMAL128 sums, {sum,count} blobs, nullable)
         li = T.host_chunk("lineitem", 0, 50_000, T.LINEITEM_Q1)
         op = ops.ScanAggOperator(ctx, Q.q1_plan(phase=K.AGG_UPDATE_SERIALIZE))
@@ -164,11 +178,16 @@ def _worker(rank, world, port, n_rows, n_keys, out_q):
         op1.set_finishing()
         inter = op1.pull_device()
         grouped, counts = part.run(inter, [0])
-        recv, _ = comm.all_to_all(grouped, counts)
+        recv, rcounts = comm.all_to_all(grouped, counts)
         op2 = ops.ScanAggOperator(ctx, Q.highcard_merge_plan())
         op2.push_chunk(recv)
         op2.set_finishing()
         rows = K.chunk_rows(op2.pull_all())
+        # the fused shuffle (scatter into the peers' receive arenas) delivers the same rows from the same sources
+        recv_nccl = K.chunk_rows(ctx.fetch_chunk(recv))
+        for _ in range(2):
+            recv2, rcounts2 = comm.shuffle(inter, [0])
+            assert rcounts2 == rcounts and K.chunk_rows(ctx.fetch_chunk(recv2)) == recv_nccl
         # low-cardinality plan: phase 1 on the rank's lineitem rows, host gather of the <= 4 intermediate rows, phase 2 everywhere
         lb, le = D.shard_range(n_rows, rank, world)
         li = T.host_chunk("lineitem", lb, le - lb, T.LINEITEM_Q1)
