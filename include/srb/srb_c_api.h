@@ -269,6 +269,32 @@ srb_status srb_join_probe_pull_chunk(srb_op* op, srb_chunk* out);
 srb_status srb_join_probe_pull_all(srb_op* op, srb_chunk* out);
 srb_status srb_join_probe_pull_device(srb_op* op, srb_chunk* out);
 
+/* ---- runtime filters: the join's build side narrows the probe side's scan ---------------------------------------
+ * HashJoinBuildOperator::set_finishing creates partial runtime filters from the build keys (hash_join_build_operator.cpp:97-208,
+ * hash_joiner.cpp:516-611): a RuntimeBloomFilter = SimdBlockFilter (exprs/runtime_filter.h:79-222, runtime_filter.cpp:26-35,114-123)
+ * + min / max + has_null (runtime_filter.h:1192-1209). The probe-side scan evaluates them on its key column and drops rows that
+ * cannot match (Operator::eval_runtime_bloom_filters, pipeline/operator.h:185; RuntimeBloomFilter::_t_evaluate, runtime_filter.h:
+ * 1369-1422: selection[i] &= test(key[i]); NULL keys pass iff has_null). The directory holds exactly the bits the reference's
+ * filter of the same size would hold for the same keys. Key types: integers up to 8 bytes, DATE, DECIMAL32/64. */
+typedef struct srb_runtime_filter srb_runtime_filter;
+/* `join` must have finished its build (srb_op_set_finishing). key_index: which build key column. expected_rows sizes the filter as
+ * SimdBlockFilter::init(expected_rows) does (0: the rows this operator built from); ranks that will merge their filters pass the
+ * same value. hash_mix = 0: the key's hash is RuntimeBloomFilter::compute_hash as the reference tree builds it — phmap_mix<8>
+ * of std::hash, and phmap_mix is the identity unless ENABLE_PHMAP_MIX is defined (util/phmap/phmap_utils.h:72-124; nothing in the tree
+ * defines it), so the directory is bit-identical to a BE-built filter and can be merged with one. hash_mix = 1: the multiplicative
+ * phmap_mix<8> of the same header (:85-95). Which rows a filter lets through by accident differs between the two; no query result
+ * does. Sparse key domains (TPC-H order keys use 8 of every 32 values) fill a quarter of the buckets under the identity hash.
+ * The filter is independent of the operator afterwards; free it with srb_runtime_filter_destroy. */
+srb_status srb_join_build_runtime_filter(srb_op* join, int32_t key_index, int64_t expected_rows, int32_t hash_mix, srb_runtime_filter** out);
+/* attach to a scan-filter operator (a srb_scan_agg plan without aggregates) BEFORE its first srb_op_push_chunk: rows whose column
+ * `slot_id` fails the filter are dropped together with those failing the plan's predicates. The filter must outlive the operator. */
+srb_status srb_op_add_runtime_filter(srb_op* scan, const srb_runtime_filter* rf, int32_t slot_id);
+srb_status srb_runtime_filter_info(const srb_runtime_filter* rf, int64_t* n_buckets, int64_t* min_value, int64_t* max_value, int32_t* has_null,
+                                   int64_t* inserted);
+/* copies the directory (n_buckets x 8 uint32) to host memory: what the tests compare with the oracle's SimdBlockFilter */
+srb_status srb_runtime_filter_directory(const srb_runtime_filter* rf, void* dst, int64_t bytes);
+void srb_runtime_filter_destroy(srb_runtime_filter* rf);
+
 /* ---- exchange: what replaces ExchangeSinkOperator / ExchangeSourceOperator + brpc between GPUs ---------------------- */
 typedef struct srb_partitioner srb_partitioner;
 typedef struct srb_comm srb_comm; /* one NCCL communicator over the ctx's rank / world_size */
@@ -302,6 +328,9 @@ srb_status srb_comm_all_to_all(srb_comm* c, const srb_chunk* send, const int64_t
  * a source's range unspecified). Needs peer access between the GPUs; fails with INTERNAL_ERROR otherwise. */
 srb_status srb_comm_shuffle(srb_comm* c, const srb_chunk* in, int32_t n_key_slots, const int32_t* key_slots, srb_chunk* recv,
                             int64_t* recv_counts);
+/* global runtime filter: OR of every rank's partial filter (SimdBlockFilter::merge), min / max / has_null combined; every rank ends
+ * up with the merged filter in place. All ranks must have built theirs with the same expected_rows. */
+srb_status srb_comm_merge_runtime_filter(srb_comm* c, srb_runtime_filter* rf);
 /* kernels launched by this communicator's fused shuffles so far */
 srb_status srb_comm_counters(srb_comm* c, int64_t* kernel_launches);
 /* UNPARTITIONED / broadcast exchange (exchange_sink_operator.cpp:508-547): every rank's rows replicated on every rank */

@@ -2,6 +2,7 @@
 #include <string>
 
 #include "orc_agg.h"
+#include "orc_rf.h"
 
 namespace orc {
 Result* run_scan_agg(const srb_scan_agg_plan* plan, const srb_chunk* in, int n_threads, int chunk_size);
@@ -95,6 +96,52 @@ uint32_t orc_xorshift32(uint32_t x) { return orc::xorshift32(x); }
 uint32_t orc_shuffle_channel(const void* value, int32_t width, uint32_t n_channels) {
     return orc::reduce_op(orc::fnv_hash(value, width, orc::FNV_SEED), n_channels);
 }
+// ---- runtime filter (orc_rf.h) ------------------------------------------------------------------------------------------------
+void* orc_rf_create(uint64_t nums, int mix) {
+    auto* f = new orc::RuntimeBloomFilter();
+    f->mix = mix != 0;
+    f->bf.init((size_t)nums);
+    return f;
+}
+void orc_rf_free(void* f) { delete (orc::RuntimeBloomFilter*)f; }
+void orc_rf_insert_hash(void* f, uint64_t hash) { ((orc::RuntimeBloomFilter*)f)->bf.insert_hash(hash); }
+int orc_rf_test_hash(void* f, uint64_t hash) { return ((orc::RuntimeBloomFilter*)f)->bf.test_hash(hash) ? 1 : 0; }
+// keys: n values of `width` bytes (1/2/4/8, signed), nulls optional
+void orc_rf_insert_column(void* f, const void* keys, int width, int64_t n, const uint8_t* nulls) {
+    auto* rf = (orc::RuntimeBloomFilter*)f;
+    for (int64_t i = 0; i < n; i++) {
+        if (nulls && nulls[i]) {
+            rf->insert_null();
+            continue;
+        }
+        int64_t v = width == 1 ? ((const int8_t*)keys)[i] : width == 2 ? ((const int16_t*)keys)[i] : width == 4 ? ((const int32_t*)keys)[i] : ((const int64_t*)keys)[i];
+        rf->insert(v);
+    }
+}
+// selection[i] = evaluate(selection[i], null, key) for every row (RuntimeBloomFilter::_t_evaluate)
+void orc_rf_evaluate(void* f, const void* keys, int width, int64_t n, const uint8_t* nulls, uint8_t* selection) {
+    auto* rf = (orc::RuntimeBloomFilter*)f;
+    for (int64_t i = 0; i < n; i++) {
+        int64_t v = width == 1 ? ((const int8_t*)keys)[i] : width == 2 ? ((const int16_t*)keys)[i] : width == 4 ? ((const int32_t*)keys)[i] : ((const int64_t*)keys)[i];
+        selection[i] = rf->evaluate(selection[i], nulls && nulls[i], v);
+    }
+}
+int orc_rf_test_data(void* f, int64_t v) { return ((orc::RuntimeBloomFilter*)f)->test_data(v) ? 1 : 0; }
+int64_t orc_rf_info(void* f, int what) { // 0 n_buckets, 1 min, 2 max, 3 has_null, 4 inserted
+    auto* rf = (orc::RuntimeBloomFilter*)f;
+    switch (what) {
+    case 0: return (int64_t)1 << rf->bf.log_num_buckets;
+    case 1: return rf->min;
+    case 2: return rf->max;
+    case 3: return rf->has_null ? 1 : 0;
+    default: return rf->inserted;
+    }
+}
+void orc_rf_directory(void* f, uint32_t* out) {
+    auto* rf = (orc::RuntimeBloomFilter*)f;
+    std::copy(rf->bf.directory.begin(), rf->bf.directory.end(), out);
+}
+
 #if defined(__SSE4_2__)
 // hardware cross-check of the software CRC32C
 uint32_t orc_hw_crc32c_u64(uint32_t crc, uint64_t v) { return (uint32_t)_mm_crc32_u64(crc, v); }

@@ -206,6 +206,49 @@ srb_status srb_join_probe_pull_all(srb_op* op, srb_chunk* out) {
     SRB_API_END
 }
 
+// ---- runtime filters ---------------------------------------------------------------------------------------------------------
+srb_status srb_join_build_runtime_filter(srb_op* op, int32_t key_index, int64_t expected_rows, int32_t hash_mix, srb_runtime_filter** out) {
+    SRB_API_BEGIN
+    OP_GUARD(op)
+    if (!out) throw srb::Error(SRB_INVALID_ARGUMENT, "null out");
+    *out = op->build_runtime_filter(key_index, expected_rows, hash_mix);
+    return SRB_OK;
+    SRB_API_END
+}
+srb_status srb_op_add_runtime_filter(srb_op* op, const srb_runtime_filter* rf, int32_t slot_id) {
+    SRB_API_BEGIN
+    OP_GUARD(op)
+    op->add_runtime_filter(rf, slot_id);
+    return SRB_OK;
+    SRB_API_END
+}
+srb_status srb_runtime_filter_info(const srb_runtime_filter* rf, int64_t* n_buckets, int64_t* min_value, int64_t* max_value, int32_t* has_null,
+                                   int64_t* inserted) {
+    SRB_API_BEGIN
+    if (!rf) throw srb::Error(SRB_INVALID_ARGUMENT, "null runtime filter");
+    if (n_buckets) *n_buckets = (int64_t)1 << rf->log_num_buckets;
+    if (min_value) *min_value = rf->min;
+    if (max_value) *max_value = rf->max;
+    if (has_null) *has_null = rf->has_null ? 1 : 0;
+    if (inserted) *inserted = rf->inserted;
+    return SRB_OK;
+    SRB_API_END
+}
+srb_status srb_runtime_filter_directory(const srb_runtime_filter* rf, void* dst, int64_t bytes) {
+    SRB_API_BEGIN
+    if (!rf || !dst) throw srb::Error(SRB_INVALID_ARGUMENT, "null argument");
+    if (bytes != (int64_t)rf->dir_bytes()) throw srb::Error(SRB_INVALID_ARGUMENT, "directory size mismatch (32 bytes per bucket)");
+    SRB_CUDA(cudaSetDevice(rf->ctx->cfg.device));
+    SRB_CUDA(cudaMemcpy(dst, rf->dir.p, (size_t)bytes, cudaMemcpyDeviceToHost));
+    return SRB_OK;
+    SRB_API_END
+}
+void srb_runtime_filter_destroy(srb_runtime_filter* rf) {
+    if (!rf) return;
+    cudaSetDevice(rf->ctx->cfg.device);
+    delete rf;
+}
+
 srb_status srb_device_alloc(srb_ctx* ctx, int64_t bytes, void** out) {
     SRB_API_BEGIN
     if (!ctx || !out || bytes < 0) throw srb::Error(SRB_INVALID_ARGUMENT, "bad argument");

@@ -264,7 +264,8 @@ struct RfView {
     int32_t log_num_buckets;
     int64_t min, max; // over the inserted non-NULL keys (min > max: nothing inserted)
     int32_t has_null;
-    int32_t _pad;
+    int32_t mix; // 0: hash = key (the reference tree as it builds: phmap_mix is the identity); 1: hash = phmap_mix<8>(key), what the
+                 // same source computes when ENABLE_PHMAP_MIX is defined (phmap_utils.h:85-95)
 };
 SRB_HD uint32_t rf_salt(int i) {
     switch (i) {
@@ -279,6 +280,7 @@ SRB_HD uint32_t rf_salt(int i) {
     }
 }
 SRB_HD uint32_t rf_word_mask(uint32_t key, int i) { return 1u << ((key * rf_salt(i)) >> 27); }
+SRB_HD uint64_t rf_hash(long long key, int mix) { return mix ? phmap_mix8((uint64_t)key, 1) : (uint64_t)key; }
 SRB_HD int rf_log_num_buckets(uint64_t nums) { // SimdBlockFilter::init: max(1, ceil(log2(max(1, nums))) - 5)
     if (nums < 1) nums = 1;
     int log_heap = 0;

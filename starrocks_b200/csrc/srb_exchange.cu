@@ -838,6 +838,68 @@ srb_status srb_comm_shuffle(srb_comm* c, const srb_chunk* in, int32_t n_key_slot
     X_END
 }
 
+// Global runtime filter (RuntimeFilterMerger / SimdBlockFilter::merge, exprs/runtime_filter.cpp): the partial filters of all ranks,
+// built with the same expected_rows, are all-gathered and ORed bucket by bucket; min / max / has_null / inserted combine on the host.
+namespace srb {
+__global__ void __launch_bounds__(256) k_rf_or(uint32_t* __restrict__ dir, const uint32_t* __restrict__ all, int64_t words, int world) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (int64_t)gridDim.x * blockDim.x) {
+        uint32_t v = 0;
+        for (int r = 0; r < world; r++) v |= all[(size_t)r * words + i];
+        dir[i] = v;
+    }
+}
+} // namespace srb
+
+srb_status srb_comm_merge_runtime_filter(srb_comm* c, srb_runtime_filter* rf) {
+    X_BEGIN
+    if (!c || !rf) throw Error(SRB_INVALID_ARGUMENT, "null argument");
+    SRB_CUDA(cudaSetDevice(c->ctx->cfg.device));
+    const int W = c->world;
+    c->counts_dev.ensure(c->ctx, (size_t)(5 + 5 * W) * 8);
+    c->counts_host.ensure((size_t)(5 + 5 * W) * 8);
+    int64_t* hc = c->counts_host.as<int64_t>();
+    int64_t* dc = c->counts_dev.as<int64_t>();
+    hc[0] = rf->log_num_buckets;
+    hc[1] = rf->min;
+    hc[2] = rf->max;
+    hc[3] = rf->has_null ? 1 : 0;
+    hc[4] = rf->inserted;
+    hc[0] |= (int64_t)rf->mix << 32; // filters hashed differently cannot be merged either
+    SRB_CUDA(cudaMemcpyAsync(dc, hc, 5 * 8, cudaMemcpyHostToDevice, c->stream));
+    SRB_NCCL(nccl().AllGather(dc, dc + 5, 5, ncclInt64_, c->comm, c->stream));
+    SRB_CUDA(cudaMemcpyAsync(hc + 5, dc + 5, (size_t)5 * W * 8, cudaMemcpyDeviceToHost, c->stream));
+    SRB_CUDA(cudaStreamSynchronize(c->stream));
+    int64_t mn = INT64_MAX, mx = INT64_MIN, ins = 0;
+    bool has_null = false;
+    for (int r = 0; r < W; r++) {
+        const int64_t* m = hc + 5 + (size_t)r * 5;
+        if (m[0] != hc[0])
+            throw Error(SRB_INVALID_ARGUMENT, "runtime filters of different sizes / hash modes cannot be merged: build them with the same expected_rows and hash_mix");
+        mn = std::min(mn, m[1]);
+        mx = std::max(mx, m[2]);
+        has_null = has_null || m[3] != 0;
+        ins += m[4];
+    }
+    if (W > 1) {
+        const size_t bytes = rf->dir_bytes();
+        DevBuf all;
+        all.ensure(c->ctx, bytes * (size_t)W);
+        SRB_NCCL(nccl().AllGather(rf->dir.p, all.p, bytes, ncclUint8_, c->comm, c->stream));
+        const int64_t words = (int64_t)(bytes / 4);
+        int grid = (int)std::max<int64_t>(1, std::min<int64_t>((words + 255) / 256, (int64_t)c->ctx->n_sms * 8));
+        k_rf_or<<<grid, 256, 0, c->stream>>>((uint32_t*)rf->dir.p, all.as<uint32_t>(), words, W);
+        SRB_CUDA(cudaGetLastError());
+        SRB_CUDA(cudaStreamSynchronize(c->stream));
+        c->x_launches++;
+    }
+    rf->min = mn;
+    rf->max = mx;
+    rf->has_null = has_null;
+    rf->inserted = ins;
+    return SRB_OK;
+    X_END
+}
+
 srb_status srb_comm_counters(srb_comm* c, int64_t* kernel_launches) {
     if (!c || !kernel_launches) return SRB_INVALID_ARGUMENT;
     *kernel_launches = c->x_launches;

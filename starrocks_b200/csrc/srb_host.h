@@ -317,7 +317,7 @@ struct srb_op {
     virtual srb_status probe_pull_chunk(srb_chunk*, bool) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
     virtual srb_status probe_pull_device(srb_chunk*) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
     // runtime filters: join ops build them from their build side, scan-filter ops apply them
-    virtual struct srb_runtime_filter* build_runtime_filter(int, int64_t) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
+    virtual struct srb_runtime_filter* build_runtime_filter(int, int64_t, int) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
     virtual void add_runtime_filter(const struct srb_runtime_filter*, int) { throw srb::Error(SRB_NOT_IMPLEMENTED, "this operator does not take runtime filters"); }
 };
 
@@ -331,8 +331,9 @@ struct srb_runtime_filter {
     int key_type = 0, key_width = 0;
     int64_t min = INT64_MAX, max = INT64_MIN, inserted = 0;
     bool has_null = false;
+    int mix = 0; // RfView::mix
     srb::RfView view() const {
-        return srb::RfView{(uint32_t*)dir.p, directory_mask, log_num_buckets, min, max, has_null ? 1 : 0, 0};
+        return srb::RfView{(uint32_t*)dir.p, directory_mask, log_num_buckets, min, max, has_null ? 1 : 0, mix};
     }
     size_t dir_bytes() const { return (size_t)32 << log_num_buckets; }
 };

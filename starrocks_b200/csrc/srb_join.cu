@@ -446,7 +446,7 @@ __global__ void __launch_bounds__(256) k_rf_build(const uint8_t* __restrict__ ke
         else if constexpr (W == 2) x = ((const int16_t*)keys)[r];
         else if constexpr (W == 4) x = ((const int32_t*)keys)[r];
         else x = ((const long long*)keys)[r];
-        const uint64_t hash = (uint64_t)x; // std::hash of an integer = its sign-extended value; phmap_mix<8> is the identity here
+        const uint64_t hash = rf_hash(x, v.mix); // std::hash of an integer = its sign-extended value, then phmap_mix<8> (identity by default)
         uint32_t* b = v.dir + (size_t)((uint32_t)hash & v.directory_mask) * 8;
         const uint32_t key = (uint32_t)(hash >> v.log_num_buckets);
 #pragma unroll
@@ -709,7 +709,7 @@ public:
 
     // partial runtime filter over build key column `key_index`; expected_rows sizes the directory (0: this op's build rows) so that
     // the partial filters of several ranks can be merged (SimdBlockFilter::merge needs equal sizes)
-    srb_runtime_filter* build_runtime_filter(int key_index, int64_t expected_rows) override {
+    srb_runtime_filter* build_runtime_filter(int key_index, int64_t expected_rows, int mix) override {
         if (!build_done_) throw Error(SRB_INTERNAL_ERROR, "runtime filter requested before the build side finished");
         if (key_index < 0 || key_index >= (int)bkeys_.size()) throw Error(SRB_INVALID_ARGUMENT, "bad build key index");
         const GrowCol& kc = bcols_[key_index];
@@ -719,6 +719,7 @@ public:
         rf->ctx = ctx;
         rf->key_type = kc.type;
         rf->key_width = kc.width;
+        rf->mix = mix ? 1 : 0;
         rf->log_num_buckets = rf_log_num_buckets((uint64_t)(expected_rows > 0 ? expected_rows : build_rows_));
         rf->directory_mask = (uint32_t)(((uint64_t)1 << rf->log_num_buckets) - 1);
         rf->dir.ensure(ctx, rf->dir_bytes());

@@ -535,7 +535,7 @@ __global__ void __launch_bounds__(256) k_filter_rf(const __grid_constant__ RfArg
             if (test[u] && (x[u] < a.v.min || x[u] > a.v.max)) on[u] = test[u] = false;
             b0[u] = b1[u] = make_uint4(0, 0, 0, 0);
             if (test[u]) {
-                const size_t bucket = (uint32_t)(uint64_t)x[u] & a.v.directory_mask;
+                const size_t bucket = (uint32_t)rf_hash(x[u], a.v.mix) & a.v.directory_mask;
                 b0[u] = __ldg(dir + bucket * 2);
                 b1[u] = __ldg(dir + bucket * 2 + 1);
             }
@@ -543,7 +543,7 @@ __global__ void __launch_bounds__(256) k_filter_rf(const __grid_constant__ RfArg
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             if (test[u]) {
-                const uint32_t key = (uint32_t)((uint64_t)x[u] >> a.v.log_num_buckets);
+                const uint32_t key = (uint32_t)(rf_hash(x[u], a.v.mix) >> a.v.log_num_buckets);
                 const uint32_t miss = (~b0[u].x & rf_word_mask(key, 0)) | (~b0[u].y & rf_word_mask(key, 1)) | (~b0[u].z & rf_word_mask(key, 2)) |
                                       (~b0[u].w & rf_word_mask(key, 3)) | (~b1[u].x & rf_word_mask(key, 4)) | (~b1[u].y & rf_word_mask(key, 5)) |
                                       (~b1[u].z & rf_word_mask(key, 6)) | (~b1[u].w & rf_word_mask(key, 7));
@@ -939,7 +939,7 @@ private:
                     L_.prog.n_cols = r.col + 1;
                 }
                 const int t = L_.cols[r.col].type;
-                if (is_binary(t) || t == SRB_TYPE_DOUBLE || type_width(t) > 8 || type_width(t) != r.rf->key_width)
+                if (is_binary(t) || t == SRB_TYPE_DOUBLE || type_width(t) > 8 || (r.rf->key_width && type_width(t) != r.rf->key_width))
                     throw Error(SRB_INVALID_ARGUMENT, fmt("runtime filter on slot %d: column type does not match the build key", r.slot));
             }
             for (int s : plan_.out_slots)

@@ -97,6 +97,30 @@ struct ShapeHighCard {
     static constexpr SKey key(int) { return SKey{0, 8}; }
 };
 
+// TPC-H Q3's aggregation over the join output (typed plan: fe/fe-core/src/test/resources/sql/external/hive/tpch/q3.sql:34-36):
+//   group by l_orderkey, o_orderdate, o_shippriority (INT, DATE, INT: a 12-byte packed key); sum(l_extendedprice * (1 - l_discount))
+// ~14 M groups at SF100: every row probes the HBM table (GMAX = 0), like the high-cardinality shape, but the expression and the
+// three-column key are compiled in and the five columns arrive through the TMA ring.
+struct ShapeQ3Agg {
+    static constexpr const char* name = "q3 (3 int keys, sum(d64 * (1 - d64)))";
+    static constexpr int N_NODES = 10, N_AGGS = 1, N_KEYS = 3, GMAX = 0, THREADS = 992, ROWS = 2;
+    static constexpr SNode node(int i) {
+        constexpr SNode t[N_NODES] = {{DOP_LOAD, 4, -1, -1, 0, 0, 0},   // 0 l_orderkey
+                                      {DOP_LOAD, 4, -1, -1, 0, 0, 0},   // 1 o_orderdate
+                                      {DOP_LOAD, 4, -1, -1, 0, 0, 0},   // 2 o_shippriority
+                                      {DOP_LOAD, 8, -1, -1, 0, 0, 0},   // 3 l_extendedprice
+                                      {DOP_LOAD, 8, -1, -1, 0, 0, 0},   // 4 l_discount
+                                      {DOP_LIT, 8, -1, -1, 0, 0, 0},    // 5 literal 1 as DECIMAL64(16,2)
+                                      {DOP_SUB, 8, 5, 4, 1, 0, 0},      // 6 1 - l_discount
+                                      {DOP_CAST, 16, 3, -1, 1, 0, 0},   // 7
+                                      {DOP_CAST, 16, 6, -1, 1, 0, 0},   // 8
+                                      {DOP_MULFAST, 16, 3, 6, 0, 0, 0}}; // 9 ext * (1 - disc)   DECIMAL128(31,4)
+        return t[i];
+    }
+    static constexpr SAgg agg(int) { return SAgg{FN_SUM, 9, 1, 1}; }
+    static constexpr SKey key(int i) { return SKey{i, 4}; }
+};
+
 // ---- matching a lowered program against a shape ---------------------------------------------------------------------
 template <class S>
 inline bool shape_matches(const DProg& p) {
@@ -1290,6 +1314,7 @@ inline int match_static_shape(const DProg& p) {
     if (shape_matches<ShapeSumMulFast>(p)) return 0;
     if (shape_matches<ShapeQ1Dict>(p)) return 1;
     if (shape_matches<ShapeHighCard>(p)) return 2;
+    if (shape_matches<ShapeQ3Agg>(p)) return 3;
     return -1;
 }
 inline const char* static_shape_name(int id) {
@@ -1297,6 +1322,7 @@ inline const char* static_shape_name(int id) {
     case 0: return ShapeSumMulFast::name;
     case 1: return ShapeQ1Dict::name;
     case 2: return ShapeHighCard::name;
+    case 3: return ShapeQ3Agg::name;
     }
     return "generic";
 }
@@ -1434,6 +1460,7 @@ inline int64_t launch_static_shape(int shape, const DProg& p, const TableView& t
     case 0: return launch_shape<ShapeSumMulFast>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
     case 1: return launch_shape<ShapeQ1Dict>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
     case 2: return launch_shape<ShapeHighCard>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
+    case 3: return launch_shape<ShapeQ3Agg>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
     }
     return 0;
 }

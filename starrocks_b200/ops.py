@@ -29,7 +29,8 @@ EXPORTS = [
     "srb_join_probe_pull_all", "srb_join_probe_pull_device",
     "srb_device_alloc", "srb_device_free", "srb_pinned_alloc", "srb_pinned_free", "srb_memcpy_h2d", "srb_memcpy_d2h",
     "srb_partition_create", "srb_partition_run", "srb_partition_destroy",
-    "srb_comm_unique_id", "srb_comm_create", "srb_comm_destroy", "srb_comm_stream", "srb_comm_all_to_all", "srb_comm_all_gather", "srb_comm_shuffle", "srb_comm_counters",
+    "srb_comm_unique_id", "srb_comm_create", "srb_comm_destroy", "srb_comm_stream", "srb_comm_all_to_all", "srb_comm_all_gather", "srb_comm_shuffle", "srb_comm_counters", "srb_comm_merge_runtime_filter",
+    "srb_join_build_runtime_filter", "srb_op_add_runtime_filter", "srb_runtime_filter_info", "srb_runtime_filter_directory", "srb_runtime_filter_destroy",
 ]
 
 
@@ -92,6 +93,13 @@ def lib() -> C.CDLL:
     L.srb_comm_all_gather.argtypes = [vp, C.POINTER(K.srb_chunk), C.POINTER(K.srb_chunk)]
     L.srb_comm_shuffle.argtypes = [vp, C.POINTER(K.srb_chunk), C.c_int32, C.POINTER(C.c_int32), C.POINTER(K.srb_chunk), C.POINTER(i64)]
     L.srb_comm_counters.argtypes = [vp, C.POINTER(i64)]
+    L.srb_comm_merge_runtime_filter.argtypes = [vp, vp]
+    L.srb_join_build_runtime_filter.argtypes = [vp, C.c_int32, i64, C.c_int32, C.POINTER(vp)]
+    L.srb_op_add_runtime_filter.argtypes = [vp, vp, C.c_int32]
+    L.srb_runtime_filter_info.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), C.POINTER(C.c_int32), C.POINTER(i64)]
+    L.srb_runtime_filter_directory.argtypes = [vp, vp, i64]
+    L.srb_runtime_filter_destroy.argtypes = [vp]
+    L.srb_runtime_filter_destroy.restype = None
     _lib = L
     return L
 
@@ -246,6 +254,11 @@ class ScanAggOperator(_Operator):
     def set_cancelled(self):
         _check(self.L.srb_op_cancel(self.h))
 
+    def add_runtime_filter(self, rf: "RuntimeFilter", slot_id: int):
+        """scan-filter plans only, before the first push_chunk (Operator::eval_runtime_bloom_filters)"""
+        _check(self.L.srb_op_add_runtime_filter(self.h, rf.h, slot_id))
+        self._rfs = getattr(self, "_rfs", []) + [rf]
+
     def sync(self):
         _check(self.L.srb_op_sync(self.h))
 
@@ -265,6 +278,31 @@ class ScanAggOperator(_Operator):
     def close(self):
         if self.h:
             self.L.srb_op_close(self.h)
+            self.h = None
+
+
+class RuntimeFilter:
+    """A join's runtime filter (bloom directory on the device + min / max / has_null), see srb_join_build_runtime_filter."""
+
+    def __init__(self, ctx: Context, handle):
+        self.ctx, self.L, self.h = ctx, ctx.L, handle
+
+    def info(self):
+        nb, mn, mx, ins, hn = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64(), C.c_int32()
+        _check(self.L.srb_runtime_filter_info(self.h, C.byref(nb), C.byref(mn), C.byref(mx), C.byref(hn), C.byref(ins)))
+        return {"n_buckets": nb.value, "min": mn.value, "max": mx.value, "has_null": bool(hn.value), "inserted": ins.value}
+
+    def directory(self):
+        """the directory as a numpy array [n_buckets, 8] of uint32"""
+        import numpy as np
+        nb = self.info()["n_buckets"]
+        out = np.empty((nb, 8), dtype=np.uint32)
+        _check(self.L.srb_runtime_filter_directory(self.h, out.ctypes.data, out.nbytes))
+        return out
+
+    def close(self):
+        if self.h:
+            self.L.srb_runtime_filter_destroy(self.h)
             self.h = None
 
 
@@ -293,6 +331,13 @@ class HashJoinOperator(_Operator):
         a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
         _check(self.L.srb_op_counters(self.h, C.byref(a), C.byref(b), C.byref(c)))
         return {"rows_in": a.value, "rows_selected": b.value, "kernel_launches": c.value}
+
+    def build_runtime_filter(self, key_index: int = 0, expected_rows: int = 0, mix: bool = False) -> "RuntimeFilter":
+        """after set_finishing: the partial runtime filter over build key `key_index` (HashJoinBuildOperator -> RuntimeBloomFilter).
+        mix=False hashes as the reference tree builds (identity); mix=True applies phmap_mix<8> (ENABLE_PHMAP_MIX)"""
+        h = C.c_void_p()
+        _check(self.L.srb_join_build_runtime_filter(self.h, key_index, expected_rows, 1 if mix else 0, C.byref(h)))
+        return RuntimeFilter(self.ctx, h)
 
     def close(self):
         if self.h:
@@ -414,6 +459,11 @@ class Communicator:
         n = C.c_int64()
         _check(self.L.srb_comm_counters(self.h, C.byref(n)))
         return n.value
+
+    def merge_runtime_filter(self, rf: "RuntimeFilter") -> "RuntimeFilter":
+        """global runtime filter: the OR of every rank's partial filter, in place on every rank"""
+        _check(self.L.srb_comm_merge_runtime_filter(self.h, rf.h))
+        return rf
 
     def all_gather(self, chunk: K.Chunk) -> K.Chunk:
         """Every rank's rows on every rank, rank 0 first. Device chunks (fixed-width columns) stay on the device; host chunks

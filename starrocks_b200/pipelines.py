@@ -35,12 +35,16 @@ class TpchQ3:
     STAGES = ["customer filter (+ broadcast) + build J1", "orders filter", "probe J1 (+ shuffle) + build J2", "lineitem filter (+ shuffle)",
               "probe J2 + gather", "group by"]
 
-    def __init__(self, ctx, comm=None, part=None, fused: Optional[bool] = None):
+    def __init__(self, ctx, comm=None, part=None, fused: Optional[bool] = None, runtime_filter: Optional[bool] = None):
         """fused (default: unless SRB_NO_P2P is set): shuffle with Communicator.shuffle (peer-memory scatter) instead of
-        Partitioner.run + Communicator.all_to_all (NCCL send/recv)"""
+        Partitioner.run + Communicator.all_to_all (NCCL send/recv).
+        runtime_filter (default: unless SRB_NO_RF is set): the orders join publishes a runtime filter on its build keys and the
+        lineitem scan applies it to l_orderkey before compacting (and before the shuffle); at N > 1 the ranks' partial filters are
+        merged into the global one first (hash_join_build_operator.cpp:97-208, the FE's plan: q3.sql "build runtime filters")."""
         import os
         self.ctx, self.comm, self.part = ctx, comm, part
         self.fused = (not os.environ.get("SRB_NO_P2P")) if fused is None else fused
+        self.use_rf = (not os.environ.get("SRB_NO_RF")) if runtime_filter is None else runtime_filter
         self.open = []
 
     def _shuffle(self, chunk, key_slot):
@@ -83,9 +87,29 @@ class TpchQ3:
         if d1 is not None and d1.n_rows:
             j2.push_chunk(d1)
         j2.set_finishing()
+        rf = None
+        if self.use_rf:
+            n_build = d1.n_rows if d1 is not None else 0
+            if self.comm is not None:  # the partial filters are merged, so every rank sizes its own for the global build side
+                import numpy as np
+                mine = K.Chunk(1, {0: K.Column.from_ints(K.TYPE_BIGINT, np.array([n_build], dtype=np.int64))})
+                n_build = int(sum(r[0] for r in K.chunk_rows(self.comm.all_gather(mine), sort=False)))
+            # order keys use 8 of every 32 values: under the reference tree's identity hash three quarters of the buckets stay empty
+            # and most lines pass by accident, so the filter is built with the mixing hash (ops.HashJoinOperator.build_runtime_filter)
+            rf = j2.build_runtime_filter(0, max(1, n_build), mix=True)
+            if self.comm is not None:
+                self.comm.merge_runtime_filter(rf)
+            self.open.append(rf)
         mark()
-        fl, dl = _filter(self.ctx, Q.q3_lineitem_filter(), line)
-        self.open.append(fl)
+        fl = ops.ScanAggOperator(self.ctx, Q.q3_lineitem_filter())
+        self.open.insert(0, fl)  # closed before the filter it reads
+        if rf is not None:
+            fl.add_runtime_filter(rf, Q.L_ORDERKEY)
+        fl.push_chunk(line)
+        fl.set_finishing()
+        dl = fl.pull_device()
+        if dl is None:
+            raise ValueError("the lineitem scan kept no row on this rank")
         rows["lineitem_kept"] = dl.n_rows
         dl = self._shuffle(dl, Q.L_ORDERKEY)
         mark()
@@ -103,7 +127,7 @@ class TpchQ3:
         return agg
 
     def launches(self) -> int:
-        return sum(o.counters()["kernel_launches"] for o in self.open)
+        return sum(o.counters()["kernel_launches"] for o in self.open if hasattr(o, "counters"))
 
     def close(self):
         for o in self.open:

@@ -63,6 +63,17 @@ class Oracle:
         L.orc_xorshift32.argtypes = [C.c_uint32]
         L.orc_shuffle_channel.restype = C.c_uint32
         L.orc_shuffle_channel.argtypes = [C.c_char_p, C.c_int32, C.c_uint32]
+        L.orc_rf_create.restype = C.c_void_p
+        L.orc_rf_create.argtypes = [C.c_uint64, C.c_int]
+        L.orc_rf_free.argtypes = [C.c_void_p]
+        L.orc_rf_insert_hash.argtypes = [C.c_void_p, C.c_uint64]
+        L.orc_rf_test_hash.argtypes = [C.c_void_p, C.c_uint64]
+        L.orc_rf_insert_column.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p]
+        L.orc_rf_evaluate.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
+        L.orc_rf_test_data.argtypes = [C.c_void_p, C.c_int64]
+        L.orc_rf_info.restype = C.c_int64
+        L.orc_rf_info.argtypes = [C.c_void_p, C.c_int]
+        L.orc_rf_directory.argtypes = [C.c_void_p, C.c_void_p]
         if L.orc_has_hw_crc():
             L.orc_hw_crc32c_u64.restype = C.c_uint32
             L.orc_hw_crc32c_u64.argtypes = [C.c_uint32, C.c_uint64]
@@ -110,3 +121,41 @@ class Oracle:
         self.lib.orc_decimal_div_integer(lo, hi, count, scale, C.byref(rlo), C.byref(rhi))
         v = K.join128(rlo.value, rhi.value)
         return v - (1 << 128) if v >= 1 << 127 else v
+
+
+class OracleRuntimeFilter:
+    """oracle/orc_rf.h: SimdBlockFilter + min / max / has_null over integer keys (the CPU restatement the GPU filter is checked against)"""
+
+    def __init__(self, oracle: Oracle, nums: int, mix: bool = False):
+        self.L = oracle.lib
+        self.h = self.L.orc_rf_create(nums, 1 if mix else 0)
+
+    def insert_column(self, col: K.Column):
+        import numpy as np
+        data = np.ascontiguousarray(col.data)
+        nulls = None if col.nulls is None else np.ascontiguousarray(col.nulls)
+        self.L.orc_rf_insert_column(self.h, data.ctypes.data, data.dtype.itemsize, len(data), None if nulls is None else nulls.ctypes.data)
+        return self
+
+    def evaluate(self, col: K.Column, selection=None):
+        import numpy as np
+        data = np.ascontiguousarray(col.data)
+        nulls = None if col.nulls is None else np.ascontiguousarray(col.nulls)
+        sel = np.ones(len(data), np.uint8) if selection is None else np.ascontiguousarray(selection, dtype=np.uint8).copy()
+        self.L.orc_rf_evaluate(self.h, data.ctypes.data, data.dtype.itemsize, len(data), None if nulls is None else nulls.ctypes.data, sel.ctypes.data)
+        return sel
+
+    def info(self):
+        g = lambda w: self.L.orc_rf_info(self.h, w)
+        return {"n_buckets": g(0), "min": g(1), "max": g(2), "has_null": bool(g(3)), "inserted": g(4)}
+
+    def directory(self):
+        import numpy as np
+        out = np.empty((self.info()["n_buckets"], 8), dtype=np.uint32)
+        self.L.orc_rf_directory(self.h, out.ctypes.data)
+        return out
+
+    def close(self):
+        if self.h:
+            self.L.orc_rf_free(self.h)
+            self.h = None

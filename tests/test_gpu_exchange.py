@@ -286,7 +286,21 @@ def _join_worker(rank, world, port, sizes, out_q):
         ssb_rows = K.chunk_rows(op2.pull_all())
         op2.close()
         ssb.close()
-        out_q.put((rank, (q3_rows, ssb_rows)))
+        # global runtime filter: every rank builds a partial filter over its slice of the keys, sized for all of them; after the
+        # merge every rank holds the OR (SimdBlockFilter::merge) and the combined min / max / has_null
+        from starrocks_b200.plan import JoinPlan
+        all_keys = sizes["rf_keys"]
+        b, e = D.shard_range(len(all_keys), rank, world)
+        nulls = np.zeros(e - b, np.uint8)
+        nulls[0] = rank  # only rank 1 inserts a NULL
+        j = ops.HashJoinOperator(ctx, JoinPlan([0], [1]))
+        j.push_chunk(K.Chunk(e - b, {0: K.Column.from_ints(K.TYPE_INT, all_keys[b:e], nulls=nulls)}))
+        j.set_finishing()
+        rf = comm.merge_runtime_filter(j.build_runtime_filter(0, len(all_keys)))
+        rf_state = (rf.info(), rf.directory())
+        rf.close()
+        j.close()
+        out_q.put((rank, (q3_rows, ssb_rows, rf_state)))
         part.close()
         comm.close()
         dist.barrier()
@@ -302,7 +316,8 @@ def test_two_gpu_shuffle_join_and_broadcast_join(oracle):
     import torch.multiprocessing as mp
     from starrocks_b200 import pipelines as P
     world = 2
-    sizes = {"q3": (6000, 60000, 240000), "ssb": (300_000, 30_000, 2_000, 200_000)}
+    sizes = {"q3": (6000, 60000, 240000), "ssb": (300_000, 30_000, 2_000, 200_000),
+             "rf_keys": np.random.default_rng(3).integers(-(1 << 28), 1 << 28, 50_001).astype(np.int32)}
     mpc = mp.get_context("spawn")
     q = mpc.Queue()
     port = _free_port()
@@ -324,3 +339,12 @@ def test_two_gpu_shuffle_join_and_broadcast_join(oracle):
             (("ssb_customer", n_c), ("ssb_supplier", n_s), ("ssb_part", n_p), ("ssb_dates", T.SSB_DAYS))}
     want_ssb = K.chunk_rows(P.ssb_q41_oracle(oracle, dims, T.host_chunk("lineorder", 0, n_lo, T.LINEORDER_Q41, **kw)))
     assert res[0][1] == want_ssb and res[1][1] == want_ssb
+    from tests.oracle_lib import OracleRuntimeFilter
+    keys = sizes["rf_keys"]
+    nulls = np.zeros(len(keys), np.uint8)
+    nulls[D.shard_range(len(keys), 1, world)[0]] = 1
+    want_rf = OracleRuntimeFilter(oracle, len(keys)).insert_column(K.Column.from_ints(K.TYPE_INT, keys, nulls=nulls))
+    for r in range(world):
+        info, directory = res[r][2]
+        assert info == want_rf.info() and info["has_null"] and (directory == want_rf.directory()).all()
+    want_rf.close()

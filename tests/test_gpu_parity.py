@@ -717,3 +717,171 @@ def test_device_pull_of_aggregate_result(ctx, oracle):
     got = ctx.fetch_chunk(d)
     op.close()
     assert K.chunk_rows(got) == K.chunk_rows(oracle.scan_agg(Q.highcard_plan(), ch))
+
+
+# ---- runtime filters: build-side bloom filter + min/max, applied by the probe-side scan ---------------------------
+def _build_join(ctx, type_, keys, nulls=None):
+    from starrocks_b200 import ops
+    build = K.Chunk(len(keys), {0: K.Column.from_ints(type_, keys, nulls=nulls)})
+    j = ops.HashJoinOperator(ctx, JoinPlan([0], [1], build_out=[], probe_out=[1]))
+    j.push_chunk(build)
+    j.set_finishing()
+    return j, build
+
+
+@pytest.mark.parametrize("type_,np_t", [(K.TYPE_INT, np.int32), (K.TYPE_BIGINT, np.int64), (K.TYPE_DATE, np.int32), (K.TYPE_SMALLINT, np.int16)])
+def test_runtime_filter_directory_is_the_reference_filter(ctx, oracle, type_, np_t):
+    """the device-built SimdBlockFilter holds exactly the bits of the oracle's (= the reference's) filter of the same size, and
+    min / max / has_null / inserted agree — for several key types, negative keys, NULL keys and an oversized expected_rows"""
+    from tests.oracle_lib import OracleRuntimeFilter
+    rng = np.random.default_rng(11)
+    n = 40_000
+    lo, hi = (-(1 << 14), 1 << 14) if np_t == np.int16 else (-(1 << 30), 1 << 30)
+    keys = rng.integers(lo, hi, n).astype(np_t)
+    nulls = (rng.random(n) < 0.01).astype(np.uint8)
+    for use_nulls, expected, mix in ((False, 0, False), (True, 0, False), (True, 500_000, False), (True, 0, True)):
+        j, build = _build_join(ctx, type_, keys, nulls if use_nulls else None)
+        rf = j.build_runtime_filter(0, expected, mix=mix)
+        want = OracleRuntimeFilter(oracle, expected or n, mix=mix).insert_column(build.columns[0])
+        try:
+            assert rf.info() == want.info()
+            assert (rf.directory() == want.directory()).all()
+        finally:
+            want.close()
+            rf.close()
+            j.close()
+
+
+def test_runtime_filter_of_an_empty_build_side_rejects_everything(ctx, oracle):
+    from starrocks_b200 import ops
+    j, _ = _build_join(ctx, K.TYPE_INT, np.array([], dtype=np.int32))
+    rf = j.build_runtime_filter()
+    assert rf.info()["inserted"] == 0 and rf.info()["min"] > rf.info()["max"]
+    probe = K.Chunk(1000, {1: K.Column.from_ints(K.TYPE_INT, np.arange(1000, dtype=np.int32))})
+    op = ops.ScanAggOperator(ctx, Q.filter_plan([], [1]))
+    op.add_runtime_filter(rf, 1)
+    op.push_chunk(probe)
+    op.set_finishing()
+    assert op.pull_all().n_rows == 0
+    op.close()
+    rf.close()
+    j.close()
+
+
+@pytest.mark.parametrize("pred_kind", ["range", "generic", "none"])
+@pytest.mark.parametrize("nullable,mix", [(False, False), (True, False), (True, True)])
+def test_scan_filter_with_runtime_filter_matches_the_oracle(ctx, oracle, pred_kind, nullable, mix):
+    """scan predicates AND the runtime filter on the key column, order-preserving compaction: the kept rows are exactly those the
+    oracle's predicate + RuntimeBloomFilter::evaluate keep (false positives included), on the vectorised and the generic mask path,
+    with NULL keys following has_null"""
+    from starrocks_b200 import ops
+    from tests.oracle_lib import OracleRuntimeFilter
+    rng = np.random.default_rng(5)
+    n_build, n = 20_000, 300_000
+    bkeys = rng.integers(0, 1 << 20, n_build).astype(np.int32)
+    for build_has_null in ((False, True) if nullable else (False,)):
+        bnulls = None
+        if build_has_null:
+            bnulls = np.zeros(n_build, np.uint8)
+            bnulls[7] = 1
+        j, build = _build_join(ctx, K.TYPE_INT, bkeys, bnulls)
+        rf = j.build_runtime_filter(mix=mix)
+        want_rf = OracleRuntimeFilter(oracle, n_build, mix=mix).insert_column(build.columns[0])
+        pk = rng.integers(-1000, (1 << 20) + 1000, n).astype(np.int32)
+        pnull = (rng.random(n) < 0.05).astype(np.uint8) if nullable else None
+        probe = K.Chunk(n, {1: K.Column.from_ints(K.TYPE_INT, pk, nulls=pnull),
+                            2: K.Column.from_ints(K.TYPE_BIGINT, rng.integers(0, 1000, n).astype(np.int64)),
+                            3: K.Column.from_ints(K.TYPE_TINYINT, rng.integers(0, 5, n).astype(np.int8))})
+        preds = {"range": [pred(2, K.PRED_LT, K.TYPE_BIGINT, 700), pred(2, K.PRED_GE, K.TYPE_BIGINT, 100)],
+                 "generic": [pred(3, K.PRED_NE, K.TYPE_TINYINT, 2)], "none": []}[pred_kind]
+        plan = Q.filter_plan(preds, [1, 2])
+        # oracle: predicate selection, then the filter's evaluate on the key column
+        v2, v3 = probe.columns[2].data, probe.columns[3].data
+        sel = {"range": (v2 < 700) & (v2 >= 100), "generic": v3 != 2, "none": np.ones(n, bool)}[pred_kind].astype(np.uint8)
+        # the filter is evaluated on its own all-ones selection (RunningContext::selection) and merged with the predicates' afterwards
+        keep = (want_rf.evaluate(probe.columns[1]) & sel).astype(bool)
+        assert 0 < keep.sum() < sel.sum()
+        want = [r for r, k in zip(K.chunk_rows(K.Chunk(n, {1: probe.columns[1], 2: probe.columns[2]}), sort=False), keep) if k]
+        for device in (False, True):
+            op = ops.ScanAggOperator(ctx, plan)
+            op.add_runtime_filter(rf, 1)
+            ptrs = []
+            src = probe
+            if device:
+                src, ptrs = ctx.device_chunk(probe)
+            op.push_chunk(src)
+            op.set_finishing()
+            got = K.chunk_rows(op.pull_all(), sort=False)
+            op.close()
+            for p in ptrs:
+                ctx.device_free(p)
+            assert got == want  # same rows, same order
+        want_rf.close()
+        rf.close()
+        j.close()
+
+
+def test_runtime_filter_misuse_is_reported(ctx):
+    from starrocks_b200 import ops
+    j, _ = _build_join(ctx, K.TYPE_INT, np.arange(10, dtype=np.int32))
+    rf = j.build_runtime_filter()
+    agg = ops.ScanAggOperator(ctx, Q.highcard_plan())
+    with pytest.raises(ops.SrbError):
+        agg.add_runtime_filter(rf, Q.HC_K)  # only scan-filter plans take runtime filters
+    agg.close()
+    f = ops.ScanAggOperator(ctx, Q.filter_plan([], [1]))
+    f.add_runtime_filter(rf, 1)
+    with pytest.raises(ops.SrbError):  # BIGINT column against a filter over INT keys
+        f.push_chunk(K.Chunk(3, {1: K.Column.from_ints(K.TYPE_BIGINT, [1, 2, 3])}))
+    f.close()
+    j2 = ops.HashJoinOperator(ctx, JoinPlan([0], [1]))
+    with pytest.raises(ops.SrbError):
+        j2.build_runtime_filter()  # build side not finished
+    j2.close()
+    rf.close()
+    j.close()
+
+
+@pytest.mark.parametrize("use_rf", [True, False])
+def test_q3_pipeline_with_and_without_runtime_filter(ctx, oracle, use_rf):
+    from starrocks_b200 import pipelines as P
+    n_c, n_o, n_l = 6000, 60000, 240000
+    cust = T.host_chunk("customer", 0, n_c, ["c_custkey", "c_mktsegment_code"])
+    orders = T.host_chunk("orders", 0, n_o, ["o_orderkey", "o_custkey", "o_orderdate", "o_shippriority"], n_customers=n_c)
+    line = T.host_chunk("lineitem", 0, n_l, ["l_orderkey", "l_extendedprice", "l_discount", "l_shipdate"])
+    want = K.chunk_rows(P.q3_oracle(oracle, cust, orders, line))
+    q = P.TpchQ3(ctx, runtime_filter=use_rf)
+    rows = {}
+    try:
+        got = K.chunk_rows(q.run(cust, orders, line, rows=rows).pull_all())
+    finally:
+        q.close()
+    assert got == want
+    plain = int((line.columns[Q.L_SHIPDATE].data > Q.Q3_DATE).sum())
+    assert (rows["lineitem_kept"] < plain // 2) if use_rf else (rows["lineitem_kept"] == plain)  # the filter drops most non-matching lines
+
+
+@pytest.mark.parametrize("n", [3000, 400_000])
+def test_q3_aggregation_static_shape(ctx, oracle, n):
+    """Q3's GROUP BY over the join output (3 INT/DATE keys, sum(ext * (1 - disc))): the statically specialised kernel, the same with
+    the general body, and the generic interpreter all give the oracle's rows — including negative keys and amounts, and a
+    discount above one; and the plan really takes the static shape"""
+    from starrocks_b200 import ops
+    rng = np.random.default_rng(n)
+    okey = np.sort(rng.integers(-50, n // 2, n)).astype(np.int32)
+    ch = K.Chunk(n, {Q.L_ORDERKEY: K.Column.from_ints(K.TYPE_INT, okey),
+                     Q.O_ORDERDATE: K.Column.from_ints(K.TYPE_DATE, (okey % 2000 + 2448000).astype(np.int32)),
+                     Q.O_SHIPPRIORITY: K.Column.from_ints(K.TYPE_INT, (okey % 3 - 1).astype(np.int32)),
+                     Q.L_EXTENDEDPRICE: K.Column.from_ints(K.TYPE_DECIMAL64, rng.integers(-10**7, 10**9, n).astype(np.int64), precision=15, scale=2),
+                     Q.L_DISCOUNT: K.Column.from_ints(K.TYPE_DECIMAL64, rng.integers(0, 120, n).astype(np.int64), precision=15, scale=2)})
+    _both_kernel_families(ctx, oracle, Q.q3_agg_plan, ch)
+    dch, ptrs = ctx.device_chunk(ch)
+    op = ops.ScanAggOperator(ctx, Q.q3_agg_plan(group_hint=n))
+    op.push_chunk(dch)
+    op.set_finishing()
+    op.pull_device()
+    prof = op.profile()
+    op.close()
+    for p in ptrs:
+        ctx.device_free(p)
+    assert prof["shape"] == 3 and (prof["static_launches"] >= 1 or n < 4096)

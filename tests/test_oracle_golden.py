@@ -282,3 +282,105 @@ def test_fixed_size_key_packing(oracle):
     # and a join on the packed BIGINT finds exactly those rows
     plan = JoinPlan([9], [4], build_out=[0, 1], probe_out=[4])
     assert K.chunk_rows(oracle.join(plan, build, probe)) == [(8589934592, 0, 2), (12884901889, 1, 3)]
+
+
+# ---- runtime filter (oracle/orc_rf.h) pinned by be/test/exprs/runtime_filter_test.cpp ----------------------------------------
+def test_simd_block_filter_known_answers(oracle):
+    # TestSimdBlockFilter :255-265: init(100), insert_hash(1, 18, ..., 188); every inserted hash tests true, every hash + 1 false
+    L = oracle.lib
+    f = L.orc_rf_create(100, 0)
+    try:
+        assert L.orc_rf_info(f, 0) == 4  # init(100): ceil(log2(100)) = 7 -> 2^(7-5) buckets of 32 bytes (runtime_filter.cpp:26-35)
+        for i in range(1, 201, 17):
+            L.orc_rf_insert_hash(f, i)
+        for i in range(1, 201, 17):
+            assert L.orc_rf_test_hash(f, i) == 1
+            assert L.orc_rf_test_hash(f, i + 1) == 0
+    finally:
+        L.orc_rf_free(f)
+
+
+def test_join_runtime_filter_known_answers(oracle):
+    # TestJoinRuntimeFilter :342-380 (Int32RF): insert 0, 17, ..., 187 -> min 0, max 187; test_data(i) true, test_data(i + 1) false;
+    # evaluating the column 0..200 keeps exactly the 12 inserted values; has_null only after insert_null
+    from tests.oracle_lib import OracleRuntimeFilter
+    rf = OracleRuntimeFilter(oracle, 100)
+    try:
+        vals = np.arange(0, 201, 17, dtype=np.int32)
+        rf.insert_column(K.Column.from_ints(K.TYPE_INT, vals))
+        info = rf.info()
+        assert (info["min"], info["max"], info["has_null"], info["inserted"]) == (0, 187, False, 12)
+        for i in vals:
+            assert oracle.lib.orc_rf_test_data(rf.h, int(i)) == 1
+            assert oracle.lib.orc_rf_test_data(rf.h, int(i) + 1) == 0
+        sel = rf.evaluate(K.Column.from_ints(K.TYPE_INT, np.arange(0, 201, dtype=np.int32)))
+        assert sel.sum() == 12 and list(np.nonzero(sel)[0]) == list(vals)
+        # NULL probe rows follow has_null (runtime_filter.h:1396-1401)
+        col = K.Column.from_ints(K.TYPE_INT, [17, 17, 18], nulls=[0, 1, 1])
+        assert list(rf.evaluate(col)) == [1, 0, 0]
+        rf.insert_column(K.Column.from_ints(K.TYPE_INT, [0], nulls=[1]))
+        assert rf.info()["has_null"] and list(rf.evaluate(col)) == [1, 1, 1]
+    finally:
+        rf.close()
+
+
+def test_runtime_filter_sizes_and_negative_keys(oracle):
+    # SimdBlockFilter::init: log_num_buckets = max(1, ceil(log2(nums)) - 5); the hash of an integer is its sign-extended value
+    L = oracle.lib
+    for nums, buckets in ((0, 2), (1, 2), (64, 2), (65, 4), (1 << 20, 1 << 15), ((1 << 20) + 1, 1 << 16)):
+        f = L.orc_rf_create(nums, 0)
+        assert L.orc_rf_info(f, 0) == buckets
+        L.orc_rf_free(f)
+    from tests.oracle_lib import OracleRuntimeFilter
+    rf = OracleRuntimeFilter(oracle, 1000)
+    try:
+        rf.insert_column(K.Column.from_ints(K.TYPE_BIGINT, [-5, 7, -(1 << 40)]))
+        assert (rf.info()["min"], rf.info()["max"]) == (-(1 << 40), 7)
+        assert list(rf.evaluate(K.Column.from_ints(K.TYPE_BIGINT, [-5, 7, -(1 << 40), 8, -(1 << 41)]))) == [1, 1, 1, 0, 0]
+        # the same key inserted through a narrower column sets the same bits (sign extension)
+        rf2 = OracleRuntimeFilter(oracle, 1000)
+        rf2.insert_column(K.Column.from_ints(K.TYPE_INT, [-5, 7]))
+        rf3 = OracleRuntimeFilter(oracle, 1000)
+        rf3.insert_column(K.Column.from_ints(K.TYPE_BIGINT, [-5, 7]))
+        assert (rf2.directory() == rf3.directory()).all()
+        rf2.close()
+        rf3.close()
+    finally:
+        rf.close()
+
+
+def test_runtime_filter_with_the_mixing_hash(oracle):
+    # the same source with ENABLE_PHMAP_MIX (phmap_utils.h:85-95): hash = hi + lo of key * 0xde5fb9d2630458e9 (= phase-1 phmap_mix8)
+    from tests.oracle_lib import OracleRuntimeFilter
+    rf = OracleRuntimeFilter(oracle, 100, mix=True)
+    plain = OracleRuntimeFilter(oracle, 100)
+    try:
+        vals = np.arange(0, 201, 17, dtype=np.int32)
+        col = K.Column.from_ints(K.TYPE_INT, vals)
+        rf.insert_column(col)
+        plain.insert_column(col)
+        assert rf.evaluate(col).all() and (rf.directory() != plain.directory()).any()
+        # equal to inserting the mixed hashes directly
+        f = oracle.lib.orc_rf_create(100, 0)
+        for v in vals:
+            oracle.lib.orc_rf_insert_hash(f, oracle.lib.orc_phmap_mix8(int(v), 1))
+        d = np.empty((4, 8), np.uint32)
+        oracle.lib.orc_rf_directory(f, d.ctypes.data)
+        oracle.lib.orc_rf_free(f)
+        assert (d == rf.directory()).all()
+        # sparse keys (8 of every 32, like TPC-H order keys): the identity hash leaves 3/4 of the buckets empty, the mix does not
+        all_idx = np.random.default_rng(1).permutation(400_000)
+        idx, other = np.sort(all_idx[:200_000]), np.sort(all_idx[200_000:300_000])  # inserted keys / keys of the same domain that are not
+        keys = K.Column.from_ints(K.TYPE_INT, ((idx // 8) * 32 + idx % 8 + 1).astype(np.int32))
+        a, b = OracleRuntimeFilter(oracle, 200_000), OracleRuntimeFilter(oracle, 200_000, mix=True)
+        a.insert_column(keys)
+        b.insert_column(keys)
+        used = lambda f: int((f.directory().any(axis=1)).sum())
+        assert used(a) * 3 < used(b)
+        probe = K.Column.from_ints(K.TYPE_INT, ((other // 8) * 32 + other % 8 + 1).astype(np.int32))
+        assert b.evaluate(probe).mean() < 0.05 < a.evaluate(probe).mean()
+        a.close()
+        b.close()
+    finally:
+        rf.close()
+        plain.close()
