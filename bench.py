@@ -296,7 +296,7 @@ def run_join_query(args):
         stage_rows = []
         agg = q.probe(tb["lineorder"], phase=K.AGG_UPDATE_SERIALIZE if comm is not None else K.AGG_UPDATE_FINALIZE, stage_rows=stage_rows)
         out = agg.pull_all()
-        launches = sum(o.counters()["kernel_launches"] for o in q.joins + q.keep + [agg])
+        launches = sum(o.counters()["kernel_launches"] for o in q.joins + q.keep + [agg]) + getattr(q, "scan_launches", 0)
         if comm is not None:  # <= 35 intermediate rows per rank: gathered and merged on every rank
             op2 = ops.ScanAggOperator(ctx, Q.ssb_q41_merge_plan())
             op2.push_chunk(comm.all_gather(out))
@@ -306,7 +306,8 @@ def run_join_query(args):
             op2.close()
         mark()
         if rows_out is not None:
-            rows_out.update(zip(["after supplier", "after customer", "after part", "after dates"], stage_rows))
+            rows_out.update(zip((["after the scan's runtime filters"] if len(stage_rows) == 5 else []) + ["after supplier", "after customer", "after part", "after dates"],
+                                stage_rows))
         agg.close()
         q.close()
         return out.n_rows, launches

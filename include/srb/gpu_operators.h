@@ -137,11 +137,15 @@ public:
         const srb_scan_agg_plan p = _plan.c_plan();
         return srb_to_status(srb_scan_agg_create(_ctx, &p, &_op));
     }
-    bool need_input() const override { return _op && srb_op_need_input(_op); }
+    // the scan waits for the joins whose runtime filters it applies (Operator::set_precondition_ready, operator.h:185): no input is
+    // taken before every such build side has finished; the filters are attached right before the first chunk
+    void wait_for_runtime_filter(std::shared_ptr<class GpuHashJoiner> joiner, int32_t slot_id);
+    bool need_input() const override { return _op && runtime_filters_ready() && srb_op_need_input(_op); }
     bool has_output() const override { return _op && srb_op_has_output(_op); }
     bool is_finished() const override { return !_op || srb_op_is_finished(_op); }
     Status push_chunk(RuntimeState* state, const ChunkPtr& chunk) override {
         if (state && state->is_cancelled()) return Status::Cancelled("query cancelled"); // aggregate_blocking_sink_operator.cpp:63
+        SRB_RETURN_IF_ERROR(attach_runtime_filters());
         SrbChunkView v;
         to_srb(*chunk, &v);
         return srb_to_status(srb_op_push_chunk(_op, &v.chunk)); // host columns are staged into HBM before this returns control of them
@@ -166,9 +170,13 @@ public:
     }
 
 private:
+    bool runtime_filters_ready() const;
+    Status attach_runtime_filters();
     srb_ctx* _ctx;
     ScanAggPlan _plan;
     srb_op* _op = nullptr;
+    std::vector<std::pair<std::shared_ptr<class GpuHashJoiner>, int32_t>> _rf_sources;
+    bool _rf_attached = false;
 };
 
 // ---- hash join: the build and probe operators share one joiner, like HashJoiner (exec/hash_joiner.h:169) -------------------------
@@ -195,6 +203,7 @@ public:
     GpuHashJoiner(srb_ctx* ctx, JoinPlan plan) : _ctx(ctx), _plan(std::move(plan)) {}
     ~GpuHashJoiner() {
         if (_op) srb_op_close(_op);
+        if (_rf) srb_runtime_filter_destroy(_rf);
     }
     Status prepare() {
         if (_op) return Status::OK();
@@ -204,12 +213,36 @@ public:
     srb_op* op() const { return _op; }
     bool build_done = false; // HashJoinPhase::BUILD -> PROBE (hash_joiner.h:60-65)
 
+    // HashJoiner::create_runtime_filters (hash_joiner.cpp:516-611): called by the build operator's set_finishing when the plan
+    // asks for a runtime filter on build key `runtime_filter_key` (-1: none). The probe-side scan picks it up with runtime_filter().
+    int runtime_filter_key = -1;
+    Status create_runtime_filter() {
+        if (runtime_filter_key < 0 || _rf) return Status::OK();
+        return srb_to_status(srb_join_build_runtime_filter(_op, runtime_filter_key, 0, /*hash_mix=*/0, &_rf));
+    }
+    const srb_runtime_filter* runtime_filter() const { return _rf; }
+
 private:
     srb_ctx* _ctx;
     JoinPlan _plan;
     srb_op* _op = nullptr;
+    srb_runtime_filter* _rf = nullptr;
 };
 using GpuHashJoinerPtr = std::shared_ptr<GpuHashJoiner>;
+
+inline void GpuScanAggregateOperator::wait_for_runtime_filter(GpuHashJoinerPtr joiner, int32_t slot_id) { _rf_sources.emplace_back(std::move(joiner), slot_id); }
+inline bool GpuScanAggregateOperator::runtime_filters_ready() const {
+    for (auto& s : _rf_sources)
+        if (!s.first->build_done) return false;
+    return true;
+}
+inline Status GpuScanAggregateOperator::attach_runtime_filters() {
+    if (_rf_attached) return Status::OK();
+    _rf_attached = true;
+    for (auto& s : _rf_sources)
+        if (s.first->runtime_filter()) SRB_RETURN_IF_ERROR(srb_to_status(srb_op_add_runtime_filter(_op, s.first->runtime_filter(), s.second)));
+    return Status::OK();
+}
 
 class GpuHashJoinBuildOperator final : public Operator { // hashjoin/hash_join_build_operator.cpp:40-213 (a sink)
 public:
@@ -226,6 +259,7 @@ public:
     Status set_finishing(RuntimeState*) override {
         if (_j->build_done) return Status::OK();
         SRB_RETURN_IF_ERROR(srb_to_status(srb_op_set_finishing(_j->op()))); // JoinHashTable::build (join_hash_map.cpp:529)
+        SRB_RETURN_IF_ERROR(_j->create_runtime_filter());                     // hash_join_build_operator.cpp:97-208
         _j->build_done = true;
         return Status::OK();
     }

@@ -16,6 +16,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <type_traits>
 
 #include "srb_host.h"
 #include "srb_lower.h"
@@ -496,64 +497,83 @@ __global__ void __launch_bounds__(256) k_filter_mask_ranges(const __grid_constan
 // bucket of its hash has all eight bits set; NULL keys keep it iff the build side inserted a NULL. Four rows per thread and step:
 // the key loads of the four rows are issued together, then their 32-byte bucket loads (the directory of a build side of a few
 // 10^7 keys is tens of MB: L2-resident), then the ballots rewrite the mask words and the tile's count.
+// one 256-bit load (sm_100: LDG.E.256) fetches a whole bucket = one 32-byte sector, one L2 request per test
+struct alignas(32) RfBucket {
+    uint32_t w[8];
+};
+SRB_D RfBucket ld_bucket(const uint32_t* p) {
+    RfBucket r;
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]), "=r"(r.w[7])
+                 : "l"(p));
+    return r;
+}
 struct RfArgs {
     RfView v;
     const uint8_t* data; // key column, already offset to the first row of the range
     const uint8_t* nulls;
 };
 template <int W>
-__global__ void __launch_bounds__(256) k_filter_rf(const __grid_constant__ RfArgs a, int64_t n, uint32_t* __restrict__ mask,
+__global__ void __launch_bounds__(256, 4) k_filter_rf(const __grid_constant__ RfArgs a, int64_t n, uint32_t* __restrict__ mask,
                                                     uint32_t* __restrict__ tile_counts) {
+    // The chain per row is mask word -> key -> bucket. To keep it short the tile's 256 mask words are fetched once (one coalesced
+    // load into shared memory) and the keys of eight rows per thread are loaded unconditionally and together (their sectors are read
+    // anyway unless the selection is already very sparse); the dependent bucket loads then go four at a time.
+    using KT = typename std::conditional<W == 8, long long, typename std::conditional<W == 4, int, typename std::conditional<W == 2, short, signed char>::type>::type>::type;
+    __shared__ uint32_t smask[FTILE / 32];
     __shared__ uint32_t wcount[8];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t tile0 = (int64_t)blockIdx.x * FTILE;
-    const uint4* dir = (const uint4*)a.v.dir;
+    const int64_t w0 = tile0 >> 5, n_words = (n + 31) >> 5;
+    smask[threadIdx.x] = w0 + threadIdx.x < n_words ? mask[w0 + threadIdx.x] : 0u; // bits past n were never set
+    __syncthreads();
+    const uint32_t* dir = a.v.dir;
+    const KT* keys = (const KT*)a.data;
     uint32_t mine = 0;
 #pragma unroll 1
-    for (int it = 0; it < FTILE / 256; it += 4) {
-        bool on[4], test[4];
-        long long x[4];
+    for (int it = 0; it < FTILE / 256; it += 8) {
+        KT x[8];
+        uint8_t isnull[8];
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const int64_t i = tile0 + (int64_t)(it + u) * 256 + threadIdx.x; // bit `lane` of mask word i >> 5
-            on[u] = i < n && ((mask[i >> 5] >> lane) & 1u);
-            test[u] = on[u];
-            x[u] = 0;
-            if (on[u]) {
-                if (a.nulls && a.nulls[i]) {
+        for (int u = 0; u < 8; u++) {
+            const int64_t i = tile0 + (int64_t)(it + u) * 256 + threadIdx.x;
+            x[u] = i < n ? keys[i] : (KT)0;
+            isnull[u] = a.nulls && i < n ? a.nulls[i] : (uint8_t)0;
+        }
+#pragma unroll
+        for (int half = 0; half < 8; half += 4) {
+            bool on[4], test[4];
+            uint64_t h[4];
+            RfBucket b[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const long long xv = (long long)x[half + u];
+                on[u] = (smask[(it + half + u) * 8 + warp] >> lane) & 1u; // row (it+half+u)*256 + tid of the tile = bit `lane` of that word
+                test[u] = on[u];
+                if (on[u] && isnull[half + u]) {
                     on[u] = a.v.has_null != 0;
                     test[u] = false;
-                } else if constexpr (W == 1) x[u] = ((const int8_t*)a.data)[i];
-                else if constexpr (W == 2) x[u] = ((const int16_t*)a.data)[i];
-                else if constexpr (W == 4) x[u] = ((const int32_t*)a.data)[i];
-                else x[u] = ((const long long*)a.data)[i];
+                }
+                if (test[u] && (xv < a.v.min || xv > a.v.max)) on[u] = test[u] = false;
+                h[u] = rf_hash(xv, a.v.mix);
+                b[u] = RfBucket{};
+                if (test[u]) b[u] = ld_bucket(dir + (size_t)((uint32_t)h[u] & a.v.directory_mask) * 8);
             }
-        }
-        uint4 b0[4], b1[4];
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-            if (test[u] && (x[u] < a.v.min || x[u] > a.v.max)) on[u] = test[u] = false;
-            b0[u] = b1[u] = make_uint4(0, 0, 0, 0);
-            if (test[u]) {
-                const size_t bucket = (uint32_t)rf_hash(x[u], a.v.mix) & a.v.directory_mask;
-                b0[u] = __ldg(dir + bucket * 2);
-                b1[u] = __ldg(dir + bucket * 2 + 1);
-            }
-        }
+            for (int u = 0; u < 4; u++) {
+                if (test[u]) {
+                    const uint32_t key = (uint32_t)(h[u] >> a.v.log_num_buckets);
+                    uint32_t miss = 0;
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-            if (test[u]) {
-                const uint32_t key = (uint32_t)(rf_hash(x[u], a.v.mix) >> a.v.log_num_buckets);
-                const uint32_t miss = (~b0[u].x & rf_word_mask(key, 0)) | (~b0[u].y & rf_word_mask(key, 1)) | (~b0[u].z & rf_word_mask(key, 2)) |
-                                      (~b0[u].w & rf_word_mask(key, 3)) | (~b1[u].x & rf_word_mask(key, 4)) | (~b1[u].y & rf_word_mask(key, 5)) |
-                                      (~b1[u].z & rf_word_mask(key, 6)) | (~b1[u].w & rf_word_mask(key, 7));
-                on[u] = miss == 0;
-            }
-            const uint32_t w = __ballot_sync(0xffffffffu, on[u]);
-            const int64_t i = tile0 + (int64_t)(it + u) * 256 + threadIdx.x;
-            if (lane == 0 && i < n) {
-                mask[i >> 5] = w;
-                mine += __popc(w);
+                    for (int i = 0; i < 8; i++) miss |= ~b[u].w[i] & rf_word_mask(key, i);
+                    on[u] = miss == 0;
+                }
+                const uint32_t w = __ballot_sync(0xffffffffu, on[u]);
+                const int64_t word = w0 + (it + half + u) * 8 + warp;
+                if (lane == 0 && word < n_words) {
+                    mask[word] = w;
+                    mine += __popc(w);
+                }
             }
         }
     }

@@ -150,9 +150,15 @@ class SsbQ41:
     table through the probes and the aggregation. `replicate` (multi-GPU): callable applied to every filtered dimension before
     its build — the broadcast exchange (ops.Communicator.all_gather)."""
 
-    def __init__(self, ctx, replicate: Optional[Callable[[K.Chunk], K.Chunk]] = None):
+    def __init__(self, ctx, replicate: Optional[Callable[[K.Chunk], K.Chunk]] = None, runtime_filter: Optional[bool] = None):
+        """runtime_filter (default: unless SRB_NO_RF is set): the three filtered dimension joins publish runtime filters and the
+        lineorder scan applies them (supplier, customer, part: 1/5 x 1/5 x 2/5 of the rows survive) before anything is copied or
+        probed — the local runtime filters of a broadcast join (hash_join_build_operator.cpp:97-208). Dimension keys are dense, so
+        the filters use the reference tree's own hash (hash_mix = 0)."""
+        import os
         self.ctx, self.replicate = ctx, replicate
-        self.joins, self.keep = [], []
+        self.use_rf = (not os.environ.get("SRB_NO_RF")) if runtime_filter is None else runtime_filter
+        self.joins, self.keep, self.rfs = [], [], []
         self.launches = 0
 
     def build(self, dims: Dict[str, K.Chunk]):
@@ -169,12 +175,26 @@ class SsbQ41:
             j.push_chunk(side)
             j.set_finishing()
             self.joins.append(j)
+            if self.use_rf and fplan is not None:
+                probe_slot = {"ssb_supplier": Q.LO_SUPPKEY, "ssb_customer": Q.LO_CUSTKEY, "ssb_part": Q.LO_PARTKEY}[name]
+                self.rfs.append((j.build_runtime_filter(0), probe_slot))
         return self
 
     def probe(self, lineorder: K.Chunk, phase: int = K.AGG_UPDATE_FINALIZE, stage_rows=None):
         """-> the aggregation operator after set_finishing (pull from it); stage_rows (list) collects the rows after each probe"""
         cur = lineorder
-        for j in self.joins:
+        scan = None
+        if self.rfs:  # the lineorder scan: no predicate of its own, three runtime filters
+            scan = ops.ScanAggOperator(self.ctx, Q.filter_plan([], [Q.LO_CUSTKEY, Q.LO_PARTKEY, Q.LO_SUPPKEY, Q.LO_ORDERDATE, Q.LO_REVENUE, Q.LO_SUPPLYCOST]))
+            for rf, slot in self.rfs:
+                scan.add_runtime_filter(rf, slot)
+            scan.push_chunk(lineorder)
+            scan.set_finishing()
+            cur = scan.pull_device()
+            self.scan_launches = scan.counters()["kernel_launches"]
+            if stage_rows is not None:
+                stage_rows.append(cur.n_rows if cur is not None else 0)
+        for j in (self.joins if cur is not None else []):
             j.probe.push_chunk(cur)
             cur = j.probe.pull_device()
             if stage_rows is not None:
@@ -185,12 +205,14 @@ class SsbQ41:
         if cur is not None and cur.n_rows:
             agg.push_chunk(cur)
         agg.set_finishing()
+        if scan is not None:
+            scan.close()  # its rows have been consumed by the first probe
         return agg
 
     def close(self):
-        for o in self.joins + self.keep:
+        for o in self.joins + self.keep + [rf for rf, _ in self.rfs]:
             o.close()
-        self.joins, self.keep = [], []
+        self.joins, self.keep, self.rfs = [], [], []
 
 
 def ssb_q41_oracle(oracle, dims: Dict[str, K.Chunk], lineorder: K.Chunk, n_threads: int = 1) -> K.Chunk:

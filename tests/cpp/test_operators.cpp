@@ -258,6 +258,76 @@ static void test_inner_join(srb_ctx* ctx) {
     std::printf("PASS inner join (%zu output rows in %zu chunks)\n", want.size(), res.value().size());
 }
 
+// ---- runtime filter: the build operator publishes it, the probe-side scan applies it, the probe sees far fewer rows -------------------
+static void test_runtime_filter_scan(srb_ctx* ctx) {
+    const int BK = 20, PK = 30, PX = 31;
+    std::set<int32_t> keys;
+    auto bk = std::make_shared<Int32Column>(SRB_TYPE_INT);
+    for (int i = 0; i < 3000; i++) {
+        const int32_t k = (int32_t)(splitmix(i) % 1000000);
+        if (keys.insert(k).second) bk->append(k);
+    }
+    auto build = std::make_shared<Chunk>();
+    build->append_column(bk, BK);
+    std::vector<ChunkPtr> probes;
+    std::multiset<std::pair<int32_t, int64_t>> want;
+    const int n_probe = 40000;
+    for (int base = 0; base < n_probe; base += 4096) {
+        auto pk = std::make_shared<Int32Column>(SRB_TYPE_INT);
+        auto px = std::make_shared<Int64Column>(SRB_TYPE_BIGINT);
+        for (int i = base; i < std::min(base + 4096, n_probe); i++) {
+            const int32_t k = (int32_t)(splitmix(i % 2 ? i + 77777 : i / 2) % 1000000); // every other row probes a build key
+            pk->append(k);
+            px->append(i);
+            if (keys.count(k)) want.emplace(k, (int64_t)i);
+        }
+        auto c = std::make_shared<Chunk>();
+        c->append_column(pk, PK);
+        c->append_column(px, PX);
+        probes.push_back(c);
+    }
+    JoinPlan jp;
+    jp.build_key_slots = {BK};
+    jp.probe_key_slots = {PK};
+    jp.probe_out_slots = {PK, PX};
+    auto joiner = std::make_shared<GpuHashJoiner>(ctx, jp);
+    joiner->runtime_filter_key = 0;
+    ScanAggPlan sp; // a scan without predicates of its own: only the runtime filter narrows it
+    sp.out_slots = {PK, PX};
+    GpuScanAggregateOperator scan(ctx, sp);
+    scan.wait_for_runtime_filter(joiner, PK);
+    RuntimeState state(4096);
+    CHECK(scan.prepare(&state).ok());
+    CHECK(!scan.need_input()); // blocked until the build side has published its filter
+    ChunkSourceOperator bsrc({build});
+    GpuHashJoinBuildOperator bop(joiner);
+    CHECK(run_pipeline(&state, {&bsrc, &bop}).ok());
+    CHECK(joiner->runtime_filter() != nullptr);
+    int64_t nb = 0, mn = 0, mx = 0, ins = 0;
+    int32_t hn = 0;
+    CHECK(srb_runtime_filter_info(joiner->runtime_filter(), &nb, &mn, &mx, &hn, &ins) == SRB_OK);
+    CHECK(ins == (int64_t)keys.size() && mn == *keys.begin() && mx == *keys.rbegin() && hn == 0 && nb == 128); // init(<=4096 keys): 2^(12-5) buckets
+    CHECK(scan.need_input());
+    ChunkSourceOperator psrc(probes);
+    GpuHashJoinProbeOperator pop(joiner);
+    auto res = run_pipeline(&state, {&psrc, &scan, &pop});
+    CHECK(res.ok());
+    if (!res.ok()) {
+        std::printf("  %s\n", res.status().to_string().c_str());
+        return;
+    }
+    std::multiset<std::pair<int32_t, int64_t>> got;
+    for (auto& ch : res.value()) {
+        const int32_t* k = (const int32_t*)ch->get_column_by_slot_id(PK)->raw_data();
+        const int64_t* x = (const int64_t*)ch->get_column_by_slot_id(PX)->raw_data();
+        for (size_t r = 0; r < ch->num_rows(); r++) got.emplace(k[r], x[r]);
+    }
+    CHECK(got == want);
+    const int64_t kept = scan.rows_selected();
+    CHECK(kept >= (int64_t)want.size() && kept < (int64_t)want.size() + n_probe / 20); // every match kept, nearly everything else dropped
+    std::printf("PASS runtime filter (%zu matches, scan kept %lld of %d rows)\n", want.size(), (long long)kept, n_probe);
+}
+
 // ---- the error convention: statuses, never exceptions ----------------------------------------------------------------------------------
 static void test_error_convention(srb_ctx* ctx) {
     ScanAggPlan plan;
@@ -305,6 +375,7 @@ int main(int argc, char** argv) {
     test_filter_and_decimal_sum(ctx);
     test_group_by_nullable_key(ctx);
     test_inner_join(ctx);
+    test_runtime_filter_scan(ctx);
     test_error_convention(ctx);
     srb_ctx_destroy(ctx);
     std::printf("%d checks, %d failed\n", g_checks, g_failed);

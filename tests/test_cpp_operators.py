@@ -42,4 +42,4 @@ def test_cpp_operators_on_gpu():
     exe = _build()
     r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
-    assert r.stdout.count("PASS") == 4 and " 0 failed" in r.stdout, r.stdout
+    assert r.stdout.count("PASS") == 5 and " 0 failed" in r.stdout, r.stdout
