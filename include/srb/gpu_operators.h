@@ -160,10 +160,14 @@ public:
         return from_srb(out);
     }
     void close(RuntimeState*) override {
-        if (_op) srb_op_close(_op);
+        if (_op) {
+            _rows_selected = rows_selected(); // the profile counter outlives the device state (RuntimeProfile is read after close)
+            srb_op_close(_op);
+        }
         _op = nullptr;
     }
     int64_t rows_selected() const {
+        if (!_op) return _rows_selected;
         int64_t in = 0, sel = 0, launches = 0;
         srb_op_counters(_op, &in, &sel, &launches);
         return sel;
@@ -177,6 +181,7 @@ private:
     srb_op* _op = nullptr;
     std::vector<std::pair<std::shared_ptr<class GpuHashJoiner>, int32_t>> _rf_sources;
     bool _rf_attached = false;
+    int64_t _rows_selected = 0;
 };
 
 // ---- hash join: the build and probe operators share one joiner, like HashJoiner (exec/hash_joiner.h:169) -------------------------
