@@ -711,9 +711,29 @@ SRB_D void compact_words(const T* __restrict__ src, T* __restrict__ dst, uint32_
     }
 }
 
+// A sparse tile (at most a quarter of its rows kept: the scan behind a selective runtime filter) is copied through the list of its
+// kept row numbers instead: work in proportion to the kept rows, consecutive threads write consecutive output rows.
+template <class T>
+SRB_D void compact_list(const T* __restrict__ src, T* __restrict__ dst, const uint16_t* sidx, uint32_t total) {
+    for (uint32_t j0 = 0; j0 < total; j0 += 256 * 4) {
+        T v[4] = {};
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t j = j0 + u * 256 + threadIdx.x;
+            if (j < total) v[u] = src[sidx[j]];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t j = j0 + u * 256 + threadIdx.x;
+            if (j < total) dst[j] = v[u];
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256, 4) k_compact(const __grid_constant__ CompactArgs ca, int64_t n, const uint32_t* __restrict__ mask,
                                                   const uint64_t* __restrict__ tile_offsets) {
     __shared__ uint32_t wtot[8];
+    __shared__ uint16_t sidx[FTILE / 4];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t tile0 = (int64_t)blockIdx.x * FTILE;
     const int64_t w0 = tile0 >> 5;
@@ -729,11 +749,37 @@ __global__ void __launch_bounds__(256, 4) k_compact(const __grid_constant__ Comp
     }
     if (lane == 31) wtot[warp] = inc;
     __syncthreads();
-    uint32_t before = 0;
-    for (int w = 0; w < warp; w++) before += wtot[w];
+    uint32_t before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        const uint32_t t = wtot[w];
+        before += w < warp ? t : 0;
+        total += t;
+    }
     const uint32_t my_pos = before + inc - c; // first output position of this thread's word, relative to the tile
-    if (__ballot_sync(0xffffffffu, word != 0) == 0) return;
+    if (total == 0) return;
     const uint64_t out0 = tile_offsets[blockIdx.x];
+    if (total <= FTILE / 4) { // block-uniform
+        uint32_t off = my_pos, bits = word;
+        while (bits) {
+            sidx[off++] = (uint16_t)(threadIdx.x * 32 + __ffs(bits) - 1);
+            bits &= bits - 1;
+        }
+        __syncthreads();
+        for (int cidx = 0; cidx < ca.n_cols; cidx++) {
+            const CompactCol& cc = ca.cols[cidx];
+            switch (cc.width) {
+            case 1: compact_list((const uint8_t*)cc.src + tile0, (uint8_t*)cc.dst + out0, sidx, total); break;
+            case 2: compact_list((const uint16_t*)cc.src + tile0, (uint16_t*)cc.dst + out0, sidx, total); break;
+            case 4: compact_list((const uint32_t*)cc.src + tile0, (uint32_t*)cc.dst + out0, sidx, total); break;
+            case 8: compact_list((const uint64_t*)cc.src + tile0, (uint64_t*)cc.dst + out0, sidx, total); break;
+            default: compact_list((const ulonglong2*)cc.src + tile0, (ulonglong2*)cc.dst + out0, sidx, total);
+            }
+            if (cc.src_null) compact_list(cc.src_null + tile0, cc.dst_null + out0, sidx, total);
+        }
+        return;
+    }
+    if (__ballot_sync(0xffffffffu, word != 0) == 0) return;
     const int64_t row0 = tile0 + (int64_t)warp * 1024;
     for (int cidx = 0; cidx < ca.n_cols; cidx++) {
         const CompactCol& cc = ca.cols[cidx];
