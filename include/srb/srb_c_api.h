@@ -178,7 +178,9 @@ typedef struct srb_scan_agg_plan {
 
 /* ---- hash join: exec/hash_joiner.h:169, exec/join_hash_map.h:101-214 -------------------------------- */
 #define SRB_JOIN_INNER 0     /* TJoinOp::INNER_JOIN */
-#define SRB_JOIN_LEFT_SEMI 3 /* TJoinOp::LEFT_SEMI_JOIN */
+#define SRB_JOIN_LEFT_SEMI 2 /* TJoinOp::LEFT_SEMI_JOIN (gensrc/thrift/PlanNodes.thrift:696-715: values count from 0) */
+#define SRB_JOIN_LEFT_ANTI 8 /* TJoinOp::LEFT_ANTI_JOIN: probe rows without a match, NULL probe keys included (join_hash_map.tpp:1349-1420);
+                                probe columns only */
 
 typedef struct srb_join_plan {
     int32_t join_type;

@@ -100,10 +100,27 @@ Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_ch
     PackedKeys pk = pack_keys(*probe, plan->probe_key_slots, plan->n_keys);
     if (pk.width != t.keys.width) throw std::runtime_error("join: key width mismatch");
     std::vector<uint32_t> probe_index, build_index; // build_index is 1-based like the reference's
+    const bool anti = plan->join_type == SRB_JOIN_LEFT_ANTI;
     for (int64_t i = 0; i < probe->n_rows; i++) {
-        if (pk.null[i]) continue;
+        if (pk.null[i]) {
+            // lookup_init leaves next[i] = 0 for NULL probe keys: no match. LEFT ANTI emits such rows (join_hash_map.tpp:1380-1420,
+            // "NULLs are not matches and therefore always returned", PlanNodes.thrift:710-713); every other type drops them
+            if (anti) {
+                probe_index.push_back((uint32_t)i);
+                build_index.push_back(1);
+            }
+            continue;
+        }
         uint32_t bi = t.first[bucket_of(pk, pk.k[i], t.bucket_size, t.log_bucket)];
         bool matched = false;
+        if (anti) {
+            for (; bi != 0 && !matched; bi = t.next[bi]) matched = t.keys.k[bi - 1] == pk.k[i];
+            if (!matched) {
+                probe_index.push_back((uint32_t)i);
+                build_index.push_back(1);
+            }
+            continue;
+        }
         while (bi != 0) {
             if (t.keys.k[bi - 1] == pk.k[i]) {
                 if (plan->join_type == SRB_JOIN_LEFT_SEMI) {
@@ -130,13 +147,13 @@ Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_ch
         r->slot_ids.push_back(plan->probe_out_slots[i]);
         copy_rows(*find_slot(*probe, plan->probe_out_slots[i]), probe_index, r->cols.back());
     }
-    if (plan->join_type != SRB_JOIN_LEFT_SEMI)
+    if (plan->join_type != SRB_JOIN_LEFT_SEMI && !anti)
         for (int i = 0; i < plan->n_build_out; i++) {
             r->cols.emplace_back();
             r->slot_ids.push_back(plan->build_out_slots[i]);
             copy_rows(*find_slot(*build, plan->build_out_slots[i]), build_rows, r->cols.back());
         }
-    if (plan->emit_indexes) {
+    if (plan->emit_indexes && !anti) {
         for (int which = 0; which < 2; which++) {
             r->cols.emplace_back();
             OutCol& c = r->cols.back();

@@ -245,7 +245,7 @@ SRB_D uint32_t jbucket_w(const JTable& t, uint64_t lo, uint64_t hi) {
 
 template <int W>
 __global__ void __launch_bounds__(JT_THREADS) k_join_probe_first(JTable t, const uint8_t* __restrict__ pkeys, const uint8_t* __restrict__ pnull, int64_t n,
-                                                                  uint32_t* __restrict__ match, uint32_t* __restrict__ tile_counts) {
+                                                                  uint32_t* __restrict__ match, uint32_t* __restrict__ tile_counts, int anti) {
     __shared__ uint32_t warp_cnt[JT_THREADS / 32];
     const int64_t n_tiles = (n + JT_TILE - 1) / JT_TILE;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -284,6 +284,7 @@ __global__ void __launch_bounds__(JT_THREADS) k_join_probe_first(JTable t, const
 #pragma unroll
         for (int j = 0; j < JT_ROWS; j++) {
             const int64_t r = tile * JT_TILE + j * JT_THREADS + threadIdx.x;
+            if (anti) m[j] = r < n && m[j] == 0 ? 1u : 0u; // LEFT ANTI keeps exactly the rows without a match (NULL keys never match)
             if (r < n) match[r] = m[j];
             cnt += m[j] ? 1u : 0u;
         }
@@ -296,6 +297,18 @@ __global__ void __launch_bounds__(JT_THREADS) k_join_probe_first(JTable t, const
             tile_counts[tile] = s;
         }
         __syncthreads();
+    }
+}
+
+// LEFT ANTI against an empty build side: every probe row is kept
+__global__ void __launch_bounds__(JT_THREADS) k_join_all_rows(int64_t n, uint32_t* __restrict__ match, uint32_t* __restrict__ tile_counts) {
+    const int64_t n_tiles = (n + JT_TILE - 1) / JT_TILE;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (int j = 0; j < JT_ROWS; j++) {
+            const int64_t r = tile * JT_TILE + j * JT_THREADS + threadIdx.x;
+            if (r < n) match[r] = 1u;
+        }
+        if (threadIdx.x == 0) tile_counts[tile] = (uint32_t)((n - tile * JT_TILE) < JT_TILE ? (n - tile * JT_TILE) : JT_TILE);
     }
 }
 
@@ -483,17 +496,19 @@ class JoinOp : public srb_op {
 public:
     JoinOp(srb_ctx* c, const srb_join_plan* p) : srb_op(c) {
         if (!p) throw Error(SRB_INVALID_ARGUMENT, "null plan");
-        if (p->join_type != SRB_JOIN_INNER && p->join_type != SRB_JOIN_LEFT_SEMI) throw Error(SRB_NOT_IMPLEMENTED, fmt("join type %d", p->join_type));
+        if (p->join_type != SRB_JOIN_INNER && p->join_type != SRB_JOIN_LEFT_SEMI && p->join_type != SRB_JOIN_LEFT_ANTI)
+            throw Error(SRB_NOT_IMPLEMENTED, fmt("join type %d", p->join_type));
         if (p->n_keys < 1 || p->n_keys > JMAX_KEYS) throw Error(SRB_NOT_IMPLEMENTED, fmt("join with %d key columns", p->n_keys));
         if (p->n_build_out < 0 || p->n_probe_out < 0 || p->n_build_out + p->n_probe_out > JMAX_OUT)
             throw Error(SRB_NOT_IMPLEMENTED, "too many join output columns");
-        semi_ = p->join_type == SRB_JOIN_LEFT_SEMI;
+        anti_ = p->join_type == SRB_JOIN_LEFT_ANTI;
+        semi_ = p->join_type == SRB_JOIN_LEFT_SEMI || anti_; // an existence test either way: at most one output row per probe row
         bkeys_.assign(p->build_key_slots, p->build_key_slots + p->n_keys);
         pkeys_.assign(p->probe_key_slots, p->probe_key_slots + p->n_keys);
         bout_.assign(p->build_out_slots, p->build_out_slots + p->n_build_out);
         pout_.assign(p->probe_out_slots, p->probe_out_slots + p->n_probe_out);
         if (semi_) bout_.clear(); // LEFT SEMI emits probe columns only
-        emit_indexes_ = p->emit_indexes != 0;
+        emit_indexes_ = p->emit_indexes != 0 && !anti_;
         chunk_size_ = c->cfg.chunk_size > 0 ? c->cfg.chunk_size : 4096;
         bcols_.resize(bkeys_.size() + bout_.size());
         total_dev_.ensure(c, 8);
@@ -580,10 +595,14 @@ public:
             }
             if (i < pkeys_.size()) total += g.width;
         }
-        if (n == 0 || build_rows_ == 0) return;
+        if (n == 0 || (build_rows_ == 0 && !anti_)) return;
+        if (build_rows_ == 0) { // LEFT ANTI against nothing: every probe row
+            probe_tiled(n, data, nulls);
+            return;
+        }
         int pw = total <= 4 ? 4 : (total <= 8 ? 8 : 16);
         if (total > 16 || pw != width_) throw Error(SRB_INVALID_ARGUMENT, "probe key width does not match the build key width");
-        if (unique_ && !force_general_) {
+        if ((unique_ && !force_general_) || anti_) {
             probe_tiled(n, data, nulls);
             return;
         }
@@ -654,7 +673,9 @@ public:
     void probe_tiled(int64_t n, const std::vector<const uint8_t*>& data, const std::vector<const uint8_t*>& nulls) {
         const uint8_t* keys = nullptr;
         const uint8_t* knull = nullptr;
-        if (pkeys_.size() == 1 && pcols_[0].width == width_) { // a single 4/8/16-byte key column is its own packed form
+        const bool all_rows = anti_ && build_rows_ == 0;
+        if (all_rows) {
+        } else if (pkeys_.size() == 1 && pcols_[0].width == width_) { // a single 4/8/16-byte key column is its own packed form
             keys = data[0];
             knull = nulls[0];
         } else {
@@ -674,15 +695,20 @@ public:
         match_.ensure(ctx, (size_t)n * 4);
         tcounts_.ensure(ctx, (size_t)tiles * 4);
         toffs_.ensure(ctx, (size_t)tiles * 8);
-        JTable t = table();
         uint32_t* match = match_.as<uint32_t>();
         uint32_t* tc = tcounts_.as<uint32_t>();
-        if (width_ == 4)
-            k_join_probe_first<4><<<grid, JT_THREADS, 0, stream>>>(t, keys, knull, n, match, tc);
-        else if (width_ == 8)
-            k_join_probe_first<8><<<grid, JT_THREADS, 0, stream>>>(t, keys, knull, n, match, tc);
-        else
-            k_join_probe_first<16><<<grid, JT_THREADS, 0, stream>>>(t, keys, knull, n, match, tc);
+        const int anti = anti_ ? 1 : 0;
+        if (all_rows) {
+            k_join_all_rows<<<grid, JT_THREADS, 0, stream>>>(n, match, tc);
+        } else {
+            JTable t = table();
+            if (width_ == 4)
+                k_join_probe_first<4><<<grid, JT_THREADS, 0, stream>>>(t, keys, knull, n, match, tc, anti);
+            else if (width_ == 8)
+                k_join_probe_first<8><<<grid, JT_THREADS, 0, stream>>>(t, keys, knull, n, match, tc, anti);
+            else
+                k_join_probe_first<16><<<grid, JT_THREADS, 0, stream>>>(t, keys, knull, n, match, tc, anti);
+        }
         k_join_scan<<<1, 1024, 0, stream>>>(tc, toffs_.as<uint64_t>(), tiles, total_dev_.as<unsigned long long>());
         SRB_CUDA(cudaMemcpyAsync(total_host_.p, total_dev_.p, 8, cudaMemcpyDeviceToHost, stream));
         SRB_CUDA(cudaStreamSynchronize(stream));
@@ -921,6 +947,7 @@ private:
         return t;
     }
 
+    bool anti_ = false;
     bool semi_ = false, emit_indexes_ = false, build_done_ = false, probe_finishing_ = false, gave_empty_ = false;
     std::vector<int32_t> bkeys_, pkeys_, bout_, pout_;
     int64_t chunk_size_;

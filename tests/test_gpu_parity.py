@@ -595,6 +595,37 @@ def test_join_reference_vectors(ctx, oracle, join_mode):
     assert rows == K.chunk_rows(oracle.join(plan, build, probe))
     semi = JoinPlan([0], [2], probe_out=[3], join_type=K.JOIN_LEFT_SEMI)
     assert K.chunk_rows(run_join(ctx, semi, build, probe)) == [(200,), (300,)]
+    # LEFT ANTI: the probe rows without a match, a NULL probe key included (join_hash_map.tpp:1349-1420)
+    anti = JoinPlan([0], [2], probe_out=[3], join_type=K.JOIN_LEFT_ANTI)
+    assert K.chunk_rows(run_join(ctx, anti, build, probe)) == [(400,), (500,), (700,)] == K.chunk_rows(oracle.join(anti, build, probe))
+
+
+@pytest.mark.parametrize("ktypes", [[K.TYPE_INT], [K.TYPE_BIGINT, K.TYPE_INT], [K.TYPE_DECIMAL128]])
+def test_left_semi_and_anti_partition_the_probe_side(ctx, oracle, ktypes):
+    """LEFT SEMI and LEFT ANTI against the oracle on duplicate-heavy build sides with NULL keys on both sides; together they return
+    every probe row exactly once, in probe order; an empty build side makes ANTI return everything"""
+    rng = np.random.default_rng(17 + len(ktypes))
+    nb, npb = 20000, 150000
+    bcols = {i: _rand_col(rng, t, nb, 0.05, small=True) for i, t in enumerate(ktypes)}
+    pcols = {10 + i: _rand_col(rng, t, npb, 0.05, small=True) for i, t in enumerate(ktypes)}
+    if ktypes == [K.TYPE_INT]:
+        bcols[0] = K.Column.from_ints(K.TYPE_INT, rng.integers(0, 50000, nb), nulls=(rng.random(nb) < 0.02).astype(np.uint8))
+        pcols[10] = K.Column.from_ints(K.TYPE_INT, rng.integers(-100, 60000, npb), nulls=(rng.random(npb) < 0.02).astype(np.uint8))
+    pcols[15] = K.Column.from_ints(K.TYPE_BIGINT, np.arange(npb))
+    build, probe = K.Chunk(nb, bcols), K.Chunk(npb, pcols)
+    keys = (list(range(len(ktypes))), [10 + i for i in range(len(ktypes))])
+    got = {}
+    for name, jt in (("semi", K.JOIN_LEFT_SEMI), ("anti", K.JOIN_LEFT_ANTI)):
+        plan = JoinPlan(*keys, probe_out=[15], join_type=jt)
+        want = K.chunk_rows(oracle.join(plan, build, probe), sort=False)
+        for device in (False, True):
+            assert K.chunk_rows(run_join(ctx, plan, build, probe, build_pieces=3, device=device), sort=False) == want
+        got[name] = [r[0] for r in want]
+    assert len(got["semi"]) > 1000 and len(got["anti"]) > 1000
+    assert sorted(got["semi"] + got["anti"]) == list(range(npb))
+    empty = K.Chunk(0, {i: K.Column.from_ints(t, []) for i, t in enumerate(ktypes)})
+    plan = JoinPlan(*keys, probe_out=[15], join_type=K.JOIN_LEFT_ANTI)
+    assert [r[0] for r in K.chunk_rows(run_join(ctx, plan, empty, probe), sort=False)] == list(range(npb))
 
 
 @pytest.mark.parametrize("ktypes", [[K.TYPE_INT], [K.TYPE_BIGINT], [K.TYPE_INT, K.TYPE_INT], [K.TYPE_SMALLINT], [K.TYPE_BIGINT, K.TYPE_INT],

@@ -266,6 +266,11 @@ def test_join_inner_one_to_many_and_nulls(oracle):
     plan = JoinPlan([0], [2], build_out=[1], probe_out=[3])
     rows = K.chunk_rows(oracle.join(plan, build, probe))
     assert rows == [(200, 20), (200, 21), (300, 30)]  # NULL keys never match (tpp:62-72)
+    # LEFT SEMI: one row per matching probe row; LEFT ANTI: the rest, the NULL probe key included (tpp:1349-1420, PlanNodes.thrift:710-713)
+    semi = JoinPlan([0], [2], probe_out=[3], join_type=K.JOIN_LEFT_SEMI)
+    anti = JoinPlan([0], [2], probe_out=[3], join_type=K.JOIN_LEFT_ANTI)
+    assert K.chunk_rows(oracle.join(semi, build, probe), sort=False) == [(200,), (300,)]
+    assert K.chunk_rows(oracle.join(anti, build, probe), sort=False) == [(400,), (500,), (700,)]
 
 
 def test_fixed_size_key_packing(oracle):
