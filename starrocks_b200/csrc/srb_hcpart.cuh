@@ -48,19 +48,25 @@ __global__ void k_hc_scan(unsigned long long* __restrict__ hist, unsigned long l
     hist[t] = 0;
 }
 
+template <int NV> // value columns carried with the key: 1 (phase 1: k, v) or 2 (phase 2: k, partial sum, partial count)
 struct HcSmem {
     uint64_t k[HC_TILE];
-    uint64_t v[HC_TILE];
+    uint64_t v[NV][HC_TILE];
     uint8_t p[HC_TILE];
     unsigned int cnt[HC_PARTS], scan[HC_PARTS], start[HC_PARTS];
     unsigned long long gbase[HC_PARTS];
 };
 
+struct HcVals {
+    const uint64_t* src[2];
+    uint64_t* dst[2];
+};
+template <int NV>
 __global__ void __launch_bounds__(HC_THREADS, 1)
-        k_hc_scatter(const uint64_t* __restrict__ keys, const uint64_t* __restrict__ vals, int64_t n, int seed, uint64_t mask, int shift,
-                     unsigned long long* __restrict__ cursor, uint64_t* __restrict__ pk, uint64_t* __restrict__ pv) {
+        k_hc_scatter(const uint64_t* __restrict__ keys, const HcVals vals, int64_t n, int seed, uint64_t mask, int shift,
+                     unsigned long long* __restrict__ cursor, uint64_t* __restrict__ pk) {
     extern __shared__ __align__(16) uint8_t raw[];
-    HcSmem& sm = *reinterpret_cast<HcSmem*>(raw);
+    HcSmem<NV>& sm = *reinterpret_cast<HcSmem<NV>*>(raw);
     const int tid = threadIdx.x;
     const int64_t n_tiles = (n + HC_TILE - 1) / HC_TILE;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -68,7 +74,7 @@ __global__ void __launch_bounds__(HC_THREADS, 1)
         const int rows = (int)(n - base < HC_TILE ? n - base : HC_TILE);
         if (tid < HC_PARTS) sm.cnt[tid] = 0;
         __syncthreads();
-        uint64_t k[HC_ROWS], v[HC_ROWS];
+        uint64_t k[HC_ROWS];
         int part[HC_ROWS];
         unsigned int rank[HC_ROWS];
 #pragma unroll
@@ -76,7 +82,6 @@ __global__ void __launch_bounds__(HC_THREADS, 1)
             const int j = r * HC_THREADS + tid;
             if (j < rows) {
                 k[r] = keys[base + j];
-                v[r] = vals[base + j];
             }
         }
 #pragma unroll
@@ -112,8 +117,23 @@ __global__ void __launch_bounds__(HC_THREADS, 1)
             if (j < rows) {
                 const unsigned int pos = sm.start[part[r]] + rank[r];
                 sm.k[pos] = k[r];
-                sm.v[pos] = v[r];
                 sm.p[pos] = (uint8_t)part[r];
+            }
+        }
+        // the value columns follow one at a time (their eight loads per thread in flight together): the keys alone had to be held
+        // across the barriers above
+#pragma unroll
+        for (int c = 0; c < NV; c++) {
+            uint64_t v[HC_ROWS];
+#pragma unroll
+            for (int r = 0; r < HC_ROWS; r++) {
+                const int j = r * HC_THREADS + tid;
+                if (j < rows) v[r] = vals.src[c][base + j];
+            }
+#pragma unroll
+            for (int r = 0; r < HC_ROWS; r++) {
+                const int j = r * HC_THREADS + tid;
+                if (j < rows) sm.v[c][sm.start[part[r]] + rank[r]] = v[r];
             }
         }
         __syncthreads();
@@ -124,7 +144,8 @@ __global__ void __launch_bounds__(HC_THREADS, 1)
                 const int p = sm.p[j];
                 const unsigned long long dst = sm.gbase[p] + (unsigned long long)(j - sm.start[p]);
                 pk[dst] = sm.k[j];
-                pv[dst] = sm.v[j];
+#pragma unroll
+                for (int c = 0; c < NV; c++) vals.dst[c][dst] = sm.v[c][j];
             }
         }
         __syncthreads();

@@ -33,6 +33,7 @@ struct SNode {
 };
 struct SAgg {
     int fn, arg, wide, has_n; // wide: state keeps the high word (off_hi >= 0); has_n: state keeps its own count
+    int merge = 0;            // phase-2 aggregate over an intermediate column (COUNT adds the partial count)
 };
 struct SKey {
     int node, width;
@@ -121,6 +122,16 @@ struct ShapeQ3Agg {
     static constexpr SKey key(int i) { return SKey{i, 4}; }
 };
 
+// Phase 2 of the two-phase high-cardinality GROUP BY (aggregator.cpp:871-875): rows are (k, partial sum, partial count) tuples
+// received from the shuffle; sum and count are merged into the final table.
+struct ShapeHighCardMerge {
+    static constexpr const char* name = "merge by bigint: sum(bigint), count";
+    static constexpr int N_NODES = 3, N_AGGS = 2, N_KEYS = 1, GMAX = 0, THREADS = 992, ROWS = 2;
+    static constexpr SNode node(int) { return SNode{DOP_LOAD, 8, -1, -1, 0, 0, 0}; }
+    static constexpr SAgg agg(int i) { return i == 0 ? SAgg{FN_SUM, 1, 0, 1, 1} : SAgg{FN_COUNT, 2, 0, 1, 1}; }
+    static constexpr SKey key(int) { return SKey{0, 8}; }
+};
+
 // ---- matching a lowered program against a shape ---------------------------------------------------------------------
 template <class S>
 inline bool shape_matches(const DProg& p) {
@@ -136,7 +147,7 @@ inline bool shape_matches(const DProg& p) {
     for (int a = 0; a < S::N_AGGS; a++) {
         const SAgg s = S::agg(a);
         const DAgg& d = p.aggs[a];
-        if (d.fn != s.fn || d.arg != s.arg || d.is_double || d.avg_as_double || d.merge) return false;
+        if (d.fn != s.fn || d.arg != s.arg || d.is_double || d.avg_as_double || (d.merge != 0) != (s.merge != 0)) return false;
         if ((d.off_hi >= 0) != (s.wide != 0) || (d.off_n >= 0) != (s.has_n != 0)) return false;
     }
     for (int k = 0; k < S::N_KEYS; k++) {
@@ -900,7 +911,9 @@ template <class S, int A>
 SRB_D void row_update_global_one(const DProg& p, uint8_t* slot, const Val* v) {
     constexpr SAgg g = S::agg(A);
     const DAgg& rt = p.aggs[A];
-    if constexpr (g.fn == FN_COUNT) {
+    if constexpr (g.fn == FN_COUNT && g.merge != 0) {
+        if (!v[g.arg].null) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)v[g.arg].lo);
+    } else if constexpr (g.fn == FN_COUNT) {
         bool on = true;
         if constexpr (g.arg >= 0) on = !v[g.arg].null;
         if (on) atomicAdd((unsigned long long*)(slot + rt.off_n), 1ULL);
@@ -1315,6 +1328,7 @@ inline int match_static_shape(const DProg& p) {
     if (shape_matches<ShapeQ1Dict>(p)) return 1;
     if (shape_matches<ShapeHighCard>(p)) return 2;
     if (shape_matches<ShapeQ3Agg>(p)) return 3;
+    if (shape_matches<ShapeHighCardMerge>(p)) return 4;
     return -1;
 }
 inline const char* static_shape_name(int id) {
@@ -1323,6 +1337,7 @@ inline const char* static_shape_name(int id) {
     case 1: return ShapeQ1Dict::name;
     case 2: return ShapeHighCard::name;
     case 3: return ShapeQ3Agg::name;
+    case 4: return ShapeHighCardMerge::name;
     }
     return "generic";
 }
@@ -1461,6 +1476,7 @@ inline int64_t launch_static_shape(int shape, const DProg& p, const TableView& t
     case 1: return launch_shape<ShapeQ1Dict>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
     case 2: return launch_shape<ShapeHighCard>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
     case 3: return launch_shape<ShapeQ3Agg>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
+    case 4: return launch_shape<ShapeHighCardMerge>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
     }
     return 0;
 }

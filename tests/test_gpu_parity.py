@@ -491,6 +491,63 @@ def test_highcard_l2_blocked_partition_path(ctx, oracle, monkeypatch):
             ctx.device_free(p)
 
 
+def test_highcard_merge_phase_static_shape_and_l2_blocked_path(ctx, oracle, monkeypatch):
+    """phase 2 of the two-phase high-cardinality GROUP BY (the tuples a rank receives from the shuffle): intermediate (k, sum, count)
+    rows from two phase-1 operators are merged by the statically specialised merge kernel — through the partition-then-aggregate path
+    when the table is far larger than L2, directly otherwise, and by the generic interpreter — all equal to one-phase aggregation"""
+    from starrocks_b200 import ops
+    n, nk = 9_000_000, 5_000_000
+    ch = T.host_chunk("highcard", 0, n, ["k", "v"], n_keys=nk)
+    want = K.chunk_rows(oracle.scan_agg(Q.highcard_plan(), ch))
+    inters = []
+    for a, b in ((0, n // 2), (n // 2, n)):
+        op = ops.ScanAggOperator(ctx, Q.highcard_plan(phase=K.AGG_UPDATE_SERIALIZE, group_hint=nk))
+        op.push_chunk(ops.slice_chunk(ch, a, b))
+        op.set_finishing()
+        inters.append(ctx.fetch_chunk(op.pull_device()))
+        op.close()
+    from starrocks_b200 import distributed as D
+    inter = D.concat_chunks(inters)
+    assert inter.n_rows > (1 << 22)
+    # the serialized SUM column is nullable (NullableAggregateFunctionUnary) but carries no NULL: the map is dropped per batch
+    sum_col = [c for c in inter.columns.values() if c.nulls is not None]
+    assert sum_col and not any(c.nulls.any() for c in sum_col)
+    dch, ptrs = ctx.device_chunk(inter)
+    try:
+        seen = {}
+        for mode, env in (("partitioned", None), ("direct", "SRB_NO_PARTITION"), ("generic", "SRB_FORCE_GENERIC")):
+            if env:
+                monkeypatch.setenv(env, "1")
+            op = ops.ScanAggOperator(ctx, Q.highcard_merge_plan(group_hint=nk))
+            op.push_chunk(dch)
+            op.set_finishing()
+            got = K.chunk_rows(op.pull_all())
+            prof = op.profile()
+            seen[mode] = (op.counters()["kernel_launches"], prof["shape"], prof["static_launches"])
+            op.close()
+            if env:
+                monkeypatch.delenv(env)
+            assert rows_equal(got, want), mode
+        assert seen["partitioned"][1] == 4 and seen["direct"][1] == 4
+        assert seen["partitioned"][2] >= 1 and seen["direct"][2] >= 1 and seen["generic"][2] == 0
+        assert seen["partitioned"][0] == seen["direct"][0] + 3  # histogram, scan, scatter
+    finally:
+        for p in ptrs:
+            ctx.device_free(p)
+    # partial sums that really are NULL (a phase-1 group whose every value was NULL): the batch keeps its null map, is not
+    # permuted, and the interpreter merges it — equal to the oracle's merge of the same tuples
+    for c in sum_col:
+        c.nulls[::7] = 1
+    want_n = K.chunk_rows(oracle.scan_agg(Q.highcard_merge_plan(), inter))
+    op = ops.ScanAggOperator(ctx, Q.highcard_merge_plan(group_hint=nk))
+    op.push_chunk(inter)
+    op.set_finishing()
+    got_n = K.chunk_rows(op.pull_all())
+    assert op.profile()["static_launches"] == 0
+    op.close()
+    assert rows_equal(got_n, want_n) and not rows_equal(got_n, want)
+
+
 def test_host_chunks_of_4096_rows_like_the_pipeline_driver(ctx, oracle):
     # pipeline_driver.cpp:345-351: chunks of <= chunk_size rows; results must not depend on the chunking
     ch = T.host_chunk("lineitem", 99, 123457, T.LINEITEM_Q1)
