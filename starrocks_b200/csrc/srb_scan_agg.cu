@@ -12,6 +12,7 @@
 // open-addressing table in HBM updated with 64-bit atomics (int128 sums as lo/hi words with carry); recognised program
 // shapes run on statically specialised kernels with TMA-staged column tiles and register pre-aggregation
 // (srb_shapes.cuh). There is no CPU path: every row is processed by a CUDA kernel.
+#include <limits>
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -590,6 +591,51 @@ SRB_D void rf_test_list(const RfArgs& a, const uint32_t* __restrict__ dir, const
     }
 }
 
+// Full tiles (every row still selected: the first filter of a scan without predicates) take a leaner body: the hash flavour and
+// the presence of a null map are compile-time, the [min, max] test runs in the key's own width (the bounds are clamped to the
+// key type's range on entry), bucket loads are unconditional (the masked index is always inside the directory) and a warp's 32
+// verdicts are one ballot = one mask word.
+template <int W, bool MIX, bool NULLS, class KT>
+SRB_D void rf_test_full(const RfArgs& a, const uint32_t* __restrict__ dir, const KT* __restrict__ keys, const uint8_t* __restrict__ nulls, uint32_t* smask,
+                        int lane) {
+    constexpr long long KMIN = (long long)std::numeric_limits<KT>::min(), KMAX = (long long)std::numeric_limits<KT>::max();
+    const long long lo64 = a.v.min > KMIN ? a.v.min : KMIN, hi64 = a.v.max < KMAX ? a.v.max : KMAX;
+    const bool empty = lo64 > hi64; // nothing inserted, or every inserted key lies outside the probe key type's range
+    const KT lo = empty ? (KT)1 : (KT)lo64, hi = empty ? (KT)0 : (KT)hi64;
+    const uint32_t dmask = a.v.directory_mask;
+    const int lnb = a.v.log_num_buckets;
+    const bool null_pass = a.v.has_null != 0;
+#pragma unroll 1
+    for (uint32_t j0 = 0; j0 < (uint32_t)FTILE; j0 += 256 * 4) {
+        KT x[4];
+        uint8_t nl[4] = {};
+        uint64_t h[4];
+        RfBucket b[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) x[u] = keys[j0 + u * 256 + threadIdx.x];
+        if constexpr (NULLS) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) nl[u] = nulls[j0 + u * 256 + threadIdx.x];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            h[u] = MIX ? phmap_mix8((uint64_t)(long long)x[u], 1) : (uint64_t)(long long)x[u];
+            b[u] = ld_bucket(dir + (size_t)((uint32_t)h[u] & dmask) * 8);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t key = (uint32_t)(h[u] >> lnb);
+            uint32_t miss = 0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) miss |= ~b[u].w[i] & rf_word_mask(key, i);
+            bool pass = miss == 0 && x[u] >= lo && x[u] <= hi;
+            if constexpr (NULLS) pass = nl[u] ? null_pass : pass;
+            const uint32_t w = __ballot_sync(0xffffffffu, pass);
+            if (lane == 0) smask[(j0 + u * 256 + threadIdx.x) >> 5] = w;
+        }
+    }
+}
+
 template <int W>
 __global__ void __launch_bounds__(256, 4) k_filter_rf(const __grid_constant__ RfArgs a, int64_t n, uint32_t* __restrict__ mask,
                                                        uint32_t* __restrict__ tile_counts) {
@@ -634,9 +680,15 @@ __global__ void __launch_bounds__(256, 4) k_filter_rf(const __grid_constant__ Rf
     const uint32_t* dir = a.v.dir;
     const KT* keys = (const KT*)a.data + tile0;
     const uint8_t* nulls = a.nulls ? a.nulls + tile0 : nullptr;
-    if (total == FTILE) // every row of the tile is still selected (the first filter of a scan without predicates): rows are their own list
-        rf_test_list<W, true, KT>(a, dir, keys, nulls, total, sidx, smask, lane);
-    else
+    if (total == FTILE) { // every row of the tile is still selected: rows are their own list
+        if (a.v.mix) {
+            if (nulls) rf_test_full<W, true, true, KT>(a, dir, keys, nulls, smask, lane);
+            else rf_test_full<W, true, false, KT>(a, dir, keys, nulls, smask, lane);
+        } else {
+            if (nulls) rf_test_full<W, false, true, KT>(a, dir, keys, nulls, smask, lane);
+            else rf_test_full<W, false, false, KT>(a, dir, keys, nulls, smask, lane);
+        }
+    } else
         rf_test_list<W, false, KT>(a, dir, keys, nulls, total, sidx, smask, lane);
     __syncthreads();
     const uint32_t now = smask[threadIdx.x];

@@ -865,7 +865,7 @@ def test_runtime_filter_of_an_empty_build_side_rejects_everything(ctx, oracle):
 
 
 @pytest.mark.parametrize("pred_kind", ["range", "generic", "none"])
-@pytest.mark.parametrize("nullable,mix", [(False, False), (True, False), (True, True)])
+@pytest.mark.parametrize("nullable,mix", [(False, False), (False, True), (True, False), (True, True)])
 def test_scan_filter_with_runtime_filter_matches_the_oracle(ctx, oracle, pred_kind, nullable, mix):
     """scan predicates AND the runtime filter on the key column, order-preserving compaction: the kept rows are exactly those the
     oracle's predicate + RuntimeBloomFilter::evaluate keep (false positives included), on the vectorised and the generic mask path,
@@ -915,6 +915,39 @@ def test_scan_filter_with_runtime_filter_matches_the_oracle(ctx, oracle, pred_ki
         want_rf.close()
         rf.close()
         j.close()
+
+
+@pytest.mark.parametrize("type_,np_t,lo,hi", [(K.TYPE_TINYINT, np.int8, -50, 60), (K.TYPE_SMALLINT, np.int16, -9000, 12000),
+                                              (K.TYPE_BIGINT, np.int64, -(1 << 40), 1 << 41)])
+def test_runtime_filter_on_full_tiles_of_every_key_width(ctx, oracle, type_, np_t, lo, hi):
+    """a scan without predicates: every tile reaches the filter fully selected (the full-tile body of k_filter_rf), for 1-, 2- and
+    8-byte keys, probe keys on both sides of [min, max]; two and a half tiles so the last one takes the list path"""
+    from starrocks_b200 import ops
+    from tests.oracle_lib import OracleRuntimeFilter
+    rng = np.random.default_rng(11)
+    n_build, n = 40, 8192 * 2 + 4000
+    bkeys = rng.integers(lo, hi, n_build).astype(np_t)
+    j, build = _build_join(ctx, type_, bkeys, None)
+    rf = j.build_runtime_filter()
+    want_rf = OracleRuntimeFilter(oracle, n_build).insert_column(build.columns[0])
+    info = np.iinfo(np_t)
+    span = hi - lo
+    pk = rng.integers(max(info.min, lo - span), min(info.max, hi + span), n).astype(np_t)
+    pk[::3] = bkeys[rng.integers(0, n_build, len(pk[::3]))]  # a third of the probe keys are build keys
+    probe = K.Chunk(n, {1: K.Column.from_ints(type_, pk), 2: K.Column.from_ints(K.TYPE_INT, np.arange(n, dtype=np.int32))})
+    keep = want_rf.evaluate(probe.columns[1]).astype(bool)
+    assert n // 3 <= keep.sum() < n
+    want = [r for r, k in zip(K.chunk_rows(probe, sort=False), keep) if k]
+    op = ops.ScanAggOperator(ctx, Q.filter_plan([], [1, 2]))
+    op.add_runtime_filter(rf, 1)
+    op.push_chunk(probe)
+    op.set_finishing()
+    got = K.chunk_rows(op.pull_all(), sort=False)
+    op.close()
+    assert got == want
+    want_rf.close()
+    rf.close()
+    j.close()
 
 
 def test_runtime_filter_misuse_is_reported(ctx):
