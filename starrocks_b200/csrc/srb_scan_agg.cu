@@ -135,13 +135,24 @@ SRB_D void flush_local(const DAgg& g, const LocalAcc& s, uint8_t* slot) {
     if (g.off_n >= 0) atomicAdd((unsigned long long*)(slot + g.off_n), (unsigned long long)s.n);
 }
 
+// Low-cardinality GROUP BY through the interpreter: a few dozen groups take every row's atomics, which then serialise in L2 on the
+// same few addresses (9.6 M rows into 35 groups: 1.25 ms). When the table is small (sh_cap slots x aggregates <= GEN_SH_ENTRIES: 48 KB) and
+// every aggregate is an integer SUM / AVG / COUNT, a CTA adds its rows into a shared-memory mirror of the table's states instead and
+// flushes each touched state with one global atomic when it retires. Integer addition commutes: the result is bit-identical.
+constexpr int GEN_SH_ENTRIES = 2048;
+
 __global__ void __launch_bounds__(256) k_scan_agg_generic(const __grid_constant__ DProg prog, const TableView tv, const int64_t base,
                                                            const int64_t n, const int64_t bit_base, const uint32_t* __restrict__ defer_in,
-                                                           uint32_t* __restrict__ defer_out, Counters* __restrict__ ctr) {
+                                                           uint32_t* __restrict__ defer_out, Counters* __restrict__ ctr, const int sh_cap) {
     const DProg& p = prog;
     Val v[MAX_NODES];
     LocalAcc acc[MAX_AGGS];
     const bool no_keys = p.n_keys == 0;
+    extern __shared__ unsigned long long sh_acc[]; // {lo, hi, n} per (slot, aggregate); sh_cap * n_aggs * 24 bytes, none when sh_cap == 0
+    if (sh_cap) {
+        for (int i = threadIdx.x; i < sh_cap * p.n_aggs * 3; i += blockDim.x) sh_acc[i] = 0;
+        __syncthreads();
+    }
     if (no_keys)
         for (int a = 0; a < p.n_aggs; a++) acc[a] = LocalAcc{0, 0, 0};
     unsigned long long selected = 0, deferred = 0, too_long = 0, inserted = 0;
@@ -170,10 +181,32 @@ __global__ void __launch_bounds__(256) k_scan_agg_generic(const __grid_constant_
             deferred++;
             continue;
         }
+        if (sh_cap) {
+            const uint32_t idx = (uint32_t)(slot - tv.slots) / (uint32_t)p.slot_bytes;
+            for (int a = 0; a < p.n_aggs; a++) {
+                LocalAcc d{0, 0, 0};
+                update_agg_local(p, p.aggs[a], d, v, row);
+                unsigned long long* e = sh_acc + (idx * p.n_aggs + a) * 3;
+                if (d.lo | d.hi) { // 128-bit add as two 64-bit atomics: the carry out of the low word travels with the high word's addend
+                    const unsigned long long old = atomicAdd(e, (unsigned long long)d.lo);
+                    const unsigned long long up = d.hi + ((old + d.lo) < old ? 1ULL : 0ULL);
+                    if (up) atomicAdd(e + 1, up);
+                }
+                if (d.n) atomicAdd(e + 2, (unsigned long long)d.n);
+            }
+            continue;
+        }
         for (int a = 0; a < p.n_aggs; a++) update_agg_global(p, p.aggs[a], slot, v, row);
     }
     if (no_keys)
         for (int a = 0; a < p.n_aggs; a++) flush_local(p.aggs[a], acc[a], tv.slots);
+    if (sh_cap) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < sh_cap * p.n_aggs; i += blockDim.x) {
+            const LocalAcc s{sh_acc[i * 3], sh_acc[i * 3 + 1], sh_acc[i * 3 + 2]};
+            flush_local(p.aggs[i % p.n_aggs], s, tv.slots + (size_t)(i / p.n_aggs) * p.slot_bytes); // a state no row touched has n == 0
+        }
+    }
     // one atomic per warp for the counters
     for (int o = 16; o > 0; o >>= 1) {
         selected += __shfl_down_sync(0xffffffffu, selected, o);
@@ -533,60 +566,51 @@ struct RfArgs {
     const uint8_t* data; // key column, already offset to the first row of the range
     const uint8_t* nulls;
 };
-template <int W, bool FULL, class KT>
+// Partly selected tiles: the threads walk the list of selected row numbers four entries at a time — key loads together, bucket
+// loads together, tests — and clear the bit of every row that fails. Entries past the end of the list repeat row 0 of the tile
+// (always a valid address) and are ignored at the end, so that no load sits behind a predicate.
+template <int W, bool MIX, bool NULLS, class KT>
 SRB_D void rf_test_list(const RfArgs& a, const uint32_t* __restrict__ dir, const KT* __restrict__ keys, const uint8_t* __restrict__ nulls, uint32_t total,
-                        const uint16_t* sidx, uint32_t* smask, int lane) {
+                        const uint16_t* sidx, uint32_t* smask) {
+    constexpr long long KMIN = (long long)std::numeric_limits<KT>::min(), KMAX = (long long)std::numeric_limits<KT>::max();
+    const long long lo64 = a.v.min > KMIN ? a.v.min : KMIN, hi64 = a.v.max < KMAX ? a.v.max : KMAX;
+    const bool empty = lo64 > hi64;
+    const KT lo = empty ? (KT)1 : (KT)lo64, hi = empty ? (KT)0 : (KT)hi64;
+    const uint32_t dmask = a.v.directory_mask;
+    const int lnb = a.v.log_num_buckets;
+    const bool null_pass = a.v.has_null != 0;
+#pragma unroll 1
     for (uint32_t j0 = 0; j0 < total; j0 += 256 * 4) {
         uint32_t r[4];
-        bool act[4], test[4];
-        long long x[4];
+        KT x[4];
+        uint8_t nl[4] = {};
         uint64_t h[4];
         RfBucket b[4];
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             const uint32_t j = j0 + u * 256 + threadIdx.x;
-            act[u] = j < total;
-            r[u] = FULL ? j : (act[u] ? sidx[j] : 0);
+            r[u] = j < total ? (uint32_t)sidx[j] : 0xFFFFFFFFu;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) x[u] = keys[r[u] == 0xFFFFFFFFu ? 0u : r[u]];
+        if constexpr (NULLS) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) nl[u] = nulls[r[u] == 0xFFFFFFFFu ? 0u : r[u]];
         }
 #pragma unroll
         for (int u = 0; u < 4; u++) {
-            x[u] = 0;
-            test[u] = act[u];
-            if (act[u]) {
-                x[u] = (long long)keys[r[u]];
-                if (nulls && nulls[r[u]]) { // NULL keys pass iff the build side inserted a NULL
-                    test[u] = false;
-                    act[u] = a.v.has_null == 0; // act now means "clear the bit"
-                } else {
-                    act[u] = false;
-                }
-            }
+            h[u] = MIX ? phmap_mix8((uint64_t)(long long)x[u], 1) : (uint64_t)(long long)x[u];
+            b[u] = ld_bucket(dir + (size_t)((uint32_t)h[u] & dmask) * 8);
         }
 #pragma unroll
         for (int u = 0; u < 4; u++) {
-            if (test[u] && (x[u] < a.v.min || x[u] > a.v.max)) {
-                test[u] = false;
-                act[u] = true;
-            }
-            h[u] = rf_hash(x[u], a.v.mix);
-            b[u] = RfBucket{};
-            if (test[u]) b[u] = ld_bucket(dir + (size_t)((uint32_t)h[u] & a.v.directory_mask) * 8);
-        }
+            const uint32_t key = (uint32_t)(h[u] >> lnb);
+            uint32_t miss = 0;
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-            if (test[u]) {
-                const uint32_t key = (uint32_t)(h[u] >> a.v.log_num_buckets);
-                uint32_t miss = 0;
-#pragma unroll
-                for (int i = 0; i < 8; i++) miss |= ~b[u].w[i] & rf_word_mask(key, i);
-                act[u] = miss != 0;
-            }
-            if (FULL) { // a warp's 32 entries are exactly one mask word: the ballot of the survivors is the new word
-                const uint32_t w = __ballot_sync(0xffffffffu, !act[u]);
-                if (lane == 0) smask[r[u] >> 5] = w;
-            } else if (act[u]) {
-                atomicAnd(&smask[r[u] >> 5], ~(1u << (r[u] & 31)));
-            }
+            for (int i = 0; i < 8; i++) miss |= ~b[u].w[i] & rf_word_mask(key, i);
+            bool pass = miss == 0 && x[u] >= lo && x[u] <= hi;
+            if constexpr (NULLS) pass = nl[u] ? null_pass : pass;
+            if (!pass && r[u] != 0xFFFFFFFFu) atomicAnd(&smask[r[u] >> 5], ~(1u << (r[u] & 31)));
         }
     }
 }
@@ -688,8 +712,13 @@ __global__ void __launch_bounds__(256, 4) k_filter_rf(const __grid_constant__ Rf
             if (nulls) rf_test_full<W, false, true, KT>(a, dir, keys, nulls, smask, lane);
             else rf_test_full<W, false, false, KT>(a, dir, keys, nulls, smask, lane);
         }
-    } else
-        rf_test_list<W, false, KT>(a, dir, keys, nulls, total, sidx, smask, lane);
+    } else if (a.v.mix) {
+        if (nulls) rf_test_list<W, true, true, KT>(a, dir, keys, nulls, total, sidx, smask);
+        else rf_test_list<W, true, false, KT>(a, dir, keys, nulls, total, sidx, smask);
+    } else {
+        if (nulls) rf_test_list<W, false, true, KT>(a, dir, keys, nulls, total, sidx, smask);
+        else rf_test_list<W, false, false, KT>(a, dir, keys, nulls, total, sidx, smask);
+    }
     __syncthreads();
     const uint32_t now = smask[threadIdx.x];
     if (now != word) mask[w0 + threadIdx.x] = now;
@@ -1145,7 +1174,7 @@ private:
         if (P.n_keys == 0) {
             cap_ = 1;
         } else {
-            uint64_t want = 1024;
+            uint64_t want = plan_.group_hint > 0 ? 64 : 1024; // a hinted small table stays small enough for the interpreter's shared mirror
             if (plan_.group_hint > 0) {
                 uint64_t h = (uint64_t)plan_.group_hint * 2;
                 while (want < h) want <<= 1;
@@ -1218,6 +1247,17 @@ private:
             launch_batch(cols, off, m);
             check_batch(cols, off, m);
         }
+    }
+
+    // the interpreter's shared-memory mirror of a small table (see k_scan_agg_generic): integer SUM / AVG / COUNT states only
+    int generic_shared_cap() const {
+        const DProg& P = L_.prog;
+        if (!P.n_keys || no_shared_agg_ || cap_ * (uint64_t)P.n_aggs > (uint64_t)GEN_SH_ENTRIES) return 0;
+        for (int a = 0; a < P.n_aggs; a++) {
+            const DAgg& g = P.aggs[a];
+            if ((g.fn != FN_SUM && g.fn != FN_AVG && g.fn != FN_COUNT) || g.is_double || g.avg_as_double) return 0;
+        }
+        return (int)cap_;
     }
 
     void bind_prog(const ColBind* cols) {
@@ -1357,7 +1397,9 @@ private:
             }
         }
         if (covered < n) {
-            k_scan_agg_generic<<<grid_for(n - covered), 256, 0, stream>>>(L_.prog, tv, off + covered, n - covered, covered, defer_in, dout, dc);
+            const int sh_cap = generic_shared_cap();
+            k_scan_agg_generic<<<grid_for(n - covered), 256, (size_t)sh_cap * L_.prog.n_aggs * 24, stream>>>(L_.prog, tv, off + covered, n - covered, covered,
+                                                                                                              defer_in, dout, dc, sh_cap);
             launches++;
         }
         SRB_CUDA(cudaEventRecord(ev1_, stream));
@@ -1816,6 +1858,7 @@ private:
     bool lowered_ = false, filter_only_ = false;
     int shape_ = -1;
     bool force_generic_ = getenv("SRB_FORCE_GENERIC") != nullptr; // test hook: compare the two kernel families
+    bool no_shared_agg_ = getenv("SRB_NO_SHARED_AGG") != nullptr; // test / measurement hook: the interpreter updates the table per row
     bool no_partition_ = getenv("SRB_NO_PARTITION") != nullptr;   // test / measurement hook: direct table updates for every batch
     DevBuf hc_k_, hc_v_, hc_v2_, hc_ctr_;                                 // permuted (key, value) copy of the current batch + its 2 x 256 counters
     ColBind hc_cols_[MAX_COLS], nn_cols_[MAX_COLS];

@@ -279,6 +279,32 @@ def test_integer_arithmetic_wraps(ctx, oracle):
     check(ctx, oracle, plan, ch)
 
 
+def test_low_cardinality_group_by_through_the_interpreter_shared_states(ctx, oracle, monkeypatch):
+    """a few groups through the interpreter: rows are added into the CTA's shared-memory mirror of the table's states and flushed
+    once per CTA — carries out of the low 64 bits (DECIMAL128 sums of large positive and negative values), AVG, COUNT of a nullable
+    column and a BIGINT sum that wraps; the same rows through per-row table atomics (SRB_NO_SHARED_AGG) give the same result"""
+    rng = np.random.default_rng(77)
+    n = 300_000
+    big = rng.integers(-(1 << 62), 1 << 62, n).astype(np.int64)
+    big[::2] = np.abs(big[::2]) | (1 << 62)  # every other row adds ~2^62: the low word carries every few rows
+    nulls = (rng.random(n) < 0.1).astype(np.uint8)
+    ch = K.Chunk(n, {0: K.Column.from_ints(K.TYPE_INT, rng.integers(0, 7, n).astype(np.int32)),
+                     1: K.Column.from_ints(K.TYPE_INT, rng.integers(0, 5, n).astype(np.int32)),
+                     2: K.Column.from_ints(K.TYPE_DECIMAL64, big, None, 18, 2),
+                     3: K.Column.from_ints(K.TYPE_BIGINT, big, nulls),
+                     4: K.Column.from_ints(K.TYPE_INT, rng.integers(-1000, 1000, n).astype(np.int32))})
+    e = ExprBuilder()
+    k0, k1 = e.slot(0, K.TYPE_INT), e.slot(1, K.TYPE_INT)
+    d, b, i = e.slot(2, K.TYPE_DECIMAL64, 18, 2), e.slot(3, K.TYPE_BIGINT), e.slot(4, K.TYPE_INT)
+    plan = ScanAggPlan(exprs=e, keys=[k0, k1], aggs=[(K.AGG_SUM, d), (K.AGG_AVG, d), (K.AGG_SUM, b), (K.AGG_COUNT, b), (K.AGG_COUNT, None),
+                                                      (K.AGG_SUM, e.sub(e.cast(i, K.TYPE_BIGINT), b, K.TYPE_BIGINT))], group_hint=64)
+    got = K.chunk_rows(check(ctx, oracle, plan, ch))
+    assert len(got) == 35
+    monkeypatch.setenv("SRB_NO_SHARED_AGG", "1")
+    assert K.chunk_rows(run_gpu(ctx, plan, ch)) == got
+    monkeypatch.delenv("SRB_NO_SHARED_AGG")
+
+
 @pytest.mark.parametrize("keys", [[K.TYPE_INT], [K.TYPE_BIGINT], [K.TYPE_DATE], [K.TYPE_TINYINT, K.TYPE_SMALLINT], [K.TYPE_INT, K.TYPE_INT],
                                   [K.TYPE_INT, K.TYPE_DATE, K.TYPE_INT], [K.TYPE_DECIMAL128], [K.TYPE_BIGINT, K.TYPE_INT]])
 @pytest.mark.parametrize("null_frac", [0.0, 0.2])
