@@ -184,6 +184,20 @@ def _rand_col(rng, type_, n, null_frac=0.0, small=False, p=0, s=0):
     return K.Column.from_ints(type_, vals, nulls, p, s)
 
 
+@pytest.mark.parametrize("type_", [K.TYPE_TINYINT, K.TYPE_SMALLINT, K.TYPE_INT, K.TYPE_BIGINT, K.TYPE_DATE])
+def test_reference_predicate_and_filter_vectors(ctx, type_):
+    """the reference's own known answers (be/test/storage/column_predicate_test.cpp test_gt/ge/lt/le/is_null/not_null over the nullable
+    column {1, 2, 3, NULL, 4}; be/test/column/fixed_length_column_test.cpp:58-74, 130-163 filter vectors) through the CUDA filter path,
+    host and device chunks"""
+    from tests.test_oracle_golden import PREDICATE_VECTORS, predicate_vector_chunk, selection_of, check_filter_vectors
+    for device in (False, True):
+        for op, want in PREDICATE_VECTORS:
+            got = run_gpu(ctx, Q.filter_plan([pred(0, op, type_, 3)], [1]), predicate_vector_chunk(type_), device=device)
+            assert selection_of(got, 5) == want, (op, device)
+        if type_ == K.TYPE_INT:
+            check_filter_vectors(lambda plan, ch: run_gpu(ctx, plan, ch, device=device))
+
+
 @pytest.mark.parametrize("type_", [K.TYPE_TINYINT, K.TYPE_SMALLINT, K.TYPE_INT, K.TYPE_BIGINT, K.TYPE_DATE, K.TYPE_DECIMAL32,
                                    K.TYPE_DECIMAL64, K.TYPE_DECIMAL128, K.TYPE_DOUBLE])
 def test_predicates_all_ops(ctx, oracle, type_):

@@ -389,3 +389,62 @@ def test_runtime_filter_with_the_mixing_hash(oracle):
     finally:
         rf.close()
         plain.close()
+
+
+# ---- be/test/storage/column_predicate_test.cpp (test_gt :1033, test_ge :1157, test_lt :1281, test_le :1405, test_is_null :1977,
+#      test_not_null :2038): nullable INT column {1, 2, 3, NULL, 4}, literal "3"; evaluate() writes these selection bytes ----------
+PREDICATE_VECTORS = [(K.PRED_GT, "0,0,0,0,1"), (K.PRED_GE, "0,0,1,0,1"), (K.PRED_LT, "1,1,0,0,0"), (K.PRED_LE, "1,1,1,0,0"),
+                     (K.PRED_IS_NULL, "0,0,0,1,0"), (K.PRED_NOT_NULL, "1,1,1,0,1"),
+                     # test_eq / test_ne's INT blocks use the same column shape; a NULL never compares equal or unequal
+                     (K.PRED_EQ, "0,0,1,0,0"), (K.PRED_NE, "1,1,0,0,1")]
+
+
+def predicate_vector_chunk(type_=K.TYPE_INT):
+    nulls = np.array([0, 0, 0, 1, 0], np.uint8)
+    return K.Chunk(5, {0: K.Column.from_ints(type_, [1, 2, 3, 0, 4], nulls), 1: K.Column.from_ints(K.TYPE_INT, np.arange(5, dtype=np.int32))})
+
+
+def selection_of(kept_chunk, n):
+    sel = ["0"] * n
+    for r in K.column_pyvalues(kept_chunk.columns[1]):
+        sel[r] = "1"
+    return ",".join(sel)
+
+
+@pytest.mark.parametrize("op,want", PREDICATE_VECTORS)
+@pytest.mark.parametrize("type_", [K.TYPE_TINYINT, K.TYPE_SMALLINT, K.TYPE_INT, K.TYPE_BIGINT, K.TYPE_DATE])
+def test_column_predicate_known_answers(oracle, op, want, type_):
+    from starrocks_b200 import queries as Q
+    got = oracle.scan_agg(Q.filter_plan([pred(0, op, type_, 3)], [1]), predicate_vector_chunk(type_))
+    assert selection_of(got, 5) == want
+
+
+def test_conjunction_is_evaluate_and(oracle):
+    # column_predicate_test.cpp:1060-1075: evaluate_and on an all-ones selection equals evaluate; two predicates AND their selections
+    from starrocks_b200 import queries as Q
+    got = oracle.scan_agg(Q.filter_plan([pred(0, K.PRED_GE, K.TYPE_INT, 2), pred(0, K.PRED_LE, K.TYPE_INT, 3)], [1]), predicate_vector_chunk())
+    assert selection_of(got, 5) == "0,1,1,0,0"
+
+
+# ---- be/test/column/fixed_length_column_test.cpp:58-74 (filter i % 2 over 0..99 keeps 2k+1) and :130-163 (nullable column, NULL
+#      where i % 3 != 0, filter keeps rows 50..99: row j is NULL iff (j + 50) % 3 != 0, else j + 50) ------------------------------
+def filter_vector_chunks():
+    v = np.arange(100, dtype=np.int32)
+    plain = K.Chunk(100, {0: K.Column.from_ints(K.TYPE_INT, v), 1: K.Column.from_ints(K.TYPE_TINYINT, (v % 2).astype(np.int8))})
+    nulls = (v % 3 != 0).astype(np.uint8)
+    nullable = K.Chunk(100, {0: K.Column.from_ints(K.TYPE_INT, np.where(nulls, 0, v).astype(np.int32), nulls), 1: K.Column.from_ints(K.TYPE_INT, v)})
+    return plain, nullable
+
+
+def check_filter_vectors(run):
+    from starrocks_b200 import queries as Q
+    plain, nullable = filter_vector_chunks()
+    got = run(Q.filter_plan([pred(1, K.PRED_EQ, K.TYPE_TINYINT, 1)], [0]), plain)
+    assert got.n_rows == 50 and K.column_pyvalues(got.columns[0]) == [2 * k + 1 for k in range(50)]
+    got = run(Q.filter_plan([pred(1, K.PRED_GE, K.TYPE_INT, 50)], [0]), nullable)
+    assert got.n_rows == 50
+    assert K.column_pyvalues(got.columns[0]) == [None if (j + 50) % 3 else j + 50 for j in range(50)]
+
+
+def test_column_filter_known_answers(oracle):
+    check_filter_vectors(lambda plan, ch: oracle.scan_agg(plan, ch))
