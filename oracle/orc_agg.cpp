@@ -316,4 +316,156 @@ Result* run_scan_agg(const srb_scan_agg_plan* plan, const srb_chunk* in, int n_t
     return r;
 }
 
+// ---- streaming pre-aggregation sink ---------------------------------------------------------------------------
+// AggregateStreamingSinkOperator::push_chunk (pipeline/aggregate/aggregate_streaming_sink_operator.cpp:73-98) dispatches on
+// TStreamingPreaggregationMode (gensrc/thrift/PlanNodes.thrift:689-694): FORCE_STREAMING passes every row through in
+// intermediate format (:93-103), FORCE_PREAGGREGATION aggregates every row (:105-122), AUTO runs the AggrAutoState machine
+// (:147-307) over AggrAutoContext's constants (exec/aggregator.h:172-193). The output is the pass-through rows in arrival order
+// with the table's groups interleaved at their creation positions; phase 2 merges both kinds alike, so the final result does not
+// depend on the mode or on which rows were passed through.
+namespace {
+struct AutoContext { // exec/aggregator.h:172-193, aggregator.cpp:104-118
+    static constexpr size_t ContinuousUpperLimit = 10000;
+    static constexpr int ForcePreaggLimit = 3, PreaggLimit = 100, StableLimit = 5;
+    static constexpr double LowReduction = 0.2, HighReduction = 0.9;
+    static constexpr size_t MaxHtSize = 64 * 1024 * 1024;
+    size_t init_preagg_count = 0, adjust_count = 0, pass_through_count = 0, preagg_count = 0, selective_preagg_count = 0;
+    size_t continuous_limit = 100;
+    void update_continuous_limit() { continuous_limit = continuous_limit * 2 > ContinuousUpperLimit ? ContinuousUpperLimit : continuous_limit * 2; }
+    static bool is_high_reduction(size_t agg_count, size_t chunk_size) { return agg_count >= HighReduction * chunk_size; }
+    static bool is_low_reduction(size_t agg_count, size_t chunk_size) { return agg_count <= LowReduction * chunk_size; }
+};
+enum AutoState { INIT_PREAGG = 0, ADJUST, PASS_THROUGH, FORCE_PREAGG, PREAGG, SELECTIVE_PREAGG };
+
+// Aggregator::should_expand_preagg_hash_tables (aggregator.cpp:770-802) with STREAMING_HT_MIN_REDUCTION (aggregator.h:200-204)
+bool should_expand_preagg_hash_tables(size_t prev_row_returned, size_t input_chunk_size, int64_t ht_mem, int64_t ht_rows, int64_t num_rows_returned) {
+    static const struct {
+        int64_t min_ht_mem;
+        double min_reduction;
+    } table[] = {{0, 0.0}, {256 * 1024, 1.1}, {2 * 1024 * 1024, 2.0}};
+    if (ht_rows == 0) return true;
+    int level = 0;
+    while (level + 1 < 3 && ht_mem >= table[level + 1].min_ht_mem) level++;
+    const int64_t input_rows = (int64_t)prev_row_returned - (int64_t)input_chunk_size;
+    const int64_t aggregated_input_rows = input_rows - num_rows_returned;
+    const double current_reduction = (double)aggregated_input_rows / (double)ht_rows;
+    if (aggregated_input_rows <= 0) return true;
+    return current_reduction > table[level].min_reduction;
+}
+} // namespace
+
+Result* run_scan_agg_streaming(const srb_scan_agg_plan* plan, const srb_chunk* in, int chunk_size, int mode, int64_t* stats) {
+    if (plan->n_keys == 0 || plan->phase != SRB_AGG_UPDATE_SERIALIZE)
+        throw std::runtime_error("streaming pre-aggregation needs GROUP BY keys and the update+serialize phase");
+    auto* r = new Result();
+    Aggregator ag(plan);
+    AutoContext ac;
+    AutoState st = INIT_PREAGG;
+    int64_t n_by_state[6] = {0, 0, 0, 0, 0, 0};
+    // bytes of the hash table as hash_map_variant().allocated_memory_usage() would see them: slots x (key record + states)
+    auto allocated_bytes = [&]() { return (size_t)ag.table.slots.size() * (size_t)(16 + 24 * plan->n_aggs); };
+    const int64_t n_chunks = (in->n_rows + chunk_size - 1) / chunk_size;
+    for (int64_t c = 0; c < n_chunks; c++) {
+        const int64_t base = c * chunk_size;
+        const size_t rows = (size_t)std::min<int64_t>(chunk_size, in->n_rows - base);
+        if (mode == 1) { // FORCE_STREAMING
+            ag.push_rows(*in, base, rows, ROWS_STREAM);
+            continue;
+        }
+        if (mode == 2) { // FORCE_PREAGGREGATION
+            ag.push_rows(*in, base, rows, ROWS_AGGREGATE);
+            continue;
+        }
+        // AUTO (and LIMITED_MEM below its limit): _push_chunk_by_auto
+        const size_t mem = allocated_bytes();
+        const size_t continuous_limit = ac.continuous_limit;
+        n_by_state[st]++;
+        switch (st) {
+        case INIT_PREAGG: {
+            const bool needs_expansion = ag.table.need_expand(rows);
+            ac.init_preagg_count++;
+            if (!needs_expansion || should_expand_preagg_hash_tables((size_t)ag.rows_in + rows, rows, (int64_t)mem, (int64_t)ag.table.n_indexed, ag.rows_streamed)) {
+                ag.push_rows(*in, base, rows, ROWS_AGGREGATE);
+                break;
+            }
+            st = ADJUST;
+            ac.adjust_count = 0;
+        }
+            [[fallthrough]];
+        case ADJUST: {
+            ac.adjust_count++;
+            // the reference first looks every key up (build_hash_map_with_selection), then picks how the whole chunk is handled by
+            // the hit count; the lookup here is a dry run of the same table
+            size_t hit_count = ag.count_hits(*in, base, rows);
+            if (ac.adjust_count < continuous_limit && AutoContext::is_low_reduction(hit_count, rows)) {
+                ag.push_rows(*in, base, rows, ROWS_STREAM);
+                ac.pass_through_count++;
+                ac.preagg_count = 0;
+                ac.selective_preagg_count = 0;
+                if (ac.pass_through_count == (size_t)AutoContext::StableLimit) st = PASS_THROUGH;
+            } else if (ac.adjust_count < continuous_limit && AutoContext::is_high_reduction(hit_count, rows) && mem < AutoContext::MaxHtSize) {
+                ag.push_rows(*in, base, rows, ROWS_AGGREGATE);
+                ac.preagg_count++;
+                ac.pass_through_count = 0;
+                ac.selective_preagg_count = 0;
+                if (ac.preagg_count == (size_t)AutoContext::StableLimit) {
+                    st = PREAGG;
+                    ac.preagg_count = 0;
+                }
+            } else {
+                ag.push_rows(*in, base, rows, ROWS_SELECTIVE);
+                ac.selective_preagg_count++;
+                ac.pass_through_count = 0;
+                ac.preagg_count = 0;
+                if (ac.selective_preagg_count == (size_t)AutoContext::StableLimit) st = SELECTIVE_PREAGG;
+            }
+            break;
+        }
+        case PASS_THROUGH: {
+            ag.push_rows(*in, base, rows, ROWS_STREAM);
+            ac.pass_through_count++;
+            if (ac.pass_through_count > continuous_limit) {
+                st = mem < AutoContext::MaxHtSize ? FORCE_PREAGG : ADJUST;
+                ac.pass_through_count = 0;
+                ac.preagg_count = 0;
+                ac.adjust_count = 0;
+                ac.update_continuous_limit();
+            }
+            break;
+        }
+        case FORCE_PREAGG:
+        case PREAGG: {
+            ag.push_rows(*in, base, rows, ROWS_AGGREGATE);
+            ac.preagg_count++;
+            const size_t limit = st == FORCE_PREAGG ? AutoContext::ForcePreaggLimit : AutoContext::PreaggLimit;
+            if (ac.preagg_count > limit) {
+                st = ADJUST;
+                ac.preagg_count = 0;
+                ac.adjust_count = 0;
+            }
+            break;
+        }
+        case SELECTIVE_PREAGG: {
+            ag.push_rows(*in, base, rows, ROWS_SELECTIVE);
+            ac.selective_preagg_count++;
+            if (ac.selective_preagg_count > continuous_limit) {
+                st = ADJUST;
+                ac.selective_preagg_count = 0;
+                ac.adjust_count = 0;
+                ac.update_continuous_limit();
+            }
+            break;
+        }
+        }
+    }
+    ag.emit(r);
+    if (stats) {
+        stats[0] = ag.rows_streamed;
+        stats[1] = (int64_t)ag.table.n_indexed;
+        for (int i = 0; i < 6; i++) stats[2 + i] = n_by_state[i];
+        stats[8] = (int64_t)st;
+    }
+    return r;
+}
+
 } // namespace orc

@@ -128,13 +128,17 @@ struct GroupTable {
     std::vector<int64_t> slots; // group index + 1
     std::vector<uint64_t> hashes;
     std::vector<std::string> keys;
+    std::vector<uint8_t> streamed; // 1: a pass-through row of the streaming sink (never findable), sized lazily
+    size_t n_indexed = 0;
     size_t mask = 0;
     int seed;
     explicit GroupTable(int seed_) : seed(seed_) { rehash(1024); }
+    bool is_streamed(size_t g) const { return g < streamed.size() && streamed[g]; }
     void rehash(size_t cap) {
         slots.assign(cap, 0);
         mask = cap - 1;
         for (size_t g = 0; g < keys.size(); g++) {
+            if (is_streamed(g)) continue;
             size_t p = hashes[g] & mask;
             while (slots[p]) p = (p + 1) & mask;
             slots[p] = (int64_t)g + 1;
@@ -177,10 +181,42 @@ struct GroupTable {
         hashes.push_back(h);
         slots[p] = (int64_t)g + 1;
         *created = true;
-        if (keys.size() * 2 > slots.size()) rehash(slots.size() * 2);
+        n_indexed++;
+        if (n_indexed * 2 > slots.size()) rehash(slots.size() * 2);
         return g;
     }
+    // streaming sink: lookup without insertion (build_hash_map_with_selection, agg_hash_map.h:298-339: not-found rows are selected
+    // for pass-through); returns false when absent
+    bool find(const std::string& k, size_t* g_out) const {
+        uint64_t h = hash_key(k);
+        size_t p = h & mask;
+        while (slots[p]) {
+            size_t g = (size_t)slots[p] - 1;
+            if (hashes[g] == h && keys[g] == k) {
+                *g_out = g;
+                return true;
+            }
+            p = (p + 1) & mask;
+        }
+        return false;
+    }
+    // a pass-through row: gets a state block of its own and an output position, never enters the hash slots
+    size_t append_streamed(const std::string& k) {
+        size_t g = keys.size();
+        keys.push_back(k);
+        hashes.push_back(0);
+        streamed.resize(g + 1, 0);
+        streamed[g] = 1;
+        return g;
+    }
+    // hash_map_variant().need_expand(n): inserting n new keys would grow the table
+    bool need_expand(size_t n) const { return (n_indexed + n) * 2 > slots.size(); }
 };
+
+// how a chunk's rows meet the table (AggregateStreamingSinkOperator::_push_chunk_by_*): every row aggregated with insertion
+// (force_preaggregation), every row passed through in intermediate format (force_streaming), or found rows aggregated and the
+// others passed through (selective_preaggregation)
+enum RowMode { ROWS_AGGREGATE = 0, ROWS_STREAM = 1, ROWS_SELECTIVE = 2 };
 
 struct Aggregator {
     const srb_scan_agg_plan* plan;
@@ -247,7 +283,51 @@ struct Aggregator {
     static bool avg_double(int t) { return !(is_decimal(t) || t == SRB_TYPE_DATE || t == SRB_TYPE_LARGEINT); }
 
     // one <=chunk_size slice of raw rows: predicates -> selection -> exprs -> table -> states
-    void push_rows(const srb_chunk& ch, int64_t base, size_t rows) {
+    void serialize_key(const std::vector<const Col*>& keys, size_t i, std::string& kb) const {
+        kb.clear();
+        for (int k = 0; k < plan->n_keys; k++) {
+            const Col& c = *keys[k];
+            bool isnull = c.is_null(i);
+            if (key_meta[k].nullable) kb.push_back((char)isnull);
+            if (is_binary(c.type)) {
+                uint32_t len = isnull ? 0 : (uint32_t)c.s[i].size();
+                kb.append((const char*)&len, 4);
+                if (!isnull) kb.append(c.s[i]);
+            } else if (c.type == SRB_TYPE_DOUBLE) {
+                double x = isnull ? 0 : c.d[i];
+                kb.append((const char*)&x, 8);
+            } else {
+                int128_t x = isnull ? 0 : c.v[i];
+                kb.append((const char*)&x, type_width(c.type));
+            }
+        }
+    }
+
+    // build_hash_map_with_selection (aggregator.h, agg_hash_map.h:298-339) as a dry run: how many selected rows of the chunk
+    // already have their group in the table. Nothing is inserted or updated.
+    size_t count_hits(const srb_chunk& ch, int64_t base, size_t rows) {
+        std::vector<uint8_t> sel;
+        eval_predicates(plan->preds, plan->n_preds, ch, base, rows, sel);
+        std::vector<uint32_t> idx;
+        for (size_t i = 0; i < rows; i++)
+            if (sel[i]) idx.push_back((uint32_t)i);
+        if (idx.empty() || !key_meta_known) return 0;
+        ExprEval ev(plan->nodes, plan->n_nodes, &ch, base, &idx);
+        std::vector<const Col*> keys(plan->n_keys);
+        for (int k = 0; k < plan->n_keys; k++) keys[k] = &ev.eval(plan->key_nodes[k]);
+        std::string kb;
+        size_t hits = 0, g;
+        for (size_t i = 0; i < idx.size(); i++) {
+            serialize_key(keys, i, kb);
+            hits += table.find(kb, &g) ? 1 : 0;
+        }
+        return hits;
+    }
+
+    int64_t rows_streamed = 0;
+    // returns the number of rows whose group already existed (the streaming sink's hit count)
+    size_t push_rows(const srb_chunk& ch, int64_t base, size_t rows, RowMode mode = ROWS_AGGREGATE) {
+        size_t hits = 0;
         rows_in += (int64_t)rows;
         std::vector<uint8_t> sel;
         eval_predicates(plan->preds, plan->n_preds, ch, base, rows, sel);
@@ -256,7 +336,7 @@ struct Aggregator {
         for (size_t i = 0; i < rows; i++)
             if (sel[i]) idx.push_back((uint32_t)i);
         rows_selected += (int64_t)idx.size();
-        if (idx.empty()) return; // empty chunks are dropped by the driver (pipeline_driver.cpp:340-342)
+        if (idx.empty()) return 0; // empty chunks are dropped by the driver (pipeline_driver.cpp:340-342)
         ExprEval ev(plan->nodes, plan->n_nodes, &ch, base, &idx);
         size_t n = idx.size();
         std::vector<const Col*> keys(plan->n_keys), args(n_aggs, nullptr);
@@ -281,25 +361,18 @@ struct Aggregator {
         if (plan->n_keys > 0) {
             std::string kb;
             for (size_t i = 0; i < n; i++) {
-                kb.clear();
-                for (int k = 0; k < plan->n_keys; k++) {
-                    const Col& c = *keys[k];
-                    bool isnull = c.is_null(i);
-                    if (key_meta[k].nullable) kb.push_back((char)isnull);
-                    if (is_binary(c.type)) {
-                        uint32_t len = isnull ? 0 : (uint32_t)c.s[i].size();
-                        kb.append((const char*)&len, 4);
-                        if (!isnull) kb.append(c.s[i]);
-                    } else if (c.type == SRB_TYPE_DOUBLE) {
-                        double x = isnull ? 0 : c.d[i];
-                        kb.append((const char*)&x, 8);
-                    } else {
-                        int128_t x = isnull ? 0 : c.v[i];
-                        kb.append((const char*)&x, type_width(c.type));
-                    }
+                serialize_key(keys, i, kb);
+                bool created = false;
+                if (mode == ROWS_AGGREGATE) {
+                    gid[i] = table.emplace(kb, &created);
+                    hits += created ? 0 : 1;
+                } else if (mode == ROWS_SELECTIVE && table.find(kb, &gid[i])) {
+                    hits++;
+                } else { // convert_to_serialize_format (aggregate.h:337): the row's own one-row state, emitted as it stands
+                    gid[i] = table.append_streamed(kb);
+                    created = true;
+                    rows_streamed++;
                 }
-                bool created;
-                gid[i] = table.emplace(kb, &created);
                 if (created) states.resize(states.size() + n_aggs);
             }
         }
@@ -309,6 +382,7 @@ struct Aggregator {
             bool ad = args[a] ? avg_double(args[a]->type) : false;
             for (size_t i = 0; i < n; i++) update_one(fn, states[gid[i] * n_aggs + a], args[a], i, ad);
         }
+        return hits;
     }
 
     // merge another aggregator's groups (phase-2 merge_batch semantics: sums add, counts add, min/max combine;

@@ -6,6 +6,7 @@
 
 namespace orc {
 Result* run_scan_agg(const srb_scan_agg_plan* plan, const srb_chunk* in, int n_threads, int chunk_size);
+Result* run_scan_agg_streaming(const srb_scan_agg_plan* plan, const srb_chunk* in, int chunk_size, int mode, int64_t* stats);
 Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe);
 void join_build_raw(const void* keys, int width, uint32_t n, uint32_t* bucket_size, uint32_t* first, uint32_t* next);
 int pack_keys_raw(const srb_chunk* ch, const int32_t* slots, int n_keys, void* out16);
@@ -21,6 +22,16 @@ const char* orc_last_error() { return g_err.c_str(); }
 void* orc_scan_agg(const srb_scan_agg_plan* plan, const srb_chunk* in, int n_threads, int chunk_size) {
     try {
         return orc::run_scan_agg(plan, in, n_threads, chunk_size);
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return nullptr;
+    }
+}
+// streaming pre-aggregation sink; mode = TStreamingPreaggregationMode (0 AUTO, 1 FORCE_STREAMING, 2 FORCE_PREAGGREGATION);
+// stats[9]: rows passed through, groups in the table, chunks seen in each of the six AggrAutoState states, final state
+void* orc_scan_agg_streaming(const srb_scan_agg_plan* plan, const srb_chunk* in, int chunk_size, int mode, int64_t* stats) {
+    try {
+        return orc::run_scan_agg_streaming(plan, in, chunk_size, mode, stats);
     } catch (const std::exception& e) {
         g_err = e.what();
         return nullptr;

@@ -28,6 +28,8 @@ class Oracle:
         L.orc_last_error.restype = C.c_char_p
         L.orc_scan_agg.restype = C.c_void_p
         L.orc_scan_agg.argtypes = [C.POINTER(K.srb_scan_agg_plan), C.POINTER(K.srb_chunk), C.c_int, C.c_int]
+        L.orc_scan_agg_streaming.restype = C.c_void_p
+        L.orc_scan_agg_streaming.argtypes = [C.POINTER(K.srb_scan_agg_plan), C.POINTER(K.srb_chunk), C.c_int, C.c_int, C.POINTER(C.c_int64)]
         L.orc_join.restype = C.c_void_p
         L.orc_join.argtypes = [C.POINTER(K.srb_join_plan), C.POINTER(K.srb_chunk), C.POINTER(K.srb_chunk)]
         L.orc_result_chunk.restype = C.POINTER(K.srb_chunk)
@@ -93,6 +95,21 @@ class Oracle:
         finally:
             self.lib.orc_result_free(r)
         return (out, a.value, b.value) if with_counters else out
+
+    def scan_agg_streaming(self, plan, chunk: K.Chunk, mode: int, chunk_size: int = 4096):
+        """streaming pre-aggregation sink (TStreamingPreaggregationMode: 0 AUTO, 1 FORCE_STREAMING, 2 FORCE_PREAGGREGATION);
+        returns (intermediate chunk, stats dict)"""
+        cch, keep = chunk.to_c()
+        stats = (C.c_int64 * 9)()
+        r = self.lib.orc_scan_agg_streaming(C.byref(plan.c), C.byref(cch), chunk_size, mode, stats)
+        if not r:
+            raise RuntimeError("oracle: " + self._err())
+        try:
+            out = K.decode_chunk(self.lib.orc_result_chunk(r).contents)
+        finally:
+            self.lib.orc_result_free(r)
+        names = ["init_preagg", "adjust", "pass_through", "force_preagg", "preagg", "selective_preagg"]
+        return out, {"rows_streamed": stats[0], "groups": stats[1], "chunks": dict(zip(names, list(stats[2:8]))), "final_state": names[stats[8]]}
 
     def join(self, plan, build: K.Chunk, probe: K.Chunk):
         b, k1 = build.to_c()
