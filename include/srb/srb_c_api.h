@@ -271,6 +271,23 @@ srb_status srb_join_probe_pull_chunk(srb_op* op, srb_chunk* out);
 srb_status srb_join_probe_pull_all(srb_op* op, srb_chunk* out);
 srb_status srb_join_probe_pull_device(srb_op* op, srb_chunk* out);
 
+/* ---- streaming pre-aggregation ---------------------------------------------------------------------------------- */
+/* Streaming pre-aggregation: the first phase of a two-phase GROUP BY in front of an exchange
+ * (AggregateStreamingSinkOperator, be/src/exec/pipeline/aggregate/aggregate_streaming_sink_operator.cpp:73-307). `mode` is
+ * TStreamingPreaggregationMode (gensrc/thrift/PlanNodes.thrift:689-694): SRB_STREAMING_AUTO runs the AggrAutoState machine
+ * (aggregator.h:170-193) per pushed range, SRB_STREAMING_FORCE_STREAMING passes every row through in intermediate format
+ * (Aggregator::output_chunk_by_streaming), SRB_STREAMING_FORCE_PREAGGREGATION aggregates every row (= the blocking sink).
+ * Valid before the first push_chunk on an aggregate operator with GROUP BY keys in SRB_AGG_UPDATE_SERIALIZE; the output is the
+ * pass-through rows followed by the table's groups, all in the plan's intermediate schema, available after set_finishing.
+ * The result of phase 2 over that output does not depend on the mode. */
+#define SRB_STREAMING_AUTO 0
+#define SRB_STREAMING_FORCE_STREAMING 1
+#define SRB_STREAMING_FORCE_PREAGGREGATION 2
+srb_status srb_op_set_streaming_mode(srb_op* op, int32_t mode);
+/* rows passed through so far, groups held by the table, current AggrAutoState (0 INIT_PREAGG, 1 ADJUST, 2 PASS_THROUGH,
+ * 3 FORCE_PREAGG, 4 PREAGG, 5 SELECTIVE_PREAGG); any pointer may be NULL */
+srb_status srb_op_streaming_stats(srb_op* op, int64_t* rows_passed_through, int64_t* groups_in_table, int32_t* auto_state);
+
 /* ---- runtime filters: the join's build side narrows the probe side's scan ---------------------------------------
  * HashJoinBuildOperator::set_finishing creates partial runtime filters from the build keys (hash_join_build_operator.cpp:97-208,
  * hash_joiner.cpp:516-611): a RuntimeBloomFilter = SimdBlockFilter (exprs/runtime_filter.h:79-222, runtime_filter.cpp:26-35,114-123)

@@ -222,6 +222,20 @@ srb_status srb_op_add_runtime_filter(srb_op* op, const srb_runtime_filter* rf, i
     return SRB_OK;
     SRB_API_END
 }
+srb_status srb_op_set_streaming_mode(srb_op* op, int32_t mode) {
+    SRB_API_BEGIN
+    OP_GUARD(op)
+    op->set_streaming_mode(mode);
+    return SRB_OK;
+    SRB_API_END
+}
+srb_status srb_op_streaming_stats(srb_op* op, int64_t* rows_passed_through, int64_t* groups_in_table, int32_t* auto_state) {
+    SRB_API_BEGIN
+    OP_GUARD(op)
+    op->streaming_stats(rows_passed_through, groups_in_table, auto_state);
+    return SRB_OK;
+    SRB_API_END
+}
 srb_status srb_runtime_filter_info(const srb_runtime_filter* rf, int64_t* n_buckets, int64_t* min_value, int64_t* max_value, int32_t* has_null,
                                    int64_t* inserted) {
     SRB_API_BEGIN

@@ -266,6 +266,29 @@ SRB_D uint8_t* table_find_or_insert(const TableView& t, uint64_t klo, uint64_t k
     return nullptr;
 }
 
+// Lookup without insertion (the streaming sink's build_hash_map_with_selection, agg_hash_map.h:298-339): the slot of (klo,khi) or
+// nullptr when the key is absent (or further than TABLE_MAX_PROBE slots from home, where no insert would have put it).
+SRB_D uint8_t* table_find(const TableView& t, uint64_t klo, uint64_t khi, uint64_t hash) {
+    const uint64_t tagw = (hash & ~3ULL) | SLOT_READY;
+    uint64_t idx = (hash >> 7) & t.mask;
+    for (int probe = 0; probe < TABLE_MAX_PROBE; probe++) {
+        uint8_t* slot = t.slots + idx * (uint64_t)t.slot_bytes;
+        const ulonglong2 a = ld_pair(slot);
+        if (a.x == SLOT_EMPTY) return nullptr;
+        if (a.x == tagw && a.y == klo) {
+            if (t.key_words == 1) return slot;
+            ulonglong2 b = ld_pair(slot + 16);
+            while (b.y == 0) { // the claimer's second pair is in flight
+                __nanosleep(20);
+                b = ld_pair(slot + 16);
+            }
+            if (b.x == khi) return slot;
+        }
+        idx = (idx + 1) & t.mask;
+    }
+    return nullptr;
+}
+
 // ---- packed group key ----------------------------------------------------------------------------------
 // per key column: [null byte if nullable][value bytes | u32 len + bytes] (AggHashMapWithSerializedKey,
 // agg_hash_map.h:746-748; BinaryColumn::serialize, column/binary_column.h:228-237). Up to 16 bytes.

@@ -292,7 +292,7 @@ __global__ void k_pack_result(const __grid_constant__ PackArgs a, uint8_t* __res
 // of a 10^8-group emit).
 constexpr int EMIT_ROWS = 8;
 __global__ void __launch_bounds__(256) k_emit(const __grid_constant__ DProg prog, const uint8_t* __restrict__ slots, uint64_t cap,
-                                              const __grid_constant__ EmitArgs ea, Counters* __restrict__ ctr) {
+                                              const __grid_constant__ EmitArgs ea, Counters* __restrict__ ctr, const int64_t row_base) {
     const DProg& p = prog;
     const int sb = p.slot_bytes;
     __shared__ unsigned int warp_tot[8];
@@ -324,7 +324,7 @@ __global__ void __launch_bounds__(256) k_emit(const __grid_constant__ DProg prog
             block_base = t ? atomicAdd(&ctr->emitted, (unsigned long long)t) : 0ULL;
         }
         __syncthreads();
-        int64_t row = (int64_t)(block_base + warp_tot[wid] + (incl - mine));
+        int64_t row = row_base + (int64_t)(block_base + warp_tot[wid] + (incl - mine)); // row_base: pass-through rows of a streaming sink come first
 #pragma unroll
         for (int r = 0; r < EMIT_ROWS; r++)
             if (ready & (1u << r)) emit_row(p, slots + (c0 + (uint64_t)r * 256 + tid) * sb, ea, row++);
@@ -332,62 +332,126 @@ __global__ void __launch_bounds__(256) k_emit(const __grid_constant__ DProg prog
     }
 }
 
-SRB_D void emit_row(const DProg& p, const uint8_t* s, const EmitArgs& ea, int64_t row) {
-    {
-        if (p.n_keys) {
-            const uint64_t* k = (const uint64_t*)s;
-            ea.keys[row] = make_ulonglong2(k[1], p.key_words > 1 ? k[2] : 0ULL);
+// one aggregate of one output row from its state words; raw: MIN / MAX words are plain values (a pass-through row's own value),
+// not the table's biased encodings
+SRB_D void emit_agg(const DAgg& g, const EmitAgg& e, uint64_t n, uint64_t lo, uint64_t hi, int64_t row, bool raw) {
+    bool isnull = e.null != nullptr && n == 0;
+    if (e.null) e.null[row] = isnull ? 1 : 0;
+    if (e.cnt) e.cnt[row] = (int64_t)n;
+    if (isnull) {
+        store_w(e.val, row, e.out_width, 0, 0);
+        return;
+    }
+    switch (e.mode) {
+    case 0: store_w(e.val, row, 8, n, 0); break;
+    case 1:
+        if (e.decode && !raw) {
+            const bool mn = e.decode == 2;
+            if (g.is_double)
+                lo = dec_f64(lo, mn);
+            else if (g.wide) {
+                i128 x = dec_i128(((u128)hi << 64) | lo, mn);
+                lo = lo64(x);
+                hi = (uint64_t)hi64(x);
+            } else
+                lo = (uint64_t)dec_i64(lo, mn);
         }
-        for (int a = 0; a < p.n_aggs; a++) {
-            const DAgg& g = p.aggs[a];
-            const EmitAgg& e = ea.aggs[a];
-            uint64_t n = g.off_n >= 0 ? *(const uint64_t*)(s + g.off_n) : 1;
-            uint64_t lo = g.off_lo >= 0 ? *(const uint64_t*)(s + g.off_lo) : 0;
-            uint64_t hi = g.off_hi >= 0 ? *(const uint64_t*)(s + g.off_hi) : (uint64_t)((int64_t)lo >> 63);
-            bool isnull = e.null != nullptr && n == 0;
-            if (e.null) e.null[row] = isnull ? 1 : 0;
-            if (e.cnt) e.cnt[row] = (int64_t)n;
-            if (isnull) {
-                store_w(e.val, row, e.out_width, 0, 0);
+        store_w(e.val, row, e.out_width, lo, hi);
+        break;
+    case 2: {
+        i128 r = decimal_div_integer(make_i128(lo, (int64_t)hi), (i128)(int64_t)n, e.scale);
+        store_w(e.val, row, 16, lo64(r), (uint64_t)hi64(r));
+        break;
+    }
+    case 3: {
+        i128 r = make_i128(lo, (int64_t)hi) / (i128)(int64_t)n; // DATE avg: truncating (avg.h:231)
+        store_w(e.val, row, 4, lo64(r), 0);
+        break;
+    }
+    case 4: {
+        double r = (double)make_i128(lo, (int64_t)hi) / (double)(int64_t)n;
+        store_w(e.val, row, 8, (uint64_t)__double_as_longlong(r), 0);
+        break;
+    }
+    default: {
+        double r = __longlong_as_double((long long)lo) / (double)(int64_t)n;
+        store_w(e.val, row, 8, (uint64_t)__double_as_longlong(r), 0);
+    }
+    }
+}
+
+SRB_D void emit_row(const DProg& p, const uint8_t* s, const EmitArgs& ea, int64_t row) {
+    if (p.n_keys) {
+        const uint64_t* k = (const uint64_t*)s;
+        ea.keys[row] = make_ulonglong2(k[1], p.key_words > 1 ? k[2] : 0ULL);
+    }
+    for (int a = 0; a < p.n_aggs; a++) {
+        const DAgg& g = p.aggs[a];
+        const uint64_t n = g.off_n >= 0 ? *(const uint64_t*)(s + g.off_n) : 1;
+        const uint64_t lo = g.off_lo >= 0 ? *(const uint64_t*)(s + g.off_lo) : 0;
+        const uint64_t hi = g.off_hi >= 0 ? *(const uint64_t*)(s + g.off_hi) : (uint64_t)((int64_t)lo >> 63);
+        emit_agg(g, ea.aggs[a], n, lo, hi, row, false);
+    }
+}
+
+// Streaming pre-aggregation (AggregateStreamingSinkOperator, pipeline/aggregate/aggregate_streaming_sink_operator.cpp:93-145):
+// rows that are not aggregated leave in intermediate format, one output row each (Aggregator::output_chunk_by_streaming ->
+// AggregateFunction::convert_to_serialize_format, exprs/agg/aggregate.h:337): keys as they are, every aggregate the serialized
+// state of that single row. selective = 0: every selected row passes through (force_streaming); selective = 1: rows whose group
+// is already in the table update it in place and only the others pass through (selective_preaggregation; the lookup never
+// inserts). Output positions come from one atomic per warp step; the order of pass-through rows is not kept (phase 2 does not see it).
+__global__ void __launch_bounds__(256) k_stream_rows(const __grid_constant__ DProg prog, const TableView tv, const int64_t base, const int64_t n,
+                                                      const int selective, const __grid_constant__ EmitArgs ea, const int64_t row_base,
+                                                      Counters* __restrict__ ctr) {
+    const DProg& p = prog;
+    Val v[MAX_NODES];
+    unsigned long long selected = 0, too_long = 0, hits = 0;
+    const int lane = threadIdx.x & 31;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const int64_t row = base + i;
+        if (!eval_preds(p, row)) continue;
+        selected++;
+        for (int k = 0; k < p.n_nodes; k++) v[k] = eval_node(p.nodes[k], v, p.cols, row);
+        const PackedKey k = pack_key(p, v, row);
+        if (k.too_long) {
+            too_long++;
+            continue;
+        }
+        if (selective) {
+            uint8_t* slot = table_find(tv, k.lo, k.hi, hash_packed_key(k, p.phase_seed));
+            if (slot) {
+                for (int a = 0; a < p.n_aggs; a++) update_agg_global(p, p.aggs[a], slot, v, row);
+                hits++;
                 continue;
             }
-            switch (e.mode) {
-            case 0: store_w(e.val, row, 8, n, 0); break;
-            case 1:
-                if (e.decode) {
-                    const bool mn = e.decode == 2;
-                    if (g.is_double)
-                        lo = dec_f64(lo, mn);
-                    else if (g.wide) {
-                        i128 x = dec_i128(((u128)hi << 64) | lo, mn);
-                        lo = lo64(x);
-                        hi = (uint64_t)hi64(x);
-                    } else
-                        lo = (uint64_t)dec_i64(lo, mn);
-                }
-                store_w(e.val, row, e.out_width, lo, hi);
-                break;
-            case 2: {
-                i128 r = decimal_div_integer(make_i128(lo, (int64_t)hi), (i128)(int64_t)n, e.scale);
-                store_w(e.val, row, 16, lo64(r), (uint64_t)hi64(r));
-                break;
-            }
-            case 3: {
-                i128 r = make_i128(lo, (int64_t)hi) / (i128)(int64_t)n; // DATE avg: truncating (avg.h:231)
-                store_w(e.val, row, 4, lo64(r), 0);
-                break;
-            }
-            case 4: {
-                double r = (double)make_i128(lo, (int64_t)hi) / (double)(int64_t)n;
-                store_w(e.val, row, 8, (uint64_t)__double_as_longlong(r), 0);
-                break;
-            }
-            default: {
-                double r = __longlong_as_double((long long)lo) / (double)(int64_t)n;
-                store_w(e.val, row, 8, (uint64_t)__double_as_longlong(r), 0);
-            }
-            }
         }
+        // the lanes that arrive here together reserve their output rows with one atomic
+        const unsigned int m = __activemask();
+        const int leader = __ffs(m) - 1;
+        unsigned long long first = 0;
+        if (lane == leader) first = atomicAdd(&ctr->emitted, (unsigned long long)__popc(m));
+        first = __shfl_sync(m, first, leader);
+        const int64_t pos = row_base + (int64_t)first + __popc(m & ((1u << lane) - 1u));
+        ea.keys[pos] = make_ulonglong2(k.lo, p.key_words > 1 ? k.hi : 0ULL);
+        for (int a = 0; a < p.n_aggs; a++) {
+            const DAgg& g = p.aggs[a];
+            LocalAcc d{0, 0, 0};
+            update_agg_local(p, g, d, v, row); // the state of this one row
+            const uint64_t cnt = g.off_n >= 0 ? d.n : 1;
+            const uint64_t hi = g.off_hi >= 0 ? d.hi : (uint64_t)((int64_t)d.lo >> 63);
+            emit_agg(g, ea.aggs[a], cnt, d.lo, hi, pos, true);
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        selected += __shfl_down_sync(0xffffffffu, selected, o);
+        too_long += __shfl_down_sync(0xffffffffu, too_long, o);
+        hits += __shfl_down_sync(0xffffffffu, hits, o);
+    }
+    if (lane == 0) {
+        if (selected) atomicAdd(&ctr->rows_selected, selected);
+        if (too_long) atomicAdd(&ctr->key_too_long, too_long);
+        if (hits) atomicAdd(&ctr->inserted, hits); // this kernel never inserts: the field carries the hit count of the batch
     }
 }
 
@@ -1231,6 +1295,10 @@ private:
             filter_range(cols, n);
             return;
         }
+        if (stream_mode_ >= 0) {
+            stream_range(cols, n);
+            return;
+        }
         // The L2-blocked path wants the LARGEST batch memory allows: the table region that is live at any moment is
         // (rows in flight / rows per batch) x table bytes, so more rows per batch means a smaller, L2-resident window and
         // more updates per table sector while it is cached.
@@ -1325,6 +1393,176 @@ private:
         hc_cols_[kc].data = hc_k_.p;
         hc_cols_[vc].data = hc_v_.p;
         if (nv == 2) hc_cols_[vc2].data = hc_v2_.p;
+    }
+
+    // ---- streaming pre-aggregation sink ------------------------------------------------------------------------
+    // AggregateStreamingSinkOperator::push_chunk dispatches on TStreamingPreaggregationMode; one pushed range (at most AGG_BATCH
+    // rows) plays the part of one chunk in the reference's AggrAutoState machine. What the reference decides from a dry-run lookup
+    // of the chunk's keys (ADJUST: build_hash_map_with_selection, then one of three treatments of the whole chunk) is decided
+    // here from the hit count of the selective pass itself — found rows update their groups, the others pass through — so the
+    // decision costs no extra pass over the rows; the counters steer the following ranges exactly as the reference's do.
+    // Thresholds that stand for CPU cache sizes in the reference (STREAMING_HT_MIN_REDUCTION: 256 KB / 2 MB; MaxHtSize 64 MB) are
+    // restated for a B200: a table that fits the 126 MB L2 resolves its atomics there, a larger one pays HBM sectors per row.
+    enum AutoState { INIT_PREAGG = 0, ADJUST, PASS_THROUGH, FORCE_PREAGG, PREAGG, SELECTIVE_PREAGG };
+    struct AutoContext { // exec/aggregator.h:172-193
+        static constexpr size_t ContinuousUpperLimit = 10000;
+        static constexpr int ForcePreaggLimit = 3, PreaggLimit = 100, StableLimit = 5;
+        static constexpr double LowReduction = 0.2, HighReduction = 0.9;
+        static constexpr size_t MaxHtSize = (size_t)8 << 30;
+        size_t adjust_count = 0, pass_through_count = 0, preagg_count = 0, selective_preagg_count = 0, continuous_limit = 100;
+        void update_continuous_limit() { continuous_limit = continuous_limit * 2 > ContinuousUpperLimit ? ContinuousUpperLimit : continuous_limit * 2; }
+    };
+    enum RowMode { ROWS_AGGREGATE, ROWS_STREAM, ROWS_SELECTIVE };
+
+    void set_streaming_mode(int mode) override {
+        if (mode < SRB_STREAMING_AUTO || mode > SRB_STREAMING_FORCE_PREAGGREGATION) throw Error(SRB_INVALID_ARGUMENT, "unknown streaming pre-aggregation mode");
+        if (rows_in > 0 || finishing) throw Error(SRB_INVALID_ARGUMENT, "the streaming mode is set before the first push_chunk");
+        if (plan_.key_nodes.empty() || plan_.aggs.empty() || plan_.phase != SRB_AGG_UPDATE_SERIALIZE)
+            throw Error(SRB_INVALID_ARGUMENT, "streaming pre-aggregation needs GROUP BY keys and the update + serialize phase");
+        stream_mode_ = mode;
+    }
+    void streaming_stats(int64_t* rows_passed_through, int64_t* groups_in_table, int32_t* auto_state) override {
+        if (rows_passed_through) *rows_passed_through = stream_rows_;
+        if (groups_in_table) *groups_in_table = (int64_t)occupied_;
+        if (auto_state) *auto_state = (int32_t)auto_state_;
+    }
+
+    // Aggregator::should_expand_preagg_hash_tables (aggregator.cpp:770-802): keep growing the table only while the rows aggregated
+    // so far reduce by more than the factor its size asks for
+    bool should_expand_preagg_table(int64_t rows_before) const {
+        if (occupied_ == 0) return true;
+        const size_t mem = (size_t)cap_ * (size_t)L_.prog.slot_bytes;
+        // a table that still fits the L2 may always grow; up to ten times that it must reduce by 1.1, beyond by 2 (the reference's
+        // STREAMING_HT_MIN_REDUCTION steps at 256 KB and 2 MB are its CPU's L2 and L3 share)
+        const double min_reduction = mem < stream_l2_bytes_ ? 0.0 : (mem < stream_l2_bytes_ * 10 ? 1.1 : 2.0);
+        const int64_t aggregated = rows_before - stream_rows_;
+        if (aggregated <= 0) return true;
+        return (double)aggregated / (double)occupied_ > min_reduction;
+    }
+
+    // AUTO learns from the hit counts of successive units: 2^24 rows each (a few per cent of an SF100 table), so that a poor
+    // reduction is noticed after the first unit instead of after a whole 2^29-row batch. SRB_STREAM_UNIT: test hook.
+    void stream_range(const ColBind* cols, int64_t n) {
+        const int64_t unit = stream_mode_ == SRB_STREAMING_AUTO ? stream_unit_ : AGG_BATCH;
+        for (int64_t off = 0; off < n; off += unit) stream_batch(cols, off, std::min<int64_t>(unit, n - off));
+    }
+
+    // rows of the range that found their group already present (aggregate: selected - newly inserted; selective: counted by the kernel)
+    int64_t run_rows(const ColBind* cols, int64_t off, int64_t n, RowMode mode) {
+        if (mode == ROWS_AGGREGATE) {
+            const uint64_t sel0 = selected_total_, occ0 = occupied_;
+            launch_batch(cols, off, n);
+            check_batch(cols, off, n);
+            return (int64_t)(selected_total_ - sel0) - (int64_t)(occupied_ - occ0);
+        }
+        const DProg& P = L_.prog;
+        EmitArgs ea = emit_args((uint64_t)stream_rows_ + (uint64_t)n); // every row of the range may pass through
+        bind_prog(cols);
+        if (!ev0_) {
+            ev0_ = ctx->take_event(true);
+            ev1_ = ctx->take_event(true);
+            if (!ev0_ || !ev1_) throw Error(SRB_INTERNAL_ERROR, "cudaEventCreate failed");
+        }
+        SRB_CUDA(cudaMemsetAsync(ctr_dev_.p, 0, sizeof(Counters), stream));
+        SRB_CUDA(cudaEventRecord(ev0_, stream));
+        k_stream_rows<<<grid_for(n), 256, 0, stream>>>(P, view(), off, n, mode == ROWS_SELECTIVE ? 1 : 0, ea, stream_rows_, ctr_dev_.as<Counters>());
+        launches++;
+        SRB_CUDA(cudaEventRecord(ev1_, stream));
+        SRB_CUDA(cudaGetLastError());
+        Counters* hc = ctr_host_.as<Counters>();
+        SRB_CUDA(cudaMemcpyAsync(hc, ctr_dev_.p, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+        SRB_CUDA(cudaMemsetAsync(ctr_dev_.p, 0, sizeof(Counters), stream));
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        float ms = 0;
+        SRB_CUDA(cudaEventElapsedTime(&ms, ev0_, ev1_));
+        kernel_ms_ += ms;
+        timed_batches_++;
+        if (hc->key_too_long) throw Error(SRB_NOT_IMPLEMENTED, "serialized group key longer than 16 bytes");
+        selected_total_ += hc->rows_selected;
+        stream_rows_ += (int64_t)hc->emitted;
+        return (int64_t)hc->inserted; // the stream kernel reports its hits there
+    }
+
+    void stream_batch(const ColBind* cols, int64_t off, int64_t n) {
+        const int64_t rows_before = stream_seen_;
+        stream_seen_ += n;
+        if (stream_mode_ == SRB_STREAMING_FORCE_STREAMING) {
+            run_rows(cols, off, n, ROWS_STREAM);
+            return;
+        }
+        if (stream_mode_ == SRB_STREAMING_FORCE_PREAGGREGATION) {
+            run_rows(cols, off, n, ROWS_AGGREGATE);
+            return;
+        }
+        AutoContext& ac = auto_;
+        const size_t mem = (size_t)cap_ * (size_t)L_.prog.slot_bytes;
+        const size_t continuous_limit = ac.continuous_limit;
+        switch (auto_state_) {
+        case INIT_PREAGG: {
+            const bool needs_expansion = (occupied_ + (uint64_t)n) * 2 > cap_;
+            if (!needs_expansion || should_expand_preagg_table(rows_before)) {
+                run_rows(cols, off, n, ROWS_AGGREGATE);
+                break;
+            }
+            auto_state_ = ADJUST;
+            ac.adjust_count = 0;
+        }
+            [[fallthrough]];
+        case ADJUST: {
+            ac.adjust_count++;
+            const uint64_t sel0 = selected_total_;
+            const int64_t hits = run_rows(cols, off, n, ROWS_SELECTIVE);
+            const int64_t rows = (int64_t)(selected_total_ - sel0);
+            if (ac.adjust_count < continuous_limit && (double)hits <= AutoContext::LowReduction * (double)rows) {
+                ac.pass_through_count++;
+                ac.preagg_count = ac.selective_preagg_count = 0;
+                if (ac.pass_through_count == (size_t)AutoContext::StableLimit) auto_state_ = PASS_THROUGH;
+            } else if (ac.adjust_count < continuous_limit && (double)hits >= AutoContext::HighReduction * (double)rows && mem < AutoContext::MaxHtSize) {
+                ac.preagg_count++;
+                ac.pass_through_count = ac.selective_preagg_count = 0;
+                if (ac.preagg_count == (size_t)AutoContext::StableLimit) {
+                    auto_state_ = PREAGG;
+                    ac.preagg_count = 0;
+                }
+            } else {
+                ac.selective_preagg_count++;
+                ac.pass_through_count = ac.preagg_count = 0;
+                if (ac.selective_preagg_count == (size_t)AutoContext::StableLimit) auto_state_ = SELECTIVE_PREAGG;
+            }
+            break;
+        }
+        case PASS_THROUGH: {
+            run_rows(cols, off, n, ROWS_STREAM);
+            ac.pass_through_count++;
+            if (ac.pass_through_count > continuous_limit) {
+                auto_state_ = mem < AutoContext::MaxHtSize ? FORCE_PREAGG : ADJUST;
+                ac.pass_through_count = ac.preagg_count = ac.adjust_count = 0;
+                ac.update_continuous_limit();
+            }
+            break;
+        }
+        case FORCE_PREAGG:
+        case PREAGG: {
+            run_rows(cols, off, n, ROWS_AGGREGATE);
+            ac.preagg_count++;
+            const size_t limit = auto_state_ == FORCE_PREAGG ? AutoContext::ForcePreaggLimit : AutoContext::PreaggLimit;
+            if (ac.preagg_count > limit) {
+                auto_state_ = ADJUST;
+                ac.preagg_count = ac.adjust_count = 0;
+            }
+            break;
+        }
+        case SELECTIVE_PREAGG: {
+            run_rows(cols, off, n, ROWS_SELECTIVE);
+            ac.selective_preagg_count++;
+            if (ac.selective_preagg_count > continuous_limit) {
+                auto_state_ = ADJUST;
+                ac.selective_preagg_count = ac.adjust_count = 0;
+                ac.update_continuous_limit();
+            }
+            break;
+        }
+        }
     }
 
     const ColBind* strip_clear_null_maps(const ColBind* cols, int64_t off, int64_t n) {
@@ -1643,26 +1881,26 @@ private:
     }
 
     // ---- output ------------------------------------------------------------------------------------------------------
-    void produce_output() {
-        if (filter_only_) return; // rows already sit in fout_
+    // output arrays for `rows` result rows; the first stream_rows_ rows (pass-through rows of a streaming sink) are preserved
+    EmitArgs emit_args(uint64_t rows) {
         const DProg& P = L_.prog;
-        uint64_t max_rows = P.n_keys ? occupied_ : 1;
+        const size_t cap = (size_t)std::max<uint64_t>(1, rows), keep = (size_t)stream_rows_;
         EmitArgs ea{};
-        ekeys_.ensure(ctx, (size_t)std::max<uint64_t>(1, max_rows) * 16);
+        grow_out(ekeys_, keep * 16, cap * 16);
         ea.keys = ekeys_.as<ulonglong2>();
         eval_.resize(P.n_aggs);
         for (int a = 0; a < P.n_aggs; a++) {
             const AggOutMeta& m = L_.agg_out[a];
             EmitAgg& e = ea.aggs[a];
-            eval_[a].val.ensure(ctx, (size_t)std::max<uint64_t>(1, max_rows) * m.out_width);
+            grow_out(eval_[a].val, keep * m.out_width, cap * m.out_width);
             e.val = eval_[a].val.p;
             e.out_width = m.out_width;
             if (m.nullable) {
-                eval_[a].null.ensure(ctx, (size_t)std::max<uint64_t>(1, max_rows));
+                grow_out(eval_[a].null, keep, cap);
                 e.null = eval_[a].null.as<uint8_t>();
             }
             if (m.blob) {
-                eval_[a].cnt.ensure(ctx, (size_t)std::max<uint64_t>(1, max_rows) * 8);
+                grow_out(eval_[a].cnt, keep * 8, cap * 8);
                 e.cnt = eval_[a].cnt.as<int64_t>();
             }
             e.scale = m.arg_scale;
@@ -1680,16 +1918,24 @@ private:
             else
                 e.mode = 5;
         }
+        return ea;
+    }
+
+    void produce_output() {
+        if (filter_only_) return; // rows already sit in fout_
+        const DProg& P = L_.prog;
+        uint64_t max_rows = P.n_keys ? occupied_ : 1;
+        EmitArgs ea = emit_args((uint64_t)stream_rows_ + max_rows);
         SRB_CUDA(cudaMemsetAsync(ctr_dev_.p, 0, sizeof(Counters), stream));
         int blocks = (int)std::min<uint64_t>((cap_ + 255) / 256, (uint64_t)ctx->n_sms * 16);
-        k_emit<<<blocks, 256, 0, stream>>>(P, slots_.as<uint8_t>(), cap_, ea, ctr_dev_.as<Counters>());
+        k_emit<<<blocks, 256, 0, stream>>>(P, slots_.as<uint8_t>(), cap_, ea, ctr_dev_.as<Counters>(), stream_rows_);
         launches++;
         SRB_CUDA(cudaGetLastError());
         Counters* hc = ctr_host_.as<Counters>();
         SRB_CUDA(cudaMemcpyAsync(hc, ctr_dev_.p, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
         SRB_CUDA(cudaStreamSynchronize(stream));
-        out_rows_ = (int64_t)hc->emitted;
-        if ((uint64_t)out_rows_ != max_rows) throw Error(SRB_INTERNAL_ERROR, fmt("emit produced %lld rows, table holds %llu", (long long)out_rows_, (unsigned long long)max_rows));
+        if (hc->emitted != max_rows) throw Error(SRB_INTERNAL_ERROR, fmt("emit produced %llu rows, table holds %llu", (unsigned long long)hc->emitted, (unsigned long long)max_rows));
+        out_rows_ = stream_rows_ + (int64_t)hc->emitted; // pass-through rows first, then the table's groups
     }
 
     // copies rows [pos, pos+n) of the device result into host columns
@@ -1896,6 +2142,14 @@ private:
     std::vector<FOut> dkeys_;
     std::vector<EVal> eval_;
     int64_t out_rows_ = 0, out_pos_ = 0;
+    // streaming pre-aggregation sink
+    int stream_mode_ = -1;    // -1: blocking sink; otherwise TStreamingPreaggregationMode
+    int64_t stream_rows_ = 0; // pass-through rows at the front of the output arrays
+    int64_t stream_seen_ = 0; // input rows the sink has been handed
+    int64_t stream_unit_ = getenv("SRB_STREAM_UNIT") ? std::max<int64_t>(1, atoll(getenv("SRB_STREAM_UNIT"))) : ((int64_t)1 << 24);
+    size_t stream_l2_bytes_ = getenv("SRB_STREAM_L2_BYTES") ? (size_t)atoll(getenv("SRB_STREAM_L2_BYTES")) : ((size_t)96 << 20); // test hook
+    AutoState auto_state_ = INIT_PREAGG;
+    AutoContext auto_;
     bool pulled_empty_ = false;
     std::vector<HostCol> hcols_;
     std::vector<int32_t> hslots_;

@@ -30,7 +30,7 @@ EXPORTS = [
     "srb_device_alloc", "srb_device_free", "srb_pinned_alloc", "srb_pinned_free", "srb_memcpy_h2d", "srb_memcpy_d2h",
     "srb_partition_create", "srb_partition_run", "srb_partition_destroy",
     "srb_comm_unique_id", "srb_comm_create", "srb_comm_destroy", "srb_comm_stream", "srb_comm_all_to_all", "srb_comm_all_gather", "srb_comm_shuffle", "srb_comm_counters", "srb_comm_merge_runtime_filter",
-    "srb_join_build_runtime_filter", "srb_op_add_runtime_filter", "srb_runtime_filter_info", "srb_runtime_filter_directory", "srb_runtime_filter_destroy",
+    "srb_join_build_runtime_filter", "srb_op_add_runtime_filter", "srb_op_set_streaming_mode", "srb_op_streaming_stats", "srb_runtime_filter_info", "srb_runtime_filter_directory", "srb_runtime_filter_destroy",
 ]
 
 
@@ -96,6 +96,8 @@ def lib() -> C.CDLL:
     L.srb_comm_merge_runtime_filter.argtypes = [vp, vp]
     L.srb_join_build_runtime_filter.argtypes = [vp, C.c_int32, i64, C.c_int32, C.POINTER(vp)]
     L.srb_op_add_runtime_filter.argtypes = [vp, vp, C.c_int32]
+    L.srb_op_set_streaming_mode.argtypes = [vp, C.c_int32]
+    L.srb_op_streaming_stats.argtypes = [vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
     L.srb_runtime_filter_info.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), C.POINTER(C.c_int32), C.POINTER(i64)]
     L.srb_runtime_filter_directory.argtypes = [vp, vp, i64]
     L.srb_runtime_filter_destroy.argtypes = [vp]
@@ -258,6 +260,17 @@ class ScanAggOperator(_Operator):
         """scan-filter plans only, before the first push_chunk (Operator::eval_runtime_bloom_filters)"""
         _check(self.L.srb_op_add_runtime_filter(self.h, rf.h, slot_id))
         self._rfs = getattr(self, "_rfs", []) + [rf]
+
+    def set_streaming_mode(self, mode: int):
+        """first phase of a two-phase GROUP BY as a streaming sink (AggregateStreamingSinkOperator): capi.STREAMING_AUTO /
+        STREAMING_FORCE_STREAMING / STREAMING_FORCE_PREAGGREGATION (TStreamingPreaggregationMode); before the first push_chunk"""
+        _check(self.L.srb_op_set_streaming_mode(self.h, mode))
+
+    def streaming_stats(self):
+        a, b, c = C.c_int64(), C.c_int64(), C.c_int32()
+        _check(self.L.srb_op_streaming_stats(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        names = ["init_preagg", "adjust", "pass_through", "force_preagg", "preagg", "selective_preagg"]
+        return {"rows_streamed": a.value, "groups": b.value, "state": names[c.value]}
 
     def sync(self):
         _check(self.L.srb_op_sync(self.h))

@@ -1054,3 +1054,68 @@ def test_q3_aggregation_static_shape(ctx, oracle, n):
     for p in ptrs:
         ctx.device_free(p)
     assert prof["shape"] == 3 and (prof["static_launches"] >= 1 or n < 4096)
+
+
+# ---- streaming pre-aggregation sink: tests/test_streaming_cpu.py pins the oracle side -----------------------------
+def _stream_gpu(ctx, plan, chunk, mode, piece_rows=0):
+    from starrocks_b200 import ops
+    op = ops.ScanAggOperator(ctx, plan)
+    op.set_streaming_mode(mode)
+    if piece_rows:
+        for a in range(0, chunk.n_rows, piece_rows):
+            op.push_chunk(ops.slice_chunk(chunk, a, min(chunk.n_rows, a + piece_rows)))
+    else:
+        op.push_chunk(chunk)
+    op.set_finishing()
+    out = op.pull_all()
+    st = op.streaming_stats()
+    op.close()
+    return out, st
+
+
+def test_force_streaming_passes_every_row_through_in_intermediate_format(ctx, oracle):
+    from tests.test_streaming_cpu import hc_chunk
+    rng = np.random.default_rng(21)
+    n = 50_000
+    ch = hc_chunk(rng.integers(0, 50, n), rng.integers(-1000, 1000, n), (rng.random(n) < 0.1).astype(np.uint8))
+    plan = Q.highcard_plan(phase=K.AGG_UPDATE_SERIALIZE)
+    want, _ = oracle.scan_agg_streaming(plan, ch, K.STREAMING_FORCE_STREAMING)
+    for piece in (0, 4096):
+        got, st = _stream_gpu(ctx, plan, ch, K.STREAMING_FORCE_STREAMING, piece)
+        assert got.n_rows == n and st["rows_streamed"] == n and st["groups"] == 0
+        assert K.chunk_rows(got) == K.chunk_rows(want)  # the same multiset of (k, value-or-NULL, 1) rows; order is not kept
+
+
+@pytest.mark.parametrize("mode", [K.STREAMING_AUTO, K.STREAMING_FORCE_STREAMING, K.STREAMING_FORCE_PREAGGREGATION])
+def test_streaming_sink_phase_two_result_does_not_depend_on_the_mode(ctx, oracle, mode, monkeypatch):
+    """heavy repetition, then all-distinct keys, then moderate repetition, pushed in 4096-row chunks with a 4096-row AUTO unit: the
+    AUTO machine leaves INIT_PREAGG, passes rows through and comes back; whatever it does, phase 2 over the sink's output equals
+    the one-phase result (oracle), and FORCE_PREAGGREGATION equals the blocking first phase"""
+    from tests.test_streaming_cpu import hc_chunk
+    monkeypatch.setenv("SRB_STREAM_UNIT", "4096")
+    monkeypatch.setenv("SRB_STREAM_L2_BYTES", "65536")  # the table outgrows "the L2" after a few thousand groups
+    rng = np.random.default_rng(22)
+    keys = np.concatenate([rng.integers(0, 100, 30_000), 10**6 + np.arange(300_000), rng.integers(0, 20_000, 50_000)])
+    ch = hc_chunk(keys, rng.integers(-10**12, 10**12, len(keys)), (rng.random(len(keys)) < 0.05).astype(np.uint8))
+    inter, st = _stream_gpu(ctx, Q.highcard_plan(phase=K.AGG_UPDATE_SERIALIZE), ch, mode, piece_rows=65536)
+    assert st["rows_streamed"] + st["groups"] == inter.n_rows
+    if mode == K.STREAMING_AUTO:
+        assert 0 < st["rows_streamed"] < len(keys)
+    elif mode == K.STREAMING_FORCE_PREAGGREGATION:
+        assert st["rows_streamed"] == 0
+        assert K.chunk_rows(inter) == K.chunk_rows(oracle.scan_agg(Q.highcard_plan(phase=K.AGG_UPDATE_SERIALIZE), ch))
+    got = K.chunk_rows(run_gpu(ctx, Q.highcard_merge_plan(), inter))
+    assert got == K.chunk_rows(oracle.scan_agg(Q.highcard_plan(), ch))
+
+
+def test_streaming_mode_misuse_is_reported(ctx):
+    from starrocks_b200 import ops
+    op = ops.ScanAggOperator(ctx, Q.highcard_plan())  # update + finalize: not the first phase of a two-phase aggregation
+    with pytest.raises(ops.SrbError) as ei:
+        op.set_streaming_mode(K.STREAMING_AUTO)
+    assert ei.value.code == K.INVALID_ARGUMENT
+    op.close()
+    op = ops.ScanAggOperator(ctx, Q.highcard_plan(phase=K.AGG_UPDATE_SERIALIZE))
+    with pytest.raises(ops.SrbError):
+        op.set_streaming_mode(7)
+    op.close()
