@@ -1762,6 +1762,9 @@ private:
         if (filter_only_) {
             filter_range(b, st.rows);
             st.rows = 0;
+        } else if (stream_mode_ >= 0) { // the streaming sink decides per unit and waits for each unit's counters
+            stream_range(b, st.rows);
+            st.rows = 0;
         } else {
             launch_batch(b, 0, st.rows);
             pending_rows_ = st.rows;
