@@ -135,8 +135,14 @@ public:
     Status prepare(RuntimeState* state) override {
         if (_op) return Status::OK();
         const srb_scan_agg_plan p = _plan.c_plan();
-        return srb_to_status(srb_scan_agg_create(_ctx, &p, &_op));
+        SRB_RETURN_IF_ERROR(srb_to_status(srb_scan_agg_create(_ctx, &p, &_op)));
+        if (_streaming_mode >= 0) return srb_to_status(srb_op_set_streaming_mode(_op, _streaming_mode));
+        return Status::OK();
     }
+    // AggregateStreamingSinkOperator in place of the blocking sink (the first phase of a two-phase aggregation in front of an
+    // exchange): TAggregationNode::streaming_preaggregation_mode (gensrc/thrift/PlanNodes.thrift:851) picks how rows meet the table.
+    // Call before prepare(); the plan must be in SRB_AGG_UPDATE_SERIALIZE with GROUP BY keys.
+    void set_streaming_preaggregation_mode(int32_t mode) { _streaming_mode = mode; }
     // the scan waits for the joins whose runtime filters it applies (Operator::set_precondition_ready, operator.h:185): no input is
     // taken before every such build side has finished; the filters are attached right before the first chunk
     void wait_for_runtime_filter(std::shared_ptr<class GpuHashJoiner> joiner, int32_t slot_id);
@@ -182,6 +188,7 @@ private:
     std::vector<std::pair<std::shared_ptr<class GpuHashJoiner>, int32_t>> _rf_sources;
     bool _rf_attached = false;
     int64_t _rows_selected = 0;
+    int32_t _streaming_mode = -1; // -1: blocking sink
 };
 
 // ---- hash join: the build and probe operators share one joiner, like HashJoiner (exec/hash_joiner.h:169) -------------------------
