@@ -7,6 +7,7 @@
 namespace orc {
 Result* run_scan_agg(const srb_scan_agg_plan* plan, const srb_chunk* in, int n_threads, int chunk_size);
 Result* run_scan_agg_streaming(const srb_scan_agg_plan* plan, const srb_chunk* in, int chunk_size, int mode, int64_t* stats);
+Result* run_sort(const srb_chunk* in, int n_keys, const int32_t* key_slots, const uint8_t* is_asc, const uint8_t* nulls_first, int64_t offset, int64_t limit);
 Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe);
 void join_build_raw(const void* keys, int width, uint32_t n, uint32_t* bucket_size, uint32_t* first, uint32_t* next);
 int pack_keys_raw(const srb_chunk* ch, const int32_t* slots, int n_keys, void* out16);
@@ -32,6 +33,16 @@ void* orc_scan_agg(const srb_scan_agg_plan* plan, const srb_chunk* in, int n_thr
 void* orc_scan_agg_streaming(const srb_scan_agg_plan* plan, const srb_chunk* in, int chunk_size, int mode, int64_t* stats) {
     try {
         return orc::run_scan_agg_streaming(plan, in, chunk_size, mode, stats);
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return nullptr;
+    }
+}
+// ORDER BY key_slots (is_asc / nulls_first per key) OFFSET offset LIMIT limit (limit < 0: every row)
+void* orc_sort(const srb_chunk* in, int n_keys, const int32_t* key_slots, const uint8_t* is_asc, const uint8_t* nulls_first, int64_t offset,
+               int64_t limit) {
+    try {
+        return orc::run_sort(in, n_keys, key_slots, is_asc, nulls_first, offset, limit);
     } catch (const std::exception& e) {
         g_err = e.what();
         return nullptr;

@@ -28,6 +28,8 @@ class Oracle:
         L.orc_last_error.restype = C.c_char_p
         L.orc_scan_agg.restype = C.c_void_p
         L.orc_scan_agg.argtypes = [C.POINTER(K.srb_scan_agg_plan), C.POINTER(K.srb_chunk), C.c_int, C.c_int]
+        L.orc_sort.restype = C.c_void_p
+        L.orc_sort.argtypes = [C.POINTER(K.srb_chunk), C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_uint8), C.POINTER(C.c_uint8), C.c_int64, C.c_int64]
         L.orc_scan_agg_streaming.restype = C.c_void_p
         L.orc_scan_agg_streaming.argtypes = [C.POINTER(K.srb_scan_agg_plan), C.POINTER(K.srb_chunk), C.c_int, C.c_int, C.POINTER(C.c_int64)]
         L.orc_join.restype = C.c_void_p
@@ -110,6 +112,19 @@ class Oracle:
             self.lib.orc_result_free(r)
         names = ["init_preagg", "adjust", "pass_through", "force_preagg", "preagg", "selective_preagg"]
         return out, {"rows_streamed": stats[0], "groups": stats[1], "chunks": dict(zip(names, list(stats[2:8]))), "final_state": names[stats[8]]}
+
+    def sort(self, chunk: K.Chunk, key_slots, is_asc, nulls_first, offset: int = 0, limit: int = -1) -> K.Chunk:
+        """ORDER BY ... OFFSET ... LIMIT (ChunksSorterTopn / ChunksSorterFullSort): every column, rows in sorted order"""
+        cch, keep = chunk.to_c()
+        n = len(key_slots)
+        r = self.lib.orc_sort(C.byref(cch), n, (C.c_int32 * n)(*key_slots), (C.c_uint8 * n)(*[int(bool(x)) for x in is_asc]),
+                              (C.c_uint8 * n)(*[int(bool(x)) for x in nulls_first]), offset, limit)
+        if not r:
+            raise RuntimeError("oracle: " + self._err())
+        try:
+            return K.decode_chunk(self.lib.orc_result_chunk(r).contents)
+        finally:
+            self.lib.orc_result_free(r)
 
     def join(self, plan, build: K.Chunk, probe: K.Chunk):
         b, k1 = build.to_c()

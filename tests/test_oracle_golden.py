@@ -448,3 +448,67 @@ def check_filter_vectors(run):
 
 def test_column_filter_known_answers(oracle):
     check_filter_vectors(lambda plan, ch: oracle.scan_agg(plan, ch))
+
+
+# ---- be/test/exec/chunks_sorter_test.cpp: the three fixture chunks (:441-482) and the sorted orders the reference asserts ----------
+def sorter_fixture():
+    cust = [2, 12, 41, 54, 58, 71, 4, 16, 49, 55, 69, 6, 24, 52, 56, 70]
+    nulls = [0, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1]
+    nation = ["JORDAN", "JORDAN", "IRAN", "EGYPT", "JORDAN", "", "EGYPT", "IRAN", "IRAN", "IRAN", "null0", "SAUDI ARABIA", "JORDAN", "IRAQ", "IRAN", "null1"]
+    region = ["MIDDLE EAST"] * 5 + [""] + ["MIDDLE EAST"] * 4 + ["null0"] + ["MIDDLE EAST"] * 4 + ["null1"]
+    mkt = ["AUTOMOBILE", "HOUSEHOLD", "HOUSEHOLD", "AUTOMOBILE", "HOUSEHOLD", "", "MACHINERY", "FURNITURE", "FURNITURE", "MACHINERY", "null0",
+           "AUTOMOBILE", "MACHINERY", "HOUSEHOLD", "FURNITURE", "null1"]
+
+    def strcol(v):
+        c = K.Column.from_strings([x.encode() for x in v])
+        c.nulls = np.array(nulls, np.uint8)
+        return c
+    return K.Chunk(16, {0: K.Column.from_ints(K.TYPE_INT, np.array(cust, np.int32)), 1: strcol(nation), 2: strcol(region), 3: strcol(mkt)})
+
+
+CUST, NATION, REGION, MKT = 0, 1, 2, 3
+SORT_VECTORS = [
+    # (key slots, is_asc, nulls_first, expected cust_key order)            chunks_sorter_test.cpp
+    ([REGION, CUST], [0, 1], [1, 1], [69, 70, 71, 2, 4, 6, 12, 16, 24, 41, 49, 52, 54, 55, 56, 58]),             # :799-837
+    ([REGION, CUST], [1, 0], [0, 0], [58, 56, 55, 54, 52, 49, 41, 24, 16, 12, 6, 4, 2, 71, 70, 69]),             # :839-877
+    ([REGION, NATION, CUST], [0, 1, 0], [1, 1, 1], [71, 70, 69, 54, 4, 56, 55, 49, 41, 16, 52, 58, 24, 12, 2, 6]),  # :879-920
+    ([MKT, REGION, NATION, CUST], [0, 1, 0, 0], [0, 1, 1, 0], [24, 55, 4, 58, 12, 52, 41, 56, 49, 16, 6, 2, 54, 71, 70, 69]),  # :922-966
+]
+
+
+def cust_keys(ch):
+    return K.column_pyvalues(ch.columns[0])
+
+
+@pytest.mark.parametrize("keys,asc,nf,want", SORT_VECTORS)
+def test_full_sort_known_answers(oracle, keys, asc, nf, want):
+    assert cust_keys(oracle.sort(sorter_fixture(), keys, asc, nf)) == want
+
+
+def test_topn_sort_with_limit(oracle):
+    # :703-747: ORDER BY <column>, cust_key (ascending, NULLs first) LIMIT 1..15
+    cases = [(CUST, [2, 4, 6, 12, 16, 24, 41, 49, 52, 54, 55, 56, 58, 69, 70, 71]),
+             (NATION, [69, 70, 71, 4, 54, 16, 41, 49, 55, 56, 52, 2, 12, 24, 58]),
+             (REGION, [69, 70, 71, 2, 4, 6, 12, 16, 24, 41, 49, 52, 54, 55, 56])]
+    ch = sorter_fixture()
+    for col, expected in cases:
+        for limit in range(1, 16):
+            assert cust_keys(oracle.sort(ch, [col, CUST], [1, 1], [1, 1], 0, limit)) == expected[:limit]
+
+
+def test_topn_offset_and_limit(oracle):
+    ch = sorter_fixture()
+    # :969-1006: region DESC, nation, cust_key, NULLs first, OFFSET 2 LIMIT 7
+    assert cust_keys(oracle.sort(ch, [REGION, NATION, CUST], [0, 1, 1], [1, 1, 1], 2, 7)) == [71, 4, 54, 16, 41, 49, 55]
+    # :1008-1060: NULLs last, OFFSET 7, LIMIT 8..9; an offset past the end gives nothing
+    for limit in (8, 9):
+        assert cust_keys(oracle.sort(ch, [REGION, NATION, CUST], [0, 1, 1], [0, 0, 0], 7, limit)) == [52, 2, 12, 24, 58, 6, 69, 70, 71][:limit]
+        assert oracle.sort(ch, [REGION, NATION, CUST], [0, 1, 1], [0, 0, 0], 100, limit).n_rows == 0
+
+
+def test_sort_is_stable_and_carries_every_column(oracle):
+    ch = sorter_fixture()
+    out = oracle.sort(ch, [REGION], [1], [1])  # ties everywhere: arrival order within NULLs and within 'MIDDLE EAST'
+    assert cust_keys(out) == [71, 69, 70, 2, 12, 41, 54, 58, 4, 16, 49, 55, 6, 24, 52, 56]
+    rows_in = {r[0]: r for r in K.chunk_rows(ch)}
+    assert all(rows_in[r[0]] == r for r in K.chunk_rows(out))
