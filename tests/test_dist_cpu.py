@@ -120,3 +120,19 @@ def test_two_rank_highcard_shuffle_merge_equals_one_rank(oracle):
     assert not (keys0 & keys1)  # a group ends on exactly one rank
     assert len(keys0) > 1000 and len(keys1) > 1000  # and the shuffle hash spreads them
     assert sorted(res[0] + res[1]) == want
+
+
+def test_four_ranks_gather_and_shuffle(oracle):
+    """the same host logic at world size 4 (the scaling run goes to 8 ranks): ragged shards, every rank ends with the merged Q1 result;
+    the shuffle leaves every group on exactly one of the four ranks"""
+    n = 40_003
+    res = _run("q1", n, world=4)
+    want = K.chunk_rows(oracle.scan_agg(Q.q1_plan(), T.host_chunk("lineitem", 0, n, T.LINEITEM_Q1)))
+    assert all(res[r] == want for r in range(4))
+    n = 30_001
+    res = _run("highcard", n, world=4)
+    want = K.chunk_rows(oracle.scan_agg(Q.highcard_plan(), T.host_chunk("highcard", 0, n, ["k", "v"], n_keys=5000)))
+    key_sets = [{row[0] for row in res[r]} for r in range(4)]
+    assert sum(len(s) for s in key_sets) == len(set().union(*key_sets)) == len(want)
+    assert all(len(s) > 500 for s in key_sets)
+    assert sorted(sum((res[r] for r in range(4)), [])) == want
