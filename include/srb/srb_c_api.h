@@ -196,6 +196,18 @@ typedef struct srb_join_plan {
     int32_t _pad;
 } srb_join_plan;
 
+/* ---- TopN: exec/chunks_sorter_topn.cpp, exec/sorting/sorting.h:86-101 ------------------- */
+#define SRB_TOPN_MAX_ROWS 1024 /* offset + limit the device TopN keeps (beyond that it is a full sort) */
+typedef struct srb_topn_plan {
+    int32_t n_keys; /* ORDER BY columns, most significant first; fixed-width types, composite key <= 32 bytes */
+    int32_t _pad;
+    const int32_t* key_slots;
+    const uint8_t* is_asc;      /* per key: 1 ascending, 0 descending */
+    const uint8_t* nulls_first; /* per key: 1 = NULLs first in the output whatever the direction (SortDesc::is_null_first) */
+    int64_t offset;
+    int64_t limit; /* rows [offset, offset + limit) of the sorted order are produced */
+} srb_topn_plan;
+
 /* ---- handles ------------------------------------------------------------------------------------- */
 typedef struct srb_ctx srb_ctx; /* device, streams, scratch pools, optional NCCL communicator */
 typedef struct srb_op srb_op;   /* one operator instance (one driver's operator) */
@@ -228,6 +240,10 @@ srb_status srb_scan_agg_create(srb_ctx* ctx, const srb_scan_agg_plan* plan, srb_
  * pipeline/hashjoin/hash_join_build_operator.cpp:40-213, hash_join_probe_operator.cpp:55-104.
  * Build side: srb_op_push_chunk(op,...) then srb_op_set_finishing(op). Probe side: srb_join_probe_* below. */
 srb_status srb_join_create(srb_ctx* ctx, const srb_join_plan* plan, srb_op** out);
+/* ChunksSorterTopn behind the operator contract: push_chunk takes host or device chunks (every column of the first chunk's schema
+ * is carried; fixed-width columns only), set_finishing ends the input, one pull_chunk / pull_all returns rows
+ * [offset, offset + limit) of the input sorted by the plan's keys, ties in arrival order. */
+srb_status srb_topn_create(srb_ctx* ctx, const srb_topn_plan* plan, srb_op** out);
 
 /* Operator::push_chunk (operator.h:121). Columns may be HOST/PINNED (staged + copied) or DEVICE (used in place,
  * must stay valid until the next srb_op_sync / set_finishing). n_rows is not limited to chunk_size. */

@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsrb.so")
-SOURCES = ["srb_scan_agg.cu", "srb_join.cu", "srb_exchange.cu", "srb_capi.cu"]
+SOURCES = ["srb_scan_agg.cu", "srb_join.cu", "srb_topn.cu", "srb_exchange.cu", "srb_capi.cu"]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "--expt-relaxed-constexpr",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "-Xcompiler", "-Wno-unknown-pragmas", "-Xcudafe", "--diag_suppress=177"]
 

@@ -92,6 +92,11 @@ class srb_join_plan(C.Structure):
                 ("emit_indexes", C.c_int32), ("_pad", C.c_int32)]
 
 
+class srb_topn_plan(C.Structure):
+    _fields_ = [("n_keys", C.c_int32), ("_pad", C.c_int32), ("key_slots", C.POINTER(C.c_int32)), ("is_asc", C.POINTER(C.c_uint8)),
+                ("nulls_first", C.POINTER(C.c_uint8)), ("offset", C.c_int64), ("limit", C.c_int64)]
+
+
 class srb_config(C.Structure):
     _fields_ = [("device", C.c_int32), ("chunk_size", C.c_int32), ("staging_rows", C.c_int64),
                 ("rank", C.c_int32), ("world_size", C.c_int32), ("mem_limit", C.c_int64)]

@@ -86,6 +86,15 @@ srb_status srb_join_create(srb_ctx* ctx, const srb_join_plan* plan, srb_op** out
     SRB_API_END
 }
 
+srb_status srb_topn_create(srb_ctx* ctx, const srb_topn_plan* plan, srb_op** out) {
+    SRB_API_BEGIN
+    if (!ctx || !out) throw srb::Error(SRB_INVALID_ARGUMENT, "null argument");
+    SRB_CUDA(cudaSetDevice(ctx->cfg.device));
+    *out = srb::make_topn_op(ctx, plan);
+    return SRB_OK;
+    SRB_API_END
+}
+
 #define OP_GUARD(op)                                                   \
     if (!(op)) throw srb::Error(SRB_INVALID_ARGUMENT, "null operator"); \
     SRB_CUDA(cudaSetDevice((op)->ctx->cfg.device));

@@ -344,4 +344,5 @@ struct srb_runtime_filter {
 namespace srb {
 srb_op* make_scan_agg_op(srb_ctx* ctx, const srb_scan_agg_plan* plan);
 srb_op* make_join_op(srb_ctx* ctx, const srb_join_plan* plan);
+srb_op* make_topn_op(srb_ctx* ctx, const srb_topn_plan* plan);
 } // namespace srb

@@ -30,7 +30,7 @@ EXPORTS = [
     "srb_device_alloc", "srb_device_free", "srb_pinned_alloc", "srb_pinned_free", "srb_memcpy_h2d", "srb_memcpy_d2h",
     "srb_partition_create", "srb_partition_run", "srb_partition_destroy",
     "srb_comm_unique_id", "srb_comm_create", "srb_comm_destroy", "srb_comm_stream", "srb_comm_all_to_all", "srb_comm_all_gather", "srb_comm_shuffle", "srb_comm_counters", "srb_comm_merge_runtime_filter",
-    "srb_join_build_runtime_filter", "srb_op_add_runtime_filter", "srb_op_set_streaming_mode", "srb_op_streaming_stats", "srb_runtime_filter_info", "srb_runtime_filter_directory", "srb_runtime_filter_destroy",
+    "srb_join_build_runtime_filter", "srb_op_add_runtime_filter", "srb_op_set_streaming_mode", "srb_op_streaming_stats", "srb_topn_create", "srb_runtime_filter_info", "srb_runtime_filter_directory", "srb_runtime_filter_destroy",
 ]
 
 
@@ -58,6 +58,7 @@ def lib() -> C.CDLL:
     L.srb_op_stream.restype = vp
     L.srb_scan_agg_create.argtypes = [vp, C.POINTER(K.srb_scan_agg_plan), C.POINTER(vp)]
     L.srb_join_create.argtypes = [vp, C.POINTER(K.srb_join_plan), C.POINTER(vp)]
+    L.srb_topn_create.argtypes = [vp, C.POINTER(K.srb_topn_plan), C.POINTER(vp)]
     for f in ("srb_op_push_chunk", "srb_join_probe_push_chunk"):
         getattr(L, f).argtypes = [vp, C.POINTER(K.srb_chunk)]
     for f in ("srb_op_set_finishing", "srb_join_probe_set_finishing", "srb_op_cancel", "srb_op_sync", "srb_op_has_output",
@@ -357,6 +358,24 @@ class HashJoinOperator(_Operator):
             self.L.srb_op_close(self.h)
             self.h = None
             self.probe.h = None
+
+
+class TopNOperator(_Operator):
+    """ORDER BY key_slots (is_asc / nulls_first per key) OFFSET offset LIMIT limit on the device (ChunksSorterTopn): push chunks,
+    set_finishing, pull_all -> every column of the input, rows [offset, offset + limit) of the sorted order"""
+
+    def __init__(self, ctx: Context, key_slots, is_asc, nulls_first, limit: int, offset: int = 0):
+        n = len(key_slots)
+        self._keep = ((C.c_int32 * n)(*key_slots), (C.c_uint8 * n)(*[int(bool(x)) for x in is_asc]), (C.c_uint8 * n)(*[int(bool(x)) for x in nulls_first]))
+        plan = K.srb_topn_plan(n, 0, self._keep[0], self._keep[1], self._keep[2], offset, limit)
+        h = C.c_void_p()
+        _check(ctx.L.srb_topn_create(ctx.h, C.byref(plan), C.byref(h)))
+        super().__init__(ctx, h)
+
+    def counters(self):
+        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
+        _check(self.L.srb_op_counters(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"rows_in": a.value, "rows_selected": b.value, "kernel_launches": c.value}
 
 
 def run_scan_agg(ctx: Context, plan, chunk: K.Chunk, piece_rows: int = 0) -> K.Chunk:

@@ -1,0 +1,81 @@
+"""Device TopN (starrocks_b200/csrc/srb_topn.cu) against the oracle's ORDER BY restatement (oracle/orc_sort.cpp, pinned to
+be/test/exec/chunks_sorter_test.cpp). The kernels were written after round 1's GPU minutes were spent: until these tests have run on
+a B200 they are expected-to-fail-or-pass (xfail, non-strict) and cannot fail the suite."""
+import numpy as np
+import pytest
+
+from starrocks_b200 import capi as K
+
+pytestmark = [pytest.mark.gpu, pytest.mark.xfail(strict=False, reason="srb_topn.cu has not run on hardware yet (round-1 GPU budget spent)")]
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from starrocks_b200 import ops
+    c = ops.Context(device=0)
+    yield c
+    c.close()
+
+
+def run_topn(ctx, chunk, keys, asc, nf, limit, offset=0, pieces=None, device=False):
+    from starrocks_b200 import ops
+    op = ops.TopNOperator(ctx, keys, asc, nf, limit, offset)
+    bounds = [0, chunk.n_rows] if not pieces else [0] + list(pieces) + [chunk.n_rows]
+    for a, b in zip(bounds[:-1], bounds[1:]):
+        part = ops.slice_chunk(chunk, a, b)
+        ptrs = []
+        if device:
+            part, ptrs = ctx.device_chunk(part)
+        op.push_chunk(part)
+        for p in ptrs:
+            ctx.device_free(p)
+    op.set_finishing()
+    out = op.pull_all()
+    op.close()
+    return out
+
+
+def test_reference_fixture_by_cust_key(ctx, oracle):
+    # chunks_sorter_test.cpp:703-747, the cust_key case: the three fixture chunks pushed one after the other, LIMIT 1..15
+    cust = [2, 12, 41, 54, 58, 71, 4, 16, 49, 55, 69, 6, 24, 52, 56, 70]
+    ch = K.Chunk(16, {0: K.Column.from_ints(K.TYPE_INT, np.array(cust, np.int32)), 1: K.Column.from_ints(K.TYPE_INT, np.arange(16, dtype=np.int32))})
+    expected = [2, 4, 6, 12, 16, 24, 41, 49, 52, 54, 55, 56, 58, 69, 70, 71]
+    for limit in range(1, 16):
+        out = run_topn(ctx, ch, [0], [1], [1], limit, pieces=[6, 11])
+        assert K.column_pyvalues(out.columns[0]) == expected[:limit]
+        assert [cust[i] for i in K.column_pyvalues(out.columns[1])] == expected[:limit]  # the payload column travels with its row
+
+
+@pytest.mark.parametrize("device", [False, True])
+def test_random_rows_against_the_oracle(ctx, oracle, device):
+    from tests.test_topn_cpu import random_chunk, TOPN_CASES
+    rng = np.random.default_rng(41)
+    n = 150_000
+    ch = random_chunk(rng, n)
+    for keys, asc, nf in TOPN_CASES:
+        for limit, offset in ((10, 0), (1000, 24), (1, 0)):
+            want = K.chunk_rows(oracle.sort(ch, keys, asc, nf, offset, limit), sort=False)
+            got = K.chunk_rows(run_topn(ctx, ch, keys, asc, nf, limit, offset, pieces=[1000, 70_001], device=device), sort=False)
+            assert got == want, (keys, limit, offset)  # same rows in the same order, ties in arrival order
+
+
+def test_fewer_rows_than_the_limit_and_limit_zero(ctx, oracle):
+    from tests.test_topn_cpu import random_chunk
+    ch = random_chunk(np.random.default_rng(5), 37)
+    want = K.chunk_rows(oracle.sort(ch, [1], [0], [1], 0, 100), sort=False)
+    assert K.chunk_rows(run_topn(ctx, ch, [1], [0], [1], 100), sort=False) == want
+    assert run_topn(ctx, ch, [1], [0], [1], 0).n_rows == 0
+    assert run_topn(ctx, ch, [1], [0], [1], 10, offset=50).n_rows == 0
+
+
+def test_unsupported_plans_are_reported(ctx):
+    from starrocks_b200 import ops
+    with pytest.raises(ops.SrbError) as ei:
+        ops.TopNOperator(ctx, [0], [1], [1], limit=2000)
+    assert ei.value.code == K.NOT_IMPLEMENTED
+    op = ops.TopNOperator(ctx, [0], [1], [1], limit=5)
+    ch = K.Chunk(2, {0: K.Column.from_ints(K.TYPE_INT, np.array([1, 2], np.int32)), 1: K.Column.from_strings([b"a", b"b"])})
+    with pytest.raises(ops.SrbError) as ei:
+        op.push_chunk(ch)
+    assert ei.value.code == K.NOT_IMPLEMENTED
+    op.close()
