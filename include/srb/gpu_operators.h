@@ -191,6 +191,62 @@ private:
     int32_t _streaming_mode = -1; // -1: blocking sink
 };
 
+// ---- TopN: PartitionSortSinkOperator + LocalMergeSortSourceOperator over a ChunksSorterTopn, as one operator ---------------------
+// (exec/pipeline/sort/partition_sort_sink_operator.cpp, exec/chunks_sorter_topn.cpp; TSortInfo::is_asc_order / nulls_first,
+// TSortNode::offset / limit)
+struct TopNPlan {
+    std::vector<int32_t> key_slots;
+    std::vector<uint8_t> is_asc, nulls_first;
+    int64_t offset = 0, limit = 0;
+    srb_topn_plan c_plan() const {
+        srb_topn_plan p{};
+        p.n_keys = (int32_t)key_slots.size();
+        p.key_slots = key_slots.data();
+        p.is_asc = is_asc.data();
+        p.nulls_first = nulls_first.data();
+        p.offset = offset;
+        p.limit = limit;
+        return p;
+    }
+};
+
+class GpuTopNOperator final : public Operator {
+public:
+    GpuTopNOperator(srb_ctx* ctx, TopNPlan plan) : Operator("gpu_topn"), _ctx(ctx), _plan(std::move(plan)) {}
+    ~GpuTopNOperator() override { close(nullptr); }
+    Status prepare(RuntimeState*) override {
+        if (_op) return Status::OK();
+        const srb_topn_plan p = _plan.c_plan();
+        return srb_to_status(srb_topn_create(_ctx, &p, &_op));
+    }
+    bool need_input() const override { return _op && srb_op_need_input(_op); }
+    bool has_output() const override { return _op && srb_op_has_output(_op); }
+    bool is_finished() const override { return !_op || srb_op_is_finished(_op); }
+    Status push_chunk(RuntimeState* state, const ChunkPtr& chunk) override {
+        if (state && state->is_cancelled()) return Status::Cancelled("query cancelled");
+        SrbChunkView v;
+        to_srb(*chunk, &v);
+        return srb_to_status(srb_op_push_chunk(_op, &v.chunk)); // the survivors' rows are copied into operator state before this returns
+    }
+    Status set_finishing(RuntimeState*) override { return srb_to_status(srb_op_set_finishing(_op)); }
+    StatusOr<ChunkPtr> pull_chunk(RuntimeState*) override {
+        srb_chunk out{};
+        const srb_status st = srb_op_pull_chunk(_op, &out);
+        if (st == SRB_END_OF_FILE) return Status::EndOfFile("gpu topn drained");
+        if (st != SRB_OK) return srb_to_status(st);
+        return from_srb(out);
+    }
+    void close(RuntimeState*) override {
+        if (_op) srb_op_close(_op);
+        _op = nullptr;
+    }
+
+private:
+    srb_ctx* _ctx;
+    TopNPlan _plan;
+    srb_op* _op = nullptr;
+};
+
 // ---- hash join: the build and probe operators share one joiner, like HashJoiner (exec/hash_joiner.h:169) -------------------------
 struct JoinPlan {
     int32_t join_type = SRB_JOIN_INNER;
