@@ -73,3 +73,29 @@ def test_composite_key_order_is_the_reference_order(oracle, keys, asc, nf):
     want = K.column_pyvalues(oracle.sort(ch, keys, asc, nf).columns[5])  # row ids in the reference's order (stable)
     order = sorted(range(n), key=lambda r: (composite_key(ch, r, keys, asc, nf), r))
     assert order == want
+
+
+def test_bitonic_network_of_the_reduce_kernel_sorts():
+    """the compare-exchange schedule of k_topn_reduce (one pair per thread: i = 2j(t / j) + t % j, partner i + j, direction by (i & k)),
+    replayed with numpy on the kernel's tile size: every step touches each element once and the result is sorted"""
+    tile, threads = 2048, 1024
+    rng = np.random.default_rng(9)
+    for trial in range(3):
+        a = rng.integers(0, 50 if trial == 0 else 2**62, tile)  # trial 0: many ties
+        a = a * tile + rng.permutation(tile)                    # the arrival number makes the order total, as in the kernel
+        t = np.arange(threads)
+        k = 2
+        while k <= tile:
+            j = k >> 1
+            while j > 0:
+                i = 2 * j * (t // j) + (t % j)
+                p = i + j
+                assert len(np.unique(np.concatenate([i, p]))) == tile
+                asc = (i & k) == 0
+                swap = np.where(asc, a[p] < a[i], a[i] < a[p])
+                ai, ap = a[i].copy(), a[p].copy()
+                a[i] = np.where(swap, ap, ai)
+                a[p] = np.where(swap, ai, ap)
+                j >>= 1
+            k <<= 1
+        assert (np.diff(a) > 0).all()
