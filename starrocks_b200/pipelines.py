@@ -126,6 +126,19 @@ class TpchQ3:
         agg.set_finishing()
         return agg
 
+    # q3.sql:36-38: ORDER BY revenue DESC, o_orderdate LIMIT 10 (DESC puts NULLs last, ASC first: StarRocks' defaults)
+    TOP_KEYS, TOP_ASC, TOP_NULLS_FIRST = [3, 1], [0, 1], [0, 1]
+
+    def top(self, agg, limit: int = 10) -> K.Chunk:
+        """the plan's last operator: the aggregation's device result through the device TopN (ops.TopNOperator)"""
+        top = ops.TopNOperator(self.ctx, self.TOP_KEYS, self.TOP_ASC, self.TOP_NULLS_FIRST, limit)
+        self.open.append(top)
+        groups = agg.pull_device()
+        if groups is not None and groups.n_rows:
+            top.push_chunk(groups)
+        top.set_finishing()
+        return top.pull_all()
+
     def launches(self) -> int:
         return sum(o.counters()["kernel_launches"] for o in self.open if hasattr(o, "counters"))
 
@@ -133,6 +146,10 @@ class TpchQ3:
         for o in self.open:
             o.close()
         self.open = []
+
+
+def q3_top_oracle(oracle, groups: K.Chunk, limit: int = 10) -> K.Chunk:
+    return oracle.sort(groups, TpchQ3.TOP_KEYS, TpchQ3.TOP_ASC, TpchQ3.TOP_NULLS_FIRST, 0, limit)
 
 
 def q3_oracle(oracle, cust: K.Chunk, orders: K.Chunk, line: K.Chunk, n_threads: int = 1) -> K.Chunk:
