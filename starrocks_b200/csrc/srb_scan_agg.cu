@@ -23,6 +23,7 @@
 #include "srb_lower.h"
 #include "srb_rowpipe.cuh"
 #include "srb_shapes.cuh"
+#include "srb_stream_policy.h"
 #include "srb_hcpart.cuh"
 
 namespace srb {
@@ -1403,16 +1404,7 @@ private:
     // decision costs no extra pass over the rows; the counters steer the following ranges exactly as the reference's do.
     // Thresholds that stand for CPU cache sizes in the reference (STREAMING_HT_MIN_REDUCTION: 256 KB / 2 MB; MaxHtSize 64 MB) are
     // restated for a B200: a table that fits the 126 MB L2 resolves its atomics there, a larger one pays HBM sectors per row.
-    enum AutoState { INIT_PREAGG = 0, ADJUST, PASS_THROUGH, FORCE_PREAGG, PREAGG, SELECTIVE_PREAGG };
-    struct AutoContext { // exec/aggregator.h:172-193
-        static constexpr size_t ContinuousUpperLimit = 10000;
-        static constexpr int ForcePreaggLimit = 3, PreaggLimit = 100, StableLimit = 5;
-        static constexpr double LowReduction = 0.2, HighReduction = 0.9;
-        static constexpr size_t MaxHtSize = (size_t)8 << 30;
-        size_t adjust_count = 0, pass_through_count = 0, preagg_count = 0, selective_preagg_count = 0, continuous_limit = 100;
-        void update_continuous_limit() { continuous_limit = continuous_limit * 2 > ContinuousUpperLimit ? ContinuousUpperLimit : continuous_limit * 2; }
-    };
-    enum RowMode { ROWS_AGGREGATE, ROWS_STREAM, ROWS_SELECTIVE };
+    enum RowMode { ROWS_AGGREGATE = STREAM_ROWS_AGGREGATE, ROWS_STREAM = STREAM_ROWS_PASS, ROWS_SELECTIVE = STREAM_ROWS_SELECTIVE };
 
     void set_streaming_mode(int mode) override {
         if (mode < SRB_STREAMING_AUTO || mode > SRB_STREAMING_FORCE_PREAGGREGATION) throw Error(SRB_INVALID_ARGUMENT, "unknown streaming pre-aggregation mode");
@@ -1420,24 +1412,12 @@ private:
         if (plan_.key_nodes.empty() || plan_.aggs.empty() || plan_.phase != SRB_AGG_UPDATE_SERIALIZE)
             throw Error(SRB_INVALID_ARGUMENT, "streaming pre-aggregation needs GROUP BY keys and the update + serialize phase");
         stream_mode_ = mode;
+        if (getenv("SRB_STREAM_L2_BYTES")) policy_.l2_bytes = (size_t)atoll(getenv("SRB_STREAM_L2_BYTES")); // test hook: a small "L2"
     }
     void streaming_stats(int64_t* rows_passed_through, int64_t* groups_in_table, int32_t* auto_state) override {
         if (rows_passed_through) *rows_passed_through = stream_rows_;
         if (groups_in_table) *groups_in_table = (int64_t)occupied_;
-        if (auto_state) *auto_state = (int32_t)auto_state_;
-    }
-
-    // Aggregator::should_expand_preagg_hash_tables (aggregator.cpp:770-802): keep growing the table only while the rows aggregated
-    // so far reduce by more than the factor its size asks for
-    bool should_expand_preagg_table(int64_t rows_before) const {
-        if (occupied_ == 0) return true;
-        const size_t mem = (size_t)cap_ * (size_t)L_.prog.slot_bytes;
-        // a table that still fits the L2 may always grow; up to ten times that it must reduce by 1.1, beyond by 2 (the reference's
-        // STREAMING_HT_MIN_REDUCTION steps at 256 KB and 2 MB are its CPU's L2 and L3 share)
-        const double min_reduction = mem < stream_l2_bytes_ ? 0.0 : (mem < stream_l2_bytes_ * 10 ? 1.1 : 2.0);
-        const int64_t aggregated = rows_before - stream_rows_;
-        if (aggregated <= 0) return true;
-        return (double)aggregated / (double)occupied_ > min_reduction;
+        if (auto_state) *auto_state = (int32_t)policy_.state;
     }
 
     // AUTO learns from the hit counts of successive units: 2^24 rows each (a few per cent of an SF100 table), so that a poor
@@ -1494,75 +1474,12 @@ private:
             run_rows(cols, off, n, ROWS_AGGREGATE);
             return;
         }
-        AutoContext& ac = auto_;
-        const size_t mem = (size_t)cap_ * (size_t)L_.prog.slot_bytes;
-        const size_t continuous_limit = ac.continuous_limit;
-        switch (auto_state_) {
-        case INIT_PREAGG: {
-            const bool needs_expansion = (occupied_ + (uint64_t)n) * 2 > cap_;
-            if (!needs_expansion || should_expand_preagg_table(rows_before)) {
-                run_rows(cols, off, n, ROWS_AGGREGATE);
-                break;
-            }
-            auto_state_ = ADJUST;
-            ac.adjust_count = 0;
-        }
-            [[fallthrough]];
-        case ADJUST: {
-            ac.adjust_count++;
-            const uint64_t sel0 = selected_total_;
-            const int64_t hits = run_rows(cols, off, n, ROWS_SELECTIVE);
-            const int64_t rows = (int64_t)(selected_total_ - sel0);
-            if (ac.adjust_count < continuous_limit && (double)hits <= AutoContext::LowReduction * (double)rows) {
-                ac.pass_through_count++;
-                ac.preagg_count = ac.selective_preagg_count = 0;
-                if (ac.pass_through_count == (size_t)AutoContext::StableLimit) auto_state_ = PASS_THROUGH;
-            } else if (ac.adjust_count < continuous_limit && (double)hits >= AutoContext::HighReduction * (double)rows && mem < AutoContext::MaxHtSize) {
-                ac.preagg_count++;
-                ac.pass_through_count = ac.selective_preagg_count = 0;
-                if (ac.preagg_count == (size_t)AutoContext::StableLimit) {
-                    auto_state_ = PREAGG;
-                    ac.preagg_count = 0;
-                }
-            } else {
-                ac.selective_preagg_count++;
-                ac.pass_through_count = ac.preagg_count = 0;
-                if (ac.selective_preagg_count == (size_t)AutoContext::StableLimit) auto_state_ = SELECTIVE_PREAGG;
-            }
-            break;
-        }
-        case PASS_THROUGH: {
-            run_rows(cols, off, n, ROWS_STREAM);
-            ac.pass_through_count++;
-            if (ac.pass_through_count > continuous_limit) {
-                auto_state_ = mem < AutoContext::MaxHtSize ? FORCE_PREAGG : ADJUST;
-                ac.pass_through_count = ac.preagg_count = ac.adjust_count = 0;
-                ac.update_continuous_limit();
-            }
-            break;
-        }
-        case FORCE_PREAGG:
-        case PREAGG: {
-            run_rows(cols, off, n, ROWS_AGGREGATE);
-            ac.preagg_count++;
-            const size_t limit = auto_state_ == FORCE_PREAGG ? AutoContext::ForcePreaggLimit : AutoContext::PreaggLimit;
-            if (ac.preagg_count > limit) {
-                auto_state_ = ADJUST;
-                ac.preagg_count = ac.adjust_count = 0;
-            }
-            break;
-        }
-        case SELECTIVE_PREAGG: {
-            run_rows(cols, off, n, ROWS_SELECTIVE);
-            ac.selective_preagg_count++;
-            if (ac.selective_preagg_count > continuous_limit) {
-                auto_state_ = ADJUST;
-                ac.selective_preagg_count = ac.adjust_count = 0;
-                ac.update_continuous_limit();
-            }
-            break;
-        }
-        }
+        // AUTO: srb_stream_policy.h
+        const size_t slot_bytes = (size_t)L_.prog.slot_bytes;
+        const StreamRowMode mode = policy_.next(n, occupied_, cap_, (size_t)cap_ * slot_bytes, rows_before, stream_rows_);
+        const uint64_t sel0 = selected_total_;
+        const int64_t hits = run_rows(cols, off, n, (RowMode)mode);
+        policy_.observe(hits, (int64_t)(selected_total_ - sel0), (size_t)cap_ * slot_bytes);
     }
 
     const ColBind* strip_clear_null_maps(const ColBind* cols, int64_t off, int64_t n) {
@@ -2150,9 +2067,7 @@ private:
     int64_t stream_rows_ = 0; // pass-through rows at the front of the output arrays
     int64_t stream_seen_ = 0; // input rows the sink has been handed
     int64_t stream_unit_ = getenv("SRB_STREAM_UNIT") ? std::max<int64_t>(1, atoll(getenv("SRB_STREAM_UNIT"))) : ((int64_t)1 << 24);
-    size_t stream_l2_bytes_ = getenv("SRB_STREAM_L2_BYTES") ? (size_t)atoll(getenv("SRB_STREAM_L2_BYTES")) : ((size_t)96 << 20); // test hook
-    AutoState auto_state_ = INIT_PREAGG;
-    AutoContext auto_;
+    StreamPolicy policy_;
     bool pulled_empty_ = false;
     std::vector<HostCol> hcols_;
     std::vector<int32_t> hslots_;

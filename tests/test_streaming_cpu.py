@@ -117,3 +117,24 @@ def test_streaming_with_predicates_avg_and_decimal_keys(oracle):
         inter, st = oracle.scan_agg_streaming(plan(K.AGG_UPDATE_SERIALIZE), ch, mode, chunk_size=1000)
         got = K.chunk_rows(oracle.scan_agg(plan(K.AGG_MERGE_FINALIZE, merge=True), inter))
         assert got == want, mode
+
+
+def test_device_auto_policy_replayed_on_the_cpu(tmp_path):
+    """the device sink's AUTO policy is host-only code (starrocks_b200/csrc/srb_stream_policy.h); tests/cpp/test_stream_policy.cpp
+    replays it against a model table. All-distinct keys: one aggregated unit, StableLimit selective units, then pass-through with
+    a short FORCE_PREAGG / ADJUST excursion every continuous_limit units — the trajectory the oracle's restatement of the reference
+    shows on the same input (test_auto_passes_through_when_nothing_reduces). A small key domain: everything is aggregated."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "test_stream_policy")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-o", exe, os.path.join(root, "tests", "cpp", "test_stream_policy.cpp")])
+
+    def run(*args):
+        return [int(x) for x in subprocess.check_output([exe] + [str(a) for a in args]).split()]
+
+    # units, rows per unit, distinct, "L2" bytes -> units aggregated / passed through / selective, rows passed, groups, final state
+    assert run(400, 4096, 1, 256 * 1024) == [9, 376, 15, 391 * 4096, 9 * 4096, 2]  # 1 INIT + 2 x 4 FORCE_PREAGG; 3 x 5 ADJUST; PASS_THROUGH
+    assert run(100, 4096, 0, 256 * 1024) == [100, 0, 0, 0, 2000, 0]
+    # B200 scale: 600 M all-distinct rows in 2^24-row units against the 96 MB threshold: one unit builds a table, 587 M rows pass through
+    assert run(36, 1 << 24, 1, 96 << 20) == [1, 30, 5, 35 << 24, 1 << 24, 2]
