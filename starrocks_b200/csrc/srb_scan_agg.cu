@@ -799,6 +799,92 @@ __global__ void __launch_bounds__(256, 4) k_filter_rf(const __grid_constant__ Rf
     }
 }
 
+// Several runtime filters in ONE pass over a tile (opt-in: SRB_RF_FUSED=1, all key columns of one width): the tile's mask words stay
+// in shared memory between the filters; after each filter the list of still-selected rows is rebuilt from them, so the second and
+// third filter of a star join walk 20 % / 4 % of the rows without a kernel launch, a global mask round trip or a pass over the
+// tiles of their own. Same tests, same result as the sequence of k_filter_rf launches.
+constexpr int RF_FUSED_MAX = 4;
+struct RfMultiArgs {
+    int32_t n;
+    RfArgs f[RF_FUSED_MAX];
+};
+template <int W>
+__global__ void __launch_bounds__(256, 4) k_filter_rf_multi(const __grid_constant__ RfMultiArgs a, int64_t n, uint32_t* __restrict__ mask,
+                                                             uint32_t* __restrict__ tile_counts) {
+    using KT = typename std::conditional<W == 8, long long, typename std::conditional<W == 4, int, typename std::conditional<W == 2, short, signed char>::type>::type>::type;
+    __shared__ uint32_t smask[FTILE / 32];
+    __shared__ uint16_t sidx[FTILE];
+    __shared__ uint32_t wsum[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t tile0 = (int64_t)blockIdx.x * FTILE;
+    const int64_t w0 = tile0 >> 5, n_words = (n + 31) >> 5;
+    const uint32_t word0 = w0 + threadIdx.x < n_words ? mask[w0 + threadIdx.x] : 0u;
+    smask[threadIdx.x] = word0;
+    __syncthreads();
+    for (int fi = 0; fi < a.n; fi++) {
+        const RfArgs& f = a.f[fi];
+        // list of the rows still selected (prefix sum of the popcounts of this thread's word, as in k_filter_rf)
+        const uint32_t word = smask[threadIdx.x];
+        const uint32_t c = __popc(word);
+        uint32_t inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += y;
+        }
+        if (lane == 31) wsum[warp] = inc;
+        __syncthreads();
+        uint32_t before = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++) {
+            const uint32_t t = wsum[w];
+            before += w < warp ? t : 0;
+            total += t;
+        }
+        if (total != FTILE) {
+            uint32_t off = before + inc - c, bits = word;
+            while (bits) {
+                sidx[off++] = (uint16_t)(threadIdx.x * 32 + __ffs(bits) - 1);
+                bits &= bits - 1;
+            }
+        }
+        __syncthreads();
+        const uint32_t* dir = f.v.dir;
+        const KT* keys = (const KT*)f.data + tile0;
+        const uint8_t* nulls = f.nulls ? f.nulls + tile0 : nullptr;
+        if (total == FTILE) {
+            if (f.v.mix) {
+                if (nulls) rf_test_full<W, true, true, KT>(f, dir, keys, nulls, smask, lane);
+                else rf_test_full<W, true, false, KT>(f, dir, keys, nulls, smask, lane);
+            } else {
+                if (nulls) rf_test_full<W, false, true, KT>(f, dir, keys, nulls, smask, lane);
+                else rf_test_full<W, false, false, KT>(f, dir, keys, nulls, smask, lane);
+            }
+        } else if (total != 0) {
+            if (f.v.mix) {
+                if (nulls) rf_test_list<W, true, true, KT>(f, dir, keys, nulls, total, sidx, smask);
+                else rf_test_list<W, true, false, KT>(f, dir, keys, nulls, total, sidx, smask);
+            } else {
+                if (nulls) rf_test_list<W, false, true, KT>(f, dir, keys, nulls, total, sidx, smask);
+                else rf_test_list<W, false, false, KT>(f, dir, keys, nulls, total, sidx, smask);
+            }
+        }
+        __syncthreads(); // smask is final for this filter; wsum / sidx are free again
+    }
+    const uint32_t now = smask[threadIdx.x];
+    if (now != word0) mask[w0 + threadIdx.x] = now;
+    uint32_t kept = __popc(now);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) kept += __shfl_down_sync(0xffffffffu, kept, o);
+    if (lane == 0) wsum[warp] = kept;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int w = 0; w < 8; w++) t += wsum[w];
+        tile_counts[blockIdx.x] = t;
+    }
+}
+
 // exclusive scan of the tile counts (a few to ~10^5 entries): one block; every thread sums a contiguous run, the 1024 run
 // totals are scanned with warp shuffles, then every thread writes its run's offsets
 __global__ void __launch_bounds__(1024) k_scan_tiles(const uint32_t* __restrict__ counts, uint64_t* __restrict__ offsets, int64_t n_tiles,
@@ -1736,7 +1822,27 @@ private:
             } else {
                 k_filter_mask<<<(int)tiles, 256, 0, stream>>>(L_.prog, off, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>());
             }
+            // opt-in (SRB_RF_FUSED=1, not yet measured): every runtime filter of the scan in one pass over the tiles
+            bool fused = rf_fused_ && rfs_.size() >= 2 && rfs_.size() <= (size_t)RF_FUSED_MAX;
+            for (const auto& r : rfs_) fused = fused && P.cols[r.col].width == P.cols[rfs_[0].col].width;
+            if (fused) {
+                RfMultiArgs ma{};
+                ma.n = (int)rfs_.size();
+                const int w = P.cols[rfs_[0].col].width;
+                for (int i = 0; i < ma.n; i++) {
+                    const int ci = rfs_[i].col;
+                    ma.f[i] = RfArgs{rfs_[i].rf->view(), (const uint8_t*)cols[ci].data + (size_t)off * w, cols[ci].nulls ? cols[ci].nulls + off : nullptr};
+                }
+                switch (w) {
+                case 1: k_filter_rf_multi<1><<<(int)tiles, 256, 0, stream>>>(ma, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>()); break;
+                case 2: k_filter_rf_multi<2><<<(int)tiles, 256, 0, stream>>>(ma, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>()); break;
+                case 4: k_filter_rf_multi<4><<<(int)tiles, 256, 0, stream>>>(ma, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>()); break;
+                default: k_filter_rf_multi<8><<<(int)tiles, 256, 0, stream>>>(ma, m, mask_.as<uint32_t>(), tile_counts_.as<uint32_t>());
+                }
+                launches++;
+            }
             for (const auto& r : rfs_) { // runtime filters narrow the mask before anything is copied
+                if (fused) break;
                 const int ci = r.col;
                 const int w = P.cols[ci].width;
                 RfArgs ra{r.rf->view(), (const uint8_t*)cols[ci].data + (size_t)off * w, cols[ci].nulls ? cols[ci].nulls + off : nullptr};
@@ -2024,6 +2130,7 @@ private:
     bool lowered_ = false, filter_only_ = false;
     int shape_ = -1;
     bool force_generic_ = getenv("SRB_FORCE_GENERIC") != nullptr; // test hook: compare the two kernel families
+    bool rf_fused_ = getenv("SRB_RF_FUSED") != nullptr;           // opt-in: all runtime filters of a scan in one kernel (k_filter_rf_multi)
     bool no_shared_agg_ = getenv("SRB_NO_SHARED_AGG") != nullptr; // test / measurement hook: the interpreter updates the table per row
     bool no_partition_ = getenv("SRB_NO_PARTITION") != nullptr;   // test / measurement hook: direct table updates for every batch
     DevBuf hc_k_, hc_v_, hc_v2_, hc_ctr_;                                 // permuted (key, value) copy of the current batch + its 2 x 256 counters

@@ -1128,3 +1128,26 @@ def test_streaming_mode_misuse_is_reported(ctx):
     with pytest.raises(ops.SrbError):
         op.set_streaming_mode(7)
     op.close()
+
+
+@NOT_YET_ON_HARDWARE
+def test_fused_runtime_filters_give_the_same_rows(ctx, oracle, monkeypatch):
+    """SRB_RF_FUSED=1: the scan's three runtime filters in one pass over the tiles (k_filter_rf_multi) keep exactly the rows the three
+    k_filter_rf launches keep — the star join's stage row counts and result do not change"""
+    from starrocks_b200 import pipelines as P
+    dims, lo = _ssb_tables(600_000, 30_000, 2_000, 200_000)
+    want = K.chunk_rows(P.ssb_q41_oracle(oracle, dims, lo))
+    seen = {}
+    for fused in (False, True):
+        if fused:
+            monkeypatch.setenv("SRB_RF_FUSED", "1")
+        q = P.SsbQ41(ctx, runtime_filter=True).build(dims)
+        stage_rows = []
+        agg = q.probe(lo, stage_rows=stage_rows)
+        got = K.chunk_rows(agg.pull_all())
+        launches = q.scan_launches if hasattr(q, "scan_launches") else None
+        agg.close()
+        q.close()
+        assert got == want
+        seen[fused] = (stage_rows, launches)
+    assert seen[True][0] == seen[False][0]

@@ -5,7 +5,7 @@
 set -u
 mkdir -p gpurun_out
 # 1. the tests marked not-yet-on-hardware, run as ordinary tests (a failure here is a real failure)
-timeout 120 python -m pytest tests/test_gpu_parity.py tests/test_gpu_topn.py -m gpu -q --runxfail -k "streaming or topn or q3_ends or reference_fixture or random_rows or fewer_rows or unsupported" \
+timeout 120 python -m pytest tests/test_gpu_parity.py tests/test_gpu_topn.py -m gpu -q --runxfail -k "streaming or topn or q3_ends or reference_fixture or random_rows or fewer_rows or unsupported or fused" \
     > gpurun_out/v_unverified_tests.log 2>&1
 tail -15 gpurun_out/v_unverified_tests.log
 # 2. the whole GPU suite (about 5 minutes, most of it the high-cardinality cases)
@@ -16,6 +16,9 @@ for q in q1 q6 q3 ssb highcard; do
     timeout 120 python bench.py --query $q --steps 5 --warmup 3 --cpu-seconds 8 2> gpurun_out/v_bench_$q.err | tail -1 > gpurun_out/v_bench_$q.json
     cut -c1-220 gpurun_out/v_bench_$q.json
 done
+# 3b. A/B of the fused runtime-filter kernel on SSB
+SRB_RF_FUSED=1 timeout 60 python bench.py --query ssb --steps 5 --warmup 3 --no-cpu --no-e2e 2>/dev/null | tail -1 > gpurun_out/v_bench_ssb_fused.json
+cut -c1-220 gpurun_out/v_bench_ssb_fused.json
 # 4. launch lists of the two join pipelines (library kernels only)
 for q in q3 ssb; do
     timeout 90 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:^k_ -c 400 --csv --log-file gpurun_out/v_${q}_launches.csv \
