@@ -1073,28 +1073,20 @@ def _stream_gpu(ctx, plan, chunk, mode, piece_rows=0):
     return out, st
 
 
-# The pass-through kernel (k_stream_rows) was written after this round's GPU minutes were spent: the one run these tests got
-# went through a staging path that bypassed it (fixed since). Until they have run on a B200 they may not fail the suite.
-NOT_YET_ON_HARDWARE = pytest.mark.xfail(strict=False, reason="k_stream_rows has not run on hardware yet (round-1 GPU budget spent)")
+def test_streaming_mode_misuse_is_reported(ctx):
+    from starrocks_b200 import ops
+    op = ops.ScanAggOperator(ctx, Q.highcard_plan())  # update + finalize: not the first phase of a two-phase aggregation
+    with pytest.raises(ops.SrbError) as ei:
+        op.set_streaming_mode(K.STREAMING_AUTO)
+    assert ei.value.code == K.INVALID_ARGUMENT
+    op.close()
+    op = ops.ScanAggOperator(ctx, Q.highcard_plan(phase=K.AGG_UPDATE_SERIALIZE))
+    with pytest.raises(ops.SrbError):
+        op.set_streaming_mode(7)
+    op.close()
 
 
-@NOT_YET_ON_HARDWARE
-def test_force_streaming_passes_every_row_through_in_intermediate_format(ctx, oracle):
-    from tests.test_streaming_cpu import hc_chunk
-    rng = np.random.default_rng(21)
-    n = 50_000
-    ch = hc_chunk(rng.integers(0, 50, n), rng.integers(-1000, 1000, n), (rng.random(n) < 0.1).astype(np.uint8))
-    plan = Q.highcard_plan(phase=K.AGG_UPDATE_SERIALIZE)
-    want, _ = oracle.scan_agg_streaming(plan, ch, K.STREAMING_FORCE_STREAMING)
-    for piece in (0, 4096):
-        got, st = _stream_gpu(ctx, plan, ch, K.STREAMING_FORCE_STREAMING, piece)
-        assert got.n_rows == n and st["rows_streamed"] == n and st["groups"] == 0
-        assert K.chunk_rows(got) == K.chunk_rows(want)  # the same multiset of (k, value-or-NULL, 1) rows; order is not kept
-
-
-@pytest.mark.parametrize("mode", [pytest.param(K.STREAMING_AUTO, marks=NOT_YET_ON_HARDWARE), pytest.param(K.STREAMING_FORCE_STREAMING, marks=NOT_YET_ON_HARDWARE),
-                                  K.STREAMING_FORCE_PREAGGREGATION])
-def test_streaming_sink_phase_two_result_does_not_depend_on_the_mode(ctx, oracle, mode, monkeypatch):
+def check_streaming_mode(ctx, oracle, mode, monkeypatch):
     """heavy repetition, then all-distinct keys, then moderate repetition, pushed in 4096-row chunks with a 4096-row AUTO unit: the
     AUTO machine leaves INIT_PREAGG, passes rows through and comes back; whatever it does, phase 2 over the sink's output equals
     the one-phase result (oracle), and FORCE_PREAGGREGATION equals the blocking first phase"""
@@ -1117,37 +1109,6 @@ def test_streaming_sink_phase_two_result_does_not_depend_on_the_mode(ctx, oracle
     assert got == K.chunk_rows(oracle.scan_agg(Q.highcard_plan(), ch))
 
 
-def test_streaming_mode_misuse_is_reported(ctx):
-    from starrocks_b200 import ops
-    op = ops.ScanAggOperator(ctx, Q.highcard_plan())  # update + finalize: not the first phase of a two-phase aggregation
-    with pytest.raises(ops.SrbError) as ei:
-        op.set_streaming_mode(K.STREAMING_AUTO)
-    assert ei.value.code == K.INVALID_ARGUMENT
-    op.close()
-    op = ops.ScanAggOperator(ctx, Q.highcard_plan(phase=K.AGG_UPDATE_SERIALIZE))
-    with pytest.raises(ops.SrbError):
-        op.set_streaming_mode(7)
-    op.close()
-
-
-@NOT_YET_ON_HARDWARE
-def test_fused_runtime_filters_give_the_same_rows(ctx, oracle, monkeypatch):
-    """SRB_RF_FUSED=1: the scan's three runtime filters in one pass over the tiles (k_filter_rf_multi) keep exactly the rows the three
-    k_filter_rf launches keep — the star join's stage row counts and result do not change"""
-    from starrocks_b200 import pipelines as P
-    dims, lo = _ssb_tables(600_000, 30_000, 2_000, 200_000)
-    want = K.chunk_rows(P.ssb_q41_oracle(oracle, dims, lo))
-    seen = {}
-    for fused in (False, True):
-        if fused:
-            monkeypatch.setenv("SRB_RF_FUSED", "1")
-        q = P.SsbQ41(ctx, runtime_filter=True).build(dims)
-        stage_rows = []
-        agg = q.probe(lo, stage_rows=stage_rows)
-        got = K.chunk_rows(agg.pull_all())
-        launches = q.scan_launches if hasattr(q, "scan_launches") else None
-        agg.close()
-        q.close()
-        assert got == want
-        seen[fused] = (stage_rows, launches)
-    assert seen[True][0] == seen[False][0]
+def test_streaming_sink_force_preaggregation_is_the_blocking_first_phase(ctx, oracle, monkeypatch):
+    # the modes that pass rows through run in tests/test_gpu_unverified.py until they have been on hardware
+    check_streaming_mode(ctx, oracle, K.STREAMING_FORCE_PREAGGREGATION, monkeypatch)

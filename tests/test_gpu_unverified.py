@@ -1,0 +1,65 @@
+"""GPU tests of kernels that were written after round 1's GPU minutes were spent and have not run on a B200 yet: the streaming
+sink's pass-through kernel (k_stream_rows) and the opt-in fused runtime-filter kernel (k_filter_rf_multi).
+They are xfail(strict=False): they run, their outcome is reported, and they cannot fail the suite. This module sorts after
+test_gpu_parity.py / test_gpu_topn.py so that a kernel fault here cannot reach tests that have passed on hardware.
+`tools/verify_on_gpu.sh` runs them with --runxfail."""
+import numpy as np
+import pytest
+
+from starrocks_b200 import capi as K
+from starrocks_b200 import queries as Q
+from tests.test_gpu_parity import _ssb_tables, _stream_gpu, check_streaming_mode
+
+pytestmark = [pytest.mark.gpu, pytest.mark.xfail(strict=False, reason="not yet run on hardware (round-1 GPU budget spent)")]
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from starrocks_b200 import ops
+    c = ops.Context(device=0, chunk_size=4096)
+    yield c
+    try:
+        c.close()
+    except Exception as e:  # a fault in one of these kernels leaves a sticky CUDA error behind
+        import warnings
+        warnings.warn(f"context close after unverified kernels: {e}")
+
+
+def test_force_streaming_passes_every_row_through_in_intermediate_format(ctx, oracle):
+    from tests.test_streaming_cpu import hc_chunk
+    rng = np.random.default_rng(21)
+    n = 50_000
+    ch = hc_chunk(rng.integers(0, 50, n), rng.integers(-1000, 1000, n), (rng.random(n) < 0.1).astype(np.uint8))
+    plan = Q.highcard_plan(phase=K.AGG_UPDATE_SERIALIZE)
+    want, _ = oracle.scan_agg_streaming(plan, ch, K.STREAMING_FORCE_STREAMING)
+    for piece in (0, 4096):
+        got, st = _stream_gpu(ctx, plan, ch, K.STREAMING_FORCE_STREAMING, piece)
+        assert got.n_rows == n and st["rows_streamed"] == n and st["groups"] == 0
+        assert K.chunk_rows(got) == K.chunk_rows(want)  # the same multiset of (k, value-or-NULL, 1) rows; order is not kept
+
+
+@pytest.mark.parametrize("mode", [K.STREAMING_AUTO, K.STREAMING_FORCE_STREAMING])
+def test_streaming_sink_phase_two_result_does_not_depend_on_the_mode(ctx, oracle, mode, monkeypatch):
+    check_streaming_mode(ctx, oracle, mode, monkeypatch)
+
+
+def test_fused_runtime_filters_give_the_same_rows(ctx, oracle, monkeypatch):
+    """SRB_RF_FUSED=1: the scan's three runtime filters in one pass over the tiles (k_filter_rf_multi) keep exactly the rows the three
+    k_filter_rf launches keep — the star join's stage row counts and result do not change"""
+    from starrocks_b200 import pipelines as P
+    dims, lo = _ssb_tables(600_000, 30_000, 2_000, 200_000)
+    want = K.chunk_rows(P.ssb_q41_oracle(oracle, dims, lo))
+    seen = {}
+    for fused in (False, True):
+        if fused:
+            monkeypatch.setenv("SRB_RF_FUSED", "1")
+        q = P.SsbQ41(ctx, runtime_filter=True).build(dims)
+        stage_rows = []
+        agg = q.probe(lo, stage_rows=stage_rows)
+        got = K.chunk_rows(agg.pull_all())
+        launches = q.scan_launches if hasattr(q, "scan_launches") else None
+        agg.close()
+        q.close()
+        assert got == want
+        seen[fused] = (stage_rows, launches)
+    assert seen[True][0] == seen[False][0]

@@ -5,8 +5,7 @@
 set -u
 mkdir -p gpurun_out
 # 1. the tests marked not-yet-on-hardware, run as ordinary tests (a failure here is a real failure)
-timeout 120 python -m pytest tests/test_gpu_parity.py tests/test_gpu_topn.py -m gpu -q --runxfail -k "streaming or topn or q3_ends or reference_fixture or random_rows or fewer_rows or unsupported or fused" \
-    > gpurun_out/v_unverified_tests.log 2>&1
+timeout 180 python -m pytest tests/test_gpu_topn.py tests/test_gpu_unverified.py -m gpu -q --runxfail > gpurun_out/v_unverified_tests.log 2>&1
 tail -15 gpurun_out/v_unverified_tests.log
 # 2. the whole GPU suite (about 5 minutes, most of it the high-cardinality cases)
 timeout 420 python -m pytest tests -m gpu -x -q > gpurun_out/v_gpu_suite.log 2>&1
