@@ -324,6 +324,35 @@ struct Aggregator {
         return hits;
     }
 
+    // build_hash_map_with_selection / build_hash_map_with_selection_and_allocation (agg_hash_map.h:298-339, aggregator.h:620-641):
+    // not_found[i] = 1 when row i's key is absent; with `allocate` an absent key is inserted as it is met, so that a later row of
+    // the same chunk with that key is found
+    void lookup_selection(const srb_chunk& ch, bool allocate, std::vector<uint8_t>& not_found) {
+        std::vector<uint32_t> idx((size_t)ch.n_rows);
+        for (size_t i = 0; i < idx.size(); i++) idx[i] = (uint32_t)i;
+        not_found.assign(idx.size(), 0);
+        if (idx.empty()) return;
+        ExprEval ev(plan->nodes, plan->n_nodes, &ch, 0, &idx);
+        std::vector<const Col*> keys(plan->n_keys);
+        for (int k = 0; k < plan->n_keys; k++) keys[k] = &ev.eval(plan->key_nodes[k]);
+        if (!key_meta_known) {
+            for (int k = 0; k < plan->n_keys; k++) key_meta.push_back({keys[k]->type, keys[k]->precision, keys[k]->scale, keys[k]->nullable});
+            key_meta_known = true;
+        }
+        std::string kb;
+        size_t g;
+        for (size_t i = 0; i < idx.size(); i++) {
+            serialize_key(keys, i, kb);
+            if (table.find(kb, &g)) continue;
+            not_found[i] = 1;
+            if (allocate) {
+                bool created;
+                table.emplace(kb, &created);
+                if (created) states.resize(states.size() + n_aggs);
+            }
+        }
+    }
+
     int64_t rows_streamed = 0;
     // returns the number of rows whose group already existed (the streaming sink's hit count)
     size_t push_rows(const srb_chunk& ch, int64_t base, size_t rows, RowMode mode = ROWS_AGGREGATE) {

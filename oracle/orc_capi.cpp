@@ -38,6 +38,28 @@ void* orc_scan_agg_streaming(const srb_scan_agg_plan* plan, const srb_chunk* in,
         return nullptr;
     }
 }
+// The streaming sink's table lookups on a sequence of key chunks (be/test/exec/agg_hash_map_test.cpp:232-275): ops[i] = 0 aggregate
+// the chunk (build_hash_map), 1 build_hash_map_with_selection, 2 build_hash_map_with_selection_and_allocation; not_found receives
+// the concatenated per-row flags of the chunks run with ops 1 and 2
+int orc_agg_lookup_sequence(const srb_scan_agg_plan* plan, int n_chunks, const srb_chunk* const* chunks, const int32_t* ops, uint8_t* not_found) {
+    try {
+        orc::Aggregator ag(plan);
+        size_t out = 0;
+        for (int c = 0; c < n_chunks; c++) {
+            if (ops[c] == 0) {
+                ag.push_rows(*chunks[c], 0, (size_t)chunks[c]->n_rows);
+                continue;
+            }
+            std::vector<uint8_t> nf;
+            ag.lookup_selection(*chunks[c], ops[c] == 2, nf);
+            for (uint8_t x : nf) not_found[out++] = x;
+        }
+        return 0;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return 1;
+    }
+}
 // ORDER BY key_slots (is_asc / nulls_first per key) OFFSET offset LIMIT limit (limit < 0: every row)
 void* orc_sort(const srb_chunk* in, int n_keys, const int32_t* key_slots, const uint8_t* is_asc, const uint8_t* nulls_first, int64_t offset,
                int64_t limit) {

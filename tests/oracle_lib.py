@@ -28,6 +28,8 @@ class Oracle:
         L.orc_last_error.restype = C.c_char_p
         L.orc_scan_agg.restype = C.c_void_p
         L.orc_scan_agg.argtypes = [C.POINTER(K.srb_scan_agg_plan), C.POINTER(K.srb_chunk), C.c_int, C.c_int]
+        L.orc_agg_lookup_sequence.restype = C.c_int
+        L.orc_agg_lookup_sequence.argtypes = [C.POINTER(K.srb_scan_agg_plan), C.c_int, C.POINTER(C.POINTER(K.srb_chunk)), C.POINTER(C.c_int32), C.POINTER(C.c_uint8)]
         L.orc_sort.restype = C.c_void_p
         L.orc_sort.argtypes = [C.POINTER(K.srb_chunk), C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_uint8), C.POINTER(C.c_uint8), C.c_int64, C.c_int64]
         L.orc_scan_agg_streaming.restype = C.c_void_p
@@ -112,6 +114,22 @@ class Oracle:
             self.lib.orc_result_free(r)
         names = ["init_preagg", "adjust", "pass_through", "force_preagg", "preagg", "selective_preagg"]
         return out, {"rows_streamed": stats[0], "groups": stats[1], "chunks": dict(zip(names, list(stats[2:8]))), "final_state": names[stats[8]]}
+
+    def agg_lookup_sequence(self, plan, chunks, ops):
+        """ops[i]: 0 build_hash_map, 1 build_hash_map_with_selection, 2 build_hash_map_with_selection_and_allocation on chunks[i];
+        returns the not-found flags of every chunk run with op 1 or 2"""
+        cs = [c.to_c() for c in chunks]
+        arr = (C.POINTER(K.srb_chunk) * len(chunks))(*[C.pointer(c[0]) for c in cs])
+        n_out = sum(c.n_rows for c, o in zip(chunks, ops) if o)
+        out = (C.c_uint8 * max(1, n_out))()
+        if self.lib.orc_agg_lookup_sequence(C.byref(plan.c), len(chunks), arr, (C.c_int32 * len(ops))(*ops), out):
+            raise RuntimeError("oracle: " + self._err())
+        flat, res, pos = list(out)[:n_out], [], 0
+        for c, o in zip(chunks, ops):
+            if o:
+                res.append(flat[pos:pos + c.n_rows])
+                pos += c.n_rows
+        return res
 
     def sort(self, chunk: K.Chunk, key_slots, is_asc, nulls_first, offset: int = 0, limit: int = -1) -> K.Chunk:
         """ORDER BY ... OFFSET ... LIMIT (ChunksSorterTopn / ChunksSorterFullSort): every column, rows in sorted order"""

@@ -512,3 +512,25 @@ def test_sort_is_stable_and_carries_every_column(oracle):
     assert cust_keys(out) == [71, 69, 70, 2, 12, 41, 54, 58, 4, 16, 49, 55, 6, 24, 52, 56]
     rows_in = {r[0]: r for r in K.chunk_rows(ch)}
     assert all(rows_in[r[0]] == r for r in K.chunk_rows(out))
+
+
+# ---- be/test/exec/agg_hash_map_test.cpp:232-292 (AggHashMapKeyNotFoundsTest): the streaming sink's lookups. Five key chunks; the first
+#      is aggregated, the others run build_hash_map_with_selection (1) / ..._and_allocation (2); expected not-found flags :290 ---------
+LOOKUP_DATA = [[1, 2, 1, 1], [1, 2, 1, 1], [1, 2, 3, 3], [4, 4, 4, 4], [5, 5, 5, 5]]
+LOOKUP_OPS = [0, 1, 2, 1, 2]
+LOOKUP_EXPECT = [[0, 0, 0, 0], [0, 0, 1, 0], [1, 1, 1, 1], [1, 0, 0, 0]]
+
+
+@pytest.mark.parametrize("kind", ["int32", "nullable int32", "string", "nullable string", "int32 + int32 (fixed-size serialized key)"])
+def test_agg_hash_map_not_found_selection(oracle, kind):
+    def col(vals):
+        nulls = np.zeros(len(vals), np.uint8) if "nullable" in kind else None
+        if "string" in kind:
+            return K.Column.from_strings([str(v).encode() for v in vals], nulls)
+        return K.Column.from_ints(K.TYPE_INT, np.array(vals, np.int32), nulls)
+    two = kind.startswith("int32 +")
+    chunks = [K.Chunk(4, {0: col(v), **({1: col([7] * 4)} if two else {})}) for v in LOOKUP_DATA]
+    e = ExprBuilder()
+    keys = [e.slot(0, K.TYPE_VARCHAR if "string" in kind else K.TYPE_INT)] + ([e.slot(1, K.TYPE_INT)] if two else [])
+    plan = ScanAggPlan(exprs=e, keys=keys, aggs=[(K.AGG_COUNT, None)], phase=K.AGG_UPDATE_SERIALIZE)
+    assert oracle.agg_lookup_sequence(plan, chunks, LOOKUP_OPS) == LOOKUP_EXPECT
