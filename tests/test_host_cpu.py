@@ -100,3 +100,11 @@ def test_oracle_runs_the_benchmark_pipelines(oracle):
     ship, disc, qty, ext = (ch.columns[s].data for s in (Q.L_SHIPDATE, Q.L_DISCOUNT, Q.L_QUANTITY, Q.L_EXTENDEDPRICE))
     m = (ship >= Q.from_date(1994, 1, 1)) & (ship < Q.from_date(1995, 1, 1)) & (disc >= 5) & (disc <= 7) & (qty < 2400)
     assert K.column_pyvalues(r6.columns[0])[0] == int((ext[m].astype(object) * disc[m].astype(object)).sum())
+
+
+def test_boundary_header_is_plain_c():
+    """the drop-in boundary is a C ABI: include/srb/srb_c_api.h compiles as C99 on its own (no C++ types, no missing includes)"""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-fsyntax-only", "-x", "c", os.path.join(root, "include", "srb", "srb_c_api.h")])
