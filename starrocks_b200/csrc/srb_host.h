@@ -6,6 +6,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
@@ -42,6 +43,20 @@ inline std::string fmt(const char* f, ...) {
             throw srb::Error(_e == cudaErrorMemoryAllocation ? SRB_MEM_LIMIT_EXCEEDED : SRB_INTERNAL_ERROR,       \
                              srb::fmt("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__)); \
     } while (0)
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute: one flag per (kernel, device), set with that device
+// current. Racing first calls both set it (idempotent); the return code is checked.
+struct SmemOptIn {
+    std::atomic<uint8_t> done[64] = {};
+    template <class F>
+    void set(F* kernel, int bytes) {
+        int d = 0;
+        SRB_CUDA(cudaGetDevice(&d));
+        if (d >= 0 && d < 64 && done[d].load(std::memory_order_acquire)) return;
+        SRB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        if (d >= 0 && d < 64) done[d].store(1, std::memory_order_release);
+    }
+};
 
 inline int type_width(int t) {
     switch (t) {

@@ -409,30 +409,36 @@ __global__ void __launch_bounds__(256) k_stream_rows(const __grid_constant__ DPr
     unsigned long long selected = 0, too_long = 0, hits = 0;
     const int lane = threadIdx.x & 31;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const int64_t row = base + i;
-        if (!eval_preds(p, row)) continue;
-        selected++;
-        for (int k = 0; k < p.n_nodes; k++) v[k] = eval_node(p.nodes[k], v, p.cols, row);
-        const PackedKey k = pack_key(p, v, row);
-        if (k.too_long) {
-            too_long++;
-            continue;
+    // the loop bound is warp-uniform (a warp's 32 rows are consecutive), so every lane reaches the ballot below in every iteration
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); i0 < n; i0 += stride) {
+        const int64_t row = base + i0 + lane;
+        bool pass = i0 + lane < n && eval_preds(p, row);
+        PackedKey k{};
+        if (pass) {
+            selected++;
+            for (int q = 0; q < p.n_nodes; q++) v[q] = eval_node(p.nodes[q], v, p.cols, row);
+            k = pack_key(p, v, row);
+            if (k.too_long) {
+                too_long++;
+                pass = false;
+            }
         }
-        if (selective) {
+        if (pass && selective) {
             uint8_t* slot = table_find(tv, k.lo, k.hi, hash_packed_key(k, p.phase_seed));
             if (slot) {
                 for (int a = 0; a < p.n_aggs; a++) update_agg_global(p, p.aggs[a], slot, v, row);
                 hits++;
-                continue;
+                pass = false;
             }
         }
-        // the lanes that arrive here together reserve their output rows with one atomic
-        const unsigned int m = __activemask();
+        // the lanes that pass a row through reserve their output rows with one atomic
+        const unsigned int m = __ballot_sync(0xffffffffu, pass);
+        if (m == 0) continue;
         const int leader = __ffs(m) - 1;
         unsigned long long first = 0;
         if (lane == leader) first = atomicAdd(&ctr->emitted, (unsigned long long)__popc(m));
-        first = __shfl_sync(m, first, leader);
+        first = __shfl_sync(0xffffffffu, first, leader);
+        if (!pass) continue;
         const int64_t pos = row_base + (int64_t)first + __popc(m & ((1u << lane) - 1u));
         ea.keys[pos] = make_ulonglong2(k.lo, p.key_words > 1 ? k.hi : 0ULL);
         for (int a = 0; a < p.n_aggs; a++) {
@@ -1463,12 +1469,9 @@ private:
             hv.src[1] = (const uint64_t*)cols[vc2].data + off;
             hv.dst[1] = hc_v2_.as<uint64_t>();
         }
-        static bool configured = false;
-        if (!configured) {
-            cudaFuncSetAttribute(k_hc_scatter<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HcSmem<1>));
-            cudaFuncSetAttribute(k_hc_scatter<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HcSmem<2>));
-            configured = true;
-        }
+        static SmemOptIn opt1, opt2; // per (kernel, device)
+        opt1.set(k_hc_scatter<1>, (int)sizeof(HcSmem<1>));
+        opt2.set(k_hc_scatter<2>, (int)sizeof(HcSmem<2>));
         k_hc_hist<<<ctx->n_sms * 2, 1024, 0, stream>>>(keys, n, P.phase_seed, cap_ - 1, shift, hist);
         k_hc_scan<<<1, HC_PARTS, 0, stream>>>(hist, cursor);
         if (nv == 1)
@@ -1621,8 +1624,10 @@ private:
             size_t words = (size_t)((n + 31) / 32);
             for (int i = 0; i < 2; i++)
                 if (defer_[i].bytes < words * 4) {
+                    // ensure() rounds the size up and the pool hands back dirty memory: clear ALL of it, since a later, larger batch
+                    // that still fits uses words past this batch's count without coming through here again
                     defer_[i].ensure(ctx, words * 4);
-                    SRB_CUDA(cudaMemsetAsync(defer_[i].p, 0, words * 4, stream));
+                    SRB_CUDA(cudaMemsetAsync(defer_[i].p, 0, defer_[i].bytes, stream));
                 }
         }
         TableView tv = view();
@@ -1631,7 +1636,7 @@ private:
         int64_t covered = 0;
         Counters* dc = ctr_dev_.as<Counters>();
         if (shape_ >= 0 && !defer_in && !force_generic_) {
-            covered = launch_static_shape(shape_, L_.prog, tv, off, n, dout, &dc->rows_selected, &dc->deferred, &dc->inserted, ctx->n_sms, stream);
+            covered = launch_static_shape(shape_, L_.prog, tv, off, n, dout, &dc->rows_selected, &dc->deferred, &dc->inserted, ctx->n_sms, stream, !no_narrow_);
             if (covered) {
                 launches++;
                 static_launches_++;
@@ -1871,7 +1876,10 @@ private:
                 if (L_.cols[ci].nullable) grow_out(fout_[k].nulls, (size_t)out_rows_, (size_t)(out_rows_ + sel));
                 ca.cols[k].src = (const uint8_t*)cols[ci].data + (size_t)off * w;
                 ca.cols[k].dst = fout_[k].data.as<uint8_t>() + (size_t)out_rows_ * w;
-                ca.cols[k].src_null = L_.cols[ci].nullable ? cols[ci].nulls + off : nullptr;
+                // a later device chunk may come without a null map for a slot that had one before: its rows are all non-NULL
+                ca.cols[k].src_null = (L_.cols[ci].nullable && cols[ci].nulls) ? cols[ci].nulls + off : nullptr;
+                if (L_.cols[ci].nullable && !cols[ci].nulls && sel > 0)
+                    SRB_CUDA(cudaMemsetAsync(fout_[k].nulls.as<uint8_t>() + out_rows_, 0, (size_t)sel, stream));
                 ca.cols[k].dst_null = L_.cols[ci].nullable ? fout_[k].nulls.as<uint8_t>() + out_rows_ : nullptr;
                 ca.cols[k].width = w;
             }
@@ -2130,6 +2138,7 @@ private:
     bool lowered_ = false, filter_only_ = false;
     int shape_ = -1;
     bool force_generic_ = getenv("SRB_FORCE_GENERIC") != nullptr; // test hook: compare the two kernel families
+    bool no_narrow_ = getenv("SRB_NO_NARROW") != nullptr;         // test / measurement hook: the static kernels' general tile body only
     bool rf_fused_ = getenv("SRB_RF_FUSED") != nullptr;           // opt-in: all runtime filters of a scan in one kernel (k_filter_rf_multi)
     bool no_shared_agg_ = getenv("SRB_NO_SHARED_AGG") != nullptr; // test / measurement hook: the interpreter updates the table per row
     bool no_partition_ = getenv("SRB_NO_PARTITION") != nullptr;   // test / measurement hook: direct table updates for every batch

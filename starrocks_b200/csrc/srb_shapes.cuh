@@ -1414,7 +1414,7 @@ inline bool lower_ranges(const DProg& p, StaticArgs& sa) {
 
 template <class S>
 inline int64_t launch_shape(const DProg& p, const TableView& tv, int64_t base, int64_t n, uint32_t* defer_out, unsigned long long* rows_selected,
-                            unsigned long long* deferred, unsigned long long* inserted, int n_sms, cudaStream_t stream) {
+                            unsigned long long* deferred, unsigned long long* inserted, int n_sms, cudaStream_t stream, bool allow_narrow) {
     constexpr int TILE = tile_rows<S>();
     StaticArgs sa{};
     // stage layout: the columns of the LOAD nodes first, in node order (compile-time offsets), then predicate-only columns
@@ -1451,13 +1451,10 @@ inline int64_t launch_shape(const DProg& p, const TableView& tv, int64_t base, i
         sa.preds[i] = SPred{sa.col_off[d.col], p.cols[d.col].width, pred_opmask(d.op), d.group, d.lit_lo, d.lit_hi};
     }
     if (!lower_ranges(p, sa)) sa.n_ranges = -1;
-    sa.narrow_ok = (narrow_literals_ok<S>(p) && !getenv("SRB_NO_NARROW")) ? 1 : 0; // the env hook: A/B runs and tests of the general body
+    sa.narrow_ok = (allow_narrow && narrow_literals_ok<S>(p)) ? 1 : 0; // allow_narrow = 0: A/B runs and tests of the general body (SRB_NO_NARROW)
     const size_t smem = (size_t)sa.acc_off + acc_bytes;
-    static bool configured = false;
-    if (!configured) {
-        cudaFuncSetAttribute(k_scan_agg_static<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM_BUDGET);
-        configured = true;
-    }
+    static SmemOptIn opt_in; // per (shape, device)
+    opt_in.set(k_scan_agg_static<S>, ST_SMEM_BUDGET);
     const int grid = (int)(n_tiles < n_sms ? n_tiles : n_sms);
     StaticCtr ctr{rows_selected, deferred, inserted};
     k_scan_agg_static<S><<<grid, S::THREADS + 32, smem, stream>>>(p, sa, tv, base, n_tiles, defer_out, ctr);
@@ -1470,13 +1467,13 @@ inline int64_t launch_shape(const DProg& p, const TableView& tv, int64_t base, i
 // runs the generic kernel over the remaining rows.
 inline int64_t launch_static_shape(int shape, const DProg& p, const TableView& tv, int64_t base, int64_t n, uint32_t* defer_out,
                                    unsigned long long* rows_selected, unsigned long long* deferred, unsigned long long* inserted, int n_sms,
-                                   cudaStream_t stream) {
+                                   cudaStream_t stream, bool allow_narrow = true) {
     switch (shape) {
-    case 0: return launch_shape<ShapeSumMulFast>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
-    case 1: return launch_shape<ShapeQ1Dict>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
-    case 2: return launch_shape<ShapeHighCard>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
-    case 3: return launch_shape<ShapeQ3Agg>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
-    case 4: return launch_shape<ShapeHighCardMerge>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream);
+    case 0: return launch_shape<ShapeSumMulFast>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream, allow_narrow);
+    case 1: return launch_shape<ShapeQ1Dict>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream, allow_narrow);
+    case 2: return launch_shape<ShapeHighCard>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream, allow_narrow);
+    case 3: return launch_shape<ShapeQ3Agg>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream, allow_narrow);
+    case 4: return launch_shape<ShapeHighCardMerge>(p, tv, base, n, defer_out, rows_selected, deferred, inserted, n_sms, stream, allow_narrow);
     }
     return 0;
 }

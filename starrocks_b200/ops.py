@@ -244,6 +244,23 @@ class _Operator:
         st = _check(getattr(self.L, self._pull_device)(self.h, C.byref(out)))
         return None if st == K.END_OF_FILE else _raw_chunk(out)
 
+    def set_cancelled(self):
+        _check(self.L.srb_op_cancel(self.h))
+
+    def sync(self):
+        _check(self.L.srb_op_sync(self.h))
+
+    def counters(self):
+        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
+        _check(self.L.srb_op_counters(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"rows_in": a.value, "rows_selected": b.value, "kernel_launches": c.value}
+
+    def close(self):
+        """Operator::close (operator.h:92): idempotent"""
+        if self.h:
+            self.L.srb_op_close(self.h)
+            self.h = None
+
 
 class ScanAggOperator(_Operator):
     """scan-filter -> project -> aggregate for one driver (see include/srb/srb_c_api.h: srb_scan_agg_create)."""
@@ -253,9 +270,6 @@ class ScanAggOperator(_Operator):
         _check(ctx.L.srb_scan_agg_create(ctx.h, C.byref(plan.c), C.byref(h)))
         super().__init__(ctx, h)
         self._plan = plan
-
-    def set_cancelled(self):
-        _check(self.L.srb_op_cancel(self.h))
 
     def add_runtime_filter(self, rf: "RuntimeFilter", slot_id: int):
         """scan-filter plans only, before the first push_chunk (Operator::eval_runtime_bloom_filters)"""
@@ -273,26 +287,13 @@ class ScanAggOperator(_Operator):
         names = ["init_preagg", "adjust", "pass_through", "force_preagg", "preagg", "selective_preagg"]
         return {"rows_streamed": a.value, "groups": b.value, "state": names[c.value]}
 
-    def sync(self):
-        _check(self.L.srb_op_sync(self.h))
-
     def stream(self) -> int:
         return self.L.srb_op_stream(self.h)
-
-    def counters(self):
-        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
-        _check(self.L.srb_op_counters(self.h, C.byref(a), C.byref(b), C.byref(c)))
-        return {"rows_in": a.value, "rows_selected": b.value, "kernel_launches": c.value}
 
     def profile(self):
         ms, b, sl, sh = C.c_double(), C.c_int64(), C.c_int64(), C.c_int32()
         _check(self.L.srb_op_profile(self.h, C.byref(ms), C.byref(b), C.byref(sl), C.byref(sh)))
         return {"kernel_ms": ms.value, "batches": b.value, "static_launches": sl.value, "shape": sh.value}
-
-    def close(self):
-        if self.h:
-            self.L.srb_op_close(self.h)
-            self.h = None
 
 
 class RuntimeFilter:
@@ -341,11 +342,6 @@ class HashJoinOperator(_Operator):
         self._plan = plan
         self.probe = _ProbeSide(ctx, h)
 
-    def counters(self):
-        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
-        _check(self.L.srb_op_counters(self.h, C.byref(a), C.byref(b), C.byref(c)))
-        return {"rows_in": a.value, "rows_selected": b.value, "kernel_launches": c.value}
-
     def build_runtime_filter(self, key_index: int = 0, expected_rows: int = 0, mix: bool = False) -> "RuntimeFilter":
         """after set_finishing: the partial runtime filter over build key `key_index` (HashJoinBuildOperator -> RuntimeBloomFilter).
         mix=False hashes as the reference tree builds (identity); mix=True applies phmap_mix<8> (ENABLE_PHMAP_MIX)"""
@@ -371,11 +367,6 @@ class TopNOperator(_Operator):
         h = C.c_void_p()
         _check(ctx.L.srb_topn_create(ctx.h, C.byref(plan), C.byref(h)))
         super().__init__(ctx, h)
-
-    def counters(self):
-        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
-        _check(self.L.srb_op_counters(self.h, C.byref(a), C.byref(b), C.byref(c)))
-        return {"rows_in": a.value, "rows_selected": b.value, "kernel_launches": c.value}
 
 
 def run_scan_agg(ctx: Context, plan, chunk: K.Chunk, piece_rows: int = 0) -> K.Chunk:

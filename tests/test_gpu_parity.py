@@ -377,6 +377,63 @@ def test_table_growth_and_deferred_rows(ctx, oracle):
     check(ctx, oracle, plan, ch, piece_rows=50000)
 
 
+def _push_device_chunks(ctx, plan, chunks):
+    from starrocks_b200 import ops
+    op = ops.ScanAggOperator(ctx, plan)
+    ptrs = []
+    try:
+        for ch in chunks:
+            dch, pp = ctx.device_chunk(ch)
+            ptrs += pp
+            op.push_chunk(dch)
+        op.set_finishing()
+        return op.pull_all()
+    finally:
+        op.close()
+        for q in ptrs:
+            ctx.device_free(q)
+
+
+def test_deferral_bitmaps_are_clean_when_device_chunks_grow(ctx, oracle):
+    # regression (round-1 advice): the two deferral bitmaps come dirty from the buffer pool with a rounded-up size; a second, larger
+    # device chunk that still fits must not see stale bits when its rows are deferred and replayed (rows would be counted twice)
+    rng = np.random.default_rng(77)
+    e = ExprBuilder()
+    k, v = e.slot(0, K.TYPE_BIGINT), e.slot(1, K.TYPE_BIGINT)
+    plan = ScanAggPlan(exprs=e, keys=[k], aggs=[(K.AGG_SUM, v), (K.AGG_COUNT, None)])
+    for attempt in range(3):
+        # dirty 16 KB buffers into the pool: filter-only results of 4096 all-ones INT rows
+        for _ in range(3):
+            ones = K.Chunk(4096, {0: K.Column.from_ints(K.TYPE_INT, np.full(4096, -1, np.int32))})
+            _push_device_chunks(ctx, ScanAggPlan(preds=[], out_slots=[0]), [ones])
+        n1, n2 = 100_000, 120_000
+        c1 = K.Chunk(n1, {0: K.Column.from_ints(K.TYPE_BIGINT, rng.integers(0, 100, n1)), 1: K.Column.from_ints(K.TYPE_BIGINT, rng.integers(0, 1000, n1))})
+        c2 = K.Chunk(n2, {0: K.Column.from_ints(K.TYPE_BIGINT, rng.integers(0, 50_000, n2)), 1: K.Column.from_ints(K.TYPE_BIGINT, rng.integers(0, 1000, n2))})
+        got = _push_device_chunks(ctx, plan, [c1, c2])
+        both = K.Chunk(n1 + n2, {s: K.Column.from_ints(K.TYPE_BIGINT, np.concatenate([c1.columns[s].data, c2.columns[s].data])) for s in (0, 1)})
+        want = oracle.scan_agg(plan, both)
+        assert K.chunk_rows(got, True) == K.chunk_rows(want, True)
+
+
+def test_filter_only_device_chunk_without_the_null_map_of_an_earlier_one(ctx, oracle):
+    # regression (round-1 advice): a slot that was nullable in the first device chunk arrives with nulls == NULL later:
+    # its rows are all non-NULL and the result's null flags must say so
+    rng = np.random.default_rng(78)
+    n = 50_000
+    plan = ScanAggPlan(preds=[pred(0, K.PRED_GT, K.TYPE_INT, 10)], out_slots=[1, 0])
+    a = K.Chunk(n, {0: _rand_col(rng, K.TYPE_INT, n, 0.0, small=True), 1: _rand_col(rng, K.TYPE_BIGINT, n, 0.3)})
+    b = K.Chunk(n, {0: _rand_col(rng, K.TYPE_INT, n, 0.0, small=True), 1: _rand_col(rng, K.TYPE_BIGINT, n, 0.0)})
+    assert a.columns[1].nulls is not None and b.columns[1].nulls is None
+    # dirty buffers of the result's size classes into the pool first
+    _push_device_chunks(ctx, ScanAggPlan(preds=[], out_slots=[1, 0]), [K.Chunk(n, {0: a.columns[0], 1: K.Column.from_ints(K.TYPE_BIGINT, a.columns[1].data, np.ones(n, np.uint8))})])
+    got = _push_device_chunks(ctx, plan, [a, b])
+    both = K.Chunk(2 * n, {0: K.Column.from_ints(K.TYPE_INT, np.concatenate([a.columns[0].data, b.columns[0].data])),
+                           1: K.Column.from_ints(K.TYPE_BIGINT, np.concatenate([a.columns[1].data, b.columns[1].data]),
+                                                 np.concatenate([a.columns[1].nulls, np.zeros(n, np.uint8)]))})
+    want = oracle.scan_agg(plan, both)
+    assert K.chunk_rows(got, False) == K.chunk_rows(want, False)
+
+
 def test_all_phases_with_groups(ctx, oracle):
     rng = np.random.default_rng(10)
     n = 20000
@@ -1110,5 +1167,5 @@ def check_streaming_mode(ctx, oracle, mode, monkeypatch):
 
 
 def test_streaming_sink_force_preaggregation_is_the_blocking_first_phase(ctx, oracle, monkeypatch):
-    # the modes that pass rows through run in tests/test_gpu_unverified.py until they have been on hardware
+    # the modes that pass rows through run in tests/test_gpu_streaming.py
     check_streaming_mode(ctx, oracle, K.STREAMING_FORCE_PREAGGREGATION, monkeypatch)

@@ -1,12 +1,11 @@
 """Device TopN (starrocks_b200/csrc/srb_topn.cu) against the oracle's ORDER BY restatement (oracle/orc_sort.cpp, pinned to
-be/test/exec/chunks_sorter_test.cpp). The kernels were written after round 1's GPU minutes were spent: until these tests have run on
-a B200 they are expected-to-fail-or-pass (xfail, non-strict) and cannot fail the suite."""
+be/test/exec/chunks_sorter_test.cpp)."""
 import numpy as np
 import pytest
 
 from starrocks_b200 import capi as K
 
-pytestmark = [pytest.mark.gpu, pytest.mark.xfail(strict=False, reason="srb_topn.cu has not run on hardware yet (round-1 GPU budget spent)")]
+pytestmark = pytest.mark.gpu
 
 
 @pytest.fixture(scope="module")
