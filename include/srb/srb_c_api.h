@@ -344,6 +344,24 @@ srb_status srb_partition_run(srb_partitioner* p, const srb_chunk* in, int32_t n_
                              int64_t* counts);
 void srb_partition_destroy(srb_partitioner* p);
 
+/* The same routing for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc). NO COUNTERPART IN THE REFERENCE. The call allocates nothing (no
+ * cudaMalloc / cudaFree / allocating library routine), never waits for the device and copies nothing to the host: the pass-1
+ * scratch (one destination byte per row + 1.5 KB of totals / cursors / first rows) is a file-scope `static __device__` array of
+ * 2 KB + SRB_PARTITION_NOALLOC_MAX_ROWS bytes that every GPU which loads the library holds until exit; larger chunks are rejected
+ * with SRB_INVALID_ARGUMENT (split them, or use srb_partition_run). Everything is enqueued on `cuda_stream` (a cudaStream_t; NULL =
+ * the legacy default stream) of device `device`, which becomes the calling thread's current device.
+ *   in          device-resident chunk of fixed-width columns (<= 16), n_partitions <= 64, <= 4 partition columns
+ *   out         the CALLER's device buffers: same n_cols / slot_ids / types as `in`, room for in->n_rows rows (out->n_rows >= in->n_rows),
+ *               a null buffer for every column of `in` that has one; filled like srb_partition_run's `out` (destination 0 first)
+ *   counts_dev  the caller's DEVICE array of n_partitions int64: rows per destination
+ * Results are valid once the work enqueued on the stream has completed. All calls on one device share the one scratch array (the
+ * call clears what must start at zero): calls whose kernels may overlap on the GPU — different streams without ordering, several
+ * threads — race and must be serialised by the caller. */
+#define SRB_PARTITION_NOALLOC_MAX_ROWS (1 << 20)
+srb_status srb_partition_run_noalloc(int32_t device, void* cuda_stream, int32_t n_partitions, const srb_chunk* in, int32_t n_key_slots,
+                                     const int32_t* key_slots, const srb_chunk* out, int64_t* counts_dev);
+
 /* communicator bootstrap: rank 0 calls srb_comm_unique_id, the 128 bytes travel out of band (the harness uses
  * torch.distributed's store), every rank calls srb_comm_create with them. */
 srb_status srb_comm_unique_id(void* out128);

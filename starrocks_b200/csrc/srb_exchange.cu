@@ -966,3 +966,159 @@ srb_status srb_comm_all_gather(srb_comm* c, const srb_chunk* mine, srb_chunk* ou
 }
 
 } // extern "C"
+
+// ---- srb_partition_run_noalloc: the partitioner for callers that cannot allocate ------------------------------------------------
+// No counterpart in the reference: the same routing as srb_partition_run, but the pass-1
+// scratch (one destination byte per row, the per-destination totals, cursors and first rows) lives in a file-scope __device__ array of
+// fixed size, and the first output row of every destination is derived on the device, so the call allocates nothing, never waits for
+// the device and never copies to the host. Every call on a device shares the one array: calls that overlap on the GPU race.
+namespace srb {
+constexpr int64_t NA_MAX_ROWS = SRB_PARTITION_NOALLOC_MAX_ROWS;
+constexpr size_t NA_HEAD = 2048; // totals[64] | cursors[64] | base[64] (u64 each), then the destination bytes
+static __device__ __align__(256) uint8_t g_na_scratch[NA_HEAD + NA_MAX_ROWS];
+
+// totals -> first output row per destination (exclusive scan) and the caller's counts
+__global__ void k_part_bases_na(const unsigned long long* __restrict__ totals, unsigned long long* __restrict__ base, int64_t* __restrict__ counts,
+                                int n_parts) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        unsigned long long acc = 0;
+        for (int d = 0; d < n_parts; d++) {
+            base[d] = acc;
+            counts[d] = (int64_t)totals[d];
+            acc += totals[d];
+        }
+    }
+}
+
+// k_part_scatter with the destinations' first rows read from device memory instead of the launch arguments
+__global__ void __launch_bounds__(256) k_part_scatter_na(const __grid_constant__ PArgs a, int64_t n, const uint8_t* __restrict__ dest,
+                                                          unsigned long long* __restrict__ cursors, const unsigned long long* __restrict__ base) {
+    __shared__ unsigned int hist[PMAX_PARTS];
+    __shared__ unsigned long long run_base[PMAX_PARTS];
+    constexpr int R = PTILE / 256;
+    const int64_t n_tiles = (n + PTILE - 1) / PTILE;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (int i = threadIdx.x; i < PMAX_PARTS; i += blockDim.x) hist[i] = 0;
+        __syncthreads();
+        uint32_t d[R], rank[R];
+        const int64_t row0 = tile * PTILE + threadIdx.x;
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const int64_t r = row0 + j * 256;
+            d[j] = 0xffffffffu;
+            rank[j] = 0;
+            const bool on = r < n;
+            if (on) d[j] = dest[r];
+            const unsigned act = __ballot_sync(0xffffffffu, on);
+            if (on) {
+                const unsigned peers = __match_any_sync(act, d[j]);
+                const int leader = __ffs(peers) - 1, lane = threadIdx.x & 31;
+                unsigned int b = 0;
+                if (lane == leader) b = atomicAdd(&hist[d[j]], __popc(peers));
+                b = __shfl_sync(peers, b, leader);
+                rank[j] = b + __popc(peers & ((1u << lane) - 1));
+            }
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < a.n_parts; i += blockDim.x)
+            run_base[i] = hist[i] ? base[i] + atomicAdd(&cursors[i], (unsigned long long)hist[i]) : 0;
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            if (d[j] == 0xffffffffu) continue;
+            const int64_t r = row0 + j * 256;
+            const unsigned long long pos = run_base[d[j]] + rank[j];
+            for (int c = 0; c < a.n_cols; c++) {
+                const PCol& pc = a.cols[c];
+                switch (pc.width) {
+                case 1: pc.dst[pos] = pc.src[r]; break;
+                case 2: ((uint16_t*)pc.dst)[pos] = ((const uint16_t*)pc.src)[r]; break;
+                case 4: ((uint32_t*)pc.dst)[pos] = ((const uint32_t*)pc.src)[r]; break;
+                case 8: ((uint64_t*)pc.dst)[pos] = ((const uint64_t*)pc.src)[r]; break;
+                default: ((ulonglong2*)pc.dst)[pos] = ((const ulonglong2*)pc.src)[r];
+                }
+                if (pc.src_null) pc.dst_null[pos] = pc.src_null[r];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// The array's name is a host-side stand-in in host code: its device address is looked up once per device, with that device current.
+static std::mutex g_na_mu;
+static uint8_t* g_na_ptr[64] = {};
+static int g_na_sms[64] = {};
+static uint8_t* na_scratch(int device, int* n_sms) {
+    if (device < 0 || device >= 64) throw Error(SRB_INVALID_ARGUMENT, "device ordinal");
+    std::lock_guard<std::mutex> g(g_na_mu);
+    if (!g_na_ptr[device]) {
+        void* p = nullptr;
+        SRB_CUDA(cudaGetSymbolAddress(&p, g_na_scratch));
+        int sms = 0;
+        SRB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+        g_na_sms[device] = sms;
+        g_na_ptr[device] = (uint8_t*)p;
+    }
+    *n_sms = g_na_sms[device];
+    return g_na_ptr[device];
+}
+} // namespace srb
+
+extern "C" srb_status srb_partition_run_noalloc(int32_t device, void* cuda_stream, int32_t n_partitions, const srb_chunk* in, int32_t n_key_slots,
+                                                const int32_t* key_slots, const srb_chunk* out, int64_t* counts_dev) {
+    X_BEGIN
+    if (!in || !out || !counts_dev || !key_slots) throw Error(SRB_INVALID_ARGUMENT, "null argument");
+    if (n_partitions < 1 || n_partitions > PMAX_PARTS) throw Error(SRB_INVALID_ARGUMENT, fmt("n_partitions must be 1..%d", PMAX_PARTS));
+    if (n_key_slots < 1 || n_key_slots > PMAX_KEYS) throw Error(SRB_INVALID_ARGUMENT, "bad number of partition columns");
+    if (in->n_cols < 1 || in->n_cols > PMAX_COLS) throw Error(SRB_NOT_IMPLEMENTED, "too many columns");
+    if (in->n_rows < 0) throw Error(SRB_INVALID_ARGUMENT, "bad chunk");
+    if (in->n_rows > NA_MAX_ROWS)
+        throw Error(SRB_INVALID_ARGUMENT, fmt("srb_partition_run_noalloc takes at most %lld rows per call (SRB_PARTITION_NOALLOC_MAX_ROWS), got %lld: "
+                                              "split the chunk or use srb_partition_run",
+                                              (long long)NA_MAX_ROWS, (long long)in->n_rows));
+    if (out->n_cols != in->n_cols || out->n_rows < in->n_rows) throw Error(SRB_INVALID_ARGUMENT, "output chunk: same columns and room for every input row");
+    SRB_CUDA(cudaSetDevice(device));
+    int n_sms = 0;
+    uint8_t* scratch = na_scratch(device, &n_sms);
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    const int64_t n = in->n_rows;
+    PArgs a{};
+    a.n_cols = in->n_cols;
+    a.n_keys = n_key_slots;
+    a.n_parts = n_partitions;
+    for (int c = 0; c < in->n_cols; c++) {
+        const srb_column& col = in->cols[c];
+        const srb_column& oc = out->cols[c];
+        const int w = type_width(col.type);
+        if (w == 0) throw Error(SRB_NOT_IMPLEMENTED, "partitioning of binary columns");
+        if (col.mem_kind != SRB_MEM_DEVICE || oc.mem_kind != SRB_MEM_DEVICE) throw Error(SRB_INVALID_ARGUMENT, "partitioner takes device-resident chunks");
+        if (oc.type != col.type || out->slot_ids[c] != in->slot_ids[c]) throw Error(SRB_INVALID_ARGUMENT, "output chunk: columns differ from the input's");
+        if (n > 0 && (!col.data || !oc.data || (col.nulls && !oc.nulls))) throw Error(SRB_INVALID_ARGUMENT, "null column buffer");
+        a.cols[c] = PCol{(const uint8_t*)col.data, (uint8_t*)oc.data, col.nulls, col.nulls ? (uint8_t*)oc.nulls : nullptr, w, 0};
+    }
+    for (int k = 0; k < n_key_slots; k++) {
+        int idx = -1;
+        for (int c = 0; c < in->n_cols; c++)
+            if (in->slot_ids[c] == key_slots[k]) idx = c;
+        if (idx < 0) throw Error(SRB_INVALID_ARGUMENT, fmt("partition slot %d not in chunk", key_slots[k]));
+        a.key_col[k] = idx;
+    }
+    unsigned long long* totals = (unsigned long long*)scratch;
+    unsigned long long* cursors = totals + PMAX_PARTS;
+    unsigned long long* base = cursors + PMAX_PARTS;
+    uint8_t* dest = scratch + NA_HEAD;
+    // the array keeps the last call's contents: totals and cursors must start at zero (base and dest are fully rewritten)
+    SRB_CUDA(cudaMemsetAsync(totals, 0, 2 * PMAX_PARTS * 8, stream));
+    if (n > 0) {
+        const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, (int64_t)n_sms * 8));
+        k_part_count<<<grid, 256, 0, stream>>>(a, n, dest, totals);
+    }
+    k_part_bases_na<<<1, 32, 0, stream>>>(totals, base, counts_dev, n_partitions);
+    if (n > 0) {
+        const int grid2 = (int)std::max<int64_t>(1, std::min<int64_t>((n + PTILE - 1) / PTILE, (int64_t)n_sms * 4));
+        k_part_scatter_na<<<grid2, 256, 0, stream>>>(a, n, dest, cursors, base);
+    }
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+    X_END
+}

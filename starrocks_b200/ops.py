@@ -28,7 +28,7 @@ EXPORTS = [
     "srb_join_probe_need_input", "srb_join_probe_is_finished", "srb_join_probe_pull_chunk",
     "srb_join_probe_pull_all", "srb_join_probe_pull_device",
     "srb_device_alloc", "srb_device_free", "srb_pinned_alloc", "srb_pinned_free", "srb_memcpy_h2d", "srb_memcpy_d2h",
-    "srb_partition_create", "srb_partition_run", "srb_partition_destroy",
+    "srb_partition_create", "srb_partition_run", "srb_partition_destroy", "srb_partition_run_noalloc",
     "srb_comm_unique_id", "srb_comm_create", "srb_comm_destroy", "srb_comm_stream", "srb_comm_all_to_all", "srb_comm_all_gather", "srb_comm_shuffle", "srb_comm_counters", "srb_comm_merge_runtime_filter",
     "srb_join_build_runtime_filter", "srb_op_add_runtime_filter", "srb_op_set_streaming_mode", "srb_op_streaming_stats", "srb_topn_create", "srb_runtime_filter_info", "srb_runtime_filter_directory", "srb_runtime_filter_destroy",
 ]
@@ -83,6 +83,7 @@ def lib() -> C.CDLL:
     L.srb_partition_create.argtypes = [vp, i32, i32, C.POINTER(vp)]
     L.srb_partition_run.argtypes = [vp, C.POINTER(K.srb_chunk), i32, vp, C.POINTER(K.srb_chunk), C.POINTER(i64)]
     L.srb_partition_destroy.argtypes = [vp]
+    L.srb_partition_run_noalloc.argtypes = [i32, vp, i32, C.POINTER(K.srb_chunk), i32, vp, C.POINTER(K.srb_chunk), vp]
     L.srb_partition_destroy.restype = None
     L.srb_comm_unique_id.argtypes = [vp]
     L.srb_comm_create.argtypes = [vp, vp, C.POINTER(vp)]
