@@ -227,6 +227,9 @@ void srb_ctx_destroy(srb_ctx* ctx);
 const char* srb_last_error(void);
 /* library/device facts for harnesses: fills n_sms, HBM bytes, compute capability (major*10+minor) */
 srb_status srb_ctx_device_info(srb_ctx* ctx, int32_t* n_sms, int64_t* hbm_bytes, int32_t* sm_arch);
+/* returns the ctx's cached (idle) device buffers to the driver (MemTracker release between queries; operators closed on this ctx
+ * park their buffers in a per-ctx pool of at most 48 GB) */
+srb_status srb_ctx_trim(srb_ctx* ctx);
 /* the CUDA stream an op launches on (cudaStream_t as void*), so harnesses can time with events on it */
 void* srb_op_stream(srb_op* op);
 

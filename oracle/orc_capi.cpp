@@ -8,7 +8,7 @@ namespace orc {
 Result* run_scan_agg(const srb_scan_agg_plan* plan, const srb_chunk* in, int n_threads, int chunk_size);
 Result* run_scan_agg_streaming(const srb_scan_agg_plan* plan, const srb_chunk* in, int chunk_size, int mode, int64_t* stats);
 Result* run_sort(const srb_chunk* in, int n_keys, const int32_t* key_slots, const uint8_t* is_asc, const uint8_t* nulls_first, int64_t offset, int64_t limit);
-Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe);
+Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe, int n_threads);
 void join_build_raw(const void* keys, int width, uint32_t n, uint32_t* bucket_size, uint32_t* first, uint32_t* next);
 int pack_keys_raw(const srb_chunk* ch, const int32_t* slots, int n_keys, void* out16);
 } // namespace orc
@@ -70,9 +70,11 @@ void* orc_sort(const srb_chunk* in, int n_keys, const int32_t* key_slots, const 
         return nullptr;
     }
 }
-void* orc_join(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe) {
+void* orc_join_mt(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe, int n_threads);
+void* orc_join(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe) { return orc_join_mt(plan, build, probe, 1); }
+void* orc_join_mt(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe, int n_threads) {
     try {
-        return orc::run_join(plan, build, probe);
+        return orc::run_join(plan, build, probe, n_threads);
     } catch (const std::exception& e) {
         g_err = e.what();
         return nullptr;

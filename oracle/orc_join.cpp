@@ -7,6 +7,7 @@
 //   serialize_fixed_size_key_column (multi-column fixed keys)         be/src/exec/join_hash_map.h:391-406
 //   _probe_output / _build_output (append_selective by index)         be/src/exec/join_hash_map.tpp:534-550,624-640
 #include <stdexcept>
+#include <thread>
 
 #include "orc_agg.h"
 
@@ -19,7 +20,23 @@ struct PackedKeys {
 };
 
 // packs the key columns of `ch` (rows 0..n) column by column at increasing byte offsets (join_hash_map.h:391-406)
-static PackedKeys pack_keys(const srb_chunk& ch, const int32_t* slots, int n_keys) {
+// The reference runs the probe side with DOP pipeline drivers over ONE shared, read-only table (HashJoinProbeOperatorFactory clones a
+// readable view per driver, be/src/exec/pipeline/hashjoin/hash_join_probe_operator.cpp:104); the build runs in one driver
+// (hash_join_build_operator.cpp:85 -> JoinHashTable::build). n_threads stands for that DOP: contiguous probe row ranges, outputs
+// concatenated in range order, so the result is the same rows in the same order as with one thread.
+template <class F>
+static void parallel_ranges(int64_t n, int n_threads, F&& f) {
+    int T = (int)std::max<int64_t>(1, std::min<int64_t>(n_threads, n / 4096));
+    if (T == 1) {
+        f(0, 0, n);
+        return;
+    }
+    std::vector<std::thread> th;
+    for (int t = 0; t < T; t++) th.emplace_back([&, t] { f(t, n * t / T, n * (t + 1) / T); });
+    for (auto& x : th) x.join();
+}
+
+static PackedKeys pack_keys(const srb_chunk& ch, const int32_t* slots, int n_keys, int n_threads = 1) {
     PackedKeys pk;
     int total = 0;
     std::vector<const srb_column*> cols(n_keys);
@@ -33,17 +50,19 @@ static PackedKeys pack_keys(const srb_chunk& ch, const int32_t* slots, int n_key
     if (total > 16) throw std::runtime_error("join: packed key wider than 16 bytes");
     pk.k.assign(ch.n_rows, 0);
     pk.null.assign(ch.n_rows, 0);
-    for (int64_t r = 0; r < ch.n_rows; r++) {
-        uint8_t buf[16] = {0};
-        int off = 0;
-        for (int i = 0; i < n_keys; i++) {
-            int w = type_width(cols[i]->type);
-            memcpy(buf + off, (const uint8_t*)cols[i]->data + (size_t)w * r, w);
-            off += w;
-            if (cols[i]->nulls && cols[i]->nulls[r]) pk.null[r] = 1;
+    parallel_ranges(ch.n_rows, n_threads, [&](int, int64_t r0, int64_t r1) {
+        for (int64_t r = r0; r < r1; r++) {
+            uint8_t buf[16] = {0};
+            int off = 0;
+            for (int i = 0; i < n_keys; i++) {
+                int w = type_width(cols[i]->type);
+                memcpy(buf + off, (const uint8_t*)cols[i]->data + (size_t)w * r, w);
+                off += w;
+                if (cols[i]->nulls && cols[i]->nulls[r]) pk.null[r] = 1;
+            }
+            memcpy(&pk.k[r], buf, 16);
         }
-        memcpy(&pk.k[r], buf, 16);
-    }
+    });
     return pk;
 }
 
@@ -73,11 +92,23 @@ static void build_table(JoinTable& t) {
     }
 }
 
-static void copy_rows(const srb_column& s, const std::vector<uint32_t>& rows, OutCol& o) {
+static void copy_rows(const srb_column& s, const std::vector<uint32_t>& rows, OutCol& o, int n_threads = 1) {
     o.type = s.type;
     o.precision = s.precision;
     o.scale = s.scale;
     o.has_nulls = s.nulls != nullptr;
+    if (!is_binary(s.type) && n_threads > 1) {
+        const int w = type_width(s.type);
+        o.data.resize(rows.size() * (size_t)w);
+        if (s.nulls) o.nulls.resize(rows.size());
+        parallel_ranges((int64_t)rows.size(), n_threads, [&](int, int64_t a, int64_t b) {
+            for (int64_t i = a; i < b; i++) {
+                memcpy(o.data.data() + (size_t)i * w, (const uint8_t*)s.data + (size_t)w * rows[i], w);
+                if (s.nulls) o.nulls[i] = s.nulls[rows[i]];
+            }
+        });
+        return;
+    }
     for (uint32_t row : rows) {
         if (s.nulls) o.nulls.push_back(s.nulls[row]);
         if (is_binary(s.type))
@@ -92,16 +123,10 @@ static void copy_rows(const srb_column& s, const std::vector<uint32_t>& rows, Ou
     if (is_binary(s.type) && o.offsets.empty()) o.offsets.push_back(0);
 }
 
-Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe) {
-    auto* r = new Result();
-    JoinTable t;
-    t.keys = pack_keys(*build, plan->build_key_slots, plan->n_keys);
-    build_table(t);
-    PackedKeys pk = pack_keys(*probe, plan->probe_key_slots, plan->n_keys);
-    if (pk.width != t.keys.width) throw std::runtime_error("join: key width mismatch");
-    std::vector<uint32_t> probe_index, build_index; // build_index is 1-based like the reference's
+static void probe_range(const srb_join_plan* plan, const JoinTable& t, const PackedKeys& pk, int64_t i0, int64_t i1, std::vector<uint32_t>& probe_index,
+                        std::vector<uint32_t>& build_index) {
     const bool anti = plan->join_type == SRB_JOIN_LEFT_ANTI;
-    for (int64_t i = 0; i < probe->n_rows; i++) {
+    for (int64_t i = i0; i < i1; i++) {
         if (pk.null[i]) {
             // lookup_init leaves next[i] = 0 for NULL probe keys: no match. LEFT ANTI emits such rows (join_hash_map.tpp:1380-1420,
             // "NULLs are not matches and therefore always returned", PlanNodes.thrift:710-713); every other type drops them
@@ -137,6 +162,30 @@ Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_ch
             bi = t.next[bi];
         }
     }
+}
+
+Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_chunk* probe, int n_threads) {
+    auto* r = new Result();
+    JoinTable t;
+    t.keys = pack_keys(*build, plan->build_key_slots, plan->n_keys, n_threads);
+    build_table(t);
+    PackedKeys pk = pack_keys(*probe, plan->probe_key_slots, plan->n_keys, n_threads);
+    if (pk.width != t.keys.width) throw std::runtime_error("join: key width mismatch");
+    std::vector<uint32_t> probe_index, build_index; // build_index is 1-based like the reference's
+    const bool anti = plan->join_type == SRB_JOIN_LEFT_ANTI;
+    {
+        const int T = std::max(1, n_threads);
+        std::vector<std::vector<uint32_t>> pi(T), bi(T);
+        parallel_ranges(probe->n_rows, T, [&](int th, int64_t a, int64_t b) { probe_range(plan, t, pk, a, b, pi[th], bi[th]); });
+        size_t total = 0;
+        for (int th = 0; th < T; th++) total += pi[th].size();
+        probe_index.reserve(total);
+        build_index.reserve(total);
+        for (int th = 0; th < T; th++) {
+            probe_index.insert(probe_index.end(), pi[th].begin(), pi[th].end());
+            build_index.insert(build_index.end(), bi[th].begin(), bi[th].end());
+        }
+    }
     r->rows_in = probe->n_rows;
     r->rows_selected = (int64_t)probe_index.size();
     r->n_rows = (int64_t)probe_index.size();
@@ -145,13 +194,13 @@ Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_ch
     for (int i = 0; i < plan->n_probe_out; i++) {
         r->cols.emplace_back();
         r->slot_ids.push_back(plan->probe_out_slots[i]);
-        copy_rows(*find_slot(*probe, plan->probe_out_slots[i]), probe_index, r->cols.back());
+        copy_rows(*find_slot(*probe, plan->probe_out_slots[i]), probe_index, r->cols.back(), n_threads);
     }
     if (plan->join_type != SRB_JOIN_LEFT_SEMI && !anti)
         for (int i = 0; i < plan->n_build_out; i++) {
             r->cols.emplace_back();
             r->slot_ids.push_back(plan->build_out_slots[i]);
-            copy_rows(*find_slot(*build, plan->build_out_slots[i]), build_rows, r->cols.back());
+            copy_rows(*find_slot(*build, plan->build_out_slots[i]), build_rows, r->cols.back(), n_threads);
         }
     if (plan->emit_indexes && !anti) {
         for (int which = 0; which < 2; which++) {

@@ -66,6 +66,15 @@ srb_status srb_ctx_device_info(srb_ctx* ctx, int32_t* n_sms, int64_t* hbm_bytes,
     SRB_API_END
 }
 
+srb_status srb_ctx_trim(srb_ctx* ctx) {
+    SRB_API_BEGIN
+    if (!ctx) throw srb::Error(SRB_INVALID_ARGUMENT, "null ctx");
+    SRB_CUDA(cudaSetDevice(ctx->cfg.device));
+    ctx->pool_clear();
+    return SRB_OK;
+    SRB_API_END
+}
+
 void* srb_op_stream(srb_op* op) { return op ? (void*)op->stream : nullptr; }
 
 srb_status srb_scan_agg_create(srb_ctx* ctx, const srb_scan_agg_plan* plan, srb_op** out) {

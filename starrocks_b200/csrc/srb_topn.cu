@@ -49,9 +49,22 @@ struct TEncodeArgs {
 
 SRB_D void key_put_byte(uint64_t (&k)[4], int pos, uint32_t b) { k[pos >> 3] |= (uint64_t)(b & 0xFFu) << (56 - 8 * (pos & 7)); }
 
-__global__ void __launch_bounds__(256) k_topn_encode(const __grid_constant__ TEncodeArgs a, int64_t n, uint64_t seq_base, TEntry* __restrict__ out) {
+// Rows [row0, row0 + n) of the pushed chunk -> entries. thr == nullptr: entry j of the range is written to out[j]. thr != nullptr (the
+// worst of `keep` already sorted candidates): only rows that sort strictly before *thr can still reach the result (ChunksSorterTopn filters
+// every new chunk against its current top rows the same way, chunks_sorter_topn.cpp); they are appended at out[atomicAdd(counter)].
+__global__ void __launch_bounds__(256) k_topn_encode(const __grid_constant__ TEncodeArgs a, int64_t row0, int64_t n, uint64_t seq_base, TEntry* __restrict__ out,
+                                                      const TEntry* __restrict__ thr, unsigned long long* __restrict__ counter) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint64_t t[5] = {0, 0, 0, 0, 0};
+    if (thr) {
+        t[0] = thr->k[0];
+        t[1] = thr->k[1];
+        t[2] = thr->k[2];
+        t[3] = thr->k[3];
+        t[4] = thr->seq;
+    }
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += stride) {
+        const int64_t i = row0 + j;
         uint64_t k[4] = {0, 0, 0, 0};
         for (int c = 0; c < a.n_keys; c++) {
             const TKeyCol& kc = a.cols[c];
@@ -94,9 +107,22 @@ __global__ void __launch_bounds__(256) k_topn_encode(const __grid_constant__ TEn
         e.k[1] = k[1];
         e.k[2] = k[2];
         e.k[3] = k[3];
-        e.seq = seq_base + (uint64_t)i;
+        e.seq = seq_base + (uint64_t)j;
         e.loc = (uint64_t)i;
-        out[i] = e;
+        if (!thr) {
+            out[j] = e;
+            continue;
+        }
+        bool before = false; // e < *thr in the order of entry_less
+        const uint64_t w[5] = {k[0], k[1], k[2], k[3], e.seq};
+#pragma unroll
+        for (int f = 0; f < 5; f++) {
+            if (w[f] != t[f]) {
+                before = w[f] < t[f];
+                break;
+            }
+        }
+        if (before) out[atomicAdd(counter, 1ULL)] = e;
     }
 }
 
@@ -261,6 +287,7 @@ public:
         // entries: the state's survivors first (already encoded, loc = state row), then the pushed rows
         const int64_t total = state_rows_ + n;
         ent_[0].ensure(ctx, (size_t)total * sizeof(TEntry));
+        ent_[1].ensure(ctx, (size_t)total * sizeof(TEntry)); // both sized for the worst case up front: ensure() does not keep contents
         TEntry* e0 = ent_[0].as<TEntry>();
         if (state_rows_) SRB_CUDA(cudaMemcpyAsync(e0, state_ent_.p, (size_t)state_rows_ * sizeof(TEntry), cudaMemcpyDeviceToDevice, stream));
         TEncodeArgs ea{};
@@ -270,24 +297,48 @@ public:
             ea.cols[k] = TKeyCol{data[key_col_[k]], nulls[key_col_[k]], cd.width, cd.type == SRB_TYPE_DOUBLE ? 1 : 0, asc_[k] ? 0 : 1,
                                  nulls_first_[k] ? 1 : 0, key_off_[k]};
         }
-        const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, (int64_t)ctx->n_sms * 8));
-        k_topn_encode<<<grid, 256, 0, stream>>>(ea, n, seq_, e0 + state_rows_);
-        launches++;
-        seq_ += (uint64_t)n;
+        auto grid_for = [&](int64_t rows) { return (int)std::max<int64_t>(1, std::min<int64_t>((rows + 255) / 256, (int64_t)ctx->n_sms * 8)); };
         // tournament: every pass keeps the best keep_ entries of each 2048-entry tile, until one (fully sorted) tile is left
-        int64_t cnt = total;
         int cur = 0;
-        for (;;) {
-            const int64_t tiles = (cnt + TOPN_TILE - 1) / TOPN_TILE;
-            const int64_t last_rows = cnt - (tiles - 1) * TOPN_TILE;
-            const int64_t out_cnt = (tiles - 1) * keep_ + std::min<int64_t>(keep_, last_rows);
-            ent_[cur ^ 1].ensure(ctx, (size_t)std::max<int64_t>(1, out_cnt) * sizeof(TEntry));
-            k_topn_reduce<<<(int)tiles, TOPN_THREADS, sizeof(TSmem), stream>>>(ent_[cur].as<TEntry>(), cnt, keep_, ent_[cur ^ 1].as<TEntry>());
+        auto tournament = [&](int64_t cnt) {
+            for (;;) {
+                const int64_t tiles = (cnt + TOPN_TILE - 1) / TOPN_TILE;
+                const int64_t last_rows = cnt - (tiles - 1) * TOPN_TILE;
+                const int64_t out_cnt = (tiles - 1) * keep_ + std::min<int64_t>(keep_, last_rows);
+                k_topn_reduce<<<(int)tiles, TOPN_THREADS, sizeof(TSmem), stream>>>(ent_[cur].as<TEntry>(), cnt, keep_, ent_[cur ^ 1].as<TEntry>());
+                launches++;
+                cur ^= 1;
+                cnt = out_cnt;
+                if (tiles == 1) return cnt;
+            }
+        };
+        // A large chunk is not sorted whole: the state and a leading sample give keep_ sorted candidates, whose worst entry is a bound no
+        // later result row can exceed; the rest of the chunk is encoded through that bound and only the rows before it (about
+        // keep_ * rows / sample of them unless the chunk arrives sorted the wrong way round) join the tournament.
+        const int64_t sample = (int64_t)ctx->n_sms * TOPN_TILE;
+        int64_t cnt;
+        if (n <= 2 * sample || getenv("SRB_TOPN_NO_BOUND")) {
+            k_topn_encode<<<grid_for(n), 256, 0, stream>>>(ea, 0, n, seq_, e0 + state_rows_, nullptr, nullptr);
             launches++;
-            cur ^= 1;
-            cnt = out_cnt;
-            if (tiles == 1) break;
+            cnt = tournament(total);
+        } else {
+            k_topn_encode<<<grid_for(sample), 256, 0, stream>>>(ea, 0, sample, seq_, e0 + state_rows_, nullptr, nullptr);
+            launches++;
+            cnt = tournament(state_rows_ + sample); // == keep_: the sample alone holds more rows than that
+            counter_.ensure(ctx, 8);
+            hcounter_.ensure(8);
+            unsigned long long* hc = hcounter_.as<unsigned long long>();
+            *hc = (unsigned long long)cnt;
+            SRB_CUDA(cudaMemcpyAsync(counter_.p, hc, 8, cudaMemcpyHostToDevice, stream));
+            TEntry* cand = ent_[cur].as<TEntry>();
+            k_topn_encode<<<grid_for(n - sample), 256, 0, stream>>>(ea, sample, n - sample, seq_ + (uint64_t)sample, cand, cand + (cnt - 1),
+                                                                    counter_.as<unsigned long long>());
+            launches++;
+            SRB_CUDA(cudaMemcpyAsync(hc, counter_.p, 8, cudaMemcpyDeviceToHost, stream));
+            SRB_CUDA(cudaStreamSynchronize(stream));
+            cnt = tournament((int64_t)*hc);
         }
+        seq_ += (uint64_t)n;
         // payload of the survivors into the other state buffer
         const int ns = state_cur_ ^ 1;
         TGatherArgs ga{};
@@ -412,7 +463,8 @@ private:
     int state_cur_ = 0;
     int64_t state_rows_ = 0, out_rows_ = 0;
     uint64_t seq_ = 0;
-    DevBuf ent_[2], state_ent_;
+    DevBuf ent_[2], state_ent_, counter_;
+    PinnedBuf hcounter_;
     std::vector<HostCol> host_;
     std::vector<srb_column> view_;
     std::vector<int32_t> slots_;

@@ -20,7 +20,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libsrb.so"
 _lib = None
 
 EXPORTS = [
-    "srb_ctx_create", "srb_ctx_destroy", "srb_last_error", "srb_ctx_device_info", "srb_op_stream",
+    "srb_ctx_create", "srb_ctx_destroy", "srb_last_error", "srb_ctx_device_info", "srb_ctx_trim", "srb_op_stream",
     "srb_scan_agg_create", "srb_join_create", "srb_op_push_chunk", "srb_op_set_finishing", "srb_op_has_output",
     "srb_op_need_input", "srb_op_is_finished", "srb_op_pull_chunk", "srb_op_pull_all", "srb_op_pull_device",
     "srb_op_cancel", "srb_op_close", "srb_op_sync", "srb_op_counters", "srb_op_profile",
@@ -54,6 +54,7 @@ def lib() -> C.CDLL:
     L.srb_ctx_destroy.argtypes = [vp]
     L.srb_ctx_destroy.restype = None
     L.srb_ctx_device_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i64), C.POINTER(i32)]
+    L.srb_ctx_trim.argtypes = [vp]
     L.srb_op_stream.argtypes = [vp]
     L.srb_op_stream.restype = vp
     L.srb_scan_agg_create.argtypes = [vp, C.POINTER(K.srb_scan_agg_plan), C.POINTER(vp)]
@@ -131,6 +132,10 @@ class Context:
         a, b, c = C.c_int32(), C.c_int64(), C.c_int32()
         _check(self.L.srb_ctx_device_info(self.h, C.byref(a), C.byref(b), C.byref(c)))
         return {"n_sms": a.value, "hbm_bytes": b.value, "sm_arch": c.value}
+
+    def trim(self):
+        """give the idle pooled device buffers back to the driver"""
+        _check(self.L.srb_ctx_trim(self.h))
 
     def close(self):
         if self.h:

@@ -129,15 +129,27 @@ class TpchQ3:
     # q3.sql:36-38: ORDER BY revenue DESC, o_orderdate LIMIT 10 (DESC puts NULLs last, ASC first: StarRocks' defaults)
     TOP_KEYS, TOP_ASC, TOP_NULLS_FIRST = [3, 1], [0, 1], [0, 1]
 
-    def top(self, agg, limit: int = 10) -> K.Chunk:
-        """the plan's last operator: the aggregation's device result through the device TopN (ops.TopNOperator)"""
+    def top(self, agg, limit: int = 10, groups: Optional[K.Chunk] = None) -> K.Chunk:
+        """the plan's last operator: the aggregation's device result (`groups`, pulled here when not given) through the device TopN
+        (ops.TopNOperator). At N > 1 every rank's groups are disjoint: the ranks' top rows are gathered (<= limit rows each) and
+        pass through a second TopN on every rank (the gather exchange + final ORDER BY ... LIMIT of q3.sql)."""
         top = ops.TopNOperator(self.ctx, self.TOP_KEYS, self.TOP_ASC, self.TOP_NULLS_FIRST, limit)
         self.open.append(top)
-        groups = agg.pull_device()
+        if groups is None:
+            groups = agg.pull_device()
         if groups is not None and groups.n_rows:
             top.push_chunk(groups)
         top.set_finishing()
-        return top.pull_all()
+        mine = top.pull_all()
+        if self.comm is None or self.comm.ctx.world_size == 1:
+            return mine
+        if not mine.columns:
+            raise ValueError("a rank without groups cannot describe the schema of the gather")
+        final = ops.TopNOperator(self.ctx, self.TOP_KEYS, self.TOP_ASC, self.TOP_NULLS_FIRST, limit)
+        self.open.append(final)
+        final.push_chunk(self.comm.all_gather(mine))
+        final.set_finishing()
+        return final.pull_all()
 
     def launches(self) -> int:
         return sum(o.counters()["kernel_launches"] for o in self.open if hasattr(o, "counters"))
@@ -146,20 +158,6 @@ class TpchQ3:
         for o in self.open:
             o.close()
         self.open = []
-
-
-def q3_top_oracle(oracle, groups: K.Chunk, limit: int = 10) -> K.Chunk:
-    return oracle.sort(groups, TpchQ3.TOP_KEYS, TpchQ3.TOP_ASC, TpchQ3.TOP_NULLS_FIRST, 0, limit)
-
-
-def q3_oracle(oracle, cust: K.Chunk, orders: K.Chunk, line: K.Chunk, n_threads: int = 1) -> K.Chunk:
-    """the same chain through the CPU oracle (tests and the CPU baseline only)"""
-    c = oracle.scan_agg(Q.q3_customer_filter(), cust, n_threads=n_threads)
-    o = oracle.scan_agg(Q.q3_orders_filter(), orders, n_threads=n_threads)
-    l = oracle.scan_agg(Q.q3_lineitem_filter(), line, n_threads=n_threads)
-    d1 = oracle.join(Q.q3_join_customer_orders(), c, o)
-    d2 = oracle.join(Q.q3_join_orders_lineitem(), d1, l)
-    return oracle.scan_agg(Q.q3_agg_plan(), d2, n_threads=n_threads)
 
 
 class SsbQ41:
@@ -230,15 +228,3 @@ class SsbQ41:
         for o in self.joins + self.keep + [rf for rf, _ in self.rfs]:
             o.close()
         self.joins, self.keep, self.rfs = [], [], []
-
-
-def ssb_q41_oracle(oracle, dims: Dict[str, K.Chunk], lineorder: K.Chunk, n_threads: int = 1) -> K.Chunk:
-    """the same chain through the CPU oracle (tests and the CPU baseline only)"""
-    s = oracle.scan_agg(Q.ssb_supplier_filter(), dims["ssb_supplier"], n_threads=n_threads)
-    c = oracle.scan_agg(Q.ssb_customer_filter(), dims["ssb_customer"], n_threads=n_threads)
-    p = oracle.scan_agg(Q.ssb_part_filter(), dims["ssb_part"], n_threads=n_threads)
-    cur = oracle.join(Q.ssb_join_supplier(), s, lineorder)
-    cur = oracle.join(Q.ssb_join_customer(), c, cur)
-    cur = oracle.join(Q.ssb_join_part(), p, cur)
-    cur = oracle.join(Q.ssb_join_dates(), dims["ssb_dates"], cur)
-    return oracle.scan_agg(Q.ssb_q41_agg_plan(), cur, n_threads=n_threads)

@@ -98,6 +98,14 @@ def q1_merge_plan(inter: K.Chunk) -> ScanAggPlan:
     return ScanAggPlan(exprs=e, keys=keys, aggs=list(zip(fns, args)), phase=K.AGG_MERGE_FINALIZE)
 
 
+def q6_merge_plan(inter: K.Chunk) -> ScanAggPlan:
+    """phase 2 of Q6 over the intermediate rows of q6_plan(phase=AGG_UPDATE_SERIALIZE): one DECIMAL128 partial sum per rank
+    (NULL when the rank selected no row), merged by SUM (aggregator.cpp:871-875, sum.h:113-117)"""
+    e = ExprBuilder()
+    c = inter.columns[0]
+    return ScanAggPlan(exprs=e, aggs=[(K.AGG_SUM, e.slot(0, c.type, c.precision, c.scale))], phase=K.AGG_MERGE_FINALIZE)
+
+
 def highcard_plan(phase: int = K.AGG_UPDATE_FINALIZE, group_hint: int = 0) -> ScanAggPlan:
     """select k, sum(v), count(*) from t group by k   (k, v BIGINT)"""
     e = ExprBuilder()

@@ -36,6 +36,8 @@ class Oracle:
         L.orc_scan_agg_streaming.argtypes = [C.POINTER(K.srb_scan_agg_plan), C.POINTER(K.srb_chunk), C.c_int, C.c_int, C.POINTER(C.c_int64)]
         L.orc_join.restype = C.c_void_p
         L.orc_join.argtypes = [C.POINTER(K.srb_join_plan), C.POINTER(K.srb_chunk), C.POINTER(K.srb_chunk)]
+        L.orc_join_mt.restype = C.c_void_p
+        L.orc_join_mt.argtypes = [C.POINTER(K.srb_join_plan), C.POINTER(K.srb_chunk), C.POINTER(K.srb_chunk), C.c_int]
         L.orc_result_chunk.restype = C.POINTER(K.srb_chunk)
         L.orc_result_chunk.argtypes = [C.c_void_p]
         L.orc_result_counters.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
@@ -144,10 +146,11 @@ class Oracle:
         finally:
             self.lib.orc_result_free(r)
 
-    def join(self, plan, build: K.Chunk, probe: K.Chunk):
+    def join(self, plan, build: K.Chunk, probe: K.Chunk, n_threads: int = 1):
+        """n_threads = the probe side's degree of parallelism (drivers over one shared table); same rows, same order"""
         b, k1 = build.to_c()
         p, k2 = probe.to_c()
-        r = self.lib.orc_join(C.byref(plan.c), C.byref(b), C.byref(p))
+        r = self.lib.orc_join_mt(C.byref(plan.c), C.byref(b), C.byref(p), n_threads)
         if not r:
             raise RuntimeError("oracle: " + self._err())
         try:

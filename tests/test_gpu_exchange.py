@@ -12,6 +12,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 from starrocks_b200 import capi as K, distributed as D, queries as Q, tpch_synth as T  # noqa: E402
+from tests import oracle_chains as OC  # noqa: E402
 
 pytestmark = pytest.mark.gpu
 
@@ -118,7 +119,7 @@ def test_q3_shuffle_plan_on_a_single_rank_communicator(ctx, oracle):
     join) through a world-size-1 communicator: same code path as N > 1, result equal to the oracle chain"""
     from starrocks_b200 import ops, pipelines as P
     cust, orders, line = _q3_tables(3000, 30000, 120000)
-    want = K.chunk_rows(P.q3_oracle(oracle, cust, orders, line))
+    want = K.chunk_rows(OC.q3_oracle(oracle, cust, orders, line))
     assert len(want) > 50
     box = {}
     comm = ops.Communicator(ctx, lambda b: box.__setitem__("id", b), lambda: box["id"])
@@ -329,7 +330,7 @@ def test_two_gpu_shuffle_join_and_broadcast_join(oracle):
         p.join(timeout=60)
         assert p.exitcode == 0
     cust, orders, line = _q3_tables(*sizes["q3"])
-    want = K.chunk_rows(P.q3_oracle(oracle, cust, orders, line))
+    want = K.chunk_rows(OC.q3_oracle(oracle, cust, orders, line))
     keys = [{r[:3] for r in res[k][0]} for k in range(world)]
     assert not (keys[0] & keys[1])  # the order key decides the rank: groups are disjoint
     assert sorted(res[0][0] + res[1][0]) == want
@@ -337,7 +338,7 @@ def test_two_gpu_shuffle_join_and_broadcast_join(oracle):
     kw = dict(n_customers=n_c, n_suppliers=n_s, n_parts=n_p)
     dims = {name: T.host_chunk(name, 0, n, P.SSB_DIM_COLS[name]) for name, n in
             (("ssb_customer", n_c), ("ssb_supplier", n_s), ("ssb_part", n_p), ("ssb_dates", T.SSB_DAYS))}
-    want_ssb = K.chunk_rows(P.ssb_q41_oracle(oracle, dims, T.host_chunk("lineorder", 0, n_lo, T.LINEORDER_Q41, **kw)))
+    want_ssb = K.chunk_rows(OC.ssb_q41_oracle(oracle, dims, T.host_chunk("lineorder", 0, n_lo, T.LINEORDER_Q41, **kw)))
     assert res[0][1] == want_ssb and res[1][1] == want_ssb
     from tests.oracle_lib import OracleRuntimeFilter
     keys = sizes["rf_keys"]

@@ -9,6 +9,7 @@ import numpy as np
 import pytest
 
 from starrocks_b200 import capi as K
+from tests import oracle_chains as OC
 from starrocks_b200 import queries as Q
 from starrocks_b200 import tpch_synth as T
 from starrocks_b200.plan import ExprBuilder, JoinPlan, ScanAggPlan, pred
@@ -877,7 +878,7 @@ def test_ssb_q41_star_join_chained_on_device(ctx, oracle, join_mode, use_rf):
     materialisation, GROUP BY d_year, c_nation — every operator output handed on as a device chunk; compared with the oracle chain."""
     from starrocks_b200 import pipelines as P
     dims, lo = _ssb_tables(600_000, 30_000, 2_000, 200_000)
-    want = K.chunk_rows(P.ssb_q41_oracle(oracle, dims, lo))
+    want = K.chunk_rows(OC.ssb_q41_oracle(oracle, dims, lo))
     assert len(want) == 7 * 5  # 7 years x the 5 nations of AMERICA
     q = P.SsbQ41(ctx, runtime_filter=use_rf).build(dims)
     stage_rows = []
@@ -1075,7 +1076,7 @@ def test_q3_pipeline_with_and_without_runtime_filter(ctx, oracle, use_rf):
     cust = T.host_chunk("customer", 0, n_c, ["c_custkey", "c_mktsegment_code"])
     orders = T.host_chunk("orders", 0, n_o, ["o_orderkey", "o_custkey", "o_orderdate", "o_shippriority"], n_customers=n_c)
     line = T.host_chunk("lineitem", 0, n_l, ["l_orderkey", "l_extendedprice", "l_discount", "l_shipdate"])
-    want = K.chunk_rows(P.q3_oracle(oracle, cust, orders, line))
+    want = K.chunk_rows(OC.q3_oracle(oracle, cust, orders, line))
     q = P.TpchQ3(ctx, runtime_filter=use_rf)
     rows = {}
     try:

@@ -4,6 +4,7 @@ import numpy as np
 import pytest
 
 from starrocks_b200 import capi as K
+from tests import oracle_chains as OC
 from starrocks_b200 import queries as Q
 from tests.test_gpu_parity import _ssb_tables, _stream_gpu, check_streaming_mode
 
@@ -45,7 +46,7 @@ def test_fused_runtime_filters_give_the_same_rows(ctx, oracle, monkeypatch):
     k_filter_rf launches keep — the star join's stage row counts and result do not change"""
     from starrocks_b200 import pipelines as P
     dims, lo = _ssb_tables(600_000, 30_000, 2_000, 200_000)
-    want = K.chunk_rows(P.ssb_q41_oracle(oracle, dims, lo))
+    want = K.chunk_rows(OC.ssb_q41_oracle(oracle, dims, lo))
     seen = {}
     for fused in (False, True):
         if fused:

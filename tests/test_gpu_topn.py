@@ -4,6 +4,7 @@ import numpy as np
 import pytest
 
 from starrocks_b200 import capi as K
+from tests import oracle_chains as OC
 
 pytestmark = pytest.mark.gpu
 
@@ -62,6 +63,29 @@ def test_random_rows_against_the_oracle(ctx, oracle, device):
             assert got == want, (keys, limit, offset)  # same rows in the same order, ties in arrival order
 
 
+@pytest.mark.parametrize("order", ["random", "worst_first"])
+def test_large_chunks_are_filtered_against_the_current_top_rows(ctx, oracle, order, monkeypatch):
+    """chunks above 2 x 148 x 2048 rows: the state + a leading sample give the candidates, the rest of the chunk is encoded through the
+    worst candidate (chunks_sorter_topn.cpp filters new chunks against its top rows the same way). Same rows as the plain tournament and the
+    oracle, also when every row of the chunk passes the bound (input sorted the wrong way round) and when a state exists already."""
+    rng = np.random.default_rng(43)
+    n = 900_000
+    vals = rng.integers(-2**40, 2**40, n)
+    if order == "worst_first":
+        vals = np.sort(vals)[::-1].copy()  # ascending ORDER BY over descending input: every later row beats the candidates
+    grp = rng.integers(0, 7, n).astype(np.int32)
+    ch = K.Chunk(n, {0: K.Column.from_ints(K.TYPE_BIGINT, vals), 1: K.Column.from_ints(K.TYPE_INT, grp, (rng.random(n) < 0.01).astype(np.uint8)),
+                     2: K.Column.from_ints(K.TYPE_INT, np.arange(n, dtype=np.int32))})
+    for keys, asc, nf, limit, offset in (([0], [1], [1], 10, 0), ([1, 0], [0, 1], [0, 0], 1000, 24), ([1], [1], [1], 50, 0)):
+        want = K.chunk_rows(oracle.sort(ch, keys, asc, nf, offset, limit), sort=False)
+        got = K.chunk_rows(run_topn(ctx, ch, keys, asc, nf, limit, offset, device=True), sort=False)
+        assert got == want, (keys, limit, offset)
+        got = K.chunk_rows(run_topn(ctx, ch, keys, asc, nf, limit, offset, pieces=[100_000], device=True), sort=False)  # a state, then a large chunk
+        assert got == want, (keys, limit, offset, "pieces")
+    monkeypatch.setenv("SRB_TOPN_NO_BOUND", "1")
+    assert K.chunk_rows(run_topn(ctx, ch, [0], [1], [1], 10, device=True), sort=False) == K.chunk_rows(oracle.sort(ch, [0], [1], [1], 0, 10), sort=False)
+
+
 def test_fewer_rows_than_the_limit_and_limit_zero(ctx, oracle):
     from tests.test_topn_cpu import random_chunk
     ch = random_chunk(np.random.default_rng(5), 37)
@@ -91,7 +115,7 @@ def test_q3_ends_with_order_by_revenue_desc_orderdate_limit_10(ctx, oracle):
     cust = T.host_chunk("customer", 0, n_c, ["c_custkey", "c_mktsegment_code"])
     orders = T.host_chunk("orders", 0, n_o, ["o_orderkey", "o_custkey", "o_orderdate", "o_shippriority"], n_customers=n_c)
     line = T.host_chunk("lineitem", 0, n_l, ["l_orderkey", "l_extendedprice", "l_discount", "l_shipdate"])
-    want = K.chunk_rows(P.q3_top_oracle(oracle, P.q3_oracle(oracle, cust, orders, line)), sort=False)
+    want = K.chunk_rows(OC.q3_top_oracle(oracle, OC.q3_oracle(oracle, cust, orders, line)), sort=False)
     assert len(want) == 10
     q = P.TpchQ3(ctx)
     try:

@@ -108,3 +108,20 @@ def test_boundary_header_is_plain_c():
     import subprocess
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-fsyntax-only", "-x", "c", os.path.join(root, "include", "srb", "srb_c_api.h")])
+
+
+def test_oracle_join_with_probe_drivers_returns_the_same_rows_in_the_same_order(oracle):
+    """the oracle's probe side runs with DOP drivers over one shared table (hash_join_probe_operator.cpp:104): any thread count, same rows"""
+    import numpy as np
+    from starrocks_b200 import capi as K
+    from starrocks_b200.plan import JoinPlan
+    rng = np.random.default_rng(8)
+    nb, npb = 20_000, 300_000
+    build = K.Chunk(nb, {0: K.Column.from_ints(K.TYPE_INT, rng.integers(0, 15_000, nb).astype(np.int32)), 1: K.Column.from_ints(K.TYPE_BIGINT, rng.integers(0, 1 << 40, nb))})
+    probe = K.Chunk(npb, {2: K.Column.from_ints(K.TYPE_INT, rng.integers(0, 30_000, npb).astype(np.int32), (rng.random(npb) < 0.05).astype(np.uint8)),
+                          3: K.Column.from_ints(K.TYPE_DECIMAL128, [int(x) for x in rng.integers(-2**40, 2**40, npb)], None, 27, 2)})
+    for jt in (K.JOIN_INNER, K.JOIN_LEFT_SEMI, K.JOIN_LEFT_ANTI):
+        plan = JoinPlan([0], [2], build_out=[1], probe_out=[2, 3], join_type=jt)
+        one = K.chunk_rows(oracle.join(plan, build, probe), sort=False)
+        for t in (2, 7):
+            assert K.chunk_rows(oracle.join(plan, build, probe, n_threads=t), sort=False) == one
