@@ -14,6 +14,7 @@
 // (srb_shapes.cuh). There is no CPU path: every row is processed by a CUDA kernel.
 #include <limits>
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <memory>
@@ -23,6 +24,7 @@
 #include "srb_lower.h"
 #include "srb_rowpipe.cuh"
 #include "srb_shapes.cuh"
+#include "srb_radix_agg.cuh"
 #include "srb_stream_policy.h"
 #include "srb_hcpart.cuh"
 
@@ -1338,12 +1340,19 @@ private:
             }
             cap_ = want;
         }
+        occupied_ = 0;
+        table_ready_ = false;
+        // a large hinted table (gigabytes to allocate and clear) is only built when a batch goes through it: the radix path does not
+        if ((size_t)cap_ * (size_t)P.slot_bytes < ((size_t)64 << 20)) ensure_table();
+    }
+    void ensure_table() {
+        if (table_ready_) return;
         alloc_table(slots_, cap_);
-        if (P.n_keys == 0) { // the single state block of a no-group-by aggregation: zero-filled states are valid, mark it taken
+        if (L_.prog.n_keys == 0) { // the single state block of a no-group-by aggregation: zero-filled states are valid, mark it taken
             static const uint64_t ready = SLOT_READY;
             SRB_CUDA(cudaMemcpyAsync(slots_.p, &ready, 8, cudaMemcpyHostToDevice, stream));
         }
-        occupied_ = 0;
+        table_ready_ = true;
     }
     void alloc_table(DevBuf& buf, uint64_t cap) {
         size_t bytes = (size_t)cap * (size_t)L_.prog.slot_bytes;
@@ -1359,6 +1368,11 @@ private:
         return t;
     }
     void grow_table(uint64_t min_cap) {
+        if (!table_ready_) { // nothing to rehash: size the first allocation directly
+            while (cap_ < min_cap) cap_ <<= 1;
+            ensure_table();
+            return;
+        }
         uint64_t ncap = cap_ * 2;
         while (ncap < min_cap) ncap <<= 1;
         DevBuf nb;
@@ -1395,6 +1409,7 @@ private:
         // The L2-blocked path wants the LARGEST batch memory allows: the table region that is live at any moment is
         // (rows in flight / rows per batch) x table bytes, so more rows per batch means a smaller, L2-resident window and
         // more updates per table sector while it is cached.
+        if (radix_applies(n) && radix_batch(cols, n)) return;
         int64_t batch = AGG_BATCH;
         if (hc_partition_applies(n)) {
             size_t free_b = 0, total_b = 0;
@@ -1433,6 +1448,111 @@ private:
         int64_t blocks = (n + 255) / 256;
         int64_t maxb = (int64_t)ctx->n_sms * 8;
         return (int)std::max<int64_t>(1, std::min(blocks, maxb));
+    }
+
+    // ---- radix-partitioned aggregation (srb_radix_agg.cuh): first batch of a high-cardinality k -> SUM, COUNT plan -------------
+    bool hc_cols_ok() const {
+        const DProg& P = L_.prog;
+        return shape_ == 2 ? (P.n_cols == 2 && P.nodes[0].col != P.nodes[1].col)
+                           : (shape_ == 4 && P.n_cols == 3 && P.nodes[0].col != P.nodes[1].col && P.nodes[0].col != P.nodes[2].col &&
+                              P.nodes[1].col != P.nodes[2].col);
+    }
+    bool radix_applies(int64_t n) const {
+        const DProg& P = L_.prog;
+        if (no_radix_ || force_generic_ || stream_mode_ >= 0 || P.n_preds != 0 || !hc_cols_ok()) return false;
+        if (occupied_ != 0 || stream_rows_ != 0 || radix_rows_ != 0) return false; // the first batch only: its groups must be the only ones
+        if (n < radix_min_rows_ || n > ((int64_t)1 << 30)) return false;
+        for (int i = 0; i < P.n_cols; i++)
+            if (P.cols[i].width != 8) return false;
+        // the planner's cardinality estimate says "many groups" (at most ~64 rows per key): with few, hot keys the partitions would overflow
+        return plan_.group_hint > 0 && (int64_t)plan_.group_hint >= n / 64;
+    }
+    template <int NV>
+    void radix_launch(const ColBind* cols, int64_t n, int fbits, uint32_t cap, const RxOut& out) {
+        const DProg& P = L_.prog;
+        const uint64_t* k = (const uint64_t*)cols[P.nodes[0].col].data;
+        const uint64_t* v0 = (const uint64_t*)cols[P.nodes[1].col].data;
+        const uint64_t* v1 = NV == 2 ? (const uint64_t*)cols[P.nodes[2].col].data : nullptr;
+        static SmemOptIn opt;
+        opt.set(k_rx_aggregate<NV>, (int)RxGeom<NV>::BYTES);
+        k_rx_scatter<NV><<<ctx->n_sms * 8, 256, 0, stream>>>(k, v0, v1, n, P.phase_seed, fbits, cap, rx_cursor_.as<uint32_t>(), rx_a_.as<ulonglong2>(),
+                                                            rx_b_.as<uint64_t>(), rx_ctr_.as<RxCounters>());
+        k_rx_aggregate<NV><<<ctx->n_sms, RX_THREADS, RxGeom<NV>::BYTES, stream>>>(rx_a_.as<ulonglong2>(), rx_b_.as<uint64_t>(), rx_cursor_.as<uint32_t>(),
+                                                                                   1 << fbits, cap, P.phase_seed, fbits, out, rx_ctr_.as<RxCounters>());
+        launches += 2;
+    }
+    // -> false when a partition (a hot key) or the output overflowed: nothing is kept and the caller takes the table path
+    bool radix_batch(const ColBind* cols, int64_t n) {
+        const DProg& P = L_.prog;
+        for (int i = 0; i < P.n_cols; i++)
+            if (cols[i].nulls) return false; // (null maps without a set byte are stripped by the table path's launch_batch only)
+        const int nv = shape_ == 4 ? 2 : 1;
+        const int cap_max = nv == 1 ? RxGeom<1>::CAP : RxGeom<2>::CAP;
+        // Rows of one key land in one partition: with c rows per key a partition's row count has variance mean * (c + 1), not mean.
+        // The finest split whose mean + 6 sigma + slack still fits a partition buffer:
+        const double c = std::max(1.0, (double)n / (double)plan_.group_hint);
+        auto cap_for = [&](int fb) {
+            const double m = (double)n / (double)((int64_t)1 << fb);
+            return m + 6.0 * std::sqrt(m * (c + 1.0)) + 64.0;
+        };
+        int fbits = 8;
+        while (cap_for(fbits) > (double)cap_max && fbits < 21) fbits++;
+        if (cap_for(fbits) > (double)cap_max) return false;
+        const int64_t F = (int64_t)1 << fbits;
+        const uint32_t cap = std::min<uint32_t>(((uint32_t)cap_for(fbits) + 63u) & ~63u, (uint32_t)cap_max);
+        rx_cursor_.ensure(ctx, (size_t)F * 4);
+        rx_a_.ensure(ctx, (size_t)F * cap * 16);
+        if (nv == 2) rx_b_.ensure(ctx, (size_t)F * cap * 8);
+        rx_ctr_.ensure(ctx, sizeof(RxCounters));
+        rx_hctr_.ensure(sizeof(RxCounters));
+        SRB_CUDA(cudaMemsetAsync(rx_cursor_.p, 0, (size_t)F * 4, stream));
+        SRB_CUDA(cudaMemsetAsync(rx_ctr_.p, 0, sizeof(RxCounters), stream));
+        const uint64_t out_cap = std::min<uint64_t>((uint64_t)n, std::max<uint64_t>((uint64_t)plan_.group_hint * 2, (uint64_t)1 << 20));
+        EmitArgs ea = emit_args(out_cap);
+        RxOut out{ea.keys, (uint64_t*)ea.aggs[0].val, ea.aggs[0].null, (uint64_t*)ea.aggs[1].val, ea.aggs[1].null, 0ULL, out_cap};
+        if (!ev0_) {
+            ev0_ = ctx->take_event(true);
+            ev1_ = ctx->take_event(true);
+            if (!ev0_ || !ev1_) throw Error(SRB_INTERNAL_ERROR, "cudaEventCreate failed");
+        }
+        SRB_CUDA(cudaEventRecord(ev0_, stream));
+        if (nv == 1)
+            radix_launch<1>(cols, n, fbits, cap, out);
+        else
+            radix_launch<2>(cols, n, fbits, cap, out);
+        SRB_CUDA(cudaEventRecord(ev1_, stream));
+        SRB_CUDA(cudaGetLastError());
+        RxCounters* hc = rx_hctr_.as<RxCounters>();
+        SRB_CUDA(cudaMemcpyAsync(hc, rx_ctr_.p, sizeof(RxCounters), cudaMemcpyDeviceToHost, stream));
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        float ms = 0;
+        SRB_CUDA(cudaEventElapsedTime(&ms, ev0_, ev1_));
+        kernel_ms_ += ms;
+        timed_batches_++;
+        if (hc->overflow) return false;
+        radix_rows_ = (int64_t)hc->groups;
+        stream_rows_ = radix_rows_; // the groups sit in front of whatever the table emits later, like pass-through rows
+        selected_total_ += (uint64_t)n;
+        radix_batches_++;
+        return true;
+    }
+    void radix_ingest() {
+        const DProg& P = L_.prog;
+        const uint64_t need = (uint64_t)radix_rows_ * 2 + 1024;
+        if (!table_ready_ || cap_ < need) grow_table(need);
+        ensure_table();
+        SRB_CUDA(cudaMemsetAsync(rx_ctr_.p, 0, sizeof(RxCounters), stream));
+        RxCounters* dc = rx_ctr_.as<RxCounters>();
+        k_rx_ingest<<<grid_for(radix_rows_), 256, 0, stream>>>(P, view(), ekeys_.as<ulonglong2>(), eval_[0].val.as<uint64_t>(), eval_[1].val.as<uint64_t>(),
+                                                               radix_rows_, &dc->groups, &dc->overflow);
+        launches++;
+        RxCounters* hc = rx_hctr_.as<RxCounters>();
+        SRB_CUDA(cudaMemcpyAsync(hc, rx_ctr_.p, sizeof(RxCounters), cudaMemcpyDeviceToHost, stream));
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        if (hc->overflow) throw Error(SRB_INTERNAL_ERROR, "radix groups did not fit the group table");
+        occupied_ += hc->groups;
+        stream_rows_ = 0;
+        radix_rows_ = 0;
     }
 
     // ---- L2-blocked high-cardinality path (srb_hcpart.cuh) ----------------------------------------------------------------
@@ -1512,6 +1632,7 @@ private:
     // AUTO learns from the hit counts of successive units: 2^24 rows each (a few per cent of an SF100 table), so that a poor
     // reduction is noticed after the first unit instead of after a whole 2^29-row batch. SRB_STREAM_UNIT: test hook.
     void stream_range(const ColBind* cols, int64_t n) {
+        ensure_table();
         const int64_t unit = stream_mode_ == SRB_STREAMING_AUTO ? stream_unit_ : AGG_BATCH;
         for (int64_t off = 0; off < n; off += unit) stream_batch(cols, off, std::min<int64_t>(unit, n - off));
     }
@@ -1599,6 +1720,8 @@ private:
     }
 
     void launch_batch(const ColBind* cols, int64_t off, int64_t n, const uint32_t* defer_in = nullptr) {
+        if (radix_rows_ > 0) radix_ingest(); // a key may occur in the radix batch's groups and in this batch: both go through the table
+        ensure_table();
         if (!ev0_) {
             ev0_ = ctx->take_event(true);
             ev1_ = ctx->take_event(true);
@@ -1960,6 +2083,14 @@ private:
         const DProg& P = L_.prog;
         uint64_t max_rows = P.n_keys ? occupied_ : 1;
         EmitArgs ea = emit_args((uint64_t)stream_rows_ + max_rows);
+        if (!table_ready_) { // every batch went through the radix path (or none arrived): the result rows are in place already
+            if (P.n_keys == 0) {
+                ensure_table();
+            } else {
+                out_rows_ = stream_rows_;
+                return;
+            }
+        }
         SRB_CUDA(cudaMemsetAsync(ctr_dev_.p, 0, sizeof(Counters), stream));
         int blocks = (int)std::min<uint64_t>((cap_ + 255) / 256, (uint64_t)ctx->n_sms * 16);
         k_emit<<<blocks, 256, 0, stream>>>(P, slots_.as<uint8_t>(), cap_, ea, ctr_dev_.as<Counters>(), stream_rows_);
@@ -2142,6 +2273,14 @@ private:
     bool rf_fused_ = getenv("SRB_RF_FUSED") != nullptr;           // opt-in: all runtime filters of a scan in one kernel (k_filter_rf_multi)
     bool no_shared_agg_ = getenv("SRB_NO_SHARED_AGG") != nullptr; // test / measurement hook: the interpreter updates the table per row
     bool no_partition_ = getenv("SRB_NO_PARTITION") != nullptr;   // test / measurement hook: direct table updates for every batch
+    // The radix-partitioned aggregation is correct (tests/test_gpu_radix_agg.py) but measured SLOWER than the table path on a B200
+    // (61 ms vs 26 ms for 600 M rows / 100 M keys), so it is opt-in: SRB_RADIX=1.
+    bool no_radix_ = getenv("SRB_RADIX") == nullptr || getenv("SRB_NO_RADIX") != nullptr;
+    int64_t radix_min_rows_ = getenv("SRB_RADIX_MIN_ROWS") ? atoll(getenv("SRB_RADIX_MIN_ROWS")) : ((int64_t)1 << 24); // (test hook: smaller batches)
+    bool table_ready_ = false;                                     // the group table is allocated and cleared (init_table defers large ones)
+    int64_t radix_rows_ = 0, radix_batches_ = 0;                   // groups the radix path left at the front of the output arrays
+    DevBuf rx_cursor_, rx_a_, rx_b_, rx_ctr_;
+    PinnedBuf rx_hctr_;
     DevBuf hc_k_, hc_v_, hc_v2_, hc_ctr_;                                 // permuted (key, value) copy of the current batch + its 2 x 256 counters
     ColBind hc_cols_[MAX_COLS], nn_cols_[MAX_COLS];
     bool batch_partitioned_ = false, batch_has_nulls_ = false, batch_stripped_ = false;

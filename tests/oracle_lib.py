@@ -82,6 +82,14 @@ class Oracle:
         L.orc_rf_info.restype = C.c_int64
         L.orc_rf_info.argtypes = [C.c_void_p, C.c_int]
         L.orc_rf_directory.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_for_encode.restype = C.c_int64
+        L.orc_for_encode.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_int64]
+        L.orc_for_decode.restype = C.c_int64
+        L.orc_for_decode.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int64]
+        L.orc_for_decode_pages.restype = C.c_int64
+        L.orc_for_decode_pages.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_int]
+        L.orc_bits.restype = C.c_uint8
+        L.orc_bits.argtypes = [C.c_int64, C.c_int64, C.c_int]
         if L.orc_has_hw_crc():
             L.orc_hw_crc32c_u64.restype = C.c_uint32
             L.orc_hw_crc32c_u64.argtypes = [C.c_uint32, C.c_uint64]
@@ -157,6 +165,43 @@ class Oracle:
             return K.decode_chunk(self.lib.orc_result_chunk(r).contents)
         finally:
             self.lib.orc_result_free(r)
+
+    # ---- segment data pages (oracle/orc_page.cpp) -------------------------------------------------------------------------------
+    def for_encode(self, values) -> bytes:
+        """one frame-of-reference page of a numpy array of a signed integer type (int8..int64, or capi.I128)"""
+        import numpy as np
+        a = np.ascontiguousarray(values)
+        cap = a.nbytes * 9 + 4096 + 2 * (len(a) // 128 + 1) * (a.dtype.itemsize + 2)
+        out = np.empty(cap, np.uint8)
+        n = self.lib.orc_for_encode(a.ctypes.data, a.dtype.itemsize, len(a), out.ctypes.data, cap)
+        if n <= 0:
+            raise RuntimeError("oracle: for_encode")
+        return out[:n].tobytes()
+
+    def for_decode(self, page: bytes, dtype):
+        import numpy as np
+        buf = np.frombuffer(page, np.uint8)
+        n = int.from_bytes(page[-4:], "little") if len(page) >= 5 else 0
+        out = np.zeros(max(n, 1), dtype)
+        got = self.lib.orc_for_decode(buf.ctypes.data, len(page), np.dtype(dtype).itemsize, out.ctypes.data, len(out))
+        if got < 0:
+            raise RuntimeError("oracle: corrupt frame-of-reference page")
+        return out[:got]
+
+    def for_decode_pages(self, data, offs, rows, dtype, n_threads: int = 1):
+        """pages [offs[p], offs[p+1]) of `data` (uint8 array) whose values start at rows[p] -> the decoded column"""
+        import numpy as np
+        offs = np.ascontiguousarray(offs, np.int64)
+        rows = np.ascontiguousarray(rows, np.int64)
+        out = np.empty(int(rows[-1]), dtype)
+        bad = self.lib.orc_for_decode_pages(data.ctypes.data, offs.ctypes.data, rows.ctypes.data, len(offs) - 1, np.dtype(dtype).itemsize, out.ctypes.data, n_threads)
+        if bad:
+            raise RuntimeError("oracle: corrupt frame-of-reference page")
+        return out
+
+    def bits(self, v: int, width: int) -> int:
+        lo, hi = K.split128(v)
+        return self.lib.orc_bits(lo, hi, width)
 
     def checked_binop(self, width, op, a, b):
         alo, ahi = K.split128(a)

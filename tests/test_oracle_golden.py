@@ -534,3 +534,49 @@ def test_agg_hash_map_not_found_selection(oracle, kind):
     keys = [e.slot(0, K.TYPE_VARCHAR if "string" in kind else K.TYPE_INT)] + ([e.slot(1, K.TYPE_INT)] if two else [])
     plan = ScanAggPlan(exprs=e, keys=keys, aggs=[(K.AGG_COUNT, None)], phase=K.AGG_UPDATE_SERIALIZE)
     assert oracle.agg_lookup_sequence(plan, chunks, LOOKUP_OPS) == LOOKUP_EXPECT
+
+
+# ---- segment data pages: frame-of-reference coding (oracle/orc_page.cpp) -----------------------------------------------------------
+def test_for_coding_round_trips_of_the_reference_tests(oracle):
+    # be/test/util/frame_of_reference_coding_test.cpp:70-84 (half / one / two / two and a half frames), :98-115 (int64), :117-159
+    for n in (64, 128, 256, 320):
+        a = np.arange(n, dtype=np.int32)
+        assert (oracle.for_decode(oracle.for_encode(a), np.int32) == a).all()
+    a = np.arange(320, dtype=np.int64)
+    assert (oracle.for_decode(oracle.for_encode(a), np.int64) == a).all()
+    assert oracle.for_decode(oracle.for_encode(np.array([2019], np.int32)), np.int32).tolist() == [2019]
+    assert oracle.for_decode(oracle.for_encode(np.array([2019, 2020], np.int32)), np.int32).tolist() == [2019, 2020]
+    empty = oracle.for_encode(np.zeros(0, np.int32))
+    assert len(empty) == 4 + 1 and len(oracle.for_decode(empty, np.int32)) == 0  # TestZeroValue
+
+
+def test_for_page_sizes_and_bits_of_the_reference_tests(oracle):
+    # be/test/storage/rowset/frame_of_reference_page_test.cpp:269-283: 0..127 ascending -> deltas of 1 bit: 4 + 16 + footer 7 = 27 bytes
+    page = oracle.for_encode(np.arange(128, dtype=np.int32))
+    assert len(page) == 27 and page[-7] == 1 and page[-6] == 1 and page[-5] == 128 and int.from_bytes(page[-4:], "little") == 128
+    # :304-318: 128..1 descending -> value - min in 7 bits: 4 + 112 + 7 = 123 bytes
+    page = oracle.for_encode((128 - np.arange(128)).astype(np.int32))
+    assert len(page) == 123 and page[-7] == 0 and page[-6] == 7
+    # :320-335 TestFindBitsOfInt
+    assert [oracle.bits(0x06, 1), oracle.bits(0x0F, 1), oracle.bits(0x000100FF, 4), oracle.bits(0x1FFFFFFFF, 8), oracle.bits(0, 16)] == [3, 4, 17, 33, 0]
+
+
+def test_for_page_layout_bit_for_bit(oracle):
+    # frame_of_reference_coding.cpp:95-117: values packed MSB first; the example of the comment: 1, 2, 4, 8 in 4 bits -> 0001 0010 0100 1000
+    page = oracle.for_encode(np.array([11, 3, 10, 5, 7, 18], np.int32))  # min 3, deltas 8 0 7 2 4 15 in 4 bits
+    assert page[:4] == (3).to_bytes(4, "little") and page[4:7] == bytes([0x80, 0x72, 0x4F]) and page[7:9] == bytes([0, 4])
+    rng = np.random.default_rng(5)
+    for dt, lo, hi in ((np.int8, -60, 60), (np.int16, -9000, 9000), (np.int32, -2**30, 2**30), (np.int64, -2**61, 2**61)):
+        for n in (1, 127, 128, 129, 1000, 4096):
+            a = rng.integers(lo, hi, n).astype(dt)
+            assert (oracle.for_decode(oracle.for_encode(a), dt) == a).all()
+            s = np.sort(a)  # non-decreasing frames take the delta format
+            p = oracle.for_encode(s)
+            assert (oracle.for_decode(p, dt) == s).all() and p[-5 - 2 * ((n + 127) // 128)] == 1
+    # the overflow format (2) keeps the values themselves: one frame whose range does not fit the type
+    a = np.array([-2**31, 2**31 - 1, 0, 5], np.int32)
+    p = oracle.for_encode(a)
+    assert p[-7] == 2 and p[-6] == 32 and (oracle.for_decode(p, np.int32) == a).all()
+    wide = K.to_i128_array([3 * 10**30, -7 * 10**29, 12345, 0, 10**37])
+    got = oracle.for_decode(oracle.for_encode(wide), K.I128)
+    assert (got["lo"] == wide["lo"]).all() and (got["hi"] == wide["hi"]).all()
