@@ -34,6 +34,7 @@ typedef int32_t srb_status;
 #define SRB_MEM_LIMIT_EXCEEDED 5
 #define SRB_INTERNAL_ERROR 6
 #define SRB_END_OF_FILE 30
+#define SRB_CORRUPTION 32
 #define SRB_INVALID_ARGUMENT 33
 
 /* ---- logical types: LogicalType (be/src/types/logical_type.h:27-77), same numeric values -------- */
@@ -251,6 +252,33 @@ srb_status srb_topn_create(srb_ctx* ctx, const srb_topn_plan* plan, srb_op** out
 /* Operator::push_chunk (operator.h:121). Columns may be HOST/PINNED (staged + copied) or DEVICE (used in place,
  * must stay valid until the next srb_op_sync / set_finishing). n_rows is not limited to chunk_size. */
 srb_status srb_op_push_chunk(srb_op* op, const srb_chunk* chunk);
+/* ---- encoded segment pages straight into a scan operator -----------------------------------------------------------
+ * What SegmentIterator / ScalarColumnIterator hand the scan on the CPU after decoding (segment_iterator.cpp:1411-1760,
+ * FrameOfReferencePageDecoder::next_batch frame_of_reference_page.h:107-223, PlainPageDecoder::next_batch plain_page.h:133-276) is decoded
+ * here on the device: the ENCODED page bytes are what crosses PCIe. One call = one row range of the table: for every column its data pages
+ * covering exactly those n_rows rows, in order. encoding = EncodingTypePB (gensrc/proto/segment.proto:49-58): SRB_ENC_PLAIN ([u32 count]
+ * [values]) or SRB_ENC_FOR (frame-of-reference, frame_of_reference_coding.h:78-101); fixed-width NOT NULL columns (type widths 1..16).
+ * Page bytes may be HOST / PINNED (copied, overlapped with the previous call's kernels) or DEVICE. A corrupt page (footer / frame sizes
+ * that do not fit) fails this or the next call on the operator with SRB_CORRUPTION, as Status::Corruption does in the decoder's init(). */
+#define SRB_ENC_PLAIN 2
+#define SRB_ENC_FOR 7
+typedef struct srb_page {
+    int64_t offset; /* first byte of the page inside srb_page_column.data */
+    int64_t bytes;
+    int64_t n_rows; /* values in the page (the footer / header says the same) */
+} srb_page;
+typedef struct srb_page_column {
+    int32_t type;      /* srb_logical_type */
+    int32_t precision; /* decimals */
+    int32_t scale;
+    int32_t encoding;  /* SRB_ENC_* */
+    const void* data;  /* the pages' bytes; pages need not be contiguous or ordered by offset */
+    int64_t bytes;     /* length of data (+ at least 0 bytes of slack: the library pads its own copy) */
+    int32_t mem_kind;  /* srb_mem_kind of data */
+    int32_t n_pages;
+    const srb_page* pages; /* in row order; their n_rows add up to the call's n_rows */
+} srb_page_column;
+srb_status srb_op_push_pages(srb_op* op, int32_t n_cols, const int32_t* slot_ids, const srb_page_column* cols, int64_t n_rows);
 /* Operator::set_finishing (operator.h:66), idempotent */
 srb_status srb_op_set_finishing(srb_op* op);
 /* Operator::has_output / need_input / is_finished (operator.h:95-105): 1 / 0 */

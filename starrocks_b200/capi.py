@@ -15,7 +15,7 @@ import numpy as np
 
 # ---- constants ------------------------------------------------------------------------------------------
 OK, CANCELLED, NOT_IMPLEMENTED, RUNTIME_ERROR, MEM_LIMIT_EXCEEDED, INTERNAL_ERROR = 0, 1, 3, 4, 5, 6
-END_OF_FILE, INVALID_ARGUMENT = 30, 33
+END_OF_FILE, CORRUPTION, INVALID_ARGUMENT = 30, 32, 33
 
 TYPE_TINYINT, TYPE_SMALLINT, TYPE_INT, TYPE_BIGINT, TYPE_LARGEINT, TYPE_DOUBLE = 1, 3, 5, 7, 9, 11
 TYPE_VARCHAR, TYPE_BOOLEAN, TYPE_VARBINARY = 17, 24, 46

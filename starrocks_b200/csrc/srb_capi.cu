@@ -115,6 +115,13 @@ srb_status srb_op_push_chunk(srb_op* op, const srb_chunk* chunk) {
     return SRB_OK;
     SRB_API_END
 }
+srb_status srb_op_push_pages(srb_op* op, int32_t n_cols, const int32_t* slot_ids, const srb_page_column* cols, int64_t n_rows) {
+    SRB_API_BEGIN
+    OP_GUARD(op)
+    op->push_pages(n_cols, slot_ids, cols, n_rows);
+    return SRB_OK;
+    SRB_API_END
+}
 srb_status srb_op_set_finishing(srb_op* op) {
     SRB_API_BEGIN
     OP_GUARD(op)

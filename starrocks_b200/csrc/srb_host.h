@@ -334,6 +334,8 @@ struct srb_op {
     // runtime filters: join ops build them from their build side, scan-filter ops apply them
     virtual struct srb_runtime_filter* build_runtime_filter(int, int64_t, int) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
     virtual void add_runtime_filter(const struct srb_runtime_filter*, int) { throw srb::Error(SRB_NOT_IMPLEMENTED, "this operator does not take runtime filters"); }
+    // encoded segment pages (scan operators): decoded on the device in front of the scan
+    virtual void push_pages(int32_t, const int32_t*, const srb_page_column*, int64_t) { throw srb::Error(SRB_NOT_IMPLEMENTED, "this operator does not take encoded pages"); }
     // streaming pre-aggregation (aggregate operators in the update+serialize phase only)
     virtual void set_streaming_mode(int) { throw srb::Error(SRB_INVALID_ARGUMENT, "not an aggregate operator"); }
     virtual void streaming_stats(int64_t*, int64_t*, int32_t*) { throw srb::Error(SRB_INVALID_ARGUMENT, "not an aggregate operator"); }

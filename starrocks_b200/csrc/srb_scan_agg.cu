@@ -25,6 +25,7 @@
 #include "srb_rowpipe.cuh"
 #include "srb_shapes.cuh"
 #include "srb_radix_agg.cuh"
+#include "srb_pages.cuh"
 #include "srb_stream_policy.h"
 #include "srb_hcpart.cuh"
 
@@ -1099,6 +1100,8 @@ struct HostCol { // result column handed out by pull_chunk (host memory owned by
 
 struct Stage { // device staging of host chunks: one buffer per bound column
     DevBuf data[MAX_COLS], nulls[MAX_COLS], offsets[MAX_COLS];
+    DevBuf enc[MAX_COLS], pdesc[MAX_COLS], fdir[MAX_COLS]; // encoded pages: their bytes, page descriptors and frame directory
+    std::vector<PageDesc> hdesc[MAX_COLS];                   // host copies of the page descriptors (alive until the stage is reused)
     int64_t rows = 0;
     int64_t bin_bytes[MAX_COLS] = {0};
     cudaEvent_t copied = nullptr;
@@ -1162,6 +1165,123 @@ public:
         }
     }
 
+    // Encoded data pages of one row range -> the current stage's column buffers, decoded on the device; then the stage is launched
+    // like a stage of host rows. The copy of this call's pages overlaps the kernels of the previous call's rows.
+    void push_pages(int32_t n_cols, const int32_t* slot_ids, const srb_page_column* pc, int64_t n_rows) override {
+        if (finishing) throw Error(SRB_INTERNAL_ERROR, "push_pages after set_finishing");
+        if (cancelled) throw Error(SRB_CANCELLED, "operator cancelled");
+        if (n_cols < 0 || (n_cols && (!slot_ids || !pc)) || n_rows < 0) throw Error(SRB_INVALID_ARGUMENT, "bad page set");
+        if (n_rows == 0) return;
+        if (n_rows >= ((int64_t)1 << 31)) throw Error(SRB_INVALID_ARGUMENT, "more than 2^31 rows in one page set");
+        if (!lowered_) { // the plan is lowered against the page set's column types (fixed width, NOT NULL)
+            std::vector<srb_column> desc((size_t)n_cols);
+            for (int i = 0; i < n_cols; i++) {
+                desc[(size_t)i] = srb_column{};
+                desc[(size_t)i].type = pc[i].type;
+                desc[(size_t)i].precision = pc[i].precision;
+                desc[(size_t)i].scale = pc[i].scale;
+            }
+            srb_chunk first{};
+            first.n_rows = n_rows;
+            first.n_cols = n_cols;
+            first.slot_ids = slot_ids;
+            first.cols = desc.data();
+            lower(&first);
+        }
+        if (stage_[cur_stage_].rows) flush_stage(); // host rows pushed earlier keep their place in front of these
+        Stage& st = stage_[cur_stage_];
+        if (!copy_stream_ && !(copy_stream_ = ctx->take_stream())) throw Error(SRB_INTERNAL_ERROR, "cudaStreamCreate failed");
+        if (!st.copied && !(st.copied = ctx->take_event(false))) throw Error(SRB_INTERNAL_ERROR, "cudaEventCreate failed");
+        if (!page_err_.p) {
+            page_err_.ensure(ctx, 8);
+            SRB_CUDA(cudaMemsetAsync(page_err_.p, 0, 8, stream));
+        }
+        struct Work {
+            int col, width, enc;
+            int64_t frames, n_pages;
+            const uint8_t* bytes;
+        };
+        std::vector<Work> work;
+        for (size_t i = 0; i < L_.cols.size(); i++) {
+            int k = -1;
+            for (int j = 0; j < n_cols; j++)
+                if (slot_ids[j] == L_.cols[i].slot) k = j;
+            if (k < 0) throw Error(SRB_INVALID_ARGUMENT, fmt("slot %d not in the page set", L_.cols[i].slot));
+            const srb_page_column& c = pc[k];
+            const int w = type_width(c.type);
+            if (c.type != L_.cols[i].type) throw Error(SRB_INVALID_ARGUMENT, fmt("slot %d changed type", L_.cols[i].slot));
+            if (w == 0 || L_.cols[i].nullable) throw Error(SRB_NOT_IMPLEMENTED, "encoded pages of binary or nullable columns");
+            if (c.encoding != SRB_ENC_FOR && c.encoding != SRB_ENC_PLAIN) throw Error(SRB_NOT_IMPLEMENTED, fmt("page encoding %d", c.encoding));
+            if (c.encoding == SRB_ENC_FOR && c.type == SRB_TYPE_DOUBLE) throw Error(SRB_INVALID_ARGUMENT, "frame-of-reference pages hold integers");
+            if (!c.data || c.bytes < 0 || c.n_pages < 0 || (c.n_pages && !c.pages)) throw Error(SRB_INVALID_ARGUMENT, "bad page column");
+            // page descriptors: row positions and frame numbers are prefix sums over the pages
+            std::vector<PageDesc>& hdesc_ = st.hdesc[i];
+            hdesc_.resize((size_t)c.n_pages);
+            int64_t rows = 0, frames = 0;
+            for (int p = 0; p < c.n_pages; p++) {
+                const srb_page& g = c.pages[p];
+                if (g.offset < 0 || g.bytes < 0 || g.n_rows < 0 || g.offset + g.bytes > c.bytes || g.bytes >= ((int64_t)1 << 32))
+                    throw Error(SRB_INVALID_ARGUMENT, "page outside its column's bytes");
+                hdesc_[(size_t)p] = PageDesc{(uint64_t)g.offset, (uint64_t)rows, (uint32_t)g.bytes, (uint32_t)g.n_rows, (uint32_t)frames, 0u};
+                rows += g.n_rows;
+                frames += (g.n_rows + 127) / 128;
+            }
+            if (rows != n_rows) throw Error(SRB_INVALID_ARGUMENT, fmt("slot %d: pages hold %lld rows, the page set %lld", L_.cols[i].slot, (long long)rows, (long long)n_rows));
+            st.data[i].ensure(ctx, (size_t)n_rows * w);
+            const uint8_t* bytes = (const uint8_t*)c.data;
+            if (c.mem_kind != SRB_MEM_DEVICE) {
+                st.enc[i].ensure(ctx, (size_t)c.bytes + 64); // decoders may read a few bytes past a frame: the copy is padded
+                if (c.bytes) SRB_CUDA(cudaMemcpyAsync(st.enc[i].p, c.data, (size_t)c.bytes, cudaMemcpyHostToDevice, copy_stream_));
+                bytes = st.enc[i].as<uint8_t>();
+            }
+            st.pdesc[i].ensure(ctx, std::max<size_t>(1, (size_t)c.n_pages) * sizeof(PageDesc));
+            if (c.n_pages)
+                SRB_CUDA(cudaMemcpyAsync(st.pdesc[i].p, hdesc_.data(), (size_t)c.n_pages * sizeof(PageDesc), cudaMemcpyHostToDevice, copy_stream_));
+            if (c.encoding == SRB_ENC_FOR) st.fdir[i].ensure(ctx, std::max<size_t>(1, (size_t)frames) * sizeof(FrameDesc));
+            work.push_back(Work{(int)i, w, c.encoding, frames, c.n_pages, bytes});
+        }
+        SRB_CUDA(cudaEventRecord(st.copied, copy_stream_));
+        SRB_CUDA(cudaStreamWaitEvent(stream, st.copied, 0));
+        unsigned int* err = page_err_.as<unsigned int>();
+        for (const Work& wk : work) {
+            if (wk.n_pages == 0) continue;
+            uint8_t* out = st.data[wk.col].as<uint8_t>();
+            const PageDesc* pd = st.pdesc[wk.col].as<PageDesc>();
+            if (wk.enc == SRB_ENC_PLAIN) {
+                k_plain_decode<<<dim3(64, (unsigned)wk.n_pages), 256, 0, stream>>>(wk.bytes, pd, wk.width, out, err);
+                launches++;
+                continue;
+            }
+            FrameDesc* fd = st.fdir[wk.col].as<FrameDesc>();
+            k_page_dir<<<(int)wk.n_pages, 256, 0, stream>>>(wk.bytes, pd, wk.width, fd, err);
+            const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((wk.frames + 7) / 8, (int64_t)ctx->n_sms * 16));
+            switch (wk.width) {
+            case 1: k_for_decode<1><<<grid, 256, 0, stream>>>(wk.bytes, fd, wk.frames, out); break;
+            case 2: k_for_decode<2><<<grid, 256, 0, stream>>>(wk.bytes, fd, wk.frames, out); break;
+            case 4: k_for_decode<4><<<grid, 256, 0, stream>>>(wk.bytes, fd, wk.frames, out); break;
+            case 8: k_for_decode<8><<<grid, 256, 0, stream>>>(wk.bytes, fd, wk.frames, out); break;
+            default: k_for_decode<16><<<grid, 256, 0, stream>>>(wk.bytes, fd, wk.frames, out);
+            }
+            launches += 2;
+        }
+        SRB_CUDA(cudaGetLastError());
+        rows_in += n_rows;
+        st.rows = n_rows;
+        pages_pushed_ = true;
+        flush_stage(); // checks the previous batch, launches this one, switches stages
+        check_page_errors(false);
+    }
+    // the decode kernels flag footers / frame sizes that do not fit their page (Status::Corruption in FrameOfReferencePageDecoder::init)
+    void check_page_errors(bool wait) {
+        if (!pages_pushed_) return;
+        if (wait) SRB_CUDA(cudaStreamSynchronize(stream));
+        // without `wait` this sees the flags of every batch whose kernels have finished (the previous call's at least: flush_stage waited for it)
+        unsigned int e[2] = {0, 0};
+        SRB_CUDA(cudaMemcpyAsync(e, page_err_.p, 8, cudaMemcpyDeviceToHost, copy_stream_));
+        SRB_CUDA(cudaStreamSynchronize(copy_stream_));
+        if (e[0]) throw Error(SRB_CORRUPTION, e[0] & PAGE_ERR_FOOTER ? "corrupt data page: footer / header does not match the page" : "corrupt data page: frames do not fit the page");
+    }
+
     // Operator::set_runtime_bloom_filters / eval_runtime_bloom_filters (pipeline/operator.h:185): a scan-filter operator narrows its
     // selection with the join's runtime filter on column `slot` before compacting. Attach before the first chunk is pushed.
     void add_runtime_filter(const srb_runtime_filter* rf, int slot) override {
@@ -1183,6 +1303,7 @@ public:
         if (!lowered_) { // no chunk ever arrived: lower against an empty description so that result types exist
             lower(nullptr);
         }
+        check_page_errors(true);
         produce_output();
     }
     bool has_output() override { return finishing && !finished && out_pos_ < out_rows_; }
@@ -2277,6 +2398,8 @@ private:
     // (61 ms vs 26 ms for 600 M rows / 100 M keys), so it is opt-in: SRB_RADIX=1.
     bool no_radix_ = getenv("SRB_RADIX") == nullptr || getenv("SRB_NO_RADIX") != nullptr;
     int64_t radix_min_rows_ = getenv("SRB_RADIX_MIN_ROWS") ? atoll(getenv("SRB_RADIX_MIN_ROWS")) : ((int64_t)1 << 24); // (test hook: smaller batches)
+    DevBuf page_err_;
+    bool pages_pushed_ = false;
     bool table_ready_ = false;                                     // the group table is allocated and cleared (init_table defers large ones)
     int64_t radix_rows_ = 0, radix_batches_ = 0;                   // groups the radix path left at the front of the output arrays
     DevBuf rx_cursor_, rx_a_, rx_b_, rx_ctr_;

@@ -21,7 +21,7 @@ _lib = None
 
 EXPORTS = [
     "srb_ctx_create", "srb_ctx_destroy", "srb_last_error", "srb_ctx_device_info", "srb_ctx_trim", "srb_op_stream",
-    "srb_scan_agg_create", "srb_join_create", "srb_op_push_chunk", "srb_op_set_finishing", "srb_op_has_output",
+    "srb_scan_agg_create", "srb_join_create", "srb_op_push_chunk", "srb_op_push_pages", "srb_op_set_finishing", "srb_op_has_output",
     "srb_op_need_input", "srb_op_is_finished", "srb_op_pull_chunk", "srb_op_pull_all", "srb_op_pull_device",
     "srb_op_cancel", "srb_op_close", "srb_op_sync", "srb_op_counters", "srb_op_profile",
     "srb_join_probe_push_chunk", "srb_join_probe_set_finishing", "srb_join_probe_has_output",
@@ -62,6 +62,8 @@ def lib() -> C.CDLL:
     L.srb_topn_create.argtypes = [vp, C.POINTER(K.srb_topn_plan), C.POINTER(vp)]
     for f in ("srb_op_push_chunk", "srb_join_probe_push_chunk"):
         getattr(L, f).argtypes = [vp, C.POINTER(K.srb_chunk)]
+    from . import pages as PG
+    L.srb_op_push_pages.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(PG.srb_page_column), i64]
     for f in ("srb_op_set_finishing", "srb_join_probe_set_finishing", "srb_op_cancel", "srb_op_sync", "srb_op_has_output",
               "srb_op_need_input", "srb_op_is_finished", "srb_join_probe_has_output", "srb_join_probe_need_input",
               "srb_join_probe_is_finished"):
@@ -276,6 +278,14 @@ class ScanAggOperator(_Operator):
         _check(ctx.L.srb_scan_agg_create(ctx.h, C.byref(plan.c), C.byref(h)))
         super().__init__(ctx, h)
         self._plan = plan
+
+    def push_pages(self, columns):
+        """columns: {slot: pages.PageColumn}, every column's encoded data pages over the same row range (srb_op_push_pages): decoded on
+        the device in front of the scan (SegmentIterator -> page decoders on the CPU in the reference)"""
+        from . import pages as PG
+        n, slots, cols, keep = PG.to_c(columns)
+        rows = next(iter(columns.values())).n_rows() if columns else 0
+        _check(self.L.srb_op_push_pages(self.h, n, slots, cols, rows))
 
     def add_runtime_filter(self, rf: "RuntimeFilter", slot_id: int):
         """scan-filter plans only, before the first push_chunk (Operator::eval_runtime_bloom_filters)"""
