@@ -154,8 +154,38 @@ def cpu_scan_baseline(w, seconds: float, threads: int, phase=None):
     orc.scan_agg(plan(), ch1, n_threads=1)
     one = r1 / (time.perf_counter() - t0)
     return {"value": rows / best, "unit": "rows/s", "cores": threads, "kind": "port", "value_1_thread": one,
+            "value_from_pages": cpu_from_pages(orc, w, ch, threads),
             "sample": f"first {rows} rows of the same synthetic table, 4096-row chunks, {threads} threads with private tables + merge, "
-                      f"1 warm-up + best of 5; value_1_thread: one run over {r1} rows"}
+                      f"1 warm-up + best of 5; value_1_thread: one run over {r1} rows; value_from_pages: the same sample fed as frame-of-reference "
+                      f"pages (decode with {threads} workers + the pipeline, best of 2), the input of the GPU arm's e2e"}
+
+
+def cpu_from_pages(orc, w, ch, threads: int, runs: int = 2):
+    """the CPU pipeline fed like the GPU arm's e2e: the chunk's columns as frame-of-reference pages (built untimed by the oracle's encoder),
+    every run = decode all pages (`threads` workers over the pages) + scan / aggregate -> rows/s (best of `runs`)"""
+    import numpy as np
+    from starrocks_b200 import capi as K
+    page_rows = 1 << 16
+    enc = {}
+    for slot, c in ch.columns.items():
+        a = np.asarray(c.data)
+        parts, offs, rows = [], [0], [0]
+        for s0 in range(0, len(a), page_rows):
+            p = orc.for_encode(a[s0:s0 + page_rows])
+            parts.append(p)
+            offs.append(offs[-1] + len(p))
+            rows.append(min(len(a), s0 + page_rows))
+        enc[slot] = (np.frombuffer(b"".join(parts) + b"\0" * 16, np.uint8), np.array(offs, np.int64), np.array(rows, np.int64), a.dtype, c)
+    best = None
+    for _ in range(runs):
+        t0 = time.perf_counter()
+        dec = K.Chunk(ch.n_rows)
+        for slot, (data, offs, rows, dt, c) in enc.items():
+            dec.columns[slot] = K.Column.from_ints(c.type, orc.for_decode_pages(data, offs, rows, dt, threads), None, c.precision, c.scale)
+        orc.scan_agg(w["plan"](), dec, n_threads=threads)
+        dt_ = time.perf_counter() - t0
+        best = dt_ if best is None else min(best, dt_)
+    return ch.n_rows / best
 
 
 JOIN_METRIC = {"q3": "TPC-H SF100 Q3 rows/s (lineitem rows)", "ssb": "SSB SF100 Q4.1 rows/s (lineorder rows)"}
@@ -268,6 +298,7 @@ def run_reference(args):
         rows = int(min(max(rate * per_step, probe_rows), 64 << 20))
         ch = T.host_chunk(w["table"], 0, rows, w["cols"], **w["kw"])
         run = lambda: orc.scan_agg(w["plan"](), ch, n_threads=threads)
+        from_pages = cpu_from_pages(orc, w, ch, threads)
         name, metric, scaling, bpr = w["name"], w["metric"], args.scaling, w["bytes_per_row"]
         rows_cfg = args.rows or w["rows"]
         sample = f"each step: first {rows} rows of the same synthetic table, 4096-row chunks, {threads} threads"
@@ -279,6 +310,10 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     value = rows * args.steps / dt
     cb = {"value": value, "unit": "rows/s", "cores": threads, "kind": "port", "sample": sample}
+    if args.query not in ("q3", "ssb"):
+        cb["value_from_pages"] = from_pages
+        cb["sample"] += ("; `value` times the pipeline over DECODED host columns (the easier job: the GPU arm's e2e starts from encoded pages); "
+                         "value_from_pages = the same sample fed as frame-of-reference pages, decode included")
     print(json.dumps({"impl": "reference", "metric": metric, "value": value, "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
                       "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "int128", "data": "synthetic",
                       "config": base_config(name, rows_cfg, bpr, world, scaling), "rows_per_step": rows,
@@ -548,6 +583,62 @@ def scan_e2e(env, args, query, w, chunk, rows, warmup, steps):
                                     + ("; the ~10^7 result groups stay on the device, the row count is read" if query == "highcard" else "")}
 
 
+def scan_e2e_pages(env, args, query, w, tensors, row0, rows, warmup, steps):
+    """The same query fed the way the BE's scan is fed: ENCODED data pages (frame-of-reference, the reference's FOR_ENCODING) in pinned host
+    memory -> srb_op_push_pages (H2D copy of the page bytes, decode on the device, scan, aggregate) -> result on the host. The pages are built
+    (untimed) from the resident synthetic columns by the torch page builder, byte-identical to the reference's ForEncoder output."""
+    import ctypes as C
+    from starrocks_b200 import capi as K, ops, pages as PG, tpch_synth as T
+    torch, ctx = env.torch, env.ctx
+    n = int(min(args.e2e_rows, rows))
+    page_rows, set_pages = 1 << 16, 128  # 64 Ki values per page, 8 Mi rows per page set
+    cols, pins, h2d = {}, [], 0
+    try:
+        for name in w["cols"]:
+            slot, t, p, s = T._SLOT[name]
+            enc, pages = PG.for_encode_column(tensors[name][row0:row0 + n], page_rows)
+            nb = int(enc.numel())
+            ptr = C.c_void_p()
+            ops._check(ctx.L.srb_pinned_alloc(ctx.h, nb + 64, C.byref(ptr)))
+            pins.append(ptr)
+            ops._check(ctx.L.srb_memcpy_d2h(ctx.h, ptr, enc.data_ptr(), nb))
+            cols[slot] = PG.PageColumn(t, ptr.value, nb, pages, PG.ENC_FOR, p, s, K.MEM_PINNED)
+            h2d += nb
+            del enc
+        torch.cuda.empty_cache()
+        n_pages = len(next(iter(cols.values())).pages)
+        sets = [PG.prepare({slot: PG.slice_pages(c, a, min(a + set_pages, n_pages)) for slot, c in cols.items()}) for a in range(0, n_pages, set_pages)]
+
+        def step():
+            op = ops.ScanAggOperator(ctx, w["plan"]())
+            try:
+                for ps in sets:
+                    op.push_pages_prepared(ps)
+                op.set_finishing()
+                return op.pull_all() if query != "highcard" else op.pull_device()
+            finally:
+                op.close()
+
+        for _ in range(max(1, warmup - 1)):
+            out = step()
+        barrier(env)
+        steps = max(2, min(steps, 5))
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            out = step()
+        barrier(env)
+        dt = max_over_ranks(env, [time.perf_counter() - t0])[0]
+    finally:
+        for p in pins:
+            ctx.L.srb_pinned_free(ctx.h, p)
+    d2h = sum(len(K.column_pyvalues(c)) * max(K.type_width(c.type), 24) for c in out.columns.values()) if query != "highcard" else 8
+    return {"value": n * env.world * steps / dt, "unit": "rows/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "rows_per_step": n, "steps": steps,
+            "encoded_bytes_per_row": h2d / n, "decoded_bytes_per_row": w["bytes_per_row"],
+            "note": "frame-of-reference data pages (the reference's FOR_ENCODING, 64 Ki values per page) in pinned host memory pushed through "
+                    "srb_op_push_pages in page sets of 8 Mi rows: H2D copy of the encoded bytes, decode on the device, scan, aggregate; the copy of a "
+                    "page set overlaps the kernels of the previous one" + ("; the ~10^7 result groups stay on the device, the row count is read" if query == "highcard" else "")}, out
+
+
 def scan_parity_sample(env, args, query, w) -> bool:
     """the SAME multi-GPU plan (phase 1 -> exchange -> phase 2) over a bounded sample split over the ranks, against the oracle on rank 0"""
     from starrocks_b200 import distributed as D, tpch_synth as T
@@ -688,13 +779,22 @@ def bench_scan(env, args, query: str, steps: int, warmup: int, scaling: str, ten
         timed = phase_ms[-steps:]
         result["phase_ms_rank0"] = [sum(t[i] for t in timed) / len(timed) for i in range(len(timed[0]))]
     if not args.no_e2e:
-        result["e2e"] = scan_e2e(env, args, query, w, chunk, rows, warmup, steps)
+        # headline e2e: the scan fed with encoded pages (what crosses PCIe is what a segment holds); beside it the same query fed with
+        # already decoded host columns (srb_op_push_chunk), as round 1 measured it
+        result["e2e"], e2e_out = scan_e2e_pages(env, args, query, w, tensors, row0, rows, warmup, steps)
+        result["e2e_decoded_columns"] = scan_e2e(env, args, query, w, chunk, rows, warmup, steps)
+        if query != "highcard" and not args.no_parity:  # the page-fed result over the e2e slice against the resident-column result of the same rows
+            n_e = result["e2e"]["rows_per_step"]
+            ref_out, _ = scan_step(env, query, w, view_rows(env, w, tensors, row0, n_e)) if env.world == 1 else (None, 0)
+            if ref_out is not None:
+                result["e2e"]["same_result_as_resident_columns"] = rows_key(e2e_out) == rows_key(ref_out)
     if not args.no_parity:
         result["parity"] = scan_parity_sample(env, args, query, w)
         result["parity_sample"] = f"{args.parity_rows} rows of the same generator split over {world} rank(s), the same plan (exchange + merge included) vs the oracle"
         if query in ("q1", "q6"):
             result["parity_full"] = scan_parity_full(env, query, w, tensors, row0, rows, out)
             result["parity"] = result["parity"] and result["parity_full"]["ok"]
+        result["parity"] = result["parity"] and result.get("e2e", {}).get("same_result_as_resident_columns", True)
     if rank == 0 and world == 1 and not args.no_cpu:
         result["cpu_baseline"] = cpu_scan_baseline(w, args.cpu_seconds, env.cores)
     return result, tensors

@@ -259,7 +259,8 @@ srb_status srb_op_push_chunk(srb_op* op, const srb_chunk* chunk);
  * covering exactly those n_rows rows, in order. encoding = EncodingTypePB (gensrc/proto/segment.proto:49-58): SRB_ENC_PLAIN ([u32 count]
  * [values]) or SRB_ENC_FOR (frame-of-reference, frame_of_reference_coding.h:78-101); fixed-width NOT NULL columns (type widths 1..16).
  * Page bytes may be HOST / PINNED (copied, overlapped with the previous call's kernels) or DEVICE. A corrupt page (footer / frame sizes
- * that do not fit) fails this or the next call on the operator with SRB_CORRUPTION, as Status::Corruption does in the decoder's init(). */
+ * that do not fit) makes srb_op_set_finishing fail with SRB_CORRUPTION, as Status::Corruption does in the decoder's init(); its frames decode
+ * to nothing and are never read out of bounds. DEVICE-resident page bytes need 16 readable bytes after the last page. */
 #define SRB_ENC_PLAIN 2
 #define SRB_ENC_FOR 7
 typedef struct srb_page {

@@ -1217,12 +1217,19 @@ public:
             // page descriptors: row positions and frame numbers are prefix sums over the pages
             std::vector<PageDesc>& hdesc_ = st.hdesc[i];
             hdesc_.resize((size_t)c.n_pages);
-            int64_t rows = 0, frames = 0;
+            int64_t rows = 0, frames = 0, lo = c.bytes, hi = 0; // [lo, hi): the bytes this page set touches (a host copy moves only those)
             for (int p = 0; p < c.n_pages; p++) {
                 const srb_page& g = c.pages[p];
                 if (g.offset < 0 || g.bytes < 0 || g.n_rows < 0 || g.offset + g.bytes > c.bytes || g.bytes >= ((int64_t)1 << 32))
                     throw Error(SRB_INVALID_ARGUMENT, "page outside its column's bytes");
-                hdesc_[(size_t)p] = PageDesc{(uint64_t)g.offset, (uint64_t)rows, (uint32_t)g.bytes, (uint32_t)g.n_rows, (uint32_t)frames, 0u};
+                lo = std::min(lo, g.offset);
+                hi = std::max(hi, g.offset + g.bytes);
+            }
+            if (hi < lo) lo = hi = 0;
+            const int64_t rebase = c.mem_kind != SRB_MEM_DEVICE ? lo : 0;
+            for (int p = 0; p < c.n_pages; p++) {
+                const srb_page& g = c.pages[p];
+                hdesc_[(size_t)p] = PageDesc{(uint64_t)(g.offset - rebase), (uint64_t)rows, (uint32_t)g.bytes, (uint32_t)g.n_rows, (uint32_t)frames, 0u};
                 rows += g.n_rows;
                 frames += (g.n_rows + 127) / 128;
             }
@@ -1230,8 +1237,8 @@ public:
             st.data[i].ensure(ctx, (size_t)n_rows * w);
             const uint8_t* bytes = (const uint8_t*)c.data;
             if (c.mem_kind != SRB_MEM_DEVICE) {
-                st.enc[i].ensure(ctx, (size_t)c.bytes + 64); // decoders may read a few bytes past a frame: the copy is padded
-                if (c.bytes) SRB_CUDA(cudaMemcpyAsync(st.enc[i].p, c.data, (size_t)c.bytes, cudaMemcpyHostToDevice, copy_stream_));
+                st.enc[i].ensure(ctx, (size_t)(hi - lo) + 64); // decoders may read a few bytes past a frame: the copy is padded
+                if (hi > lo) SRB_CUDA(cudaMemcpyAsync(st.enc[i].p, (const uint8_t*)c.data + lo, (size_t)(hi - lo), cudaMemcpyHostToDevice, copy_stream_));
                 bytes = st.enc[i].as<uint8_t>();
             }
             st.pdesc[i].ensure(ctx, std::max<size_t>(1, (size_t)c.n_pages) * sizeof(PageDesc));
@@ -1269,13 +1276,12 @@ public:
         st.rows = n_rows;
         pages_pushed_ = true;
         flush_stage(); // checks the previous batch, launches this one, switches stages
-        check_page_errors(false);
+        // (corrupt pages are reported by set_finishing: asking the device here would stall the copy queue behind this call's own copies)
     }
     // the decode kernels flag footers / frame sizes that do not fit their page (Status::Corruption in FrameOfReferencePageDecoder::init)
     void check_page_errors(bool wait) {
         if (!pages_pushed_) return;
         if (wait) SRB_CUDA(cudaStreamSynchronize(stream));
-        // without `wait` this sees the flags of every batch whose kernels have finished (the previous call's at least: flush_stage waited for it)
         unsigned int e[2] = {0, 0};
         SRB_CUDA(cudaMemcpyAsync(e, page_err_.p, 8, cudaMemcpyDeviceToHost, copy_stream_));
         SRB_CUDA(cudaStreamSynchronize(copy_stream_));

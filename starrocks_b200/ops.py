@@ -279,6 +279,11 @@ class ScanAggOperator(_Operator):
         super().__init__(ctx, h)
         self._plan = plan
 
+    def push_pages_prepared(self, prepared):
+        """prepared = pages.prepare(columns): the C structures built once (a hot loop pushes the same page sets again and again)"""
+        n, slots, cols, keep, rows = prepared
+        _check(self.L.srb_op_push_pages(self.h, n, slots, cols, rows))
+
     def push_pages(self, columns):
         """columns: {slot: pages.PageColumn}, every column's encoded data pages over the same row range (srb_op_push_pages): decoded on
         the device in front of the scan (SegmentIterator -> page decoders on the CPU in the reference)"""

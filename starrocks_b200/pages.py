@@ -59,6 +59,13 @@ def to_c(columns: Dict[int, PageColumn]):
     return n, slots, cols, keep
 
 
+def prepare(columns: Dict[int, PageColumn]):
+    """-> the argument tuple of ops.ScanAggOperator.push_pages_prepared"""
+    n, slots, cols, keep = to_c(columns)
+    rows = next(iter(columns.values())).n_rows() if columns else 0
+    return n, slots, cols, keep, rows
+
+
 def slice_pages(col: PageColumn, first: int, last: int) -> PageColumn:
     """pages [first, last) of a column as a page set of their own (same byte buffer)"""
     return PageColumn(col.type, col.data, col.nbytes, col.pages[first:last], col.encoding, col.precision, col.scale, col.mem_kind, col.keep)
