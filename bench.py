@@ -58,8 +58,9 @@ def parse():
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-sub", action="store_true", help="headline only: skip the workloads under `queries`")
     ap.add_argument("--phase-times", action="store_true", help="add the per-stage host times of a step to the JSON line")
-    ap.add_argument("--gather", choices=["device", "nccl", "gloo", "torch"], default="nccl",
-                    help="N > 1, low-cardinality plans: how the intermediate rows travel (device = srb_comm_all_gather on the device chunk)")
+    ap.add_argument("--gather", choices=["device", "nccl", "gloo", "torch"], default="device",
+                    help="N > 1, low-cardinality plans: device = the ranks' aggregate states gathered and merged on the device in one call "
+                         "(srb_op_set_finishing_merged); nccl / gloo / torch = serialize -> host rows gathered -> merge operator")
     return ap.parse_args()
 
 
@@ -461,24 +462,26 @@ def scan_step(env, query: str, w, chunk, marks=None, collect=None, device_result
 
     mark()
     kw = {} if group_hint is None else {"group_hint": group_hint}
-    plan = w["plan"](phase=K.AGG_UPDATE_SERIALIZE, **kw) if two_phase else w["plan"](**kw)
+    merged_finish = two_phase and query in ("q1", "q6") and env.gather_device
+    plan = w["plan"](phase=K.AGG_UPDATE_SERIALIZE, **kw) if two_phase and not merged_finish else w["plan"](**kw)
     op = ops.ScanAggOperator(ctx, plan)
     op2 = None
     try:
         op.push_chunk(chunk)
-        op.set_finishing()
+        if merged_finish:
+            # phase 1 -> gather of the ranks' aggregate states -> merge -> finalize in ONE call, on the device (srb_op_set_finishing_merged)
+            mark()
+            op.set_finishing_merged(comm)
+            two_phase = False
+        else:
+            op.set_finishing()
         mark()
         if two_phase:
             if query in ("q1", "q6"):
                 # <= 4 intermediate rows per rank (AVG states are {sum,count} blobs): gathered, then merged on every rank
-                if env.host_ex is comm and env.gather_device:
-                    inter = op.pull_device()
-                    mark()
-                    recv = comm.all_gather(inter)
-                else:
-                    inter = op.pull_all()
-                    mark()
-                    recv = env.host_ex.all_gather(inter)
+                inter = op.pull_all()
+                mark()
+                recv = env.host_ex.all_gather(inter)
                 mark()
                 op2 = ops.ScanAggOperator(ctx, merge_plan(query, inter, env.world))
             else:

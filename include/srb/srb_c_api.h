@@ -394,6 +394,23 @@ void srb_partition_destroy(srb_partitioner* p);
 srb_status srb_partition_run_noalloc(int32_t device, void* cuda_stream, int32_t n_partitions, const srb_chunk* in, int32_t n_key_slots,
                                      const int32_t* key_slots, const srb_chunk* out, int64_t* counts_dev);
 
+/* Cancellation that reaches in-flight collectives (PipelineDriver::cancel -> operators' set_cancelled, pipeline_driver.cpp:316; the brpc
+ * exchange fails its pending RPCs): ncclCommAbort on this rank's communicator, callable from another thread while a collective is queued or
+ * running. Afterwards every call on the communicator returns SRB_CANCELLED; destroy it. srb_comm_check reports the communicator's asynchronous
+ * NCCL error state (a dead peer) without blocking. */
+srb_status srb_comm_abort(srb_comm* c);
+srb_status srb_comm_check(srb_comm* c);
+
+/* set_finishing of a low-cardinality aggregate operator on EVERY rank of the communicator at once: the ranks' group tables (their raw
+ * aggregate states) are all-gathered on the device and merged into every rank's table, then the operator finalises as usual — every rank
+ * pulls the GLOBAL result. One call stands for AggregateBlockingSink (update, serialize) -> ExchangeSink / ExchangeSource (gather,
+ * exchange_sink_operator.cpp:508-547) -> AggregateBlockingSink (merge, aggregator.cpp:871-875) -> finalize, without the intermediate rows
+ * ever visiting the host: states are what serialize carries (sum.h:113-117, avg.h:161-181, count.h:92-96, maxmin.h), and integer states
+ * merge exactly. Collective: every rank must call it, with the same plan. Tables of at most 1024 slots (a few hundred groups); a rank whose
+ * table outgrew that makes the call fail with SRB_NOT_IMPLEMENTED on every rank (use the serialize -> srb_comm_all_gather -> merge operators
+ * then). The plan's phase must be SRB_AGG_UPDATE_FINALIZE. */
+srb_status srb_op_set_finishing_merged(srb_op* op, srb_comm* comm);
+
 /* communicator bootstrap: rank 0 calls srb_comm_unique_id, the 128 bytes travel out of band (the harness uses
  * torch.distributed's store), every rank calls srb_comm_create with them. */
 srb_status srb_comm_unique_id(void* out128);

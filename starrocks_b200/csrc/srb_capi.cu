@@ -122,6 +122,13 @@ srb_status srb_op_push_pages(srb_op* op, int32_t n_cols, const int32_t* slot_ids
     return SRB_OK;
     SRB_API_END
 }
+srb_status srb_op_set_finishing_merged(srb_op* op, srb_comm* comm) {
+    SRB_API_BEGIN
+    OP_GUARD(op)
+    op->set_finishing_merged(comm);
+    return SRB_OK;
+    SRB_API_END
+}
 srb_status srb_op_set_finishing(srb_op* op) {
     SRB_API_BEGIN
     OP_GUARD(op)

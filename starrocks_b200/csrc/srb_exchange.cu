@@ -15,6 +15,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -240,6 +241,8 @@ struct Nccl {
     int (*GetUniqueId)(ncclUniqueId_*) = nullptr;
     int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId_, int) = nullptr;
     int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*CommAbort)(ncclComm_t) = nullptr;
+    int (*CommGetAsyncError)(ncclComm_t, int*) = nullptr;
     int (*GroupStart)() = nullptr;
     int (*GroupEnd)() = nullptr;
     int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
@@ -262,6 +265,8 @@ Nccl& nccl() {
     g_nccl.GetUniqueId = (decltype(g_nccl.GetUniqueId))sym("ncclGetUniqueId");
     g_nccl.CommInitRank = (decltype(g_nccl.CommInitRank))sym("ncclCommInitRank");
     g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))sym("ncclCommDestroy");
+    g_nccl.CommAbort = (decltype(g_nccl.CommAbort))sym("ncclCommAbort");
+    g_nccl.CommGetAsyncError = (decltype(g_nccl.CommGetAsyncError))sym("ncclCommGetAsyncError");
     g_nccl.GroupStart = (decltype(g_nccl.GroupStart))sym("ncclGroupStart");
     g_nccl.GroupEnd = (decltype(g_nccl.GroupEnd))sym("ncclGroupEnd");
     g_nccl.Send = (decltype(g_nccl.Send))sym("ncclSend");
@@ -310,7 +315,13 @@ struct srb_comm {
     DevBuf x_dest, x_totals, x_dst_dev, x_hs_dev;
     PinnedBuf x_dst_host, x_hs_host;
     int64_t x_launches = 0;
+    cudaEvent_t ev_in = nullptr, ev_out = nullptr; // ordering between an operator's stream and the communicator's (comm_all_gather_device)
+    std::atomic<int> aborted{0}; // srb_comm_abort: the NCCL communicator is gone, every later call fails with SRB_CANCELLED
 };
+
+static inline void comm_alive(const srb_comm* c) {
+    if (c->aborted.load(std::memory_order_acquire)) throw srb::Error(SRB_CANCELLED, "communicator aborted (srb_comm_abort)");
+}
 
 // the C ABI's error string lives in srb_capi.cu; exchange entry points report through the same convention
 namespace srb {
@@ -596,11 +607,63 @@ void srb_comm_destroy(srb_comm* c) {
     for (int d = 0; d < (int)c->peers.size(); d++)
         if (d != c->rank && c->peers[d].base) cudaIpcCloseMemHandle(c->peers[d].base);
     if (c->arena) cudaFree(c->arena);
-    if (c->comm) nccl().CommDestroy(c->comm);
+    if (c->ev_in) cudaEventDestroy(c->ev_in);
+    if (c->ev_out) cudaEventDestroy(c->ev_out);
+    if (c->comm && !c->aborted.load()) nccl().CommDestroy(c->comm);
     delete c;
 }
 
 void* srb_comm_stream(srb_comm* c) { return c ? (void*)c->stream : nullptr; }
+
+// Cancellation that reaches in-flight collectives (PipelineDriver cancels a fragment's drivers, pipeline_driver.cpp:316; the brpc exchange
+// of the reference fails its pending RPCs): ncclCommAbort makes every collective queued or running on this communicator return, on this
+// rank, so a peer that died or a cancelled query cannot leave the stream blocked. May be called from another thread than the one inside a
+// collective. Afterwards every call on the communicator fails with SRB_CANCELLED; only srb_comm_destroy is allowed.
+srb_status srb_comm_abort(srb_comm* c) {
+    X_BEGIN
+    if (!c) throw Error(SRB_INVALID_ARGUMENT, "null communicator");
+    if (c->aborted.exchange(1)) return SRB_OK;
+    if (c->comm) SRB_NCCL(nccl().CommAbort(c->comm));
+    return SRB_OK;
+    X_END
+}
+// the communicator's asynchronous error state (ncclCommGetAsyncError): SRB_OK, SRB_CANCELLED after an abort, SRB_INTERNAL_ERROR otherwise
+srb_status srb_comm_check(srb_comm* c) {
+    X_BEGIN
+    if (!c) throw Error(SRB_INVALID_ARGUMENT, "null communicator");
+    comm_alive(c);
+    int err = 0;
+    SRB_NCCL(nccl().CommGetAsyncError(c->comm, &err));
+    if (err) throw Error(SRB_INTERNAL_ERROR, fmt("NCCL asynchronous error: %s", nccl().GetErrorString(err)));
+    return SRB_OK;
+    X_END
+}
+} // extern "C" (reopened below)
+
+namespace srb {
+// Fixed-size all-gather of device bytes ordered against a caller's stream, no host synchronisation: `send` (bytes_per_rank) of every rank
+// lands in recv[rank * bytes_per_rank ...] on every rank. Work queued on `user_stream` before the call happens before the collective,
+// work queued after it sees the gathered bytes. (The gather exchange of a two-phase low-cardinality aggregation: see
+// ScanAggOp::set_finishing_merged.)
+void comm_all_gather_device(srb_comm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t user_stream) {
+    if (!c) throw Error(SRB_INVALID_ARGUMENT, "null communicator");
+    comm_alive(c);
+    if (!c->ev_in) {
+        SRB_CUDA(cudaEventCreateWithFlags(&c->ev_in, cudaEventDisableTiming));
+        SRB_CUDA(cudaEventCreateWithFlags(&c->ev_out, cudaEventDisableTiming));
+    }
+    SRB_CUDA(cudaEventRecord(c->ev_in, user_stream));
+    SRB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_in, 0));
+    SRB_NCCL(nccl().AllGather(send, recv, bytes_per_rank, ncclUint8_, c->comm, c->stream));
+    SRB_CUDA(cudaEventRecord(c->ev_out, c->stream));
+    SRB_CUDA(cudaStreamWaitEvent(user_stream, c->ev_out, 0));
+    c->x_launches++;
+}
+int comm_world(const srb_comm* c) { return c->world; }
+int comm_rank(const srb_comm* c) { return c->rank; }
+} // namespace srb
+
+extern "C" {
 
 // send: device chunk whose rows are grouped by destination rank (srb_partition_run output), send_counts[world].
 // recv: library-owned device chunk holding the rows received from rank 0, 1, ... in that order; recv_counts[world].
@@ -608,6 +671,7 @@ srb_status srb_comm_all_to_all(srb_comm* c, const srb_chunk* send, const int64_t
     X_BEGIN
     if (!c || !send || !send_counts || !recv || !recv_counts) throw Error(SRB_INVALID_ARGUMENT, "null argument");
     if (send->n_cols > PMAX_COLS) throw Error(SRB_NOT_IMPLEMENTED, "too many columns");
+    comm_alive(c);
     SRB_CUDA(cudaSetDevice(c->ctx->cfg.device));
     const int W = c->world;
     // counts: every rank learns the whole W x W matrix
@@ -679,6 +743,7 @@ srb_status srb_comm_shuffle(srb_comm* c, const srb_chunk* in, int32_t n_key_slot
     if (!c || !in || !key_slots || !recv || !recv_counts) throw Error(SRB_INVALID_ARGUMENT, "null argument");
     if (n_key_slots < 1 || n_key_slots > PMAX_KEYS) throw Error(SRB_INVALID_ARGUMENT, "bad number of partition columns");
     if (in->n_cols < 1 || in->n_cols > PMAX_COLS) throw Error(SRB_NOT_IMPLEMENTED, "too many columns");
+    comm_alive(c);
     SRB_CUDA(cudaSetDevice(c->ctx->cfg.device));
     const int W = c->world, me = c->rank;
     const int64_t n = in->n_rows;
@@ -853,6 +918,7 @@ __global__ void __launch_bounds__(256) k_rf_or(uint32_t* __restrict__ dir, const
 srb_status srb_comm_merge_runtime_filter(srb_comm* c, srb_runtime_filter* rf) {
     X_BEGIN
     if (!c || !rf) throw Error(SRB_INVALID_ARGUMENT, "null argument");
+    comm_alive(c);
     SRB_CUDA(cudaSetDevice(c->ctx->cfg.device));
     const int W = c->world;
     c->counts_dev.ensure(c->ctx, (size_t)(5 + 5 * W) * 8);
@@ -911,6 +977,7 @@ srb_status srb_comm_counters(srb_comm* c, int64_t* kernel_launches) {
 srb_status srb_comm_all_gather(srb_comm* c, const srb_chunk* mine, srb_chunk* out) {
     X_BEGIN
     if (!c || !mine || !out) throw Error(SRB_INVALID_ARGUMENT, "null argument");
+    comm_alive(c);
     SRB_CUDA(cudaSetDevice(c->ctx->cfg.device));
     const int W = c->world;
     bool all_host = mine->n_cols > 0;

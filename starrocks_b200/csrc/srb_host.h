@@ -334,6 +334,8 @@ struct srb_op {
     // runtime filters: join ops build them from their build side, scan-filter ops apply them
     virtual struct srb_runtime_filter* build_runtime_filter(int, int64_t, int) { throw srb::Error(SRB_INVALID_ARGUMENT, "not a join operator"); }
     virtual void add_runtime_filter(const struct srb_runtime_filter*, int) { throw srb::Error(SRB_NOT_IMPLEMENTED, "this operator does not take runtime filters"); }
+    // set_finishing + gather exchange + merge phase in one (aggregate operators with small tables)
+    virtual void set_finishing_merged(struct srb_comm*) { throw srb::Error(SRB_NOT_IMPLEMENTED, "this operator has no cross-rank merge"); }
     // encoded segment pages (scan operators): decoded on the device in front of the scan
     virtual void push_pages(int32_t, const int32_t*, const srb_page_column*, int64_t) { throw srb::Error(SRB_NOT_IMPLEMENTED, "this operator does not take encoded pages"); }
     // streaming pre-aggregation (aggregate operators in the update+serialize phase only)
@@ -362,4 +364,11 @@ namespace srb {
 srb_op* make_scan_agg_op(srb_ctx* ctx, const srb_scan_agg_plan* plan);
 srb_op* make_join_op(srb_ctx* ctx, const srb_join_plan* plan);
 srb_op* make_topn_op(srb_ctx* ctx, const srb_topn_plan* plan);
+} // namespace srb
+
+struct srb_comm;
+namespace srb {
+void comm_all_gather_device(srb_comm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t user_stream);
+int comm_world(const srb_comm* c);
+int comm_rank(const srb_comm* c);
 } // namespace srb

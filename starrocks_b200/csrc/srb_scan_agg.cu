@@ -247,6 +247,75 @@ __global__ void k_rehash(const __grid_constant__ DProg prog, const uint8_t* __re
     }
 }
 
+// ---- cross-rank merge of small group tables (ScanAggOp::set_finishing_merged) ---------------------------------------------------
+// wire region of a rank: [u64 slots sent][u64 flag: 1 = table too large to send][slots x slot_bytes]
+constexpr int MERGE_MAX_SLOTS = 1024;
+__global__ void k_merge_pack(const uint8_t* __restrict__ slots, uint64_t cap, int slot_bytes, uint8_t* __restrict__ wire) {
+    const bool fits = cap <= (uint64_t)MERGE_MAX_SLOTS;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        ((uint64_t*)wire)[0] = fits ? cap : 0;
+        ((uint64_t*)wire)[1] = fits ? 0 : 1;
+    }
+    if (!fits) return;
+    const uint64_t words = cap * (uint64_t)slot_bytes / 8;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (uint64_t)gridDim.x * blockDim.x)
+        ((uint64_t*)(wire + 16))[i] = ((const uint64_t*)slots)[i];
+}
+// One block. The peers' tables are folded in one after the other: inside one table every key occurs once, so its slots go to distinct
+// local slots and plain read-modify-writes are safe between the barriers. States merge as the reference's merge() does: sums and counts
+// add (sum.h:113-117, avg.h:161-166, count.h:92-96), MIN / MAX keep the larger order-preserving encoding (maxmin.h).
+__global__ void __launch_bounds__(256) k_merge_tables(const __grid_constant__ DProg prog, const TableView tv, const uint8_t* __restrict__ wire,
+                                                       const size_t region, const int world, const int me, unsigned long long* __restrict__ inserted,
+                                                       unsigned long long* __restrict__ failed) {
+    const DProg& p = prog;
+    const int sb = p.slot_bytes;
+    for (int r = 0; r < world; r++) {
+        const uint8_t* reg = wire + (size_t)r * region;
+        if (((const uint64_t*)reg)[1] != 0) {
+            if (threadIdx.x == 0) atomicAdd(failed, 1ULL);
+            continue;
+        }
+        if (r == me) continue;
+        const uint64_t cap = ((const uint64_t*)reg)[0];
+        for (uint64_t i = threadIdx.x; i < cap; i += blockDim.x) {
+            const uint8_t* s = reg + 16 + i * sb;
+            const uint64_t m = *(const uint64_t*)s;
+            if ((m & 3ULL) != SLOT_READY) continue;
+            bool fresh = false;
+            uint8_t* d = table_find_or_insert(tv, ((const uint64_t*)s)[1], p.key_words > 1 ? ((const uint64_t*)s)[2] : 0ULL, m & ~3ULL, &fresh);
+            if (!d) {
+                atomicAdd(failed, 1ULL);
+                continue;
+            }
+            if (fresh) atomicAdd(inserted, 1ULL);
+            for (int a = 0; a < p.n_aggs; a++) {
+                const DAgg& g = p.aggs[a];
+                if (g.off_n >= 0) *(uint64_t*)(d + g.off_n) += *(const uint64_t*)(s + g.off_n);
+                if (g.fn == FN_COUNT || g.off_lo < 0) continue;
+                if (g.fn == FN_MIN || g.fn == FN_MAX) {
+                    if (g.wide && !g.is_double) {
+                        const u128 x = ((u128) * (const uint64_t*)(s + g.off_lo + 8) << 64) | *(const uint64_t*)(s + g.off_lo);
+                        const u128 c = ((u128) * (const uint64_t*)(d + g.off_lo + 8) << 64) | *(const uint64_t*)(d + g.off_lo);
+                        if (x > c) {
+                            *(uint64_t*)(d + g.off_lo) = (uint64_t)x;
+                            *(uint64_t*)(d + g.off_lo + 8) = (uint64_t)(x >> 64);
+                        }
+                    } else if (*(const uint64_t*)(s + g.off_lo) > *(const uint64_t*)(d + g.off_lo)) {
+                        *(uint64_t*)(d + g.off_lo) = *(const uint64_t*)(s + g.off_lo);
+                    }
+                } else if (g.is_double || g.avg_as_double) {
+                    *(double*)(d + g.off_lo) += *(const double*)(s + g.off_lo);
+                } else {
+                    const uint64_t lo = *(const uint64_t*)(s + g.off_lo), old = *(uint64_t*)(d + g.off_lo);
+                    *(uint64_t*)(d + g.off_lo) = old + lo;
+                    if (g.off_hi >= 0) *(uint64_t*)(d + g.off_hi) += *(const uint64_t*)(s + g.off_hi) + (old + lo < old ? 1ULL : 0ULL);
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
 // ---- emit: table -> columnar result (K5), with AVG finalisation on the device --------------------------------
 struct EmitAgg {
     void* val;      // out_width bytes per row (blob: the sum part)
@@ -1312,6 +1381,46 @@ public:
         check_page_errors(true);
         produce_output();
     }
+    // set_finishing on every rank at once + the gather exchange + the merge phase, on the device (srb_op_set_finishing_merged)
+    void set_finishing_merged(srb_comm* comm) override {
+        if (!comm) throw Error(SRB_INVALID_ARGUMENT, "null communicator");
+        if (finishing) throw Error(SRB_INTERNAL_ERROR, "set_finishing_merged after set_finishing");
+        if (filter_only_ || stream_mode_ >= 0) throw Error(SRB_INVALID_ARGUMENT, "set_finishing_merged is for blocking aggregate operators");
+        if (plan_.phase != SRB_AGG_UPDATE_FINALIZE) throw Error(SRB_INVALID_ARGUMENT, "set_finishing_merged finalises: the plan's phase must be UPDATE_FINALIZE");
+        finishing = true;
+        if (cancelled) {
+            finished = true;
+            return;
+        }
+        flush_stage();
+        wait_pending();
+        if (!lowered_) lower(nullptr);
+        check_page_errors(true);
+        if (radix_rows_ > 0) radix_ingest();
+        ensure_table();
+        const DProg& P = L_.prog;
+        const int W = comm_world(comm), me = comm_rank(comm);
+        // room for the peers' groups (every rank of a low-cardinality plan holds about the same few groups; a full table fails the merge)
+        if (P.n_keys && (occupied_ + 16) * 4 > cap_ && cap_ < (uint64_t)MERGE_MAX_SLOTS) grow_table(std::min<uint64_t>((occupied_ + 16) * 4, MERGE_MAX_SLOTS));
+        const size_t region = 16 + (size_t)MERGE_MAX_SLOTS * (size_t)P.slot_bytes;
+        merge_send_.ensure(ctx, region);
+        merge_recv_.ensure(ctx, region * (size_t)W);
+        rx_ctr_.ensure(ctx, sizeof(RxCounters));
+        rx_hctr_.ensure(sizeof(RxCounters));
+        SRB_CUDA(cudaMemsetAsync(rx_ctr_.p, 0, sizeof(RxCounters), stream));
+        k_merge_pack<<<8, 256, 0, stream>>>(slots_.as<uint8_t>(), cap_, P.slot_bytes, merge_send_.as<uint8_t>());
+        comm_all_gather_device(comm, merge_send_.p, merge_recv_.p, region, stream);
+        RxCounters* dc = rx_ctr_.as<RxCounters>();
+        k_merge_tables<<<1, 256, 0, stream>>>(P, view(), merge_recv_.as<uint8_t>(), region, W, me, &dc->groups, &dc->overflow);
+        launches += 2;
+        SRB_CUDA(cudaGetLastError());
+        // emit straight away: the number of merged-in groups arrives with the emit's own counters (one host wait for both)
+        RxCounters* hc = rx_hctr_.as<RxCounters>();
+        SRB_CUDA(cudaMemcpyAsync(hc, rx_ctr_.p, sizeof(RxCounters), cudaMemcpyDeviceToHost, stream));
+        produce_output(P.n_keys ? (uint64_t)std::min<uint64_t>(cap_, occupied_ + (uint64_t)(W - 1) * MERGE_MAX_SLOTS) : 1, false);
+        if (hc->overflow) throw Error(SRB_NOT_IMPLEMENTED, "set_finishing_merged: a rank's group table is too large (or full) for the state-level gather");
+        occupied_ += hc->groups;
+    }
     bool has_output() override { return finishing && !finished && out_pos_ < out_rows_; }
     bool need_input() override { return !finishing; }
     bool is_finished() override { return finished || (finishing && out_pos_ >= out_rows_); }
@@ -2205,10 +2314,11 @@ private:
         return ea;
     }
 
-    void produce_output() {
+    void produce_output() { produce_output(L_.prog.n_keys ? occupied_ : 1, true); }
+    // max_rows: an upper bound of the table's groups (exact when `exact`: a mismatch is an internal error)
+    void produce_output(uint64_t max_rows, bool exact) {
         if (filter_only_) return; // rows already sit in fout_
         const DProg& P = L_.prog;
-        uint64_t max_rows = P.n_keys ? occupied_ : 1;
         EmitArgs ea = emit_args((uint64_t)stream_rows_ + max_rows);
         if (!table_ready_) { // every batch went through the radix path (or none arrived): the result rows are in place already
             if (P.n_keys == 0) {
@@ -2225,9 +2335,54 @@ private:
         SRB_CUDA(cudaGetLastError());
         Counters* hc = ctr_host_.as<Counters>();
         SRB_CUDA(cudaMemcpyAsync(hc, ctr_dev_.p, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+        prefetch_small_result((int64_t)stream_rows_ + (int64_t)max_rows); // a handful of rows reach the host with this same wait
         SRB_CUDA(cudaStreamSynchronize(stream));
-        if (hc->emitted != max_rows) throw Error(SRB_INTERNAL_ERROR, fmt("emit produced %llu rows, table holds %llu", (unsigned long long)hc->emitted, (unsigned long long)max_rows));
+        if (exact ? hc->emitted != max_rows : hc->emitted > max_rows) throw Error(SRB_INTERNAL_ERROR, fmt("emit produced %llu rows, table holds %llu", (unsigned long long)hc->emitted, (unsigned long long)max_rows));
         out_rows_ = stream_rows_ + (int64_t)hc->emitted; // pass-through rows first, then the table's groups
+    }
+
+    // the device arrays a result row is made of: (base pointer, bytes per row), in the order materialize() consumes them
+    struct RowPiece {
+        const uint8_t* base;
+        size_t unit;
+    };
+    std::vector<RowPiece> row_pieces() const {
+        const DProg& P = L_.prog;
+        std::vector<RowPiece> v;
+        if (P.n_keys) v.push_back({ekeys_.as<uint8_t>(), 16});
+        for (int a = 0; a < P.n_aggs; a++) {
+            const AggOutMeta& m = L_.agg_out[a];
+            v.push_back({eval_[a].val.as<uint8_t>(), (size_t)m.out_width});
+            if (m.nullable) v.push_back({eval_[a].null.as<uint8_t>(), 1});
+            if (m.blob) v.push_back({(const uint8_t*)eval_[a].cnt.as<int64_t>(), 8});
+        }
+        return v;
+    }
+    // Results of at most 64 rows (Q1's four, Q6's one) are packed and copied to the host right behind the emit kernel, so that
+    // pull_chunk finds them there: one host wait per set_finishing + pull instead of two.
+    void prefetch_small_result(int64_t rows) {
+        prefetch_rows_ = 0;
+        if (rows <= 0 || rows > 64) return;
+        const std::vector<RowPiece> rp = row_pieces();
+        if ((int)rp.size() > PackArgs::MAX) return;
+        PackArgs pa{};
+        pa.n = (int)rp.size();
+        size_t off = 0;
+        prefetch_off_.assign(rp.size(), 0);
+        for (int i = 0; i < pa.n; i++) {
+            pa.src[i] = rp[(size_t)i].base;
+            pa.bytes[i] = (uint32_t)(rp[(size_t)i].unit * (size_t)rows);
+            pa.dst_off[i] = (uint32_t)off;
+            prefetch_off_[(size_t)i] = off;
+            off += (pa.bytes[i] + 15) & ~(size_t)15;
+        }
+        if (!pa.n) return;
+        pack_dev_.ensure(ctx, off);
+        pack_host_.ensure(off);
+        k_pack_result<<<std::min(64, pa.n * 4), 256, 0, stream>>>(pa, pack_dev_.as<uint8_t>());
+        launches++;
+        SRB_CUDA(cudaMemcpyAsync(pack_host_.p, pack_dev_.p, off, cudaMemcpyDeviceToHost, stream));
+        prefetch_rows_ = rows;
     }
 
     // copies rows [pos, pos+n) of the device result into host columns
@@ -2284,7 +2439,11 @@ private:
         }
         size_t total = 0;
         for (auto& pc : pieces) total += (pc.bytes + 15) & ~(size_t)15;
-        if (total <= ((size_t)1 << 20) && (int)pieces.size() <= PackArgs::MAX) { // (<= 1 MB: the pinned buffer comes from the pool)
+        if (n > 0 && prefetch_rows_ > 0 && pos + n <= prefetch_rows_) { // already on the host (prefetch_small_result): same piece order
+            const std::vector<RowPiece> rp = row_pieces();
+            for (size_t i = 0; i < pieces.size() && i < rp.size(); i++)
+                memcpy(pieces[i].dst, pack_host_.as<uint8_t>() + prefetch_off_[i] + (size_t)pos * rp[i].unit, pieces[i].bytes);
+        } else if (total <= ((size_t)1 << 20) && (int)pieces.size() <= PackArgs::MAX) { // (<= 1 MB: the pinned buffer comes from the pool)
             // small result: one pack kernel + ONE pinned copy instead of a pageable copy per column
             PackArgs pa{};
             pa.n = (int)pieces.size();
@@ -2296,6 +2455,7 @@ private:
                 off += (pieces[i].bytes + 15) & ~(size_t)15;
             }
             if (pa.n) {
+                prefetch_rows_ = 0; // the buffers are reused
                 pack_dev_.ensure(ctx, total);
                 pack_host_.ensure(total);
                 k_pack_result<<<std::min(64, pa.n * 4), 256, 0, stream>>>(pa, pack_dev_.as<uint8_t>());
@@ -2404,7 +2564,9 @@ private:
     // (61 ms vs 26 ms for 600 M rows / 100 M keys), so it is opt-in: SRB_RADIX=1.
     bool no_radix_ = getenv("SRB_RADIX") == nullptr || getenv("SRB_NO_RADIX") != nullptr;
     int64_t radix_min_rows_ = getenv("SRB_RADIX_MIN_ROWS") ? atoll(getenv("SRB_RADIX_MIN_ROWS")) : ((int64_t)1 << 24); // (test hook: smaller batches)
-    DevBuf page_err_;
+    DevBuf page_err_, merge_send_, merge_recv_;
+    int64_t prefetch_rows_ = 0;        // result rows [0, prefetch_rows_) sit in pack_host_ (prefetch_small_result)
+    std::vector<size_t> prefetch_off_; // where each row piece starts there
     bool pages_pushed_ = false;
     bool table_ready_ = false;                                     // the group table is allocated and cleared (init_table defers large ones)
     int64_t radix_rows_ = 0, radix_batches_ = 0;                   // groups the radix path left at the front of the output arrays

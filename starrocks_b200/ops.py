@@ -21,7 +21,7 @@ _lib = None
 
 EXPORTS = [
     "srb_ctx_create", "srb_ctx_destroy", "srb_last_error", "srb_ctx_device_info", "srb_ctx_trim", "srb_op_stream",
-    "srb_scan_agg_create", "srb_join_create", "srb_op_push_chunk", "srb_op_push_pages", "srb_op_set_finishing", "srb_op_has_output",
+    "srb_scan_agg_create", "srb_join_create", "srb_op_push_chunk", "srb_op_push_pages", "srb_op_set_finishing_merged", "srb_op_set_finishing", "srb_op_has_output",
     "srb_op_need_input", "srb_op_is_finished", "srb_op_pull_chunk", "srb_op_pull_all", "srb_op_pull_device",
     "srb_op_cancel", "srb_op_close", "srb_op_sync", "srb_op_counters", "srb_op_profile",
     "srb_join_probe_push_chunk", "srb_join_probe_set_finishing", "srb_join_probe_has_output",
@@ -29,7 +29,7 @@ EXPORTS = [
     "srb_join_probe_pull_all", "srb_join_probe_pull_device",
     "srb_device_alloc", "srb_device_free", "srb_pinned_alloc", "srb_pinned_free", "srb_memcpy_h2d", "srb_memcpy_d2h",
     "srb_partition_create", "srb_partition_run", "srb_partition_destroy", "srb_partition_run_noalloc",
-    "srb_comm_unique_id", "srb_comm_create", "srb_comm_destroy", "srb_comm_stream", "srb_comm_all_to_all", "srb_comm_all_gather", "srb_comm_shuffle", "srb_comm_counters", "srb_comm_merge_runtime_filter",
+    "srb_comm_unique_id", "srb_comm_create", "srb_comm_destroy", "srb_comm_abort", "srb_comm_check", "srb_comm_stream", "srb_comm_all_to_all", "srb_comm_all_gather", "srb_comm_shuffle", "srb_comm_counters", "srb_comm_merge_runtime_filter",
     "srb_join_build_runtime_filter", "srb_op_add_runtime_filter", "srb_op_set_streaming_mode", "srb_op_streaming_stats", "srb_topn_create", "srb_runtime_filter_info", "srb_runtime_filter_directory", "srb_runtime_filter_destroy",
 ]
 
@@ -62,6 +62,7 @@ def lib() -> C.CDLL:
     L.srb_topn_create.argtypes = [vp, C.POINTER(K.srb_topn_plan), C.POINTER(vp)]
     for f in ("srb_op_push_chunk", "srb_join_probe_push_chunk"):
         getattr(L, f).argtypes = [vp, C.POINTER(K.srb_chunk)]
+    L.srb_op_set_finishing_merged.argtypes = [vp, vp]
     from . import pages as PG
     L.srb_op_push_pages.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(PG.srb_page_column), i64]
     for f in ("srb_op_set_finishing", "srb_join_probe_set_finishing", "srb_op_cancel", "srb_op_sync", "srb_op_has_output",
@@ -92,6 +93,8 @@ def lib() -> C.CDLL:
     L.srb_comm_create.argtypes = [vp, vp, C.POINTER(vp)]
     L.srb_comm_destroy.argtypes = [vp]
     L.srb_comm_destroy.restype = None
+    L.srb_comm_abort.argtypes = [vp]
+    L.srb_comm_check.argtypes = [vp]
     L.srb_comm_stream.argtypes = [vp]
     L.srb_comm_stream.restype = vp
     L.srb_comm_all_to_all.argtypes = [vp, C.POINTER(K.srb_chunk), C.POINTER(i64), C.POINTER(K.srb_chunk), C.POINTER(i64)]
@@ -278,6 +281,11 @@ class ScanAggOperator(_Operator):
         _check(ctx.L.srb_scan_agg_create(ctx.h, C.byref(plan.c), C.byref(h)))
         super().__init__(ctx, h)
         self._plan = plan
+
+    def set_finishing_merged(self, comm: "Communicator"):
+        """collective over the communicator's ranks: set_finishing + gather of the ranks' aggregate states on the device + merge; every
+        rank then pulls the global result (srb_op_set_finishing_merged)"""
+        _check(self.L.srb_op_set_finishing_merged(self.h, comm.h))
 
     def push_pages_prepared(self, prepared):
         """prepared = pages.prepare(columns): the C structures built once (a hot loop pushes the same page sets again and again)"""
@@ -498,6 +506,14 @@ class Communicator:
         out = K.srb_chunk()
         _check(self.L.srb_comm_shuffle(self.h, C.byref(cch), len(key_slots), ks, C.byref(out), rc))
         return _raw_chunk(out), list(rc)
+
+    def abort(self):
+        """ncclCommAbort: in-flight and later collectives on this rank return; every later call fails with CANCELLED"""
+        _check(self.L.srb_comm_abort(self.h))
+
+    def check(self):
+        """raises when the communicator was aborted or NCCL reports an asynchronous error"""
+        _check(self.L.srb_comm_check(self.h))
 
     def launches(self) -> int:
         n = C.c_int64()

@@ -28,6 +28,19 @@ def _filter(ctx, plan, chunk):
     return op, op.pull_device()
 
 
+def having(ctx, agg_op, preds, out_slots):
+    """HAVING: the conjuncts AggregateBlockingSourceOperator::pull_chunk applies to the chunks it emits (eval_conjuncts_and_in_filters,
+    be/src/exec/pipeline/aggregate/aggregate_blocking_source_operator.cpp:62-68) = a filter operator over the aggregate's device result,
+    no host hop in between. `preds` name the result's slots (group keys 0..k-1, then the aggregates). -> the filter operator after
+    set_finishing (pull from it; close it and the aggregate afterwards)."""
+    f = ops.ScanAggOperator(ctx, Q.filter_plan(preds, out_slots))
+    groups = agg_op.pull_device()
+    if groups is not None and groups.n_rows:
+        f.push_chunk(groups)
+    f.set_finishing()
+    return f
+
+
 class TpchQ3:
     """One pass of Q3 over this rank's row ranges of customer / orders / lineitem. `comm` (ops.Communicator) and `part`
     (ops.Partitioner over world_size destinations) switch on the multi-GPU plan; without them everything is local."""

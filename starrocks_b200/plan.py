@@ -75,6 +75,15 @@ def pred(slot_id: int, op: int, type_: int, literal=0, or_group: int = 0) -> K.s
     return p
 
 
+def pred_in(slot_id: int, type_: int, values, or_group: int, negate: bool = False):
+    """`col IN (v1, ..., vk)` / `col NOT IN (...)` as the predicates the plan takes (ColumnInPredicate / ColumnNotInPredicate,
+    be/src/storage/column_predicate.h:249-277, column_in_predicate.cpp): IN = the OR of k EQ predicates (one or_group), NOT IN = k NE
+    conjuncts. A NULL row satisfies neither, as in the reference (a NULL never passes a comparison). At most 16 predicates per plan."""
+    if negate:
+        return [pred(slot_id, K.PRED_NE, type_, v) for v in values]
+    return [pred(slot_id, K.PRED_EQ, type_, v, or_group=or_group) for v in values]
+
+
 class ScanAggPlan:
     """Owns the ctypes arrays behind one srb_scan_agg_plan."""
 

@@ -55,6 +55,63 @@ def test_partitioner_routes_rows_like_the_shuffle_hash(ctx, oracle, world):
             ctx.device_free(p)
 
 
+def test_set_finishing_merged_on_a_single_rank_communicator(ctx, oracle):
+    """the one-call two-phase aggregation with world size 1: the gather returns the rank's own table, nothing is merged in, the result is
+    the local result (MIN / MAX / AVG / DOUBLE states included)"""
+    from starrocks_b200 import ops
+    from starrocks_b200.plan import ExprBuilder, ScanAggPlan
+    box = {}
+    comm = ops.Communicator(ctx, lambda b: box.__setitem__("id", b), lambda: box["id"])
+    try:
+        ch = T.host_chunk("lineitem", 3, 300_000, T.LINEITEM_Q1)
+        for plan in (Q.q1_plan(), Q.q6_plan()):
+            op = ops.ScanAggOperator(ctx, plan)
+            op.push_chunk(ch)
+            op.set_finishing_merged(comm)
+            assert K.chunk_rows(op.pull_all()) == K.chunk_rows(oracle.scan_agg(plan, ch))
+            op.close()
+        e = ExprBuilder()
+        k = e.slot(Q.L_RETURNFLAG_CODE, K.TYPE_INT)
+        qty = e.slot(Q.L_QUANTITY, K.TYPE_DECIMAL64, 15, 2)
+        plan = ScanAggPlan(exprs=e, keys=[k], aggs=[(K.AGG_MIN, qty), (K.AGG_MAX, qty), (K.AGG_AVG, qty), (K.AGG_COUNT, None)], group_hint=8)
+        op = ops.ScanAggOperator(ctx, plan)
+        op.push_chunk(ch)
+        op.set_finishing_merged(comm)
+        assert K.chunk_rows(op.pull_all()) == K.chunk_rows(oracle.scan_agg(plan, ch))
+        op.close()
+        with pytest.raises(ops.SrbError):  # a serialize-phase plan does not finalise
+            op = ops.ScanAggOperator(ctx, Q.q1_plan(phase=K.AGG_UPDATE_SERIALIZE))
+            try:
+                op.push_chunk(ch)
+                op.set_finishing_merged(comm)
+            finally:
+                op.close()
+    finally:
+        comm.close()
+
+
+def test_comm_abort_cancels_the_communicator(ctx):
+    """srb_comm_abort (ncclCommAbort): afterwards every collective on the communicator fails with CANCELLED instead of blocking"""
+    from starrocks_b200 import ops
+    box = {}
+    comm = ops.Communicator(ctx, lambda b: box.__setitem__("id", b), lambda: box["id"])
+    ch = T.host_chunk("highcard", 0, 1000, ["k", "v"], n_keys=10)
+    dch, ptrs = ctx.device_chunk(ch)
+    try:
+        comm.check()
+        assert comm.all_gather(dch).n_rows == 1000
+        comm.abort()
+        comm.abort()  # idempotent
+        for call in (lambda: comm.all_gather(dch), lambda: comm.shuffle(dch, [Q.HC_K]), lambda: comm.all_to_all(dch, [1000]), comm.check):
+            with pytest.raises(ops.SrbError) as ei:
+                call()
+            assert ei.value.code == K.CANCELLED
+    finally:
+        comm.close()
+        for p in ptrs:
+            ctx.device_free(p)
+
+
 def test_single_rank_communicator_round_trip(ctx):
     from starrocks_b200 import ops
     box = {}
@@ -203,7 +260,19 @@ def _worker(rank, world, port, n_rows, n_keys, out_q):
         op4.push_chunk(everyone)
         op4.set_finishing()
         q1_rows = K.chunk_rows(op4.pull_all())
-        out_q.put((rank, (rows, q1_rows)))
+        # the same two-phase plan as ONE call: the ranks' group tables are gathered and merged on the device (srb_op_set_finishing_merged);
+        # a rank without rows takes part with an empty table, and a no-GROUP-BY plan merges its single state block
+        merged = []
+        for plan, cols in ((Q.q1_plan(), T.LINEITEM_Q1), (Q.q6_plan(), T.LINEITEM_Q6)):
+            piece = T.host_chunk("lineitem", lb, le - lb, cols)
+            if rank == 1 and cols is T.LINEITEM_Q1:
+                piece = ops.slice_chunk(piece, 0, 0)
+            op5 = ops.ScanAggOperator(ctx, plan)
+            op5.push_chunk(piece)
+            op5.set_finishing_merged(comm)
+            merged.append(K.chunk_rows(op5.pull_all()))
+            op5.close()
+        out_q.put((rank, (rows, q1_rows, merged)))
         for o in (op1, op2, op3, op4):
             o.close()
         part.close()
@@ -240,6 +309,9 @@ def test_two_gpu_highcard_two_phase(oracle):
     b0, e0 = D.shard_range(n, 0, world)
     want_q1 = K.chunk_rows(oracle.scan_agg(Q.q1_plan(), T.host_chunk("lineitem", b0, e0 - b0, T.LINEITEM_Q1)))
     assert res[0][1] == want_q1 and res[1][1] == want_q1
+    want_q6 = K.chunk_rows(oracle.scan_agg(Q.q6_plan(), T.host_chunk("lineitem", 0, n, T.LINEITEM_Q6)))
+    for r in range(world):
+        assert res[r][2][0] == want_q1 and res[r][2][1] == want_q6
 
 
 def _join_worker(rank, world, port, sizes, out_q):

@@ -12,7 +12,7 @@ from starrocks_b200 import capi as K
 from tests import oracle_chains as OC
 from starrocks_b200 import queries as Q
 from starrocks_b200 import tpch_synth as T
-from starrocks_b200.plan import ExprBuilder, JoinPlan, ScanAggPlan, pred
+from starrocks_b200.plan import ExprBuilder, JoinPlan, ScanAggPlan, pred, pred_in
 
 pytestmark = pytest.mark.gpu
 
@@ -226,6 +226,53 @@ def test_predicate_conjunction_and_or_groups(ctx, oracle):
     plan = ScanAggPlan(preds=preds, exprs=e, aggs=[(K.AGG_SUM, arg), (K.AGG_COUNT, None), (K.AGG_MIN, arg), (K.AGG_MAX, arg)])
     check(ctx, oracle, plan, ch)
     check(ctx, oracle, plan, ch, device=True)
+
+
+def test_in_list_and_not_in_predicates(ctx, oracle):
+    # ColumnInPredicate / ColumnNotInPredicate (storage/column_predicate.h:249-277): IN = OR of EQ, NOT IN = AND of NE; NULL rows never pass
+    rng = np.random.default_rng(14)
+    n = 200_003
+    ch = K.Chunk(n, {0: _rand_col(rng, K.TYPE_INT, n, 0.1, small=True), 1: _rand_col(rng, K.TYPE_BIGINT, n, 0.0, small=True),
+                     2: _rand_col(rng, K.TYPE_DECIMAL128, n, 0.05, small=True, p=27, s=2)})
+    for preds in (pred_in(0, K.TYPE_INT, [3, -7, 11, 49], or_group=1),
+                  pred_in(0, K.TYPE_INT, [3, -7, 11], or_group=1) + pred_in(1, K.TYPE_BIGINT, [0, 1, 2, 3, 4], or_group=2),
+                  pred_in(1, K.TYPE_BIGINT, [5, 6, 7, -1], 0, negate=True) + [pred(0, K.PRED_GT, K.TYPE_INT, -10)],
+                  pred_in(2, K.TYPE_DECIMAL128, [1, 2, 3, -40], or_group=3)):
+        check(ctx, oracle, ScanAggPlan(preds=preds, out_slots=[0, 1, 2]), ch, sort=False)
+        check(ctx, oracle, ScanAggPlan(preds=preds, out_slots=[0, 1, 2]), ch, sort=False, device=True)
+        e = ExprBuilder()
+        plan = ScanAggPlan(preds=preds, exprs=e, keys=[e.slot(0, K.TYPE_INT)], aggs=[(K.AGG_SUM, e.slot(1, K.TYPE_BIGINT)), (K.AGG_COUNT, None)])
+        check(ctx, oracle, plan, ch, device=True)
+
+
+def test_having_is_a_filter_over_the_aggregate_result_on_the_device(ctx, oracle):
+    # aggregate_blocking_source_operator.cpp:62-68: HAVING conjuncts run over the emitted groups
+    from starrocks_b200 import ops, pipelines as P
+    rng = np.random.default_rng(15)
+    n = 300_000
+    ch = K.Chunk(n, {0: K.Column.from_ints(K.TYPE_INT, rng.integers(0, 5000, n).astype(np.int32)),
+                     1: K.Column.from_ints(K.TYPE_DECIMAL64, rng.integers(-1000, 100000, n), (rng.random(n) < 0.01).astype(np.uint8), 15, 2)})
+    e = ExprBuilder()
+    plan = ScanAggPlan(exprs=e, keys=[e.slot(0, K.TYPE_INT)], aggs=[(K.AGG_SUM, e.slot(1, K.TYPE_DECIMAL64, 15, 2)), (K.AGG_COUNT, None)], group_hint=5000)
+    groups = oracle.scan_agg(plan, ch)
+    # HAVING sum(v) > 3,100,000 (DECIMAL128 scaled) AND count(*) <> 60
+    hv = [pred(1, K.PRED_GT, K.TYPE_DECIMAL128, 3_100_000), pred(2, K.PRED_NE, K.TYPE_BIGINT, 60)]
+    want = K.chunk_rows(oracle.scan_agg(ScanAggPlan(preds=hv, out_slots=[0, 1, 2]), groups))
+    assert 0 < len(want) < groups.n_rows
+    dch, ptrs = ctx.device_chunk(ch)
+    agg = ops.ScanAggOperator(ctx, plan)
+    try:
+        agg.push_chunk(dch)
+        agg.set_finishing()
+        f = P.having(ctx, agg, hv, [0, 1, 2])
+        try:
+            assert K.chunk_rows(f.pull_all()) == want
+        finally:
+            f.close()
+    finally:
+        agg.close()
+        for p in ptrs:
+            ctx.device_free(p)
 
 
 def test_filter_only_compaction_preserves_order(ctx, oracle):
