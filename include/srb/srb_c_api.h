@@ -182,6 +182,17 @@ typedef struct srb_scan_agg_plan {
 #define SRB_JOIN_LEFT_SEMI 2 /* TJoinOp::LEFT_SEMI_JOIN (gensrc/thrift/PlanNodes.thrift:696-715: values count from 0) */
 #define SRB_JOIN_LEFT_ANTI 8 /* TJoinOp::LEFT_ANTI_JOIN: probe rows without a match, NULL probe keys included (join_hash_map.tpp:1349-1420);
                                 probe columns only */
+/* Outer joins and the right-side existence joins (join_hash_map.tpp:1187-1986; dispatch :851-870). "left" = the probe side, "right" = the
+ * build side, as in the reference. Columns of the side that may be missing come back nullable. RIGHT OUTER / FULL OUTER / RIGHT SEMI /
+ * RIGHT ANTI remember which build rows matched across all probe chunks and emit the build-side remainder after
+ * srb_join_probe_set_finishing (the probe side then has output once more; push an empty probe chunk first if no probe chunk ever
+ * arrived, so that the probe columns' types are known). NULL keys never match: such probe rows are "unmatched" for LEFT / FULL OUTER,
+ * such build rows for RIGHT / FULL OUTER and RIGHT ANTI. emit_indexes is ignored for these types. */
+#define SRB_JOIN_LEFT_OUTER 1  /* every probe row; build columns NULL where nothing matched */
+#define SRB_JOIN_RIGHT_OUTER 3 /* matches, then every build row that never matched with NULL probe columns */
+#define SRB_JOIN_FULL_OUTER 4  /* both */
+#define SRB_JOIN_RIGHT_SEMI 7  /* build rows with at least one match, build columns only */
+#define SRB_JOIN_RIGHT_ANTI 9  /* build rows without a match, build columns only */
 
 typedef struct srb_join_plan {
     int32_t join_type;

@@ -6,6 +6,9 @@
 //   JoinHashMap::_do_probe_from_ht (inner-join chain walk)            be/src/exec/join_hash_map.tpp:1066-1143
 //   serialize_fixed_size_key_column (multi-column fixed keys)         be/src/exec/join_hash_map.h:391-406
 //   _probe_output / _build_output (append_selective by index)         be/src/exec/join_hash_map.tpp:534-550,624-640
+//   outer / right-side joins: _probe_from_ht_for_left_outer_join, _for_right_outer_join, _for_full_outer_join, _for_right_semi_join,
+//   _for_right_anti_join + _search_ht_remain (unmatched build rows, null-key rows included)   be/src/exec/join_hash_map.tpp:1187-1986;
+//   a missing side's columns are NULL (append_default on nullable output columns, tpp:656-752)
 #include <stdexcept>
 #include <thread>
 
@@ -92,11 +95,30 @@ static void build_table(JoinTable& t) {
     }
 }
 
-static void copy_rows(const srb_column& s, const std::vector<uint32_t>& rows, OutCol& o, int n_threads = 1) {
+constexpr uint32_t NO_ROW = 0xFFFFFFFFu; // an output row whose side is missing: the column is NULL there
+
+static void copy_rows(const srb_column& s, const std::vector<uint32_t>& rows, OutCol& o, int n_threads = 1, bool side_may_miss = false) {
     o.type = s.type;
     o.precision = s.precision;
     o.scale = s.scale;
-    o.has_nulls = s.nulls != nullptr;
+    o.has_nulls = s.nulls != nullptr || side_may_miss;
+    if (side_may_miss) { // (outer joins: row by row, fixed-width and binary alike)
+        for (uint32_t row : rows) {
+            const bool miss = row == NO_ROW;
+            o.nulls.push_back(miss ? 1 : (s.nulls ? s.nulls[row] : 0));
+            if (is_binary(s.type)) {
+                if (miss) o.push_bytes("", 0);
+                else o.push_bytes((const char*)s.data + s.offsets[row], s.offsets[row + 1] - s.offsets[row]);
+            } else {
+                const int w = type_width(s.type);
+                const size_t off = o.data.size();
+                o.data.resize(off + w, 0);
+                if (!miss) memcpy(o.data.data() + off, (const uint8_t*)s.data + (size_t)w * row, w);
+            }
+        }
+        if (is_binary(s.type) && o.offsets.empty()) o.offsets.push_back(0);
+        return;
+    }
     if (!is_binary(s.type) && n_threads > 1) {
         const int w = type_width(s.type);
         o.data.resize(rows.size() * (size_t)w);
@@ -124,9 +146,30 @@ static void copy_rows(const srb_column& s, const std::vector<uint32_t>& rows, Ou
 }
 
 static void probe_range(const srb_join_plan* plan, const JoinTable& t, const PackedKeys& pk, int64_t i0, int64_t i1, std::vector<uint32_t>& probe_index,
-                        std::vector<uint32_t>& build_index) {
+                        std::vector<uint32_t>& build_index, std::vector<uint8_t>* matched) {
     const bool anti = plan->join_type == SRB_JOIN_LEFT_ANTI;
+    const bool keep_left = plan->join_type == SRB_JOIN_LEFT_OUTER || plan->join_type == SRB_JOIN_FULL_OUTER; // unmatched probe rows stay, build index 0
+    const bool right_only = plan->join_type == SRB_JOIN_RIGHT_SEMI || plan->join_type == SRB_JOIN_RIGHT_ANTI; // pairs are not emitted
     for (int64_t i = i0; i < i1; i++) {
+        if (keep_left || matched) {
+            bool any = false;
+            if (!pk.null[i]) {
+                for (uint32_t bi = t.first[bucket_of(pk, pk.k[i], t.bucket_size, t.log_bucket)]; bi != 0; bi = t.next[bi]) {
+                    if (t.keys.k[bi - 1] != pk.k[i]) continue;
+                    any = true;
+                    if (matched) (*matched)[bi] = 1;
+                    if (!right_only) {
+                        probe_index.push_back((uint32_t)i);
+                        build_index.push_back(bi);
+                    }
+                }
+            }
+            if (!any && keep_left) {
+                probe_index.push_back((uint32_t)i);
+                build_index.push_back(0);
+            }
+            continue;
+        }
         if (pk.null[i]) {
             // lookup_init leaves next[i] = 0 for NULL probe keys: no match. LEFT ANTI emits such rows (join_hash_map.tpp:1380-1420,
             // "NULLs are not matches and therefore always returned", PlanNodes.thrift:710-713); every other type drops them
@@ -173,10 +216,21 @@ Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_ch
     if (pk.width != t.keys.width) throw std::runtime_error("join: key width mismatch");
     std::vector<uint32_t> probe_index, build_index; // build_index is 1-based like the reference's
     const bool anti = plan->join_type == SRB_JOIN_LEFT_ANTI;
+    const int jt = plan->join_type;
+    const bool track_right = jt == SRB_JOIN_RIGHT_OUTER || jt == SRB_JOIN_FULL_OUTER || jt == SRB_JOIN_RIGHT_SEMI || jt == SRB_JOIN_RIGHT_ANTI;
+    const bool left_may_miss = jt == SRB_JOIN_RIGHT_OUTER || jt == SRB_JOIN_FULL_OUTER;
+    const bool right_may_miss = jt == SRB_JOIN_LEFT_OUTER || jt == SRB_JOIN_FULL_OUTER;
+    std::vector<uint8_t> matched; // per build row (1-based), HashTableProbeState::build_match_index
     {
         const int T = std::max(1, n_threads);
         std::vector<std::vector<uint32_t>> pi(T), bi(T);
-        parallel_ranges(probe->n_rows, T, [&](int th, int64_t a, int64_t b) { probe_range(plan, t, pk, a, b, pi[th], bi[th]); });
+        std::vector<std::vector<uint8_t>> mt(track_right ? T : 0, std::vector<uint8_t>((size_t)t.row_count + 1, 0));
+        parallel_ranges(probe->n_rows, T, [&](int th, int64_t a, int64_t b) { probe_range(plan, t, pk, a, b, pi[th], bi[th], track_right ? &mt[th] : nullptr); });
+        if (track_right) {
+            matched.assign((size_t)t.row_count + 1, 0);
+            for (auto& m : mt)
+                for (size_t i = 0; i < m.size(); i++) matched[i] |= m[i];
+        }
         size_t total = 0;
         for (int th = 0; th < T; th++) total += pi[th].size();
         probe_index.reserve(total);
@@ -186,23 +240,35 @@ Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_ch
             build_index.insert(build_index.end(), bi[th].begin(), bi[th].end());
         }
     }
+    // _search_ht_remain: the build rows that never matched (RIGHT / FULL OUTER, RIGHT ANTI) or did (RIGHT SEMI), in build order; rows with
+    // NULL keys were never inserted and therefore never match
+    if (track_right) {
+        const bool want = jt == SRB_JOIN_RIGHT_SEMI;
+        for (uint32_t b = 1; b <= t.row_count; b++)
+            if ((matched[b] != 0) == want) {
+                probe_index.push_back(NO_ROW);
+                build_index.push_back(b);
+            }
+    }
     r->rows_in = probe->n_rows;
     r->rows_selected = (int64_t)probe_index.size();
     r->n_rows = (int64_t)probe_index.size();
     std::vector<uint32_t> build_rows(build_index.size());
-    for (size_t i = 0; i < build_index.size(); i++) build_rows[i] = build_index[i] - 1;
-    for (int i = 0; i < plan->n_probe_out; i++) {
-        r->cols.emplace_back();
-        r->slot_ids.push_back(plan->probe_out_slots[i]);
-        copy_rows(*find_slot(*probe, plan->probe_out_slots[i]), probe_index, r->cols.back(), n_threads);
-    }
+    for (size_t i = 0; i < build_index.size(); i++) build_rows[i] = build_index[i] == 0 ? NO_ROW : build_index[i] - 1;
+    const bool right_only = jt == SRB_JOIN_RIGHT_SEMI || jt == SRB_JOIN_RIGHT_ANTI;
+    if (!right_only)
+        for (int i = 0; i < plan->n_probe_out; i++) {
+            r->cols.emplace_back();
+            r->slot_ids.push_back(plan->probe_out_slots[i]);
+            copy_rows(*find_slot(*probe, plan->probe_out_slots[i]), probe_index, r->cols.back(), n_threads, left_may_miss);
+        }
     if (plan->join_type != SRB_JOIN_LEFT_SEMI && !anti)
         for (int i = 0; i < plan->n_build_out; i++) {
             r->cols.emplace_back();
             r->slot_ids.push_back(plan->build_out_slots[i]);
-            copy_rows(*find_slot(*build, plan->build_out_slots[i]), build_rows, r->cols.back(), n_threads);
+            copy_rows(*find_slot(*build, plan->build_out_slots[i]), build_rows, r->cols.back(), n_threads, right_may_miss);
         }
-    if (plan->emit_indexes && !anti) {
+    if (plan->emit_indexes && !anti && !track_right && !right_may_miss) {
         for (int which = 0; which < 2; which++) {
             r->cols.emplace_back();
             OutCol& c = r->cols.back();

@@ -106,11 +106,32 @@ struct srb_ctx {
         pool_bytes -= (int64_t)rounded;
         return p;
     }
+    // The buffers an operator returns at close are the ones the next, identical operator asks for: when the pool is full, older
+    // entries of OTHER sizes make room (freed here) before the newcomer is turned away. Refusing the newcomer instead made every
+    // step of a steady loop pay cudaFree + cudaMalloc of gigabytes once the pool had filled with stale sizes.
     bool pool_give(size_t rounded, void* p) {
-        std::lock_guard<std::mutex> g(pool_mu);
-        if (pool_bytes + (int64_t)rounded > ((int64_t)48 << 30)) return false;
-        pool.emplace(rounded, p);
-        pool_bytes += (int64_t)rounded;
+        std::vector<void*> evict;
+        {
+            std::lock_guard<std::mutex> g(pool_mu);
+            const int64_t limit = std::max<int64_t>((int64_t)48 << 30, hbm_bytes / 2);
+            if ((int64_t)rounded > limit) return false;
+            for (auto it = pool.begin(); it != pool.end() && pool_bytes + (int64_t)rounded > limit;) {
+                if (it->first == rounded) {
+                    ++it;
+                    continue;
+                }
+                evict.push_back(it->second);
+                pool_bytes -= (int64_t)it->first;
+                it = pool.erase(it);
+            }
+            if (pool_bytes + (int64_t)rounded > limit) {
+                for (void* q : evict) cudaFree(q);
+                return false;
+            }
+            pool.emplace(rounded, p);
+            pool_bytes += (int64_t)rounded;
+        }
+        for (void* q : evict) cudaFree(q);
         return true;
     }
     void pool_clear() {

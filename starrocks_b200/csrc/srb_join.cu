@@ -100,10 +100,14 @@ __global__ void __launch_bounds__(256) k_join_build(JTable t) {
 }
 
 // K7: mode 0 counts matches (block-reduced into *total); mode 1 appends (probe_index, build_index) pairs
+// Outer / right-side joins (join_hash_map.tpp:1187-1986): keep_left = a probe row without a match still yields one output row with build
+// index 0 (LEFT / FULL OUTER); matched = one byte per build row (1-based) set when the row matches (RIGHT / FULL OUTER, RIGHT SEMI / ANTI:
+// HashTableProbeState::build_match_index); pairs = 0: only the flags are wanted (RIGHT SEMI / ANTI), nothing is counted or appended.
 template <int MODE>
 __global__ void __launch_bounds__(256) k_join_probe(JTable t, const uint8_t* __restrict__ pkeys, const uint8_t* __restrict__ pnull, int64_t n,
                                                      int semi, unsigned long long* __restrict__ total, uint32_t* __restrict__ out_probe,
-                                                     uint32_t* __restrict__ out_build) {
+                                                     uint32_t* __restrict__ out_build, int keep_left = 0, uint8_t* __restrict__ matched = nullptr,
+                                                     int pairs = 1) {
     unsigned long long mine = 0;
     const int lane = threadIdx.x & 31;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -122,13 +126,16 @@ __global__ void __launch_bounds__(256) k_join_probe(JTable t, const uint8_t* __r
                 jload(t.keys, t.width, bi - 1, &blo, &bhi);
                 if (blo == lo && bhi == hi) {
                     cnt++;
+                    if (matched) matched[bi] = 1;
                     if (semi) break;
                 }
                 bi = t.next[bi];
             }
-            mine += cnt;
+            if (keep_left && r < n && cnt == 0) cnt = 1;
+            mine += pairs ? cnt : 0;
         } else {
             // walk the chain; every match takes a ticket from a warp-aggregated atomic
+            bool ever = false;
             for (;;) {
                 bool hit = false;
                 while (bi) {
@@ -151,6 +158,22 @@ __global__ void __launch_bounds__(256) k_join_probe(JTable t, const uint8_t* __r
                     out_probe[pos] = (uint32_t)r;
                     out_build[pos] = bi; // 1-based, as the reference's build_index
                     bi = semi ? 0 : t.next[bi];
+                    ever = true;
+                }
+            }
+            if (keep_left) { // the probe rows nothing matched: one output row each, build index 0 = "no build row"
+                const bool lone = r < n && !ever;
+                const unsigned m = __ballot_sync(0xffffffffu, lone);
+                if (m) {
+                    unsigned long long base = 0;
+                    const int leader = __ffs(m) - 1;
+                    if (lane == leader) base = atomicAdd(total, (unsigned long long)__popc(m));
+                    base = __shfl_sync(0xffffffffu, base, leader);
+                    if (lone) {
+                        const unsigned long long pos = base + __popc(m & ((1u << lane) - 1));
+                        out_probe[pos] = (uint32_t)r;
+                        out_build[pos] = 0;
+                    }
                 }
             }
         }
@@ -178,10 +201,22 @@ struct GatherArgs {
 __global__ void __launch_bounds__(256) k_join_gather(const __grid_constant__ GatherArgs g, int64_t n, const uint32_t* __restrict__ probe_idx,
                                                       const uint32_t* __restrict__ build_idx) {
     for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
-        const uint32_t pi = probe_idx[j], bi = build_idx[j] - 1;
+        // probe_idx == nullptr / build index 0: that side is missing in this output row (outer joins): its columns are NULL
+        const uint32_t pi = probe_idx ? probe_idx[j] : 0xFFFFFFFFu, bi = build_idx[j] - 1;
         for (int c = 0; c < g.n_cols; c++) {
             const GatherCol& gc = g.cols[c];
             const size_t s = gc.from_build ? bi : pi;
+            if (s == 0xFFFFFFFFu) {
+                switch (gc.width) {
+                case 1: gc.dst[j] = 0; break;
+                case 2: ((uint16_t*)gc.dst)[j] = 0; break;
+                case 4: ((uint32_t*)gc.dst)[j] = 0; break;
+                case 8: ((uint64_t*)gc.dst)[j] = 0; break;
+                default: ((ulonglong2*)gc.dst)[j] = make_ulonglong2(0, 0);
+                }
+                if (gc.dst_null) gc.dst_null[j] = 1;
+                continue;
+            }
             switch (gc.width) {
             case 1: gc.dst[j] = gc.src[s]; break;
             case 2: ((uint16_t*)gc.dst)[j] = ((const uint16_t*)gc.src)[s]; break;
@@ -189,8 +224,25 @@ __global__ void __launch_bounds__(256) k_join_gather(const __grid_constant__ Gat
             case 8: ((uint64_t*)gc.dst)[j] = ((const uint64_t*)gc.src)[s]; break;
             default: ((ulonglong2*)gc.dst)[j] = ((const ulonglong2*)gc.src)[s];
             }
-            if (gc.src_null) gc.dst_null[j] = gc.src_null[s];
+            if (gc.dst_null) gc.dst_null[j] = gc.src_null ? gc.src_null[s] : 0;
         }
+    }
+}
+
+// the build rows (1-based) whose matched flag equals `want`, in any order (_search_ht_remain, join_hash_map.tpp)
+__global__ void __launch_bounds__(256) k_join_remainder(const uint8_t* __restrict__ matched, uint32_t rows, int want, unsigned long long* __restrict__ total,
+                                                         uint32_t* __restrict__ out_build) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t rounds = (rows + 31) & ~31u;
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < rounds; j += gridDim.x * blockDim.x) {
+        const bool take = j < rows && (matched[j + 1] != 0) == (want != 0);
+        const unsigned m = __ballot_sync(0xffffffffu, take);
+        if (!m) continue;
+        unsigned long long base = 0;
+        const int leader = __ffs(m) - 1;
+        if (lane == leader) base = atomicAdd(total, (unsigned long long)__popc(m));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (take && out_build) out_build[base + __popc(m & ((1u << lane) - 1))] = j + 1;
     }
 }
 
@@ -496,8 +548,14 @@ class JoinOp : public srb_op {
 public:
     JoinOp(srb_ctx* c, const srb_join_plan* p) : srb_op(c) {
         if (!p) throw Error(SRB_INVALID_ARGUMENT, "null plan");
-        if (p->join_type != SRB_JOIN_INNER && p->join_type != SRB_JOIN_LEFT_SEMI && p->join_type != SRB_JOIN_LEFT_ANTI)
+        const int jt = p->join_type;
+        if (jt != SRB_JOIN_INNER && jt != SRB_JOIN_LEFT_SEMI && jt != SRB_JOIN_LEFT_ANTI && jt != SRB_JOIN_LEFT_OUTER && jt != SRB_JOIN_RIGHT_OUTER &&
+            jt != SRB_JOIN_FULL_OUTER && jt != SRB_JOIN_RIGHT_SEMI && jt != SRB_JOIN_RIGHT_ANTI)
             throw Error(SRB_NOT_IMPLEMENTED, fmt("join type %d", p->join_type));
+        keep_left_ = jt == SRB_JOIN_LEFT_OUTER || jt == SRB_JOIN_FULL_OUTER;
+        track_right_ = jt == SRB_JOIN_RIGHT_OUTER || jt == SRB_JOIN_FULL_OUTER || jt == SRB_JOIN_RIGHT_SEMI || jt == SRB_JOIN_RIGHT_ANTI;
+        right_only_ = jt == SRB_JOIN_RIGHT_SEMI || jt == SRB_JOIN_RIGHT_ANTI;
+        right_want_ = jt == SRB_JOIN_RIGHT_SEMI ? 1 : 0;
         if (p->n_keys < 1 || p->n_keys > JMAX_KEYS) throw Error(SRB_NOT_IMPLEMENTED, fmt("join with %d key columns", p->n_keys));
         if (p->n_build_out < 0 || p->n_probe_out < 0 || p->n_build_out + p->n_probe_out > JMAX_OUT)
             throw Error(SRB_NOT_IMPLEMENTED, "too many join output columns");
@@ -508,7 +566,8 @@ public:
         bout_.assign(p->build_out_slots, p->build_out_slots + p->n_build_out);
         pout_.assign(p->probe_out_slots, p->probe_out_slots + p->n_probe_out);
         if (semi_) bout_.clear(); // LEFT SEMI emits probe columns only
-        emit_indexes_ = p->emit_indexes != 0 && !anti_;
+        if (right_only_) pout_.clear(); // RIGHT SEMI / ANTI emit build columns only
+        emit_indexes_ = p->emit_indexes != 0 && !anti_ && !keep_left_ && !track_right_;
         chunk_size_ = c->cfg.chunk_size > 0 ? c->cfg.chunk_size : 4096;
         bcols_.resize(bkeys_.size() + bout_.size());
         total_dev_.ensure(c, 8);
@@ -520,7 +579,14 @@ public:
     void push_chunk(const srb_chunk* ch) override {
         if (finishing) throw Error(SRB_INTERNAL_ERROR, "push_chunk after set_finishing");
         if (!ch || ch->n_rows < 0) throw Error(SRB_INVALID_ARGUMENT, "bad chunk");
-        if (ch->n_rows == 0) return;
+        if (ch->n_rows == 0) { // an empty chunk still tells the column types (an outer join against nothing emits typed NULL columns)
+            for (size_t i = 0; i < bcols_.size(); i++) {
+                const int slot = i < bkeys_.size() ? bkeys_[i] : bout_[i - bkeys_.size()];
+                for (int c = 0; c < ch->n_cols; c++)
+                    if (ch->slot_ids[c] == slot) describe(bcols_[i], &ch->cols[c], slot);
+            }
+            return;
+        }
         if ((uint64_t)build_rows_ + (uint64_t)ch->n_rows >= ((uint64_t)1 << 32) - 1)
             throw Error(SRB_NOT_IMPLEMENTED, "build side exceeds 2^32 rows (uint32 first/next, join_hash_map.h:101-120)");
         for (size_t i = 0; i < bcols_.size(); i++) {
@@ -559,7 +625,36 @@ public:
     bool probe_need_input() override { return build_done_ && !probe_finishing_ && out_pos_ >= out_rows_; }
     bool probe_has_output() override { return out_pos_ < out_rows_; }
     bool probe_is_finished() override { return probe_finishing_ && out_pos_ >= out_rows_; }
-    void probe_set_finishing() override { probe_finishing_ = true; }
+    void probe_set_finishing() override {
+        if (probe_finishing_) return;
+        probe_finishing_ = true;
+        if (!track_right_ || !build_done_ || build_rows_ == 0) return;
+        if (out_pos_ < out_rows_) throw Error(SRB_INTERNAL_ERROR, "probe set_finishing while output is pending");
+        // the build side's remainder (_search_ht_remain): rows that never matched (RIGHT / FULL OUTER, RIGHT ANTI) or did (RIGHT SEMI)
+        out_rows_ = out_pos_ = 0;
+        for (size_t i = 0; i < pout_.size(); i++)
+            if (pkeys_.size() + i >= pcols_.size() || !pcols_[pkeys_.size() + i].known)
+                throw Error(SRB_INTERNAL_ERROR, "outer join: no probe chunk described the probe columns (push an empty probe chunk first)");
+        SRB_CUDA(cudaMemsetAsync(total_dev_.p, 0, 8, stream));
+        const int grid = grid_for(build_rows_);
+        k_join_remainder<<<grid, 256, 0, stream>>>(matched_.as<uint8_t>(), (uint32_t)build_rows_, right_want_, total_dev_.as<unsigned long long>(), nullptr);
+        SRB_CUDA(cudaMemcpyAsync(total_host_.p, total_dev_.p, 8, cudaMemcpyDeviceToHost, stream));
+        SRB_CUDA(cudaMemsetAsync(total_dev_.p, 0, 8, stream));
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        const int64_t m = (int64_t)*total_host_.as<unsigned long long>();
+        launches++;
+        if (m == 0) return;
+        obuild_.ensure(ctx, (size_t)m * 4);
+        k_join_remainder<<<grid, 256, 0, stream>>>(matched_.as<uint8_t>(), (uint32_t)build_rows_, right_want_, total_dev_.as<unsigned long long>(), obuild_.as<uint32_t>());
+        std::vector<const uint8_t*> none(pcols_.size(), nullptr);
+        GatherArgs ga = describe_outputs(m, none, none);
+        if (ga.n_cols) k_join_gather<<<grid_for(m), 256, 0, stream>>>(ga, m, nullptr, obuild_.as<uint32_t>());
+        launches += 2;
+        SRB_CUDA(cudaGetLastError());
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        rows_selected += m;
+        out_rows_ = m;
+    }
 
     void probe_push_chunk(const srb_chunk* ch) override {
         if (!build_done_) throw Error(SRB_INTERNAL_ERROR, "probe before the build side finished (need_input() is false)");
@@ -595,14 +690,19 @@ public:
             }
             if (i < pkeys_.size()) total += g.width;
         }
-        if (n == 0 || (build_rows_ == 0 && !anti_)) return;
-        if (build_rows_ == 0) { // LEFT ANTI against nothing: every probe row
+        if (n == 0 || (build_rows_ == 0 && !anti_ && !keep_left_)) return;
+        if (build_rows_ == 0 && anti_) { // LEFT ANTI against nothing: every probe row
             probe_tiled(n, data, nulls);
             return;
         }
         int pw = total <= 4 ? 4 : (total <= 8 ? 8 : 16);
+        if (build_rows_ == 0 && width_ == 0) { // LEFT / FULL OUTER against a build side that never described its keys: an empty table
+            width_ = pw;
+            build_table();
+        }
         if (total > 16 || pw != width_) throw Error(SRB_INVALID_ARGUMENT, "probe key width does not match the build key width");
-        if ((unique_ && !force_general_) || anti_) {
+        const bool outer = keep_left_ || track_right_;
+        if (((unique_ && !force_general_) || anti_) && !outer) {
             probe_tiled(n, data, nulls);
             return;
         }
@@ -618,8 +718,9 @@ public:
         // pass 1: count
         JTable t = table();
         SRB_CUDA(cudaMemsetAsync(total_dev_.p, 0, 8, stream));
+        uint8_t* matched = track_right_ ? matched_.as<uint8_t>() : nullptr;
         k_join_probe<0><<<grid, 256, 0, stream>>>(t, ppacked_.as<uint8_t>(), pnull_.as<uint8_t>(), n, semi_ ? 1 : 0,
-                                                   total_dev_.as<unsigned long long>(), nullptr, nullptr);
+                                                   total_dev_.as<unsigned long long>(), nullptr, nullptr, keep_left_ ? 1 : 0, matched, right_only_ ? 0 : 1);
         SRB_CUDA(cudaMemcpyAsync(total_host_.p, total_dev_.p, 8, cudaMemcpyDeviceToHost, stream));
         SRB_CUDA(cudaMemsetAsync(total_dev_.p, 0, 8, stream));
         SRB_CUDA(cudaStreamSynchronize(stream));
@@ -632,7 +733,7 @@ public:
         oprobe_.ensure(ctx, (size_t)m * 4);
         obuild_.ensure(ctx, (size_t)m * 4);
         k_join_probe<1><<<grid, 256, 0, stream>>>(t, ppacked_.as<uint8_t>(), pnull_.as<uint8_t>(), n, semi_ ? 1 : 0,
-                                                   total_dev_.as<unsigned long long>(), oprobe_.as<uint32_t>(), obuild_.as<uint32_t>());
+                                                   total_dev_.as<unsigned long long>(), oprobe_.as<uint32_t>(), obuild_.as<uint32_t>(), keep_left_ ? 1 : 0);
         launches++;
         // K8 gather
         GatherArgs ga = describe_outputs(m, data, nulls);
@@ -652,6 +753,7 @@ public:
         for (size_t i = 0; i < ocols_.size(); i++) {
             bool fb = i >= pout_.size();
             const GrowCol& src = fb ? bcols_[bkeys_.size() + (i - pout_.size())] : pcols_[pkeys_.size() + i];
+            if (!src.known) throw Error(SRB_INTERNAL_ERROR, "join output column of a side that never described its columns (push an empty chunk of that side first)");
             GrowCol& o = ocols_[i];
             o.type = src.type;
             o.precision = src.precision;
@@ -660,7 +762,9 @@ public:
             o.known = true;
             const uint8_t* sdata = fb ? src.data.as<uint8_t>() : data[pkeys_.size() + i];
             const uint8_t* snull = fb ? (src.nullable ? src.nulls.as<uint8_t>() : nullptr) : nulls[pkeys_.size() + i];
-            o.nullable = snull != nullptr;
+            // a side that may be missing in an output row comes back nullable: build columns of LEFT / FULL OUTER, probe columns of
+            // RIGHT / FULL OUTER
+            o.nullable = snull != nullptr || (fb ? keep_left_ : (track_right_ && !right_only_));
             o.data.ensure(ctx, (size_t)m * o.width);
             if (o.nullable) o.nulls.ensure(ctx, (size_t)m);
             ga.cols[i] = GatherCol{sdata, o.data.as<uint8_t>(), snull, o.nullable ? o.nulls.as<uint8_t>() : nullptr, o.width, fb ? 1 : 0};
@@ -917,6 +1021,10 @@ private:
         log_bucket_ = (uint32_t)__builtin_ctz(bucket_size_);
         first_.ensure(ctx, (size_t)bucket_size_ * 4);
         next_.ensure(ctx, (size_t)(n + 1) * 4);
+        if (track_right_) {
+            matched_.ensure(ctx, (size_t)(n + 1));
+            SRB_CUDA(cudaMemsetAsync(matched_.p, 0, (size_t)(n + 1), stream));
+        }
         SRB_CUDA(cudaMemsetAsync(first_.p, 0, (size_t)bucket_size_ * 4, stream));
         SRB_CUDA(cudaMemsetAsync(next_.p, 0, (size_t)(n + 1) * 4, stream));
         if (n > 0) {
@@ -947,7 +1055,9 @@ private:
         return t;
     }
 
-    bool anti_ = false;
+    bool anti_ = false, keep_left_ = false, track_right_ = false, right_only_ = false;
+    int right_want_ = 0;
+    DevBuf matched_; // one byte per build row (1-based): the row matched some probe row (RIGHT / FULL OUTER, RIGHT SEMI / ANTI)
     bool semi_ = false, emit_indexes_ = false, build_done_ = false, probe_finishing_ = false, gave_empty_ = false;
     std::vector<int32_t> bkeys_, pkeys_, bout_, pout_;
     int64_t chunk_size_;

@@ -14,6 +14,7 @@
 // (srb_shapes.cuh). There is no CPU path: every row is processed by a CUDA kernel.
 #include <limits>
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -1167,6 +1168,18 @@ struct HostCol { // result column handed out by pull_chunk (host memory owned by
     bool has_nulls = false;
 };
 
+// SRB_TRACE=1: host-side wall time of the stages of a push / set_finishing on stderr (a diagnostic, off by default)
+struct HostTrace {
+    bool on = getenv("SRB_TRACE") != nullptr;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    void mark(const char* what) {
+        if (!on) return;
+        auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[srb trace] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+
 struct Stage { // device staging of host chunks: one buffer per bound column
     DevBuf data[MAX_COLS], nulls[MAX_COLS], offsets[MAX_COLS];
     DevBuf enc[MAX_COLS], pdesc[MAX_COLS], fdir[MAX_COLS]; // encoded pages: their bytes, page descriptors and frame directory
@@ -1654,10 +1667,13 @@ private:
             batch = (int64_t)1 << 30;
             while (batch > AGG_BATCH && (size_t)std::min<int64_t>(batch, n) * 17 + ((size_t)1 << 30) > free_b) batch >>= 1;
         }
+        HostTrace tr;
         for (int64_t off = 0; off < n; off += batch) {
             int64_t m = std::min<int64_t>(batch, n - off);
             launch_batch(cols, off, m);
+            tr.mark("launch_batch");
             check_batch(cols, off, m);
+            tr.mark("check_batch");
         }
     }
 
@@ -1957,7 +1973,9 @@ private:
 
     void launch_batch(const ColBind* cols, int64_t off, int64_t n, const uint32_t* defer_in = nullptr) {
         if (radix_rows_ > 0) radix_ingest(); // a key may occur in the radix batch's groups and in this batch: both go through the table
+        HostTrace tr;
         ensure_table();
+        tr.mark("  ensure_table");
         if (!ev0_) {
             ev0_ = ctx->take_event(true);
             ev1_ = ctx->take_event(true);
@@ -1969,8 +1987,10 @@ private:
             // the static kernel (and the L2-blocked permutation, which moves values but not null maps) can take it
             batch_has_nulls_ = batch_stripped_ = false;
             if (shape_ >= 0 && !force_generic_) cols = strip_clear_null_maps(cols, off, n);
+            tr.mark("  strip null maps");
             batch_partitioned_ = !batch_has_nulls_ && hc_partition_applies(n);
             if (batch_partitioned_) hc_partition(cols, off, n);
+            tr.mark("  hc_partition");
         } else if (!batch_partitioned_ && batch_stripped_) {
             cols = nn_cols_; // the replay sees the batch as its first launch did
         }
@@ -2010,6 +2030,7 @@ private:
         SRB_CUDA(cudaEventRecord(ev1_, stream));
         timed_pending_ = true;
         SRB_CUDA(cudaGetLastError());
+        tr.mark("  kernels enqueued");
     }
 
     // waits for the batch, folds the counters, replays deferred rows after growing the table
@@ -2319,7 +2340,9 @@ private:
     void produce_output(uint64_t max_rows, bool exact) {
         if (filter_only_) return; // rows already sit in fout_
         const DProg& P = L_.prog;
+        HostTrace tr;
         EmitArgs ea = emit_args((uint64_t)stream_rows_ + max_rows);
+        tr.mark("emit_args (output arrays)");
         if (!table_ready_) { // every batch went through the radix path (or none arrived): the result rows are in place already
             if (P.n_keys == 0) {
                 ensure_table();
@@ -2338,6 +2361,7 @@ private:
         prefetch_small_result((int64_t)stream_rows_ + (int64_t)max_rows); // a handful of rows reach the host with this same wait
         SRB_CUDA(cudaStreamSynchronize(stream));
         if (exact ? hc->emitted != max_rows : hc->emitted > max_rows) throw Error(SRB_INTERNAL_ERROR, fmt("emit produced %llu rows, table holds %llu", (unsigned long long)hc->emitted, (unsigned long long)max_rows));
+        tr.mark("k_emit + wait");
         out_rows_ = stream_rows_ + (int64_t)hc->emitted; // pass-through rows first, then the table's groups
     }
 

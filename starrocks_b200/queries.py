@@ -62,7 +62,7 @@ def q6_plan(phase: int = K.AGG_UPDATE_FINALIZE) -> ScanAggPlan:
     return ScanAggPlan(preds=preds, exprs=e, aggs=[(K.AGG_SUM, prod)], phase=phase)
 
 
-def q1_plan(dict_keys: bool = True, phase: int = K.AGG_UPDATE_FINALIZE, group_hint: int = 4) -> ScanAggPlan:
+def q1_plan(dict_keys: bool = True, phase: int = K.AGG_UPDATE_FINALIZE, group_hint: int = 4, with_min_max: bool = False) -> ScanAggPlan:
     """select l_returnflag, l_linestatus, sum(qty), sum(ext), sum(ext*(1-disc)), sum(ext*(1-disc)*(1+tax)),
               avg(qty), avg(ext), avg(disc), count(*) from lineitem where l_shipdate <= '1998-09-02' group by 1, 2"""
     e = ExprBuilder()
@@ -83,6 +83,8 @@ def q1_plan(dict_keys: bool = True, phase: int = K.AGG_UPDATE_FINALIZE, group_hi
     charge = e.mul(disc_price, e.cast(one_plus_tax, D128, 16, 2), D128, 38)                           # DECIMAL128(38,6), checked
     aggs = [(K.AGG_SUM, qty), (K.AGG_SUM, ext), (K.AGG_SUM, disc_price), (K.AGG_SUM, charge),
             (K.AGG_AVG, qty), (K.AGG_AVG, ext), (K.AGG_AVG, disc), (K.AGG_COUNT, None)]
+    if with_min_max:  # a ninth and tenth aggregate: the plan no longer matches a static shape
+        aggs += [(K.AGG_MIN, ext), (K.AGG_MAX, ext)]
     preds = [pred(L_SHIPDATE, K.PRED_LE, K.TYPE_DATE, from_date(1998, 9, 2))]
     return ScanAggPlan(preds=preds, exprs=e, keys=[k1, k2], aggs=aggs, phase=phase, group_hint=group_hint)
 

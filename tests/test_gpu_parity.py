@@ -785,6 +785,89 @@ def run_join(ctx, plan, build, probe, build_pieces=1, device=False):
         op.close()
 
 
+def run_join_chunks(ctx, plan, build, probes, device=False, build_pieces=2):
+    """build in pieces, one probe chunk after the other (every chunk's output pulled before the next push, as the driver does), then
+    probe set_finishing and the final pull: the build-side remainder of RIGHT / FULL OUTER and RIGHT SEMI / ANTI joins"""
+    from starrocks_b200 import ops
+    op = ops.HashJoinOperator(ctx, plan)
+    ptrs, rows = [], []
+    try:
+        step = max(1, build.n_rows // build_pieces)
+        for a in range(0, max(build.n_rows, 1), step):
+            op.push_chunk(ops.slice_chunk(build, a, min(build.n_rows, a + step)))
+        op.set_finishing()
+        for pr in probes:
+            if device:
+                pr, pp = ctx.device_chunk(pr)
+                ptrs += pp
+            op.probe.push_chunk(pr)
+            rows += K.chunk_rows(op.probe.pull_all(), sort=False)
+        op.probe.set_finishing()
+        rows += K.chunk_rows(op.probe.pull_all(), sort=False)
+        assert op.probe.is_finished()
+        return rows
+    finally:
+        for p in ptrs:
+            ctx.device_free(p)
+        op.close()
+
+
+OUTER_TYPES = [K.JOIN_LEFT_OUTER, K.JOIN_RIGHT_OUTER, K.JOIN_FULL_OUTER, K.JOIN_RIGHT_SEMI, K.JOIN_RIGHT_ANTI]
+
+
+@pytest.mark.parametrize("jt", OUTER_TYPES)
+@pytest.mark.parametrize("ktypes", [[K.TYPE_INT], [K.TYPE_BIGINT, K.TYPE_SMALLINT], [K.TYPE_DECIMAL128]])
+def test_outer_and_right_side_joins(ctx, oracle, jt, ktypes):
+    # join_hash_map.tpp:1187-1986: LEFT / RIGHT / FULL OUTER, RIGHT SEMI / ANTI; duplicate keys, NULL keys on both sides, several probe chunks
+    from starrocks_b200 import ops
+    rng = np.random.default_rng(23 + jt)
+    nb, npr = 40_000, 150_000
+
+    def keycols(n, base_slot, span):
+        cols = {}
+        for i, t in enumerate(ktypes):
+            v = rng.integers(0, span if i == 0 else 3, n)
+            if K.type_width(t) == 16:
+                v = [int(x) * 10**20 for x in v]
+            cols[base_slot + i] = K.Column.from_ints(t, v, (rng.random(n) < 0.03).astype(np.uint8), 38 if K.type_width(t) == 16 else 0, 0)
+        return cols
+
+    bcols = keycols(nb, 0, 30_000)
+    bcols[8] = K.Column.from_ints(K.TYPE_BIGINT, np.arange(nb))
+    bcols[9] = K.Column.from_ints(K.TYPE_DECIMAL64, rng.integers(0, 999, nb), (rng.random(nb) < 0.1).astype(np.uint8), 15, 2)
+    build = K.Chunk(nb, bcols)
+    pcols = keycols(npr, 20, 60_000)
+    pcols[28] = K.Column.from_ints(K.TYPE_INT, np.arange(npr, dtype=np.int32))
+    probe = K.Chunk(npr, pcols)
+    nk = len(ktypes)
+    plan = JoinPlan(list(range(nk)), list(range(20, 20 + nk)), build_out=[8, 9], probe_out=[28, 20], join_type=jt)
+    want = sorted(K.chunk_rows(oracle.join(plan, build, probe), sort=False), key=repr)
+    assert len(want) > 1000
+    pieces = [ops.slice_chunk(probe, 0, 50_000), ops.slice_chunk(probe, 50_000, 50_001), ops.slice_chunk(probe, 50_001, npr)]
+    for device in (False, True):
+        got = run_join_chunks(ctx, plan, build, pieces, device=device)
+        assert sorted(got, key=repr) == want, (jt, device)
+
+
+@pytest.mark.parametrize("jt,rows", [(K.JOIN_LEFT_OUTER, 5), (K.JOIN_FULL_OUTER, 5), (K.JOIN_LEFT_ANTI, 5), (K.JOIN_INNER, 0), (K.JOIN_LEFT_SEMI, 0),
+                                     (K.JOIN_RIGHT_SEMI, 0), (K.JOIN_RIGHT_OUTER, 0), (K.JOIN_RIGHT_ANTI, 0)])
+def test_joins_against_an_empty_build_side(ctx, oracle, jt, rows):
+    # be/test/exec/join_hash_map_test.cpp:2376-2388 EmptyHashMapTest: 5 probe rows against an empty hash table
+    build = K.Chunk(0, {0: K.Column.from_ints(K.TYPE_INT, np.zeros(0, np.int32)), 1: K.Column.from_ints(K.TYPE_BIGINT, np.zeros(0, np.int64))})
+    probe = K.Chunk(5, {2: K.Column.from_ints(K.TYPE_INT, np.arange(5, dtype=np.int32)), 3: K.Column.from_ints(K.TYPE_BIGINT, np.arange(5) * 7)})
+    plan = JoinPlan([0], [2], build_out=[1], probe_out=[2, 3], join_type=jt)
+    want = K.chunk_rows(oracle.join(plan, build, probe), sort=False)
+    assert len(want) == rows
+    got = run_join_chunks(ctx, plan, build, [probe])
+    assert sorted(got, key=repr) == sorted(want, key=repr)
+    # and an empty probe side against a real build side: only the right-side remainder comes out
+    build = K.Chunk(3, {0: K.Column.from_ints(K.TYPE_INT, np.array([4, 5, 5], np.int32)), 1: K.Column.from_ints(K.TYPE_BIGINT, np.array([1, 2, 3]))})
+    none = K.Chunk(0, {2: K.Column.from_ints(K.TYPE_INT, np.zeros(0, np.int32)), 3: K.Column.from_ints(K.TYPE_BIGINT, np.zeros(0, np.int64))})
+    want = K.chunk_rows(oracle.join(plan, build, none), sort=False)
+    got = run_join_chunks(ctx, plan, build, [none])
+    assert sorted(got, key=repr) == sorted(want, key=repr)
+
+
 def test_join_reference_vectors(ctx, oracle, join_mode):
     # be/test/exec/join_hash_map_test.cpp semantics: 1-based build indexes, NULL keys never match, one-to-many chains
     build = K.Chunk(6, {0: K.Column.from_ints(K.TYPE_INT, [1, 2, 2, 3, 5, 7], nulls=[0, 0, 0, 0, 1, 0]),

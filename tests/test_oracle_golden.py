@@ -580,3 +580,27 @@ def test_for_page_layout_bit_for_bit(oracle):
     wide = K.to_i128_array([3 * 10**30, -7 * 10**29, 12345, 0, 10**37])
     got = oracle.for_decode(oracle.for_encode(wide), K.I128)
     assert (got["lo"] == wide["lo"]).all() and (got["hi"] == wide["hi"]).all()
+
+
+def test_joins_against_an_empty_hash_table_like_the_reference(oracle):
+    # be/test/exec/join_hash_map_test.cpp:2376-2388 EmptyHashMapTest: check_empty_hash_map(join type, 5 probe rows, expected rows, columns)
+    from starrocks_b200.plan import JoinPlan
+    build = K.Chunk(0, {0: K.Column.from_ints(K.TYPE_INT, np.zeros(0, np.int32)), 1: K.Column.from_ints(K.TYPE_BIGINT, np.zeros(0, np.int64))})
+    probe = K.Chunk(5, {2: K.Column.from_ints(K.TYPE_INT, np.arange(5, dtype=np.int32)), 3: K.Column.from_ints(K.TYPE_BIGINT, np.arange(5))})
+    expect = {K.JOIN_LEFT_OUTER: 5, K.JOIN_FULL_OUTER: 5, K.JOIN_LEFT_ANTI: 5, K.JOIN_INNER: 0, K.JOIN_LEFT_SEMI: 0, K.JOIN_RIGHT_SEMI: 0,
+              K.JOIN_RIGHT_OUTER: 0, K.JOIN_RIGHT_ANTI: 0}
+    for jt, rows in expect.items():
+        out = oracle.join(JoinPlan([0], [2], build_out=[1], probe_out=[2, 3], join_type=jt), build, probe)
+        assert out.n_rows == rows, jt
+    # a small hand-checked case: build keys 1, 2, 2, NULL; probe keys 2, 3, 1, NULL
+    build = K.Chunk(4, {0: K.Column.from_ints(K.TYPE_INT, np.array([1, 2, 2, 9], np.int32), np.array([0, 0, 0, 1], np.uint8)),
+                        1: K.Column.from_ints(K.TYPE_BIGINT, np.array([10, 20, 21, 90]))})
+    probe = K.Chunk(4, {2: K.Column.from_ints(K.TYPE_INT, np.array([2, 3, 1, 7], np.int32), np.array([0, 0, 0, 1], np.uint8)),
+                        3: K.Column.from_ints(K.TYPE_BIGINT, np.array([200, 300, 100, 700]))})
+    rows = lambda jt: K.chunk_rows(oracle.join(JoinPlan([0], [2], build_out=[1], probe_out=[2, 3], join_type=jt), build, probe), sort=False)
+    inner = [(2, 200, 21), (2, 200, 20), (1, 100, 10)]
+    assert rows(K.JOIN_INNER) == inner
+    assert rows(K.JOIN_LEFT_OUTER) == [(2, 200, 21), (2, 200, 20), (3, 300, None), (1, 100, 10), (None, 700, None)]
+    assert rows(K.JOIN_RIGHT_OUTER) == inner + [(None, None, 90)]
+    assert rows(K.JOIN_FULL_OUTER) == [(2, 200, 21), (2, 200, 20), (3, 300, None), (1, 100, 10), (None, 700, None), (None, None, 90)]
+    assert rows(K.JOIN_RIGHT_SEMI) == [(10,), (20,), (21,)] and rows(K.JOIN_RIGHT_ANTI) == [(90,)]
