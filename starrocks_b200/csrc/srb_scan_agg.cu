@@ -189,15 +189,22 @@ __global__ void __launch_bounds__(256) k_scan_agg_generic(const __grid_constant_
         if (sh_cap) {
             const uint32_t idx = (uint32_t)(slot - tv.slots) / (uint32_t)p.slot_bytes;
             for (int a = 0; a < p.n_aggs; a++) {
+                const DAgg& g = p.aggs[a];
                 LocalAcc d{0, 0, 0};
-                update_agg_local(p, p.aggs[a], d, v, row);
+                update_agg_local(p, g, d, v, row);
+                if (d.n == 0) continue; // a NULL argument: nothing to add
                 unsigned long long* e = sh_acc + (idx * p.n_aggs + a) * 3;
-                if (d.lo | d.hi) { // 128-bit add as two 64-bit atomics: the carry out of the low word travels with the high word's addend
+                if (g.fn == FN_MIN || g.fn == FN_MAX) { // the mirror keeps the table's own order-preserving encoding (identity: zero)
+                    const bool mn = g.fn == FN_MIN;
+                    atomicMax(e, (unsigned long long)(g.is_double ? enc_f64(d.lo, mn) : enc_i64((int64_t)d.lo, mn)));
+                } else if (g.fn != FN_COUNT && (g.is_double || g.avg_as_double)) {
+                    atomicAdd((double*)e, __longlong_as_double((long long)d.lo));
+                } else if (d.lo | d.hi) { // 128-bit add as two 64-bit atomics: the carry out of the low word travels with the high word's addend
                     const unsigned long long old = atomicAdd(e, (unsigned long long)d.lo);
                     const unsigned long long up = d.hi + ((old + d.lo) < old ? 1ULL : 0ULL);
                     if (up) atomicAdd(e + 1, up);
                 }
-                if (d.n) atomicAdd(e + 2, (unsigned long long)d.n);
+                atomicAdd(e + 2, (unsigned long long)d.n);
             }
             continue;
         }
@@ -209,7 +216,14 @@ __global__ void __launch_bounds__(256) k_scan_agg_generic(const __grid_constant_
         __syncthreads();
         for (int i = threadIdx.x; i < sh_cap * p.n_aggs; i += blockDim.x) {
             const LocalAcc s{sh_acc[i * 3], sh_acc[i * 3 + 1], sh_acc[i * 3 + 2]};
-            flush_local(p.aggs[i % p.n_aggs], s, tv.slots + (size_t)(i / p.n_aggs) * p.slot_bytes); // a state no row touched has n == 0
+            const DAgg& g = p.aggs[i % p.n_aggs];
+            uint8_t* slot = tv.slots + (size_t)(i / p.n_aggs) * p.slot_bytes;
+            if (s.n && (g.fn == FN_MIN || g.fn == FN_MAX)) { // already encoded: fold it in as it is
+                atomicMax((unsigned long long*)(slot + g.off_lo), (unsigned long long)s.lo);
+                if (g.off_n >= 0) atomicAdd((unsigned long long*)(slot + g.off_n), (unsigned long long)s.n);
+            } else {
+                flush_local(g, s, slot); // a state no row touched has n == 0
+            }
         }
     }
     // one atomic per warp for the counters
@@ -220,6 +234,132 @@ __global__ void __launch_bounds__(256) k_scan_agg_generic(const __grid_constant_
         inserted += __shfl_down_sync(0xffffffffu, inserted, o);
     }
     if ((threadIdx.x & 31) == 0) {
+        if (selected) atomicAdd(&ctr->rows_selected, selected);
+        if (deferred) atomicAdd(&ctr->deferred, deferred);
+        if (too_long) atomicAdd(&ctr->key_too_long, too_long);
+        if (inserted) atomicAdd(&ctr->inserted, inserted);
+    }
+}
+
+// ---- low-cardinality GROUP BY through the interpreter: thread-private accumulators ------------------------------------------------
+// A handful of groups (TPC-H Q1's four) take every row: per-row atomics — on the table or on a shared mirror — serialise on the same few
+// addresses (134 M rows of Q1 with VARCHAR(1) keys: 48 ms through the shared mirror; with one MIN / MAX, which the mirror does not
+// cover, 1.06 s of global atomicMax). Here a CTA keeps a small directory of the table slots its rows have hit (<= LC_MAXG) and every
+// THREAD its own accumulator {lo, hi, n} per (directory entry, aggregate) in shared memory, laid out [entry][aggregate][field][thread]:
+// an update is three conflict-free LDS, the same update_agg_local the no-GROUP-BY path uses (every function, DOUBLE and MIN / MAX
+// included), three STS — no atomics. At retirement the threads' accumulators are merged with warp shuffles and one lane per (entry,
+// aggregate) folds the result into the table. Rows of a group beyond the directory update the table directly. Integer results are
+// bit-identical; DOUBLE sums are added in a different order (1e-9 relative, as everywhere).
+constexpr int LC_THREADS = 128, LC_MAXG = 8;
+constexpr uint32_t LC_EMPTY = 0xFFFFFFFFu;
+
+SRB_D void merge_local(const DAgg& g, LocalAcc& into, const LocalAcc& from) {
+    if (from.n == 0) return;
+    if (g.fn == FN_SUM || g.fn == FN_AVG) {
+        if (g.is_double || g.avg_as_double) {
+            into.lo = (uint64_t)__double_as_longlong(__longlong_as_double((long long)into.lo) + __longlong_as_double((long long)from.lo));
+        } else {
+            const u128 sum = (u128)make_i128(into.lo, (int64_t)into.hi) + (u128)make_i128(from.lo, (int64_t)from.hi);
+            into.lo = (uint64_t)sum;
+            into.hi = (uint64_t)(sum >> 64);
+        }
+    } else if (g.fn == FN_MIN || g.fn == FN_MAX) {
+        const bool mn = g.fn == FN_MIN;
+        bool better;
+        if (g.is_double) {
+            const double c = __longlong_as_double((long long)into.lo), d = __longlong_as_double((long long)from.lo);
+            better = mn ? d < c : d > c;
+        } else {
+            const i128 c = make_i128(into.lo, (int64_t)into.hi), d = make_i128(from.lo, (int64_t)from.hi);
+            better = mn ? d < c : d > c;
+        }
+        if (into.n == 0 || better) {
+            into.lo = from.lo;
+            into.hi = from.hi;
+        }
+    }
+    into.n += from.n;
+}
+
+__global__ void __launch_bounds__(LC_THREADS) k_scan_agg_lowcard(const __grid_constant__ DProg prog, const TableView tv, const int64_t base, const int64_t n,
+                                                                  const int64_t bit_base, uint32_t* __restrict__ defer_out, Counters* __restrict__ ctr,
+                                                                  const int G) {
+    const DProg& p = prog;
+    extern __shared__ unsigned long long lc_acc[]; // [entry][aggregate][field][thread]
+    __shared__ uint32_t dir[LC_MAXG];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < G * p.n_aggs * 3 * LC_THREADS; i += LC_THREADS) lc_acc[i] = 0;
+    if (tid < LC_MAXG) dir[tid] = LC_EMPTY;
+    __syncthreads();
+    Val v[MAX_NODES];
+    unsigned long long selected = 0, deferred = 0, too_long = 0, inserted = 0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + tid; i < n; i += stride) {
+        const int64_t row = base + i;
+        if (!eval_preds(p, row)) continue;
+        selected++;
+        for (int k = 0; k < p.n_nodes; k++) v[k] = eval_node(p.nodes[k], v, p.cols, row);
+        PackedKey k = pack_key(p, v, row);
+        if (k.too_long) {
+            too_long++;
+            continue;
+        }
+        bool fresh;
+        uint8_t* slot = table_find_or_insert(tv, k.lo, k.hi, hash_packed_key(k, p.phase_seed), &fresh);
+        inserted += fresh ? 1 : 0;
+        if (!slot) {
+            atomicOr(&defer_out[(i + bit_base) >> 5], 1u << ((i + bit_base) & 31));
+            deferred++;
+            continue;
+        }
+        const uint32_t idx = (uint32_t)((slot - tv.slots) / (uint32_t)p.slot_bytes);
+        int e = -1;
+        for (int j = 0; j < G && e < 0; j++) {
+            uint32_t cur = ((volatile uint32_t*)dir)[j];
+            if (cur == LC_EMPTY) cur = atomicCAS(&dir[j], LC_EMPTY, idx), cur = cur == LC_EMPTY ? idx : cur;
+            if (cur == idx) e = j;
+        }
+        if (e < 0) { // more groups than directory entries: this row goes to the table directly
+            for (int a = 0; a < p.n_aggs; a++) update_agg_global(p, p.aggs[a], slot, v, row);
+            continue;
+        }
+        for (int a = 0; a < p.n_aggs; a++) {
+            unsigned long long* w = lc_acc + (size_t)((e * p.n_aggs + a) * 3) * LC_THREADS + tid;
+            LocalAcc d{w[0], w[LC_THREADS], w[2 * LC_THREADS]};
+            update_agg_local(p, p.aggs[a], d, v, row);
+            w[0] = d.lo;
+            w[LC_THREADS] = d.hi;
+            w[2 * LC_THREADS] = d.n;
+        }
+    }
+    __syncthreads();
+    // merge the threads' accumulators: warp w takes the (entry, aggregate) pairs w, w + 4, ...
+    for (int pair = warp; pair < G * p.n_aggs; pair += LC_THREADS / 32) {
+        const int e = pair / p.n_aggs, a = pair % p.n_aggs;
+        const uint32_t idx = dir[e];
+        if (idx == LC_EMPTY) continue;
+        const DAgg& g = p.aggs[a];
+        LocalAcc s{0, 0, 0};
+        for (int t = lane; t < LC_THREADS; t += 32) {
+            const unsigned long long* w = lc_acc + (size_t)(pair * 3) * LC_THREADS + t;
+            merge_local(g, s, LocalAcc{w[0], w[LC_THREADS], w[2 * LC_THREADS]});
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            LocalAcc y;
+            y.lo = __shfl_down_sync(0xffffffffu, s.lo, o);
+            y.hi = __shfl_down_sync(0xffffffffu, s.hi, o);
+            y.n = __shfl_down_sync(0xffffffffu, s.n, o);
+            merge_local(g, s, y);
+        }
+        if (lane == 0) flush_local(g, s, tv.slots + (size_t)idx * p.slot_bytes);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        selected += __shfl_down_sync(0xffffffffu, selected, o);
+        deferred += __shfl_down_sync(0xffffffffu, deferred, o);
+        too_long += __shfl_down_sync(0xffffffffu, too_long, o);
+        inserted += __shfl_down_sync(0xffffffffu, inserted, o);
+    }
+    if (lane == 0) {
         if (selected) atomicAdd(&ctr->rows_selected, selected);
         if (deferred) atomicAdd(&ctr->deferred, deferred);
         if (too_long) atomicAdd(&ctr->key_too_long, too_long);
@@ -1677,15 +1817,27 @@ private:
         }
     }
 
-    // the interpreter's shared-memory mirror of a small table (see k_scan_agg_generic): integer SUM / AVG / COUNT states only
+    // the interpreter's shared-memory mirror of a small table (see k_scan_agg_generic): every state but 128-bit MIN / MAX
     int generic_shared_cap() const {
         const DProg& P = L_.prog;
         if (!P.n_keys || no_shared_agg_ || cap_ * (uint64_t)P.n_aggs > (uint64_t)GEN_SH_ENTRIES) return 0;
         for (int a = 0; a < P.n_aggs; a++) {
             const DAgg& g = P.aggs[a];
-            if ((g.fn != FN_SUM && g.fn != FN_AVG && g.fn != FN_COUNT) || g.is_double || g.avg_as_double) return 0;
+            if ((g.fn == FN_MIN || g.fn == FN_MAX) && g.wide && !g.is_double) return 0; // 128-bit MIN / MAX has no shared-memory atomic
+            if (g.merge && g.fn == FN_AVG && (g.is_double || g.avg_as_double)) return 0;
         }
         return (int)cap_;
+    }
+
+    // directory entries of the thread-private low-cardinality kernel (k_scan_agg_lowcard), 0 = not applicable: a GROUP BY whose table is
+    // small (hinted: at most 64 slots), a batch large enough to amortise the per-CTA merge, and room for >= 2 entries per CTA
+    int lowcard_entries(int64_t n) const {
+        const DProg& P = L_.prog;
+        if (!P.n_keys || no_lowcard_ || plan_.group_hint <= 0 || n < ((int64_t)1 << 18) || P.n_aggs < 1) return 0;
+        const size_t per_entry = (size_t)P.n_aggs * 3 * LC_THREADS * 8;
+        const int fit = std::min((int)((size_t)(110 * 1024) / per_entry), LC_MAXG); // two CTAs per SM
+        // the planner expects no more groups than a CTA's directory holds (more groups: the shared mirror of k_scan_agg_generic does better)
+        return fit >= 2 && plan_.group_hint <= fit ? fit : 0;
     }
 
     void bind_prog(const ColBind* cols) {
@@ -2022,9 +2174,19 @@ private:
             }
         }
         if (covered < n) {
-            const int sh_cap = generic_shared_cap();
-            k_scan_agg_generic<<<grid_for(n - covered), 256, (size_t)sh_cap * L_.prog.n_aggs * 24, stream>>>(L_.prog, tv, off + covered, n - covered, covered,
-                                                                                                              defer_in, dout, dc, sh_cap);
+            const int lc_entries = defer_in ? 0 : lowcard_entries(n - covered);
+            if (lc_entries) {
+                const size_t smem = (size_t)lc_entries * L_.prog.n_aggs * 3 * LC_THREADS * 8;
+                static SmemOptIn opt;
+                opt.set(k_scan_agg_lowcard, 112 * 1024);
+                const int64_t rest = n - covered;
+                const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((rest + LC_THREADS - 1) / LC_THREADS, (int64_t)ctx->n_sms * 2));
+                k_scan_agg_lowcard<<<blocks, LC_THREADS, smem, stream>>>(L_.prog, tv, off + covered, rest, covered, dout, dc, lc_entries);
+            } else {
+                const int sh_cap = generic_shared_cap();
+                k_scan_agg_generic<<<grid_for(n - covered), 256, (size_t)sh_cap * L_.prog.n_aggs * 24, stream>>>(L_.prog, tv, off + covered, n - covered, covered,
+                                                                                                                  defer_in, dout, dc, sh_cap);
+            }
             launches++;
         }
         SRB_CUDA(cudaEventRecord(ev1_, stream));
@@ -2582,6 +2744,9 @@ private:
     bool force_generic_ = getenv("SRB_FORCE_GENERIC") != nullptr; // test hook: compare the two kernel families
     bool no_narrow_ = getenv("SRB_NO_NARROW") != nullptr;         // test / measurement hook: the static kernels' general tile body only
     bool rf_fused_ = getenv("SRB_RF_FUSED") != nullptr;           // opt-in: all runtime filters of a scan in one kernel (k_filter_rf_multi)
+    // k_scan_agg_lowcard measured SLOWER than the shared mirror on a B200 (Q1 with VARCHAR keys: 92 vs 49 ms per 134 M rows — its
+    // 96 KB of private accumulators leave 8 warps per SM for an interpreter that lives on latency hiding): opt-in, SRB_LOWCARD=1
+    bool no_lowcard_ = getenv("SRB_LOWCARD") == nullptr || getenv("SRB_NO_LOWCARD") != nullptr;
     bool no_shared_agg_ = getenv("SRB_NO_SHARED_AGG") != nullptr; // test / measurement hook: the interpreter updates the table per row
     bool no_partition_ = getenv("SRB_NO_PARTITION") != nullptr;   // test / measurement hook: direct table updates for every batch
     // The radix-partitioned aggregation is correct (tests/test_gpu_radix_agg.py) but measured SLOWER than the table path on a B200
