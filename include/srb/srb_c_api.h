@@ -106,6 +106,10 @@ typedef struct srb_predicate {
     int32_t or_group; /* 0 = plain conjunct */
     int64_t lit_lo;   /* literal, low 64 bits (sign-extended into lit_hi for <=64-bit types) */
     int64_t lit_hi;
+    /* VARCHAR / VARBINARY columns (BinaryColumnPredicateCmpBase, storage/column_predicate_cmp.cpp:559-700): the literal's bytes, compared
+     * like Slice::compare (memcmp over the common length, then the shorter one is smaller). At most 16 bytes; NULL / 0 for other types. */
+    const void* lit_bytes;
+    int64_t lit_len;
 } srb_predicate;
 
 /* ---- scalar expressions: flattened Expr tree (exprs/expr.h, exprs/arithmetic_expr.cpp:66-128) ----- */

@@ -111,7 +111,17 @@ inline void pred_evaluate(const srb_predicate& p, const srb_chunk& ch, int64_t b
             r = isnull;
         else if (p.op == SRB_PRED_NOT_NULL)
             r = !isnull;
-        else if (c->type == SRB_TYPE_DOUBLE)
+        else if (is_binary(c->type)) {
+            // BinaryColumnPredicateCmpBase (storage/column_predicate_cmp.cpp:559-700): Slice::compare = memcmp over the common length, then lengths
+            r = 0;
+            if (!isnull) {
+                const uint8_t* sp = (const uint8_t*)c->data + c->offsets[row];
+                const size_t n = c->offsets[row + 1] - c->offsets[row], m = (size_t)p.lit_len;
+                int d = memcmp(sp, p.lit_bytes, n < m ? n : m);
+                if (d == 0) d = n == m ? 0 : (n < m ? -1 : 1);
+                r = (uint8_t)cmp_apply(p.op, (int128_t)d, (int128_t)0);
+            }
+        } else if (c->type == SRB_TYPE_DOUBLE)
             r = (uint8_t)((!isnull) & cmp_apply_d(p.op, ((const double*)c->data)[row], dlit));
         else
             r = (uint8_t)((!isnull) & cmp_apply(p.op, load_int(*c, row), lit));

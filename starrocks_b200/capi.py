@@ -63,7 +63,7 @@ class srb_chunk(C.Structure):
 
 class srb_predicate(C.Structure):
     _fields_ = [("slot_id", C.c_int32), ("op", C.c_int32), ("type", C.c_int32), ("or_group", C.c_int32),
-                ("lit_lo", C.c_int64), ("lit_hi", C.c_int64)]
+                ("lit_lo", C.c_int64), ("lit_hi", C.c_int64), ("lit_bytes", C.c_void_p), ("lit_len", C.c_int64)]
 
 
 class srb_expr_node(C.Structure):

@@ -160,12 +160,21 @@ inline Lowered lower_plan(const PlanCopy& plan, const srb_chunk* first) {
         auto put = [&](const srb_predicate& s, int group) {
             DPred& d = P.preds[np++];
             d.col = bind(s.slot_id);
-            if (P.cols[d.col].kind == CK_BINARY && s.op != SRB_PRED_IS_NULL && s.op != SRB_PRED_NOT_NULL)
-                throw Error(SRB_NOT_IMPLEMENTED, "comparison predicate on a binary column");
             d.op = s.op;
             d.group = group;
             d.lit_lo = (uint64_t)s.lit_lo;
             d.lit_hi = s.lit_hi;
+            d.lit_len = 0;
+            if (P.cols[d.col].kind == CK_BINARY && s.op != SRB_PRED_IS_NULL && s.op != SRB_PRED_NOT_NULL) {
+                // BinaryColumnPredicateCmpBase (column_predicate_cmp.cpp:559-700): the literal's bytes ride inside the program
+                if (s.lit_len < 0 || s.lit_len > 16 || (s.lit_len && !s.lit_bytes))
+                    throw Error(SRB_NOT_IMPLEMENTED, "string predicate literal longer than 16 bytes");
+                uint8_t raw[16] = {0};
+                if (s.lit_len) memcpy(raw, s.lit_bytes, (size_t)s.lit_len);
+                memcpy(&d.lit_lo, raw, 8);
+                memcpy(&d.lit_hi, raw + 8, 8);
+                d.lit_len = (int32_t)s.lit_len;
+            }
         };
         if (plan.preds[i].or_group == 0) {
             put(plan.preds[i], 0);

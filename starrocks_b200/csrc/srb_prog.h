@@ -53,7 +53,7 @@ struct DPred {
     int32_t col;
     int32_t op;    // SRB_PRED_*
     int32_t group; // 0 = conjunct; otherwise OR-group id (groups are contiguous after lowering)
-    int32_t _pad;
+    int32_t lit_len; // binary columns: bytes of the literal, which sit in (lit_lo, lit_hi) in memory order
     uint64_t lit_lo;
     int64_t lit_hi;
 };

@@ -101,8 +101,34 @@ SRB_D bool cmp_f64(int op, double a, double b) {
     }
 }
 
+// Slice::compare of a BinaryColumn value with a literal of <= 16 bytes: memcmp over the common length, then the lengths
+SRB_D int cmp_bytes(const uint8_t* __restrict__ s, uint32_t n, uint64_t lit_lo, uint64_t lit_hi, uint32_t m) {
+    const uint32_t k = n < m ? n : m;
+    for (uint32_t i = 0; i < k; i++) {
+        const uint8_t b = (uint8_t)((i < 8 ? lit_lo >> (8 * i) : lit_hi >> (8 * (i - 8))) & 0xFF);
+        if (s[i] != b) return s[i] < b ? -1 : 1;
+    }
+    return n == m ? 0 : (n < m ? -1 : 1);
+}
+
 SRB_D bool eval_one_pred(const DProg& p, const DPred& pr, int64_t row) {
     const ColBind& c = p.cols[pr.col];
+    if (c.kind == CK_BINARY) {
+        const bool isnull = c.nulls && c.nulls[row];
+        if (pr.op == 9) return isnull;
+        if (pr.op == 10) return !isnull;
+        if (isnull) return false;
+        const uint32_t b = c.offsets[row], e = c.offsets[row + 1];
+        const int r = cmp_bytes((const uint8_t*)c.data + b, e - b, pr.lit_lo, (uint64_t)pr.lit_hi, (uint32_t)pr.lit_len);
+        switch (pr.op) {
+        case 1: return r == 0;
+        case 2: return r != 0;
+        case 3: return r > 0;
+        case 4: return r >= 0;
+        case 5: return r < 0;
+        default: return r <= 0;
+        }
+    }
     Val v = load_col(c, row);
     if (pr.op == 9) return v.null;
     if (pr.op == 10) return !v.null;

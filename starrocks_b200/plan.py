@@ -66,7 +66,12 @@ class ExprBuilder:
 def pred(slot_id: int, op: int, type_: int, literal=0, or_group: int = 0) -> K.srb_predicate:
     p = K.srb_predicate()
     p.slot_id, p.op, p.type, p.or_group = slot_id, op, type_, or_group
-    if type_ == K.TYPE_DOUBLE:
+    if K.is_binary(type_):  # a string literal: its bytes travel with the predicate (kept alive on the Python object)
+        raw = bytes(literal) if not isinstance(literal, str) else literal.encode()
+        p._keep = C.create_string_buffer(raw, max(1, len(raw)))
+        p.lit_bytes = C.cast(p._keep, C.c_void_p)
+        p.lit_len = len(raw)
+    elif type_ == K.TYPE_DOUBLE:
         import struct
         p.lit_lo = struct.unpack("<q", struct.pack("<d", float(literal)))[0]
         p.lit_hi = 0
@@ -92,6 +97,7 @@ class ScanAggPlan:
                  out_slots: Sequence[int] = (), group_hint: int = 0):
         """aggs: sequence of (fn, Node | None)."""
         self.preds = (K.srb_predicate * max(1, len(preds)))(*preds)
+        self._pred_keep = [getattr(q, "_keep", None) for q in preds]  # string literals stay alive with the plan
         nodes = exprs.nodes if exprs else []
         self.nodes = (K.srb_expr_node * max(1, len(nodes)))(*nodes)
         self.key_nodes = (C.c_int32 * max(1, len(keys)))(*[k.index for k in keys])

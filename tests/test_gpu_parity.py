@@ -228,6 +228,38 @@ def test_predicate_conjunction_and_or_groups(ctx, oracle):
     check(ctx, oracle, plan, ch, device=True)
 
 
+def test_string_predicates(ctx, oracle):
+    # BinaryColumnPredicateCmpBase (storage/column_predicate_cmp.cpp:559-700): every comparison on a VARCHAR column, NULL rows, empty
+    # strings, prefixes, IN lists of strings; the reference's own vectors first (column_predicate_test.cpp:564-660)
+    ids = lambda n: K.Column.from_ints(K.TYPE_INT, np.arange(n, dtype=np.int32))
+    keep = lambda plan, c, **kw: [r[0] for r in K.chunk_rows(run_gpu(ctx, plan, c, **kw), sort=False)]
+    ch = K.Chunk(3, {0: K.Column.from_strings([b"aa", b"ab", b"ac"]), 1: ids(3)})
+    assert keep(ScanAggPlan(preds=[pred(0, K.PRED_EQ, K.TYPE_VARCHAR, b"aa")], out_slots=[1]), ch) == [0]
+    ch = K.Chunk(5, {0: K.Column.from_strings([b"xxx", b"yyy", b"abc", b"", b"abc"], nulls=np.array([0, 0, 0, 1, 0], np.uint8)), 1: ids(5)})
+    assert keep(ScanAggPlan(preds=[pred(0, K.PRED_EQ, K.TYPE_VARCHAR, b"abc")], out_slots=[1]), ch) == [2, 4]
+    rng = np.random.default_rng(16)
+    n = 150_001
+    words = [b"", b"a", b"ab", b"abc", b"abd", b"AUTOMOBILE", b"BUILDING", b"BUILDINGS", b"BUILD", b"MACHINERY", b"zz", b"0123456789abcdef", b"0123456789abcdefX"]
+    vals = [words[i] for i in rng.integers(0, len(words), n)]
+    ch = K.Chunk(n, {0: K.Column.from_strings(vals, nulls=(rng.random(n) < 0.05).astype(np.uint8)), 1: ids(n), 2: _rand_col(rng, K.TYPE_BIGINT, n, 0.0, small=True)})
+    for op in (K.PRED_EQ, K.PRED_NE, K.PRED_LT, K.PRED_LE, K.PRED_GT, K.PRED_GE):
+        for lit in (b"BUILDING", b"", b"abc", b"0123456789abcdef"):
+            plan = ScanAggPlan(preds=[pred(0, op, K.TYPE_VARCHAR, lit)], out_slots=[1, 2])
+            check(ctx, oracle, plan, ch, sort=False)
+    plan = ScanAggPlan(preds=pred_in(0, K.TYPE_VARCHAR, [b"BUILDING", b"zz", b"a"], or_group=1) + [pred(2, K.PRED_GT, K.TYPE_BIGINT, 0), pred(0, K.PRED_NOT_NULL, K.TYPE_VARCHAR)],
+                       out_slots=[1, 2])
+    check(ctx, oracle, plan, ch, sort=False)
+    check(ctx, oracle, plan, ch, sort=False, device=True)
+    check(ctx, oracle, plan, ch, sort=False, piece_rows=4096)
+    e = ExprBuilder()
+    aggp = ScanAggPlan(preds=[pred(0, K.PRED_GE, K.TYPE_VARCHAR, b"BUILD")], exprs=e, keys=[e.slot(0, K.TYPE_VARCHAR)], aggs=[(K.AGG_SUM, e.slot(2, K.TYPE_BIGINT)), (K.AGG_COUNT, None)])
+    check(ctx, oracle, aggp, ch)
+    from starrocks_b200 import ops
+    with pytest.raises(ops.SrbError) as ei:  # literals ride inside the lowered program: at most 16 bytes
+        run_gpu(ctx, ScanAggPlan(preds=[pred(0, K.PRED_EQ, K.TYPE_VARCHAR, b"0123456789abcdefX")], out_slots=[1]), ch)
+    assert ei.value.code == K.NOT_IMPLEMENTED
+
+
 def test_in_list_and_not_in_predicates(ctx, oracle):
     # ColumnInPredicate / ColumnNotInPredicate (storage/column_predicate.h:249-277): IN = OR of EQ, NOT IN = AND of NE; NULL rows never pass
     rng = np.random.default_rng(14)

@@ -46,7 +46,7 @@ def test_struct_sizes_match_the_header():
     # byte-for-byte mirrors of the C PODs
     assert C.sizeof(K.srb_column) == 48
     assert C.sizeof(K.srb_chunk) == 32
-    assert C.sizeof(K.srb_predicate) == 32
+    assert C.sizeof(K.srb_predicate) == 48  # + the string literal (pointer, length)
     assert C.sizeof(K.srb_expr_node) == 48
     assert C.sizeof(K.srb_agg_fn) == 8
     assert C.sizeof(K.srb_config) == 32

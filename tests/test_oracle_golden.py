@@ -604,3 +604,20 @@ def test_joins_against_an_empty_hash_table_like_the_reference(oracle):
     assert rows(K.JOIN_RIGHT_OUTER) == inner + [(None, None, 90)]
     assert rows(K.JOIN_FULL_OUTER) == [(2, 200, 21), (2, 200, 20), (3, 300, None), (1, 100, 10), (None, 700, None), (None, None, 90)]
     assert rows(K.JOIN_RIGHT_SEMI) == [(10,), (20,), (21,)] and rows(K.JOIN_RIGHT_ANTI) == [(90,)]
+
+
+def test_string_predicates_of_the_reference_tests(oracle):
+    # be/test/storage/column_predicate_test.cpp:564-660: col = 'aa' over {aa, ab, ac} -> 1,0,0; nullable col = 'abc' over
+    # {xxx, yyy, abc, NULL, abc} -> 0,0,1,0,1 (a NULL never satisfies a comparison)
+    from starrocks_b200.plan import ScanAggPlan, pred
+    ids = K.Column.from_ints(K.TYPE_INT, np.arange(5, dtype=np.int32))
+    ch = K.Chunk(3, {0: K.Column.from_strings([b"aa", b"ab", b"ac"]), 1: K.Column.from_ints(K.TYPE_INT, np.arange(3, dtype=np.int32))})
+    keep = lambda plan, c: [r[0] for r in K.chunk_rows(oracle.scan_agg(plan, c), sort=False)]
+    assert keep(ScanAggPlan(preds=[pred(0, K.PRED_EQ, K.TYPE_VARCHAR, b"aa")], out_slots=[1]), ch) == [0]
+    ch = K.Chunk(5, {0: K.Column.from_strings([b"xxx", b"yyy", b"abc", b"", b"abc"], nulls=np.array([0, 0, 0, 1, 0], np.uint8)), 1: ids})
+    assert keep(ScanAggPlan(preds=[pred(0, K.PRED_EQ, K.TYPE_VARCHAR, b"abc")], out_slots=[1]), ch) == [2, 4]
+    assert keep(ScanAggPlan(preds=[pred(0, K.PRED_NE, K.TYPE_VARCHAR, b"abc")], out_slots=[1]), ch) == [0, 1]
+    # Slice::compare: memcmp over the common length, then the shorter string is smaller
+    ch = K.Chunk(5, {0: K.Column.from_strings([b"", b"ab", b"abc", b"abd", b"b"]), 1: ids})
+    assert keep(ScanAggPlan(preds=[pred(0, K.PRED_LT, K.TYPE_VARCHAR, b"abc")], out_slots=[1]), ch) == [0, 1]
+    assert keep(ScanAggPlan(preds=[pred(0, K.PRED_GE, K.TYPE_VARCHAR, b"abc")], out_slots=[1]), ch) == [2, 3, 4]
