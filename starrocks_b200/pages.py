@@ -71,6 +71,28 @@ def slice_pages(col: PageColumn, first: int, last: int) -> PageColumn:
     return PageColumn(col.type, col.data, col.nbytes, col.pages[first:last], col.encoding, col.precision, col.scale, col.mem_kind, col.keep)
 
 
+class PageTable:
+    """a table's columns as encoded pages, cut into page sets (row ranges) that are pushed one after the other: what a scan operator is fed
+    instead of a chunk (pipelines accept either)"""
+
+    def __init__(self, columns: Dict[int, PageColumn], pages_per_set: int = 128):
+        self.columns = columns
+        n_pages = len(next(iter(columns.values())).pages)
+        assert all(len(c.pages) == n_pages for c in columns.values()), "the columns' pages must cover the same row ranges"
+        self.sets = [prepare({slot: slice_pages(c, a, min(a + pages_per_set, n_pages)) for slot, c in columns.items()}) for a in range(0, n_pages, pages_per_set)]
+        self.n_rows = next(iter(columns.values())).n_rows()
+        self.nbytes = sum(c.nbytes for c in columns.values())
+
+
+def push_source(op, src):
+    """push a chunk, or every page set of a PageTable, into a scan operator"""
+    if isinstance(src, PageTable):
+        for ps in src.sets:
+            op.push_pages_prepared(ps)
+    else:
+        op.push_chunk(src)
+
+
 # ---- the builder ----------------------------------------------------------------------------------------------------------------
 def _bit_length(x):
     """significant bits of non-negative int64 values (bits() of frame_of_reference_coding.h:50-71)"""

@@ -15,15 +15,16 @@ from __future__ import annotations
 
 from typing import Callable, Dict, Optional
 
-from . import capi as K, ops, queries as Q
+from . import capi as K, ops, pages as PG, queries as Q
 
 SSB_DIM_COLS = {"ssb_customer": ["sc_custkey", "sc_nation_code", "sc_region_code"], "ssb_supplier": ["ss_suppkey", "ss_region_code"],
                 "ssb_part": ["sp_partkey", "sp_mfgr_code"], "ssb_dates": ["sd_datekey", "sd_year"]}
 
 
 def _filter(ctx, plan, chunk):
+    """chunk: a Chunk, or a pages.PageTable (encoded segment pages, decoded on the device in front of the scan)"""
     op = ops.ScanAggOperator(ctx, plan)
-    op.push_chunk(chunk)
+    PG.push_source(op, chunk)
     op.set_finishing()
     return op, op.pull_device()
 
@@ -118,7 +119,7 @@ class TpchQ3:
         self.open.insert(0, fl)  # closed before the filter it reads
         if rf is not None:
             fl.add_runtime_filter(rf, Q.L_ORDERKEY)
-        fl.push_chunk(line)
+        PG.push_source(fl, line)
         fl.set_finishing()
         dl = fl.pull_device()
         if dl is None:
@@ -212,11 +213,11 @@ class SsbQ41:
         """-> the aggregation operator after set_finishing (pull from it); stage_rows (list) collects the rows after each probe"""
         cur = lineorder
         scan = None
-        if self.rfs:  # the lineorder scan: no predicate of its own, three runtime filters
+        if self.rfs or isinstance(lineorder, PG.PageTable):  # the lineorder scan: no predicate of its own, three runtime filters (or just the page decode)
             scan = ops.ScanAggOperator(self.ctx, Q.filter_plan([], [Q.LO_CUSTKEY, Q.LO_PARTKEY, Q.LO_SUPPKEY, Q.LO_ORDERDATE, Q.LO_REVENUE, Q.LO_SUPPLYCOST]))
             for rf, slot in self.rfs:
                 scan.add_runtime_filter(rf, slot)
-            scan.push_chunk(lineorder)
+            PG.push_source(scan, lineorder)
             scan.set_finishing()
             cur = scan.pull_device()
             self.scan_launches = scan.counters()["kernel_launches"]

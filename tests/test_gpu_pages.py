@@ -189,3 +189,40 @@ def test_corrupt_pages_are_reported(ctx, oracle):
         finally:
             op.close()
     assert ei.value.code == K.INVALID_ARGUMENT
+
+
+def _page_table(chunk, page_rows=1 << 12, pages_per_set=5):
+    cols = {slot: torch_page_column(c.type, np.asarray(c.data), page_rows, c.precision, c.scale) for slot, c in chunk.columns.items()}
+    return PG.PageTable(cols, pages_per_set)
+
+
+def test_join_pipelines_fed_from_pages(ctx, oracle):
+    """Q3 and SSB Q4.1 with their fact tables arriving as page tables (several page sets each) instead of chunks: the scan operators decode
+    them on the device (with the runtime filters of the joins applied to the decoded rows); same result as the oracle's operator chain"""
+    from starrocks_b200 import pipelines as P
+    from tests import oracle_chains as OC
+    n_c, n_o, n_l = 6000, 60000, 240000
+    cust = T.host_chunk("customer", 0, n_c, ["c_custkey", "c_mktsegment_code"])
+    orders = T.host_chunk("orders", 0, n_o, ["o_orderkey", "o_custkey", "o_orderdate", "o_shippriority"], n_customers=n_c)
+    line = T.host_chunk("lineitem", 0, n_l, ["l_orderkey", "l_extendedprice", "l_discount", "l_shipdate"])
+    want = K.chunk_rows(OC.q3_oracle(oracle, cust, orders, line))
+    q = P.TpchQ3(ctx)
+    try:
+        got = K.chunk_rows(q.run(cust, _page_table(orders), _page_table(line)).pull_all())
+    finally:
+        q.close()
+    assert got == want and len(got) > 100
+    n_lo, n_cu, n_s, n_p = 300_000, 30_000, 2_000, 200_000
+    kw = dict(n_customers=n_cu, n_suppliers=n_s, n_parts=n_p)
+    dims = {name: T.host_chunk(name, 0, n, P.SSB_DIM_COLS[name]) for name, n in
+            (("ssb_customer", n_cu), ("ssb_supplier", n_s), ("ssb_part", n_p), ("ssb_dates", T.SSB_DAYS))}
+    lo = T.host_chunk("lineorder", 0, n_lo, T.LINEORDER_Q41, **kw)
+    want = K.chunk_rows(OC.ssb_q41_oracle(oracle, dims, lo))
+    for use_rf in (True, False):
+        q = P.SsbQ41(ctx, runtime_filter=use_rf).build(dims)
+        agg = q.probe(_page_table(lo))
+        try:
+            assert K.chunk_rows(agg.pull_all()) == want
+        finally:
+            agg.close()
+            q.close()
