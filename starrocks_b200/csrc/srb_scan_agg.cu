@@ -515,10 +515,30 @@ __global__ void __launch_bounds__(256) k_emit(const __grid_constant__ DProg prog
     const uint64_t chunk = (uint64_t)EMIT_ROWS * 256;
     for (uint64_t c0 = (uint64_t)blockIdx.x * chunk; c0 < cap; c0 += (uint64_t)gridDim.x * chunk) {
         unsigned int ready = 0;
+        // 32-byte slots (k -> sum, count: the high-cardinality plans, ~10^8 of them): the whole slot is fetched with two 16-byte loads per
+        // row, all of a thread's sixteen loads in flight together, and the row is emitted from registers — the table is read once
+        ulonglong2 s0[EMIT_ROWS], s1[EMIT_ROWS];
+        const bool whole = sb == 32;
+        if (whole) {
 #pragma unroll
-        for (int r = 0; r < EMIT_ROWS; r++) {
-            const uint64_t i = c0 + (uint64_t)r * 256 + tid;
-            if (i < cap && ((*(const uint64_t*)(slots + i * sb)) & 3ULL) == SLOT_READY) ready |= 1u << r;
+            for (int r = 0; r < EMIT_ROWS; r++) {
+                const uint64_t i = c0 + (uint64_t)r * 256 + tid;
+                s0[r] = s1[r] = make_ulonglong2(0, 0);
+                if (i < cap) {
+                    const ulonglong2* q = reinterpret_cast<const ulonglong2*>(slots + i * 32);
+                    s0[r] = __ldg(q);
+                    s1[r] = __ldg(q + 1);
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < EMIT_ROWS; r++)
+                if ((s0[r].x & 3ULL) == SLOT_READY) ready |= 1u << r;
+        } else {
+#pragma unroll
+            for (int r = 0; r < EMIT_ROWS; r++) {
+                const uint64_t i = c0 + (uint64_t)r * 256 + tid;
+                if (i < cap && ((*(const uint64_t*)(slots + i * sb)) & 3ULL) == SLOT_READY) ready |= 1u << r;
+            }
         }
         const unsigned int mine = __popc(ready);
         unsigned int incl = mine;
@@ -541,7 +561,14 @@ __global__ void __launch_bounds__(256) k_emit(const __grid_constant__ DProg prog
         int64_t row = row_base + (int64_t)(block_base + warp_tot[wid] + (incl - mine)); // row_base: pass-through rows of a streaming sink come first
 #pragma unroll
         for (int r = 0; r < EMIT_ROWS; r++)
-            if (ready & (1u << r)) emit_row(p, slots + (c0 + (uint64_t)r * 256 + tid) * sb, ea, row++);
+            if (ready & (1u << r)) {
+                if (whole) {
+                    const uint64_t copy[4] = {s0[r].x, s0[r].y, s1[r].x, s1[r].y};
+                    emit_row(p, reinterpret_cast<const uint8_t*>(copy), ea, row++);
+                } else {
+                    emit_row(p, slots + (c0 + (uint64_t)r * 256 + tid) * sb, ea, row++);
+                }
+            }
         __syncthreads(); // warp_tot / block_base are rewritten by the next chunk
     }
 }
@@ -1784,7 +1811,7 @@ private:
 
     // ---- batches ---------------------------------------------------------------------------------------------
     static constexpr int64_t BATCH = (int64_t)1 << 31;     // filter batches: one mask + count pass, one exactly sized growth, one compaction
-    static constexpr int64_t AGG_BATCH = (int64_t)1 << 29; // aggregation batches: the host waits for the counters once per batch
+    static constexpr int64_t AGG_BATCH = (int64_t)1 << 30; // aggregation batches: the host waits for the counters once per batch (a static launch covers <= 2^30 rows)
 
     void process_device_range(const ColBind* cols, int64_t n) {
         if (filter_only_) {
