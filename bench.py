@@ -449,6 +449,9 @@ def merge_plan(query: str, inter, world: int):
     return Q.highcard_merge_plan(group_hint=max(1024, HIGHCARD_KEYS // world))
 
 
+_PLANS = {}
+
+
 def scan_step(env, query: str, w, chunk, marks=None, collect=None, device_result=False, group_hint=None):
     """one pass of the hot path over this rank's shard; at N > 1 it includes the exchange and the phase-2 merge (starrocks_b200/distributed.py:
     gather for the low-cardinality plans, hash shuffle for the high-cardinality one) -> (result chunk or None, result rows on this rank)"""
@@ -463,7 +466,11 @@ def scan_step(env, query: str, w, chunk, marks=None, collect=None, device_result
     mark()
     kw = {} if group_hint is None else {"group_hint": group_hint}
     merged_finish = two_phase and query in ("q1", "q6") and env.gather_device
-    plan = w["plan"](phase=K.AGG_UPDATE_SERIALIZE, **kw) if two_phase and not merged_finish else w["plan"](**kw)
+    # the plan is what the FE hands the BE once per query: built once, not once per step
+    pkey = (query, two_phase and not merged_finish, group_hint)
+    plan = _PLANS.get(pkey)
+    if plan is None:
+        plan = _PLANS[pkey] = w["plan"](phase=K.AGG_UPDATE_SERIALIZE, **kw) if two_phase and not merged_finish else w["plan"](**kw)
     op = ops.ScanAggOperator(ctx, plan)
     op2 = None
     try:
@@ -821,6 +828,8 @@ def bench_q1_variants(env, args, tensors, steps: int, warmup: int):
     out = {}
 
     def run(name, plan_fn, chunk, bytes_per_row):
+        torch.cuda.synchronize()  # the chunk's columns were just written on torch's stream; the library launches on its own
+
         def step():
             op = ops.ScanAggOperator(ctx, plan_fn())
             try:

@@ -55,7 +55,8 @@ typedef int32_t srb_status;
 /* where a column's buffers live */
 #define SRB_MEM_HOST 0   /* pageable host memory (std::vector-backed Buffer<T>, column/vectorized_fwd.h:47) */
 #define SRB_MEM_PINNED 1 /* page-locked host memory */
-#define SRB_MEM_DEVICE 2 /* device memory of the ctx's GPU */
+#define SRB_MEM_DEVICE 2 /* device memory of the ctx's GPU. The library launches on streams of its own: whatever wrote the buffer on another
+                            stream must have completed (stream / device synchronised by the caller) before the chunk is pushed. */
 
 /*
  * One column of a chunk. Layouts are the reference's:
@@ -197,6 +198,9 @@ typedef struct srb_scan_agg_plan {
 #define SRB_JOIN_FULL_OUTER 4  /* both */
 #define SRB_JOIN_RIGHT_SEMI 7  /* build rows with at least one match, build columns only */
 #define SRB_JOIN_RIGHT_ANTI 9  /* build rows without a match, build columns only */
+#define SRB_JOIN_NULL_AWARE_LEFT_ANTI 10 /* NOT IN (join_hash_map.tpp:1356-1383, hash_joiner.h:386-396): like LEFT ANTI, but a NULL probe key
+                                            is not kept, and a NULL key anywhere on a non-empty build side means no row qualifies; against an
+                                            empty build side every probe row is kept. Without other-conjuncts. */
 
 typedef struct srb_join_plan {
     int32_t join_type;

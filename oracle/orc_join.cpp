@@ -147,7 +147,8 @@ static void copy_rows(const srb_column& s, const std::vector<uint32_t>& rows, Ou
 
 static void probe_range(const srb_join_plan* plan, const JoinTable& t, const PackedKeys& pk, int64_t i0, int64_t i1, std::vector<uint32_t>& probe_index,
                         std::vector<uint32_t>& build_index, std::vector<uint8_t>* matched) {
-    const bool anti = plan->join_type == SRB_JOIN_LEFT_ANTI;
+    const bool null_aware = plan->join_type == SRB_JOIN_NULL_AWARE_LEFT_ANTI;
+    const bool anti = plan->join_type == SRB_JOIN_LEFT_ANTI || null_aware;
     const bool keep_left = plan->join_type == SRB_JOIN_LEFT_OUTER || plan->join_type == SRB_JOIN_FULL_OUTER; // unmatched probe rows stay, build index 0
     const bool right_only = plan->join_type == SRB_JOIN_RIGHT_SEMI || plan->join_type == SRB_JOIN_RIGHT_ANTI; // pairs are not emitted
     for (int64_t i = i0; i < i1; i++) {
@@ -172,8 +173,9 @@ static void probe_range(const srb_join_plan* plan, const JoinTable& t, const Pac
         }
         if (pk.null[i]) {
             // lookup_init leaves next[i] = 0 for NULL probe keys: no match. LEFT ANTI emits such rows (join_hash_map.tpp:1380-1420,
-            // "NULLs are not matches and therefore always returned", PlanNodes.thrift:710-713); every other type drops them
-            if (anti) {
+            // "NULLs are not matches and therefore always returned", PlanNodes.thrift:710-713); every other type drops them; the NULL-aware
+            // variant (NOT IN) skips them unless the build side is empty (join_hash_map.tpp:1356-1362, join_hash_map.cpp:676-690)
+            if (anti && !(null_aware && t.row_count > 0)) {
                 probe_index.push_back((uint32_t)i);
                 build_index.push_back(1);
             }
@@ -215,7 +217,10 @@ Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_ch
     PackedKeys pk = pack_keys(*probe, plan->probe_key_slots, plan->n_keys, n_threads);
     if (pk.width != t.keys.width) throw std::runtime_error("join: key width mismatch");
     std::vector<uint32_t> probe_index, build_index; // build_index is 1-based like the reference's
-    const bool anti = plan->join_type == SRB_JOIN_LEFT_ANTI;
+    const bool anti = plan->join_type == SRB_JOIN_LEFT_ANTI || plan->join_type == SRB_JOIN_NULL_AWARE_LEFT_ANTI;
+    bool build_null = false; // NULL-aware LEFT ANTI: a NULL key on a non-empty build side ends the join (hash_joiner.h:386-396)
+    if (plan->join_type == SRB_JOIN_NULL_AWARE_LEFT_ANTI)
+        for (uint8_t x : t.keys.null) build_null = build_null || x != 0;
     const int jt = plan->join_type;
     const bool track_right = jt == SRB_JOIN_RIGHT_OUTER || jt == SRB_JOIN_FULL_OUTER || jt == SRB_JOIN_RIGHT_SEMI || jt == SRB_JOIN_RIGHT_ANTI;
     const bool left_may_miss = jt == SRB_JOIN_RIGHT_OUTER || jt == SRB_JOIN_FULL_OUTER;
@@ -225,7 +230,8 @@ Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_ch
         const int T = std::max(1, n_threads);
         std::vector<std::vector<uint32_t>> pi(T), bi(T);
         std::vector<std::vector<uint8_t>> mt(track_right ? T : 0, std::vector<uint8_t>((size_t)t.row_count + 1, 0));
-        parallel_ranges(probe->n_rows, T, [&](int th, int64_t a, int64_t b) { probe_range(plan, t, pk, a, b, pi[th], bi[th], track_right ? &mt[th] : nullptr); });
+        if (!build_null)
+            parallel_ranges(probe->n_rows, T, [&](int th, int64_t a, int64_t b) { probe_range(plan, t, pk, a, b, pi[th], bi[th], track_right ? &mt[th] : nullptr); });
         if (track_right) {
             matched.assign((size_t)t.row_count + 1, 0);
             for (auto& m : mt)

@@ -337,6 +337,7 @@ __global__ void __launch_bounds__(JT_THREADS) k_join_probe_first(JTable t, const
         for (int j = 0; j < JT_ROWS; j++) {
             const int64_t r = tile * JT_TILE + j * JT_THREADS + threadIdx.x;
             if (anti) m[j] = r < n && m[j] == 0 ? 1u : 0u; // LEFT ANTI keeps exactly the rows without a match (NULL keys never match)
+            if (anti == 2 && m[j] && pnull && pnull[r]) m[j] = 0; // NULL-aware (NOT IN): a NULL probe key is never "not in" a non-empty set
             if (r < n) match[r] = m[j];
             cnt += m[j] ? 1u : 0u;
         }
@@ -350,6 +351,13 @@ __global__ void __launch_bounds__(JT_THREADS) k_join_probe_first(JTable t, const
         }
         __syncthreads();
     }
+}
+
+// does any build row carry a NULL key? (NULL-aware LEFT ANTI: then NOT IN is never true, hash_joiner.h:386-396)
+__global__ void __launch_bounds__(256) k_join_any_null(const uint8_t* __restrict__ nulls, int64_t n, unsigned int* __restrict__ flag) {
+    bool any = false;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) any = any || nulls[i] != 0;
+    if (__any_sync(0xffffffffu, any) && (threadIdx.x & 31) == 0) atomicOr(flag, 1u);
 }
 
 // LEFT ANTI against an empty build side: every probe row is kept
@@ -550,7 +558,7 @@ public:
         if (!p) throw Error(SRB_INVALID_ARGUMENT, "null plan");
         const int jt = p->join_type;
         if (jt != SRB_JOIN_INNER && jt != SRB_JOIN_LEFT_SEMI && jt != SRB_JOIN_LEFT_ANTI && jt != SRB_JOIN_LEFT_OUTER && jt != SRB_JOIN_RIGHT_OUTER &&
-            jt != SRB_JOIN_FULL_OUTER && jt != SRB_JOIN_RIGHT_SEMI && jt != SRB_JOIN_RIGHT_ANTI)
+            jt != SRB_JOIN_FULL_OUTER && jt != SRB_JOIN_RIGHT_SEMI && jt != SRB_JOIN_RIGHT_ANTI && jt != SRB_JOIN_NULL_AWARE_LEFT_ANTI)
             throw Error(SRB_NOT_IMPLEMENTED, fmt("join type %d", p->join_type));
         keep_left_ = jt == SRB_JOIN_LEFT_OUTER || jt == SRB_JOIN_FULL_OUTER;
         track_right_ = jt == SRB_JOIN_RIGHT_OUTER || jt == SRB_JOIN_FULL_OUTER || jt == SRB_JOIN_RIGHT_SEMI || jt == SRB_JOIN_RIGHT_ANTI;
@@ -559,7 +567,8 @@ public:
         if (p->n_keys < 1 || p->n_keys > JMAX_KEYS) throw Error(SRB_NOT_IMPLEMENTED, fmt("join with %d key columns", p->n_keys));
         if (p->n_build_out < 0 || p->n_probe_out < 0 || p->n_build_out + p->n_probe_out > JMAX_OUT)
             throw Error(SRB_NOT_IMPLEMENTED, "too many join output columns");
-        anti_ = p->join_type == SRB_JOIN_LEFT_ANTI;
+        null_aware_ = p->join_type == SRB_JOIN_NULL_AWARE_LEFT_ANTI;
+        anti_ = p->join_type == SRB_JOIN_LEFT_ANTI || null_aware_;
         semi_ = p->join_type == SRB_JOIN_LEFT_SEMI || anti_; // an existence test either way: at most one output row per probe row
         bkeys_.assign(p->build_key_slots, p->build_key_slots + p->n_keys);
         pkeys_.assign(p->probe_key_slots, p->probe_key_slots + p->n_keys);
@@ -691,6 +700,7 @@ public:
             if (i < pkeys_.size()) total += g.width;
         }
         if (n == 0 || (build_rows_ == 0 && !anti_ && !keep_left_)) return;
+        if (null_aware_ && build_rows_ > 0 && build_has_null_) return; // x NOT IN (..., NULL, ...) is never true (hash_joiner.h:386-396)
         if (build_rows_ == 0 && anti_) { // LEFT ANTI against nothing: every probe row
             probe_tiled(n, data, nulls);
             return;
@@ -801,7 +811,7 @@ public:
         toffs_.ensure(ctx, (size_t)tiles * 8);
         uint32_t* match = match_.as<uint32_t>();
         uint32_t* tc = tcounts_.as<uint32_t>();
-        const int anti = anti_ ? 1 : 0;
+        const int anti = anti_ ? (null_aware_ && build_rows_ > 0 ? 2 : 1) : 0;
         if (all_rows) {
             k_join_all_rows<<<grid, JT_THREADS, 0, stream>>>(n, match, tc);
         } else {
@@ -1031,6 +1041,14 @@ private:
             k_join_pack<<<grid_for(n), 256, 0, stream>>>(pa, n, bpacked_.as<uint8_t>(), bnull_.as<uint8_t>());
             k_join_build<<<grid_for(n), 256, 0, stream>>>(table());
             launches += 2;
+            if (null_aware_) {
+                SRB_CUDA(cudaMemsetAsync(total_dev_.p, 0, 8, stream));
+                k_join_any_null<<<grid_for(n), 256, 0, stream>>>(bnull_.as<uint8_t>(), n, total_dev_.as<unsigned int>());
+                SRB_CUDA(cudaMemcpyAsync(total_host_.p, total_dev_.p, 8, cudaMemcpyDeviceToHost, stream));
+                SRB_CUDA(cudaStreamSynchronize(stream));
+                build_has_null_ = *total_host_.as<unsigned int>() != 0;
+                launches++;
+            }
             if (!semi_) { // does any key occur twice? (decides whether INNER probes may take the one-match-per-row path)
                 SRB_CUDA(cudaMemsetAsync(total_dev_.p, 0, 8, stream));
                 k_join_unique<<<grid_for(n), 256, 0, stream>>>(table(), total_dev_.as<unsigned int>());
@@ -1055,6 +1073,7 @@ private:
         return t;
     }
 
+    bool null_aware_ = false, build_has_null_ = false;
     bool anti_ = false, keep_left_ = false, track_right_ = false, right_only_ = false;
     int right_want_ = 0;
     DevBuf matched_; // one byte per build row (1-based): the row matched some probe row (RIGHT / FULL OUTER, RIGHT SEMI / ANTI)

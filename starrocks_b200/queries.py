@@ -9,6 +9,8 @@ Slot ids are this package's own numbering of the synthetic tables (tpch_synth.py
 """
 from __future__ import annotations
 
+import functools
+
 from . import capi as K
 from .plan import ExprBuilder, JoinPlan, ScanAggPlan, pred
 
@@ -134,28 +136,34 @@ Q3_DATE = from_date(1995, 3, 15)
 SEG_BUILDING = 1  # code of 'BUILDING' in tpch_synth.MKTSEGMENTS
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def q3_customer_filter() -> ScanAggPlan:
     return filter_plan([pred(C_MKTSEGMENT_CODE, K.PRED_EQ, K.TYPE_TINYINT, SEG_BUILDING)], [C_CUSTKEY])
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def q3_orders_filter() -> ScanAggPlan:
     return filter_plan([pred(O_ORDERDATE, K.PRED_LT, K.TYPE_DATE, Q3_DATE)], [O_ORDERKEY, O_CUSTKEY, O_ORDERDATE, O_SHIPPRIORITY])
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def q3_lineitem_filter() -> ScanAggPlan:
     return filter_plan([pred(L_SHIPDATE, K.PRED_GT, K.TYPE_DATE, Q3_DATE)], [L_ORDERKEY, L_EXTENDEDPRICE, L_DISCOUNT])
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def q3_join_customer_orders() -> JoinPlan:
     # build: filtered customer; probe: filtered orders; output: the orders columns the next join needs
     return JoinPlan([C_CUSTKEY], [O_CUSTKEY], build_out=[], probe_out=[O_ORDERKEY, O_ORDERDATE, O_SHIPPRIORITY])
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def q3_join_orders_lineitem() -> JoinPlan:
     return JoinPlan([O_ORDERKEY], [L_ORDERKEY], build_out=[O_ORDERDATE, O_SHIPPRIORITY],
                     probe_out=[L_ORDERKEY, L_EXTENDEDPRICE, L_DISCOUNT])
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def q3_agg_plan(group_hint: int = 0) -> ScanAggPlan:
     """group by l_orderkey, o_orderdate, o_shippriority; sum(l_extendedprice * (1 - l_discount))"""
     e = ExprBuilder()
@@ -179,35 +187,43 @@ REGION_AMERICA = 1  # code of 'AMERICA' in tpch_synth.REGIONS
 MFGR_1, MFGR_2 = 0, 1
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def ssb_customer_filter() -> ScanAggPlan:
     return filter_plan([pred(SC_REGION_CODE, K.PRED_EQ, K.TYPE_INT, REGION_AMERICA)], [SC_CUSTKEY, SC_NATION_CODE])
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def ssb_supplier_filter() -> ScanAggPlan:
     return filter_plan([pred(SS_REGION_CODE, K.PRED_EQ, K.TYPE_INT, REGION_AMERICA)], [SS_SUPPKEY])
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def ssb_part_filter() -> ScanAggPlan:
     return filter_plan([pred(SP_MFGR_CODE, K.PRED_EQ, K.TYPE_INT, MFGR_1, or_group=1), pred(SP_MFGR_CODE, K.PRED_EQ, K.TYPE_INT, MFGR_2, or_group=1)],
                        [SP_PARTKEY])
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def ssb_join_supplier() -> JoinPlan:
     return JoinPlan([SS_SUPPKEY], [LO_SUPPKEY], build_out=[], probe_out=[LO_CUSTKEY, LO_PARTKEY, LO_ORDERDATE, LO_REVENUE, LO_SUPPLYCOST])
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def ssb_join_customer() -> JoinPlan:
     return JoinPlan([SC_CUSTKEY], [LO_CUSTKEY], build_out=[SC_NATION_CODE], probe_out=[LO_PARTKEY, LO_ORDERDATE, LO_REVENUE, LO_SUPPLYCOST])
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def ssb_join_part() -> JoinPlan:
     return JoinPlan([SP_PARTKEY], [LO_PARTKEY], build_out=[], probe_out=[SC_NATION_CODE, LO_ORDERDATE, LO_REVENUE, LO_SUPPLYCOST])
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def ssb_join_dates() -> JoinPlan:
     return JoinPlan([SD_DATEKEY], [LO_ORDERDATE], build_out=[SD_YEAR], probe_out=[SC_NATION_CODE, LO_REVENUE, LO_SUPPLYCOST])
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def ssb_q41_agg_plan(phase: int = K.AGG_UPDATE_FINALIZE, group_hint: int = 64) -> ScanAggPlan:
     """group by d_year, c_nation; sum(lo_revenue - lo_supplycost): INT - INT is computed in BIGINT, the sum is BIGINT"""
     e = ExprBuilder()
@@ -218,6 +234,7 @@ def ssb_q41_agg_plan(phase: int = K.AGG_UPDATE_FINALIZE, group_hint: int = 64) -
     return ScanAggPlan(exprs=e, keys=[year, nation], aggs=[(K.AGG_SUM, e.sub(rev, cost, K.TYPE_BIGINT))], phase=phase, group_hint=group_hint)
 
 
+@functools.lru_cache(maxsize=None)  # a plan is immutable once built: the FE hands it over once per query
 def ssb_q41_merge_plan(group_hint: int = 64) -> ScanAggPlan:
     e = ExprBuilder()
     year = e.slot(0, K.TYPE_INT)

@@ -915,8 +915,46 @@ def test_outer_and_right_side_joins(ctx, oracle, jt, ktypes):
         assert sorted(got, key=repr) == want, (jt, device)
 
 
+@pytest.mark.parametrize("build_nulls", [False, True])
+@pytest.mark.parametrize("ktypes", [[K.TYPE_INT], [K.TYPE_BIGINT, K.TYPE_SMALLINT], [K.TYPE_DECIMAL128]])
+def test_null_aware_left_anti_join(ctx, oracle, build_nulls, ktypes):
+    # NOT IN (join_hash_map.tpp:1356-1383, hash_joiner.h:386-396): NULL probe keys are dropped; one NULL key on the build side and nothing
+    # qualifies; plain LEFT ANTI over the same rows keeps the NULL probe keys
+    from starrocks_b200 import ops
+    rng = np.random.default_rng(5)
+    nb, npr = 30_000, 120_000
+
+    def keycols(n, base_slot, span, p_null):
+        cols = {}
+        for i, t in enumerate(ktypes):
+            v = rng.integers(0, span if i == 0 else 3, n)
+            if K.type_width(t) == 16:
+                v = [int(x) * 10**20 for x in v]
+            cols[base_slot + i] = K.Column.from_ints(t, v, (rng.random(n) < p_null).astype(np.uint8), 38 if K.type_width(t) == 16 else 0, 0)
+        return cols
+
+    bcols = keycols(nb, 0, 30_000, 0.001 if build_nulls else 0.0)
+    bcols[8] = K.Column.from_ints(K.TYPE_BIGINT, np.arange(nb))
+    build = K.Chunk(nb, bcols)
+    pcols = keycols(npr, 20, 60_000, 0.05)
+    pcols[28] = K.Column.from_ints(K.TYPE_INT, np.arange(npr, dtype=np.int32))
+    probe = K.Chunk(npr, pcols)
+    nk = len(ktypes)
+    pieces = [ops.slice_chunk(probe, 0, 70_000), ops.slice_chunk(probe, 70_000, npr)]
+    counts = {}
+    for jt in (K.JOIN_NULL_AWARE_LEFT_ANTI, K.JOIN_LEFT_ANTI):
+        plan = JoinPlan(list(range(nk)), list(range(20, 20 + nk)), build_out=[], probe_out=[28, 20], join_type=jt)
+        want = sorted(K.chunk_rows(oracle.join(plan, build, probe), sort=False), key=repr)
+        for device in (False, True):
+            got = run_join_chunks(ctx, plan, build, pieces, device=device)
+            assert sorted(got, key=repr) == want, (jt, device)
+        counts[jt] = len(want)
+    assert counts[K.JOIN_LEFT_ANTI] > 1000
+    assert counts[K.JOIN_NULL_AWARE_LEFT_ANTI] == 0 if build_nulls else 0 < counts[K.JOIN_NULL_AWARE_LEFT_ANTI] < counts[K.JOIN_LEFT_ANTI]
+
+
 @pytest.mark.parametrize("jt,rows", [(K.JOIN_LEFT_OUTER, 5), (K.JOIN_FULL_OUTER, 5), (K.JOIN_LEFT_ANTI, 5), (K.JOIN_INNER, 0), (K.JOIN_LEFT_SEMI, 0),
-                                     (K.JOIN_RIGHT_SEMI, 0), (K.JOIN_RIGHT_OUTER, 0), (K.JOIN_RIGHT_ANTI, 0)])
+                                     (K.JOIN_RIGHT_SEMI, 0), (K.JOIN_RIGHT_OUTER, 0), (K.JOIN_RIGHT_ANTI, 0), (K.JOIN_NULL_AWARE_LEFT_ANTI, 5)])
 def test_joins_against_an_empty_build_side(ctx, oracle, jt, rows):
     # be/test/exec/join_hash_map_test.cpp:2376-2388 EmptyHashMapTest: 5 probe rows against an empty hash table
     build = K.Chunk(0, {0: K.Column.from_ints(K.TYPE_INT, np.zeros(0, np.int32)), 1: K.Column.from_ints(K.TYPE_BIGINT, np.zeros(0, np.int64))})

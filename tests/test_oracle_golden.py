@@ -588,7 +588,7 @@ def test_joins_against_an_empty_hash_table_like_the_reference(oracle):
     build = K.Chunk(0, {0: K.Column.from_ints(K.TYPE_INT, np.zeros(0, np.int32)), 1: K.Column.from_ints(K.TYPE_BIGINT, np.zeros(0, np.int64))})
     probe = K.Chunk(5, {2: K.Column.from_ints(K.TYPE_INT, np.arange(5, dtype=np.int32)), 3: K.Column.from_ints(K.TYPE_BIGINT, np.arange(5))})
     expect = {K.JOIN_LEFT_OUTER: 5, K.JOIN_FULL_OUTER: 5, K.JOIN_LEFT_ANTI: 5, K.JOIN_INNER: 0, K.JOIN_LEFT_SEMI: 0, K.JOIN_RIGHT_SEMI: 0,
-              K.JOIN_RIGHT_OUTER: 0, K.JOIN_RIGHT_ANTI: 0}
+              K.JOIN_RIGHT_OUTER: 0, K.JOIN_RIGHT_ANTI: 0, K.JOIN_NULL_AWARE_LEFT_ANTI: 5}
     for jt, rows in expect.items():
         out = oracle.join(JoinPlan([0], [2], build_out=[1], probe_out=[2, 3], join_type=jt), build, probe)
         assert out.n_rows == rows, jt
@@ -604,6 +604,12 @@ def test_joins_against_an_empty_hash_table_like_the_reference(oracle):
     assert rows(K.JOIN_RIGHT_OUTER) == inner + [(None, None, 90)]
     assert rows(K.JOIN_FULL_OUTER) == [(2, 200, 21), (2, 200, 20), (3, 300, None), (1, 100, 10), (None, 700, None), (None, None, 90)]
     assert rows(K.JOIN_RIGHT_SEMI) == [(10,), (20,), (21,)] and rows(K.JOIN_RIGHT_ANTI) == [(90,)]
+    # NOT IN: LEFT ANTI keeps the NULL probe key, the NULL-aware type sees a NULL on the build side and keeps nothing
+    # (hash_joiner.h:386-396); without that NULL it drops the NULL probe key (join_hash_map.tpp:1356-1383)
+    assert rows(K.JOIN_LEFT_ANTI) == [(3, 300), (None, 700)] and rows(K.JOIN_NULL_AWARE_LEFT_ANTI) == []
+    build = K.Chunk(3, {0: K.Column.from_ints(K.TYPE_INT, np.array([1, 2, 2], np.int32), np.zeros(3, np.uint8)),
+                        1: K.Column.from_ints(K.TYPE_BIGINT, np.array([10, 20, 21]))})
+    assert rows(K.JOIN_LEFT_ANTI) == [(3, 300), (None, 700)] and rows(K.JOIN_NULL_AWARE_LEFT_ANTI) == [(3, 300)]
 
 
 def test_string_predicates_of_the_reference_tests(oracle):
