@@ -253,6 +253,22 @@ srb_status srb_ctx_trim(srb_ctx* ctx);
 /* the CUDA stream an op launches on (cudaStream_t as void*), so harnesses can time with events on it */
 void* srb_op_stream(srb_op* op);
 
+/*
+ * Run-time compiled scan / aggregate kernels. A plan that none of the library's built-in kernel shapes matches is described to the same
+ * kernel template at run time (NVRTC, in the background; the general kernel serves the operator until the compiled one is ready; results are
+ * the same bits either way). The reference picks one of its ahead-of-time template instantiations per plan instead
+ * (exec/aggregate/agg_hash_variant.h, exprs/agg/factory/): there is no reference entry point these replace.
+ *   SRB_JIT = off | async (default) | sync     SRB_JIT_MIN_ROWS (default 4 Mi rows per batch)     SRB_JIT_CACHE_DIR (default ~/.cache/srb_jit)
+ */
+/* blocks until every compilation started so far has finished (benchmarks and tests: the next operator of a compiled shape uses it at once) */
+srb_status srb_jit_wait(void);
+/* process-wide counts: shapes compiled here, loaded from the disk cache, failed (the text of one failure in last_error), still compiling */
+srb_status srb_jit_stats(int64_t* compiled, int64_t* from_disk_cache, int64_t* failed, int64_t* pending, char* last_error, int64_t last_error_len);
+/* lowers `plan` against the column types of `first_chunk` (no data is read), generates its kernel shape and compiles it on the calling thread;
+ * needs no GPU. SRB_OK: `description` says which shape; SRB_NOT_IMPLEMENTED: the plan is outside what the static kernel covers (the general
+ * kernel runs it); SRB_INTERNAL_ERROR: the compiler's log is the error message. */
+srb_status srb_jit_check_plan(const srb_scan_agg_plan* plan, const srb_chunk* first_chunk, char* description, int64_t description_len);
+
 /* ---- operators ----------------------------------------------------------------------------------- */
 /* replaces OlapScan predicate evaluation + Project + AggregateBlockingSink/Source (or the streaming pair)
  * for one driver: be/src/exec/pipeline/scan/olap_chunk_source.cpp:586-624,

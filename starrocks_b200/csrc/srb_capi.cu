@@ -77,6 +77,36 @@ srb_status srb_ctx_trim(srb_ctx* ctx) {
 
 void* srb_op_stream(srb_op* op) { return op ? (void*)op->stream : nullptr; }
 
+srb_status srb_jit_wait(void) {
+    SRB_API_BEGIN
+    srb::jit_wait_all();
+    return SRB_OK;
+    SRB_API_END
+}
+
+srb_status srb_jit_stats(int64_t* compiled, int64_t* from_disk_cache, int64_t* failed, int64_t* pending, char* last_error, int64_t last_error_len) {
+    SRB_API_BEGIN
+    int64_t st[4];
+    std::string err;
+    srb::jit_stats(st, &err);
+    if (compiled) *compiled = st[0];
+    if (from_disk_cache) *from_disk_cache = st[1];
+    if (failed) *failed = st[2];
+    if (pending) *pending = st[3];
+    if (last_error && last_error_len > 0) snprintf(last_error, (size_t)last_error_len, "%s", err.c_str());
+    return SRB_OK;
+    SRB_API_END
+}
+
+srb_status srb_jit_check_plan(const srb_scan_agg_plan* plan, const srb_chunk* first_chunk, char* description, int64_t description_len) {
+    SRB_API_BEGIN
+    std::string d;
+    srb::jit_check_plan(plan, first_chunk, &d);
+    if (description && description_len > 0) snprintf(description, (size_t)description_len, "%s", d.c_str());
+    return SRB_OK;
+    SRB_API_END
+}
+
 srb_status srb_scan_agg_create(srb_ctx* ctx, const srb_scan_agg_plan* plan, srb_op** out) {
     SRB_API_BEGIN
     if (!ctx || !out) throw srb::Error(SRB_INVALID_ARGUMENT, "null argument");

@@ -14,7 +14,25 @@
 // Functions are __host__ __device__ so the host operators (AVG finalize of a handful of groups, bucket sizing)
 // run the very same code; nothing here is a CPU fallback for a kernel.
 #pragma once
+#if defined(__CUDACC_RTC__) // compiled at run time by NVRTC (srb_jit.h): no host headers, the fixed-width types are spelled out
+typedef signed char int8_t;
+typedef short int16_t;
+typedef int int32_t;
+typedef long long int64_t;
+typedef unsigned char uint8_t;
+typedef unsigned short uint16_t;
+typedef unsigned int uint32_t;
+typedef unsigned long long uint64_t;
+typedef unsigned long uintptr_t;
+#define INT32_MIN (-2147483647 - 1)
+#define INT32_MAX 2147483647
+#define INT64_MIN (-9223372036854775807LL - 1)
+#define INT64_MAX 9223372036854775807LL
+#define UINT32_MAX 4294967295U
+#define UINT64_MAX 18446744073709551615ULL
+#else
 #include <cstdint>
+#endif
 
 #if defined(__CUDACC__)
 #define SRB_HD __host__ __device__ __forceinline__
@@ -237,7 +255,13 @@ SRB_HD uint32_t join_key_hash128(uint64_t lo, uint64_t hi, uint32_t num_buckets)
     h = (h << 16) | (h >> 16);
     return h & (num_buckets - 1);
 }
-SRB_HD uint64_t normalize_capacity(uint64_t n) { return n ? (~0ULL >> __builtin_clzll(n)) : 1; }
+SRB_HD uint64_t normalize_capacity(uint64_t n) {
+#if defined(__CUDA_ARCH__)
+    return n ? (~0ULL >> __clzll((long long)n)) : 1;
+#else
+    return n ? (~0ULL >> __builtin_clzll(n)) : 1;
+#endif
+}
 SRB_HD uint32_t calc_bucket_size(uint32_t size) {
     uint64_t expect = (uint64_t)size + (size - 1) / 4;
     if (expect >= (1u << 31)) return 1u << 31;

@@ -385,6 +385,10 @@ namespace srb {
 srb_op* make_scan_agg_op(srb_ctx* ctx, const srb_scan_agg_plan* plan);
 srb_op* make_join_op(srb_ctx* ctx, const srb_join_plan* plan);
 srb_op* make_topn_op(srb_ctx* ctx, const srb_topn_plan* plan);
+// run-time compiled shapes (srb_jit.h; defined in srb_scan_agg.cu, the one translation unit that carries the embedded kernel headers)
+void jit_wait_all();
+void jit_stats(int64_t out[4], std::string* last_error);
+void jit_check_plan(const srb_scan_agg_plan* plan, const srb_chunk* first, std::string* description);
 } // namespace srb
 
 struct srb_comm;

@@ -6,7 +6,6 @@
 // byte offsets inside a group-table slot. Kernels either interpret this program (runtime form) or are instantiated
 // on a compile-time copy of the same structures (static shapes, srb_shapes.cuh) so the interpreter folds away.
 #pragma once
-#include <cstdint>
 
 #include "srb_dev.cuh"
 

@@ -12,7 +12,9 @@
 // Every function is templated on a program accessor P: RuntimeProg reads the DProg the host lowered; a static shape
 // (srb_shapes.cuh) returns compile-time constants from the same accessors so that loops unroll and the switches fold.
 #pragma once
+#if !defined(__CUDACC_RTC__)
 #include <cuda_runtime.h>
+#endif
 
 #include "srb_prog.h"
 

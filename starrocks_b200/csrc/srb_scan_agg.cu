@@ -25,6 +25,7 @@
 #include "srb_lower.h"
 #include "srb_rowpipe.cuh"
 #include "srb_shapes.cuh"
+#include "srb_jit.h"
 #include "srb_radix_agg.cuh"
 #include "srb_pages.cuh"
 #include "srb_stream_policy.h"
@@ -1627,7 +1628,7 @@ public:
         *kernel_ms = kernel_ms_;
         *batches = timed_batches_;
         *static_launches = static_launches_;
-        *shape = shape_;
+        *shape = jit_launches_ ? SHAPE_JIT : shape_;
     }
 
     // all remaining rows as device-resident columns (operator chaining on the GPU)
@@ -1739,7 +1740,12 @@ private:
                     }
         } else {
             init_table();
-            shape_ = match_static_shape(L_.prog);
+            shape_ = getenv("SRB_NO_BUILTIN_SHAPES") ? -1 : match_static_shape(L_.prog); // hook: A/B of a built-in shape against its run-time compiled twin
+            // no built-in shape: can the static kernel be compiled for this plan at run time (srb_jit.h)?
+            if (shape_ < 0 && jit_mode_ && !force_generic_ && jit_shape_of(L_.prog, (int)std::min<int64_t>(plan_.group_hint, 1 << 30), jit_shape_)) {
+                jit_src_ = jit_source(jit_shape_);
+                jit_ = JitCache::get().peek(jit_src_); // an earlier operator of the same shape may have compiled it already
+            }
         }
         lowered_ = true;
     }
@@ -2165,7 +2171,17 @@ private:
             // a recognised shape whose columns arrive with null maps: maps without a set byte are dropped for this batch, so that
             // the static kernel (and the L2-blocked permutation, which moves values but not null maps) can take it
             batch_has_nulls_ = batch_stripped_ = false;
-            if (shape_ >= 0 && !force_generic_) cols = strip_clear_null_maps(cols, off, n);
+            if (!jit_src_.empty() && !jit_failed_) { // a shape compiled at run time: start the compilation at the first large batch, use it once ready
+                if (!jit_ && n >= jit_min_rows_) jit_ = JitCache::get().acquire(jit_src_, jit_mode_ == 2);
+                if (jit_ && !jit_kernel_) {
+                    jit_kernel_ = jit_->get(ctx->cfg.device);
+                    if (!jit_kernel_ && jit_->failed()) {
+                        jit_failed_ = true; // the interpreter serves the operator; the reason is kept for srb_jit_stats / SRB_TRACE
+                        if (getenv("SRB_TRACE")) fprintf(stderr, "[srb] run-time compilation failed: %s\n", jit_->error().c_str());
+                    }
+                }
+            }
+            if ((shape_ >= 0 || jit_kernel_) && !force_generic_) cols = strip_clear_null_maps(cols, off, n);
             tr.mark("  strip null maps");
             batch_partitioned_ = !batch_has_nulls_ && hc_partition_applies(n);
             if (batch_partitioned_) hc_partition(cols, off, n);
@@ -2193,11 +2209,14 @@ private:
         // recognised shapes run the TMA-staged static kernel over the whole tiles; the generic kernel takes the rest
         int64_t covered = 0;
         Counters* dc = ctr_dev_.as<Counters>();
-        if (shape_ >= 0 && !defer_in && !force_generic_) {
-            covered = launch_static_shape(shape_, L_.prog, tv, off, n, dout, &dc->rows_selected, &dc->deferred, &dc->inserted, ctx->n_sms, stream, !no_narrow_);
+        if ((shape_ >= 0 || jit_kernel_) && !defer_in && !force_generic_) {
+            covered = jit_kernel_ ? jit_launch(*jit_kernel_, L_.prog, tv, off, n, dout, &dc->rows_selected, &dc->deferred, &dc->inserted, ctx->n_sms, stream, !no_narrow_)
+                                  : launch_static_shape(shape_, L_.prog, tv, off, n, dout, &dc->rows_selected, &dc->deferred, &dc->inserted, ctx->n_sms, stream,
+                                                        !no_narrow_);
             if (covered) {
                 launches++;
                 static_launches_++;
+                jit_launches_ += jit_kernel_ ? 1 : 0;
             }
         }
         if (covered < n) {
@@ -2768,6 +2787,22 @@ private:
     Lowered L_;
     bool lowered_ = false, filter_only_ = false;
     int shape_ = -1;
+    // the static kernel compiled at run time for this plan (srb_jit.h); SRB_JIT = off | async (default) | sync
+    static constexpr int SHAPE_JIT = 100; // what profile() reports as the shape once such a kernel has run
+    int jit_mode_ = jit_mode_from_env();
+    int64_t jit_min_rows_ = getenv("SRB_JIT_MIN_ROWS") ? atoll(getenv("SRB_JIT_MIN_ROWS")) : ((int64_t)4 << 20);
+    JitShape jit_shape_;
+    std::string jit_src_;
+    std::shared_ptr<JitEntry> jit_;
+    const JitLoaded* jit_kernel_ = nullptr;
+    bool jit_failed_ = false;
+    int64_t jit_launches_ = 0;
+    static int jit_mode_from_env() {
+        const char* m = getenv("SRB_JIT");
+        if (!m || !*m || !strcmp(m, "async") || !strcmp(m, "1")) return 1;
+        if (!strcmp(m, "sync")) return 2;
+        return (!strcmp(m, "off") || !strcmp(m, "0")) ? 0 : 1;
+    }
     bool force_generic_ = getenv("SRB_FORCE_GENERIC") != nullptr; // test hook: compare the two kernel families
     bool no_narrow_ = getenv("SRB_NO_NARROW") != nullptr;         // test / measurement hook: the static kernels' general tile body only
     bool rf_fused_ = getenv("SRB_RF_FUSED") != nullptr;           // opt-in: all runtime filters of a scan in one kernel (k_filter_rf_multi)
@@ -2877,6 +2912,31 @@ void ScanAggOp::device_result_columns(int64_t n) {
         hslots_.push_back(P.n_keys + a);
     }
     SRB_CUDA(cudaStreamSynchronize(stream));
+}
+
+void jit_wait_all() { JitCache::get().wait_all(); }
+void jit_stats(int64_t out[4], std::string* last_error) {
+    JitCache::get().stats(out);
+    if (last_error) *last_error = JitCache::get().last_error();
+}
+// lowers the plan against the first chunk's column types, generates its shape and compiles it (on the calling thread; no GPU needed)
+void jit_check_plan(const srb_scan_agg_plan* plan, const srb_chunk* first, std::string* description) {
+    if (!plan || !first) throw Error(SRB_INVALID_ARGUMENT, "null argument");
+    PlanCopy pc(plan);
+    if (pc.aggs.empty()) throw Error(SRB_NOT_IMPLEMENTED, "filter-only plans have no static kernel");
+    Lowered L = lower_plan(pc, first);
+    JitShape js;
+    if (match_static_shape(L.prog) >= 0) {
+        if (description) *description = std::string("built-in shape: ") + static_shape_name(match_static_shape(L.prog));
+        return;
+    }
+    if (!jit_shape_of(L.prog, (int)std::min<int64_t>(pc.group_hint, 1 << 30), js))
+        throw Error(SRB_NOT_IMPLEMENTED, "the plan is outside what the static kernel covers: the interpreter runs it");
+    std::shared_ptr<JitEntry> e = JitCache::get().acquire(jit_source(js), true);
+    if (e->failed()) throw Error(SRB_INTERNAL_ERROR, e->error());
+    if (description)
+        *description = fmt("compiled shape: %d nodes, %d aggregates, %d keys, directory %d, %d threads x %d rows, cubin %zu bytes, %.0f ms%s", js.n_nodes,
+                           js.n_aggs, js.n_keys, js.gmax, js.threads, js.rows, e->cubin.size(), e->compile_ms, e->from_disk ? " (disk cache)" : "");
 }
 
 srb_op* make_scan_agg_op(srb_ctx* ctx, const srb_scan_agg_plan* plan) {

@@ -20,11 +20,21 @@
 // (exprs/decimal_binary_function.h:47-213), AggHashMap compute_agg_states + update_batch (exec/aggregate/agg_hash_map.h:228-339,
 // exprs/agg/aggregate.h:403-408).
 #pragma once
-#include <utility>
-
 #include "srb_rowpipe.cuh"
 
 namespace srb {
+
+// compile-time index packs (what std::integer_sequence gives; spelled out so that NVRTC needs no host headers)
+template <int... I>
+struct iseq {};
+template <int N, int... I>
+struct make_iseq_impl : make_iseq_impl<N - 1, N - 1, I...> {};
+template <int... I>
+struct make_iseq_impl<0, I...> {
+    typedef iseq<I...> type;
+};
+template <int N>
+using make_iseq = typename make_iseq_impl<N>::type;
 
 struct Counters;
 
@@ -489,7 +499,7 @@ SRB_D void eval_static_node(const DProg& p, Val (&v)[R][S::N_NODES], const uint8
     }
 }
 template <class S, int R, int... I>
-SRB_D void eval_static_all(const DProg& p, Val (&v)[R][S::N_NODES], const uint8_t* stage, int r0, std::integer_sequence<int, I...>) {
+SRB_D void eval_static_all(const DProg& p, Val (&v)[R][S::N_NODES], const uint8_t* stage, int r0, iseq<I...>) {
     (eval_static_node<S, I, R>(p, v, stage, r0), ...);
 }
 
@@ -600,7 +610,7 @@ SRB_D void acc_rare_one(RareAcc<S>& ra, int gid, const Val* v, bool on, const ui
 // spills and NULLs of all R rows. All 32 lanes must call.
 template <class S, int R, int... A>
 SRB_D void acc_update_rows(RareAcc<S>& ra, uint8_t* acc_tid, uint8_t* rows_tid, uint8_t* trash, const Val (&v)[R][S::N_NODES], const bool (&on)[R],
-                           const int (&gid)[R], std::integer_sequence<int, A...>) {
+                           const int (&gid)[R], iseq<A...>) {
     uint64_t dh[R][AccGeom<S>::NR];
     uint64_t any_spill = 0;
     bool any_null = false;
@@ -671,19 +681,6 @@ constexpr bool shape_has_narrow() {
     }
     return true;
 }
-// uniform part of the assumption, checked once on the host: literals in [0, 2^32), casts that do not rescale
-template <class S>
-inline bool narrow_literals_ok(const DProg& p) {
-    constexpr bool has = shape_has_narrow<S>();
-    for (int i = 0; has && i < S::N_NODES; i++) {
-        const SNode nd = S::node(i);
-        const DNode& rt = p.nodes[i];
-        if (nd.op == DOP_LIT && !(rt.lit_hi == 0 && (rt.lit_lo >> 32) == 0)) return false;
-        if (nd.op == DOP_CAST && !(rt.lit_hi == 0 && rt.lit_lo == 1)) return false;
-    }
-    return has;
-}
-
 template <class S, int I, int R>
 SRB_D void eval_narrow_node(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const uint8_t* stage, int r0, uint32_t& esc) {
     constexpr SNode nd = S::node(I);
@@ -724,7 +721,7 @@ SRB_D void eval_narrow_node(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const
     }
 }
 template <class S, int R, int... I>
-SRB_D void eval_narrow_all(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const uint8_t* stage, int r0, uint32_t& esc, std::integer_sequence<int, I...>) {
+SRB_D void eval_narrow_all(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const uint8_t* stage, int r0, uint32_t& esc, iseq<I...>) {
     (eval_narrow_node<S, I, R>(p, nv, stage, r0, esc), ...);
 }
 template <class S>
@@ -797,7 +794,7 @@ static __device__ __noinline__ void acc_narrow_fixup(RareAcc<S>* ra, uint8_t* ac
 }
 template <class S, int R, int... A>
 SRB_D void acc_narrow_rows(RareAcc<S>& ra, uint8_t* acc_tid, uint8_t* rows_tid, uint8_t* trash, const uint64_t (&nv)[R][S::N_NODES], const bool (&on)[R],
-                           const int (&gid)[R], std::integer_sequence<int, A...>) {
+                           const int (&gid)[R], iseq<A...>) {
     uint32_t flag = 0;
 #pragma unroll
     for (int j = 0; j < R; j++) {
@@ -863,7 +860,7 @@ struct Flusher {
     // step 1, whole warps: group q of this warp's lanes -> stash
     template <int... A>
     static __device__ __forceinline__ void stash(const RareAcc<S>& ra, const uint8_t* acc_tid, const uint8_t* rows_tid, int q, uint64_t* stash_base,
-                                                 std::integer_sequence<int, A...>) {
+                                                 iseq<A...>) {
         uint64_t* st = stash_base + (size_t)((threadIdx.x >> 5) * G + q) * WORDS;
         const uint64_t rows = warp_sum_u64(*(const uint32_t*)(rows_tid + (size_t)q * (S::THREADS * 4)));
         if ((threadIdx.x & 31) == 0) st[3 * NR] = rows;
@@ -886,7 +883,7 @@ struct Flusher {
     }
     // step 2, one thread: totals of group q over the warps -> table slot
     template <int... A>
-    static __device__ __forceinline__ void fold(const DProg& p, const uint64_t* stash_base, int q, uint8_t* slot, std::integer_sequence<int, A...>) {
+    static __device__ __forceinline__ void fold(const DProg& p, const uint64_t* stash_base, int q, uint8_t* slot, iseq<A...>) {
         uint64_t tot[WORDS];
 #pragma unroll
         for (int k = 0; k < WORDS; k++) tot[k] = 0;
@@ -926,7 +923,7 @@ SRB_D void row_update_global_one(const DProg& p, uint8_t* slot, const Val* v) {
     }
 }
 template <class S, int... A>
-SRB_D void row_update_global(const DProg& p, uint8_t* slot, const Val* v, std::integer_sequence<int, A...>) {
+SRB_D void row_update_global(const DProg& p, uint8_t* slot, const Val* v, iseq<A...>) {
     (row_update_global_one<S, A>(p, slot, v), ...);
 }
 
@@ -1028,7 +1025,7 @@ struct AggArgs {
     uint32_t nulls; // bit a: the argument of aggregate a is NULL
 };
 template <class S, int... A>
-SRB_D AggArgs<S> pack_agg_args(const Val* v, std::integer_sequence<int, A...>) {
+SRB_D AggArgs<S> pack_agg_args(const Val* v, iseq<A...>) {
     AggArgs<S> r;
     r.nulls = 0;
     ((r.lo[A] = S::agg(A).arg >= 0 ? v[S::agg(A).arg < 0 ? 0 : S::agg(A).arg].lo : 0,
@@ -1053,7 +1050,7 @@ SRB_D void row_update_args_one(const DProg& p, uint8_t* slot, const AggArgs<S>& 
 }
 template <class S, int... A>
 static __device__ __noinline__ int global_row_cold(const DProg* pp, uint8_t* slots, uint64_t mask, int slot_bytes, int key_words, uint64_t klo, uint64_t khi,
-                                                   AggArgs<S> x, std::integer_sequence<int, A...>) {
+                                                   AggArgs<S> x, iseq<A...>) {
     const TableView tv{slots, mask, slot_bytes, key_words};
     const PackedKey k{klo, khi, static_key_bytes<S>(), false};
     bool fresh;
@@ -1082,8 +1079,8 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
     __shared__ uint64_t full_bar[ST_MAX_STAGES], empty_bar[ST_MAX_STAGES];
     __shared__ GroupDir<G> dir;
     const DProg& p = prog;
-    using NodeSeq = std::make_integer_sequence<int, S::N_NODES>;
-    using AggSeq = std::make_integer_sequence<int, S::N_AGGS>;
+    using NodeSeq = make_iseq<S::N_NODES>;
+    using AggSeq = make_iseq<S::N_AGGS>;
 
     const int stage_bytes = sa.stage_bytes, n_stages = sa.n_stages;
     const int tid = threadIdx.x;
@@ -1322,6 +1319,31 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
 }
 
 
+// What the host must know about a shape to lay out a stage and launch its kernel. Built-in shapes fill it from their templates; a shape
+// compiled at run time (srb_jit.h) exports the same struct as a device constant of its module, so the two can never disagree.
+struct ShapeMeta {
+    int32_t n_nodes, threads, rows, tile, acc_bytes, has_narrow, gmax, _pad;
+    int32_t load_width[MAX_NODES]; // bytes of the column a LOAD node reads, 0 for every other node
+    int32_t load_off[MAX_NODES];   // its offset inside a stage
+};
+template <class S>
+constexpr ShapeMeta shape_meta() {
+    ShapeMeta m{};
+    m.n_nodes = S::N_NODES;
+    m.threads = S::THREADS;
+    m.rows = S::ROWS;
+    m.tile = tile_rows<S>();
+    m.acc_bytes = AccGeom<S>::BYTES;
+    m.has_narrow = shape_has_narrow<S>() ? 1 : 0;
+    m.gmax = S::GMAX;
+    for (int i = 0; i < S::N_NODES; i++) {
+        m.load_width[i] = S::node(i).op == DOP_LOAD ? S::node(i).width : 0;
+        m.load_off[i] = load_off<S>(i);
+    }
+    return m;
+}
+
+#if !defined(__CUDACC_RTC__) // host side: shape registry, predicate lowering, launch
 // ---- registry ---------------------------------------------------------------------------------------------------------------
 inline int match_static_shape(const DProg& p) {
     if (shape_matches<ShapeSumMulFast>(p)) return 0;
@@ -1412,35 +1434,44 @@ inline bool lower_ranges(const DProg& p, StaticArgs& sa) {
     return true;
 }
 
-template <class S>
-inline int64_t launch_shape(const DProg& p, const TableView& tv, int64_t base, int64_t n, uint32_t* defer_out, unsigned long long* rows_selected,
-                            unsigned long long* deferred, unsigned long long* inserted, int n_sms, cudaStream_t stream, bool allow_narrow) {
-    constexpr int TILE = tile_rows<S>();
-    StaticArgs sa{};
-    // stage layout: the columns of the LOAD nodes first, in node order (compile-time offsets), then predicate-only columns
+// uniform part of the narrow body's assumption, checked once on the host: literals in [0, 2^32), casts that do not rescale (the program's
+// nodes are the shape's nodes: shape_matches / the generator guarantee it)
+inline bool narrow_literals_ok_rt(const ShapeMeta& m, const DProg& p) {
+    if (!m.has_narrow) return false;
+    for (int i = 0; i < p.n_nodes; i++) {
+        const DNode& rt = p.nodes[i];
+        if (rt.op == DOP_LIT && !(rt.lit_hi == 0 && (rt.lit_lo >> 32) == 0)) return false;
+        if (rt.op == DOP_CAST && !(rt.lit_hi == 0 && rt.lit_lo == 1)) return false;
+    }
+    return true;
+}
+
+// Stage layout and kernel arguments of one launch of a static kernel over the leading whole tiles of [base, base+n): the number of tiles,
+// 0 when the preconditions (no null maps, 16-byte aligned columns, every column bound once, two stages beside the accumulators) do not hold.
+inline int64_t prepare_static(const ShapeMeta& m, const DProg& p, int64_t base, int64_t n, bool allow_narrow, StaticArgs& sa, size_t& smem) {
+    // the columns of the LOAD nodes first, in node order (compile-time offsets), then predicate-only columns
     bool placed[MAX_COLS] = {};
     int bytes = 0;
-    for (int i = 0; i < S::N_NODES; i++) {
-        if (S::node(i).op != DOP_LOAD) continue;
+    for (int i = 0; i < m.n_nodes; i++) {
+        if (!m.load_width[i]) continue;
         const int c = p.nodes[i].col;
-        if (c < 0 || c >= p.n_cols || placed[c] || p.cols[c].width != S::node(i).width) return 0; // a column bound twice: generic kernel
+        if (c < 0 || c >= p.n_cols || placed[c] || p.cols[c].width != m.load_width[i]) return 0; // a column bound twice: generic kernel
         placed[c] = true;
-        sa.col_off[c] = load_off<S>(i);
-        bytes = load_off<S>(i) + S::node(i).width * TILE;
+        sa.col_off[c] = m.load_off[i];
+        bytes = m.load_off[i] + m.load_width[i] * m.tile;
     }
     for (int c = 0; c < p.n_cols; c++) {
         if (!placed[c]) {
             sa.col_off[c] = bytes;
-            bytes += p.cols[c].width * TILE;
+            bytes += p.cols[c].width * m.tile;
         }
         // TMA bulk copies need 16-byte aligned sources: tile starts are multiples of 1024 rows, so the base pointers decide
         if (p.cols[c].nulls || (((uintptr_t)p.cols[c].data + (size_t)base * p.cols[c].width) & 15)) return 0;
     }
-    const int64_t n_tiles = n / TILE;
+    const int64_t n_tiles = n / m.tile;
     if (n_tiles == 0 || bytes == 0) return 0;
     sa.stage_bytes = bytes;
-    const int acc_bytes = AccGeom<S>::BYTES;
-    int stages = (ST_SMEM_BUDGET - acc_bytes) / sa.stage_bytes;
+    int stages = (ST_SMEM_BUDGET - m.acc_bytes) / sa.stage_bytes;
     if (stages > ST_MAX_STAGES) stages = ST_MAX_STAGES;
     if (stages < 2) return 0;
     sa.n_stages = stages;
@@ -1451,14 +1482,25 @@ inline int64_t launch_shape(const DProg& p, const TableView& tv, int64_t base, i
         sa.preds[i] = SPred{sa.col_off[d.col], p.cols[d.col].width, pred_opmask(d.op), d.group, d.lit_lo, d.lit_hi};
     }
     if (!lower_ranges(p, sa)) sa.n_ranges = -1;
-    sa.narrow_ok = (allow_narrow && narrow_literals_ok<S>(p)) ? 1 : 0; // allow_narrow = 0: A/B runs and tests of the general body (SRB_NO_NARROW)
-    const size_t smem = (size_t)sa.acc_off + acc_bytes;
+    sa.narrow_ok = (allow_narrow && narrow_literals_ok_rt(m, p)) ? 1 : 0; // allow_narrow = 0: A/B runs and tests of the general body (SRB_NO_NARROW)
+    smem = (size_t)sa.acc_off + m.acc_bytes;
+    return n_tiles;
+}
+
+template <class S>
+inline int64_t launch_shape(const DProg& p, const TableView& tv, int64_t base, int64_t n, uint32_t* defer_out, unsigned long long* rows_selected,
+                            unsigned long long* deferred, unsigned long long* inserted, int n_sms, cudaStream_t stream, bool allow_narrow) {
+    constexpr ShapeMeta m = shape_meta<S>();
+    StaticArgs sa{};
+    size_t smem = 0;
+    const int64_t n_tiles = prepare_static(m, p, base, n, allow_narrow, sa, smem);
+    if (n_tiles == 0) return 0;
     static SmemOptIn opt_in; // per (shape, device)
     opt_in.set(k_scan_agg_static<S>, ST_SMEM_BUDGET);
     const int grid = (int)(n_tiles < n_sms ? n_tiles : n_sms);
     StaticCtr ctr{rows_selected, deferred, inserted};
     k_scan_agg_static<S><<<grid, S::THREADS + 32, smem, stream>>>(p, sa, tv, base, n_tiles, defer_out, ctr);
-    return n_tiles * TILE;
+    return n_tiles * m.tile;
 }
 
 
@@ -1477,5 +1519,6 @@ inline int64_t launch_static_shape(int shape, const DProg& p, const TableView& t
     }
     return 0;
 }
+#endif // !__CUDACC_RTC__
 
 } // namespace srb

@@ -20,7 +20,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libsrb.so"
 _lib = None
 
 EXPORTS = [
-    "srb_ctx_create", "srb_ctx_destroy", "srb_last_error", "srb_ctx_device_info", "srb_ctx_trim", "srb_op_stream",
+    "srb_ctx_create", "srb_ctx_destroy", "srb_last_error", "srb_ctx_device_info", "srb_ctx_trim", "srb_op_stream", "srb_jit_wait", "srb_jit_stats", "srb_jit_check_plan",
     "srb_scan_agg_create", "srb_join_create", "srb_op_push_chunk", "srb_op_push_pages", "srb_op_set_finishing_merged", "srb_op_set_finishing", "srb_op_has_output",
     "srb_op_need_input", "srb_op_is_finished", "srb_op_pull_chunk", "srb_op_pull_all", "srb_op_pull_device",
     "srb_op_cancel", "srb_op_close", "srb_op_sync", "srb_op_counters", "srb_op_profile",
@@ -57,6 +57,9 @@ def lib() -> C.CDLL:
     L.srb_ctx_trim.argtypes = [vp]
     L.srb_op_stream.argtypes = [vp]
     L.srb_op_stream.restype = vp
+    L.srb_jit_wait.argtypes = []
+    L.srb_jit_stats.argtypes = [C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), C.c_char_p, i64]
+    L.srb_jit_check_plan.argtypes = [C.POINTER(K.srb_scan_agg_plan), C.POINTER(K.srb_chunk), C.c_char_p, i64]
     L.srb_scan_agg_create.argtypes = [vp, C.POINTER(K.srb_scan_agg_plan), C.POINTER(vp)]
     L.srb_join_create.argtypes = [vp, C.POINTER(K.srb_join_plan), C.POINTER(vp)]
     L.srb_topn_create.argtypes = [vp, C.POINTER(K.srb_topn_plan), C.POINTER(vp)]
@@ -118,6 +121,28 @@ def _check(st: int):
     if st not in (K.OK, K.END_OF_FILE):
         raise SrbError(st, lib().srb_last_error().decode())
     return st
+
+
+def jit_wait():
+    """blocks until every run-time kernel compilation started so far has finished (srb_jit_wait)"""
+    _check(lib().srb_jit_wait())
+
+
+def jit_stats() -> dict:
+    """process-wide counts of run-time compiled kernel shapes (srb_jit_stats)"""
+    v = [C.c_int64() for _ in range(4)]
+    err = C.create_string_buffer(4096)
+    _check(lib().srb_jit_stats(*[C.byref(x) for x in v], err, len(err)))
+    return {"compiled": v[0].value, "from_disk_cache": v[1].value, "failed": v[2].value, "pending": v[3].value, "last_error": err.value.decode(errors="replace")}
+
+
+def jit_check_plan(plan, first_chunk: K.Chunk) -> str:
+    """compiles the kernel shape of `plan` for chunks typed like `first_chunk` on the calling thread (no GPU needed); returns its description,
+    raises SrbError NOT_IMPLEMENTED when the plan is outside what the static kernel covers (srb_jit_check_plan)"""
+    cch, keep = first_chunk.to_c()
+    out = C.create_string_buffer(512)
+    _check(lib().srb_jit_check_plan(C.byref(plan.c), C.byref(cch), out, len(out)))
+    return out.value.decode()
 
 
 class Context:

@@ -1,0 +1,224 @@
+"""Run-time compiled kernel shapes (csrc/srb_jit.h): a plan that no built-in shape matches gets the static TMA-staged kernel compiled for it.
+
+CPU part (no GPU needed: NVRTC cross-compiles): the generator + compiler accept the plan families below and reject what the static kernel
+does not cover. GPU part: the compiled kernel's results through the C ABI against the oracle, bit for bit, with the operator's profile
+confirming that the compiled kernel (not the interpreter) did the work."""
+import os
+
+import numpy as np
+import pytest
+
+from starrocks_b200 import capi as K
+from starrocks_b200 import queries as Q
+from starrocks_b200 import tpch_synth as T
+from starrocks_b200.plan import ExprBuilder, ScanAggPlan, pred
+
+D64, D128 = K.TYPE_DECIMAL64, K.TYPE_DECIMAL128
+SHAPE_JIT = 100
+
+
+def lineitem_plan(n_keys=2, hint=4, extra=True, phase=K.AGG_UPDATE_FINALIZE, charge=False, preds=True):
+    """a Q1-like plan that is NOT one of the built-in shapes: other aggregates, other key lists, other cardinality estimates"""
+    e = ExprBuilder()
+    qty = e.slot(Q.L_QUANTITY, D64, 15, 2)
+    ext = e.slot(Q.L_EXTENDEDPRICE, D64, 15, 2)
+    disc = e.slot(Q.L_DISCOUNT, D64, 15, 2)
+    tax = e.slot(Q.L_TAX, D64, 15, 2)
+    keys = [e.slot(Q.L_RETURNFLAG_CODE, K.TYPE_INT), e.slot(Q.L_LINESTATUS_CODE, K.TYPE_INT)][:n_keys]
+    one = e.lit(100, D64, 16, 2)
+    omd = e.sub(one, disc, D64, 16)
+    dp = e.mul(e.cast(ext, D128, 15, 2), e.cast(omd, D128, 16, 2), D128, 31)
+    aggs = [(K.AGG_SUM, qty), (K.AGG_SUM, dp), (K.AGG_AVG, disc), (K.AGG_COUNT, None)]
+    if charge:
+        opt = e.add(one, tax, D64, 16)
+        aggs.append((K.AGG_SUM, e.mul(dp, e.cast(opt, D128, 16, 2), D128, 38)))
+    if extra:
+        aggs += [(K.AGG_SUM, tax), (K.AGG_COUNT, tax)]
+    ps = [pred(Q.L_SHIPDATE, K.PRED_LE, K.TYPE_DATE, Q.from_date(1998, 9, 2))] if preds else []
+    return ScanAggPlan(preds=ps, exprs=e, keys=keys, aggs=aggs, phase=phase, group_hint=hint)
+
+
+def orderkey_plan(hint):
+    """GROUP BY l_orderkey (INT): SUM(l_extendedprice), COUNT(*), AVG(l_discount) — many groups"""
+    e = ExprBuilder()
+    k = e.slot(Q.L_ORDERKEY, K.TYPE_INT)
+    ext = e.slot(Q.L_EXTENDEDPRICE, D64, 15, 2)
+    disc = e.slot(Q.L_DISCOUNT, D64, 15, 2)
+    return ScanAggPlan(preds=[], exprs=e, keys=[k], aggs=[(K.AGG_SUM, ext), (K.AGG_COUNT, None), (K.AGG_AVG, disc)], group_hint=hint)
+
+
+PLANS = {
+    "two keys, six aggregates": (lambda: lineitem_plan(), T.LINEITEM_Q1),
+    "no group by": (lambda: lineitem_plan(n_keys=0), T.LINEITEM_Q1),
+    "one key": (lambda: lineitem_plan(n_keys=1, extra=False), T.LINEITEM_Q1),
+    "directory of 16": (lambda: lineitem_plan(hint=12), T.LINEITEM_Q1),
+    "serialize phase": (lambda: lineitem_plan(phase=K.AGG_UPDATE_SERIALIZE), T.LINEITEM_Q1),
+    "checked product": (lambda: lineitem_plan(charge=True, extra=False), T.LINEITEM_Q1),
+    "no predicate": (lambda: lineitem_plan(preds=False), T.LINEITEM_Q1),
+    "many groups": (lambda: orderkey_plan(100_000), ["l_orderkey", "l_extendedprice", "l_discount"]),
+    "unknown cardinality": (lambda: orderkey_plan(0), ["l_orderkey", "l_extendedprice", "l_discount"]),
+}
+
+
+# ---- CPU: generator + NVRTC ------------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def no_disk_cache(tmp_path_factory):
+    old = os.environ.get("SRB_JIT_CACHE_DIR")
+    os.environ["SRB_JIT_CACHE_DIR"] = str(tmp_path_factory.mktemp("srb_jit"))
+    yield os.environ["SRB_JIT_CACHE_DIR"]
+    if old is None:
+        os.environ.pop("SRB_JIT_CACHE_DIR")
+    else:
+        os.environ["SRB_JIT_CACHE_DIR"] = old
+
+
+@pytest.mark.parametrize("name", ["two keys, six aggregates", "no group by", "many groups"])
+def test_generated_shapes_compile_without_a_gpu(no_disk_cache, name):
+    from starrocks_b200 import ops
+    plan_fn, cols = PLANS[name]
+    first = T.host_chunk("lineitem", 0, 16, cols)
+    d = ops.jit_check_plan(plan_fn(), first)
+    assert d.startswith("compiled shape"), d
+    st = ops.jit_stats()
+    assert st["failed"] == 0 and st["pending"] == 0, st
+
+
+def test_builtin_shapes_are_recognised_and_uncovered_plans_are_refused(no_disk_cache):
+    from starrocks_b200 import ops
+    first = T.host_chunk("lineitem", 0, 16, T.LINEITEM_Q1)
+    assert ops.jit_check_plan(Q.q1_plan(), first).startswith("built-in shape")
+    with pytest.raises(ops.SrbError) as ex:  # MIN / MAX: the interpreter's
+        ops.jit_check_plan(Q.q1_plan(with_min_max=True), first)
+    assert ex.value.code == K.NOT_IMPLEMENTED
+
+
+def test_compiled_shapes_are_cached_on_disk(no_disk_cache):
+    from starrocks_b200 import ops
+    first = T.host_chunk("lineitem", 0, 16, T.LINEITEM_Q1)
+    ops.jit_check_plan(lineitem_plan(hint=7), first)
+    files = [f for f in os.listdir(no_disk_cache) if f.endswith(".cubin")]
+    assert files and all(os.path.getsize(os.path.join(no_disk_cache, f)) > 10_000 for f in files)
+
+
+# ---- GPU: parity of the compiled kernels ---------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def ctx():
+    from starrocks_b200 import ops
+    c = ops.Context(device=0, chunk_size=4096)
+    yield c
+    c.close()
+
+
+@pytest.fixture()
+def jit_sync():
+    keep = {k: os.environ.get(k) for k in ("SRB_JIT", "SRB_JIT_MIN_ROWS")}
+    os.environ["SRB_JIT"] = "sync"
+    os.environ["SRB_JIT_MIN_ROWS"] = "0"
+    yield
+    for k, v in keep.items():
+        if v is None:
+            os.environ.pop(k, None)
+        else:
+            os.environ[k] = v
+
+
+def run_device(ctx, plan, chunk):
+    """-> (result chunk, profile of the operator)"""
+    from starrocks_b200 import ops
+    dch, ptrs = ctx.device_chunk(chunk)
+    op = ops.ScanAggOperator(ctx, plan)
+    try:
+        op.push_chunk(dch)
+        op.set_finishing()
+        return op.pull_all(), op.profile()
+    finally:
+        op.close()
+        for p in ptrs:
+            ctx.device_free(p)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(PLANS))
+def test_compiled_shape_matches_the_oracle(ctx, oracle, jit_sync, name):
+    plan_fn, cols = PLANS[name]
+    n = 700_001  # whole tiles through the compiled kernel, the ragged tail through the interpreter
+    chunk = T.host_chunk("lineitem", 0, n, cols)
+    want = K.chunk_rows(oracle.scan_agg(plan_fn(), chunk))
+    got, prof = run_device(ctx, plan_fn(), chunk)
+    assert prof["shape"] == SHAPE_JIT and prof["static_launches"] >= 1, prof
+    assert K.chunk_rows(got) == want
+    assert len(want) >= 1
+
+
+@pytest.mark.gpu
+def test_compiled_twin_of_a_builtin_shape_gives_the_same_rows(ctx, oracle, jit_sync):
+    # SRB_NO_BUILTIN_SHAPES: Q1 itself goes through the generator -> the same kernel source as the built-in ShapeQ1Dict
+    chunk = T.host_chunk("lineitem", 0, 500_000, T.LINEITEM_Q1)
+    want = K.chunk_rows(oracle.scan_agg(Q.q1_plan(), chunk))
+    os.environ["SRB_NO_BUILTIN_SHAPES"] = "1"
+    try:
+        got, prof = run_device(ctx, Q.q1_plan(), chunk)
+    finally:
+        os.environ.pop("SRB_NO_BUILTIN_SHAPES")
+    assert prof["shape"] == SHAPE_JIT, prof
+    assert K.chunk_rows(got) == want
+    got, prof = run_device(ctx, Q.q1_plan(), chunk)
+    assert prof["shape"] == 1 and K.chunk_rows(got) == want
+
+
+@pytest.mark.gpu
+def test_asynchronous_compilation_serves_the_first_operator_from_the_interpreter(ctx, oracle):
+    from starrocks_b200 import ops
+    keep = {k: os.environ.get(k) for k in ("SRB_JIT", "SRB_JIT_MIN_ROWS")}
+    os.environ["SRB_JIT"] = "async"
+    os.environ["SRB_JIT_MIN_ROWS"] = "0"
+    try:
+        plan_fn = lambda: lineitem_plan(hint=3, extra=False)  # a shape no other test compiles
+        chunk = T.host_chunk("lineitem", 0, 300_000, T.LINEITEM_Q1)
+        want = K.chunk_rows(oracle.scan_agg(plan_fn(), chunk))
+        got, prof = run_device(ctx, plan_fn(), chunk)  # compilation starts; this operator is (almost certainly) served by the interpreter
+        assert K.chunk_rows(got) == want
+        ops.jit_wait()
+        st = ops.jit_stats()
+        assert st["pending"] == 0 and st["failed"] == 0, st
+        got, prof = run_device(ctx, plan_fn(), chunk)
+        assert prof["shape"] == SHAPE_JIT and K.chunk_rows(got) == want
+    finally:
+        for k, v in keep.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+@pytest.mark.gpu
+def test_compiled_shape_with_null_maps_and_many_chunks(ctx, oracle, jit_sync):
+    # null maps without a set byte are stripped per batch (the compiled kernel takes it); a batch whose maps hold NULLs goes to the interpreter;
+    # both update the same table
+    from starrocks_b200 import ops
+    n = 400_000
+    chunk = T.host_chunk("lineitem", 0, n, T.LINEITEM_Q1)
+    clean = K.Chunk(n, dict(chunk.columns))
+    c = chunk.columns[Q.L_TAX]
+    clean.columns[Q.L_TAX] = K.Column(c.type, c.data, np.zeros(n, np.uint8), None, c.precision, c.scale)
+    dirty = K.Chunk(n, dict(chunk.columns))
+    nm = (np.arange(n) % 97 == 0).astype(np.uint8)
+    dirty.columns[Q.L_TAX] = K.Column(c.type, c.data, nm, None, c.precision, c.scale)
+    plan_fn = lambda: lineitem_plan()
+    from starrocks_b200 import distributed as D
+    both = D.concat_chunks([clean, dirty])
+    want = K.chunk_rows(oracle.scan_agg(plan_fn(), both))
+    d1, p1 = ctx.device_chunk(clean)
+    d2, p2 = ctx.device_chunk(dirty)
+    op = ops.ScanAggOperator(ctx, plan_fn())
+    try:
+        op.push_chunk(d1)
+        op.push_chunk(d2)
+        op.set_finishing()
+        got = op.pull_all()
+        prof = op.profile()
+    finally:
+        op.close()
+        for p in p1 + p2:
+            ctx.device_free(p)
+    assert prof["shape"] == SHAPE_JIT and K.chunk_rows(got) == want
