@@ -45,14 +45,48 @@ struct JitShape {
     SKey keys[MAX_KEYS];
 };
 
-// accumulator planes of the low-cardinality path: one per distinct SUM / AVG argument (agg_rep / n_reps of srb_shapes.cuh, at run time)
+// node_can_be_null / plane_kind / n_reps of srb_shapes.cuh, at run time (the geometry must be chosen before anything is compiled)
+inline bool jit_node_can_be_null(const JitShape& js, int n) {
+    if (n < 0) return false;
+    const SNode& nd = js.nodes[n];
+    if (nd.op == DOP_LOAD) return nd.nullable != 0;
+    if (nd.op == DOP_LIT) return false;
+    if (nd.checked) return true;
+    return jit_node_can_be_null(js, nd.lhs) || jit_node_can_be_null(js, nd.rhs);
+}
+inline int jit_plane_kind(const JitShape& js, int a) {
+    const SAgg& g = js.aggs[a];
+    if (g.fn == FN_SUM || g.fn == FN_AVG) return 1;
+    if (g.fn == FN_COUNT) return (g.merge == 0 && g.arg >= 0 && jit_node_can_be_null(js, g.arg)) ? 1 : 0;
+    return 2;
+}
 inline int jit_n_reps(const JitShape& js) {
     int n = 0;
     for (int a = 0; a < js.n_aggs; a++) {
-        if (js.aggs[a].fn != FN_SUM && js.aggs[a].fn != FN_AVG) continue;
+        const int kind = jit_plane_kind(js, a);
+        if (kind == 0) continue;
         bool first = true;
-        for (int b = 0; b < a; b++)
-            if ((js.aggs[b].fn == FN_SUM || js.aggs[b].fn == FN_AVG) && js.aggs[b].arg == js.aggs[a].arg) first = false;
+        for (int b = 0; kind == 1 && b < a; b++)
+            if (jit_plane_kind(js, b) == 1 && js.aggs[b].arg == js.aggs[a].arg) first = false;
+        n += first ? 1 : 0;
+    }
+    return n;
+}
+inline bool jit_node_reads_nullable(const JitShape& js, int n) {
+    if (n < 0) return false;
+    const SNode& nd = js.nodes[n];
+    if (nd.op == DOP_LOAD) return nd.nullable != 0;
+    if (nd.op == DOP_LIT) return false;
+    return jit_node_reads_nullable(js, nd.lhs) || jit_node_reads_nullable(js, nd.rhs);
+}
+inline int jit_n_cnt(const JitShape& js) { // planes that count the rows they took (n_cnt of srb_shapes.cuh)
+    int n = 0;
+    for (int a = 0; a < js.n_aggs; a++) {
+        const int kind = jit_plane_kind(js, a);
+        if (kind == 0 || !jit_node_reads_nullable(js, js.aggs[a].arg)) continue;
+        bool first = true;
+        for (int b = 0; kind == 1 && b < a; b++)
+            if (jit_plane_kind(js, b) == 1 && js.aggs[b].arg == js.aggs[a].arg) first = false;
         n += first ? 1 : 0;
     }
     return n;
@@ -60,12 +94,13 @@ inline int jit_n_reps(const JitShape& js) {
 inline int jit_acc_bytes(const JitShape& js) { // AccGeom<S>::BYTES
     if (js.gmax <= 0) return 0;
     const int nr = std::max(1, jit_n_reps(js));
-    return nr * js.gmax * js.threads * 8 + js.gmax * js.threads * 4 + js.threads * 8;
+    return nr * js.gmax * js.threads * 8 + js.gmax * js.threads * 4 + js.threads * 8 + jit_n_cnt(js) * js.gmax * js.threads * 4;
 }
 
-// Can the static kernel run this program, and with which geometry? The conditions are shape_matches()'s (integer columns and values,
-// SUM / AVG / COUNT over integers, fixed-width NOT NULL keys that are plain columns), for ANY node / aggregate / key list.
-inline bool jit_shape_of(const DProg& p, int group_hint, JitShape& js) {
+// Can the static kernel run this program, and with which geometry? Integer columns and values (with or without null maps: `col_nullable`
+// says which columns of THIS variant carry one), SUM / AVG / COUNT over integers, MIN / MAX over values of up to 8 bytes, up to four
+// fixed-width keys that are plain columns — for ANY node / aggregate / key list.
+inline bool jit_shape_of(const DProg& p, int group_hint, const bool* col_nullable, JitShape& js) {
     if (p.n_nodes < 1 || p.n_aggs < 1 || p.n_nodes > MAX_NODES) return false;
     js = JitShape{};
     js.n_nodes = p.n_nodes;
@@ -74,7 +109,7 @@ inline bool jit_shape_of(const DProg& p, int group_hint, JitShape& js) {
     int row_bytes = 0;
     for (int c = 0; c < p.n_cols; c++) {
         if (p.cols[c].kind != CK_INT || p.cols[c].width < 1 || p.cols[c].width > 16) return false;
-        row_bytes += p.cols[c].width;
+        row_bytes += p.cols[c].width + (col_nullable && col_nullable[c] ? 1 : 0);
     }
     bool col_seen[MAX_COLS] = {};
     for (int i = 0; i < p.n_nodes; i++) {
@@ -89,12 +124,14 @@ inline bool jit_shape_of(const DProg& p, int group_hint, JitShape& js) {
         }
         const bool leaf = d.op == DOP_LOAD || d.op == DOP_LIT;
         js.nodes[i] = SNode{d.op, d.width, leaf ? -1 : d.lhs, (leaf || d.op == DOP_CAST) ? -1 : d.rhs, leaf ? 0 : d.checked,
-                            (leaf || d.op == DOP_CAST) ? 0 : d.adj_l, (leaf || d.op == DOP_CAST) ? 0 : d.adj_r};
+                            (leaf || d.op == DOP_CAST) ? 0 : d.adj_l, (leaf || d.op == DOP_CAST) ? 0 : d.adj_r,
+                            (d.op == DOP_LOAD && col_nullable && col_nullable[d.col]) ? 1 : 0};
     }
     for (int a = 0; a < p.n_aggs; a++) {
         const DAgg& d = p.aggs[a];
-        if (d.fn != FN_SUM && d.fn != FN_AVG && d.fn != FN_COUNT) return false;
+        if (d.fn < FN_SUM || d.fn > FN_MAX) return false;
         if (d.is_double || d.avg_as_double) return false;
+        if ((d.fn == FN_MIN || d.fn == FN_MAX) && (d.wide || d.arg < 0 || p.nodes[d.arg].width > 8)) return false;
         if (d.merge && d.fn == FN_AVG) return false; // {sum, count} blobs: the interpreter's job
         if (d.fn != FN_COUNT && (d.arg < 0 || d.arg >= p.n_nodes)) return false;
         if (d.arg >= p.n_nodes) return false;
@@ -103,9 +140,9 @@ inline bool jit_shape_of(const DProg& p, int group_hint, JitShape& js) {
     int key_bytes = 0;
     for (int k = 0; k < p.n_keys; k++) {
         const DKey& d = p.keys[k];
-        if (p.n_keys > 4 || d.nullable || d.width < 1 || d.width > 8 || d.node < 0 || d.node >= p.n_nodes || p.nodes[d.node].op != DOP_LOAD) return false;
-        js.keys[k] = SKey{d.node, d.width};
-        key_bytes += d.width;
+        if (p.n_keys > 4 || d.width < 1 || d.width > 8 || d.node < 0 || d.node >= p.n_nodes || p.nodes[d.node].op != DOP_LOAD) return false;
+        js.keys[k] = SKey{d.node, d.width, d.nullable ? 1 : 0};
+        key_bytes += d.width + (d.nullable ? 1 : 0);
     }
     if (key_bytes > 16) return false;
     // geometry: few groups (the planner's estimate) -> per-thread accumulators and a CTA directory of GMAX groups; otherwise every row goes to
@@ -147,7 +184,7 @@ inline std::string jit_source(const JitShape& js) {
     s += "    static constexpr SNode node(int i) {\n        constexpr SNode t[N_NODES] = {\n";
     for (int i = 0; i < js.n_nodes; i++) {
         const SNode& n = js.nodes[i];
-        snprintf(buf, sizeof buf, "            {%d, %d, %d, %d, %d, %d, %d},\n", n.op, n.width, n.lhs, n.rhs, n.checked, n.adj_l, n.adj_r);
+        snprintf(buf, sizeof buf, "            {%d, %d, %d, %d, %d, %d, %d, %d},\n", n.op, n.width, n.lhs, n.rhs, n.checked, n.adj_l, n.adj_r, n.nullable);
         s += buf;
     }
     s += "        };\n        return t[i];\n    }\n    static constexpr SAgg agg(int i) {\n        constexpr SAgg t[N_AGGS] = {\n";
@@ -160,7 +197,7 @@ inline std::string jit_source(const JitShape& js) {
     if (js.n_keys) {
         s += "        constexpr SKey t[N_KEYS] = {\n";
         for (int k = 0; k < js.n_keys; k++) {
-            snprintf(buf, sizeof buf, "            {%d, %d},\n", js.keys[k].node, js.keys[k].width);
+            snprintf(buf, sizeof buf, "            {%d, %d, %d},\n", js.keys[k].node, js.keys[k].width, js.keys[k].nullable);
             s += buf;
         }
         s += "        };\n        return t[i];\n";

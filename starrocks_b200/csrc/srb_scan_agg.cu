@@ -1742,9 +1742,18 @@ private:
             init_table();
             shape_ = getenv("SRB_NO_BUILTIN_SHAPES") ? -1 : match_static_shape(L_.prog); // hook: A/B of a built-in shape against its run-time compiled twin
             // no built-in shape: can the static kernel be compiled for this plan at run time (srb_jit.h)?
-            if (shape_ < 0 && jit_mode_ && !force_generic_ && jit_shape_of(L_.prog, (int)std::min<int64_t>(plan_.group_hint, 1 << 30), jit_shape_)) {
-                jit_src_ = jit_source(jit_shape_);
-                jit_ = JitCache::get().peek(jit_src_); // an earlier operator of the same shape may have compiled it already
+            // Two variants: [0] for batches without null maps (or whose maps hold no NULL: they are stripped), [1] with the maps of the
+            // columns that arrived nullable compiled in.
+            if (shape_ < 0 && jit_mode_ && !force_generic_) {
+                bool nullable[MAX_COLS] = {};
+                bool any = false;
+                for (size_t i = 0; i < L_.cols.size() && i < (size_t)MAX_COLS; i++) any = (nullable[i] = L_.cols[i].nullable) || any;
+                const int hint = (int)std::min<int64_t>(plan_.group_hint, 1 << 30);
+                JitShape js;
+                if (jit_shape_of(L_.prog, hint, nullptr, js)) jit_src_[0] = jit_source(js);
+                if (any && jit_shape_of(L_.prog, hint, nullable, js)) jit_src_[1] = jit_source(js);
+                for (int v = 0; v < 2; v++)
+                    if (!jit_src_[v].empty()) jit_[v] = JitCache::get().peek(jit_src_[v]); // an earlier operator may have compiled it already
             }
         }
         lowered_ = true;
@@ -2171,17 +2180,26 @@ private:
             // a recognised shape whose columns arrive with null maps: maps without a set byte are dropped for this batch, so that
             // the static kernel (and the L2-blocked permutation, which moves values but not null maps) can take it
             batch_has_nulls_ = batch_stripped_ = false;
-            if (!jit_src_.empty() && !jit_failed_) { // a shape compiled at run time: start the compilation at the first large batch, use it once ready
-                if (!jit_ && n >= jit_min_rows_) jit_ = JitCache::get().acquire(jit_src_, jit_mode_ == 2);
-                if (jit_ && !jit_kernel_) {
-                    jit_kernel_ = jit_->get(ctx->cfg.device);
-                    if (!jit_kernel_ && jit_->failed()) {
-                        jit_failed_ = true; // the interpreter serves the operator; the reason is kept for srb_jit_stats / SRB_TRACE
-                        if (getenv("SRB_TRACE")) fprintf(stderr, "[srb] run-time compilation failed: %s\n", jit_->error().c_str());
-                    }
+            jit_kernel_ = nullptr;
+            bool maps = false;
+            for (int i = 0; i < L_.prog.n_cols; i++) maps = maps || cols[i].nulls;
+            // a shape compiled at run time: start the compilation at the first large batch, use it once it is ready
+            auto jit_variant = [&](int v) -> const JitLoaded* {
+                if (jit_src_[v].empty() || jit_failed_[v]) return nullptr;
+                if (!jit_[v] && n >= jit_min_rows_) jit_[v] = JitCache::get().acquire(jit_src_[v], jit_mode_ == 2);
+                if (!jit_[v]) return nullptr;
+                const JitLoaded* k = jit_[v]->get(ctx->cfg.device);
+                if (!k && jit_[v]->failed()) {
+                    jit_failed_[v] = true; // the interpreter serves the operator; the reason is kept for srb_jit_stats / SRB_TRACE
+                    if (getenv("SRB_TRACE")) fprintf(stderr, "[srb] run-time compilation failed: %s\n", jit_[v]->error().c_str());
                 }
+                return k;
+            };
+            if (!maps) jit_kernel_ = jit_variant(0);
+            if (maps && !force_generic_ && (shape_ >= 0 || !jit_src_[0].empty())) {
+                cols = strip_clear_null_maps(cols, off, n); // maps without a set byte are dropped: the NULL-free kernel takes the batch
+                jit_kernel_ = jit_variant(batch_has_nulls_ ? 1 : 0);
             }
-            if ((shape_ >= 0 || jit_kernel_) && !force_generic_) cols = strip_clear_null_maps(cols, off, n);
             tr.mark("  strip null maps");
             batch_partitioned_ = !batch_has_nulls_ && hc_partition_applies(n);
             if (batch_partitioned_) hc_partition(cols, off, n);
@@ -2791,11 +2809,10 @@ private:
     static constexpr int SHAPE_JIT = 100; // what profile() reports as the shape once such a kernel has run
     int jit_mode_ = jit_mode_from_env();
     int64_t jit_min_rows_ = getenv("SRB_JIT_MIN_ROWS") ? atoll(getenv("SRB_JIT_MIN_ROWS")) : ((int64_t)4 << 20);
-    JitShape jit_shape_;
-    std::string jit_src_;
-    std::shared_ptr<JitEntry> jit_;
-    const JitLoaded* jit_kernel_ = nullptr;
-    bool jit_failed_ = false;
+    std::string jit_src_[2];
+    std::shared_ptr<JitEntry> jit_[2];
+    const JitLoaded* jit_kernel_ = nullptr; // the variant this batch runs, nullptr: a built-in shape or the interpreter
+    bool jit_failed_[2] = {false, false};
     int64_t jit_launches_ = 0;
     static int jit_mode_from_env() {
         const char* m = getenv("SRB_JIT");
@@ -2930,7 +2947,10 @@ void jit_check_plan(const srb_scan_agg_plan* plan, const srb_chunk* first, std::
         if (description) *description = std::string("built-in shape: ") + static_shape_name(match_static_shape(L.prog));
         return;
     }
-    if (!jit_shape_of(L.prog, (int)std::min<int64_t>(pc.group_hint, 1 << 30), js))
+    bool nullable[MAX_COLS] = {};
+    bool any = false;
+    for (size_t i = 0; i < L.cols.size() && i < (size_t)MAX_COLS; i++) any = (nullable[i] = L.cols[i].nullable) || any;
+    if (!jit_shape_of(L.prog, (int)std::min<int64_t>(pc.group_hint, 1 << 30), any ? nullable : nullptr, js))
         throw Error(SRB_NOT_IMPLEMENTED, "the plan is outside what the static kernel covers: the interpreter runs it");
     std::shared_ptr<JitEntry> e = JitCache::get().acquire(jit_source(js), true);
     if (e->failed()) throw Error(SRB_INTERNAL_ERROR, e->error());

@@ -40,6 +40,7 @@ struct Counters;
 
 struct SNode {
     int op, width, lhs, rhs, checked, adj_l, adj_r;
+    int nullable = 0; // LOAD: the column arrives with a null map (one byte per row in the stage)
 };
 struct SAgg {
     int fn, arg, wide, has_n; // wide: state keeps the high word (off_hi >= 0); has_n: state keeps its own count
@@ -47,6 +48,7 @@ struct SAgg {
 };
 struct SKey {
     int node, width;
+    int nullable = 0; // the key area carries a leading null byte for this column (DKey::nullable)
 };
 
 // ---- the registered shapes ---------------------------------------------------------------------------------------
@@ -242,13 +244,17 @@ struct SRange {
 struct SPred {
     int32_t col_off;
     int32_t width;
-    uint32_t opmask;
+    uint32_t opmask; // bit 3: the result for a NULL value (IS NULL)
     int32_t group;
+    int32_t null_off; // the column's null bytes inside a stage, -1: NULL-free
+    int32_t _pad;
     uint64_t lit_lo;
     int64_t lit_hi;
 };
 struct StaticArgs { // host-computed tile layout: column c sits at col_off[c] inside a stage of stage_bytes
     int32_t col_off[MAX_COLS];
+    int32_t null_off[MAX_COLS];       // its null map (one byte per row), -1: none
+    int32_t node_null_off[MAX_NODES]; // the same offset by LOAD node (a compile-time index in the kernel)
     int32_t stage_bytes;
     int32_t n_stages;
     int32_t n_preds;
@@ -323,6 +329,7 @@ SRB_D Val lds_val(const uint8_t* col, int r) {
 
 // one predicate on one row of the tile (NULL-free columns): NULL never satisfies a compare, IS_NULL is constant false
 SRB_D bool spred_eval(const SPred& pr, const uint8_t* stage, int r) {
+    if (pr.null_off >= 0 && stage[pr.null_off + r]) return (pr.opmask >> 3) & 1u; // NULL: only IS NULL holds
     const uint8_t* col = stage + pr.col_off;
     int idx;
     if (pr.width == 16) {
@@ -386,12 +393,15 @@ static __device__ __noinline__ Mul128Res mul_overflow128_cold(uint64_t xl, int64
 // and no overflow flag can be set); everything else is the generic primitive of srb_dev.cuh, so results are the same bits
 // as the interpreter's. Must be called by all 32 lanes (votes inside).
 template <class S, int I, int R>
-SRB_D void eval_static_node(const DProg& p, Val (&v)[R][S::N_NODES], const uint8_t* stage, int r0) {
+SRB_D void eval_static_node(const DProg& p, const StaticArgs& sa, Val (&v)[R][S::N_NODES], const uint8_t* stage, int r0) {
     constexpr SNode nd = S::node(I);
     const DNode& rt = p.nodes[I];
     if constexpr (nd.op == DOP_LOAD) {
 #pragma unroll
-        for (int j = 0; j < R; j++) v[j][I] = lds_val<nd.width>(stage + load_off<S>(I), r0 + j * S::THREADS);
+        for (int j = 0; j < R; j++) {
+            v[j][I] = lds_val<nd.width>(stage + load_off<S>(I), r0 + j * S::THREADS);
+            if constexpr (nd.nullable != 0) v[j][I].null = stage[sa.node_null_off[I] + r0 + j * S::THREADS] != 0;
+        }
     } else if constexpr (nd.op == DOP_LIT) {
 #pragma unroll
         for (int j = 0; j < R; j++) {
@@ -499,45 +509,84 @@ SRB_D void eval_static_node(const DProg& p, Val (&v)[R][S::N_NODES], const uint8
     }
 }
 template <class S, int R, int... I>
-SRB_D void eval_static_all(const DProg& p, Val (&v)[R][S::N_NODES], const uint8_t* stage, int r0, iseq<I...>) {
-    (eval_static_node<S, I, R>(p, v, stage, r0), ...);
+SRB_D void eval_static_all(const DProg& p, const StaticArgs& sa, Val (&v)[R][S::N_NODES], const uint8_t* stage, int r0, iseq<I...>) {
+    (eval_static_node<S, I, R>(p, sa, v, stage, r0), ...);
 }
 
 
-// aggregate a is a "representative" when no earlier SUM/AVG aggregate has the same argument (their partial sums are identical)
+// can the value of node n be NULL? (a column with a null map, a checked operation that overflowed)
+template <class S>
+constexpr bool node_can_be_null(int n) {
+    if (n < 0) return false;
+    const SNode nd = S::node(n);
+    if (nd.op == DOP_LOAD) return nd.nullable != 0;
+    if (nd.op == DOP_LIT) return false;
+    if (nd.checked) return true;
+    return node_can_be_null<S>(nd.lhs) || node_can_be_null<S>(nd.rhs);
+}
+
+// Accumulator planes of the low-cardinality path. Kind 1 (sum plane): SUM / AVG, and COUNT(x) over an argument that can be NULL (it needs the
+// plane's NULL counter) — aggregates over the same argument share one plane, the first of them is its "representative". Kind 2 (max plane):
+// MIN / MAX over a value of up to 8 bytes, one plane each, holding the table's own order-preserving encoding (enc_i64: identity zero).
+// Kind 0: COUNT(*) and COUNT over an argument that is never NULL — the group's row count.
+template <class S>
+constexpr int plane_kind(int a) {
+    const SAgg g = S::agg(a);
+    if (g.fn == FN_SUM || g.fn == FN_AVG) return 1;
+    if (g.fn == FN_COUNT) return (g.merge == 0 && g.arg >= 0 && node_can_be_null<S>(g.arg)) ? 1 : 0;
+    return 2;
+}
 template <class S>
 constexpr int agg_rep(int a) {
-    const SAgg g = S::agg(a);
-    if (g.fn != FN_SUM && g.fn != FN_AVG) return a;
-    for (int b = 0; b < a; b++) {
-        const SAgg h = S::agg(b);
-        if ((h.fn == FN_SUM || h.fn == FN_AVG) && h.arg == g.arg) return b;
-    }
+    if (plane_kind<S>(a) != 1) return a;
+    for (int b = 0; b < a; b++)
+        if (plane_kind<S>(b) == 1 && S::agg(b).arg == S::agg(a).arg) return b;
     return a;
 }
 // dense index of a representative among the representatives (its accumulator plane), and their number
 template <class S>
 constexpr int rep_index(int a) {
     int n = 0;
-    for (int b = 0; b < a; b++) {
-        const SAgg h = S::agg(b);
-        if ((h.fn == FN_SUM || h.fn == FN_AVG) && agg_rep<S>(b) == b) n++;
-    }
+    for (int b = 0; b < a; b++)
+        if (plane_kind<S>(b) != 0 && agg_rep<S>(b) == b) n++;
     return n;
 }
 template <class S>
 constexpr int n_reps() {
     return rep_index<S>(S::N_AGGS);
 }
-// can the value of node n be NULL? (static shapes bind NOT NULL columns, so only checked ops produce NULLs)
+// Planes whose argument reads a column with a null map see NULLs on ordinary rows, not once in a blue moon: they keep a per-thread count
+// of the rows they TOOK in shared memory (one more u32 per (plane, group, thread)) instead of sending every NULL down the rare path.
 template <class S>
-constexpr bool node_can_be_null(int n) {
+constexpr bool node_reads_nullable(int n) {
     if (n < 0) return false;
     const SNode nd = S::node(n);
-    if (nd.checked) return true;
-    return node_can_be_null<S>(nd.lhs) || node_can_be_null<S>(nd.rhs);
+    if (nd.op == DOP_LOAD) return nd.nullable != 0;
+    if (nd.op == DOP_LIT) return false;
+    return node_reads_nullable<S>(nd.lhs) || node_reads_nullable<S>(nd.rhs);
 }
-
+template <class S>
+constexpr bool plane_counts(int a) { // a: a representative
+    return plane_kind<S>(a) != 0 && node_reads_nullable<S>(S::agg(a).arg);
+}
+template <class S>
+constexpr int cnt_index(int a) {
+    int n = 0;
+    for (int b = 0; b < a; b++)
+        if (plane_kind<S>(b) != 0 && agg_rep<S>(b) == b && plane_counts<S>(b)) n++;
+    return n;
+}
+template <class S>
+constexpr int n_cnt() {
+    return cnt_index<S>(S::N_AGGS);
+}
+// is plane ri a max plane? (fold() walks the planes by index)
+template <class S>
+constexpr bool plane_is_max(int ri) {
+    for (int a = 0; a < S::N_AGGS; a++)
+        if (plane_kind<S>(a) == 2 && rep_index<S>(a) == ri) return true;
+    return false;
+}
 // Per-thread accumulators of the low-cardinality path. The LOW 64 bits of every partial sum and the row count live in
 // shared memory, one private word per (representative, group, thread): lanes of a warp hit distinct banks whatever their
 // groups are, so an update is a plain LDS / add / STS with the group as a runtime address — no atomics, no per-group
@@ -551,7 +600,9 @@ struct AccGeom {
     static constexpr int LO_BYTES = NR * G * S::THREADS * 8; // [rep][group][thread] u64
     static constexpr int ROWS_BYTES = G * S::THREADS * 4;    // [group][thread] u32
     static constexpr int TRASH_BYTES = S::THREADS * 8;       // [thread] u64: where rows that do not count are steered
-    static constexpr int BYTES = S::GMAX > 0 ? LO_BYTES + ROWS_BYTES + TRASH_BYTES : 0;
+    static constexpr int NC = n_cnt<S>();
+    static constexpr int CNT_BYTES = NC * G * S::THREADS * 4; // [counting plane][group][thread] u32: rows the plane took
+    static constexpr int BYTES = S::GMAX > 0 ? LO_BYTES + ROWS_BYTES + TRASH_BYTES + CNT_BYTES : 0;
 };
 template <class S>
 struct RareAcc {
@@ -576,34 +627,56 @@ SRB_D void add_word_spill(uint64_t old, uint64_t xlo, uint64_t xhi, uint64_t& nw
 // One representative, one row. Branch-free: a row that does not count (filtered out, NULL argument) is steered to the
 // thread's trash word instead of being skipped, so the instruction stream is the same for every lane.
 template <class S, int A>
-SRB_D void acc_one(uint8_t* a, uint8_t* trash, const Val* v, bool on, uint64_t* dh, uint64_t& row_spill, bool& any_null) {
+SRB_D void acc_one(uint8_t* a, uint8_t* c, uint8_t* trash, const Val* v, bool on, uint64_t* dh, uint64_t& row_spill, bool& any_null) {
     constexpr SAgg g = S::agg(A);
-    if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
+    if constexpr (plane_kind<S>(A) == 1 && agg_rep<S>(A) == A) {
         constexpr int RI = rep_index<S>(A);
         const Val& x = v[g.arg];
         bool take = on;
         if constexpr (node_can_be_null<S>(g.arg)) {
             take = on && !x.null;
-            any_null = any_null || (on && x.null);
+            if constexpr (!plane_counts<S>(A)) any_null = any_null || (on && x.null);
         }
         uint64_t* slot = (uint64_t*)(take ? a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8 : trash);
         uint64_t nw;
         add_word_spill(*slot, x.lo, (uint64_t)x.hi, nw, dh[RI]);
         *slot = nw;
-        row_spill |= dh[RI]; // meaningless for a trashed row: the caller masks it (or any_null already forces the rare path)
+        if constexpr (plane_counts<S>(A)) {
+            row_spill |= take ? dh[RI] : 0ULL;
+            uint32_t* tc = (uint32_t*)(take ? c + (size_t)cnt_index<S>(A) * AccGeom<S>::G * S::THREADS * 4 : trash);
+            *tc += 1u;
+        } else {
+            row_spill |= dh[RI]; // meaningless for a trashed row: the caller masks it (or any_null already forces the rare path)
+        }
+    } else if constexpr (plane_kind<S>(A) == 2) {
+        constexpr int RI = rep_index<S>(A);
+        const Val& x = v[g.arg];
+        bool take = on;
+        if constexpr (node_can_be_null<S>(g.arg)) {
+            take = on && !x.null;
+            if constexpr (!plane_counts<S>(A)) any_null = any_null || (on && x.null);
+        }
+        uint64_t* slot = (uint64_t*)(take ? a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8 : trash);
+        const uint64_t e = enc_i64((int64_t)x.lo, g.fn == FN_MIN), cur = *slot;
+        *slot = e > cur ? e : cur;
+        dh[RI] = 0;
+        if constexpr (plane_counts<S>(A)) {
+            uint32_t* tc = (uint32_t*)(take ? c + (size_t)cnt_index<S>(A) * AccGeom<S>::G * S::THREADS * 4 : trash);
+            *tc += 1u;
+        }
     }
 }
 template <class S, int A>
 SRB_D void acc_rare_one(RareAcc<S>& ra, int gid, const Val* v, bool on, const uint64_t* dh) {
     constexpr SAgg g = S::agg(A);
-    if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
+    if constexpr (plane_kind<S>(A) != 0 && agg_rep<S>(A) == A) {
         constexpr int RI = rep_index<S>(A);
         bool take = on;
         if constexpr (node_can_be_null<S>(g.arg)) {
             take = on && !v[g.arg].null;
-            ra.nulls[gid * AccGeom<S>::NR + RI] += (on && v[g.arg].null) ? 1u : 0u;
+            if constexpr (!plane_counts<S>(A)) ra.nulls[gid * AccGeom<S>::NR + RI] += (on && v[g.arg].null) ? 1u : 0u;
         }
-        ra.hi[gid * AccGeom<S>::NR + RI] += take ? dh[RI] : 0ULL;
+        if constexpr (plane_kind<S>(A) == 1) ra.hi[gid * AccGeom<S>::NR + RI] += take ? dh[RI] : 0ULL;
     }
 }
 // the R rows of a tile into their groups (0 <= gid[j] < G; on[j] false: the row does not count). One vote covers the
@@ -617,8 +690,9 @@ SRB_D void acc_update_rows(RareAcc<S>& ra, uint8_t* acc_tid, uint8_t* rows_tid, 
 #pragma unroll
     for (int j = 0; j < R; j++) {
         uint8_t* a = acc_tid + (size_t)gid[j] * (S::THREADS * 8);
+        uint8_t* c = rows_tid + AccGeom<S>::ROWS_BYTES + AccGeom<S>::TRASH_BYTES + (size_t)gid[j] * (S::THREADS * 4); // the counting planes of this group
         uint64_t row_spill = 0;
-        (acc_one<S, A>(a, trash, v[j], on[j], dh[j], row_spill, any_null), ...);
+        (acc_one<S, A>(a, c, trash, v[j], on[j], dh[j], row_spill, any_null), ...);
         any_spill |= on[j] ? row_spill : 0ULL;
         uint32_t* rc = (uint32_t*)(on[j] ? rows_tid + (size_t)gid[j] * (S::THREADS * 4) : trash);
         *rc += 1u;
@@ -660,7 +734,7 @@ constexpr bool shape_has_narrow() {
         if (key && (nd.op != DOP_LOAD || node_is_operand<S>(i))) return false; // keys: plain columns, bits taken as they are
         switch (nd.op) {
         case DOP_LOAD:
-            if (nd.width != 8 && !(key && nd.width == 4)) return false;
+            if (nd.nullable != 0 || (nd.width != 8 && !(key && nd.width == 4))) return false;
             break;
         case DOP_LIT: break;
         case DOP_CAST:
@@ -679,6 +753,8 @@ constexpr bool shape_has_narrow() {
         const SAgg g = S::agg(a);
         if (g.fn == FN_COUNT ? g.arg >= 0 : (g.fn != FN_SUM && g.fn != FN_AVG)) return false;
     }
+    for (int k = 0; k < S::N_KEYS; k++)
+        if (S::key(k).nullable != 0) return false;
     return true;
 }
 template <class S, int I, int R>
@@ -840,16 +916,31 @@ struct Flusher {
     static constexpr int STASH_BYTES = (S::THREADS / 32) * G * WORDS * 8;
 
     template <int A>
-    static __device__ __forceinline__ void stash_rep(const RareAcc<S>& ra, const uint8_t* acc_tid, int q, uint64_t* st) {
+    static __device__ __forceinline__ void stash_rep(const RareAcc<S>& ra, const uint8_t* acc_tid, const uint8_t* rows_tid, int q, uint64_t* st) {
         constexpr SAgg g = S::agg(A);
-        if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
+        if constexpr (plane_kind<S>(A) != 0 && agg_rep<S>(A) == A) {
             constexpr int RI = rep_index<S>(A);
             const uint64_t w = *(const uint64_t*)(acc_tid + (size_t)(RI * G + q) * S::THREADS * 8);
-            uint64_t lo = w + ra.lo[q * NR + RI];
-            uint64_t hi = ra.hi[q * NR + RI] + (lo < w ? 1ULL : 0ULL);
-            warp_sum_u128(lo, hi);
-            uint64_t nulls = 0;
-            if constexpr (node_can_be_null<S>(g.arg)) nulls = warp_sum_u64(ra.nulls[q * NR + RI]);
+            uint64_t lo, hi;
+            if constexpr (plane_kind<S>(A) == 2) {
+                lo = w;
+                hi = 0;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const uint64_t y = __shfl_xor_sync(0xffffffffu, lo, o);
+                    lo = y > lo ? y : lo;
+                }
+            } else {
+                lo = w + ra.lo[q * NR + RI];
+                hi = ra.hi[q * NR + RI] + (lo < w ? 1ULL : 0ULL);
+                warp_sum_u128(lo, hi);
+            }
+            uint64_t nulls = 0; // a counting plane: the rows it took; otherwise the selected rows whose argument was NULL
+            if constexpr (plane_counts<S>(A))
+                nulls = warp_sum_u64(*(const uint32_t*)(rows_tid + AccGeom<S>::ROWS_BYTES + AccGeom<S>::TRASH_BYTES +
+                                                        (size_t)(cnt_index<S>(A) * G + q) * (S::THREADS * 4)));
+            else if constexpr (node_can_be_null<S>(g.arg))
+                nulls = warp_sum_u64(ra.nulls[q * NR + RI]);
             if ((threadIdx.x & 31) == 0) {
                 st[RI * 3 + 0] = lo;
                 st[RI * 3 + 1] = hi;
@@ -864,20 +955,27 @@ struct Flusher {
         uint64_t* st = stash_base + (size_t)((threadIdx.x >> 5) * G + q) * WORDS;
         const uint64_t rows = warp_sum_u64(*(const uint32_t*)(rows_tid + (size_t)q * (S::THREADS * 4)));
         if ((threadIdx.x & 31) == 0) st[3 * NR] = rows;
-        (stash_rep<A>(ra, acc_tid, q, st), ...);
+        (stash_rep<A>(ra, acc_tid, rows_tid, q, st), ...);
     }
     template <int A>
     static __device__ __forceinline__ void emit(const DProg& p, uint8_t* slot, const uint64_t* tot, uint64_t rows_total) {
         constexpr SAgg g = S::agg(A);
         const DAgg& rt = p.aggs[A];
-        if constexpr (g.fn == FN_COUNT) {
+        if constexpr (plane_kind<S>(A) == 0) {
             if (rows_total) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)rows_total);
         } else {
             constexpr int RI = rep_index<S>(agg_rep<S>(A));
-            const uint64_t n = rows_total - tot[RI * 3 + 2];
+            const uint64_t n = plane_counts<S>(agg_rep<S>(A)) ? tot[RI * 3 + 2] : rows_total - tot[RI * 3 + 2];
             if (n) {
-                atomic_add128(slot, rt.off_lo, rt.off_hi, tot[RI * 3 + 0], tot[RI * 3 + 1]);
-                if (rt.off_n >= 0) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)n);
+                if constexpr (g.fn == FN_COUNT) {
+                    atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)n);
+                } else {
+                    if constexpr (plane_kind<S>(A) == 2)
+                        atomicMax((unsigned long long*)(slot + rt.off_lo), (unsigned long long)tot[RI * 3 + 0]);
+                    else
+                        atomic_add128(slot, rt.off_lo, rt.off_hi, tot[RI * 3 + 0], tot[RI * 3 + 1]);
+                    if (rt.off_n >= 0) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)n);
+                }
             }
         }
     }
@@ -891,9 +989,13 @@ struct Flusher {
             const uint64_t* st = stash_base + (size_t)(w * G + q) * WORDS;
 #pragma unroll
             for (int r = 0; r < NR; r++) {
-                const uint64_t lo = tot[r * 3] + st[r * 3];
-                tot[r * 3 + 1] += st[r * 3 + 1] + (lo < st[r * 3] ? 1ULL : 0ULL);
-                tot[r * 3] = lo;
+                if (plane_is_max<S>(r)) {
+                    tot[r * 3] = st[r * 3] > tot[r * 3] ? st[r * 3] : tot[r * 3];
+                } else {
+                    const uint64_t lo = tot[r * 3] + st[r * 3];
+                    tot[r * 3 + 1] += st[r * 3 + 1] + (lo < st[r * 3] ? 1ULL : 0ULL);
+                    tot[r * 3] = lo;
+                }
                 tot[r * 3 + 2] += st[r * 3 + 2];
             }
             tot[3 * NR] += st[3 * NR];
@@ -917,7 +1019,10 @@ SRB_D void row_update_global_one(const DProg& p, uint8_t* slot, const Val* v) {
     } else {
         const Val& x = v[g.arg];
         if (!x.null) {
-            atomic_add128(slot, rt.off_lo, rt.off_hi, x.lo, (uint64_t)x.hi);
+            if constexpr (g.fn == FN_MIN || g.fn == FN_MAX)
+                atomicMax((unsigned long long*)(slot + rt.off_lo), (unsigned long long)enc_i64((int64_t)x.lo, g.fn == FN_MIN));
+            else
+                atomic_add128(slot, rt.off_lo, rt.off_hi, x.lo, (uint64_t)x.hi);
             if (rt.off_n >= 0) atomicAdd((unsigned long long*)(slot + rt.off_n), 1ULL);
         }
     }
@@ -930,7 +1035,7 @@ SRB_D void row_update_global(const DProg& p, uint8_t* slot, const Val* v, iseq<A
 template <class S>
 constexpr int static_key_bytes() {
     int n = 0;
-    for (int k = 0; k < S::N_KEYS; k++) n += S::key(k).width;
+    for (int k = 0; k < S::N_KEYS; k++) n += S::key(k).width + (S::key(k).nullable != 0 ? 1 : 0);
     return n;
 }
 // hash of a packed key whose length is a compile-time constant (same functions as hash_packed_key)
@@ -942,13 +1047,27 @@ SRB_D uint64_t hash_packed_key_static(const PackedKey& k, int seed) {
     return hash_packed_key(k, seed);
 }
 
+// key column K of the packed key: [null byte if the column is nullable][value, zero when NULL] (pack_key of srb_rowpipe.cuh)
+template <class S, int KI>
+SRB_D void key_put_static(PackedKey& k, const Val* v) {
+    if constexpr (KI < S::N_KEYS) {
+        constexpr SKey kd = S::key(KI);
+        const Val& x = v[kd.node];
+        if constexpr (kd.nullable != 0) {
+            key_put(k, x.null ? 1 : 0, 1);
+            key_put(k, x.null ? 0ULL : x.lo, kd.width);
+        } else {
+            key_put(k, x.lo, kd.width);
+        }
+    }
+}
 template <class S>
 SRB_D PackedKey pack_key_static(const Val* v) {
     PackedKey k{0, 0, 0, false};
-    if constexpr (S::N_KEYS >= 1) key_put(k, v[S::key(0).node].lo, S::key(0).width);
-    if constexpr (S::N_KEYS >= 2) key_put(k, v[S::key(1).node].lo, S::key(1).width);
-    if constexpr (S::N_KEYS >= 3) key_put(k, v[S::key(2).node].lo, S::key(2).width);
-    if constexpr (S::N_KEYS >= 4) key_put(k, v[S::key(3).node].lo, S::key(3).width);
+    key_put_static<S, 0>(k, v);
+    key_put_static<S, 1>(k, v);
+    key_put_static<S, 2>(k, v);
+    key_put_static<S, 3>(k, v);
     return k;
 }
 
@@ -1043,7 +1162,10 @@ SRB_D void row_update_args_one(const DProg& p, uint8_t* slot, const AggArgs<S>& 
         if (!null) atomicAdd((unsigned long long*)(slot + rt.off_n), 1ULL);
     } else {
         if (!null) {
-            atomic_add128(slot, rt.off_lo, rt.off_hi, x.lo[A], (uint64_t)x.hi[A]);
+            if constexpr (g.fn == FN_MIN || g.fn == FN_MAX)
+                atomicMax((unsigned long long*)(slot + rt.off_lo), (unsigned long long)enc_i64((int64_t)x.lo[A], g.fn == FN_MIN));
+            else
+                atomic_add128(slot, rt.off_lo, rt.off_hi, x.lo[A], (uint64_t)x.hi[A]);
             if (rt.off_n >= 0) atomicAdd((unsigned long long*)(slot + rt.off_n), 1ULL);
         }
     }
@@ -1104,6 +1226,9 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
             for (int k = 0; k < AccGeom<S>::NR * G; k++) *(uint64_t*)(acc_tid + (size_t)k * THREADS * 8) = 0;
 #pragma unroll
             for (int k = 0; k < G; k++) *(uint32_t*)(rows_tid + (size_t)k * THREADS * 4) = 0;
+#pragma unroll
+            for (int k = 0; k < AccGeom<S>::NC * G; k++)
+                *(uint32_t*)(rows_tid + AccGeom<S>::ROWS_BYTES + AccGeom<S>::TRASH_BYTES + (size_t)k * THREADS * 4) = 0;
         }
 #pragma unroll
         for (int k = 0; k < AccGeom<S>::NR * G; k++) {
@@ -1129,6 +1254,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                     const int w = p.cols[c].width;
                     tma_load_1d(dst + sa.col_off[c], (const uint8_t*)p.cols[c].data + (size_t)(base + tile * TILE) * w, (uint32_t)(TILE * w),
                                 &full_bar[s]);
+                    if (sa.null_off[c] >= 0) tma_load_1d(dst + sa.null_off[c], p.cols[c].nulls + (size_t)(base + tile * TILE), (uint32_t)TILE, &full_bar[s]);
                 }
                 if (++s == n_stages) {
                     s = 0;
@@ -1204,7 +1330,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
             }
             if (!done && __any_sync(0xffffffffu, any_pass)) {
                 Val v[R][S::N_NODES];
-                eval_static_all<S, R>(p, v, stage, tid, NodeSeq{});
+                eval_static_all<S, R>(p, sa, v, stage, tid, NodeSeq{});
                 if constexpr (S::N_KEYS == 0) {
                     int gid[R];
 #pragma unroll
@@ -1325,6 +1451,7 @@ struct ShapeMeta {
     int32_t n_nodes, threads, rows, tile, acc_bytes, has_narrow, gmax, _pad;
     int32_t load_width[MAX_NODES]; // bytes of the column a LOAD node reads, 0 for every other node
     int32_t load_off[MAX_NODES];   // its offset inside a stage
+    int32_t load_nullable[MAX_NODES]; // the kernel reads a null byte per row for this LOAD node
 };
 template <class S>
 constexpr ShapeMeta shape_meta() {
@@ -1339,6 +1466,7 @@ constexpr ShapeMeta shape_meta() {
     for (int i = 0; i < S::N_NODES; i++) {
         m.load_width[i] = S::node(i).op == DOP_LOAD ? S::node(i).width : 0;
         m.load_off[i] = load_off<S>(i);
+        m.load_nullable[i] = (S::node(i).op == DOP_LOAD && S::node(i).nullable != 0) ? 1 : 0;
     }
     return m;
 }
@@ -1372,8 +1500,8 @@ inline uint32_t pred_opmask(int op) {
     case 4: return 0b011; // GE
     case 5: return 0b100; // LT
     case 6: return 0b110; // LE
-    case 10: return 0b111; // NOT NULL on a NULL-free column
-    default: return 0;     // IS NULL
+    case 10: return 0b0111; // NOT NULL: every non-NULL value
+    default: return 0b1000; // IS NULL: bit 3 = the answer for a NULL (spred_eval), no non-NULL value
     }
 }
 
@@ -1384,7 +1512,7 @@ inline bool lower_ranges(const DProg& p, StaticArgs& sa) {
     for (int i = 0; i < p.n_preds; i++) {
         const DPred& d = p.preds[i];
         const int w = p.cols[d.col].width;
-        if (d.group != 0 || (w != 4 && w != 8)) return false;
+        if (d.group != 0 || (w != 4 && w != 8) || sa.null_off[d.col] >= 0) return false;
         const i128 tmin = w == 4 ? (i128)INT32_MIN : (i128)INT64_MIN, tmax = w == 4 ? (i128)INT32_MAX : (i128)INT64_MAX;
         const i128 lit = make_i128(d.lit_lo, d.lit_hi);
         i128 lo = tmin, hi = tmax; // inclusive bounds
@@ -1451,12 +1579,19 @@ inline bool narrow_literals_ok_rt(const ShapeMeta& m, const DProg& p) {
 inline int64_t prepare_static(const ShapeMeta& m, const DProg& p, int64_t base, int64_t n, bool allow_narrow, StaticArgs& sa, size_t& smem) {
     // the columns of the LOAD nodes first, in node order (compile-time offsets), then predicate-only columns
     bool placed[MAX_COLS] = {};
+    int node_of[MAX_COLS];
     int bytes = 0;
+    for (int c = 0; c < MAX_COLS; c++) {
+        node_of[c] = -1;
+        sa.null_off[c] = -1;
+    }
+    for (int i = 0; i < MAX_NODES; i++) sa.node_null_off[i] = -1;
     for (int i = 0; i < m.n_nodes; i++) {
         if (!m.load_width[i]) continue;
         const int c = p.nodes[i].col;
         if (c < 0 || c >= p.n_cols || placed[c] || p.cols[c].width != m.load_width[i]) return 0; // a column bound twice: generic kernel
         placed[c] = true;
+        node_of[c] = i;
         sa.col_off[c] = m.load_off[i];
         bytes = m.load_off[i] + m.load_width[i] * m.tile;
     }
@@ -1465,8 +1600,17 @@ inline int64_t prepare_static(const ShapeMeta& m, const DProg& p, int64_t base, 
             sa.col_off[c] = bytes;
             bytes += p.cols[c].width * m.tile;
         }
-        // TMA bulk copies need 16-byte aligned sources: tile starts are multiples of 1024 rows, so the base pointers decide
-        if (p.cols[c].nulls || (((uintptr_t)p.cols[c].data + (size_t)base * p.cols[c].width) & 15)) return 0;
+        // TMA bulk copies need 16-byte aligned sources: tile starts are multiples of 16 rows, so the base pointers decide
+        if (((uintptr_t)p.cols[c].data + (size_t)base * p.cols[c].width) & 15) return 0;
+        // null maps: the kernel was compiled for exactly the LOAD columns that carry one (predicate-only columns may or may not)
+        const bool compiled_nullable = node_of[c] >= 0 && m.load_nullable[node_of[c]];
+        if (node_of[c] >= 0 && compiled_nullable != (p.cols[c].nulls != nullptr)) return 0;
+        if (p.cols[c].nulls) {
+            if (((uintptr_t)p.cols[c].nulls + (size_t)base) & 15) return 0;
+            sa.null_off[c] = bytes;
+            if (node_of[c] >= 0) sa.node_null_off[node_of[c]] = bytes;
+            bytes += m.tile;
+        }
     }
     const int64_t n_tiles = n / m.tile;
     if (n_tiles == 0 || bytes == 0) return 0;
@@ -1479,7 +1623,7 @@ inline int64_t prepare_static(const ShapeMeta& m, const DProg& p, int64_t base, 
     sa.n_preds = p.n_preds;
     for (int i = 0; i < p.n_preds; i++) {
         const DPred& d = p.preds[i];
-        sa.preds[i] = SPred{sa.col_off[d.col], p.cols[d.col].width, pred_opmask(d.op), d.group, d.lit_lo, d.lit_hi};
+        sa.preds[i] = SPred{sa.col_off[d.col], p.cols[d.col].width, pred_opmask(d.op), d.group, sa.null_off[d.col], 0, d.lit_lo, d.lit_hi};
     }
     if (!lower_ranges(p, sa)) sa.n_ranges = -1;
     sa.narrow_ok = (allow_narrow && narrow_literals_ok_rt(m, p)) ? 1 : 0; // allow_narrow = 0: A/B runs and tests of the general body (SRB_NO_NARROW)

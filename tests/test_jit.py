@@ -47,6 +47,17 @@ def orderkey_plan(hint):
     return ScanAggPlan(preds=[], exprs=e, keys=[k], aggs=[(K.AGG_SUM, ext), (K.AGG_COUNT, None), (K.AGG_AVG, disc)], group_hint=hint)
 
 
+def minmax_plan(n_keys):
+    e = ExprBuilder()
+    keys = [e.slot(Q.L_ORDERKEY, K.TYPE_INT)] if n_keys else []
+    ext = e.slot(Q.L_EXTENDEDPRICE, D64, 15, 2)
+    disc = e.slot(Q.L_DISCOUNT, D64, 15, 2)
+    qty = e.slot(Q.L_QUANTITY, D64, 15, 2)
+    neg = e.sub(disc, ext, D64, 16)  # negative values through the order-preserving encoding
+    return ScanAggPlan(preds=[], exprs=e, keys=keys, group_hint=100_000 if n_keys else 0,
+                       aggs=[(K.AGG_MIN, ext), (K.AGG_MAX, neg), (K.AGG_MIN, neg), (K.AGG_SUM, qty), (K.AGG_COUNT, None), (K.AGG_MAX, qty)])
+
+
 PLANS = {
     "two keys, six aggregates": (lambda: lineitem_plan(), T.LINEITEM_Q1),
     "no group by": (lambda: lineitem_plan(n_keys=0), T.LINEITEM_Q1),
@@ -55,6 +66,9 @@ PLANS = {
     "serialize phase": (lambda: lineitem_plan(phase=K.AGG_UPDATE_SERIALIZE), T.LINEITEM_Q1),
     "checked product": (lambda: lineitem_plan(charge=True, extra=False), T.LINEITEM_Q1),
     "no predicate": (lambda: lineitem_plan(preds=False), T.LINEITEM_Q1),
+    "min and max": (lambda: Q.q1_plan(with_min_max=True), T.LINEITEM_Q1),
+    "min and max, no group by": (lambda: minmax_plan(0), T.LINEITEM_Q1),
+    "min and max, many groups": (lambda: minmax_plan(1), ["l_orderkey", "l_extendedprice", "l_discount", "l_quantity"]),
     "many groups": (lambda: orderkey_plan(100_000), ["l_orderkey", "l_extendedprice", "l_discount"]),
     "unknown cardinality": (lambda: orderkey_plan(0), ["l_orderkey", "l_extendedprice", "l_discount"]),
 }
@@ -87,9 +101,18 @@ def test_builtin_shapes_are_recognised_and_uncovered_plans_are_refused(no_disk_c
     from starrocks_b200 import ops
     first = T.host_chunk("lineitem", 0, 16, T.LINEITEM_Q1)
     assert ops.jit_check_plan(Q.q1_plan(), first).startswith("built-in shape")
-    with pytest.raises(ops.SrbError) as ex:  # MIN / MAX: the interpreter's
-        ops.jit_check_plan(Q.q1_plan(with_min_max=True), first)
+    assert ops.jit_check_plan(Q.q1_plan(with_min_max=True), first).startswith("compiled shape")  # MIN / MAX of up to 8 bytes: covered
+    e = ExprBuilder()
+    ext = e.slot(Q.L_EXTENDEDPRICE, D64, 15, 2)
+    wide = ScanAggPlan(preds=[], exprs=e, keys=[], aggs=[(K.AGG_MAX, e.cast(ext, D128, 15, 2))])
+    with pytest.raises(ops.SrbError) as ex:  # MAX over a 16-byte value: the interpreter's
+        ops.jit_check_plan(wide, first)
     assert ex.value.code == K.NOT_IMPLEMENTED
+    # columns that arrive with null maps get a variant of their own
+    nul = K.Chunk(16, dict(first.columns))
+    c = first.columns[Q.L_DISCOUNT]
+    nul.columns[Q.L_DISCOUNT] = K.Column(c.type, c.data, np.zeros(16, np.uint8), None, c.precision, c.scale)
+    assert ops.jit_check_plan(lineitem_plan(), nul).startswith("compiled shape")
 
 
 def test_compiled_shapes_are_cached_on_disk(no_disk_cache):
@@ -222,3 +245,32 @@ def test_compiled_shape_with_null_maps_and_many_chunks(ctx, oracle, jit_sync):
         for p in p1 + p2:
             ctx.device_free(p)
     assert prof["shape"] == SHAPE_JIT and K.chunk_rows(got) == want
+
+
+def with_nulls(chunk, slots, frac, seed=3):
+    rng = np.random.default_rng(seed)
+    out = K.Chunk(chunk.n_rows, dict(chunk.columns))
+    for slot in slots:
+        c = chunk.columns[slot]
+        out.columns[slot] = K.Column(c.type, c.data, (rng.random(chunk.n_rows) < frac).astype(np.uint8), None, c.precision, c.scale)
+    return out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,slots", [
+    ("two keys, six aggregates", [Q.L_QUANTITY, Q.L_DISCOUNT, Q.L_TAX]),       # nullable measures: SUM / AVG / COUNT(x) skip NULLs
+    ("two keys, six aggregates", [Q.L_RETURNFLAG_CODE, Q.L_TAX]),               # a nullable key: NULL is a group of its own
+    ("two keys, six aggregates", [Q.L_SHIPDATE, Q.L_EXTENDEDPRICE]),            # a nullable predicate column: NULL never passes a compare
+    ("no group by", [Q.L_QUANTITY, Q.L_EXTENDEDPRICE, Q.L_DISCOUNT, Q.L_TAX]),
+    ("min and max", [Q.L_EXTENDEDPRICE, Q.L_LINESTATUS_CODE]),
+    ("min and max, many groups", [Q.L_EXTENDEDPRICE, Q.L_DISCOUNT, Q.L_ORDERKEY]),
+    ("checked product", [Q.L_TAX, Q.L_DISCOUNT]),
+])
+@pytest.mark.parametrize("frac", [0.02, 0.6])
+def test_compiled_shape_with_nulls_matches_the_oracle(ctx, oracle, jit_sync, name, slots, frac):
+    plan_fn, cols = PLANS[name]
+    chunk = with_nulls(T.host_chunk("lineitem", 0, 600_001, cols), slots, frac)
+    want = K.chunk_rows(oracle.scan_agg(plan_fn(), chunk))
+    got, prof = run_device(ctx, plan_fn(), chunk)
+    assert prof["shape"] == SHAPE_JIT and prof["static_launches"] >= 1, prof
+    assert K.chunk_rows(got) == want

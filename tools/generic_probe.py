@@ -17,6 +17,9 @@ if variant == "nullable":
         keep[f"null{slot}"] = nm
         c = chunk.columns[slot]
         chunk.columns[slot] = K.Column(c.type, c.data, nm.data_ptr(), None, c.precision, c.scale, K.MEM_DEVICE)
+elif variant == "extra":  # two more aggregates than the built-in Q1 shape
+    from tests.test_jit import lineitem_plan
+    plan_fn = lambda: lineitem_plan(charge=True)
 elif variant == "minmax":
     plan_fn = lambda: Q.q1_plan(with_min_max=True)
 elif variant == "binary":
@@ -36,6 +39,6 @@ for it in range(3):
     op.set_finishing()
     out = op.pull_all()
     p = op.profile()
-    print(f"{variant}: {rows} rows, kernel {p['kernel_ms']:.3f} ms, {rows / p['kernel_ms'] / 1e6:.2f} G rows/s, shape {p['shape']}, result rows {out.n_rows}")
+    print(f"{variant}: {rows} rows, kernel {p['kernel_ms']:.3f} ms, {rows / p['kernel_ms'] / 1e6:.2f} G rows/s, shape {p['shape']}, static launches {p['static_launches']}, result rows {out.n_rows}")
     op.close()
 ctx.close()
