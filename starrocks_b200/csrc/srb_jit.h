@@ -155,10 +155,22 @@ inline bool jit_shape_of(const DProg& p, int group_hint, const bool* col_nullabl
     const Geo low_geo[] = {{512, 2}, {512, 1}, {256, 2}, {256, 1}};
     const Geo flat_geo[] = {{512, 4}, {512, 2}, {512, 1}, {256, 1}}; // no GROUP BY: one accumulator set, room for a bigger tile
     const Geo high_geo[] = {{992, 2}, {992, 1}, {480, 2}, {480, 1}};
-    auto pick = [&](const Geo* geo) { // the largest tile that leaves two stages beside the accumulators (the launch takes up to four)
+    if (const char* force = getenv("SRB_JIT_GEO")) { // experiments: "threads,rows[,gmax]"
+        int t = 0, r = 0, g = -1;
+        if (sscanf(force, "%d,%d,%d", &t, &r, &g) >= 2 && t > 0 && t % 32 == 0 && t <= 992 && r >= 1 && r <= 4) {
+            js.threads = t;
+            js.rows = r;
+            js.gmax = g >= 0 ? g : (low ? gmax_want : 0);
+            return jit_acc_bytes(js) + 2 * row_bytes * t * r <= ST_SMEM_BUDGET;
+        }
+    }
+    auto pick = [&](const Geo* geo) { // the largest tile that leaves two stages beside the accumulators (measured: 512 x 2 with a ring of two beats
+                                      // smaller tiles with deeper rings on every Q1 variant; the launch takes up to ST_MAX_STAGES when they fit)
         for (int i = 0; i < 4; i++) {
             js.threads = geo[i].threads;
             js.rows = geo[i].rows;
+            // the end-of-kernel stash ((warp, group) x {lo, hi, nulls} per plane + the row count) is bounded by the kernel's static_assert
+            if (js.gmax > 0 && (js.threads / 32) * js.gmax * (3 * std::max(1, jit_n_reps(js)) + 1) * 8 > 32 * 1024) continue;
             if (jit_acc_bytes(js) + 2 * row_bytes * js.threads * js.rows <= ST_SMEM_BUDGET) return true;
         }
         return false;

@@ -209,7 +209,7 @@ SRB_D void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" :
 SRB_D void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
 // ---- static row pipeline ---------------------------------------------------------------------------------------------------
-constexpr int ST_MAX_STAGES = 4;   // ring depth (the host picks the deepest ring that fits beside the accumulators)
+constexpr int ST_MAX_STAGES = 6;   // ring depth (the host picks the deepest ring that fits beside the accumulators)
 constexpr int ST_SMEM_BUDGET = 226 * 1024; // of the 227 KB a CTA may take; the kernel's static shared data is < 1 KB
 constexpr int ST_MAX_RANGES = 6;   // conjunct predicates after lowering to per-column ranges (more: the generic predicate loop)
 
@@ -751,7 +751,10 @@ constexpr bool shape_has_narrow() {
     }
     for (int a = 0; a < S::N_AGGS; a++) {
         const SAgg g = S::agg(a);
-        if (g.fn == FN_COUNT ? g.arg >= 0 : (g.fn != FN_SUM && g.fn != FN_AVG)) return false;
+        if (g.merge != 0) return false;
+        // every function qualifies: under the narrow assumption nothing is NULL, so COUNT(x) is the row count, and MIN / MAX arguments are
+        // 8-byte values in [0, 2^63)
+        if ((g.fn == FN_MIN || g.fn == FN_MAX) && S::node(g.arg).width != 8) return false;
     }
     for (int k = 0; k < S::N_KEYS; k++)
         if (S::key(k).nullable != 0) return false;
@@ -791,6 +794,7 @@ SRB_D void eval_narrow_node(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const
                 esc |= (uint32_t)(r >> 32);
                 nv[j][I] = (uint32_t)r;
             } else {
+                if constexpr (nd.width == 8) esc |= (uint32_t)(r >> 32) & 0x80000000u; // a checked 8-byte product must stay below 2^63
                 nv[j][I] = r;
             }
         }
@@ -816,13 +820,20 @@ SRB_D PackedKey pack_key_narrow(const uint64_t* nv) {
 template <class S, int A>
 SRB_D void acc_narrow_one(uint8_t* a, uint8_t* trash, const uint64_t* nv, bool on, uint32_t& flag) {
     constexpr SAgg g = S::agg(A);
-    if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
+    if constexpr (plane_kind<S>(A) == 1 && agg_rep<S>(A) == A) {
         constexpr int RI = rep_index<S>(A);
         const uint64_t x = nv[g.arg];
         uint64_t* slot = (uint64_t*)(on ? a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8 : trash);
         const uint64_t old = *slot;
         *slot = old + x;
         flag |= (uint32_t)(old >> 32) | (uint32_t)(x >> 32);
+    } else if constexpr (plane_kind<S>(A) == 2) {
+        // a max plane: the word itself, whatever `on` says (an encoded value has its top bit set: it must stay away from the trash word,
+        // whose top bit the sum planes read as "look for carries")
+        constexpr int RI = rep_index<S>(A);
+        uint64_t* slot = (uint64_t*)(a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8);
+        const uint64_t e = enc_i64((int64_t)nv[g.arg], g.fn == FN_MIN), cur = *slot;
+        *slot = (on && e > cur) ? e : cur;
     }
 }
 // Rare: some word or addend of the warp had bit 63 set. Every add of the tile has already been applied modulo 2^64; the
@@ -837,15 +848,25 @@ struct NarrowFix { // by value into the out-of-line fix-up: the tile's arrays mu
 template <class S, int R, int A>
 SRB_D void narrow_fix_put(NarrowFix<S, R>& f, const uint64_t (&nv)[R][S::N_NODES]) {
     constexpr SAgg g = S::agg(A);
-    if constexpr ((g.fn == FN_SUM || g.fn == FN_AVG) && agg_rep<S>(A) == A) {
+    if constexpr (plane_kind<S>(A) == 1 && agg_rep<S>(A) == A) {
 #pragma unroll
         for (int j = 0; j < R; j++) f.x[j][rep_index<S>(A)] = nv[j][g.arg];
     }
 }
+template <class S>
+struct MaxPlaneMask { // bit ri: plane ri is a max plane (encodings, not sums: nothing to carry)
+    static constexpr uint32_t value() {
+        uint32_t m = 0;
+        for (int ri = 0; ri < AccGeom<S>::NR; ri++) m |= plane_is_max<S>(ri) ? (1u << ri) : 0u;
+        return m;
+    }
+};
 template <class S, int R>
 static __device__ __noinline__ void acc_narrow_fixup(RareAcc<S>* ra, uint8_t* acc_tid, uint8_t* trash, const NarrowFix<S, R> f) {
     constexpr int NR = AccGeom<S>::NR;
+    constexpr uint32_t max_planes = MaxPlaneMask<S>::value();
     for (int ri = 0; ri < NR; ri++) {
+        if ((max_planes >> ri) & 1u) continue;
         for (int j = R - 1; j >= 0; j--) {
             if (!f.on[j]) continue;
             const uint64_t* slot = (const uint64_t*)(acc_tid + (size_t)f.gid[j] * (S::THREADS * 8) + (size_t)ri * AccGeom<S>::G * S::THREADS * 8);
@@ -965,7 +986,8 @@ struct Flusher {
             if (rows_total) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)rows_total);
         } else {
             constexpr int RI = rep_index<S>(agg_rep<S>(A));
-            const uint64_t n = plane_counts<S>(agg_rep<S>(A)) ? tot[RI * 3 + 2] : rows_total - tot[RI * 3 + 2];
+            constexpr bool counts = plane_counts<S>(agg_rep<S>(A));
+            const uint64_t n = counts ? tot[RI * 3 + 2] : rows_total - tot[RI * 3 + 2];
             if (n) {
                 if constexpr (g.fn == FN_COUNT) {
                     atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)n);
@@ -980,6 +1002,23 @@ struct Flusher {
         }
     }
     // step 2, one thread: totals of group q over the warps -> table slot
+    // one warp's stash entry of plane RI into the running totals (which kind of plane it is must be a compile-time fact: evaluated per call,
+    // the constexpr walks over the aggregate list cost more than the rest of the kernel's epilogue)
+    template <int RI>
+    static __device__ __forceinline__ void fold_plane(uint64_t* tot, const uint64_t* st) {
+        if constexpr (plane_is_max<S>(RI)) {
+            tot[RI * 3] = st[RI * 3] > tot[RI * 3] ? st[RI * 3] : tot[RI * 3];
+        } else {
+            const uint64_t lo = tot[RI * 3] + st[RI * 3];
+            tot[RI * 3 + 1] += st[RI * 3 + 1] + (lo < st[RI * 3] ? 1ULL : 0ULL);
+            tot[RI * 3] = lo;
+        }
+        tot[RI * 3 + 2] += st[RI * 3 + 2];
+    }
+    template <int... RI>
+    static __device__ __forceinline__ void fold_planes(uint64_t* tot, const uint64_t* st, iseq<RI...>) {
+        (fold_plane<RI>(tot, st), ...);
+    }
     template <int... A>
     static __device__ __forceinline__ void fold(const DProg& p, const uint64_t* stash_base, int q, uint8_t* slot, iseq<A...>) {
         uint64_t tot[WORDS];
@@ -987,17 +1026,7 @@ struct Flusher {
         for (int k = 0; k < WORDS; k++) tot[k] = 0;
         for (int w = 0; w < S::THREADS / 32; w++) {
             const uint64_t* st = stash_base + (size_t)(w * G + q) * WORDS;
-#pragma unroll
-            for (int r = 0; r < NR; r++) {
-                if (plane_is_max<S>(r)) {
-                    tot[r * 3] = st[r * 3] > tot[r * 3] ? st[r * 3] : tot[r * 3];
-                } else {
-                    const uint64_t lo = tot[r * 3] + st[r * 3];
-                    tot[r * 3 + 1] += st[r * 3 + 1] + (lo < st[r * 3] ? 1ULL : 0ULL);
-                    tot[r * 3] = lo;
-                }
-                tot[r * 3 + 2] += st[r * 3 + 2];
-            }
+            fold_planes(tot, st, make_iseq<NR>{});
             tot[3 * NR] += st[3 * NR];
         }
         (emit<A>(p, slot, tot, tot[3 * NR]), ...);
@@ -1243,23 +1272,35 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
     unsigned long long deferred = 0, inserted = 0;
     if (tid >= THREADS) {
         // ---- producer warp ----
-        if (tid == THREADS) {
-            int s = 0;
-            uint32_t parity = 1; // a fresh mbarrier passes a wait on parity 1: the first lap needs no arrivals
-            for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        // Lane c issues column c's bulk copy, lane 16 + c the copy of its null map: a tile's copies leave in one instruction slot instead of
+        // one after the other from a single thread (with 7-9 copies per 22 KB stage the lone thread could not keep the ring full).
+        static_assert(MAX_COLS <= 16, "one producer lane per column and per null map");
+        const int lane = tid - THREADS;
+        const uint8_t* src = nullptr; // this lane's source at row `base`, nullptr: nothing to copy
+        uint32_t tile_bytes = 0;
+        int dst_off = 0;
+        if (lane < p.n_cols) {
+            const int w = p.cols[lane].width;
+            src = (const uint8_t*)p.cols[lane].data + (size_t)base * w;
+            tile_bytes = (uint32_t)(TILE * w);
+            dst_off = sa.col_off[lane];
+        } else if (lane >= 16 && lane - 16 < p.n_cols && sa.null_off[lane - 16] >= 0) {
+            src = p.cols[lane - 16].nulls + (size_t)base;
+            tile_bytes = (uint32_t)TILE;
+            dst_off = sa.null_off[lane - 16];
+        }
+        int s = 0;
+        uint32_t parity = 1; // a fresh mbarrier passes a wait on parity 1: the first lap needs no arrivals
+        for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            if (lane == 0) {
                 mbar_wait(&empty_bar[s], parity);
                 mbar_expect_tx(&full_bar[s], (uint32_t)stage_bytes);
-                uint8_t* dst = smem + (size_t)s * stage_bytes;
-                for (int c = 0; c < p.n_cols; c++) {
-                    const int w = p.cols[c].width;
-                    tma_load_1d(dst + sa.col_off[c], (const uint8_t*)p.cols[c].data + (size_t)(base + tile * TILE) * w, (uint32_t)(TILE * w),
-                                &full_bar[s]);
-                    if (sa.null_off[c] >= 0) tma_load_1d(dst + sa.null_off[c], p.cols[c].nulls + (size_t)(base + tile * TILE), (uint32_t)TILE, &full_bar[s]);
-                }
-                if (++s == n_stages) {
-                    s = 0;
-                    parity ^= 1u;
-                }
+            }
+            __syncwarp(); // the stage is free and its byte count registered before any copy can complete
+            if (src) tma_load_1d(smem + (size_t)s * stage_bytes + dst_off, src + (size_t)tile * tile_bytes, tile_bytes, &full_bar[s]);
+            if (++s == n_stages) {
+                s = 0;
+                parity ^= 1u;
             }
         }
     } else {

@@ -64,7 +64,8 @@ def q6_plan(phase: int = K.AGG_UPDATE_FINALIZE) -> ScanAggPlan:
     return ScanAggPlan(preds=preds, exprs=e, aggs=[(K.AGG_SUM, prod)], phase=phase)
 
 
-def q1_plan(dict_keys: bool = True, phase: int = K.AGG_UPDATE_FINALIZE, group_hint: int = 4, with_min_max: bool = False) -> ScanAggPlan:
+def q1_plan(dict_keys: bool = True, phase: int = K.AGG_UPDATE_FINALIZE, group_hint: int = 4, with_min_max: bool = False,
+            more_aggs: bool = False) -> ScanAggPlan:
     """select l_returnflag, l_linestatus, sum(qty), sum(ext), sum(ext*(1-disc)), sum(ext*(1-disc)*(1+tax)),
               avg(qty), avg(ext), avg(disc), count(*) from lineitem where l_shipdate <= '1998-09-02' group by 1, 2"""
     e = ExprBuilder()
@@ -87,6 +88,8 @@ def q1_plan(dict_keys: bool = True, phase: int = K.AGG_UPDATE_FINALIZE, group_hi
             (K.AGG_AVG, qty), (K.AGG_AVG, ext), (K.AGG_AVG, disc), (K.AGG_COUNT, None)]
     if with_min_max:  # a ninth and tenth aggregate: the plan no longer matches a static shape
         aggs += [(K.AGG_MIN, ext), (K.AGG_MAX, ext)]
+    if more_aggs:  # Q1 as someone else would have written it: two more aggregates, one of them COUNT(x)
+        aggs += [(K.AGG_SUM, tax), (K.AGG_COUNT, tax)]
     preds = [pred(L_SHIPDATE, K.PRED_LE, K.TYPE_DATE, from_date(1998, 9, 2))]
     return ScanAggPlan(preds=preds, exprs=e, keys=[k1, k2], aggs=aggs, phase=phase, group_hint=group_hint)
 
