@@ -818,10 +818,9 @@ def bench_scan(env, args, query: str, steps: int, warmup: int, scaling: str, ten
 def bench_q1_variants(env, args, tensors, steps: int, warmup: int):
     """Q1 as a real BE would hand it over — none of these matches a built-in kernel shape: VARCHAR(1) group keys as BinaryColumns
     (AggHashMapWithSerializedKey, agg_hash_map.h:652-898; 46 B/row in SURVEY 8d), nullable measures (null maps that do hold NULLs), one
-    extra MIN / MAX, two more aggregates. The last three get the static TMA-staged kernel compiled for them at run time (csrc/srb_jit.h;
-    the first step starts the compilation, srb_jit_wait() waits for it, the timed steps run the compiled kernel); binary keys stay on the
-    interpreter (k_scan_agg_generic). Every variant is also run once with SRB_JIT=off: same rows, and the interpreter's time for the record
-    (VERDICT r1, weak #8)."""
+    extra MIN / MAX, two more aggregates. Each gets the static TMA-staged kernel compiled for it at run time (csrc/srb_jit.h; the first step
+    starts the compilation, srb_jit_wait() waits for it, the timed steps run the compiled kernel). Every variant is also run with SRB_JIT=off
+    first: same rows, and the interpreter's (k_scan_agg_generic) time for the record (VERDICT r1, weak #8)."""
     import numpy as np
     from starrocks_b200 import capi as K, ops, queries as Q, tpch_synth as T
     from starrocks_b200.plan import ExprBuilder, ScanAggPlan, pred

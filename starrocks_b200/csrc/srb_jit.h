@@ -106,24 +106,35 @@ inline bool jit_shape_of(const DProg& p, int group_hint, const bool* col_nullabl
     js.n_nodes = p.n_nodes;
     js.n_aggs = p.n_aggs;
     js.n_keys = p.n_keys;
-    int row_bytes = 0;
+    int row_bytes = 0; // stage bytes per row (binary key columns: 4 bytes of offsets + 8 of window, and ~64 bytes per tile that the slack below covers)
+    bool binary_col[MAX_COLS] = {};
     for (int c = 0; c < p.n_cols; c++) {
+        if (p.cols[c].kind == CK_BINARY) {
+            binary_col[c] = true;
+            row_bytes += 12 + (col_nullable && col_nullable[c] ? 1 : 0);
+            continue;
+        }
         if (p.cols[c].kind != CK_INT || p.cols[c].width < 1 || p.cols[c].width > 16) return false;
         row_bytes += p.cols[c].width + (col_nullable && col_nullable[c] ? 1 : 0);
     }
+    for (int i = 0; i < p.n_preds; i++)
+        if (binary_col[p.preds[i].col]) return false; // string predicates: the interpreter's
     bool col_seen[MAX_COLS] = {};
     for (int i = 0; i < p.n_nodes; i++) {
         const DNode& d = p.nodes[i];
-        if (d.kind != CK_INT) return false;
         if (d.op < DOP_LOAD || d.op > DOP_MULFAST) return false;
         if (d.op == DOP_LOAD) {
-            if (d.col < 0 || d.col >= p.n_cols || col_seen[d.col] || p.cols[d.col].width != d.width) return false; // one LOAD per column
+            if (d.col < 0 || d.col >= p.n_cols || col_seen[d.col]) return false; // one LOAD per column
+            if (binary_col[d.col] ? d.kind != CK_BINARY : (d.kind != CK_INT || p.cols[d.col].width != d.width)) return false;
             col_seen[d.col] = true;
+        } else if (d.kind != CK_INT) {
+            return false;
         } else if (d.op != DOP_LIT) {
             if (d.lhs < 0 || d.lhs >= i || (d.op != DOP_CAST && (d.rhs < 0 || d.rhs >= i))) return false;
         }
         const bool leaf = d.op == DOP_LOAD || d.op == DOP_LIT;
-        js.nodes[i] = SNode{d.op, d.width, leaf ? -1 : d.lhs, (leaf || d.op == DOP_CAST) ? -1 : d.rhs, leaf ? 0 : d.checked,
+        if (!leaf && (p.nodes[d.lhs].kind != CK_INT || (d.op != DOP_CAST && p.nodes[d.rhs].kind != CK_INT))) return false; // strings are keys only
+        js.nodes[i] = SNode{d.op, (d.op == DOP_LOAD && binary_col[d.col]) ? 0 : d.width, leaf ? -1 : d.lhs, (leaf || d.op == DOP_CAST) ? -1 : d.rhs, leaf ? 0 : d.checked,
                             (leaf || d.op == DOP_CAST) ? 0 : d.adj_l, (leaf || d.op == DOP_CAST) ? 0 : d.adj_r,
                             (d.op == DOP_LOAD && col_nullable && col_nullable[d.col]) ? 1 : 0};
     }
@@ -135,16 +146,26 @@ inline bool jit_shape_of(const DProg& p, int group_hint, const bool* col_nullabl
         if (d.merge && d.fn == FN_AVG) return false; // {sum, count} blobs: the interpreter's job
         if (d.fn != FN_COUNT && (d.arg < 0 || d.arg >= p.n_nodes)) return false;
         if (d.arg >= p.n_nodes) return false;
+        if (d.arg >= 0 && p.nodes[d.arg].kind != CK_INT) return false;
         js.aggs[a] = SAgg{d.fn, d.arg, d.off_hi >= 0 ? 1 : 0, d.off_n >= 0 ? 1 : 0, d.merge ? 1 : 0};
     }
     int key_bytes = 0;
     for (int k = 0; k < p.n_keys; k++) {
         const DKey& d = p.keys[k];
-        if (p.n_keys > 4 || d.width < 1 || d.width > 8 || d.node < 0 || d.node >= p.n_nodes || p.nodes[d.node].op != DOP_LOAD) return false;
+        if (p.n_keys > 4 || d.width < 0 || d.width > 8 || d.node < 0 || d.node >= p.n_nodes || p.nodes[d.node].op != DOP_LOAD) return false;
+        if ((d.width == 0) != (p.nodes[d.node].kind == CK_BINARY)) return false;
         js.keys[k] = SKey{d.node, d.width, d.nullable ? 1 : 0};
-        key_bytes += d.width + (d.nullable ? 1 : 0);
+        key_bytes += (d.width ? d.width : 4) + (d.nullable ? 1 : 0);
     }
     if (key_bytes > 16) return false;
+    for (int i = 0; i < p.n_nodes; i++) { // a binary column is loaded for one purpose: being a group key
+        if (p.nodes[i].op != DOP_LOAD || !binary_col[p.nodes[i].col]) continue;
+        bool is_key = false;
+        for (int k = 0; k < p.n_keys; k++) is_key = is_key || p.keys[k].node == i;
+        if (!is_key) return false;
+    }
+    for (int c = 0; c < p.n_cols; c++)
+        if (binary_col[c] && !col_seen[c]) return false;
     // geometry: few groups (the planner's estimate) -> per-thread accumulators and a CTA directory of GMAX groups; otherwise every row goes to
     // the table. Threads x rows per tile: the largest tile that leaves room for >= 2 stages (3 when it can) beside the accumulators.
     const bool low = p.n_keys == 0 || (group_hint > 0 && group_hint <= 16);
@@ -171,7 +192,7 @@ inline bool jit_shape_of(const DProg& p, int group_hint, const bool* col_nullabl
             js.rows = geo[i].rows;
             // the end-of-kernel stash ((warp, group) x {lo, hi, nulls} per plane + the row count) is bounded by the kernel's static_assert
             if (js.gmax > 0 && (js.threads / 32) * js.gmax * (3 * std::max(1, jit_n_reps(js)) + 1) * 8 > 32 * 1024) continue;
-            if (jit_acc_bytes(js) + 2 * row_bytes * js.threads * js.rows <= ST_SMEM_BUDGET) return true;
+            if (jit_acc_bytes(js) + 2 * (row_bytes * js.threads * js.rows + 64 * MAX_KEYS) <= ST_SMEM_BUDGET) return true;
         }
         return false;
     };

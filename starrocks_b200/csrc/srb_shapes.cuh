@@ -220,13 +220,31 @@ constexpr int tile_rows() {
 }
 // LOAD nodes own the leading columns of a stage, in node order: their offsets are compile-time constants, so a row's
 // operands are fetched with LDS [row_base + immediate]
+// A BinaryColumn (LOAD of width 0; group keys only) is staged as its u32 offsets — tile + 1 of them, padded to tile + 4 for the 16-byte
+// granularity of bulk copies — and a window of its bytes (bin_window_bytes) whose position the producer decides per tile.
+constexpr int bin_window_bytes(int tile) { return tile * 8 + 32; }
+template <class S>
+constexpr int load_bytes(int node) {
+    return S::node(node).width == 0 ? 4 * tile_rows<S>() + 16 : S::node(node).width * tile_rows<S>();
+}
 template <class S>
 constexpr int load_off(int node) {
     int off = 0;
     for (int j = 0; j < node; j++)
-        if (S::node(j).op == DOP_LOAD) off += S::node(j).width * tile_rows<S>();
+        if (S::node(j).op == DOP_LOAD) off += load_bytes<S>(j);
     return off;
 }
+template <class S>
+constexpr bool shape_has_binary() {
+    for (int i = 0; i < S::N_NODES; i++)
+        if (S::node(i).op == DOP_LOAD && S::node(i).width == 0) return true;
+    return false;
+}
+// where the bytes of the binary key columns of the current tile are: base[k] + (a value's offset in the column) is its first byte,
+// whether the window was staged or (it did not fit) the bytes are read from the column itself
+struct TileBin {
+    const uint8_t* base[4];
+};
 
 // A conjunct (or several on one column) lowered to "lo <= v <= lo + span" (unsigned compare after the subtraction),
 // optionally negated: one subtract and one compare per row whatever the operator was.
@@ -255,6 +273,8 @@ struct StaticArgs { // host-computed tile layout: column c sits at col_off[c] in
     int32_t col_off[MAX_COLS];
     int32_t null_off[MAX_COLS];       // its null map (one byte per row), -1: none
     int32_t node_null_off[MAX_NODES]; // the same offset by LOAD node (a compile-time index in the kernel)
+    int32_t bin_win_off[MAX_COLS];    // binary column: its byte window inside a stage, -1: not binary
+    int32_t bin_hdr_off[MAX_COLS];    // and the 16-byte header the producer writes per tile: {u32 window start in the column, u32 overflow}
     int32_t stage_bytes;
     int32_t n_stages;
     int32_t n_preds;
@@ -396,7 +416,17 @@ template <class S, int I, int R>
 SRB_D void eval_static_node(const DProg& p, const StaticArgs& sa, Val (&v)[R][S::N_NODES], const uint8_t* stage, int r0) {
     constexpr SNode nd = S::node(I);
     const DNode& rt = p.nodes[I];
-    if constexpr (nd.op == DOP_LOAD) {
+    if constexpr (nd.op == DOP_LOAD && nd.width == 0) { // a BinaryColumn value: (offset of its first byte, length)
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const uint32_t* o = (const uint32_t*)(stage + load_off<S>(I)) + r0 + j * S::THREADS;
+            const uint32_t b = o[0], e = o[1];
+            v[j][I].lo = b;
+            v[j][I].hi = (int64_t)(e - b);
+            v[j][I].null = false;
+            if constexpr (nd.nullable != 0) v[j][I].null = stage[sa.node_null_off[I] + r0 + j * S::THREADS] != 0;
+        }
+    } else if constexpr (nd.op == DOP_LOAD) {
 #pragma unroll
         for (int j = 0; j < R; j++) {
             v[j][I] = lds_val<nd.width>(stage + load_off<S>(I), r0 + j * S::THREADS);
@@ -734,7 +764,7 @@ constexpr bool shape_has_narrow() {
         if (key && (nd.op != DOP_LOAD || node_is_operand<S>(i))) return false; // keys: plain columns, bits taken as they are
         switch (nd.op) {
         case DOP_LOAD:
-            if (nd.nullable != 0 || (nd.width != 8 && !(key && nd.width == 4))) return false;
+            if (nd.nullable != 0 || (nd.width != 8 && !(key && (nd.width == 4 || nd.width == 0)))) return false;
             break;
         case DOP_LIT: break;
         case DOP_CAST:
@@ -763,7 +793,14 @@ constexpr bool shape_has_narrow() {
 template <class S, int I, int R>
 SRB_D void eval_narrow_node(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const uint8_t* stage, int r0, uint32_t& esc) {
     constexpr SNode nd = S::node(I);
-    if constexpr (nd.op == DOP_LOAD && nd.width == 4) {
+    if constexpr (nd.op == DOP_LOAD && nd.width == 0) { // a binary key: (length << 32) | offset
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const uint32_t* o = (const uint32_t*)(stage + load_off<S>(I)) + r0 + j * S::THREADS;
+            const uint32_t b = o[0], e = o[1];
+            nv[j][I] = ((uint64_t)(e - b) << 32) | b;
+        }
+    } else if constexpr (nd.op == DOP_LOAD && nd.width == 4) {
 #pragma unroll
         for (int j = 0; j < R; j++) nv[j][I] = ((const uint32_t*)(stage + load_off<S>(I)))[r0 + j * S::THREADS]; // key bits
     } else if constexpr (nd.op == DOP_LOAD) {
@@ -804,13 +841,28 @@ template <class S, int R, int... I>
 SRB_D void eval_narrow_all(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const uint8_t* stage, int r0, uint32_t& esc, iseq<I...>) {
     (eval_narrow_node<S, I, R>(p, nv, stage, r0, esc), ...);
 }
+// [u32 length][bytes] of a BinaryColumn value (BinaryColumn::serialize, column/binary_column.h:228-237); a key beyond 16 bytes sets too_long
+SRB_D void key_put_binary(PackedKey& k, const uint8_t* first, uint32_t len) {
+    key_put(k, len, 4);
+    for (uint32_t j = 0; j < len && !k.too_long; j++) key_put(k, first[j], 1);
+}
+template <class S, int KI>
+SRB_D void key_put_narrow(PackedKey& k, const uint64_t* nv, const TileBin& tb) {
+    if constexpr (KI < S::N_KEYS) {
+        constexpr SKey kd = S::key(KI);
+        if constexpr (kd.width == 0)
+            key_put_binary(k, tb.base[KI] + (uint32_t)nv[kd.node], (uint32_t)(nv[kd.node] >> 32));
+        else
+            key_put(k, nv[kd.node], kd.width);
+    }
+}
 template <class S>
-SRB_D PackedKey pack_key_narrow(const uint64_t* nv) {
+SRB_D PackedKey pack_key_narrow(const uint64_t* nv, const TileBin& tb) {
     PackedKey k{0, 0, 0, false};
-    if constexpr (S::N_KEYS >= 1) key_put(k, nv[S::key(0).node], S::key(0).width);
-    if constexpr (S::N_KEYS >= 2) key_put(k, nv[S::key(1).node], S::key(1).width);
-    if constexpr (S::N_KEYS >= 3) key_put(k, nv[S::key(2).node], S::key(2).width);
-    if constexpr (S::N_KEYS >= 4) key_put(k, nv[S::key(3).node], S::key(3).width);
+    key_put_narrow<S, 0>(k, nv, tb);
+    key_put_narrow<S, 1>(k, nv, tb);
+    key_put_narrow<S, 2>(k, nv, tb);
+    key_put_narrow<S, 3>(k, nv, tb);
     return k;
 }
 
@@ -1064,7 +1116,10 @@ SRB_D void row_update_global(const DProg& p, uint8_t* slot, const Val* v, iseq<A
 template <class S>
 constexpr int static_key_bytes() {
     int n = 0;
-    for (int k = 0; k < S::N_KEYS; k++) n += S::key(k).width + (S::key(k).nullable != 0 ? 1 : 0);
+    for (int k = 0; k < S::N_KEYS; k++) {
+        if (S::key(k).width == 0) return 0; // a binary key: the packed length is a per-row fact (PackedKey::len)
+        n += S::key(k).width + (S::key(k).nullable != 0 ? 1 : 0);
+    }
     return n;
 }
 // hash of a packed key whose length is a compile-time constant (same functions as hash_packed_key)
@@ -1078,11 +1133,18 @@ SRB_D uint64_t hash_packed_key_static(const PackedKey& k, int seed) {
 
 // key column K of the packed key: [null byte if the column is nullable][value, zero when NULL] (pack_key of srb_rowpipe.cuh)
 template <class S, int KI>
-SRB_D void key_put_static(PackedKey& k, const Val* v) {
+SRB_D void key_put_static(PackedKey& k, const Val* v, const TileBin& tb) {
     if constexpr (KI < S::N_KEYS) {
         constexpr SKey kd = S::key(KI);
         const Val& x = v[kd.node];
-        if constexpr (kd.nullable != 0) {
+        if constexpr (kd.width == 0) {
+            bool isnull = false;
+            if constexpr (kd.nullable != 0) {
+                isnull = x.null;
+                key_put(k, isnull ? 1 : 0, 1);
+            }
+            key_put_binary(k, tb.base[KI] + (uint32_t)x.lo, isnull ? 0u : (uint32_t)x.hi);
+        } else if constexpr (kd.nullable != 0) {
             key_put(k, x.null ? 1 : 0, 1);
             key_put(k, x.null ? 0ULL : x.lo, kd.width);
         } else {
@@ -1091,13 +1153,36 @@ SRB_D void key_put_static(PackedKey& k, const Val* v) {
     }
 }
 template <class S>
-SRB_D PackedKey pack_key_static(const Val* v) {
+SRB_D PackedKey pack_key_static(const Val* v, const TileBin& tb) {
     PackedKey k{0, 0, 0, false};
-    key_put_static<S, 0>(k, v);
-    key_put_static<S, 1>(k, v);
-    key_put_static<S, 2>(k, v);
-    key_put_static<S, 3>(k, v);
+    key_put_static<S, 0>(k, v, tb);
+    key_put_static<S, 1>(k, v, tb);
+    key_put_static<S, 2>(k, v, tb);
+    key_put_static<S, 3>(k, v, tb);
     return k;
+}
+// the current tile's byte sources of the binary key columns, from the headers the producer wrote into the stage
+template <class S, int KI>
+SRB_D void tile_bin_one(TileBin& tb, const DProg& p, const StaticArgs& sa, const uint8_t* stage) {
+    if constexpr (KI < S::N_KEYS) {
+        if constexpr (S::key(KI).width == 0) {
+            const int c = p.nodes[S::key(KI).node].col;
+            const uint2 hdr = *(const uint2*)(stage + sa.bin_hdr_off[c]);
+            tb.base[KI] = hdr.y ? (const uint8_t*)p.cols[c].data
+                                : (const uint8_t*)((uintptr_t)(stage + sa.bin_win_off[c]) - (uintptr_t)hdr.x); // + a value's offset >= hdr.x: inside the window
+        }
+    }
+}
+template <class S>
+SRB_D TileBin tile_bin(const DProg& p, const StaticArgs& sa, const uint8_t* stage) {
+    TileBin tb{};
+    if constexpr (shape_has_binary<S>()) {
+        tile_bin_one<S, 0>(tb, p, sa, stage);
+        tile_bin_one<S, 1>(tb, p, sa, stage);
+        tile_bin_one<S, 2>(tb, p, sa, stage);
+        tile_bin_one<S, 3>(tb, p, sa, stage);
+    }
+    return tb;
 }
 
 struct StaticCtr {
@@ -1129,7 +1214,7 @@ SRB_D bool dir_has(const GroupDir<G>* d, int c, uint64_t klo, uint64_t khi) {
 // insert by this lane. Out of line: it runs a handful of times per CTA.
 template <int G, int KEYLEN>
 static __device__ __noinline__ int dir_resolve(GroupDir<G>* d, uint8_t* slots, uint64_t mask, int slot_bytes, int key_words, uint64_t klo, uint64_t khi,
-                                               int seed, bool need) {
+                                               int klen, int seed, bool need) {
     const unsigned need_mask = __ballot_sync(0xffffffffu, need);
     const unsigned peers = __match_any_sync(0xffffffffu, klo ^ (khi * 0x9e3779b97f4a7c15ULL)) & need_mask;
     int inserted = 0;
@@ -1141,7 +1226,7 @@ static __device__ __noinline__ int dir_resolve(GroupDir<G>* d, uint8_t* slots, u
                 const int c2 = *(volatile int*)&d->cnt;
                 if (c2 < G && !dir_has(d, c2, klo, khi)) {
                     const TableView tv{slots, mask, slot_bytes, key_words};
-                    PackedKey k{klo, khi, KEYLEN, false};
+                    PackedKey k{klo, khi, KEYLEN ? KEYLEN : klen, false}; // KEYLEN 0: binary keys, the length travels with the row
                     bool fresh;
                     uint8_t* sl = table_find_or_insert(tv, klo, khi, hash_packed_key_static<KEYLEN>(k, seed), &fresh);
                     inserted = fresh ? 1 : 0;
@@ -1201,9 +1286,9 @@ SRB_D void row_update_args_one(const DProg& p, uint8_t* slot, const AggArgs<S>& 
 }
 template <class S, int... A>
 static __device__ __noinline__ int global_row_cold(const DProg* pp, uint8_t* slots, uint64_t mask, int slot_bytes, int key_words, uint64_t klo, uint64_t khi,
-                                                   AggArgs<S> x, iseq<A...>) {
+                                                   int klen, AggArgs<S> x, iseq<A...>) {
     const TableView tv{slots, mask, slot_bytes, key_words};
-    const PackedKey k{klo, khi, static_key_bytes<S>(), false};
+    const PackedKey k{klo, khi, static_key_bytes<S>() ? static_key_bytes<S>() : klen, false};
     bool fresh;
     uint8_t* slot = table_find_or_insert(tv, klo, khi, hash_packed_key_static<static_key_bytes<S>()>(k, pp->phase_seed), &fresh);
     if (!slot) return 2;
@@ -1224,7 +1309,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
     constexpr int R = S::ROWS;
     constexpr int TILE = tile_rows<S>();
     constexpr int G = AccGeom<S>::G;
-    constexpr int KW = static_key_bytes<S>() > 8 ? 2 : 1;
+    constexpr int KW = (static_key_bytes<S>() > 8 || (S::N_KEYS > 0 && static_key_bytes<S>() == 0)) ? 2 : 1; // binary keys: always two words
     static_assert(THREADS % 32 == 0 && THREADS + 32 <= 1024 && (TILE * 1) % 16 == 0, "block / tile geometry");
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ uint64_t full_bar[ST_MAX_STAGES], empty_bar[ST_MAX_STAGES];
@@ -1277,27 +1362,73 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
         static_assert(MAX_COLS <= 16, "one producer lane per column and per null map");
         const int lane = tid - THREADS;
         const uint8_t* src = nullptr; // this lane's source at row `base`, nullptr: nothing to copy
-        uint32_t tile_bytes = 0;
+        uint32_t tile_bytes = 0, tile_stride = 0; // bytes copied per tile, and how far the source moves from tile to tile
         int dst_off = 0;
+        // a binary column: the lane copies tile + 4 of its offsets and, per tile, the 16-byte aligned window of its bytes that the tile's rows
+        // reference (bin_window_bytes at most; a tile of longer strings is flagged and its consumers read the column itself)
+        const uint32_t* goffs = nullptr;
+        const uint8_t* gdata = nullptr;
+        int win_off = 0, hdr_off = 0;
         if (lane < p.n_cols) {
-            const int w = p.cols[lane].width;
-            src = (const uint8_t*)p.cols[lane].data + (size_t)base * w;
-            tile_bytes = (uint32_t)(TILE * w);
+            if (shape_has_binary<S>() && p.cols[lane].kind == CK_BINARY) {
+                goffs = p.cols[lane].offsets + base;
+                gdata = (const uint8_t*)p.cols[lane].data;
+                src = (const uint8_t*)goffs;
+                tile_bytes = (uint32_t)(TILE * 4 + 16);
+                tile_stride = (uint32_t)(TILE * 4);
+                win_off = sa.bin_win_off[lane];
+                hdr_off = sa.bin_hdr_off[lane];
+            } else {
+                const int w = p.cols[lane].width;
+                src = (const uint8_t*)p.cols[lane].data + (size_t)base * w;
+                tile_bytes = tile_stride = (uint32_t)(TILE * w);
+            }
             dst_off = sa.col_off[lane];
         } else if (lane >= 16 && lane - 16 < p.n_cols && sa.null_off[lane - 16] >= 0) {
             src = p.cols[lane - 16].nulls + (size_t)base;
-            tile_bytes = (uint32_t)TILE;
+            tile_bytes = tile_stride = (uint32_t)TILE;
             dst_off = sa.null_off[lane - 16];
+        }
+        uint32_t nb = 0, ne = 0; // first and one-past-last byte of the NEXT tile's strings (fetched one tile ahead: the load's latency is off the ring's path)
+        if (goffs && (int64_t)blockIdx.x < n_tiles) {
+            nb = goffs[(size_t)blockIdx.x * TILE];
+            ne = goffs[(size_t)blockIdx.x * TILE + TILE];
         }
         int s = 0;
         uint32_t parity = 1; // a fresh mbarrier passes a wait on parity 1: the first lap needs no arrivals
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-            if (lane == 0) {
-                mbar_wait(&empty_bar[s], parity);
-                mbar_expect_tx(&full_bar[s], (uint32_t)stage_bytes);
+            uint32_t total = (uint32_t)stage_bytes, wb = 0, wlen = 0;
+            bool ovf = false;
+            if constexpr (shape_has_binary<S>()) {
+                uint32_t mine = src ? tile_bytes : 0u;
+                if (goffs) {
+                    wb = nb & ~15u;
+                    wlen = (ne - wb + 15u) & ~15u;
+                    ovf = wlen > (uint32_t)bin_window_bytes(TILE);
+                    mine += ovf ? 0u : wlen;
+                }
+                total = __reduce_add_sync(0xffffffffu, mine);
             }
-            __syncwarp(); // the stage is free and its byte count registered before any copy can complete
-            if (src) tma_load_1d(smem + (size_t)s * stage_bytes + dst_off, src + (size_t)tile * tile_bytes, tile_bytes, &full_bar[s]);
+            if (lane == 0) mbar_wait(&empty_bar[s], parity);
+            __syncwarp(); // the stage is free
+            uint8_t* dst = smem + (size_t)s * stage_bytes;
+            if constexpr (shape_has_binary<S>()) {
+                if (goffs) *(uint2*)(dst + hdr_off) = make_uint2(wb, ovf ? 1u : 0u);
+                __syncwarp(); // the headers are written before lane 0's arrive releases them to the consumers
+            }
+            if (lane == 0) mbar_expect_tx(&full_bar[s], total);
+            __syncwarp(); // the byte count is registered before any copy can complete
+            if (src) tma_load_1d(dst + dst_off, src + (size_t)tile * tile_stride, tile_bytes, &full_bar[s]);
+            if constexpr (shape_has_binary<S>()) {
+                if (goffs) {
+                    if (!ovf && wlen) tma_load_1d(dst + win_off, gdata + wb, wlen, &full_bar[s]);
+                    const int64_t next = tile + gridDim.x;
+                    if (next < n_tiles) {
+                        nb = goffs[(size_t)next * TILE];
+                        ne = goffs[(size_t)next * TILE + TILE];
+                    }
+                }
+            }
             if (++s == n_stages) {
                 s = 0;
                 parity ^= 1u;
@@ -1346,6 +1477,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                 any_pass = any_pass || pass[j];
             }
             bool done = false; // warp-uniform: the narrow body handled this tile
+            const TileBin tb = tile_bin<S>(p, sa, stage);
             if constexpr (shape_has_narrow<S>() && S::N_KEYS > 0) {
                 if (sa.narrow_ok && __any_sync(0xffffffffu, any_pass)) {
                     uint64_t nv[R][S::N_NODES];
@@ -1355,12 +1487,12 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                     bool bad = esc != 0;
 #pragma unroll
                     for (int j = 0; j < R; j++) {
-                        const PackedKey k = pack_key_narrow<S>(nv[j]);
+                        const PackedKey k = pack_key_narrow<S>(nv[j], tb);
                         gid[j] = G;
 #pragma unroll
                         for (int q = G - 1; q >= 0; q--)
                             if (kd_lo[q] == k.lo && (KW == 1 || kd_hi[q] == k.hi)) gid[j] = q;
-                        bad = bad || (pass[j] && gid[j] >= my_cnt);
+                        bad = bad || (pass[j] && (gid[j] >= my_cnt || k.too_long));
                         if (gid[j] >= my_cnt) gid[j] = 0;
                     }
                     if (!__any_sync(0xffffffffu, bad)) {
@@ -1382,7 +1514,15 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                     bool miss[R]; // row j still has to reach its group
 #pragma unroll
                     for (int j = 0; j < R; j++) {
-                        k[j] = pack_key_static<S>(v[j]);
+                        k[j] = pack_key_static<S>(v[j], tb);
+                        if constexpr (shape_has_binary<S>()) {
+                            if (k[j].too_long && pass[j]) { // a serialized key beyond 16 bytes: the row is left to the replay, which reports it
+                                const int64_t i = (int64_t)tile * TILE + tid + j * THREADS;
+                                atomicOr(&defer_out[i >> 5], 1u << (i & 31));
+                                deferred++;
+                                pass[j] = false;
+                            }
+                        }
                         miss[j] = pass[j];
                     }
                     if constexpr (S::GMAX > 0) {
@@ -1407,7 +1547,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
 #pragma unroll
                             for (int j = 0; j < R; j++)
                                 inserted += dir_resolve<G, static_key_bytes<S>()>(&dir, tv.slots, tv.mask, tv.slot_bytes, tv.key_words, k[j].lo, k[j].hi,
-                                                                                  p.phase_seed, pass[j] && !hit[j]);
+                                                                                  k[j].len, p.phase_seed, pass[j] && !hit[j]);
                             my_cnt = (int)__reduce_min_sync(0xffffffffu, (unsigned)*(volatile int*)&dir.cnt);
 #pragma unroll
                             for (int q = 0; q < G; q++) {
@@ -1435,8 +1575,8 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                             // global-table path: the directory is full of other groups (or the shape keeps none)
                             int rc;
                             if constexpr (S::GMAX > 0) { // the exception here: keep its code out of the loop body
-                                rc = global_row_cold<S>(&prog, tv.slots, tv.mask, tv.slot_bytes, tv.key_words, k[j].lo, k[j].hi, pack_agg_args<S>(v[j], AggSeq{}),
-                                                        AggSeq{});
+                                rc = global_row_cold<S>(&prog, tv.slots, tv.mask, tv.slot_bytes, tv.key_words, k[j].lo, k[j].hi, k[j].len,
+                                                        pack_agg_args<S>(v[j], AggSeq{}), AggSeq{});
                             } else {
                                 bool fresh;
                                 uint8_t* slot =
@@ -1493,6 +1633,7 @@ struct ShapeMeta {
     int32_t load_width[MAX_NODES]; // bytes of the column a LOAD node reads, 0 for every other node
     int32_t load_off[MAX_NODES];   // its offset inside a stage
     int32_t load_nullable[MAX_NODES]; // the kernel reads a null byte per row for this LOAD node
+    int32_t load_binary[MAX_NODES];   // a BinaryColumn: offsets + byte window (load_width 0)
 };
 template <class S>
 constexpr ShapeMeta shape_meta() {
@@ -1508,6 +1649,7 @@ constexpr ShapeMeta shape_meta() {
         m.load_width[i] = S::node(i).op == DOP_LOAD ? S::node(i).width : 0;
         m.load_off[i] = load_off<S>(i);
         m.load_nullable[i] = (S::node(i).op == DOP_LOAD && S::node(i).nullable != 0) ? 1 : 0;
+        m.load_binary[i] = (S::node(i).op == DOP_LOAD && S::node(i).width == 0) ? 1 : 0;
     }
     return m;
 }
@@ -1622,27 +1764,42 @@ inline int64_t prepare_static(const ShapeMeta& m, const DProg& p, int64_t base, 
     bool placed[MAX_COLS] = {};
     int node_of[MAX_COLS];
     int bytes = 0;
+    bool any_binary = false;
     for (int c = 0; c < MAX_COLS; c++) {
         node_of[c] = -1;
         sa.null_off[c] = -1;
+        sa.bin_win_off[c] = -1;
+        sa.bin_hdr_off[c] = -1;
     }
     for (int i = 0; i < MAX_NODES; i++) sa.node_null_off[i] = -1;
     for (int i = 0; i < m.n_nodes; i++) {
-        if (!m.load_width[i]) continue;
+        if (!m.load_width[i] && !m.load_binary[i]) continue;
         const int c = p.nodes[i].col;
         if (c < 0 || c >= p.n_cols || placed[c] || p.cols[c].width != m.load_width[i]) return 0; // a column bound twice: generic kernel
+        if ((p.cols[c].kind == CK_BINARY) != (m.load_binary[i] != 0)) return 0;
         placed[c] = true;
         node_of[c] = i;
         sa.col_off[c] = m.load_off[i];
-        bytes = m.load_off[i] + m.load_width[i] * m.tile;
+        bytes = m.load_off[i] + (m.load_binary[i] ? 4 * m.tile + 16 : m.load_width[i] * m.tile);
     }
     for (int c = 0; c < p.n_cols; c++) {
-        if (!placed[c]) {
-            sa.col_off[c] = bytes;
-            bytes += p.cols[c].width * m.tile;
+        if (p.cols[c].kind == CK_BINARY) {
+            // offsets and bytes both start 16-byte aligned (bulk copies); the bytes keep the reference's 16 bytes of tail padding
+            // (column/bytes.h:27): the last window is rounded up to 16
+            if (!placed[c] || !p.cols[c].offsets || (((uintptr_t)p.cols[c].offsets + (size_t)base * 4) & 15) || ((uintptr_t)p.cols[c].data & 15)) return 0;
+            any_binary = true;
+            sa.bin_win_off[c] = bytes;
+            bytes += bin_window_bytes(m.tile);
+            sa.bin_hdr_off[c] = bytes;
+            bytes += 16;
+        } else {
+            if (!placed[c]) {
+                sa.col_off[c] = bytes;
+                bytes += p.cols[c].width * m.tile;
+            }
+            // TMA bulk copies need 16-byte aligned sources: tile starts are multiples of 16 rows, so the base pointers decide
+            if (((uintptr_t)p.cols[c].data + (size_t)base * p.cols[c].width) & 15) return 0;
         }
-        // TMA bulk copies need 16-byte aligned sources: tile starts are multiples of 16 rows, so the base pointers decide
-        if (((uintptr_t)p.cols[c].data + (size_t)base * p.cols[c].width) & 15) return 0;
         // null maps: the kernel was compiled for exactly the LOAD columns that carry one (predicate-only columns may or may not)
         const bool compiled_nullable = node_of[c] >= 0 && m.load_nullable[node_of[c]];
         if (node_of[c] >= 0 && compiled_nullable != (p.cols[c].nulls != nullptr)) return 0;
@@ -1653,8 +1810,9 @@ inline int64_t prepare_static(const ShapeMeta& m, const DProg& p, int64_t base, 
             bytes += m.tile;
         }
     }
-    const int64_t n_tiles = n / m.tile;
-    if (n_tiles == 0 || bytes == 0) return 0;
+    int64_t n_tiles = n / m.tile;
+    if (any_binary && n_tiles * m.tile + 3 > n) n_tiles--; // a tile copies tile + 4 offsets (n + 1 exist): the last one must leave three rows behind it
+    if (n_tiles <= 0 || bytes == 0) return 0;
     sa.stage_bytes = bytes;
     int stages = (ST_SMEM_BUDGET - m.acc_bytes) / sa.stage_bytes;
     if (stages > ST_MAX_STAGES) stages = ST_MAX_STAGES;

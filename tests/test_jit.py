@@ -274,3 +274,67 @@ def test_compiled_shape_with_nulls_matches_the_oracle(ctx, oracle, jit_sync, nam
     got, prof = run_device(ctx, plan_fn(), chunk)
     assert prof["shape"] == SHAPE_JIT and prof["static_launches"] >= 1, prof
     assert K.chunk_rows(got) == want
+
+
+# ---- BinaryColumn group keys on the compiled kernel: offsets + a window of the bytes staged per tile ------------------------------------
+def string_key_chunk(n, maker, nulls=0.0, seed=11, second_int_key=False):
+    rng = np.random.default_rng(seed)
+    vals = [maker(rng, i) for i in range(n)]
+    nl = (rng.random(n) < nulls).astype(np.uint8) if nulls else None
+    cols = {0: K.Column.from_strings(vals, nulls=nl), 1: K.Column.from_ints(K.TYPE_BIGINT, rng.integers(-1000, 1000, n)),
+            2: K.Column.from_ints(D64, rng.integers(0, 10**6, n), None, 15, 2)}
+    if second_int_key:
+        cols[3] = K.Column.from_ints(K.TYPE_SMALLINT, rng.integers(0, 3, n).astype(np.int16))
+    return K.Chunk(n, cols)
+
+
+def string_key_plan(hint, second_int_key=False):
+    e = ExprBuilder()
+    keys = [e.slot(0, K.TYPE_VARCHAR)]
+    v = e.slot(1, K.TYPE_BIGINT)
+    d = e.slot(2, D64, 15, 2)
+    if second_int_key:
+        keys.append(e.slot(3, K.TYPE_SMALLINT))
+    return ScanAggPlan(preds=[pred(1, K.PRED_GE, K.TYPE_BIGINT, -900)], exprs=e, keys=keys, group_hint=hint,
+                       aggs=[(K.AGG_SUM, v), (K.AGG_COUNT, None), (K.AGG_AVG, d), (K.AGG_MAX, v)])
+
+
+STRING_CASES = {
+    "one byte, four groups": (lambda r, i: bytes([65 + int(r.integers(0, 4))]), 4, 0.0, False),
+    "0 to 6 bytes, nullable": (lambda r, i: b"abcdef"[:int(r.integers(0, 7))], 8, 0.05, False),
+    "with a SMALLINT key": (lambda r, i: [b"x", b"yy", b"zzz"][int(r.integers(0, 3))], 12, 0.0, True),
+    "11 bytes: the tile's strings overflow the window": (lambda r, i: b"0123456789" + bytes([65 + int(r.integers(0, 3))]), 4, 0.0, False),
+    "many groups": (lambda r, i: b"k%05d" % int(r.integers(0, 20000)), 50000, 0.0, False),
+}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(STRING_CASES))
+def test_compiled_shape_with_string_keys_matches_the_oracle(ctx, oracle, jit_sync, name):
+    maker, hint, nulls, second = STRING_CASES[name]
+    chunk = string_key_chunk(150_003, maker, nulls, second_int_key=second)
+    plan_fn = lambda: string_key_plan(hint, second)
+    want = K.chunk_rows(oracle.scan_agg(plan_fn(), chunk))
+    got, prof = run_device(ctx, plan_fn(), chunk)
+    assert prof["shape"] == SHAPE_JIT and prof["static_launches"] >= 1, prof
+    assert K.chunk_rows(got) == want and len(want) >= 3
+
+
+@pytest.mark.gpu
+def test_q1_with_varchar_keys_on_the_compiled_kernel(ctx, oracle, jit_sync):
+    chunk = T.add_binary_keys(T.host_chunk("lineitem", 0, 400_003, T.LINEITEM_Q1))
+    for s_ in (Q.L_RETURNFLAG_CODE, Q.L_LINESTATUS_CODE):
+        chunk.columns.pop(s_)
+    plan_fn = lambda: Q.q1_plan(dict_keys=False)
+    want = K.chunk_rows(oracle.scan_agg(plan_fn(), chunk))
+    got, prof = run_device(ctx, plan_fn(), chunk)
+    assert prof["shape"] == SHAPE_JIT and K.chunk_rows(got) == want and len(want) == 4
+
+
+@pytest.mark.gpu
+def test_string_key_beyond_16_bytes_is_refused_on_the_compiled_kernel_too(ctx, jit_sync):
+    from starrocks_b200 import ops
+    chunk = string_key_chunk(100_000, lambda r, i: b"short" if i != 77_777 else b"a key of twenty bytes")
+    with pytest.raises(ops.SrbError) as ex:
+        run_device(ctx, string_key_plan(4), chunk)
+    assert ex.value.code == K.NOT_IMPLEMENTED
