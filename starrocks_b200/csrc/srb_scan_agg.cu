@@ -2405,7 +2405,10 @@ private:
         bool fast = !getenv("SRB_NO_FAST_FILTER");
         if (fast) {
             StaticArgs sa{};
-            for (int c = 0; c < P.n_cols; c++) sa.col_off[c] = c; // lower_ranges identifies a column by this field
+            for (int c = 0; c < MAX_COLS; c++) {
+                sa.col_off[c] = c;    // lower_ranges identifies a column by this field
+                sa.null_off[c] = -1;  // and refuses columns with a staged null map (the null maps of this path are checked below)
+            }
             fast = lower_ranges(P, sa);
             for (int i = 0; fast && i < P.n_preds; i++) fast = cols[P.preds[i].col].nulls == nullptr;
             for (int k = 0; fast && k < sa.n_ranges; k++) {
