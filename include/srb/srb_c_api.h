@@ -379,6 +379,16 @@ srb_status srb_op_streaming_stats(srb_op* op, int64_t* rows_passed_through, int6
  * 1369-1422: selection[i] &= test(key[i]); NULL keys pass iff has_null). The directory holds exactly the bits the reference's
  * filter of the same size would hold for the same keys. Key types: integers up to 8 bytes, DATE, DECIMAL32/64. */
 typedef struct srb_runtime_filter srb_runtime_filter;
+/* bits of srb_join_build_runtime_filter's `hash_mix` argument */
+#define SRB_RF_HASH_MIX 1     /* hash_mix = 1 below */
+#define SRB_RF_MAYBE_BITSET 2 /* the reference's maybe_use_bitset_filter (exec/pipeline/runtime_filter_types.cpp:149-152): this builder holds the
+                                 whole build side (a broadcast join), so RuntimeFilterHelper::create_join_runtime_filter's rule
+                                 (exprs/runtime_filter_bank.cpp:160-205) may pick a RuntimeBitsetFilter — one bit per value of [min, max],
+                                 exact membership (exprs/runtime_filter.h:1583-1700) — instead of the bloom filter: when the bitset is no
+                                 larger than one byte per build row, or at most 4x that and fits the cache (here: the GPU's L2). Like the
+                                 reference's, a bitset filter cannot be merged across ranks. Ignored with expected_rows > 0. */
+#define SRB_RF_KIND_BLOOM 1   /* RuntimeFilterSerializeType (exprs/runtime_filter.h:46-51) */
+#define SRB_RF_KIND_BITSET 3
 /* `join` must have finished its build (srb_op_set_finishing). key_index: which build key column. expected_rows sizes the filter as
  * SimdBlockFilter::init(expected_rows) does (0: the rows this operator built from); ranks that will merge their filters pass the
  * same value. hash_mix = 0: the key's hash is RuntimeBloomFilter::compute_hash as the reference tree builds it — phmap_mix<8>
@@ -395,6 +405,10 @@ srb_status srb_runtime_filter_info(const srb_runtime_filter* rf, int64_t* n_buck
                                    int64_t* inserted);
 /* copies the directory (n_buckets x 8 uint32) to host memory: what the tests compare with the oracle's SimdBlockFilter */
 srb_status srb_runtime_filter_directory(const srb_runtime_filter* rf, void* dst, int64_t bytes);
+/* which filter the probe side tests (SRB_RF_KIND_*), and for a bitset its size in bytes (whole 32-bit words over [min, max]) */
+srb_status srb_runtime_filter_kind(const srb_runtime_filter* rf, int32_t* kind, int64_t* bitset_bytes);
+/* copies the bitset to host memory: bit (x - min) of a little-endian bit string, as Bitset::insert sets it (exprs/runtime_filter.cpp:287-292) */
+srb_status srb_runtime_filter_bitset(const srb_runtime_filter* rf, void* dst, int64_t bytes);
 void srb_runtime_filter_destroy(srb_runtime_filter* rf);
 
 /* ---- exchange: what replaces ExchangeSinkOperator / ExchangeSourceOperator + brpc between GPUs ---------------------- */

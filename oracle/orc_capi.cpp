@@ -188,6 +188,40 @@ void orc_rf_directory(void* f, uint32_t* out) {
     std::copy(rf->bf.directory.begin(), rf->bf.directory.end(), out);
 }
 
+// RuntimeBitsetFilter (orc_rf.h)
+int orc_rf_choose_bitset(int64_t min, int64_t max, uint64_t row_count, uint64_t l2_cache, uint64_t l3_cache) {
+    return orc::choose_bitset_filter(min, max, row_count, l2_cache, l3_cache) ? 1 : 0;
+}
+void* orc_bitset_create(int64_t min, int64_t max) {
+    auto* f = new orc::RuntimeBitsetFilter();
+    f->set_min_max(min, max);
+    f->init();
+    return f;
+}
+void orc_bitset_free(void* f) { delete (orc::RuntimeBitsetFilter*)f; }
+void orc_bitset_insert_column(void* f, const void* keys, int width, int64_t n, const uint8_t* nulls) {
+    auto* rf = (orc::RuntimeBitsetFilter*)f;
+    for (int64_t i = 0; i < n; i++) {
+        if (nulls && nulls[i]) {
+            rf->has_null = true;
+            continue;
+        }
+        rf->insert(width == 1 ? ((const int8_t*)keys)[i] : width == 2 ? ((const int16_t*)keys)[i] : width == 4 ? ((const int32_t*)keys)[i] : ((const int64_t*)keys)[i]);
+    }
+}
+void orc_bitset_evaluate(void* f, const void* keys, int width, int64_t n, const uint8_t* nulls, uint8_t* selection) {
+    auto* rf = (orc::RuntimeBitsetFilter*)f;
+    for (int64_t i = 0; i < n; i++) {
+        int64_t v = width == 1 ? ((const int8_t*)keys)[i] : width == 2 ? ((const int16_t*)keys)[i] : width == 4 ? ((const int32_t*)keys)[i] : ((const int64_t*)keys)[i];
+        selection[i] = rf->evaluate(selection[i], nulls && nulls[i], v);
+    }
+}
+int64_t orc_bitset_bytes(void* f) { return (int64_t)((orc::RuntimeBitsetFilter*)f)->bitset.size(); }
+void orc_bitset_data(void* f, uint8_t* out) {
+    auto* rf = (orc::RuntimeBitsetFilter*)f;
+    std::copy(rf->bitset.begin(), rf->bitset.end(), out);
+}
+
 #if defined(__SSE4_2__)
 // hardware cross-check of the software CRC32C
 uint32_t orc_hw_crc32c_u64(uint32_t crc, uint64_t v) { return (uint32_t)_mm_crc32_u64(crc, v); }

@@ -85,4 +85,39 @@ struct RuntimeBloomFilter {
     }
 };
 
+// RuntimeBitsetFilter over integer keys: Bitset (be/src/exprs/runtime_filter.h:1587-1655, runtime_filter.cpp:287-292,350-354) behind the
+// ComposedRuntimeFilter's min / max test (contains<CheckRange>); NULL rows: selection = has_null (contains_batch<.., NullIsTrue>).
+// Pinned by be/test/exprs/runtime_filter_test.cpp:1409-1455 (TestEvaluateBitsetFilter), restated in tests/test_oracle_golden.py.
+struct RuntimeBitsetFilter {
+    int64_t min = 0, max = -1;
+    bool has_null = false;
+    std::vector<uint8_t> bitset;
+    void set_min_max(int64_t mn, int64_t mx) {
+        min = mn;
+        max = mx;
+    }
+    void init() { // value_interval() + 1 values, eight per byte
+        const uint64_t key_interval = ((uint64_t)max - (uint64_t)min) + 1;
+        bitset.assign((size_t)((key_interval + 7) / 8), 0);
+    }
+    void insert(int64_t v) {
+        const uint64_t bucket = (uint64_t)v - (uint64_t)min;
+        bitset[bucket / 8] |= (uint8_t)(1 << (bucket % 8));
+    }
+    uint8_t evaluate(uint8_t selected, bool is_null, int64_t v) const {
+        if (is_null) return has_null ? 1 : 0;
+        if (!selected || v < min || v > max) return 0;
+        const uint64_t bucket = (uint64_t)v - (uint64_t)min;
+        return (bitset[bucket / 8] >> (bucket % 8)) & 1;
+    }
+};
+// try_create_runtime_bitset_filter (be/src/exprs/runtime_filter_bank.cpp:160-200): the bitset replaces the bloom filter when it needs no more
+// memory than the bloom filter's budget (row_count bytes), or at most 4x / 2x that and fits the L2 / L3 cache
+inline bool choose_bitset_filter(int64_t min, int64_t max, uint64_t row_count, uint64_t l2_cache, uint64_t l3_cache) {
+    const uint64_t value_interval = (uint64_t)max - (uint64_t)min + 1;
+    if (min > max || value_interval == 0) return false;
+    const uint64_t bitset_mem = (value_interval + 7) / 8, bloom_mem = row_count;
+    return bitset_mem <= bloom_mem || (bitset_mem <= bloom_mem * 4 && bitset_mem <= l2_cache) || (bitset_mem <= bloom_mem * 2 && bitset_mem <= l3_cache);
+}
+
 } // namespace orc

@@ -28,6 +28,7 @@ EXPR_SLOT_REF, EXPR_LITERAL, EXPR_CAST, EXPR_ADD, EXPR_SUB, EXPR_MUL = 1, 2, 3, 
 AGG_SUM, AGG_AVG, AGG_COUNT, AGG_MIN, AGG_MAX = 1, 2, 3, 4, 5
 AGG_UPDATE_FINALIZE, AGG_UPDATE_SERIALIZE, AGG_MERGE_FINALIZE, AGG_MERGE_SERIALIZE = 0, 1, 2, 3
 JOIN_INNER, JOIN_LEFT_SEMI, JOIN_LEFT_ANTI = 0, 2, 8
+RF_KIND_BLOOM, RF_KIND_BITSET = 1, 3  # RuntimeFilterSerializeType (exprs/runtime_filter.h:46-51)
 JOIN_LEFT_OUTER, JOIN_RIGHT_OUTER, JOIN_FULL_OUTER, JOIN_RIGHT_SEMI, JOIN_RIGHT_ANTI, JOIN_NULL_AWARE_LEFT_ANTI = 1, 3, 4, 7, 9, 10
 STREAMING_AUTO, STREAMING_FORCE_STREAMING, STREAMING_FORCE_PREAGGREGATION = 0, 1, 2  # TStreamingPreaggregationMode
 

@@ -47,6 +47,7 @@ srb_status srb_ctx_create(const srb_config* cfg, srb_ctx** out) {
     c->cfg = *cfg;
     if (c->cfg.world_size <= 0) c->cfg.world_size = 1;
     c->n_sms = p.multiProcessorCount;
+    c->l2_bytes = p.l2CacheSize;
     c->sm_arch = p.major * 10 + p.minor;
     c->hbm_bytes = (int64_t)p.totalGlobalMem;
     *out = c;
@@ -316,6 +317,23 @@ srb_status srb_runtime_filter_directory(const srb_runtime_filter* rf, void* dst,
     if (bytes != (int64_t)rf->dir_bytes()) throw srb::Error(SRB_INVALID_ARGUMENT, "directory size mismatch (32 bytes per bucket)");
     SRB_CUDA(cudaSetDevice(rf->ctx->cfg.device));
     SRB_CUDA(cudaMemcpy(dst, rf->dir.p, (size_t)bytes, cudaMemcpyDeviceToHost));
+    return SRB_OK;
+    SRB_API_END
+}
+srb_status srb_runtime_filter_kind(const srb_runtime_filter* rf, int32_t* kind, int64_t* bitset_bytes) {
+    SRB_API_BEGIN
+    if (!rf || !kind) throw srb::Error(SRB_INVALID_ARGUMENT, "null argument");
+    *kind = rf->is_bitset ? SRB_RF_KIND_BITSET : SRB_RF_KIND_BLOOM;
+    if (bitset_bytes) *bitset_bytes = (int64_t)rf->bits_bytes();
+    return SRB_OK;
+    SRB_API_END
+}
+srb_status srb_runtime_filter_bitset(const srb_runtime_filter* rf, void* dst, int64_t bytes) {
+    SRB_API_BEGIN
+    if (!rf || !dst) throw srb::Error(SRB_INVALID_ARGUMENT, "null argument");
+    if (!rf->is_bitset || bytes != (int64_t)rf->bits_bytes()) throw srb::Error(SRB_INVALID_ARGUMENT, "not a bitset filter / size mismatch");
+    SRB_CUDA(cudaSetDevice(rf->ctx->cfg.device));
+    SRB_CUDA(cudaMemcpy(dst, rf->bits.p, (size_t)bytes, cudaMemcpyDeviceToHost));
     return SRB_OK;
     SRB_API_END
 }

@@ -290,6 +290,9 @@ struct RfView {
     int32_t has_null;
     int32_t mix; // 0: hash = key (the reference tree as it builds: phmap_mix is the identity); 1: hash = phmap_mix<8>(key), what the
                  // same source computes when ENABLE_PHMAP_MIX is defined (phmap_utils.h:85-95)
+    // RuntimeBitsetFilter (exprs/runtime_filter.h:1583-1700): one bit per value of [min, max], bit (x - min) of a little-endian bit string
+    // (Bitset::insert, runtime_filter.cpp:287-292); nullptr: the filter is a bloom filter
+    const uint32_t* bits;
 };
 SRB_HD uint32_t rf_salt(int i) {
     switch (i) {

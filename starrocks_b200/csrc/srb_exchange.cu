@@ -919,6 +919,8 @@ srb_status srb_comm_merge_runtime_filter(srb_comm* c, srb_runtime_filter* rf) {
     X_BEGIN
     if (!c || !rf) throw Error(SRB_INVALID_ARGUMENT, "null argument");
     comm_alive(c);
+    // "RuntimeBitsetFilter only support for broadcast join, so merge and concat are not supported" (exprs/runtime_filter.h:1686-1688)
+    if (rf->is_bitset && c->world > 1) throw Error(SRB_INVALID_ARGUMENT, "a bitset runtime filter cannot be merged: build partial filters without SRB_RF_MAYBE_BITSET");
     SRB_CUDA(cudaSetDevice(c->ctx->cfg.device));
     const int W = c->world;
     c->counts_dev.ensure(c->ctx, (size_t)(5 + 5 * W) * 8);

@@ -82,6 +82,7 @@ inline bool is_binary(int t) { return t == SRB_TYPE_VARCHAR || t == SRB_TYPE_VAR
 struct srb_ctx {
     srb_config cfg{};
     int n_sms = 0;
+    int64_t l2_bytes = 0;
     int sm_arch = 0;
     int64_t hbm_bytes = 0;
     int64_t mem_in_use = 0;
@@ -375,8 +376,13 @@ struct srb_runtime_filter {
     int64_t min = INT64_MAX, max = INT64_MIN, inserted = 0;
     bool has_null = false;
     int mix = 0; // RfView::mix
+    // RuntimeBitsetFilter instead of the bloom filter (chosen by create_join_runtime_filter's rule, runtime_filter_bank.cpp:160-205): one bit
+    // per value of [min, max], padded to whole 32-bit words
+    srb::DevBuf bits;
+    bool is_bitset = false;
+    size_t bits_bytes() const { return is_bitset ? (size_t)((((uint64_t)max - (uint64_t)min + 1) + 31) / 32) * 4 : 0; }
     srb::RfView view() const {
-        return srb::RfView{(uint32_t*)dir.p, directory_mask, log_num_buckets, min, max, has_null ? 1 : 0, mix};
+        return srb::RfView{(uint32_t*)dir.p, directory_mask, log_num_buckets, min, max, has_null ? 1 : 0, mix, is_bitset ? (const uint32_t*)bits.p : nullptr};
     }
     size_t dir_bytes() const { return (size_t)32 << log_num_buckets; }
 };

@@ -545,6 +545,22 @@ __global__ void __launch_bounds__(256) k_rf_build(const uint8_t* __restrict__ ke
     }
 }
 
+// RuntimeBitsetFilter: bit (x - min) for every non-NULL build key (Bitset::insert, exprs/runtime_filter.cpp:287-292)
+template <int W>
+__global__ void __launch_bounds__(256) k_rf_bits_build(const uint8_t* __restrict__ keys, const uint8_t* __restrict__ nulls, int64_t n, long long mn,
+                                                        uint32_t* __restrict__ bits) {
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        if (nulls && nulls[r]) continue;
+        long long x;
+        if constexpr (W == 1) x = ((const int8_t*)keys)[r];
+        else if constexpr (W == 2) x = ((const int16_t*)keys)[r];
+        else if constexpr (W == 4) x = ((const int32_t*)keys)[r];
+        else x = ((const long long*)keys)[r];
+        const uint64_t b = (uint64_t)x - (uint64_t)mn;
+        atomicOr(&bits[b >> 5], 1u << (b & 31));
+    }
+}
+
 // =================================================================================================================
 struct GrowCol { // device column that grows by appends
     DevBuf data, nulls;
@@ -849,7 +865,8 @@ public:
 
     // partial runtime filter over build key column `key_index`; expected_rows sizes the directory (0: this op's build rows) so that
     // the partial filters of several ranks can be merged (SimdBlockFilter::merge needs equal sizes)
-    srb_runtime_filter* build_runtime_filter(int key_index, int64_t expected_rows, int mix) override {
+    srb_runtime_filter* build_runtime_filter(int key_index, int64_t expected_rows, int flags) override {
+        const int mix = flags & SRB_RF_HASH_MIX;
         if (!build_done_) throw Error(SRB_INTERNAL_ERROR, "runtime filter requested before the build side finished");
         if (key_index < 0 || key_index >= (int)bkeys_.size()) throw Error(SRB_INVALID_ARGUMENT, "bad build key index");
         const GrowCol& kc = bcols_[key_index];
@@ -891,6 +908,31 @@ public:
         rf->max = hm->max;
         rf->inserted = (int64_t)hm->inserted;
         rf->has_null = hm->has_null != 0;
+        // RuntimeFilterHelper::create_join_runtime_filter (runtime_filter_bank.cpp:160-205): a builder that holds the WHOLE build side (a
+        // broadcast join: the caller says so) takes a bitset over [min, max] instead of the bloom filter when it is no larger than the bloom
+        // filter's budget (one byte per build row), or at most 4x that and cache resident (the reference asks the CPU's L2 / L3; here: the
+        // GPU's L2). The bloom directory stays (srb_runtime_filter_directory still reads it); the probe tests the bitset.
+        if ((flags & SRB_RF_MAYBE_BITSET) && expected_rows <= 0 && rf->inserted > 0 && rf->min <= rf->max) {
+            const uint64_t interval = (uint64_t)rf->max - (uint64_t)rf->min + 1;
+            const uint64_t bitset_bytes = (interval + 7) / 8, bloom_bytes = (uint64_t)build_rows_;
+            if (interval != 0 && (bitset_bytes <= bloom_bytes || (bitset_bytes <= bloom_bytes * 4 && bitset_bytes <= (uint64_t)ctx->l2_bytes))) {
+                rf->is_bitset = true;
+                rf->bits.ensure(ctx, rf->bits_bytes());
+                SRB_CUDA(cudaMemsetAsync(rf->bits.p, 0, rf->bits_bytes(), stream));
+                const uint8_t* keys = kc.data.as<uint8_t>();
+                const uint8_t* nulls = kc.nullable ? kc.nulls.as<uint8_t>() : nullptr;
+                const int grid = grid_for(build_rows_);
+                switch (kc.width) {
+                case 1: k_rf_bits_build<1><<<grid, 256, 0, stream>>>(keys, nulls, build_rows_, rf->min, rf->bits.as<uint32_t>()); break;
+                case 2: k_rf_bits_build<2><<<grid, 256, 0, stream>>>(keys, nulls, build_rows_, rf->min, rf->bits.as<uint32_t>()); break;
+                case 4: k_rf_bits_build<4><<<grid, 256, 0, stream>>>(keys, nulls, build_rows_, rf->min, rf->bits.as<uint32_t>()); break;
+                default: k_rf_bits_build<8><<<grid, 256, 0, stream>>>(keys, nulls, build_rows_, rf->min, rf->bits.as<uint32_t>());
+                }
+                SRB_CUDA(cudaGetLastError());
+                SRB_CUDA(cudaStreamSynchronize(stream));
+                launches++;
+            }
+        }
         return rf.release();
     }
 

@@ -972,6 +972,89 @@ SRB_D void rf_test_full(const RfArgs& a, const uint32_t* __restrict__ dir, const
     }
 }
 
+// RuntimeBitsetFilter (exprs/runtime_filter.h:1583-1700, ComposedRuntimeFilter's min / max in front of it): a row passes iff its key lies in
+// [min, max] and bit (key - min) is set; NULL keys pass iff has_null. One word load and a shift instead of a 32-byte bucket and eight
+// salted multiplies; the bitsets of dimension keys (a few hundred KB) stay in L1 / L2.
+template <bool NULLS, class KT>
+SRB_D void rf_bits_full(const RfArgs& a, const KT* __restrict__ keys, const uint8_t* __restrict__ nulls, uint32_t* smask, int lane) {
+    constexpr long long KMIN = (long long)std::numeric_limits<KT>::min(), KMAX = (long long)std::numeric_limits<KT>::max();
+    const long long lo64 = a.v.min > KMIN ? a.v.min : KMIN, hi64 = a.v.max < KMAX ? a.v.max : KMAX;
+    const bool empty = lo64 > hi64;
+    const KT lo = empty ? (KT)1 : (KT)lo64, hi = empty ? (KT)0 : (KT)hi64;
+    const uint32_t* __restrict__ bits = a.v.bits;
+    const long long mn = a.v.min;
+    const bool null_pass = a.v.has_null != 0;
+#pragma unroll 1
+    for (uint32_t j0 = 0; j0 < (uint32_t)FTILE; j0 += 256 * 4) {
+        KT x[4];
+        uint8_t nl[4] = {};
+        uint64_t idx[4];
+        uint32_t w[4];
+        bool in[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) x[u] = keys[j0 + u * 256 + threadIdx.x];
+        if constexpr (NULLS) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) nl[u] = nulls[j0 + u * 256 + threadIdx.x];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            in[u] = x[u] >= lo && x[u] <= hi;
+            idx[u] = in[u] ? (uint64_t)((long long)x[u] - mn) : 0ULL;
+            w[u] = __ldg(bits + (idx[u] >> 5));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            bool pass = in[u] && ((w[u] >> (idx[u] & 31)) & 1u);
+            if constexpr (NULLS) pass = nl[u] ? null_pass : pass;
+            const uint32_t word = __ballot_sync(0xffffffffu, pass);
+            if (lane == 0) smask[(j0 + u * 256 + threadIdx.x) >> 5] = word;
+        }
+    }
+}
+template <bool NULLS, class KT>
+SRB_D void rf_bits_list(const RfArgs& a, const KT* __restrict__ keys, const uint8_t* __restrict__ nulls, uint32_t total, const uint16_t* sidx,
+                        uint32_t* smask) {
+    constexpr long long KMIN = (long long)std::numeric_limits<KT>::min(), KMAX = (long long)std::numeric_limits<KT>::max();
+    const long long lo64 = a.v.min > KMIN ? a.v.min : KMIN, hi64 = a.v.max < KMAX ? a.v.max : KMAX;
+    const bool empty = lo64 > hi64;
+    const KT lo = empty ? (KT)1 : (KT)lo64, hi = empty ? (KT)0 : (KT)hi64;
+    const uint32_t* __restrict__ bits = a.v.bits;
+    const long long mn = a.v.min;
+    const bool null_pass = a.v.has_null != 0;
+#pragma unroll 1
+    for (uint32_t j0 = 0; j0 < total; j0 += 256 * 4) {
+        uint32_t r[4], w[4];
+        KT x[4];
+        uint8_t nl[4] = {};
+        uint64_t idx[4];
+        bool in[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t j = j0 + u * 256 + threadIdx.x;
+            r[u] = j < total ? (uint32_t)sidx[j] : 0xFFFFFFFFu;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) x[u] = keys[r[u] == 0xFFFFFFFFu ? 0u : r[u]];
+        if constexpr (NULLS) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) nl[u] = nulls[r[u] == 0xFFFFFFFFu ? 0u : r[u]];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            in[u] = x[u] >= lo && x[u] <= hi;
+            idx[u] = in[u] ? (uint64_t)((long long)x[u] - mn) : 0ULL;
+            w[u] = __ldg(bits + (idx[u] >> 5));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            bool pass = in[u] && ((w[u] >> (idx[u] & 31)) & 1u);
+            if constexpr (NULLS) pass = nl[u] ? null_pass : pass;
+            if (!pass && r[u] != 0xFFFFFFFFu) atomicAnd(&smask[r[u] >> 5], ~(1u << (r[u] & 31)));
+        }
+    }
+}
+
 template <int W>
 __global__ void __launch_bounds__(256, 4) k_filter_rf(const __grid_constant__ RfArgs a, int64_t n, uint32_t* __restrict__ mask,
                                                        uint32_t* __restrict__ tile_counts) {
@@ -1016,7 +1099,15 @@ __global__ void __launch_bounds__(256, 4) k_filter_rf(const __grid_constant__ Rf
     const uint32_t* dir = a.v.dir;
     const KT* keys = (const KT*)a.data + tile0;
     const uint8_t* nulls = a.nulls ? a.nulls + tile0 : nullptr;
-    if (total == FTILE) { // every row of the tile is still selected: rows are their own list
+    if (a.v.bits) { // a bitset filter (uniform: one filter per launch)
+        if (total == FTILE) {
+            if (nulls) rf_bits_full<true, KT>(a, keys, nulls, smask, lane);
+            else rf_bits_full<false, KT>(a, keys, nulls, smask, lane);
+        } else {
+            if (nulls) rf_bits_list<true, KT>(a, keys, nulls, total, sidx, smask);
+            else rf_bits_list<false, KT>(a, keys, nulls, total, sidx, smask);
+        }
+    } else if (total == FTILE) { // every row of the tile is still selected: rows are their own list
         if (a.v.mix) {
             if (nulls) rf_test_full<W, true, true, KT>(a, dir, keys, nulls, smask, lane);
             else rf_test_full<W, true, false, KT>(a, dir, keys, nulls, smask, lane);
@@ -2438,7 +2529,7 @@ private:
             }
             // opt-in (SRB_RF_FUSED=1, not yet measured): every runtime filter of the scan in one pass over the tiles
             bool fused = rf_fused_ && rfs_.size() >= 2 && rfs_.size() <= (size_t)RF_FUSED_MAX;
-            for (const auto& r : rfs_) fused = fused && P.cols[r.col].width == P.cols[rfs_[0].col].width;
+            for (const auto& r : rfs_) fused = fused && P.cols[r.col].width == P.cols[rfs_[0].col].width && !r.rf->is_bitset;
             if (fused) {
                 RfMultiArgs ma{};
                 ma.n = (int)rfs_.size();

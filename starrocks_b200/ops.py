@@ -20,7 +20,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libsrb.so"
 _lib = None
 
 EXPORTS = [
-    "srb_ctx_create", "srb_ctx_destroy", "srb_last_error", "srb_ctx_device_info", "srb_ctx_trim", "srb_op_stream", "srb_jit_wait", "srb_jit_stats", "srb_jit_check_plan",
+    "srb_ctx_create", "srb_ctx_destroy", "srb_last_error", "srb_ctx_device_info", "srb_ctx_trim", "srb_op_stream", "srb_jit_wait", "srb_jit_stats", "srb_jit_check_plan", "srb_runtime_filter_kind", "srb_runtime_filter_bitset",
     "srb_scan_agg_create", "srb_join_create", "srb_op_push_chunk", "srb_op_push_pages", "srb_op_set_finishing_merged", "srb_op_set_finishing", "srb_op_has_output",
     "srb_op_need_input", "srb_op_is_finished", "srb_op_pull_chunk", "srb_op_pull_all", "srb_op_pull_device",
     "srb_op_cancel", "srb_op_close", "srb_op_sync", "srb_op_counters", "srb_op_profile",
@@ -111,6 +111,8 @@ def lib() -> C.CDLL:
     L.srb_op_streaming_stats.argtypes = [vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
     L.srb_runtime_filter_info.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), C.POINTER(C.c_int32), C.POINTER(i64)]
     L.srb_runtime_filter_directory.argtypes = [vp, vp, i64]
+    L.srb_runtime_filter_kind.argtypes = [vp, C.POINTER(i32), C.POINTER(i64)]
+    L.srb_runtime_filter_bitset.argtypes = [vp, vp, i64]
     L.srb_runtime_filter_destroy.argtypes = [vp]
     L.srb_runtime_filter_destroy.restype = None
     _lib = L
@@ -361,6 +363,21 @@ class RuntimeFilter:
         _check(self.L.srb_runtime_filter_info(self.h, C.byref(nb), C.byref(mn), C.byref(mx), C.byref(hn), C.byref(ins)))
         return {"n_buckets": nb.value, "min": mn.value, "max": mx.value, "has_null": bool(hn.value), "inserted": ins.value}
 
+    def kind(self) -> int:
+        """K.RF_KIND_BLOOM or K.RF_KIND_BITSET: what the probe side tests"""
+        k, nb = C.c_int32(), C.c_int64()
+        _check(self.L.srb_runtime_filter_kind(self.h, C.byref(k), C.byref(nb)))
+        return k.value
+
+    def bitset(self):
+        """the bitset as a numpy uint32 array (bit (x - min) of a little-endian bit string)"""
+        import numpy as np
+        k, nb = C.c_int32(), C.c_int64()
+        _check(self.L.srb_runtime_filter_kind(self.h, C.byref(k), C.byref(nb)))
+        out = np.empty(nb.value // 4, dtype=np.uint32)
+        _check(self.L.srb_runtime_filter_bitset(self.h, out.ctypes.data, out.nbytes))
+        return out
+
     def directory(self):
         """the directory as a numpy array [n_buckets, 8] of uint32"""
         import numpy as np
@@ -396,11 +413,12 @@ class HashJoinOperator(_Operator):
         self._plan = plan
         self.probe = _ProbeSide(ctx, h)
 
-    def build_runtime_filter(self, key_index: int = 0, expected_rows: int = 0, mix: bool = False) -> "RuntimeFilter":
+    def build_runtime_filter(self, key_index: int = 0, expected_rows: int = 0, mix: bool = False, bitset: bool = False) -> "RuntimeFilter":
         """after set_finishing: the partial runtime filter over build key `key_index` (HashJoinBuildOperator -> RuntimeBloomFilter).
-        mix=False hashes as the reference tree builds (identity); mix=True applies phmap_mix<8> (ENABLE_PHMAP_MIX)"""
+        mix=False hashes as the reference tree builds (identity); mix=True applies phmap_mix<8> (ENABLE_PHMAP_MIX); bitset=True: this
+        builder holds the whole build side (broadcast join), so a RuntimeBitsetFilter may be chosen (SRB_RF_MAYBE_BITSET)"""
         h = C.c_void_p()
-        _check(self.L.srb_join_build_runtime_filter(self.h, key_index, expected_rows, 1 if mix else 0, C.byref(h)))
+        _check(self.L.srb_join_build_runtime_filter(self.h, key_index, expected_rows, (1 if mix else 0) | (2 if bitset else 0), C.byref(h)))
         return RuntimeFilter(self.ctx, h)
 
     def close(self):

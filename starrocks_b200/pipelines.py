@@ -110,7 +110,8 @@ class TpchQ3:
                 n_build = int(sum(r[0] for r in K.chunk_rows(self.comm.all_gather(mine), sort=False)))
             # order keys use 8 of every 32 values: under the reference tree's identity hash three quarters of the buckets stay empty
             # and most lines pass by accident, so the filter is built with the mixing hash (ops.HashJoinOperator.build_runtime_filter)
-            rf = j2.build_runtime_filter(0, max(1, n_build), mix=True)
+            # one rank: this builder holds the whole build side, so the filter may be a RuntimeBitsetFilter (create_join_runtime_filter)
+            rf = j2.build_runtime_filter(0, max(1, n_build), mix=True) if self.comm is not None else j2.build_runtime_filter(0, 0, mix=True, bitset=True)
             if self.comm is not None:
                 self.comm.merge_runtime_filter(rf)
             self.open.append(rf)
@@ -206,7 +207,7 @@ class SsbQ41:
             self.joins.append(j)
             if self.use_rf and fplan is not None:
                 probe_slot = {"ssb_supplier": Q.LO_SUPPKEY, "ssb_customer": Q.LO_CUSTKEY, "ssb_part": Q.LO_PARTKEY}[name]
-                self.rfs.append((j.build_runtime_filter(0), probe_slot))
+                self.rfs.append((j.build_runtime_filter(0, bitset=True), probe_slot))  # a broadcast join: every rank builds from the whole dimension
         return self
 
     def probe(self, lineorder: K.Chunk, phase: int = K.AGG_UPDATE_FINALIZE, stage_rows=None):

@@ -82,6 +82,15 @@ class Oracle:
         L.orc_rf_info.restype = C.c_int64
         L.orc_rf_info.argtypes = [C.c_void_p, C.c_int]
         L.orc_rf_directory.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_rf_choose_bitset.argtypes = [C.c_int64, C.c_int64, C.c_uint64, C.c_uint64, C.c_uint64]
+        L.orc_bitset_create.restype = C.c_void_p
+        L.orc_bitset_create.argtypes = [C.c_int64, C.c_int64]
+        L.orc_bitset_free.argtypes = [C.c_void_p]
+        L.orc_bitset_insert_column.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p]
+        L.orc_bitset_evaluate.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
+        L.orc_bitset_bytes.restype = C.c_int64
+        L.orc_bitset_bytes.argtypes = [C.c_void_p]
+        L.orc_bitset_data.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_for_encode.restype = C.c_int64
         L.orc_for_encode.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_int64]
         L.orc_for_decode.restype = C.c_int64
@@ -219,6 +228,45 @@ class Oracle:
         self.lib.orc_decimal_div_integer(lo, hi, count, scale, C.byref(rlo), C.byref(rhi))
         v = K.join128(rlo.value, rhi.value)
         return v - (1 << 128) if v >= 1 << 127 else v
+
+
+class OracleBitsetFilter:
+    """oracle/orc_rf.h RuntimeBitsetFilter: one bit per value of [min, max] behind the min / max test; NULL rows pass iff a NULL was inserted"""
+
+    def __init__(self, oracle: Oracle, mn: int, mx: int):
+        self.L = oracle.lib
+        self.h = self.L.orc_bitset_create(mn, mx)
+
+    @staticmethod
+    def chosen(oracle: Oracle, mn: int, mx: int, row_count: int, l2_cache: int, l3_cache: int = 0) -> bool:
+        """try_create_runtime_bitset_filter's rule"""
+        return bool(oracle.lib.orc_rf_choose_bitset(mn, mx, row_count, l2_cache, l3_cache))
+
+    def insert_column(self, col: K.Column):
+        import numpy as np
+        data = np.ascontiguousarray(col.data)
+        nulls = None if col.nulls is None else np.ascontiguousarray(col.nulls)
+        self.L.orc_bitset_insert_column(self.h, data.ctypes.data, data.dtype.itemsize, len(data), None if nulls is None else nulls.ctypes.data)
+        return self
+
+    def evaluate(self, col: K.Column, selection=None):
+        import numpy as np
+        data = np.ascontiguousarray(col.data)
+        nulls = None if col.nulls is None else np.ascontiguousarray(col.nulls)
+        sel = np.ones(len(data), np.uint8) if selection is None else np.ascontiguousarray(selection, dtype=np.uint8).copy()
+        self.L.orc_bitset_evaluate(self.h, data.ctypes.data, data.dtype.itemsize, len(data), None if nulls is None else nulls.ctypes.data, sel.ctypes.data)
+        return sel
+
+    def data(self):
+        import numpy as np
+        out = np.empty(self.L.orc_bitset_bytes(self.h), dtype=np.uint8)
+        self.L.orc_bitset_data(self.h, out.ctypes.data)
+        return out
+
+    def close(self):
+        if self.h:
+            self.L.orc_bitset_free(self.h)
+            self.h = None
 
 
 class OracleRuntimeFilter:

@@ -1282,6 +1282,84 @@ def test_runtime_filter_on_full_tiles_of_every_key_width(ctx, oracle, type_, np_
     j.close()
 
 
+@pytest.mark.parametrize("type_,np_t,lo,hi,n_build", [(K.TYPE_INT, np.int32, -3000, 40_000, 9000), (K.TYPE_BIGINT, np.int64, 1 << 40, (1 << 40) + 100_000, 30_000),
+                                                      (K.TYPE_SMALLINT, np.int16, -20_000, 20_000, 6000), (K.TYPE_TINYINT, np.int8, -50, 60, 40),
+                                                      (K.TYPE_DATE, np.int32, 8000, 10_600, 2000)])
+@pytest.mark.parametrize("nullable", [False, True])
+def test_bitset_runtime_filter_matches_the_oracle(ctx, oracle, type_, np_t, lo, hi, n_build, nullable):
+    """a builder that holds the whole build side may take a RuntimeBitsetFilter (create_join_runtime_filter's rule): the device bitset holds
+    the oracle's bits, and a scan with it keeps exactly the rows RuntimeBitsetFilter::evaluate keeps (exact membership inside [min, max],
+    NULL keys following has_null), on full and on partly selected tiles"""
+    from starrocks_b200 import ops
+    from tests.oracle_lib import OracleBitsetFilter
+    rng = np.random.default_rng(17)
+    bkeys = rng.integers(lo, hi, n_build).astype(np_t)
+    bnulls = None
+    if nullable:
+        bnulls = np.zeros(n_build, np.uint8)
+        bnulls[3] = 1
+    j, build = _build_join(ctx, type_, bkeys, bnulls)
+    rf = j.build_runtime_filter(bitset=True)
+    info = rf.info()
+    live = bkeys[bnulls == 0] if nullable else bkeys
+    assert rf.kind() == K.RF_KIND_BITSET and info["min"] == int(live.min()) and info["max"] == int(live.max())
+    assert OracleBitsetFilter.chosen(oracle, info["min"], info["max"], n_build, 126 << 20)  # the cache of the rule: the GPU's L2
+    want_rf = OracleBitsetFilter(oracle, info["min"], info["max"]).insert_column(build.columns[0])
+    bits = rf.bitset().view(np.uint8)
+    assert bits[:len(want_rf.data())].tolist() == want_rf.data().tolist() and not bits[len(want_rf.data()):].any()
+    n = 8192 * 3 + 1234
+    tinfo = np.iinfo(np_t)
+    span = hi - lo
+    pk = rng.integers(max(tinfo.min, lo - span // 2), min(tinfo.max, hi + span // 2), n).astype(np_t)
+    pnull = (rng.random(n) < 0.04).astype(np.uint8) if nullable else None
+    probe = K.Chunk(n, {1: K.Column.from_ints(type_, pk, nulls=pnull), 2: K.Column.from_ints(K.TYPE_INT, np.arange(n, dtype=np.int32))})
+    for preds, sel in (([], np.ones(n, bool)), ([pred(2, K.PRED_GE, K.TYPE_INT, 5000)], np.arange(n) >= 5000)):
+        keep = (want_rf.evaluate(probe.columns[1]).astype(bool)) & sel
+        assert 0 < keep.sum() < sel.sum()
+        want = [r for r, k in zip(K.chunk_rows(probe, sort=False), keep) if k]
+        for device in (False, True):
+            op = ops.ScanAggOperator(ctx, Q.filter_plan(preds, [1, 2]))
+            op.add_runtime_filter(rf, 1)
+            src, ptrs = (ctx.device_chunk(probe) if device else (probe, []))
+            op.push_chunk(src)
+            op.set_finishing()
+            got = K.chunk_rows(op.pull_all(), sort=False)
+            op.close()
+            for p in ptrs:
+                ctx.device_free(p)
+            assert got == want
+    want_rf.close()
+    rf.close()
+    j.close()
+
+
+def test_bitset_runtime_filter_is_only_taken_when_the_rule_says_so(ctx, oracle):
+    # be/test/exprs/runtime_filter_test.cpp:1409-1455 through the device; sparse keys and partial filters stay bloom filters
+    from starrocks_b200 import ops
+    j, build = _build_join(ctx, K.TYPE_INT, np.arange(0, 200, 2, dtype=np.int32))
+    rf = j.build_runtime_filter(bitset=True)
+    assert rf.kind() == K.RF_KIND_BITSET
+    probe = K.Chunk(9, {1: K.Column.from_ints(K.TYPE_INT, np.array([-1, 5, 10, 15, 20, 25, 200, 0, 0], np.int32), np.array([0] * 7 + [1, 1], np.uint8)),
+                        2: K.Column.from_ints(K.TYPE_INT, np.arange(9, dtype=np.int32))})
+    op = ops.ScanAggOperator(ctx, Q.filter_plan([], [2]))
+    op.add_runtime_filter(rf, 1)
+    op.push_chunk(probe)
+    op.set_finishing()
+    assert [r[0] for r in K.chunk_rows(op.pull_all(), sort=False)] == [2, 4]
+    op.close()
+    rf.close()
+    partial = j.build_runtime_filter(expected_rows=1000, bitset=True)  # a partial filter that will be merged: never a bitset
+    assert partial.kind() == K.RF_KIND_BLOOM
+    partial.close()
+    j.close()
+    rng = np.random.default_rng(2)
+    j, _ = _build_join(ctx, K.TYPE_INT, rng.integers(0, 1 << 30, 5000).astype(np.int32))  # 128 MB of bitset for 5000 rows
+    rf = j.build_runtime_filter(bitset=True)
+    assert rf.kind() == K.RF_KIND_BLOOM
+    rf.close()
+    j.close()
+
+
 def test_runtime_filter_misuse_is_reported(ctx):
     from starrocks_b200 import ops
     j, _ = _build_join(ctx, K.TYPE_INT, np.arange(10, dtype=np.int32))

@@ -627,3 +627,27 @@ def test_string_predicates_of_the_reference_tests(oracle):
     ch = K.Chunk(5, {0: K.Column.from_strings([b"", b"ab", b"abc", b"abd", b"b"]), 1: ids})
     assert keep(ScanAggPlan(preds=[pred(0, K.PRED_LT, K.TYPE_VARCHAR, b"abc")], out_slots=[1]), ch) == [0, 1]
     assert keep(ScanAggPlan(preds=[pred(0, K.PRED_GE, K.TYPE_VARCHAR, b"abc")], out_slots=[1]), ch) == [2, 3, 4]
+
+
+def test_bitset_runtime_filter_of_the_reference_test(oracle):
+    # be/test/exprs/runtime_filter_test.cpp:1409-1455 TestEvaluateBitsetFilter: even keys 0..198, min 0 / max 198
+    from tests.oracle_lib import OracleBitsetFilter
+    keys = K.Column.from_ints(K.TYPE_INT, np.arange(0, 200, 2, dtype=np.int32))
+    probe = np.array([-1, 5, 10, 15, 20, 25, 200], np.int32)
+    f = OracleBitsetFilter(oracle, 0, 198).insert_column(keys)
+    assert f.evaluate(K.Column.from_ints(K.TYPE_INT, probe)).tolist() == [0, 0, 1, 0, 1, 0, 0]
+    with_nulls = K.Column.from_ints(K.TYPE_INT, np.concatenate([probe, [0, 0]]).astype(np.int32), np.array([0] * 7 + [1, 1], np.uint8))
+    assert f.evaluate(with_nulls).tolist() == [0, 0, 1, 0, 1, 0, 0, 0, 0]
+    f.close()
+    f = OracleBitsetFilter(oracle, 0, 198).insert_column(K.Column.from_ints(K.TYPE_INT, np.concatenate([np.arange(0, 200, 2), [7]]).astype(np.int32),
+                                                                            np.array([0] * 100 + [1], np.uint8)))  # insert_null()
+    assert f.evaluate(K.Column.from_ints(K.TYPE_INT, probe)).tolist() == [0, 0, 1, 0, 1, 0, 0]
+    assert f.evaluate(with_nulls).tolist() == [0, 0, 1, 0, 1, 0, 0, 1, 1]
+    assert len(f.data()) == 25 and f.data()[0] == 0b01010101  # 199 values, eight per byte, bit (x - min) % 8
+    f.close()
+    # try_create_runtime_bitset_filter (runtime_filter_bank.cpp:160-200): bitset bytes against one byte per build row, the L2 and the L3 cache
+    ch = lambda mn, mx, rows, l2, l3: OracleBitsetFilter.chosen(oracle, mn, mx, rows, l2, l3)
+    assert ch(0, 799, 100, 0, 0) and not ch(0, 800, 100, 0, 0)            # 100 bytes of bitset for 100 rows; 101 bytes is too many
+    assert ch(0, 3199, 100, 1 << 20, 0) and not ch(0, 3200, 100, 1 << 20, 0)  # up to 4x when it fits the L2
+    assert not ch(0, 3199, 100, 399, 0) and ch(0, 1599, 100, 0, 1 << 25) and not ch(0, 1600, 100, 0, 1 << 25)  # 2x for the L3
+    assert not ch(5, 4, 100, 1 << 20, 1 << 25)                            # empty build side: min > max
