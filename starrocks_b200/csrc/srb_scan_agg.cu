@@ -1841,8 +1841,14 @@ private:
                 for (size_t i = 0; i < L_.cols.size() && i < (size_t)MAX_COLS; i++) any = (nullable[i] = L_.cols[i].nullable) || any;
                 const int hint = (int)std::min<int64_t>(plan_.group_hint, 1 << 30);
                 JitShape js;
-                if (jit_shape_of(L_.prog, hint, nullptr, js)) jit_src_[0] = jit_source(js);
-                if (any && jit_shape_of(L_.prog, hint, nullable, js)) jit_src_[1] = jit_source(js);
+                if (jit_shape_of(L_.prog, hint, nullptr, js)) {
+                    jit_src_[0] = jit_source(js);
+                    jit_gmax_[0] = js.gmax;
+                }
+                if (any && jit_shape_of(L_.prog, hint, nullable, js)) {
+                    jit_src_[1] = jit_source(js);
+                    jit_gmax_[1] = js.gmax;
+                }
                 for (int v = 0; v < 2; v++)
                     if (!jit_src_[v].empty()) jit_[v] = JitCache::get().peek(jit_src_[v]); // an earlier operator may have compiled it already
             }
@@ -2277,6 +2283,13 @@ private:
             // a shape compiled at run time: start the compilation at the first large batch, use it once it is ready
             auto jit_variant = [&](int v) -> const JitLoaded* {
                 if (jit_src_[v].empty() || jit_failed_[v]) return nullptr;
+                if (L_.prog.n_keys) {
+                    // a table-path shape sends every row to the table: with a few dozen groups the atomics pile up on the same addresses
+                    // (SSB Q4.1's 35 groups: 2.1 ms for 9.5 M rows), where the interpreter's shared-memory mirror takes 0.1 ms. And a
+                    // directory shape whose directory the table has outgrown (the planner's estimate was wrong) would do the same.
+                    if (jit_gmax_[v] == 0 && generic_shared_cap() > 0) return nullptr;
+                    if (jit_gmax_[v] > 0 && occupied_ > (uint64_t)jit_gmax_[v]) return nullptr;
+                }
                 if (!jit_[v] && n >= jit_min_rows_) jit_[v] = JitCache::get().acquire(jit_src_[v], jit_mode_ == 2);
                 if (!jit_[v]) return nullptr;
                 const JitLoaded* k = jit_[v]->get(ctx->cfg.device);
@@ -2907,6 +2920,7 @@ private:
     std::shared_ptr<JitEntry> jit_[2];
     const JitLoaded* jit_kernel_ = nullptr; // the variant this batch runs, nullptr: a built-in shape or the interpreter
     bool jit_failed_[2] = {false, false};
+    int jit_gmax_[2] = {0, 0}; // directory size of the variant's shape (0: table path)
     int64_t jit_launches_ = 0;
     static int jit_mode_from_env() {
         const char* m = getenv("SRB_JIT");
