@@ -975,6 +975,7 @@ SRB_D void rf_test_full(const RfArgs& a, const uint32_t* __restrict__ dir, const
 // RuntimeBitsetFilter (exprs/runtime_filter.h:1583-1700, ComposedRuntimeFilter's min / max in front of it): a row passes iff its key lies in
 // [min, max] and bit (key - min) is set; NULL keys pass iff has_null. One word load and a shift instead of a 32-byte bucket and eight
 // salted multiplies; the bitsets of dimension keys (a few hundred KB) stay in L1 / L2.
+constexpr int RF_BITS_U = 8; // rows per thread and step of the bitset paths: eight independent key loads in flight (the test is a load and a shift: latency is all there is)
 template <bool NULLS, class KT>
 SRB_D void rf_bits_full(const RfArgs& a, const KT* __restrict__ keys, const uint8_t* __restrict__ nulls, uint32_t* smask, int lane) {
     constexpr long long KMIN = (long long)std::numeric_limits<KT>::min(), KMAX = (long long)std::numeric_limits<KT>::max();
@@ -985,26 +986,26 @@ SRB_D void rf_bits_full(const RfArgs& a, const KT* __restrict__ keys, const uint
     const long long mn = a.v.min;
     const bool null_pass = a.v.has_null != 0;
 #pragma unroll 1
-    for (uint32_t j0 = 0; j0 < (uint32_t)FTILE; j0 += 256 * 4) {
-        KT x[4];
-        uint8_t nl[4] = {};
-        uint64_t idx[4];
-        uint32_t w[4];
-        bool in[4];
+    for (uint32_t j0 = 0; j0 < (uint32_t)FTILE; j0 += 256 * RF_BITS_U) {
+        KT x[RF_BITS_U];
+        uint8_t nl[RF_BITS_U] = {};
+        uint64_t idx[RF_BITS_U];
+        uint32_t w[RF_BITS_U];
+        bool in[RF_BITS_U];
 #pragma unroll
-        for (int u = 0; u < 4; u++) x[u] = keys[j0 + u * 256 + threadIdx.x];
+        for (int u = 0; u < RF_BITS_U; u++) x[u] = keys[j0 + u * 256 + threadIdx.x];
         if constexpr (NULLS) {
 #pragma unroll
-            for (int u = 0; u < 4; u++) nl[u] = nulls[j0 + u * 256 + threadIdx.x];
+            for (int u = 0; u < RF_BITS_U; u++) nl[u] = nulls[j0 + u * 256 + threadIdx.x];
         }
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < RF_BITS_U; u++) {
             in[u] = x[u] >= lo && x[u] <= hi;
             idx[u] = in[u] ? (uint64_t)((long long)x[u] - mn) : 0ULL;
             w[u] = __ldg(bits + (idx[u] >> 5));
         }
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < RF_BITS_U; u++) {
             bool pass = in[u] && ((w[u] >> (idx[u] & 31)) & 1u);
             if constexpr (NULLS) pass = nl[u] ? null_pass : pass;
             const uint32_t word = __ballot_sync(0xffffffffu, pass);
@@ -1023,31 +1024,31 @@ SRB_D void rf_bits_list(const RfArgs& a, const KT* __restrict__ keys, const uint
     const long long mn = a.v.min;
     const bool null_pass = a.v.has_null != 0;
 #pragma unroll 1
-    for (uint32_t j0 = 0; j0 < total; j0 += 256 * 4) {
-        uint32_t r[4], w[4];
-        KT x[4];
-        uint8_t nl[4] = {};
-        uint64_t idx[4];
-        bool in[4];
+    for (uint32_t j0 = 0; j0 < total; j0 += 256 * RF_BITS_U) {
+        uint32_t r[RF_BITS_U], w[RF_BITS_U];
+        KT x[RF_BITS_U];
+        uint8_t nl[RF_BITS_U] = {};
+        uint64_t idx[RF_BITS_U];
+        bool in[RF_BITS_U];
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < RF_BITS_U; u++) {
             const uint32_t j = j0 + u * 256 + threadIdx.x;
             r[u] = j < total ? (uint32_t)sidx[j] : 0xFFFFFFFFu;
         }
 #pragma unroll
-        for (int u = 0; u < 4; u++) x[u] = keys[r[u] == 0xFFFFFFFFu ? 0u : r[u]];
+        for (int u = 0; u < RF_BITS_U; u++) x[u] = keys[r[u] == 0xFFFFFFFFu ? 0u : r[u]];
         if constexpr (NULLS) {
 #pragma unroll
-            for (int u = 0; u < 4; u++) nl[u] = nulls[r[u] == 0xFFFFFFFFu ? 0u : r[u]];
+            for (int u = 0; u < RF_BITS_U; u++) nl[u] = nulls[r[u] == 0xFFFFFFFFu ? 0u : r[u]];
         }
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < RF_BITS_U; u++) {
             in[u] = x[u] >= lo && x[u] <= hi;
             idx[u] = in[u] ? (uint64_t)((long long)x[u] - mn) : 0ULL;
             w[u] = __ldg(bits + (idx[u] >> 5));
         }
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < RF_BITS_U; u++) {
             bool pass = in[u] && ((w[u] >> (idx[u] & 31)) & 1u);
             if constexpr (NULLS) pass = nl[u] ? null_pass : pass;
             if (!pass && r[u] != 0xFFFFFFFFu) atomicAnd(&smask[r[u] >> 5], ~(1u << (r[u] & 31)));
@@ -1355,6 +1356,26 @@ __global__ void __launch_bounds__(256, 4) k_compact(const __grid_constant__ Comp
             bits &= bits - 1;
         }
         __syncthreads();
+        if (total * (uint32_t)ca.n_cols <= 1024u) {
+            // a handful of rows (a star join's scan keeps 1-2 % of a tile): one (column, row) per thread, so the loads of ALL columns are in
+            // flight together instead of one column's round trip after the other
+            const uint32_t work = total * (uint32_t)ca.n_cols;
+            for (uint32_t i = threadIdx.x; i < work; i += 256) {
+                const uint32_t cidx = i / total, j = i - cidx * total;
+                const CompactCol& cc = ca.cols[cidx];
+                const uint32_t r = sidx[j];
+                switch (cc.width) {
+                case 1: ((uint8_t*)cc.dst)[out0 + j] = ((const uint8_t*)cc.src)[tile0 + r]; break;
+                case 2: ((uint16_t*)cc.dst)[out0 + j] = ((const uint16_t*)cc.src)[tile0 + r]; break;
+                case 4: ((uint32_t*)cc.dst)[out0 + j] = ((const uint32_t*)cc.src)[tile0 + r]; break;
+                case 8: ((uint64_t*)cc.dst)[out0 + j] = ((const uint64_t*)cc.src)[tile0 + r]; break;
+                default: ((ulonglong2*)cc.dst)[out0 + j] = ((const ulonglong2*)cc.src)[tile0 + r];
+                }
+            }
+            for (int cidx = 0; cidx < ca.n_cols; cidx++)
+                if (ca.cols[cidx].src_null) compact_list(ca.cols[cidx].src_null + tile0, ca.cols[cidx].dst_null + out0, sidx, total);
+            return;
+        }
         for (int cidx = 0; cidx < ca.n_cols; cidx++) {
             const CompactCol& cc = ca.cols[cidx];
             switch (cc.width) {
