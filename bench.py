@@ -746,11 +746,13 @@ def bench_scan(env, args, query: str, steps: int, warmup: int, scaling: str, ten
     stats = []
     barrier(env)
     sampler.start()
+    alloc0 = env.ctx.alloc_stats()
     t0 = time.perf_counter()
     for _ in range(steps):
         out, n_out = step(stats)
     barrier(env)
     dt = time.perf_counter() - t0
+    alloc1 = env.ctx.alloc_stats()
     clocks = sampler.finish()
     # device-side time of the timed steps: CUDA events recorded by the library on the operator's own stream
     kernel_ms = sum(p["kernel_ms"] for _, p in stats)
@@ -787,6 +789,8 @@ def bench_scan(env, args, query: str, steps: int, warmup: int, scaling: str, ten
                                 if query != "highcard" else f"whole phase-1 operator per step: {rows} rows x 16 B in + {n_out // world} groups x 24 B out, "
                                 f"{kernel_s_max / steps * 1e3:.3f} ms of kernels (CUDA events on the op stream)")},
         "clocks": clocks, "result_rows": n_out,
+        # the timed steps should live off the context's buffer pool: driver allocator calls inside them, and the time they took (rank 0)
+        "allocator_in_timed_steps_rank0": {k: alloc1[k] - alloc0[k] for k in ("n_malloc", "n_free", "malloc_us", "free_us")} | {"pooled_bytes": alloc1["pooled_bytes"]},
     }
     if stats and "phase2" in stats[-1][1]:
         result["phase2_profile_rank0"] = dict(stats[-1][1]["phase2"], rows_in=stats[-1][1]["phase2_rows_in"])

@@ -250,6 +250,9 @@ srb_status srb_ctx_device_info(srb_ctx* ctx, int32_t* n_sms, int64_t* hbm_bytes,
 /* returns the ctx's cached (idle) device buffers to the driver (MemTracker release between queries; operators closed on this ctx
  * park their buffers in a per-ctx pool of at most 48 GB) */
 srb_status srb_ctx_trim(srb_ctx* ctx);
+/* harness diagnostics: how often this ctx reached cudaMalloc / cudaFree (a steady loop of operators should live off the pool) and for how
+ * long, and the bytes parked in the pool now */
+srb_status srb_ctx_alloc_stats(srb_ctx* ctx, int64_t* n_malloc, int64_t* n_free, int64_t* malloc_us, int64_t* free_us, int64_t* pooled_bytes);
 /* the CUDA stream an op launches on (cudaStream_t as void*), so harnesses can time with events on it */
 void* srb_op_stream(srb_op* op);
 

@@ -162,13 +162,14 @@ class Column:
         return Column(type_, data, nl, None, precision, scale)
 
     @staticmethod
-    def from_strings(values: Sequence[bytes], nulls=None, type_: int = TYPE_VARCHAR) -> "Column":
+    def from_strings(values: Sequence[bytes], nulls=None, type_: int = TYPE_VARCHAR, max_len: int = 0) -> "Column":
+        """max_len: the column's declared length (VARCHAR(n): TypeDescriptor::len), carried in `precision`; 0 = not declared"""
         offs = np.zeros(len(values) + 1, dtype=np.uint32)
         for i, v in enumerate(values):
             offs[i + 1] = offs[i] + len(v)
         data = np.frombuffer(b"".join(values) + b"\0" * 16, dtype=np.uint8).copy()  # 16-byte tail padding, column/bytes.h:27
         nl = None if nulls is None else np.ascontiguousarray(nulls, dtype=np.uint8)
-        return Column(type_, data, nl, offs, n_bytes=int(offs[-1]))
+        return Column(type_, data, nl, offs, precision=max_len, n_bytes=int(offs[-1]))
 
     def ptr(self, what) -> Optional[int]:
         if what is None:

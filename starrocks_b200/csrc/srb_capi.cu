@@ -78,6 +78,21 @@ srb_status srb_ctx_trim(srb_ctx* ctx) {
 
 void* srb_op_stream(srb_op* op) { return op ? (void*)op->stream : nullptr; }
 
+srb_status srb_ctx_alloc_stats(srb_ctx* ctx, int64_t* n_malloc, int64_t* n_free, int64_t* malloc_us, int64_t* free_us, int64_t* pooled_bytes) {
+    SRB_API_BEGIN
+    if (!ctx) throw srb::Error(SRB_INVALID_ARGUMENT, "null ctx");
+    if (n_malloc) *n_malloc = ctx->n_malloc.load();
+    if (n_free) *n_free = ctx->n_free.load();
+    if (malloc_us) *malloc_us = ctx->malloc_us.load();
+    if (free_us) *free_us = ctx->free_us.load();
+    if (pooled_bytes) {
+        std::lock_guard<std::mutex> g(ctx->pool_mu);
+        *pooled_bytes = ctx->pool_bytes;
+    }
+    return SRB_OK;
+    SRB_API_END
+}
+
 srb_status srb_jit_wait(void) {
     SRB_API_BEGIN
     srb::jit_wait_all();

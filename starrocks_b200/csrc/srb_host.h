@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <chrono>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
@@ -91,6 +92,21 @@ struct srb_ctx {
     std::mutex pool_mu;
     std::multimap<size_t, void*> pool;
     int64_t pool_bytes = 0;
+    // how often (and for how long) the driver's allocator was reached: what a steady loop of operators should not do (srb_ctx_alloc_stats)
+    std::atomic<int64_t> n_malloc{0}, n_free{0}, malloc_us{0}, free_us{0};
+    cudaError_t timed_malloc(void** p, size_t n) {
+        const auto t0 = std::chrono::steady_clock::now();
+        const cudaError_t e = cudaMalloc(p, n);
+        malloc_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count();
+        n_malloc++;
+        return e;
+    }
+    void timed_free(void* p) {
+        const auto t0 = std::chrono::steady_clock::now();
+        cudaFree(p);
+        free_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count();
+        n_free++;
+    }
     static size_t round_size(size_t n) {
         if (n <= 256) return 256;
         if (n >= ((size_t)2 << 20)) return (n + ((size_t)2 << 20) - 1) & ~(((size_t)2 << 20) - 1);
@@ -126,18 +142,18 @@ struct srb_ctx {
                 it = pool.erase(it);
             }
             if (pool_bytes + (int64_t)rounded > limit) {
-                for (void* q : evict) cudaFree(q);
+                for (void* q : evict) timed_free(q);
                 return false;
             }
             pool.emplace(rounded, p);
             pool_bytes += (int64_t)rounded;
         }
-        for (void* q : evict) cudaFree(q);
+        for (void* q : evict) timed_free(q);
         return true;
     }
     void pool_clear() {
         std::lock_guard<std::mutex> g(pool_mu);
-        for (auto& kv : pool) cudaFree(kv.second);
+        for (auto& kv : pool) timed_free(kv.second);
         pool.clear();
         pool_bytes = 0;
     }
@@ -213,7 +229,10 @@ struct DevBuf {
     ~DevBuf() { release(); }
     void release() {
         if (p) {
-            if (!ctx || !ctx->pool_give(bytes, p)) cudaFree(p);
+            if (!ctx)
+                cudaFree(p);
+            else if (!ctx->pool_give(bytes, p))
+                ctx->timed_free(p);
             if (ctx) ctx->mem_in_use -= (int64_t)bytes;
         }
         p = nullptr;
@@ -230,11 +249,11 @@ struct DevBuf {
                                                     (long long)c->cfg.mem_limit));
         p = c->pool_take(n);
         if (!p) {
-            cudaError_t e = cudaMalloc(&p, n);
+            cudaError_t e = c->timed_malloc(&p, n);
             if (e == cudaErrorMemoryAllocation) { // give the cached buffers back to the driver and retry once
                 cudaGetLastError();
                 c->pool_clear();
-                e = cudaMalloc(&p, n);
+                e = c->timed_malloc(&p, n);
             }
             if (e != cudaSuccess) {
                 p = nullptr;

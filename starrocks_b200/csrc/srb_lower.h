@@ -286,13 +286,15 @@ inline Lowered lower_plan(const PlanCopy& plan, const srb_chunk* first) {
         const ColMeta& cm = L.cols[nd.col];
         d.nullable = cm.nullable ? 1 : 0;
         d.width = nd.kind == CK_BINARY ? 0 : nd.width;
-        kb += d.nullable + (d.width ? d.width : 4);
+        // a CHAR / VARCHAR key column may carry its declared length (TypeDescriptor::len) in `precision`: the key area is sized for it.
+        // Without one (0) the key area stays at 16 bytes and a row whose serialized key is longer is reported when it is met.
+        kb += d.nullable + (d.width ? d.width : 4 + std::max(0, cm.precision));
         if (d.width == 0) var = true;
         L.key_out.push_back({k, cm.type, cm.precision, cm.scale, cm.nullable});
     }
-    if (kb > 16) throw Error(SRB_NOT_IMPLEMENTED, fmt("packed group key of %d bytes (limit 16)", kb));
+    if (kb > 8 * MAX_KEY_WORDS) throw Error(SRB_NOT_IMPLEMENTED, fmt("packed group key of %d bytes (limit %d)", kb, 8 * MAX_KEY_WORDS));
     P.key_bytes = var ? 0 : kb;
-    P.key_words = (var || kb > 8) ? 2 : 1;
+    P.key_words = kb > 16 ? (kb + 7) / 8 : ((var || kb > 8) ? 2 : 1); // beyond two words: wide keys (the interpreter's, srb_rowpipe.cuh)
     // aggregates + slot layout
     P.n_aggs = (int)plan.aggs.size();
     auto can_be_null = [&](int ni) {
@@ -310,7 +312,7 @@ inline Lowered lower_plan(const PlanCopy& plan, const srb_chunk* first) {
         return false;
     };
     // slot header: pair A {meta, key word 0}, pair B {key word 1, ready flag} for 16-byte keys (srb_prog.h)
-    int off = (P.n_keys && P.key_words == 2) ? 32 : 16;
+    int off = (P.n_keys && P.key_words >= 2) ? 32 + (((P.key_words - 2) * 8 + 15) & ~15) : 16;
     P.off_state = off;
     // pairs need 16-byte alignment
     std::vector<int> need_pair(P.n_aggs, 0), need_n(P.n_aggs, 0);

@@ -16,6 +16,7 @@ constexpr int MAX_NODES = 24;
 constexpr int MAX_PREDS = 16;
 constexpr int MAX_KEYS = 8;
 constexpr int MAX_AGGS = 12;
+constexpr int MAX_KEY_WORDS = 8; // a packed group key is at most 64 bytes (one or two words: the fast paths; three to eight: "wide" keys)
 
 // column kinds
 constexpr int CK_INT = 0, CK_DOUBLE = 1, CK_BINARY = 2;
@@ -82,9 +83,9 @@ struct DProg {
     int32_t n_cols, n_nodes, n_preds, n_keys, n_aggs;
     int32_t phase_seed;  // 1 or 2: which phmap seed the table hash uses (agg_hash_variant.h:303-308)
     int32_t key_bytes;   // fixed packed key length, 0 when a binary key makes it per-row
-    int32_t key_words;   // 1 or 2 (8- or 16-byte key area in a slot)
+    int32_t key_words;   // 1 or 2 (8- or 16-byte key area in a slot), 3..MAX_KEY_WORDS for wide keys (the words past the second follow pair B)
     int32_t slot_bytes;  // stride of one table slot (multiple of 16)
-    int32_t off_state;   // first byte after the key header (16 or 32)
+    int32_t off_state;   // first byte after the key header (16, 32, or 32 + the wide key's further words rounded up to 16)
     int32_t _pad[2];
     ColBind cols[MAX_COLS];
     DNode nodes[MAX_NODES];

@@ -370,6 +370,119 @@ SRB_D PackedKey pack_key(const DProg& p, const Val* v, int64_t row) {
     return k;
 }
 
+// ---- wide keys: 17 to 64 packed bytes (three BIGINT keys, a DECIMAL128 beside a date, a VARCHAR(40)) -----------------------------------
+// Same serialisation (AggHashMapWithSerializedKey, agg_hash_map.h:652-898: the key columns' bytes one after the other), more words. The
+// slot keeps word 0 in pair A and word 1 + the ready flag in pair B as a 16-byte key does; words 2.. follow pair B and are written BEFORE
+// pair B is published, so a reader that has seen the flag (and fenced) sees them. Only the interpreter takes these keys.
+struct WideKey {
+    uint64_t w[MAX_KEY_WORDS];
+    int len;
+    bool too_long;
+};
+SRB_D void wide_put(WideKey& k, uint64_t bits, int nbytes, int cap_bytes) { // append the low `nbytes` (<= 8) bytes of `bits`
+    if (nbytes < 8) bits &= (1ULL << (8 * nbytes)) - 1;
+    const int off = k.len;
+    if (off + nbytes > cap_bytes) {
+        k.too_long = true;
+        return;
+    }
+    const int word = off >> 3, sh = (off & 7) * 8;
+    k.w[word] |= bits << sh;
+    if (sh && (off & 7) + nbytes > 8) k.w[word + 1] |= bits >> (64 - sh);
+    k.len = off + nbytes;
+}
+SRB_D WideKey pack_key_wide(const DProg& p, const Val* v, int64_t row) {
+    WideKey k;
+#pragma unroll
+    for (int i = 0; i < MAX_KEY_WORDS; i++) k.w[i] = 0;
+    k.len = 0;
+    k.too_long = false;
+    const int cap = p.key_words * 8;
+    for (int i = 0; i < p.n_keys; i++) {
+        const DKey& kd = p.keys[i];
+        const DNode& nd = p.nodes[kd.node];
+        const ColBind& c = p.cols[nd.col];
+        const bool isnull = c.nulls != nullptr && c.nulls[row] != 0;
+        if (kd.nullable) wide_put(k, isnull ? 1 : 0, 1, cap);
+        if (kd.width == 0) { // binary: [u32 length][bytes]
+            const uint32_t b = c.offsets[row], e = c.offsets[row + 1];
+            const uint32_t len = isnull ? 0 : e - b;
+            wide_put(k, len, 4, cap);
+            const uint8_t* s = (const uint8_t*)c.data + b;
+            for (uint32_t j = 0; j < len && !k.too_long; j++) wide_put(k, s[j], 1, cap);
+        } else {
+            const Val& x = v[kd.node];
+            const uint64_t lo = isnull ? 0 : x.lo, hi = isnull ? 0 : (uint64_t)x.hi;
+            if (kd.width <= 8) {
+                wide_put(k, lo, kd.width, cap);
+            } else {
+                wide_put(k, lo, 8, cap);
+                wide_put(k, hi, 8, cap);
+            }
+        }
+    }
+    return k;
+}
+SRB_D uint64_t hash_wide_key(const WideKey& k, int seed) { // SliceHashWithSeed over the serialized bytes (crc_hash_64, util/hash.h:139-170)
+    const uint64_t h = crc_hash_64((const uint8_t*)k.w, k.len, seed == 1 ? 0x811C9DC5ULL : 0x811C9DD7ULL);
+    return h * 0x9E3779B97F4A7C15ULL; // crc values are 32 bits wide: spread them over tag and bucket index
+}
+SRB_D bool wide_rest_equal(const uint8_t* slot, const WideKey& k, int key_words) {
+    bool eq = true;
+    for (int i = 2; i < key_words; i++) eq = eq && ld_relaxed_u64((const uint64_t*)(slot + 32) + (i - 2)) == k.w[i];
+    return eq;
+}
+SRB_D uint8_t* table_find_or_insert_wide(const TableView& t, const WideKey& k, uint64_t hash, bool* inserted) {
+    const uint64_t tagw = (hash & ~3ULL) | SLOT_READY;
+    uint64_t idx = (hash >> 7) & t.mask;
+    *inserted = false;
+    for (int probe = 0; probe < TABLE_MAX_PROBE; probe++) {
+        uint8_t* slot = t.slots + idx * (uint64_t)t.slot_bytes;
+        ulonglong2 a = ld_pair(slot);
+        if (a.x == SLOT_EMPTY) {
+            a = cas_pair(slot, 0ULL, 0ULL, tagw, k.w[0]);
+            if (a.x == SLOT_EMPTY) {
+                for (int i = 2; i < t.key_words; i++) st_relaxed_u64((uint64_t*)(slot + 32) + (i - 2), k.w[i]);
+                __threadfence(); // words 2.. are visible before the flag of pair B is
+                st_pair(slot + 16, k.w[1], 1ULL);
+                *inserted = true;
+                return slot;
+            }
+        }
+        if (a.x == tagw && a.y == k.w[0]) {
+            ulonglong2 b = ld_pair(slot + 16);
+            while (b.y == 0) { // the claimer's further words are in flight
+                __nanosleep(20);
+                b = ld_pair(slot + 16);
+            }
+            __threadfence();
+            if (b.x == k.w[1] && wide_rest_equal(slot, k, t.key_words)) return slot;
+        }
+        idx = (idx + 1) & t.mask;
+    }
+    return nullptr;
+}
+SRB_D uint8_t* table_find_wide(const TableView& t, const WideKey& k, uint64_t hash) {
+    const uint64_t tagw = (hash & ~3ULL) | SLOT_READY;
+    uint64_t idx = (hash >> 7) & t.mask;
+    for (int probe = 0; probe < TABLE_MAX_PROBE; probe++) {
+        uint8_t* slot = t.slots + idx * (uint64_t)t.slot_bytes;
+        const ulonglong2 a = ld_pair(slot);
+        if (a.x == SLOT_EMPTY) return nullptr;
+        if (a.x == tagw && a.y == k.w[0]) {
+            ulonglong2 b = ld_pair(slot + 16);
+            while (b.y == 0) {
+                __nanosleep(20);
+                b = ld_pair(slot + 16);
+            }
+            __threadfence();
+            if (b.x == k.w[1] && wide_rest_equal(slot, k, t.key_words)) return slot;
+        }
+        idx = (idx + 1) & t.mask;
+    }
+    return nullptr;
+}
+
 // hash of the packed key with the reference's functions (agg_hash_map.h:58-98, column/hash_set.h:86-159):
 // 4/8-byte keys as one integer through phmap_mix, 16-byte through Hash128WithSeed, anything else crc_hash_64.
 SRB_D uint64_t hash_packed_key(const PackedKey& k, int seed) {

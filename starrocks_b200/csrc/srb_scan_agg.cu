@@ -174,13 +174,23 @@ __global__ void __launch_bounds__(256) k_scan_agg_generic(const __grid_constant_
             for (int a = 0; a < p.n_aggs; a++) update_agg_local(p, p.aggs[a], acc[a], v, row);
             continue;
         }
-        PackedKey k = pack_key(p, v, row);
-        if (k.too_long) {
-            too_long++;
-            continue;
-        }
         bool fresh;
-        uint8_t* slot = table_find_or_insert(tv, k.lo, k.hi, hash_packed_key(k, p.phase_seed), &fresh);
+        uint8_t* slot;
+        if (p.key_words > 2) { // a wide key (17-64 bytes)
+            const WideKey wk = pack_key_wide(p, v, row);
+            if (wk.too_long) {
+                too_long++;
+                continue;
+            }
+            slot = table_find_or_insert_wide(tv, wk, hash_wide_key(wk, p.phase_seed), &fresh);
+        } else {
+            const PackedKey k = pack_key(p, v, row);
+            if (k.too_long) {
+                too_long++;
+                continue;
+            }
+            slot = table_find_or_insert(tv, k.lo, k.hi, hash_packed_key(k, p.phase_seed), &fresh);
+        }
         inserted += fresh ? 1 : 0;
         if (!slot) {
             atomicOr(&defer_out[bit >> 5], 1u << (bit & 31));
@@ -469,7 +479,9 @@ struct EmitAgg {
     int32_t decode; // MIN/MAX states are biased encodings (srb_rowpipe.cuh): 0 none, 1 max, 2 min; width/is_double pick the codec
 };
 struct EmitArgs {
-    ulonglong2* keys;
+    ulonglong2* keys;      // one record per result row: the packed key, 16 bytes (keys of one or two words) or key_rec_words * 8 (wide keys)
+    int32_t key_rec_words; // 2, or the wide key's word count
+    int32_t _pad;
     EmitAgg aggs[MAX_AGGS];
 };
 
@@ -625,7 +637,14 @@ SRB_D void emit_agg(const DAgg& g, const EmitAgg& e, uint64_t n, uint64_t lo, ui
 SRB_D void emit_row(const DProg& p, const uint8_t* s, const EmitArgs& ea, int64_t row) {
     if (p.n_keys) {
         const uint64_t* k = (const uint64_t*)s;
-        ea.keys[row] = make_ulonglong2(k[1], p.key_words > 1 ? k[2] : 0ULL);
+        if (p.key_words > 2) { // word 0 in pair A, word 1 in pair B, the rest behind pair B
+            uint64_t* rec = (uint64_t*)ea.keys + (size_t)row * ea.key_rec_words;
+            rec[0] = k[1];
+            rec[1] = k[2];
+            for (int i = 2; i < p.key_words; i++) rec[i] = k[4 + (i - 2)];
+        } else {
+            ea.keys[row] = make_ulonglong2(k[1], p.key_words > 1 ? k[2] : 0ULL);
+        }
     }
     for (int a = 0; a < p.n_aggs; a++) {
         const DAgg& g = p.aggs[a];
@@ -655,17 +674,26 @@ __global__ void __launch_bounds__(256) k_stream_rows(const __grid_constant__ DPr
         const int64_t row = base + i0 + lane;
         bool pass = i0 + lane < n && eval_preds(p, row);
         PackedKey k{};
+        WideKey wk;
+        const bool wide = p.key_words > 2;
         if (pass) {
             selected++;
             for (int q = 0; q < p.n_nodes; q++) v[q] = eval_node(p.nodes[q], v, p.cols, row);
-            k = pack_key(p, v, row);
-            if (k.too_long) {
+            bool too;
+            if (wide) {
+                wk = pack_key_wide(p, v, row);
+                too = wk.too_long;
+            } else {
+                k = pack_key(p, v, row);
+                too = k.too_long;
+            }
+            if (too) {
                 too_long++;
                 pass = false;
             }
         }
         if (pass && selective) {
-            uint8_t* slot = table_find(tv, k.lo, k.hi, hash_packed_key(k, p.phase_seed));
+            uint8_t* slot = wide ? table_find_wide(tv, wk, hash_wide_key(wk, p.phase_seed)) : table_find(tv, k.lo, k.hi, hash_packed_key(k, p.phase_seed));
             if (slot) {
                 for (int a = 0; a < p.n_aggs; a++) update_agg_global(p, p.aggs[a], slot, v, row);
                 hits++;
@@ -681,7 +709,12 @@ __global__ void __launch_bounds__(256) k_stream_rows(const __grid_constant__ DPr
         first = __shfl_sync(0xffffffffu, first, leader);
         if (!pass) continue;
         const int64_t pos = row_base + (int64_t)first + __popc(m & ((1u << lane) - 1u));
-        ea.keys[pos] = make_ulonglong2(k.lo, p.key_words > 1 ? k.hi : 0ULL);
+        if (wide) {
+            uint64_t* rec = (uint64_t*)ea.keys + (size_t)pos * ea.key_rec_words;
+            for (int i = 0; i < p.key_words; i++) rec[i] = wk.w[i];
+        } else {
+            ea.keys[pos] = make_ulonglong2(k.lo, p.key_words > 1 ? k.hi : 0ULL);
+        }
         for (int a = 0; a < p.n_aggs; a++) {
             const DAgg& g = p.aggs[a];
             LocalAcc d{0, 0, 0};
@@ -1416,13 +1449,13 @@ struct UnpackArgs {
     int32_t _pad;
     UnpackKey keys[MAX_KEYS];
 };
-__global__ void __launch_bounds__(256) k_unpack_keys(const __grid_constant__ UnpackArgs ua, const ulonglong2* __restrict__ packed, int64_t n) {
+__global__ void __launch_bounds__(256) k_unpack_keys(const __grid_constant__ UnpackArgs ua, const uint64_t* __restrict__ packed, int rec_words, int64_t n) {
     for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
-        const ulonglong2 k = packed[r];
+        const uint64_t* k = packed + (size_t)r * rec_words;
         int off = 0;
         for (int i = 0; i < ua.n_keys; i++) {
             const UnpackKey& u = ua.keys[i];
-            auto byte_at = [&](int o) -> uint64_t { return ((o < 8 ? k.x >> (8 * o) : k.y >> (8 * (o - 8))) & 0xffULL); };
+            auto byte_at = [&](int o) -> uint64_t { return (k[o >> 3] >> (8 * (o & 7))) & 0xffULL; };
             if (u.nullable) u.dst_null[r] = (uint8_t)byte_at(off++);
             uint64_t lo = 0, hi = 0;
             for (int b = 0; b < u.width; b++) {
@@ -1692,6 +1725,7 @@ public:
         if (radix_rows_ > 0) radix_ingest();
         ensure_table();
         const DProg& P = L_.prog;
+        if (P.key_words > 2) throw Error(SRB_NOT_IMPLEMENTED, "set_finishing_merged with group keys beyond 16 bytes: gather the serialized states instead");
         const int W = comm_world(comm), me = comm_rank(comm);
         // room for the peers' groups (every rank of a low-cardinality plan holds about the same few groups; a full table fails the merge)
         if (P.n_keys && (occupied_ + 16) * 4 > cap_ && cap_ < (uint64_t)MERGE_MAX_SLOTS) grow_table(std::min<uint64_t>((occupied_ + 16) * 4, MERGE_MAX_SLOTS));
@@ -1993,7 +2027,7 @@ private:
     // small (hinted: at most 64 slots), a batch large enough to amortise the per-CTA merge, and room for >= 2 entries per CTA
     int lowcard_entries(int64_t n) const {
         const DProg& P = L_.prog;
-        if (!P.n_keys || no_lowcard_ || plan_.group_hint <= 0 || n < ((int64_t)1 << 18) || P.n_aggs < 1) return 0;
+        if (!P.n_keys || P.key_words > 2 || no_lowcard_ || plan_.group_hint <= 0 || n < ((int64_t)1 << 18) || P.n_aggs < 1) return 0;
         const size_t per_entry = (size_t)P.n_aggs * 3 * LC_THREADS * 8;
         const int fit = std::min((int)((size_t)(110 * 1024) / per_entry), LC_MAXG); // two CTAs per SM
         // the planner expects no more groups than a CTA's directory holds (more groups: the shared mirror of k_scan_agg_generic does better)
@@ -2650,12 +2684,15 @@ private:
 
     // ---- output ------------------------------------------------------------------------------------------------------
     // output arrays for `rows` result rows; the first stream_rows_ rows (pass-through rows of a streaming sink) are preserved
+    // bytes of one packed key record in the result's key buffer
+    size_t key_rec_bytes() const { return L_.prog.key_words > 2 ? (size_t)L_.prog.key_words * 8 : 16; }
     EmitArgs emit_args(uint64_t rows) {
         const DProg& P = L_.prog;
         const size_t cap = (size_t)std::max<uint64_t>(1, rows), keep = (size_t)stream_rows_;
         EmitArgs ea{};
-        grow_out(ekeys_, keep * 16, cap * 16);
+        grow_out(ekeys_, keep * key_rec_bytes(), cap * key_rec_bytes());
         ea.keys = ekeys_.as<ulonglong2>();
+        ea.key_rec_words = (int32_t)(key_rec_bytes() / 8);
         eval_.resize(P.n_aggs);
         for (int a = 0; a < P.n_aggs; a++) {
             const AggOutMeta& m = L_.agg_out[a];
@@ -2727,7 +2764,7 @@ private:
     std::vector<RowPiece> row_pieces() const {
         const DProg& P = L_.prog;
         std::vector<RowPiece> v;
-        if (P.n_keys) v.push_back({ekeys_.as<uint8_t>(), 16});
+        if (P.n_keys) v.push_back({ekeys_.as<uint8_t>(), key_rec_bytes()});
         for (int a = 0; a < P.n_aggs; a++) {
             const AggOutMeta& m = L_.agg_out[a];
             v.push_back({eval_[a].val.as<uint8_t>(), (size_t)m.out_width});
@@ -2789,9 +2826,10 @@ private:
             return;
         }
         const DProg& P = L_.prog;
-        // keys: packed 16-byte records -> one column per key
+        // keys: packed records (16 bytes; a wide key's words) -> one column per key
+        const size_t krec = key_rec_bytes();
         std::vector<uint8_t> packed;
-        if (P.n_keys) packed.resize((size_t)n * 16);
+        if (P.n_keys) packed.resize((size_t)n * krec);
         std::vector<std::vector<uint8_t>> vals(P.n_aggs), nulls(P.n_aggs);
         std::vector<std::vector<int64_t>> cnts(P.n_aggs);
         // every piece of the result rows [pos, pos+n): (device source, bytes, host destination)
@@ -2801,7 +2839,7 @@ private:
             void* dst;
         };
         std::vector<Piece> pieces;
-        if (P.n_keys && n) pieces.push_back({ekeys_.as<uint8_t>() + (size_t)pos * 16, (size_t)n * 16, packed.data()});
+        if (P.n_keys && n) pieces.push_back({ekeys_.as<uint8_t>() + (size_t)pos * krec, (size_t)n * krec, packed.data()});
         for (int a = 0; a < P.n_aggs; a++) {
             const AggOutMeta& m = L_.agg_out[a];
             vals[a].resize((size_t)n * m.out_width);
@@ -2858,7 +2896,7 @@ private:
             hslots_.push_back(k);
         }
         for (int64_t r = 0; r < n; r++) {
-            const uint8_t* kb = packed.data() + (size_t)r * 16;
+            const uint8_t* kb = packed.data() + (size_t)r * krec;
             int off = 0;
             for (int k = 0; k < P.n_keys; k++) {
                 HostCol& h = hcols_[k];
@@ -3040,7 +3078,7 @@ void ScanAggOp::device_result_columns(int64_t n) {
         hslots_.push_back(k);
     }
     if (P.n_keys && n > 0) {
-        k_unpack_keys<<<grid_for(n), 256, 0, stream>>>(ua, ekeys_.as<ulonglong2>() + out_pos_, n);
+        k_unpack_keys<<<grid_for(n), 256, 0, stream>>>(ua, ekeys_.as<uint64_t>() + (size_t)out_pos_ * (key_rec_bytes() / 8), (int)(key_rec_bytes() / 8), n);
         launches++;
         SRB_CUDA(cudaGetLastError());
     }

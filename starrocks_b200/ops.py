@@ -20,7 +20,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libsrb.so"
 _lib = None
 
 EXPORTS = [
-    "srb_ctx_create", "srb_ctx_destroy", "srb_last_error", "srb_ctx_device_info", "srb_ctx_trim", "srb_op_stream", "srb_jit_wait", "srb_jit_stats", "srb_jit_check_plan", "srb_runtime_filter_kind", "srb_runtime_filter_bitset",
+    "srb_ctx_create", "srb_ctx_destroy", "srb_last_error", "srb_ctx_device_info", "srb_ctx_trim", "srb_ctx_alloc_stats", "srb_op_stream", "srb_jit_wait", "srb_jit_stats", "srb_jit_check_plan", "srb_runtime_filter_kind", "srb_runtime_filter_bitset",
     "srb_scan_agg_create", "srb_join_create", "srb_op_push_chunk", "srb_op_push_pages", "srb_op_set_finishing_merged", "srb_op_set_finishing", "srb_op_has_output",
     "srb_op_need_input", "srb_op_is_finished", "srb_op_pull_chunk", "srb_op_pull_all", "srb_op_pull_device",
     "srb_op_cancel", "srb_op_close", "srb_op_sync", "srb_op_counters", "srb_op_profile",
@@ -55,6 +55,7 @@ def lib() -> C.CDLL:
     L.srb_ctx_destroy.restype = None
     L.srb_ctx_device_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i64), C.POINTER(i32)]
     L.srb_ctx_trim.argtypes = [vp]
+    L.srb_ctx_alloc_stats.argtypes = [vp] + [C.POINTER(i64)] * 5
     L.srb_op_stream.argtypes = [vp]
     L.srb_op_stream.restype = vp
     L.srb_jit_wait.argtypes = []
@@ -164,6 +165,12 @@ class Context:
         a, b, c = C.c_int32(), C.c_int64(), C.c_int32()
         _check(self.L.srb_ctx_device_info(self.h, C.byref(a), C.byref(b), C.byref(c)))
         return {"n_sms": a.value, "hbm_bytes": b.value, "sm_arch": c.value}
+
+    def alloc_stats(self) -> dict:
+        """cudaMalloc / cudaFree calls and microseconds of this context, and the bytes parked in its pool (srb_ctx_alloc_stats)"""
+        v = [C.c_int64() for _ in range(5)]
+        _check(self.L.srb_ctx_alloc_stats(self.h, *[C.byref(x) for x in v]))
+        return dict(zip(("n_malloc", "n_free", "malloc_us", "free_us", "pooled_bytes"), [x.value for x in v]))
 
     def trim(self):
         """give the idle pooled device buffers back to the driver"""

@@ -450,13 +450,7 @@ def test_group_by_key_shapes(ctx, oracle, keys, null_frac):
     aggs = [(K.AGG_SUM, m), (K.AGG_AVG, m), (K.AGG_COUNT, m), (K.AGG_COUNT, None), (K.AGG_MIN, m), (K.AGG_MAX, m), (K.AGG_SUM, d), (K.AGG_AVG, d),
             (K.AGG_MIN, d), (K.AGG_MAX, d)]
     plan = ScanAggPlan(exprs=e, keys=ks, aggs=aggs)
-    if keys == [K.TYPE_DECIMAL128] and null_frac > 0:
-        # null byte + 16 value bytes = 17 > the 16-byte packed key area: reported, never silently wrong
-        from starrocks_b200 import ops
-        with pytest.raises(ops.SrbError) as ei:
-            run_gpu(ctx, plan, ch)
-        assert ei.value.code == K.NOT_IMPLEMENTED
-        return
+    # (a nullable DECIMAL128 key packs to 17 bytes: a wide key, three words)
     check(ctx, oracle, plan, ch)
     check(ctx, oracle, plan, ch, piece_rows=4096)
 
@@ -475,6 +469,88 @@ def test_group_by_binary_keys(ctx, oracle):
     check(ctx, oracle, plan, ch)
     check(ctx, oracle, plan, ch, piece_rows=1000)
     check(ctx, oracle, plan, ch, device=True)
+
+
+WIDE_KEY_CASES = {
+    "three BIGINT (24 bytes)": [K.TYPE_BIGINT, K.TYPE_BIGINT, K.TYPE_BIGINT],
+    "four BIGINT (32 bytes)": [K.TYPE_BIGINT] * 4,
+    "nullable BIGINT, DECIMAL128, INT (30 bytes)": [(K.TYPE_BIGINT, True), K.TYPE_DECIMAL128, (K.TYPE_INT, True)],
+    "VARCHAR(40) and INT (up to 48 bytes)": [("str", 40, True), K.TYPE_INT],
+    "two VARCHAR(20) (up to 48 bytes)": [("str", 20, False), ("str", 20, False)],
+    "eight words: DECIMAL128 x 4": [K.TYPE_DECIMAL128] * 4,
+}
+
+
+def _wide_key_chunk(rng, spec, n, n_groups):
+    """key columns drawn from a pool of n_groups distinct key tuples + a BIGINT and a DECIMAL64 measure"""
+    pool = []
+    for _ in range(n_groups):
+        t = []
+        for s_ in spec:
+            if isinstance(s_, tuple) and s_[0] == "str":
+                t.append(bytes(rng.integers(97, 123, int(rng.integers(0, s_[1] + 1))).astype(np.uint8)))
+            else:
+                ty = s_[0] if isinstance(s_, tuple) else s_
+                t.append(int(rng.integers(-(1 << 62), 1 << 62)) * (10**15 if ty == K.TYPE_DECIMAL128 else 1) if ty != K.TYPE_INT else int(rng.integers(-1000, 1000)))
+        pool.append(t)
+    pick = rng.integers(0, n_groups, n)
+    cols = {}
+    for i, s_ in enumerate(spec):
+        vals = [pool[g][i] for g in pick]
+        if isinstance(s_, tuple) and s_[0] == "str":
+            cols[i] = K.Column.from_strings(vals, (rng.random(n) < 0.03).astype(np.uint8) if s_[2] else None, max_len=s_[1])
+        else:
+            ty, nullable = s_ if isinstance(s_, tuple) else (s_, False)
+            cols[i] = K.Column.from_ints(ty, vals, (rng.random(n) < 0.03).astype(np.uint8) if nullable else None, 38 if ty == K.TYPE_DECIMAL128 else 0, 0)
+    cols[20] = K.Column.from_ints(K.TYPE_BIGINT, rng.integers(-1000, 1000, n))
+    cols[21] = K.Column.from_ints(K.TYPE_DECIMAL64, rng.integers(0, 10**6, n), (rng.random(n) < 0.05).astype(np.uint8), 15, 2)
+    return K.Chunk(n, cols)
+
+
+def _wide_key_plan(spec, phase=K.AGG_UPDATE_FINALIZE, hint=0):
+    e = ExprBuilder()
+    keys = []
+    for i, s_ in enumerate(spec):
+        if isinstance(s_, tuple) and s_[0] == "str":
+            keys.append(e.slot(i, K.TYPE_VARCHAR))
+        else:
+            ty = s_[0] if isinstance(s_, tuple) else s_
+            keys.append(e.slot(i, ty, 38 if ty == K.TYPE_DECIMAL128 else 0, 0))
+    v, d = e.slot(20, K.TYPE_BIGINT), e.slot(21, K.TYPE_DECIMAL64, 15, 2)
+    return ScanAggPlan(preds=[pred(20, K.PRED_GE, K.TYPE_BIGINT, -900)], exprs=e, keys=keys, phase=phase, group_hint=hint,
+                       aggs=[(K.AGG_SUM, v), (K.AGG_COUNT, None), (K.AGG_AVG, d), (K.AGG_MIN, v), (K.AGG_MAX, d)])
+
+
+@pytest.mark.parametrize("name", list(WIDE_KEY_CASES))
+def test_group_keys_beyond_16_bytes(ctx, oracle, name):
+    # AggHashMapWithSerializedKey (agg_hash_map.h:652-898) with 17-64 serialized bytes: the slot carries the further key words behind pair B;
+    # few groups (every row on the same slots), many groups (the table grows from 1024 slots: rehash + replay), host pieces and device chunks
+    spec = WIDE_KEY_CASES[name]
+    rng = np.random.default_rng(31)
+    few = _wide_key_chunk(rng, spec, 40_000, 50)
+    check(ctx, oracle, _wide_key_plan(spec, hint=50), few)
+    check(ctx, oracle, _wide_key_plan(spec), few, device=True)
+    many = _wide_key_chunk(rng, spec, 200_000, 60_000)
+    got = check(ctx, oracle, _wide_key_plan(spec), many)
+    assert got.n_rows > 30_000
+    check(ctx, oracle, _wide_key_plan(spec), many, piece_rows=30_000)
+    check(ctx, oracle, _wide_key_plan(spec, hint=100_000), many, device=True)
+
+
+def test_wide_group_keys_serialize_phase_and_too_long(ctx, oracle):
+    from starrocks_b200 import ops
+    spec = WIDE_KEY_CASES["VARCHAR(40) and INT (up to 48 bytes)"]
+    rng = np.random.default_rng(32)
+    ch = _wide_key_chunk(rng, spec, 60_000, 3000)
+    want = K.chunk_rows(oracle.scan_agg(_wide_key_plan(spec), ch))
+    check(ctx, oracle, _wide_key_plan(spec, phase=K.AGG_UPDATE_SERIALIZE), ch)  # intermediate rows (AVG blobs) keyed by the wide keys
+    # a string longer than the declared length does not fit the key area: reported, not truncated
+    bad = K.Chunk(3, {0: K.Column.from_strings([b"a", b"b" * 41, b"c"], max_len=40), 1: K.Column.from_ints(K.TYPE_INT, np.arange(3, dtype=np.int32)),
+                      20: K.Column.from_ints(K.TYPE_BIGINT, np.arange(3)), 21: K.Column.from_ints(K.TYPE_DECIMAL64, np.arange(3), np.zeros(3, np.uint8), 15, 2)})
+    with pytest.raises(ops.SrbError) as ex:
+        run_gpu(ctx, _wide_key_plan(spec), bad)
+    assert ex.value.code == K.NOT_IMPLEMENTED
+    assert len(want) > 2000
 
 
 def test_table_growth_and_deferred_rows(ctx, oracle):

@@ -61,3 +61,16 @@ def test_fused_runtime_filters_give_the_same_rows(ctx, oracle, monkeypatch):
         assert got == want
         seen[fused] = (stage_rows, launches)
     assert seen[True][0] == seen[False][0]
+
+
+def test_force_streaming_with_group_keys_beyond_16_bytes(ctx, oracle):
+    # pass-through rows carry the wide key's words as they are (k_stream_rows writes key_words x 8 bytes per row)
+    from tests.test_gpu_parity import WIDE_KEY_CASES, _wide_key_chunk, _wide_key_plan
+    spec = WIDE_KEY_CASES["nullable BIGINT, DECIMAL128, INT (30 bytes)"]
+    rng = np.random.default_rng(5)
+    ch = _wide_key_chunk(rng, spec, 20_000, 300)
+    plan = _wide_key_plan(spec, phase=K.AGG_UPDATE_SERIALIZE)
+    want, _ = oracle.scan_agg_streaming(plan, ch, K.STREAMING_FORCE_STREAMING)
+    got, st = _stream_gpu(ctx, plan, ch, K.STREAMING_FORCE_STREAMING, 4096)
+    assert got.n_rows == want.n_rows and st["groups"] == 0
+    assert K.chunk_rows(got) == K.chunk_rows(want)
