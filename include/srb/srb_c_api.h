@@ -67,7 +67,8 @@ typedef int32_t srb_status;
  */
 typedef struct srb_column {
     int32_t type; /* SRB_TYPE_* */
-    int32_t precision;
+    int32_t precision;       /* decimals; CHAR / VARCHAR: the declared length (TypeDescriptor::len) when known, 0 otherwise — a GROUP BY
+                                over such a column sizes its key area for it (serialized keys of up to 64 bytes; undeclared: 16) */
     int32_t scale;
     int32_t mem_kind;        /* SRB_MEM_* */
     const void* data;        /* T[n_rows]; for VARCHAR/VARBINARY the byte buffer */
