@@ -49,7 +49,7 @@ def parse():
     ap.add_argument("--query", default="q1", choices=["q1", "q6", "highcard", "q3", "ssb"])
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"], help="scan queries at N > 1: every rank its own SF100 shard (weak) or SF100 split over the ranks (strong)")
     ap.add_argument("--rows", type=int, default=0, help="rows per rank (default: the SF100 table)")
-    ap.add_argument("--e2e-rows", type=int, default=64 << 20)
+    ap.add_argument("--e2e-rows", type=int, default=256 << 20, help="rows per end-to-end step fed as encoded pages (the decoded-column variant uses at most 64 Mi)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="CPU time budget of every cpu_baseline (1 warm-up + best of 5 on a sample sized for it)")
     ap.add_argument("--sub-steps", type=int, default=5, help="timed steps of every workload under `queries`")
     ap.add_argument("--parity-rows", type=int, default=8 << 20, help="rows (fact-table rows) of the bounded parity sample, over all ranks")
@@ -557,7 +557,7 @@ def scan_e2e(env, args, query, w, chunk, rows, warmup, steps):
     import ctypes as C
     from starrocks_b200 import capi as K, ops
     ctx = env.ctx
-    n = int(min(args.e2e_rows, rows))
+    n = int(min(args.e2e_rows, rows, 64 << 20))
     host = K.Chunk(n)
     pins, h2d = [], 0
     for slot, c in chunk.columns.items():
@@ -604,7 +604,9 @@ def scan_e2e_pages(env, args, query, w, tensors, row0, rows, warmup, steps):
     from starrocks_b200 import capi as K, ops, pages as PG, tpch_synth as T
     torch, ctx = env.torch, env.ctx
     n = int(min(args.e2e_rows, rows))
-    page_rows, set_pages = 1 << 16, 128  # 64 Ki values per page, 8 Mi rows per page set
+    # 64 Ki values per page, 32 Mi rows per page set: a column's encoded bytes of a set (~40 MB for an 8-byte column of Q1) cross PCIe as ONE
+    # copy, and copies below ~30 MB do not reach the link's rate (measured: 7 x 9.5 MB 46.7 GB/s, 7 x 38 MB 55.2 GB/s; tools/h2d_probe.py)
+    page_rows, set_pages = 1 << 16, int(os.environ.get("SRB_E2E_SET_PAGES", "512"))
     cols, pins, h2d = {}, [], 0
     try:
         for name in w["cols"]:
@@ -648,7 +650,7 @@ def scan_e2e_pages(env, args, query, w, tensors, row0, rows, warmup, steps):
     return {"value": n * env.world * steps / dt, "unit": "rows/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "rows_per_step": n, "steps": steps,
             "encoded_bytes_per_row": h2d / n, "decoded_bytes_per_row": w["bytes_per_row"],
             "note": "frame-of-reference data pages (the reference's FOR_ENCODING, 64 Ki values per page) in pinned host memory pushed through "
-                    "srb_op_push_pages in page sets of 8 Mi rows: H2D copy of the encoded bytes, decode on the device, scan, aggregate; the copy of a "
+                    "srb_op_push_pages in page sets of 32 Mi rows: H2D copy of the encoded bytes, decode on the device, scan, aggregate; the copy of a "
                     "page set overlaps the kernels of the previous one" + ("; the ~10^7 result groups stay on the device, the row count is read" if query == "highcard" else "")}, out
 
 

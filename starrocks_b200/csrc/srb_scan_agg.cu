@@ -1584,6 +1584,7 @@ public:
             lower(&first);
         }
         if (stage_[cur_stage_].rows) flush_stage(); // host rows pushed earlier keep their place in front of these
+        HostTrace ptr_;
         Stage& st = stage_[cur_stage_];
         if (!copy_stream_ && !(copy_stream_ = ctx->take_stream())) throw Error(SRB_INTERNAL_ERROR, "cudaStreamCreate failed");
         if (!st.copied && !(st.copied = ctx->take_event(false))) throw Error(SRB_INTERNAL_ERROR, "cudaEventCreate failed");
@@ -1632,7 +1633,10 @@ public:
             st.data[i].ensure(ctx, (size_t)n_rows * w);
             const uint8_t* bytes = (const uint8_t*)c.data;
             if (c.mem_kind != SRB_MEM_DEVICE) {
-                st.enc[i].ensure(ctx, (size_t)(hi - lo) + 64); // decoders may read a few bytes past a frame: the copy is padded
+                // decoders may read a few bytes past a frame: the copy is padded. Sized like the decoded rows (an encoded page set is smaller,
+                // bar a few pathological frames), so that page sets of slightly different encoded sizes reuse the buffer instead of
+                // reallocating it (cudaFree + cudaMalloc in the middle of the copy queue: 0.2 ms per page set)
+                st.enc[i].ensure(ctx, std::max((size_t)(hi - lo) + 64, (size_t)n_rows * w + 4096));
                 if (hi > lo) SRB_CUDA(cudaMemcpyAsync(st.enc[i].p, (const uint8_t*)c.data + lo, (size_t)(hi - lo), cudaMemcpyHostToDevice, copy_stream_));
                 bytes = st.enc[i].as<uint8_t>();
             }
@@ -1644,6 +1648,12 @@ public:
         }
         SRB_CUDA(cudaEventRecord(st.copied, copy_stream_));
         SRB_CUDA(cudaStreamWaitEvent(stream, st.copied, 0));
+        ptr_.mark("push_pages: copies enqueued");
+        // The previous page set's batch is checked NOW, while only its own kernels are on the compute stream: waiting after this set's
+        // decode kernels were enqueued made the host wait for this set's copy as well, so the next set's copy was never queued behind it
+        // (one decode time of idle PCIe per page set)
+        wait_pending();
+        ptr_.mark("push_pages: previous batch");
         unsigned int* err = page_err_.as<unsigned int>();
         for (const Work& wk : work) {
             if (wk.n_pages == 0) continue;
@@ -1670,7 +1680,9 @@ public:
         rows_in += n_rows;
         st.rows = n_rows;
         pages_pushed_ = true;
+        ptr_.mark("push_pages: decodes enqueued");
         flush_stage(); // checks the previous batch, launches this one, switches stages
+        ptr_.mark("push_pages: flush_stage");
         // (corrupt pages are reported by set_finishing: asking the device here would stall the copy queue behind this call's own copies)
     }
     // the decode kernels flag footers / frame sizes that do not fit their page (Status::Corruption in FrameOfReferencePageDecoder::init)

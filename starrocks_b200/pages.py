@@ -75,7 +75,7 @@ class PageTable:
     """a table's columns as encoded pages, cut into page sets (row ranges) that are pushed one after the other: what a scan operator is fed
     instead of a chunk (pipelines accept either)"""
 
-    def __init__(self, columns: Dict[int, PageColumn], pages_per_set: int = 128):
+    def __init__(self, columns: Dict[int, PageColumn], pages_per_set: int = 512):
         self.columns = columns
         n_pages = len(next(iter(columns.values())).pages)
         assert all(len(c.pages) == n_pages for c in columns.values()), "the columns' pages must cover the same row ranges"
