@@ -841,11 +841,6 @@ template <class S, int R, int... I>
 SRB_D void eval_narrow_all(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const uint8_t* stage, int r0, uint32_t& esc, iseq<I...>) {
     (eval_narrow_node<S, I, R>(p, nv, stage, r0, esc), ...);
 }
-// [u32 length][bytes] of a BinaryColumn value (BinaryColumn::serialize, column/binary_column.h:228-237); a key beyond 16 bytes sets too_long
-SRB_D void key_put_binary(PackedKey& k, const uint8_t* first, uint32_t len) {
-    key_put(k, len, 4);
-    for (uint32_t j = 0; j < len && !k.too_long; j++) key_put(k, first[j], 1);
-}
 template <class S, int KI>
 SRB_D void key_put_narrow(PackedKey& k, const uint64_t* nv, const TileBin& tb) {
     if constexpr (KI < S::N_KEYS) {
