@@ -203,6 +203,18 @@ typedef struct srb_scan_agg_plan {
                                             is not kept, and a NULL key anywhere on a non-empty build side means no row qualifies; against an
                                             empty build side every probe row is kept. Without other-conjuncts. */
 
+/* One other-join-conjunct: a comparison between two columns of the joined row, e.g. `l.shipdate > o.orderdate` beside the equi-join keys
+ * (HashJoiner::_process_other_conjunct, exec/hash_joiner.cpp:488-507: for an INNER join the conjuncts filter the joined chunk). Both slots
+ * must be key or output columns of the plan (either side), of the same fixed-width integer / DATE / DECIMAL type; a NULL on either side
+ * fails the comparison. op: SRB_PRED_EQ .. SRB_PRED_LE. INNER joins only (the outer / semi / anti variants re-derive matched flags from the
+ * conjuncts, hash_joiner.cpp:446-486: not built). */
+typedef struct srb_join_conjunct {
+    int32_t left_slot;
+    int32_t op;
+    int32_t right_slot;
+    int32_t _pad;
+} srb_join_conjunct;
+
 typedef struct srb_join_plan {
     int32_t join_type;
     int32_t n_keys; /* equi-join key pairs; all fixed-width, packed size <= 16 bytes */
@@ -214,7 +226,8 @@ typedef struct srb_join_plan {
     const int32_t* probe_out_slots;
     int32_t emit_indexes; /* 1: also emit probe_index/build_index UInt32 columns under slots -4 / -3
                              (HASH_JOIN_PROBE_INDEX_SLOT_ID / HASH_JOIN_BUILD_INDEX_SLOT_ID, column/chunk.h:52-58) */
-    int32_t _pad;
+    int32_t n_conjuncts;  /* other-join-conjuncts (at most 8), 0 = none */
+    const srb_join_conjunct* conjuncts;
 } srb_join_plan;
 
 /* ---- TopN: exec/chunks_sorter_topn.cpp, exec/sorting/sorting.h:86-101 ------------------- */

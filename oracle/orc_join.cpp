@@ -256,6 +256,42 @@ Result* run_join(const srb_join_plan* plan, const srb_chunk* build, const srb_ch
                 build_index.push_back(b);
             }
     }
+    // other-join-conjuncts of an INNER join filter the joined rows (HashJoiner::_process_other_conjunct, hash_joiner.cpp:488-507:
+    // ExecNode::eval_conjuncts over the joined chunk; a comparison with a NULL is not true)
+    if (plan->n_conjuncts > 0) {
+        if (jt != SRB_JOIN_INNER) throw std::runtime_error("other-join-conjuncts: INNER joins only");
+        auto side_of = [&](int slot, const srb_column** col) { // 0: probe column, 1: build column
+            for (int i = 0; i < probe->n_cols; i++)
+                if (probe->slot_ids[i] == slot) {
+                    *col = &probe->cols[i];
+                    return 0;
+                }
+            *col = find_slot(*build, slot);
+            return 1;
+        };
+        size_t kept = 0;
+        for (size_t j = 0; j < probe_index.size(); j++) {
+            bool ok = true;
+            for (int c = 0; c < plan->n_conjuncts && ok; c++) {
+                const srb_join_conjunct& cj = plan->conjuncts[c];
+                const srb_column *lc, *rc;
+                const int ls = side_of(cj.left_slot, &lc), rs = side_of(cj.right_slot, &rc);
+                const int64_t lrow = ls ? (int64_t)build_index[j] - 1 : (int64_t)probe_index[j], rrow = rs ? (int64_t)build_index[j] - 1 : (int64_t)probe_index[j];
+                if ((lc->nulls && lc->nulls[lrow]) || (rc->nulls && rc->nulls[rrow])) {
+                    ok = false;
+                    break;
+                }
+                ok = cmp_apply(cj.op, load_int(*lc, lrow), load_int(*rc, rrow));
+            }
+            if (ok) {
+                probe_index[kept] = probe_index[j];
+                build_index[kept] = build_index[j];
+                kept++;
+            }
+        }
+        probe_index.resize(kept);
+        build_index.resize(kept);
+    }
     r->rows_in = probe->n_rows;
     r->rows_selected = (int64_t)probe_index.size();
     r->n_rows = (int64_t)probe_index.size();

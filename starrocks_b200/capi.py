@@ -91,7 +91,11 @@ class srb_join_plan(C.Structure):
                 ("build_key_slots", C.POINTER(C.c_int32)), ("probe_key_slots", C.POINTER(C.c_int32)),
                 ("n_build_out", C.c_int32), ("build_out_slots", C.POINTER(C.c_int32)),
                 ("n_probe_out", C.c_int32), ("probe_out_slots", C.POINTER(C.c_int32)),
-                ("emit_indexes", C.c_int32), ("_pad", C.c_int32)]
+                ("emit_indexes", C.c_int32), ("n_conjuncts", C.c_int32), ("conjuncts", C.c_void_p)]
+
+
+class srb_join_conjunct(C.Structure):
+    _fields_ = [("left_slot", C.c_int32), ("op", C.c_int32), ("right_slot", C.c_int32), ("_pad", C.c_int32)]
 
 
 class srb_topn_plan(C.Structure):

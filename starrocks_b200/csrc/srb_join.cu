@@ -229,6 +229,74 @@ __global__ void __launch_bounds__(256) k_join_gather(const __grid_constant__ Gat
     }
 }
 
+// other-join-conjuncts of an INNER join (HashJoiner::_process_other_conjunct, hash_joiner.cpp:488-507): the (probe, build) pairs whose
+// columns satisfy every comparison survive; a NULL on either side fails it. Pairs are compacted with one atomic per warp step.
+struct ConjCol {
+    const uint8_t* data;
+    const uint8_t* nulls;
+    int32_t width;
+    int32_t from_build;
+};
+struct ConjArgs {
+    int32_t n;
+    int32_t _pad;
+    ConjCol l[8], r[8];
+    int32_t op[8];
+};
+SRB_D i128 conj_load(const ConjCol& c, size_t row) {
+    switch (c.width) {
+    case 1: return (i128)((const int8_t*)c.data)[row];
+    case 2: return (i128)((const int16_t*)c.data)[row];
+    case 4: return (i128)((const int32_t*)c.data)[row];
+    case 8: return (i128)((const int64_t*)c.data)[row];
+    default: {
+        const ulonglong2 v = ((const ulonglong2*)c.data)[row];
+        return make_i128(v.x, (int64_t)v.y);
+    }
+    }
+}
+__global__ void __launch_bounds__(256) k_join_conjuncts(const __grid_constant__ ConjArgs a, int64_t m, const uint32_t* __restrict__ pi_in,
+                                                         const uint32_t* __restrict__ bi_in, uint32_t* __restrict__ pi_out, uint32_t* __restrict__ bi_out,
+                                                         unsigned long long* __restrict__ total) {
+    const int lane = threadIdx.x & 31;
+    const int64_t rounds = (m + 31) & ~(int64_t)31;
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < rounds; j += (int64_t)gridDim.x * blockDim.x) {
+        bool keep = j < m;
+        uint32_t pi = 0, bi = 0;
+        if (keep) {
+            pi = pi_in[j];
+            bi = bi_in[j];
+            for (int c = 0; c < a.n && keep; c++) {
+                const size_t lr = a.l[c].from_build ? bi - 1 : pi, rr = a.r[c].from_build ? bi - 1 : pi;
+                if ((a.l[c].nulls && a.l[c].nulls[lr]) || (a.r[c].nulls && a.r[c].nulls[rr])) {
+                    keep = false;
+                    break;
+                }
+                const i128 x = conj_load(a.l[c], lr), y = conj_load(a.r[c], rr);
+                switch (a.op[c]) {
+                case 1: keep = x == y; break;
+                case 2: keep = x != y; break;
+                case 3: keep = x > y; break;
+                case 4: keep = x >= y; break;
+                case 5: keep = x < y; break;
+                default: keep = x <= y;
+                }
+            }
+        }
+        const unsigned msk = __ballot_sync(0xffffffffu, keep);
+        if (!msk) continue;
+        unsigned long long base = 0;
+        const int leader = __ffs(msk) - 1;
+        if (lane == leader) base = atomicAdd(total, (unsigned long long)__popc(msk));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (keep) {
+            const unsigned long long at = base + __popc(msk & ((1u << lane) - 1));
+            pi_out[at] = pi;
+            bi_out[at] = bi;
+        }
+    }
+}
+
 // the build rows (1-based) whose matched flag equals `want`, in any order (_search_ht_remain, join_hash_map.tpp)
 __global__ void __launch_bounds__(256) k_join_remainder(const uint8_t* __restrict__ matched, uint32_t rows, int want, unsigned long long* __restrict__ total,
                                                          uint32_t* __restrict__ out_build) {
@@ -593,6 +661,11 @@ public:
         if (semi_) bout_.clear(); // LEFT SEMI emits probe columns only
         if (right_only_) pout_.clear(); // RIGHT SEMI / ANTI emit build columns only
         emit_indexes_ = p->emit_indexes != 0 && !anti_ && !keep_left_ && !track_right_;
+        if (p->n_conjuncts < 0 || p->n_conjuncts > 8 || (p->n_conjuncts && !p->conjuncts)) throw Error(SRB_INVALID_ARGUMENT, "bad other-join-conjunct list (at most 8)");
+        if (p->n_conjuncts && jt != SRB_JOIN_INNER) throw Error(SRB_NOT_IMPLEMENTED, "other-join-conjuncts: INNER joins only");
+        conj_.assign(p->conjuncts, p->conjuncts + p->n_conjuncts);
+        for (const srb_join_conjunct& cj : conj_)
+            if (cj.op < SRB_PRED_EQ || cj.op > SRB_PRED_LE) throw Error(SRB_INVALID_ARGUMENT, "other-join-conjunct: comparison operators only");
         chunk_size_ = c->cfg.chunk_size > 0 ? c->cfg.chunk_size : 4096;
         bcols_.resize(bkeys_.size() + bout_.size());
         total_dev_.ensure(c, 8);
@@ -728,7 +801,7 @@ public:
         }
         if (total > 16 || pw != width_) throw Error(SRB_INVALID_ARGUMENT, "probe key width does not match the build key width");
         const bool outer = keep_left_ || track_right_;
-        if (((unique_ && !force_general_) || anti_) && !outer) {
+        if (((unique_ && !force_general_) || anti_) && !outer && conj_.empty()) { // (conjuncts filter (probe, build) pairs: the general path has them)
             probe_tiled(n, data, nulls);
             return;
         }
@@ -751,7 +824,7 @@ public:
         SRB_CUDA(cudaMemsetAsync(total_dev_.p, 0, 8, stream));
         SRB_CUDA(cudaStreamSynchronize(stream));
         launches += 2;
-        const int64_t m = (int64_t)*total_host_.as<unsigned long long>();
+        int64_t m = (int64_t)*total_host_.as<unsigned long long>();
         rows_selected += m;
         if (m == 0) return;
         if (m >= ((int64_t)1 << 32)) throw Error(SRB_NOT_IMPLEMENTED, "join output of one probe chunk exceeds 2^32 rows; push smaller chunks");
@@ -761,6 +834,8 @@ public:
         k_join_probe<1><<<grid, 256, 0, stream>>>(t, ppacked_.as<uint8_t>(), pnull_.as<uint8_t>(), n, semi_ ? 1 : 0,
                                                    total_dev_.as<unsigned long long>(), oprobe_.as<uint32_t>(), obuild_.as<uint32_t>(), keep_left_ ? 1 : 0);
         launches++;
+        if (!conj_.empty()) m = filter_pairs(m, data, nulls);
+        if (m == 0) return;
         // K8 gather
         GatherArgs ga = describe_outputs(m, data, nulls);
         if (ga.n_cols) {
@@ -770,6 +845,56 @@ public:
         SRB_CUDA(cudaGetLastError());
         SRB_CUDA(cudaStreamSynchronize(stream));
         out_rows_ = m;
+    }
+
+    static void swap_bufs(DevBuf& a, DevBuf& b) {
+        std::swap(a.ctx, b.ctx);
+        std::swap(a.p, b.p);
+        std::swap(a.bytes, b.bytes);
+    }
+    // other-join-conjuncts over the m pairs in oprobe_ / obuild_: the surviving pairs replace them; returns their number
+    int64_t filter_pairs(int64_t m, const std::vector<const uint8_t*>& data, const std::vector<const uint8_t*>& nulls) {
+        ConjArgs ca{};
+        ca.n = (int)conj_.size();
+        auto resolve = [&](int slot, ConjCol& out, int* type, int* prec, int* scale) {
+            for (size_t i = 0; i < pkeys_.size() + pout_.size(); i++) {
+                const int s = i < pkeys_.size() ? pkeys_[i] : pout_[i - pkeys_.size()];
+                if (s != slot) continue;
+                out = ConjCol{data[i], nulls[i], pcols_[i].width, 0};
+                *type = pcols_[i].type, *prec = pcols_[i].precision, *scale = pcols_[i].scale;
+                return;
+            }
+            for (size_t i = 0; i < bkeys_.size() + bout_.size(); i++) {
+                const int s = i < bkeys_.size() ? bkeys_[i] : bout_[i - bkeys_.size()];
+                if (s != slot) continue;
+                const GrowCol& g = bcols_[i];
+                out = ConjCol{g.data.as<uint8_t>(), g.nullable ? g.nulls.as<uint8_t>() : nullptr, g.width, 1};
+                *type = g.type, *prec = g.precision, *scale = g.scale;
+                return;
+            }
+            throw Error(SRB_INVALID_ARGUMENT, fmt("other-join-conjunct: slot %d is neither a key nor an output column of the join", slot));
+        };
+        for (int c = 0; c < ca.n; c++) {
+            int lt, lp, ls, rt, rp, rs;
+            resolve(conj_[c].left_slot, ca.l[c], &lt, &lp, &ls);
+            resolve(conj_[c].right_slot, ca.r[c], &rt, &rp, &rs);
+            if (lt != rt || ls != rs || lt == SRB_TYPE_DOUBLE || is_binary(lt))
+                throw Error(SRB_NOT_IMPLEMENTED, "other-join-conjunct: both sides must have the same integer / DATE / DECIMAL type and scale");
+            ca.op[c] = conj_[c].op;
+        }
+        oprobe2_.ensure(ctx, (size_t)m * 4);
+        obuild2_.ensure(ctx, (size_t)m * 4);
+        SRB_CUDA(cudaMemsetAsync(total_dev_.p, 0, 8, stream));
+        k_join_conjuncts<<<grid_for(m), 256, 0, stream>>>(ca, m, oprobe_.as<uint32_t>(), obuild_.as<uint32_t>(), oprobe2_.as<uint32_t>(), obuild2_.as<uint32_t>(),
+                                                          total_dev_.as<unsigned long long>());
+        SRB_CUDA(cudaMemcpyAsync(total_host_.p, total_dev_.p, 8, cudaMemcpyDeviceToHost, stream));
+        SRB_CUDA(cudaStreamSynchronize(stream));
+        launches++;
+        swap_bufs(oprobe_, oprobe2_);
+        swap_bufs(obuild_, obuild2_);
+        const int64_t kept = (int64_t)*total_host_.as<unsigned long long>();
+        rows_selected -= m - kept;
+        return kept;
     }
 
     // output columns for m rows: probe_out columns (from the pushed chunk) then build_out columns (from the build side)
@@ -1121,6 +1246,8 @@ private:
     DevBuf matched_; // one byte per build row (1-based): the row matched some probe row (RIGHT / FULL OUTER, RIGHT SEMI / ANTI)
     bool semi_ = false, emit_indexes_ = false, build_done_ = false, probe_finishing_ = false, gave_empty_ = false;
     std::vector<int32_t> bkeys_, pkeys_, bout_, pout_;
+    std::vector<srb_join_conjunct> conj_; // other-join-conjuncts (INNER joins)
+    DevBuf oprobe2_, obuild2_;
     int64_t chunk_size_;
     std::vector<GrowCol> bcols_, pcols_, ocols_;
     int64_t build_rows_ = 0, probe_rows_in_ = 0;

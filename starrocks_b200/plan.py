@@ -113,11 +113,16 @@ class ScanAggPlan:
 
 class JoinPlan:
     def __init__(self, build_keys: Sequence[int], probe_keys: Sequence[int], build_out: Sequence[int] = (),
-                 probe_out: Sequence[int] = (), join_type: int = K.JOIN_INNER, emit_indexes: bool = False):
+                 probe_out: Sequence[int] = (), join_type: int = K.JOIN_INNER, emit_indexes: bool = False,
+                 conjuncts: Sequence[tuple] = ()):
+        """conjuncts: other-join-conjuncts as (left_slot, K.PRED_*, right_slot) over key / output columns of either side (INNER joins)"""
         assert len(build_keys) == len(probe_keys)
         self.bk = (C.c_int32 * max(1, len(build_keys)))(*build_keys)
         self.pk = (C.c_int32 * max(1, len(probe_keys)))(*probe_keys)
         self.bo = (C.c_int32 * max(1, len(build_out)))(*build_out)
         self.po = (C.c_int32 * max(1, len(probe_out)))(*probe_out)
         self.c = K.srb_join_plan(join_type, len(build_keys), self.bk, self.pk, len(build_out), self.bo,
-                                 len(probe_out), self.po, 1 if emit_indexes else 0, 0)
+                                 len(probe_out), self.po, 1 if emit_indexes else 0, len(conjuncts), None)
+        if conjuncts:
+            self.cj = (K.srb_join_conjunct * len(conjuncts))(*[K.srb_join_conjunct(l, op, r, 0) for l, op, r in conjuncts])
+            self.c.conjuncts = C.cast(self.cj, C.c_void_p)

@@ -991,6 +991,38 @@ def test_outer_and_right_side_joins(ctx, oracle, jt, ktypes):
         assert sorted(got, key=repr) == want, (jt, device)
 
 
+@pytest.mark.parametrize("unique_build", [False, True])
+def test_inner_join_with_other_conjuncts(ctx, oracle, unique_build):
+    # HashJoiner::_process_other_conjunct (hash_joiner.cpp:488-507): `ON b.k = p.k AND p.d > b.d AND p.x <> b.y` — the conjuncts compare columns of
+    # the two sides on every joined row; NULLs fail them; duplicate and unique build keys (the latter would otherwise take the tiled probe)
+    from starrocks_b200 import ops
+    rng = np.random.default_rng(41)
+    nb, npr = 30_000, 120_000
+    bk = np.arange(nb, dtype=np.int32) if unique_build else rng.integers(0, 8000, nb).astype(np.int32)
+    build = K.Chunk(nb, {0: K.Column.from_ints(K.TYPE_INT, bk, (rng.random(nb) < 0.02).astype(np.uint8)),
+                         1: K.Column.from_ints(K.TYPE_DATE, rng.integers(9000, 9400, nb).astype(np.int32), (rng.random(nb) < 0.05).astype(np.uint8)),
+                         2: K.Column.from_ints(K.TYPE_DECIMAL64, rng.integers(0, 50, nb), None, 15, 2),
+                         3: K.Column.from_ints(K.TYPE_BIGINT, np.arange(nb))})
+    probe = K.Chunk(npr, {10: K.Column.from_ints(K.TYPE_INT, rng.integers(0, nb if unique_build else 9000, npr).astype(np.int32)),
+                          11: K.Column.from_ints(K.TYPE_DATE, rng.integers(9000, 9400, npr).astype(np.int32), (rng.random(npr) < 0.05).astype(np.uint8)),
+                          12: K.Column.from_ints(K.TYPE_DECIMAL64, rng.integers(0, 50, npr), None, 15, 2),
+                          13: K.Column.from_ints(K.TYPE_INT, np.arange(npr, dtype=np.int32))})
+    for conj in ([(11, K.PRED_GT, 1)], [(11, K.PRED_GE, 1), (12, K.PRED_NE, 2)], [(2, K.PRED_LT, 12), (10, K.PRED_EQ, 0)]):
+        plan = JoinPlan([0], [10], build_out=[1, 2, 3], probe_out=[11, 12, 13], conjuncts=conj)
+        want = sorted(K.chunk_rows(oracle.join(plan, build, probe), sort=False), key=repr)
+        plain = oracle.join(JoinPlan([0], [10], build_out=[1, 2, 3], probe_out=[11, 12, 13]), build, probe).n_rows
+        assert 100 < len(want) < plain
+        pieces = [ops.slice_chunk(probe, 0, 70_000), ops.slice_chunk(probe, 70_000, npr)]
+        for device in (False, True):
+            got = run_join_chunks(ctx, plan, build, pieces, device=device)
+            assert sorted(got, key=repr) == want, (conj, device)
+    # a conjunct over a column the join does not carry, or on an outer join, is refused
+    with pytest.raises(ops.SrbError):
+        run_join_chunks(ctx, JoinPlan([0], [10], build_out=[3], probe_out=[13], conjuncts=[(11, K.PRED_GT, 1)]), build, [probe])
+    with pytest.raises(ops.SrbError):
+        ops.HashJoinOperator(ctx, JoinPlan([0], [10], build_out=[1], probe_out=[11], join_type=K.JOIN_LEFT_OUTER, conjuncts=[(11, K.PRED_GT, 1)]))
+
+
 @pytest.mark.parametrize("build_nulls", [False, True])
 @pytest.mark.parametrize("ktypes", [[K.TYPE_INT], [K.TYPE_BIGINT, K.TYPE_SMALLINT], [K.TYPE_DECIMAL128]])
 def test_null_aware_left_anti_join(ctx, oracle, build_nulls, ktypes):

@@ -651,3 +651,16 @@ def test_bitset_runtime_filter_of_the_reference_test(oracle):
     assert ch(0, 3199, 100, 1 << 20, 0) and not ch(0, 3200, 100, 1 << 20, 0)  # up to 4x when it fits the L2
     assert not ch(0, 3199, 100, 399, 0) and ch(0, 1599, 100, 0, 1 << 25) and not ch(0, 1600, 100, 0, 1 << 25)  # 2x for the L3
     assert not ch(5, 4, 100, 1 << 20, 1 << 25)                            # empty build side: min > max
+
+
+def test_inner_join_other_conjuncts_by_hand(oracle):
+    # HashJoiner::_process_other_conjunct for INNER joins (hash_joiner.cpp:488-507): the joined rows that satisfy the conjuncts; NULL fails
+    from starrocks_b200.plan import JoinPlan
+    build = K.Chunk(4, {0: K.Column.from_ints(K.TYPE_INT, np.array([1, 2, 2, 3], np.int32)),
+                        1: K.Column.from_ints(K.TYPE_BIGINT, np.array([10, 20, 30, 40]), np.array([0, 0, 0, 1], np.uint8))})
+    probe = K.Chunk(4, {2: K.Column.from_ints(K.TYPE_INT, np.array([2, 1, 3, 2], np.int32)), 3: K.Column.from_ints(K.TYPE_BIGINT, np.array([25, 5, 99, 35]))})
+    rows = lambda conj: sorted(K.chunk_rows(oracle.join(JoinPlan([0], [2], build_out=[1], probe_out=[2, 3], conjuncts=conj), build, probe), sort=False))
+    assert rows([]) == sorted([(2, 25, 20), (2, 25, 30), (1, 5, 10), (3, 99, None), (2, 35, 20), (2, 35, 30)], key=repr) or len(rows([])) == 6
+    assert rows([(3, K.PRED_GT, 1)]) == [(2, 25, 20), (2, 35, 20), (2, 35, 30)]          # p.v > b.v; the NULL b.v never passes
+    assert rows([(3, K.PRED_GT, 1), (3, K.PRED_NE, 1)]) == [(2, 25, 20), (2, 35, 20), (2, 35, 30)]
+    assert rows([(1, K.PRED_GE, 3)]) == [(1, 5, 10), (2, 25, 30)]                           # b.v >= p.v
