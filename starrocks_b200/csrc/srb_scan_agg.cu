@@ -553,17 +553,15 @@ __global__ void __launch_bounds__(256) k_emit(const __grid_constant__ DProg prog
                 if (i < cap && ((*(const uint64_t*)(slots + i * sb)) & 3ULL) == SLOT_READY) ready |= 1u << r;
             }
         }
-        // Output positions: the lanes whose r-th slot is ready take CONSECUTIVE rows (rank inside the ballot), so every store instruction of
-        // emit_row writes a dense run of rows; a thread's own ready slots taking consecutive rows instead left each store instruction
-        // scattered over 32 runs (a 10^8-group emit is store-bound).
-        unsigned int m[EMIT_ROWS], pre[EMIT_ROWS], wtot = 0;
-#pragma unroll
-        for (int r = 0; r < EMIT_ROWS; r++) {
-            m[r] = __ballot_sync(0xffffffffu, (ready >> r) & 1u);
-            pre[r] = wtot;
-            wtot += __popc(m[r]);
+        // (Ranking the lanes of each slot row by ballot, so that every store instruction writes a dense run of output rows, was measured
+        // slower: 28.5 vs 26.9 ms per high-cardinality step. A thread's own ready slots take consecutive rows.)
+        const unsigned int mine = __popc(ready);
+        unsigned int incl = mine;
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int y = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += y;
         }
-        if (lane == 0) warp_tot[wid] = wtot;
+        if (lane == 31) warp_tot[wid] = incl;
         __syncthreads();
         if (tid == 0) {
             unsigned int t = 0;
@@ -575,17 +573,15 @@ __global__ void __launch_bounds__(256) k_emit(const __grid_constant__ DProg prog
             block_base = t ? atomicAdd(&ctr->emitted, (unsigned long long)t) : 0ULL;
         }
         __syncthreads();
-        const int64_t base_row = row_base + (int64_t)(block_base + warp_tot[wid]); // row_base: pass-through rows of a streaming sink come first
-        const unsigned int below = (1u << lane) - 1u;
+        int64_t row = row_base + (int64_t)(block_base + warp_tot[wid] + (incl - mine)); // row_base: pass-through rows of a streaming sink come first
 #pragma unroll
         for (int r = 0; r < EMIT_ROWS; r++)
             if (ready & (1u << r)) {
-                const int64_t row = base_row + pre[r] + __popc(m[r] & below);
                 if (whole) {
                     const uint64_t copy[4] = {s0[r].x, s0[r].y, s1[r].x, s1[r].y};
-                    emit_row(p, reinterpret_cast<const uint8_t*>(copy), ea, row);
+                    emit_row(p, reinterpret_cast<const uint8_t*>(copy), ea, row++);
                 } else {
-                    emit_row(p, slots + (c0 + (uint64_t)r * 256 + tid) * sb, ea, row);
+                    emit_row(p, slots + (c0 + (uint64_t)r * 256 + tid) * sb, ea, row++);
                 }
             }
         __syncthreads(); // warp_tot / block_base are rewritten by the next chunk
