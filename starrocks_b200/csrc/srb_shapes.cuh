@@ -764,8 +764,8 @@ constexpr bool shape_has_narrow() {
         if (key && (nd.op != DOP_LOAD || node_is_operand<S>(i))) return false; // keys: plain columns, bits taken as they are
         switch (nd.op) {
         case DOP_LOAD:
-            if (nd.nullable != 0 || (nd.width != 8 && !(key && (nd.width == 4 || nd.width == 0)))) return false;
-            break;
+            if ((key && nd.nullable != 0) || (nd.width != 8 && !(key && (nd.width == 4 || nd.width == 0)))) return false;
+            break; // (a nullable VALUE column is fine: the narrow body carries one NULL bit per such column and row)
         case DOP_LIT: break;
         case DOP_CAST:
             if (nd.width < 8) return false;
@@ -790,8 +790,25 @@ constexpr bool shape_has_narrow() {
         if (S::key(k).nullable != 0) return false;
     return true;
 }
+// NULL bits of the narrow body: nullable LOAD node I owns bit null_bit<S>(I) of a row's mask; a value is NULL iff the mask meets the bits of
+// the nullable loads under it (null_dep). A NULL load contributes the value 0, so nothing derived from it can break the narrow assumption.
+template <class S>
+constexpr int null_bit(int n) {
+    int b = 0;
+    for (int i = 0; i < n; i++)
+        if (S::node(i).op == DOP_LOAD && S::node(i).nullable != 0) b++;
+    return b;
+}
+template <class S>
+constexpr uint32_t null_dep(int n) {
+    if (n < 0) return 0u;
+    const SNode nd = S::node(n);
+    if (nd.op == DOP_LOAD) return nd.nullable != 0 ? (1u << null_bit<S>(n)) : 0u;
+    if (nd.op == DOP_LIT) return 0u;
+    return null_dep<S>(nd.lhs) | null_dep<S>(nd.rhs);
+}
 template <class S, int I, int R>
-SRB_D void eval_narrow_node(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const uint8_t* stage, int r0, uint32_t& esc) {
+SRB_D void eval_narrow_node(const DProg& p, const StaticArgs& sa, uint64_t (&nv)[R][S::N_NODES], uint32_t (&ln)[R], const uint8_t* stage, int r0, uint32_t& esc) {
     constexpr SNode nd = S::node(I);
     if constexpr (nd.op == DOP_LOAD && nd.width == 0) { // a binary key: (length << 32) | offset
 #pragma unroll
@@ -803,6 +820,15 @@ SRB_D void eval_narrow_node(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const
     } else if constexpr (nd.op == DOP_LOAD && nd.width == 4) {
 #pragma unroll
         for (int j = 0; j < R; j++) nv[j][I] = ((const uint32_t*)(stage + load_off<S>(I)))[r0 + j * S::THREADS]; // key bits
+    } else if constexpr (nd.op == DOP_LOAD && nd.nullable != 0) {
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const bool isnull = stage[sa.node_null_off[I] + r0 + j * S::THREADS] != 0;
+            const uint64_t x = isnull ? 0ULL : ((const uint64_t*)(stage + load_off<S>(I)))[r0 + j * S::THREADS];
+            ln[j] |= isnull ? (1u << null_bit<S>(I)) : 0u;
+            esc |= (uint32_t)(x >> 32);
+            nv[j][I] = (uint32_t)x;
+        }
     } else if constexpr (nd.op == DOP_LOAD) {
 #pragma unroll
         for (int j = 0; j < R; j++) {
@@ -838,8 +864,11 @@ SRB_D void eval_narrow_node(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const
     }
 }
 template <class S, int R, int... I>
-SRB_D void eval_narrow_all(const DProg& p, uint64_t (&nv)[R][S::N_NODES], const uint8_t* stage, int r0, uint32_t& esc, iseq<I...>) {
-    (eval_narrow_node<S, I, R>(p, nv, stage, r0, esc), ...);
+SRB_D void eval_narrow_all(const DProg& p, const StaticArgs& sa, uint64_t (&nv)[R][S::N_NODES], uint32_t (&ln)[R], const uint8_t* stage, int r0, uint32_t& esc,
+                           iseq<I...>) {
+#pragma unroll
+    for (int j = 0; j < R; j++) ln[j] = 0;
+    (eval_narrow_node<S, I, R>(p, sa, nv, ln, stage, r0, esc), ...);
 }
 template <class S, int KI>
 SRB_D void key_put_narrow(PackedKey& k, const uint64_t* nv, const TileBin& tb) {
@@ -865,15 +894,29 @@ SRB_D PackedKey pack_key_narrow(const uint64_t* nv, const TileBin& tb) {
 // addend are both below 2^63; `flag` collects the top bits of both, and when its sign bit is set after the tile the
 // exact carries are recovered from the words themselves (acc_narrow_fixup).
 template <class S, int A>
-SRB_D void acc_narrow_one(uint8_t* a, uint8_t* trash, const uint64_t* nv, bool on, uint32_t& flag) {
+SRB_D void acc_narrow_one(uint8_t* a, uint8_t* c, uint8_t* trash, const uint64_t* nv, uint32_t ln, bool on, uint32_t& flag) {
     constexpr SAgg g = S::agg(A);
     if constexpr (plane_kind<S>(A) == 1 && agg_rep<S>(A) == A) {
         constexpr int RI = rep_index<S>(A);
         const uint64_t x = nv[g.arg];
-        uint64_t* slot = (uint64_t*)(on ? a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8 : trash);
+        bool take = on;
+        if constexpr (null_dep<S>(g.arg) != 0) take = on && (ln & null_dep<S>(g.arg)) == 0;
+        uint64_t* slot = (uint64_t*)(take ? a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8 : trash);
         const uint64_t old = *slot;
         *slot = old + x;
         flag |= (uint32_t)(old >> 32) | (uint32_t)(x >> 32);
+        if constexpr (plane_counts<S>(A)) {
+            uint32_t* tc = (uint32_t*)(take ? c + (size_t)cnt_index<S>(A) * AccGeom<S>::G * S::THREADS * 4 : trash);
+            *tc += 1u;
+        }
+    } else if constexpr (plane_kind<S>(A) == 2 && null_dep<S>(S::agg(A).arg) != 0) {
+        constexpr int RI = rep_index<S>(A);
+        const bool take = on && (ln & null_dep<S>(g.arg)) == 0;
+        uint64_t* slot = (uint64_t*)(a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8);
+        const uint64_t e = enc_i64((int64_t)nv[g.arg], g.fn == FN_MIN), cur = *slot;
+        *slot = (take && e > cur) ? e : cur;
+        uint32_t* tc = (uint32_t*)(take ? c + (size_t)cnt_index<S>(A) * AccGeom<S>::G * S::THREADS * 4 : trash);
+        *tc += 1u;
     } else if constexpr (plane_kind<S>(A) == 2) {
         // a max plane: the word itself, whatever `on` says (an encoded value has its top bit set: it must stay away from the trash word,
         // whose top bit the sum planes read as "look for carries")
@@ -893,11 +936,12 @@ struct NarrowFix { // by value into the out-of-line fix-up: the tile's arrays mu
     bool on[R];
 };
 template <class S, int R, int A>
-SRB_D void narrow_fix_put(NarrowFix<S, R>& f, const uint64_t (&nv)[R][S::N_NODES]) {
+SRB_D void narrow_fix_put(NarrowFix<S, R>& f, const uint64_t (&nv)[R][S::N_NODES], const uint32_t (&ln)[R]) {
     constexpr SAgg g = S::agg(A);
     if constexpr (plane_kind<S>(A) == 1 && agg_rep<S>(A) == A) {
 #pragma unroll
-        for (int j = 0; j < R; j++) f.x[j][rep_index<S>(A)] = nv[j][g.arg];
+        for (int j = 0; j < R; j++) // (a row whose argument was NULL added nothing to this plane: it carries nothing)
+            f.x[j][rep_index<S>(A)] = (ln[j] & null_dep<S>(g.arg)) ? 0ULL : nv[j][g.arg];
     }
 }
 template <class S>
@@ -937,19 +981,20 @@ static __device__ __noinline__ void acc_narrow_fixup(RareAcc<S>* ra, uint8_t* ac
     if (*(uint64_t*)trash >> 63) *(uint64_t*)trash = 0; // the trash word only ever matters through its top bit
 }
 template <class S, int R, int... A>
-SRB_D void acc_narrow_rows(RareAcc<S>& ra, uint8_t* acc_tid, uint8_t* rows_tid, uint8_t* trash, const uint64_t (&nv)[R][S::N_NODES], const bool (&on)[R],
-                           const int (&gid)[R], iseq<A...>) {
+SRB_D void acc_narrow_rows(RareAcc<S>& ra, uint8_t* acc_tid, uint8_t* rows_tid, uint8_t* trash, const uint64_t (&nv)[R][S::N_NODES], const uint32_t (&ln)[R],
+                           const bool (&on)[R], const int (&gid)[R], iseq<A...>) {
     uint32_t flag = 0;
 #pragma unroll
     for (int j = 0; j < R; j++) {
         uint8_t* a = acc_tid + (size_t)gid[j] * (S::THREADS * 8);
-        (acc_narrow_one<S, A>(a, trash, nv[j], on[j], flag), ...);
+        uint8_t* c = rows_tid + AccGeom<S>::ROWS_BYTES + AccGeom<S>::TRASH_BYTES + (size_t)gid[j] * (S::THREADS * 4); // the counting planes of this group
+        (acc_narrow_one<S, A>(a, c, trash, nv[j], ln[j], on[j], flag), ...);
         uint32_t* rc = (uint32_t*)(on[j] ? rows_tid + (size_t)gid[j] * (S::THREADS * 4) : trash);
         *rc += 1u;
     }
     if (__any_sync(0xffffffffu, (int32_t)flag < 0)) {
         NarrowFix<S, R> f;
-        (narrow_fix_put<S, R, A>(f, nv), ...);
+        (narrow_fix_put<S, R, A>(f, nv, ln), ...);
 #pragma unroll
         for (int j = 0; j < R; j++) {
             f.gid[j] = gid[j];
@@ -1477,7 +1522,8 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                 if (sa.narrow_ok && __any_sync(0xffffffffu, any_pass)) {
                     uint64_t nv[R][S::N_NODES];
                     uint32_t esc = 0;
-                    eval_narrow_all<S, R>(p, nv, stage, tid, esc, NodeSeq{});
+                    uint32_t ln[R];
+                    eval_narrow_all<S, R>(p, sa, nv, ln, stage, tid, esc, NodeSeq{});
                     int gid[R];
                     bool bad = esc != 0;
 #pragma unroll
@@ -1491,7 +1537,7 @@ __global__ void __launch_bounds__(S::THREADS + 32, 1)
                         if (gid[j] >= my_cnt) gid[j] = 0;
                     }
                     if (!__any_sync(0xffffffffu, bad)) {
-                        acc_narrow_rows<S, R>(ra, acc_tid, rows_tid, trash, nv, pass, gid, AggSeq{});
+                        acc_narrow_rows<S, R>(ra, acc_tid, rows_tid, trash, nv, ln, pass, gid, AggSeq{});
                         done = true;
                     }
                 }
