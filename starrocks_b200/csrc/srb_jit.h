@@ -238,6 +238,7 @@ inline std::string jit_source(const JitShape& js) {
         s += "        return SKey{0, 0};\n";
     }
     s += "    }\n};\nextern \"C\" __device__ const ShapeMeta srb_jit_meta = shape_meta<ShapeJit>();\n} // namespace srb\n";
+    if (getenv("SRB_JIT_BREAK")) s += "#error SRB_JIT_BREAK is set: this translation unit is made to fail (test hook for the fallback to the interpreter)\n";
     return s;
 }
 constexpr const char* JIT_KERNEL_EXPR = "srb::k_scan_agg_static<srb::ShapeJit>";

@@ -883,10 +883,10 @@ def test_error_convention(ctx):
     assert op.is_finished() and not op.has_output() and not op.need_input()
     op.close()
     e = ExprBuilder()
-    long_keys = [e.slot(i, K.TYPE_BIGINT) for i in range(3)]  # 24-byte packed key
+    long_keys = [e.slot(i, K.TYPE_DECIMAL128, 38, 0) for i in range(5)]  # an 80-byte packed key: beyond the 64 bytes of a wide key
     op = ops.ScanAggOperator(ctx, ScanAggPlan(exprs=e, keys=long_keys, aggs=[(K.AGG_COUNT, None)]))
     with pytest.raises(ops.SrbError) as ei:
-        op.push_chunk(K.Chunk(1, {i: K.Column.from_ints(K.TYPE_BIGINT, [1]) for i in range(3)}))
+        op.push_chunk(K.Chunk(1, {i: K.Column.from_ints(K.TYPE_DECIMAL128, [1], None, 38, 0) for i in range(5)}))
     assert ei.value.code == K.NOT_IMPLEMENTED
     op.close()
 

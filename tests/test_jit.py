@@ -338,3 +338,25 @@ def test_string_key_beyond_16_bytes_is_refused_on_the_compiled_kernel_too(ctx, j
     with pytest.raises(ops.SrbError) as ex:
         run_device(ctx, string_key_plan(4), chunk)
     assert ex.value.code == K.NOT_IMPLEMENTED
+
+
+# ---- a compilation that fails leaves the operator on the interpreter ---------------------------------------------------------------------
+def test_a_failed_compilation_is_reported_by_check_plan(no_disk_cache, monkeypatch):
+    from starrocks_b200 import ops
+    monkeypatch.setenv("SRB_JIT_BREAK", "1")
+    first = T.host_chunk("lineitem", 0, 16, T.LINEITEM_Q1)
+    with pytest.raises(ops.SrbError) as ex:
+        ops.jit_check_plan(lineitem_plan(hint=5), first)
+    assert ex.value.code == K.INTERNAL_ERROR and "SRB_JIT_BREAK" in str(ex.value)
+    assert ops.jit_stats()["failed"] >= 1
+
+
+@pytest.mark.gpu
+def test_a_failed_compilation_falls_back_to_the_interpreter(ctx, oracle, jit_sync, monkeypatch):
+    monkeypatch.setenv("SRB_JIT_BREAK", "1")
+    plan_fn = lambda: lineitem_plan(hint=6, charge=True)  # a shape of its own: nothing cached
+    chunk = T.host_chunk("lineitem", 0, 300_000, T.LINEITEM_Q1)
+    want = K.chunk_rows(oracle.scan_agg(plan_fn(), chunk))
+    got, prof = run_device(ctx, plan_fn(), chunk)
+    assert prof["shape"] != SHAPE_JIT and prof["static_launches"] == 0
+    assert K.chunk_rows(got) == want
