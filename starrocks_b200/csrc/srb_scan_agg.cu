@@ -147,6 +147,27 @@ SRB_D void flush_local(const DAgg& g, const LocalAcc& s, uint8_t* slot) {
 // flushes each touched state with one global atomic when it retires. Integer addition commutes: the result is bit-identical.
 constexpr int GEN_SH_ENTRIES = 2048;
 
+// x added to a 64-bit shared-memory word with two NATIVE 32-bit atomics; returns the carry out of the word. A 64-bit atomicAdd on shared
+// memory is a compare-and-swap loop (SASS ATOMS.CAST.SPIN: with 32 lanes on a few dozen addresses every round lets one lane per address
+// through — profiles/r2_interpreter_nullable_full.txt), a 32-bit one is a single ATOMS.ADD that the unit serialises itself. Every carry is
+// handed on exactly once, so the multi-word sum is exact whatever the interleaving.
+SRB_D unsigned int smem_add64(unsigned long long* w, unsigned long long x) {
+    unsigned int* p = (unsigned int*)w;
+    const unsigned int xl = (unsigned int)x, xh = (unsigned int)(x >> 32);
+    unsigned int c = 0;
+    if (xl) {
+        const unsigned int o = atomicAdd(p, xl);
+        c = (o + xl) < o ? 1u : 0u;
+    }
+    const unsigned int add = xh + c;
+    unsigned int cout = (c && add == 0) ? 1u : 0u; // 0xFFFFFFFF + the carry: nothing to add here, one to hand on
+    if (add) {
+        const unsigned int o = atomicAdd(p + 1, add);
+        cout |= (o + add) < o ? 1u : 0u;
+    }
+    return cout;
+}
+
 __global__ void __launch_bounds__(256) k_scan_agg_generic(const __grid_constant__ DProg prog, const TableView tv, const int64_t base,
                                                            const int64_t n, const int64_t bit_base, const uint32_t* __restrict__ defer_in,
                                                            uint32_t* __restrict__ defer_out, Counters* __restrict__ ctr, const int sh_cap) {
@@ -207,15 +228,15 @@ __global__ void __launch_bounds__(256) k_scan_agg_generic(const __grid_constant_
                 unsigned long long* e = sh_acc + (idx * p.n_aggs + a) * 3;
                 if (g.fn == FN_MIN || g.fn == FN_MAX) { // the mirror keeps the table's own order-preserving encoding (identity: zero)
                     const bool mn = g.fn == FN_MIN;
-                    atomicMax(e, (unsigned long long)(g.is_double ? enc_f64(d.lo, mn) : enc_i64((int64_t)d.lo, mn)));
+                    const unsigned long long enc = (unsigned long long)(g.is_double ? enc_f64(d.lo, mn) : enc_i64((int64_t)d.lo, mn));
+                    if (enc > *(volatile unsigned long long*)e) atomicMax(e, enc); // (the word only grows: a value that does not beat it needs no atomic)
                 } else if (g.fn != FN_COUNT && (g.is_double || g.avg_as_double)) {
                     atomicAdd((double*)e, __longlong_as_double((long long)d.lo));
-                } else if (d.lo | d.hi) { // 128-bit add as two 64-bit atomics: the carry out of the low word travels with the high word's addend
-                    const unsigned long long old = atomicAdd(e, (unsigned long long)d.lo);
-                    const unsigned long long up = d.hi + ((old + d.lo) < old ? 1ULL : 0ULL);
-                    if (up) atomicAdd(e + 1, up);
+                } else if (d.lo | d.hi) { // 128-bit add word by word: the carry out of the low word travels with the high word's addend
+                    const unsigned long long up = d.hi + smem_add64(e, (unsigned long long)d.lo);
+                    if (up) smem_add64(e + 1, up);
                 }
-                atomicAdd(e + 2, (unsigned long long)d.n);
+                smem_add64(e + 2, (unsigned long long)d.n);
             }
             continue;
         }
