@@ -383,7 +383,12 @@ srb_status srb_join_probe_pull_device(srb_op* op, srb_chunk* out);
 #define SRB_STREAMING_AUTO 0
 #define SRB_STREAMING_FORCE_STREAMING 1
 #define SRB_STREAMING_FORCE_PREAGGREGATION 2
+#define SRB_STREAMING_LIMITED_MEM 3 /* _push_chunk_by_limited_memory (aggregate_streaming_sink_operator.cpp:311-319): AUTO while the group table
+                                       is smaller than the limit below, FORCE_STREAMING once it has reached it (LimitedMemAggState::has_limited,
+                                       exec/aggregator.h:209-212, 664-666); a limit of 0 never limits */
 srb_status srb_op_set_streaming_mode(srb_op* op, int32_t mode);
+/* the limit of SRB_STREAMING_LIMITED_MEM in bytes of group table (slots x slot size: what Aggregator::memory_usage counts for the hash map) */
+srb_status srb_op_set_streaming_memory_limit(srb_op* op, int64_t bytes);
 /* rows passed through so far, groups held by the table, current AggrAutoState (0 INIT_PREAGG, 1 ADJUST, 2 PASS_THROUGH,
  * 3 FORCE_PREAGG, 4 PREAGG, 5 SELECTIVE_PREAGG); any pointer may be NULL */
 srb_status srb_op_streaming_stats(srb_op* op, int64_t* rows_passed_through, int64_t* groups_in_table, int32_t* auto_state);

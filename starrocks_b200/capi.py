@@ -30,7 +30,7 @@ AGG_UPDATE_FINALIZE, AGG_UPDATE_SERIALIZE, AGG_MERGE_FINALIZE, AGG_MERGE_SERIALI
 JOIN_INNER, JOIN_LEFT_SEMI, JOIN_LEFT_ANTI = 0, 2, 8
 RF_KIND_BLOOM, RF_KIND_BITSET = 1, 3  # RuntimeFilterSerializeType (exprs/runtime_filter.h:46-51)
 JOIN_LEFT_OUTER, JOIN_RIGHT_OUTER, JOIN_FULL_OUTER, JOIN_RIGHT_SEMI, JOIN_RIGHT_ANTI, JOIN_NULL_AWARE_LEFT_ANTI = 1, 3, 4, 7, 9, 10
-STREAMING_AUTO, STREAMING_FORCE_STREAMING, STREAMING_FORCE_PREAGGREGATION = 0, 1, 2  # TStreamingPreaggregationMode
+STREAMING_AUTO, STREAMING_FORCE_STREAMING, STREAMING_FORCE_PREAGGREGATION, STREAMING_LIMITED_MEM = 0, 1, 2, 3  # TStreamingPreaggregationMode
 
 _WIDTH = {
     TYPE_TINYINT: 1, TYPE_BOOLEAN: 1, TYPE_SMALLINT: 2, TYPE_INT: 4, TYPE_DATE: 4, TYPE_DECIMAL32: 4,

@@ -307,6 +307,13 @@ srb_status srb_op_set_streaming_mode(srb_op* op, int32_t mode) {
     return SRB_OK;
     SRB_API_END
 }
+srb_status srb_op_set_streaming_memory_limit(srb_op* op, int64_t bytes) {
+    SRB_API_BEGIN
+    OP_GUARD(op)
+    op->set_streaming_memory_limit(bytes);
+    return SRB_OK;
+    SRB_API_END
+}
 srb_status srb_op_streaming_stats(srb_op* op, int64_t* rows_passed_through, int64_t* groups_in_table, int32_t* auto_state) {
     SRB_API_BEGIN
     OP_GUARD(op)

@@ -381,6 +381,7 @@ struct srb_op {
     virtual void push_pages(int32_t, const int32_t*, const srb_page_column*, int64_t) { throw srb::Error(SRB_NOT_IMPLEMENTED, "this operator does not take encoded pages"); }
     // streaming pre-aggregation (aggregate operators in the update+serialize phase only)
     virtual void set_streaming_mode(int) { throw srb::Error(SRB_INVALID_ARGUMENT, "not an aggregate operator"); }
+    virtual void set_streaming_memory_limit(int64_t) { throw srb::Error(SRB_INVALID_ARGUMENT, "not an aggregate operator"); }
     virtual void streaming_stats(int64_t*, int64_t*, int32_t*) { throw srb::Error(SRB_INVALID_ARGUMENT, "not an aggregate operator"); }
 };
 

@@ -2249,12 +2249,16 @@ private:
     enum RowMode { ROWS_AGGREGATE = STREAM_ROWS_AGGREGATE, ROWS_STREAM = STREAM_ROWS_PASS, ROWS_SELECTIVE = STREAM_ROWS_SELECTIVE };
 
     void set_streaming_mode(int mode) override {
-        if (mode < SRB_STREAMING_AUTO || mode > SRB_STREAMING_FORCE_PREAGGREGATION) throw Error(SRB_INVALID_ARGUMENT, "unknown streaming pre-aggregation mode");
+        if (mode < SRB_STREAMING_AUTO || mode > SRB_STREAMING_LIMITED_MEM) throw Error(SRB_INVALID_ARGUMENT, "unknown streaming pre-aggregation mode");
         if (rows_in > 0 || finishing) throw Error(SRB_INVALID_ARGUMENT, "the streaming mode is set before the first push_chunk");
         if (plan_.key_nodes.empty() || plan_.aggs.empty() || plan_.phase != SRB_AGG_UPDATE_SERIALIZE)
             throw Error(SRB_INVALID_ARGUMENT, "streaming pre-aggregation needs GROUP BY keys and the update + serialize phase");
         stream_mode_ = mode;
         if (getenv("SRB_STREAM_L2_BYTES")) policy_.l2_bytes = (size_t)atoll(getenv("SRB_STREAM_L2_BYTES")); // test hook: a small "L2"
+    }
+    void set_streaming_memory_limit(int64_t bytes) override {
+        if (bytes < 0) throw Error(SRB_INVALID_ARGUMENT, "negative memory limit");
+        stream_mem_limit_ = bytes;
     }
     void streaming_stats(int64_t* rows_passed_through, int64_t* groups_in_table, int32_t* auto_state) override {
         if (rows_passed_through) *rows_passed_through = stream_rows_;
@@ -2266,7 +2270,7 @@ private:
     // reduction is noticed after the first unit instead of after a whole 2^29-row batch. SRB_STREAM_UNIT: test hook.
     void stream_range(const ColBind* cols, int64_t n) {
         ensure_table();
-        const int64_t unit = stream_mode_ == SRB_STREAMING_AUTO ? stream_unit_ : AGG_BATCH;
+        const int64_t unit = (stream_mode_ == SRB_STREAMING_AUTO || stream_mode_ == SRB_STREAMING_LIMITED_MEM) ? stream_unit_ : AGG_BATCH;
         for (int64_t off = 0; off < n; off += unit) stream_batch(cols, off, std::min<int64_t>(unit, n - off));
     }
 
@@ -2300,7 +2304,7 @@ private:
         SRB_CUDA(cudaEventElapsedTime(&ms, ev0_, ev1_));
         kernel_ms_ += ms;
         timed_batches_++;
-        if (hc->key_too_long) throw Error(SRB_NOT_IMPLEMENTED, "serialized group key longer than 16 bytes");
+        if (hc->key_too_long) throw Error(SRB_NOT_IMPLEMENTED, "serialized group key longer than its key area (16 bytes, or the declared 17-64)");
         selected_total_ += hc->rows_selected;
         stream_rows_ += (int64_t)hc->emitted;
         return (int64_t)hc->inserted; // the stream kernel reports its hits there
@@ -2317,8 +2321,13 @@ private:
             run_rows(cols, off, n, ROWS_AGGREGATE);
             return;
         }
-        // AUTO: srb_stream_policy.h
         const size_t slot_bytes = (size_t)L_.prog.slot_bytes;
+        // LIMITED_MEM (_push_chunk_by_limited_memory): once the table has reached the limit every further row passes through
+        if (stream_mode_ == SRB_STREAMING_LIMITED_MEM && stream_mem_limit_ > 0 && (int64_t)((size_t)cap_ * slot_bytes) >= stream_mem_limit_) {
+            run_rows(cols, off, n, ROWS_STREAM);
+            return;
+        }
+        // AUTO: srb_stream_policy.h
         const StreamRowMode mode = policy_.next(n, occupied_, cap_, (size_t)cap_ * slot_bytes, rows_before, stream_rows_);
         const uint64_t sel0 = selected_total_;
         const int64_t hits = run_rows(cols, off, n, (RowMode)mode);
@@ -3080,6 +3089,7 @@ private:
     int64_t out_rows_ = 0, out_pos_ = 0;
     // streaming pre-aggregation sink
     int stream_mode_ = -1;    // -1: blocking sink; otherwise TStreamingPreaggregationMode
+    int64_t stream_mem_limit_ = 0; // LIMITED_MEM: bytes of group table from which on rows pass through (0: never)
     int64_t stream_rows_ = 0; // pass-through rows at the front of the output arrays
     int64_t stream_seen_ = 0; // input rows the sink has been handed
     int64_t stream_unit_ = getenv("SRB_STREAM_UNIT") ? std::max<int64_t>(1, atoll(getenv("SRB_STREAM_UNIT"))) : ((int64_t)1 << 24);

@@ -30,7 +30,7 @@ EXPORTS = [
     "srb_device_alloc", "srb_device_free", "srb_pinned_alloc", "srb_pinned_free", "srb_memcpy_h2d", "srb_memcpy_d2h",
     "srb_partition_create", "srb_partition_run", "srb_partition_destroy", "srb_partition_run_noalloc",
     "srb_comm_unique_id", "srb_comm_create", "srb_comm_destroy", "srb_comm_abort", "srb_comm_check", "srb_comm_stream", "srb_comm_all_to_all", "srb_comm_all_gather", "srb_comm_shuffle", "srb_comm_counters", "srb_comm_merge_runtime_filter",
-    "srb_join_build_runtime_filter", "srb_op_add_runtime_filter", "srb_op_set_streaming_mode", "srb_op_streaming_stats", "srb_topn_create", "srb_runtime_filter_info", "srb_runtime_filter_directory", "srb_runtime_filter_destroy",
+    "srb_join_build_runtime_filter", "srb_op_add_runtime_filter", "srb_op_set_streaming_mode", "srb_op_set_streaming_memory_limit", "srb_op_streaming_stats", "srb_topn_create", "srb_runtime_filter_info", "srb_runtime_filter_directory", "srb_runtime_filter_destroy",
 ]
 
 
@@ -109,6 +109,7 @@ def lib() -> C.CDLL:
     L.srb_join_build_runtime_filter.argtypes = [vp, C.c_int32, i64, C.c_int32, C.POINTER(vp)]
     L.srb_op_add_runtime_filter.argtypes = [vp, vp, C.c_int32]
     L.srb_op_set_streaming_mode.argtypes = [vp, C.c_int32]
+    L.srb_op_set_streaming_memory_limit.argtypes = [vp, C.c_int64]
     L.srb_op_streaming_stats.argtypes = [vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
     L.srb_runtime_filter_info.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), C.POINTER(C.c_int32), C.POINTER(i64)]
     L.srb_runtime_filter_directory.argtypes = [vp, vp, i64]
@@ -343,6 +344,10 @@ class ScanAggOperator(_Operator):
         """first phase of a two-phase GROUP BY as a streaming sink (AggregateStreamingSinkOperator): capi.STREAMING_AUTO /
         STREAMING_FORCE_STREAMING / STREAMING_FORCE_PREAGGREGATION (TStreamingPreaggregationMode); before the first push_chunk"""
         _check(self.L.srb_op_set_streaming_mode(self.h, mode))
+
+    def set_streaming_memory_limit(self, nbytes: int):
+        """STREAMING_LIMITED_MEM: bytes of group table from which on every row passes through (LimitedMemAggState)"""
+        _check(self.L.srb_op_set_streaming_memory_limit(self.h, nbytes))
 
     def streaming_stats(self):
         a, b, c = C.c_int64(), C.c_int64(), C.c_int32()

@@ -74,3 +74,32 @@ def test_force_streaming_with_group_keys_beyond_16_bytes(ctx, oracle):
     got, st = _stream_gpu(ctx, plan, ch, K.STREAMING_FORCE_STREAMING, 4096)
     assert got.n_rows == want.n_rows and st["groups"] == 0
     assert K.chunk_rows(got) == K.chunk_rows(want)
+
+
+def test_limited_memory_mode_streams_once_the_table_has_reached_the_limit(ctx, oracle, monkeypatch):
+    # _push_chunk_by_limited_memory (aggregate_streaming_sink_operator.cpp:311-319): AUTO below the limit, FORCE_STREAMING from it on;
+    # phase 2 over the sink's output equals the one-phase result either way
+    from starrocks_b200 import ops
+    from tests.test_gpu_parity import run_gpu
+    from tests.test_streaming_cpu import hc_chunk
+    monkeypatch.setenv("SRB_STREAM_UNIT", "4096")
+    rng = np.random.default_rng(23)
+    keys = rng.integers(0, 40_000, 200_000)
+    ch = hc_chunk(keys, rng.integers(-10**9, 10**9, len(keys)), (rng.random(len(keys)) < 0.05).astype(np.uint8))
+    want = K.chunk_rows(oracle.scan_agg(Q.highcard_plan(), ch))
+    seen = {}
+    for limit in (0, 1 << 40, 64 << 10):  # never limited, far above the table, reached after a few thousand groups
+        op = ops.ScanAggOperator(ctx, Q.highcard_plan(phase=K.AGG_UPDATE_SERIALIZE))
+        op.set_streaming_mode(K.STREAMING_LIMITED_MEM)
+        op.set_streaming_memory_limit(limit)
+        for a in range(0, ch.n_rows, 65536):
+            op.push_chunk(ops.slice_chunk(ch, a, min(ch.n_rows, a + 65536)))
+        op.set_finishing()
+        inter = op.pull_all()
+        st = op.streaming_stats()
+        op.close()
+        assert st["rows_streamed"] + st["groups"] == inter.n_rows
+        seen[limit] = st
+        assert K.chunk_rows(run_gpu(ctx, Q.highcard_merge_plan(), inter)) == want
+    assert seen[0] == seen[1 << 40]  # both are plain AUTO
+    assert seen[64 << 10]["rows_streamed"] > seen[0]["rows_streamed"] and seen[64 << 10]["groups"] * 32 <= 4 * (64 << 10)
