@@ -56,9 +56,13 @@ inline bool jit_node_can_be_null(const JitShape& js, int n) {
 }
 inline int jit_plane_kind(const JitShape& js, int a) {
     const SAgg& g = js.aggs[a];
-    if (g.fn == FN_SUM || g.fn == FN_AVG) return 1;
+    if (g.fn == FN_SUM || g.fn == FN_AVG) return g.dbl != 0 ? 3 : 1;
     if (g.fn == FN_COUNT) return (g.merge == 0 && g.arg >= 0 && jit_node_can_be_null(js, g.arg)) ? 1 : 0;
     return 2;
+}
+inline bool jit_same_plane(const JitShape& js, int a, int b) { // do two sum aggregates share an accumulator plane?
+    const int ka = jit_plane_kind(js, a);
+    return (ka == 1 || ka == 3) && jit_plane_kind(js, b) == ka && js.aggs[a].arg == js.aggs[b].arg && (ka == 1 || js.aggs[a].dbl == js.aggs[b].dbl);
 }
 inline int jit_n_reps(const JitShape& js) {
     int n = 0;
@@ -66,8 +70,8 @@ inline int jit_n_reps(const JitShape& js) {
         const int kind = jit_plane_kind(js, a);
         if (kind == 0) continue;
         bool first = true;
-        for (int b = 0; kind == 1 && b < a; b++)
-            if (jit_plane_kind(js, b) == 1 && js.aggs[b].arg == js.aggs[a].arg) first = false;
+        for (int b = 0; b < a; b++)
+            if (jit_same_plane(js, a, b)) first = false;
         n += first ? 1 : 0;
     }
     return n;
@@ -85,8 +89,8 @@ inline int jit_n_cnt(const JitShape& js) { // planes that count the rows they to
         const int kind = jit_plane_kind(js, a);
         if (kind == 0 || !jit_node_reads_nullable(js, js.aggs[a].arg)) continue;
         bool first = true;
-        for (int b = 0; kind == 1 && b < a; b++)
-            if (jit_plane_kind(js, b) == 1 && js.aggs[b].arg == js.aggs[a].arg) first = false;
+        for (int b = 0; b < a; b++)
+            if (jit_same_plane(js, a, b)) first = false;
         n += first ? 1 : 0;
     }
     return n;
@@ -114,18 +118,18 @@ inline bool jit_shape_of(const DProg& p, int group_hint, const bool* col_nullabl
             row_bytes += 12 + (col_nullable && col_nullable[c] ? 1 : 0);
             continue;
         }
-        if (p.cols[c].kind != CK_INT || p.cols[c].width < 1 || p.cols[c].width > 16) return false;
+        if ((p.cols[c].kind != CK_INT && p.cols[c].kind != CK_DOUBLE) || p.cols[c].width < 1 || p.cols[c].width > 16) return false;
         row_bytes += p.cols[c].width + (col_nullable && col_nullable[c] ? 1 : 0);
     }
     for (int i = 0; i < p.n_preds; i++)
-        if (binary_col[p.preds[i].col]) return false; // string predicates: the interpreter's
+        if (p.cols[p.preds[i].col].kind != CK_INT) return false; // string / DOUBLE predicates: the interpreter's
     bool col_seen[MAX_COLS] = {};
     for (int i = 0; i < p.n_nodes; i++) {
         const DNode& d = p.nodes[i];
         if (d.op < DOP_LOAD || d.op > DOP_MULFAST) return false;
         if (d.op == DOP_LOAD) {
             if (d.col < 0 || d.col >= p.n_cols || col_seen[d.col]) return false; // one LOAD per column
-            if (binary_col[d.col] ? d.kind != CK_BINARY : (d.kind != CK_INT || p.cols[d.col].width != d.width)) return false;
+            if (binary_col[d.col] ? d.kind != CK_BINARY : (d.kind != p.cols[d.col].kind || p.cols[d.col].width != d.width)) return false; // (DOUBLE: an aggregate argument only)
             col_seen[d.col] = true;
         } else if (d.kind != CK_INT) {
             return false;
@@ -141,19 +145,20 @@ inline bool jit_shape_of(const DProg& p, int group_hint, const bool* col_nullabl
     for (int a = 0; a < p.n_aggs; a++) {
         const DAgg& d = p.aggs[a];
         if (d.fn < FN_SUM || d.fn > FN_MAX) return false;
-        if (d.is_double || d.avg_as_double) return false;
-        if ((d.fn == FN_MIN || d.fn == FN_MAX) && (d.wide || d.arg < 0 || p.nodes[d.arg].width > 8)) return false;
+        if ((d.fn == FN_MIN || d.fn == FN_MAX) && ((d.wide && !d.is_double) || d.arg < 0 || p.nodes[d.arg].width > 8)) return false;
+        if (d.arg >= 0 && d.fn != FN_COUNT && (p.nodes[d.arg].kind == CK_DOUBLE) != (d.is_double != 0)) return false;
+        if (d.avg_as_double && d.fn != FN_AVG) return false;
         if (d.merge && d.fn == FN_AVG) return false; // {sum, count} blobs: the interpreter's job
         if (d.fn != FN_COUNT && (d.arg < 0 || d.arg >= p.n_nodes)) return false;
         if (d.arg >= p.n_nodes) return false;
-        if (d.arg >= 0 && p.nodes[d.arg].kind != CK_INT) return false;
-        js.aggs[a] = SAgg{d.fn, d.arg, d.off_hi >= 0 ? 1 : 0, d.off_n >= 0 ? 1 : 0, d.merge ? 1 : 0};
+        if (d.arg >= 0 && p.nodes[d.arg].kind == CK_BINARY) return false;
+        js.aggs[a] = SAgg{d.fn, d.arg, d.off_hi >= 0 ? 1 : 0, d.off_n >= 0 ? 1 : 0, d.merge ? 1 : 0, d.fn == FN_COUNT ? 0 : (d.is_double ? 1 : (d.avg_as_double ? 2 : 0))};
     }
     int key_bytes = 0;
     for (int k = 0; k < p.n_keys; k++) {
         const DKey& d = p.keys[k];
         if (p.n_keys > 4 || d.width < 0 || d.width > 8 || d.node < 0 || d.node >= p.n_nodes || p.nodes[d.node].op != DOP_LOAD) return false;
-        if ((d.width == 0) != (p.nodes[d.node].kind == CK_BINARY)) return false;
+        if ((d.width == 0) != (p.nodes[d.node].kind == CK_BINARY) || p.nodes[d.node].kind == CK_DOUBLE) return false;
         js.keys[k] = SKey{d.node, d.width, d.nullable ? 1 : 0};
         key_bytes += (d.width ? d.width : 4) + (d.nullable ? 1 : 0);
     }
@@ -223,7 +228,7 @@ inline std::string jit_source(const JitShape& js) {
     s += "        };\n        return t[i];\n    }\n    static constexpr SAgg agg(int i) {\n        constexpr SAgg t[N_AGGS] = {\n";
     for (int a = 0; a < js.n_aggs; a++) {
         const SAgg& g = js.aggs[a];
-        snprintf(buf, sizeof buf, "            {%d, %d, %d, %d, %d},\n", g.fn, g.arg, g.wide, g.has_n, g.merge);
+        snprintf(buf, sizeof buf, "            {%d, %d, %d, %d, %d, %d},\n", g.fn, g.arg, g.wide, g.has_n, g.merge, g.dbl);
         s += buf;
     }
     s += "        };\n        return t[i];\n    }\n    static constexpr SKey key(int i) {\n";

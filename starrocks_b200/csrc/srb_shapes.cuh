@@ -45,6 +45,8 @@ struct SNode {
 struct SAgg {
     int fn, arg, wide, has_n; // wide: state keeps the high word (off_hi >= 0); has_n: state keeps its own count
     int merge = 0;            // phase-2 aggregate over an intermediate column (COUNT adds the partial count)
+    int dbl = 0;              // 1: the argument is a DOUBLE (the state holds a double), 2: an integer argument accumulated in double (AVG over plain
+                              // integers, avg.h:49-53)
 };
 struct SKey {
     int node, width;
@@ -562,15 +564,16 @@ constexpr bool node_can_be_null(int n) {
 template <class S>
 constexpr int plane_kind(int a) {
     const SAgg g = S::agg(a);
-    if (g.fn == FN_SUM || g.fn == FN_AVG) return 1;
+    if (g.fn == FN_SUM || g.fn == FN_AVG) return g.dbl != 0 ? 3 : 1; // kind 3: a sum kept as a double (no spill word, no carries)
     if (g.fn == FN_COUNT) return (g.merge == 0 && g.arg >= 0 && node_can_be_null<S>(g.arg)) ? 1 : 0;
     return 2;
 }
 template <class S>
 constexpr int agg_rep(int a) {
-    if (plane_kind<S>(a) != 1) return a;
+    const int kind = plane_kind<S>(a);
+    if (kind != 1 && kind != 3) return a;
     for (int b = 0; b < a; b++)
-        if (plane_kind<S>(b) == 1 && S::agg(b).arg == S::agg(a).arg) return b;
+        if (plane_kind<S>(b) == kind && S::agg(b).arg == S::agg(a).arg && (kind == 1 || S::agg(b).dbl == S::agg(a).dbl)) return b;
     return a;
 }
 // dense index of a representative among the representatives (its accumulator plane), and their number
@@ -609,6 +612,13 @@ constexpr int cnt_index(int a) {
 template <class S>
 constexpr int n_cnt() {
     return cnt_index<S>(S::N_AGGS);
+}
+// a double-sum plane?
+template <class S>
+constexpr bool plane_is_dbl(int ri) {
+    for (int a = 0; a < S::N_AGGS; a++)
+        if (plane_kind<S>(a) == 3 && agg_rep<S>(a) == a && rep_index<S>(a) == ri) return true;
+    return false;
 }
 // is plane ri a max plane? (fold() walks the planes by index)
 template <class S>
@@ -687,8 +697,24 @@ SRB_D void acc_one(uint8_t* a, uint8_t* c, uint8_t* trash, const Val* v, bool on
             if constexpr (!plane_counts<S>(A)) any_null = any_null || (on && x.null);
         }
         uint64_t* slot = (uint64_t*)(take ? a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8 : trash);
-        const uint64_t e = enc_i64((int64_t)x.lo, g.fn == FN_MIN), cur = *slot;
+        const uint64_t e = g.dbl != 0 ? enc_f64(x.lo, g.fn == FN_MIN) : enc_i64((int64_t)x.lo, g.fn == FN_MIN), cur = *slot;
         *slot = e > cur ? e : cur;
+        dh[RI] = 0;
+        if constexpr (plane_counts<S>(A)) {
+            uint32_t* tc = (uint32_t*)(take ? c + (size_t)cnt_index<S>(A) * AccGeom<S>::G * S::THREADS * 4 : trash);
+            *tc += 1u;
+        }
+    } else if constexpr (plane_kind<S>(A) == 3 && agg_rep<S>(A) == A) {
+        constexpr int RI = rep_index<S>(A);
+        const Val& x = v[g.arg];
+        bool take = on;
+        if constexpr (node_can_be_null<S>(g.arg)) {
+            take = on && !x.null;
+            if constexpr (!plane_counts<S>(A)) any_null = any_null || (on && x.null);
+        }
+        uint64_t* slot = (uint64_t*)(take ? a + (size_t)RI * AccGeom<S>::G * S::THREADS * 8 : trash);
+        const double val = g.dbl == 1 ? __longlong_as_double((long long)x.lo) : (double)(int64_t)x.lo;
+        *slot = (uint64_t)__double_as_longlong(__longlong_as_double((long long)*slot) + val);
         dh[RI] = 0;
         if constexpr (plane_counts<S>(A)) {
             uint32_t* tc = (uint32_t*)(take ? c + (size_t)cnt_index<S>(A) * AccGeom<S>::G * S::THREADS * 4 : trash);
@@ -781,7 +807,7 @@ constexpr bool shape_has_narrow() {
     }
     for (int a = 0; a < S::N_AGGS; a++) {
         const SAgg g = S::agg(a);
-        if (g.merge != 0) return false;
+        if (g.merge != 0 || g.dbl != 0) return false;
         // every function qualifies: under the narrow assumption nothing is NULL, so COUNT(x) is the row count, and MIN / MAX arguments are
         // 8-byte values in [0, 2^63)
         if ((g.fn == FN_MIN || g.fn == FN_MAX) && S::node(g.arg).width != 8) return false;
@@ -1043,6 +1069,12 @@ struct Flusher {
                     const uint64_t y = __shfl_xor_sync(0xffffffffu, lo, o);
                     lo = y > lo ? y : lo;
                 }
+            } else if constexpr (plane_kind<S>(A) == 3) {
+                double sum = __longlong_as_double((long long)w);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                lo = (uint64_t)__double_as_longlong(sum);
+                hi = 0;
             } else {
                 lo = w + ra.lo[q * NR + RI];
                 hi = ra.hi[q * NR + RI] + (lo < w ? 1ULL : 0ULL);
@@ -1086,6 +1118,8 @@ struct Flusher {
                 } else {
                     if constexpr (plane_kind<S>(A) == 2)
                         atomicMax((unsigned long long*)(slot + rt.off_lo), (unsigned long long)tot[RI * 3 + 0]);
+                    else if constexpr (plane_kind<S>(A) == 3)
+                        atomicAdd((double*)(slot + rt.off_lo), __longlong_as_double((long long)tot[RI * 3 + 0]));
                     else
                         atomic_add128(slot, rt.off_lo, rt.off_hi, tot[RI * 3 + 0], tot[RI * 3 + 1]);
                     if (rt.off_n >= 0) atomicAdd((unsigned long long*)(slot + rt.off_n), (unsigned long long)n);
@@ -1100,6 +1134,8 @@ struct Flusher {
     static __device__ __forceinline__ void fold_plane(uint64_t* tot, const uint64_t* st) {
         if constexpr (plane_is_max<S>(RI)) {
             tot[RI * 3] = st[RI * 3] > tot[RI * 3] ? st[RI * 3] : tot[RI * 3];
+        } else if constexpr (plane_is_dbl<S>(RI)) {
+            tot[RI * 3] = (uint64_t)__double_as_longlong(__longlong_as_double((long long)tot[RI * 3]) + __longlong_as_double((long long)st[RI * 3]));
         } else {
             const uint64_t lo = tot[RI * 3] + st[RI * 3];
             tot[RI * 3 + 1] += st[RI * 3 + 1] + (lo < st[RI * 3] ? 1ULL : 0ULL);
@@ -1141,7 +1177,10 @@ SRB_D void row_update_global_one(const DProg& p, uint8_t* slot, const Val* v) {
         const Val& x = v[g.arg];
         if (!x.null) {
             if constexpr (g.fn == FN_MIN || g.fn == FN_MAX)
-                atomicMax((unsigned long long*)(slot + rt.off_lo), (unsigned long long)enc_i64((int64_t)x.lo, g.fn == FN_MIN));
+                atomicMax((unsigned long long*)(slot + rt.off_lo),
+                          (unsigned long long)(g.dbl != 0 ? enc_f64(x.lo, g.fn == FN_MIN) : enc_i64((int64_t)x.lo, g.fn == FN_MIN)));
+            else if constexpr (g.dbl != 0)
+                atomicAdd((double*)(slot + rt.off_lo), g.dbl == 1 ? __longlong_as_double((long long)x.lo) : (double)(int64_t)x.lo);
             else
                 atomic_add128(slot, rt.off_lo, rt.off_hi, x.lo, (uint64_t)x.hi);
             if (rt.off_n >= 0) atomicAdd((unsigned long long*)(slot + rt.off_n), 1ULL);
@@ -1317,7 +1356,10 @@ SRB_D void row_update_args_one(const DProg& p, uint8_t* slot, const AggArgs<S>& 
     } else {
         if (!null) {
             if constexpr (g.fn == FN_MIN || g.fn == FN_MAX)
-                atomicMax((unsigned long long*)(slot + rt.off_lo), (unsigned long long)enc_i64((int64_t)x.lo[A], g.fn == FN_MIN));
+                atomicMax((unsigned long long*)(slot + rt.off_lo),
+                          (unsigned long long)(g.dbl != 0 ? enc_f64(x.lo[A], g.fn == FN_MIN) : enc_i64((int64_t)x.lo[A], g.fn == FN_MIN)));
+            else if constexpr (g.dbl != 0)
+                atomicAdd((double*)(slot + rt.off_lo), g.dbl == 1 ? __longlong_as_double((long long)x.lo[A]) : (double)(int64_t)x.lo[A]);
             else
                 atomic_add128(slot, rt.off_lo, rt.off_hi, x.lo[A], (uint64_t)x.hi[A]);
             if (rt.off_n >= 0) atomicAdd((unsigned long long*)(slot + rt.off_n), 1ULL);
