@@ -97,6 +97,24 @@ def test_generated_shapes_compile_without_a_gpu(no_disk_cache, name):
     assert st["failed"] == 0 and st["pending"] == 0, st
 
 
+def test_every_shape_family_of_the_gpu_tests_compiles_without_a_gpu(no_disk_cache):
+    # what the GPU parity cases below run is generated and compiled here as well: null-map variants, MIN / MAX, VARCHAR keys (offsets +
+    # byte window), DOUBLE aggregates, table-path and directory geometries
+    from starrocks_b200 import ops
+    first = T.host_chunk("lineitem", 0, 16, T.LINEITEM_Q1)
+    nul = K.Chunk(16, dict(first.columns))
+    for slot in (Q.L_QUANTITY, Q.L_DISCOUNT, Q.L_RETURNFLAG_CODE):
+        c = first.columns[slot]
+        nul.columns[slot] = K.Column(c.type, c.data, np.zeros(16, np.uint8), None, c.precision, c.scale)
+    cases = [(Q.q1_plan(with_min_max=True), first), (Q.q1_plan(with_min_max=True), nul), (lineitem_plan(hint=12), nul), (lineitem_plan(n_keys=0), nul),
+             (string_key_plan(4), string_key_chunk(16, lambda r, i: b"ab")), (string_key_plan(50_000, True), string_key_chunk(16, lambda r, i: b"k", 0.3, second_int_key=True)),
+             (double_plan(0, 4), double_chunk(16)), (double_plan(4, 100_000), double_chunk(16)), (double_plan(None, 0), double_chunk(16))]
+    for plan, chunk in cases:
+        assert ops.jit_check_plan(plan, chunk).startswith("compiled shape")
+    st = ops.jit_stats()
+    assert st["failed"] == 0 and st["pending"] == 0, st
+
+
 def test_builtin_shapes_are_recognised_and_uncovered_plans_are_refused(no_disk_cache):
     from starrocks_b200 import ops
     first = T.host_chunk("lineitem", 0, 16, T.LINEITEM_Q1)
