@@ -1506,7 +1506,11 @@ struct HostCol { // result column handed out by pull_chunk (host memory owned by
 
 // SRB_TRACE=1: host-side wall time of the stages of a push / set_finishing on stderr (a diagnostic, off by default)
 struct HostTrace {
-    bool on = getenv("SRB_TRACE") != nullptr;
+    bool on = enabled();
+    static bool enabled() { // read once per process: a trace object is made per push / launch
+        static const bool e = getenv("SRB_TRACE") != nullptr;
+        return e;
+    }
     std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
     void mark(const char* what) {
         if (!on) return;
@@ -2605,7 +2609,7 @@ private:
         const DProg& P = L_.prog;
         // predicates that lower to ranges over NULL-free, 16-byte aligned 4- / 8-byte columns take the vectorised mask kernel
         FRangeArgs fa{};
-        bool fast = !getenv("SRB_NO_FAST_FILTER");
+        bool fast = !no_fast_filter_;
         if (fast) {
             StaticArgs sa{};
             for (int c = 0; c < MAX_COLS; c++) {
@@ -3032,6 +3036,7 @@ private:
         return (!strcmp(m, "off") || !strcmp(m, "0")) ? 0 : 1;
     }
     bool force_generic_ = getenv("SRB_FORCE_GENERIC") != nullptr; // test hook: compare the two kernel families
+    bool no_fast_filter_ = getenv("SRB_NO_FAST_FILTER") != nullptr; // test hook: the per-row mask kernel for every filter-only plan
     bool no_narrow_ = getenv("SRB_NO_NARROW") != nullptr;         // test / measurement hook: the static kernels' general tile body only
     bool rf_fused_ = getenv("SRB_RF_FUSED") != nullptr;           // opt-in: all runtime filters of a scan in one kernel (k_filter_rf_multi)
     // k_scan_agg_lowcard measured SLOWER than the shared mirror on a B200 (Q1 with VARCHAR keys: 92 vs 49 ms per 134 M rows — its
