@@ -136,13 +136,18 @@ public:
         if (_op) return Status::OK();
         const srb_scan_agg_plan p = _plan.c_plan();
         SRB_RETURN_IF_ERROR(srb_to_status(srb_scan_agg_create(_ctx, &p, &_op)));
-        if (_streaming_mode >= 0) return srb_to_status(srb_op_set_streaming_mode(_op, _streaming_mode));
+        if (_streaming_mode >= 0) {
+            SRB_RETURN_IF_ERROR(srb_to_status(srb_op_set_streaming_mode(_op, _streaming_mode)));
+            if (_streaming_mode == SRB_STREAMING_LIMITED_MEM) return srb_to_status(srb_op_set_streaming_memory_limit(_op, _streaming_memory_limit));
+        }
         return Status::OK();
     }
     // AggregateStreamingSinkOperator in place of the blocking sink (the first phase of a two-phase aggregation in front of an
     // exchange): TAggregationNode::streaming_preaggregation_mode (gensrc/thrift/PlanNodes.thrift:851) picks how rows meet the table.
     // Call before prepare(); the plan must be in SRB_AGG_UPDATE_SERIALIZE with GROUP BY keys.
     void set_streaming_preaggregation_mode(int32_t mode) { _streaming_mode = mode; }
+    // LimitedMemAggState::limited_memory_size (exec/aggregator.h:209-212) for SRB_STREAMING_LIMITED_MEM: bytes of group table
+    void set_streaming_memory_limit(int64_t bytes) { _streaming_memory_limit = bytes; }
     // the scan waits for the joins whose runtime filters it applies (Operator::set_precondition_ready, operator.h:185): no input is
     // taken before every such build side has finished; the filters are attached right before the first chunk
     void wait_for_runtime_filter(std::shared_ptr<class GpuHashJoiner> joiner, int32_t slot_id);
@@ -189,6 +194,7 @@ private:
     bool _rf_attached = false;
     int64_t _rows_selected = 0;
     int32_t _streaming_mode = -1; // -1: blocking sink
+    int64_t _streaming_memory_limit = 0;
 };
 
 // ---- TopN: PartitionSortSinkOperator + LocalMergeSortSourceOperator over a ChunksSorterTopn, as one operator ---------------------
@@ -252,6 +258,7 @@ struct JoinPlan {
     int32_t join_type = SRB_JOIN_INNER;
     std::vector<int32_t> build_key_slots, probe_key_slots, build_out_slots, probe_out_slots;
     bool emit_indexes = false;
+    std::vector<srb_join_conjunct> conjuncts; // HashJoiner::_other_join_conjunct_ctxs of an INNER join as column-to-column comparisons
     srb_join_plan c_plan() const {
         srb_join_plan p{};
         p.join_type = join_type;
@@ -263,6 +270,8 @@ struct JoinPlan {
         p.n_probe_out = (int32_t)probe_out_slots.size();
         p.probe_out_slots = probe_out_slots.data();
         p.emit_indexes = emit_indexes ? 1 : 0;
+        p.n_conjuncts = (int32_t)conjuncts.size();
+        p.conjuncts = conjuncts.empty() ? nullptr : conjuncts.data();
         return p;
     }
 };
@@ -284,9 +293,12 @@ public:
     // HashJoiner::create_runtime_filters (hash_joiner.cpp:516-611): called by the build operator's set_finishing when the plan
     // asks for a runtime filter on build key `runtime_filter_key` (-1: none). The probe-side scan picks it up with runtime_filter().
     int runtime_filter_key = -1;
+    // PartialRuntimeFilterMerger's maybe_use_bitset_filter (exec/pipeline/runtime_filter_types.cpp:149-152): set for broadcast joins, where
+    // this joiner holds the whole build side and create_join_runtime_filter's rule may pick a RuntimeBitsetFilter
+    bool maybe_use_bitset_filter = false;
     Status create_runtime_filter() {
         if (runtime_filter_key < 0 || _rf) return Status::OK();
-        return srb_to_status(srb_join_build_runtime_filter(_op, runtime_filter_key, 0, /*hash_mix=*/0, &_rf));
+        return srb_to_status(srb_join_build_runtime_filter(_op, runtime_filter_key, 0, maybe_use_bitset_filter ? SRB_RF_MAYBE_BITSET : 0, &_rf));
     }
     const srb_runtime_filter* runtime_filter() const { return _rf; }
 
