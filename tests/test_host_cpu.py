@@ -52,6 +52,23 @@ def test_struct_sizes_match_the_header():
     assert C.sizeof(K.srb_config) == 32
 
 
+def test_ctypes_mirrors_have_the_sizes_the_c_compiler_gives_the_header(tmp_path):
+    # sizeof of every POD of include/srb/srb_c_api.h as gcc lays it out, against the ctypes mirrors the Python host side passes
+    import subprocess
+    from starrocks_b200 import pages as PG
+    mirrors = {"srb_column": K.srb_column, "srb_chunk": K.srb_chunk, "srb_predicate": K.srb_predicate, "srb_expr_node": K.srb_expr_node,
+               "srb_agg_fn": K.srb_agg_fn, "srb_config": K.srb_config, "srb_scan_agg_plan": K.srb_scan_agg_plan, "srb_join_plan": K.srb_join_plan,
+               "srb_join_conjunct": K.srb_join_conjunct, "srb_topn_plan": K.srb_topn_plan, "srb_page": PG.srb_page, "srb_page_column": PG.srb_page_column}
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "srb/srb_c_api.h"\nint main(void) {\n' +
+                   "".join(f'    printf("{n} %zu\\n", sizeof({n}));\n' for n in mirrors) + "    return 0;\n}\n")
+    exe = tmp_path / "sizes"
+    subprocess.check_call(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    got = dict(line.split() for line in subprocess.check_output([str(exe)], text=True).splitlines())
+    for n, cls in mirrors.items():
+        assert int(got[n]) == C.sizeof(cls), (n, got[n], C.sizeof(cls))
+
+
 def test_from_date_matches_oracle(oracle):
     for y, m, d in [(1970, 1, 1), (1992, 1, 2), (1994, 1, 1), (1995, 3, 15), (1998, 9, 2), (2000, 2, 29), (1000, 1, 1)]:
         assert Q.from_date(y, m, d) == oracle.lib.orc_from_date(y, m, d)
